@@ -1,0 +1,140 @@
+/*
+ * b200jpeg.h -- plain C ABI of the B200-native batched baseline-JPEG decoder.
+ *
+ * This is the boundary a foreign-language binding (ctypes, cgo, JNI ...) links
+ * against: plain pointers and sizes, no C++ or torch types.  The nvImageCodec
+ * extension entry point (nvimgcodecExtensionModuleEntry, exported by the same
+ * shared object) is a thin adapter over these calls; see INTEGRATION.md.
+ *
+ * Each declaration cites the reference interface it stands in for
+ * (paths relative to NVIDIA/nvImageCodec v0.8.0).
+ */
+#ifndef B200JPEG_H_
+#define B200JPEG_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B200JPEG_API __attribute__((visibility("default")))
+#else
+#define B200JPEG_API
+#endif
+
+typedef struct b200jpegDecoder_st* b200jpegDecoder_t;
+
+/* status codes (per call and per image) */
+enum {
+    B200JPEG_OK = 0,
+    B200JPEG_ERR_ARG = 1,
+    B200JPEG_ERR_NOT_JPEG = 2,
+    B200JPEG_ERR_UNSUPPORTED = 3, /* valid JPEG outside the baseline subset this decoder handles */
+    B200JPEG_ERR_CORRUPT = 4,     /* header or entropy data damaged */
+    B200JPEG_ERR_CUDA = 5,
+    B200JPEG_ERR_STATE = 6,
+    B200JPEG_ERR_TOO_LARGE = 7
+};
+
+/* output sample formats; mirror nvimgcodecSampleFormat_t subsets accepted by the
+ * reference CPU decoder (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:165-178). */
+enum {
+    B200JPEG_FMT_I_RGB = 0,
+    B200JPEG_FMT_I_BGR = 1,
+    B200JPEG_FMT_P_RGB = 2,
+    B200JPEG_FMT_P_BGR = 3,
+    B200JPEG_FMT_Y = 4 /* single plane: P_Y / I_Y */
+};
+
+/* What the host marker walk found.  Superset of what the reference's header
+ * parser reports (src/parsers/jpeg.cpp:238-404: dims, components, sampling, SOF). */
+typedef struct {
+    int width, height, num_components;
+    int h[4], v[4];          /* sampling factors per component */
+    int sof_marker;          /* 0xC0 baseline, 0xC2 progressive ... */
+    int precision;
+    int restart_interval;    /* in MCUs, 0 = none */
+    int num_scans_seen;      /* 1 for single interleaved scan */
+    int supported;           /* 1 if b200jpegDecodeBatch accepts the stream */
+    int reason;              /* B200JPEG_* explaining supported == 0 */
+    uint64_t scan_offset;    /* first entropy-coded byte */
+    uint64_t scan_length;    /* entropy-coded bytes (byte-stuffed, markers included, EOI excluded) */
+    int mcus_x, mcus_y, blocks_per_mcu;
+} b200jpegStreamInfo_t;
+
+/* Where and how one image is written.  Stands in for the nvimgcodecImageInfo_t the
+ * plugin reads per sample (include/nvimgcodec.h:538-559) plus the ROI from
+ * nvimgcodecCodeStreamView_t::region (include/nvimgcodec.h:503-521; start/end are [y,x]). */
+typedef struct {
+    void* buffer;       /* device pointer on the decoder's GPU, or host pointer if buffer_is_host */
+    int format;         /* B200JPEG_FMT_* */
+    int buffer_is_host; /* 0 = device (kernels store straight into it), 1 = host (decoder bounces + D2H) */
+    size_t row_stride;  /* bytes per row of a plane; 0 = tight */
+    int roi_x0, roi_y0, roi_x1, roi_y1; /* all zero = full image; else [x0,x1) x [y0,y1) inside the image */
+} b200jpegOutput_t;
+
+/* Host-only marker walk (SOI .. SOS): tables present, sampling, restart interval,
+ * scan extent.  Replaces the acceptance predicate of
+ * extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:110-212 (canDecode) for the
+ * stream-dependent part; never touches the GPU. */
+B200JPEG_API int b200jpegProbe(const void* data, size_t length, b200jpegStreamInfo_t* info);
+
+/* Create / destroy a decoder bound to one GPU.  options is the nvImageCodec
+ * option string ("<id>:<name>=<value>" tokens, include/nvimgcodec.h:1967-1971);
+ * understood: fancy_upsampling=<0|1> (default 1, as libjpeg_turbo_decoder.cpp:223-249).
+ * Replaces nvimgcodecDecoderDesc_t::create / destroy (include/nvimgcodec.h:1466-1482). */
+B200JPEG_API int b200jpegCreate(b200jpegDecoder_t* decoder, int device_id, const char* options);
+B200JPEG_API int b200jpegDestroy(b200jpegDecoder_t decoder);
+
+/* Decode a batch: host bitstreams in, pixels out (device or host buffers).
+ * Replaces nvimgcodecDecoderDesc_t::decodeBatch (include/nvimgcodec.h:1519-1533) /
+ * DecoderImpl::decode (libjpeg_turbo_decoder.cpp:295-420).  status[i] receives
+ * B200JPEG_* per image.  cuda_stream is a cudaStream_t.  The call returns after the
+ * stream has been synchronised, so statuses reflect entropy-decode errors too. */
+B200JPEG_API int b200jpegDecodeBatch(b200jpegDecoder_t decoder, int batch_size, const void* const* data, const size_t* lengths,
+    const b200jpegOutput_t* outputs, int* status, void* cuda_stream);
+
+/* The same work split in three so callers can overlap and so the device-resident
+ * part can be timed on its own:
+ *   Prepare : host marker walk, staging, async H2D of bitstreams and descriptors
+ *   Execute : the CUDA kernels only (everything already in HBM); asynchronous
+ *   Finish  : synchronise, run the rare re-synchronisation path, D2H of host outputs, statuses
+ * Prepare/Execute/Finish must be called in that order on one decoder; Execute may be
+ * repeated on the same prepared batch (it is idempotent). */
+B200JPEG_API int b200jpegPrepareBatch(b200jpegDecoder_t decoder, int batch_size, const void* const* data, const size_t* lengths,
+    const b200jpegOutput_t* outputs, void* cuda_stream);
+B200JPEG_API int b200jpegExecuteBatch(b200jpegDecoder_t decoder, void* cuda_stream);
+B200JPEG_API int b200jpegFinishBatch(b200jpegDecoder_t decoder, int* status, void* cuda_stream);
+
+/* Introspection for benchmarks and tests. */
+enum {
+    B200JPEG_STAT_KERNEL_LAUNCHES = 0, /* kernels launched by the last Execute */
+    B200JPEG_STAT_ALGO_BYTES = 1,      /* C + 4*N_coef + P of the last prepared batch */
+    B200JPEG_STAT_COMPRESSED_BYTES = 2,
+    B200JPEG_STAT_NUM_COEFS = 3,
+    B200JPEG_STAT_OUTPUT_BYTES = 4,
+    B200JPEG_STAT_RESYNC_IMAGES = 5,   /* images that needed the re-synchronisation path in the last Finish */
+    B200JPEG_STAT_DEVICE_BYTES = 6,    /* device memory currently held */
+    B200JPEG_STAT_NUM_SUBSEQ = 7
+};
+B200JPEG_API int64_t b200jpegGetStat(b200jpegDecoder_t decoder, int which);
+
+/* Per-stage device times (ms) of the last Execute, measured with CUDA events on the
+ * launch stream when enabled with b200jpegSetProfiling(decoder, 1).  names[i] are static strings. */
+B200JPEG_API int b200jpegSetProfiling(b200jpegDecoder_t decoder, int enable);
+B200JPEG_API int b200jpegGetStageTimes(b200jpegDecoder_t decoder, float* ms, const char** names, int capacity);
+
+/* Intermediate results of image `index` of the last executed batch (tests only):
+ * coefficients as int16 [mcu][block-in-mcu][64] in zig-zag order. */
+B200JPEG_API int b200jpegDebugCopyCoefficients(b200jpegDecoder_t decoder, int index, int16_t* host_out, size_t capacity_elems);
+
+B200JPEG_API const char* b200jpegGetLastError(b200jpegDecoder_t decoder);
+B200JPEG_API const char* b200jpegVersion(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200JPEG_H_ */

@@ -1,0 +1,170 @@
+// extern "C" surface declared in include/b200jpeg.h.
+#include <cstring>
+#include <new>
+
+#include "b200jpeg.h"
+#include "decoder.h"
+
+using b200jpeg::Decoder;
+
+struct b200jpegDecoder_st {
+    Decoder* impl;
+};
+
+namespace {
+const char* kDecoderId = "b200_jpeg_decoder";
+thread_local char g_err[256] = "";
+} // namespace
+
+extern "C" {
+
+int b200jpegProbe(const void* data, size_t length, b200jpegStreamInfo_t* info)
+{
+    if (!data || !info)
+        return B200JPEG_ERR_ARG;
+    std::memset(info, 0, sizeof(*info));
+    b200jpeg::StreamHeader hd;
+    const b200jpeg::StreamStatus st = b200jpeg::parse_stream(static_cast<const uint8_t*>(data), length, &hd);
+    info->width = hd.width;
+    info->height = hd.height;
+    info->num_components = hd.ncomp;
+    for (int c = 0; c < 4; ++c) {
+        info->h[c] = hd.h[c];
+        info->v[c] = hd.v[c];
+    }
+    info->sof_marker = hd.sof;
+    info->precision = hd.precision;
+    info->restart_interval = hd.restart_interval;
+    info->num_scans_seen = hd.nscans;
+    info->scan_offset = hd.scan_offset;
+    info->scan_length = hd.scan_length;
+    info->mcus_x = hd.mcus_x;
+    info->mcus_y = hd.mcus_y;
+    info->blocks_per_mcu = hd.blocks_per_mcu;
+    info->supported = (st == b200jpeg::kStreamOk) ? 1 : 0;
+    switch (st) {
+    case b200jpeg::kStreamOk: info->reason = B200JPEG_OK; break;
+    case b200jpeg::kStreamNotJpeg: info->reason = B200JPEG_ERR_NOT_JPEG; break;
+    case b200jpeg::kStreamUnsupported: info->reason = B200JPEG_ERR_UNSUPPORTED; break;
+    default: info->reason = B200JPEG_ERR_CORRUPT; break;
+    }
+    if (st == b200jpeg::kStreamOk && hd.scan_length >= (size_t(1) << 29)) {
+        info->supported = 0;
+        info->reason = B200JPEG_ERR_TOO_LARGE;
+    }
+    return info->reason;
+}
+
+int b200jpegCreate(b200jpegDecoder_t* decoder, int device_id, const char* options)
+{
+    if (!decoder)
+        return B200JPEG_ERR_ARG;
+    *decoder = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        std::strncpy(g_err, "no CUDA device: this decoder has no CPU path", sizeof(g_err) - 1);
+        return B200JPEG_ERR_CUDA;
+    }
+    if (device_id < 0) {
+        if (cudaGetDevice(&device_id) != cudaSuccess)
+            return B200JPEG_ERR_CUDA;
+    }
+    if (device_id >= count)
+        return B200JPEG_ERR_ARG;
+    auto* h = new (std::nothrow) b200jpegDecoder_st;
+    if (!h)
+        return B200JPEG_ERR_ARG;
+    h->impl = new (std::nothrow) Decoder(device_id, b200jpeg::parse_options(options, kDecoderId));
+    if (!h->impl) {
+        delete h;
+        return B200JPEG_ERR_ARG;
+    }
+    *decoder = h;
+    return B200JPEG_OK;
+}
+
+int b200jpegDestroy(b200jpegDecoder_t decoder)
+{
+    if (!decoder)
+        return B200JPEG_OK;
+    delete decoder->impl;
+    delete decoder;
+    return B200JPEG_OK;
+}
+
+int b200jpegPrepareBatch(b200jpegDecoder_t decoder, int batch_size, const void* const* data, const size_t* lengths,
+    const b200jpegOutput_t* outputs, void* cuda_stream)
+{
+    if (!decoder)
+        return B200JPEG_ERR_ARG;
+    try {
+        return decoder->impl->prepare(batch_size, data, lengths, outputs, static_cast<cudaStream_t>(cuda_stream));
+    } catch (...) {
+        return B200JPEG_ERR_STATE;
+    }
+}
+
+int b200jpegExecuteBatch(b200jpegDecoder_t decoder, void* cuda_stream)
+{
+    if (!decoder)
+        return B200JPEG_ERR_ARG;
+    try {
+        return decoder->impl->execute(static_cast<cudaStream_t>(cuda_stream));
+    } catch (...) {
+        return B200JPEG_ERR_STATE;
+    }
+}
+
+int b200jpegFinishBatch(b200jpegDecoder_t decoder, int* status, void* cuda_stream)
+{
+    if (!decoder)
+        return B200JPEG_ERR_ARG;
+    try {
+        return decoder->impl->finish(status, static_cast<cudaStream_t>(cuda_stream));
+    } catch (...) {
+        return B200JPEG_ERR_STATE;
+    }
+}
+
+int b200jpegDecodeBatch(b200jpegDecoder_t decoder, int batch_size, const void* const* data, const size_t* lengths,
+    const b200jpegOutput_t* outputs, int* status, void* cuda_stream)
+{
+    int rc = b200jpegPrepareBatch(decoder, batch_size, data, lengths, outputs, cuda_stream);
+    if (rc != B200JPEG_OK)
+        return rc;
+    rc = b200jpegExecuteBatch(decoder, cuda_stream);
+    if (rc != B200JPEG_OK)
+        return rc;
+    return b200jpegFinishBatch(decoder, status, cuda_stream);
+}
+
+int64_t b200jpegGetStat(b200jpegDecoder_t decoder, int which) { return decoder ? decoder->impl->stat(which) : -1; }
+
+int b200jpegSetProfiling(b200jpegDecoder_t decoder, int enable)
+{
+    if (!decoder)
+        return B200JPEG_ERR_ARG;
+    decoder->impl->set_profiling(enable != 0);
+    return B200JPEG_OK;
+}
+
+int b200jpegGetStageTimes(b200jpegDecoder_t decoder, float* ms, const char** names, int capacity)
+{
+    if (!decoder || !ms)
+        return 0;
+    return decoder->impl->stage_times(ms, names, capacity);
+}
+
+int b200jpegDebugCopyCoefficients(b200jpegDecoder_t decoder, int index, int16_t* host_out, size_t capacity_elems)
+{
+    if (!decoder || !host_out)
+        return B200JPEG_ERR_ARG;
+    return decoder->impl->copy_coefficients(index, host_out, capacity_elems);
+}
+
+const char* b200jpegGetLastError(b200jpegDecoder_t decoder) { return decoder ? decoder->impl->last_error() : g_err; }
+
+const char* b200jpegVersion(void) { return "b200jpeg 0.1.0 (sm_100a)"; }
+
+} // extern "C"

@@ -1,0 +1,574 @@
+// Batch orchestration (see decoder.h).  Host work per batch: marker walk per image, one
+// pinned staging arena, ONE host->device copy, a fixed kernel sequence, one status read-back.
+#include "decoder.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+
+namespace b200jpeg {
+
+namespace {
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+const char* kStageNames[] = {"scan(K0)", "huff_sync(K1)", "verify_scan(K2)", "coef_clear", "huff_write(K3)", "idct(K4a)", "color(K4b)", "fixup"};
+} // namespace
+
+bool DeviceBuffer::ensure(size_t bytes, size_t* total)
+{
+    if (bytes <= cap)
+        return true;
+    if (ptr) {
+        cudaFree(ptr);
+        *total -= cap;
+        ptr = nullptr;
+        cap = 0;
+    }
+    const size_t want = align_up(bytes + bytes / 8, size_t(2) << 20);
+    if (cudaMalloc(&ptr, want) != cudaSuccess) {
+        ptr = nullptr;
+        cudaGetLastError();
+        return false;
+    }
+    cap = want;
+    *total += cap;
+    return true;
+}
+void DeviceBuffer::release()
+{
+    if (ptr)
+        cudaFree(ptr);
+    ptr = nullptr;
+    cap = 0;
+}
+bool PinnedBuffer::ensure(size_t bytes)
+{
+    if (bytes <= cap)
+        return true;
+    if (ptr)
+        cudaFreeHost(ptr);
+    ptr = nullptr;
+    cap = 0;
+    const size_t want = align_up(bytes + bytes / 8, size_t(2) << 20);
+    if (cudaMallocHost(&ptr, want) != cudaSuccess) {
+        ptr = nullptr;
+        cudaGetLastError();
+        return false;
+    }
+    cap = want;
+    return true;
+}
+void PinnedBuffer::release()
+{
+    if (ptr)
+        cudaFreeHost(ptr);
+    ptr = nullptr;
+    cap = 0;
+}
+
+// "<decoder_id>:<name>=<value>" tokens separated by spaces; an empty id addresses every decoder
+// (include/nvimgcodec.h:1967-1971; same idiom as libjpeg_turbo_decoder.cpp:229-248).
+Options parse_options(const char* options, const char* decoder_id)
+{
+    Options o;
+    if (!options)
+        return o;
+    std::string s(options);
+    size_t pos = 0;
+    while (pos < s.size()) {
+        size_t end = s.find(' ', pos);
+        if (end == std::string::npos)
+            end = s.size();
+        std::string tok = s.substr(pos, end - pos);
+        pos = end + 1;
+        if (tok.empty())
+            continue;
+        std::string module, name = tok, value;
+        const size_t colon = tok.find(':');
+        if (colon != std::string::npos) {
+            module = tok.substr(0, colon);
+            name = tok.substr(colon + 1);
+        }
+        const size_t eq = name.find('=');
+        if (eq == std::string::npos)
+            continue;
+        value = name.substr(eq + 1);
+        name = name.substr(0, eq);
+        if (!module.empty() && module != decoder_id)
+            continue;
+        if (name == "fancy_upsampling")
+            o.fancy_upsampling = std::atoi(value.c_str()) != 0;
+        else if (name == "debug_no_warm")
+            o.debug_no_warm = std::atoi(value.c_str()) != 0;
+        else if (name == "max_fix_rounds")
+            o.max_fix_rounds = std::atoi(value.c_str());
+    }
+    return o;
+}
+
+Decoder::Decoder(int device_id, const Options& opt)
+    : device_(device_id)
+    , opt_(opt)
+{
+}
+
+Decoder::~Decoder()
+{
+    cudaSetDevice(device_);
+    if (ev_valid_)
+        for (auto& e : ev_)
+            cudaEventDestroy(e);
+    upload_.release();
+    scratch_.release();
+    cmp_.release();
+    coef_.release();
+    planes_.release();
+    bounce_.release();
+    upload_host_.release();
+    state_host_.release();
+}
+
+int Decoder::fail(int code, const std::string& msg)
+{
+    err_ = msg;
+    return code;
+}
+
+bool Decoder::cuda_ok(cudaError_t e, const char* what)
+{
+    if (e == cudaSuccess)
+        return true;
+    err_ = std::string(what) + ": " + cudaGetErrorString(e);
+    return false;
+}
+
+void Decoder::mark(int stage, cudaStream_t s)
+{
+    if (profiling_ && ev_valid_)
+        cudaEventRecord(ev_[stage], s);
+}
+
+int Decoder::prepare(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, cudaStream_t stream)
+{
+    if (n < 0 || (n > 0 && (!data || !len || !outs)))
+        return fail(B200JPEG_ERR_ARG, "null argument");
+    if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
+        return B200JPEG_ERR_CUDA;
+    prepared_ = executed_ = false;
+    n_in_ = n;
+    host_status_.assign(n, B200JPEG_OK);
+    dev_index_.assign(n, -1);
+    in_index_.clear();
+    imgs_.clear();
+    host_outs_.clear();
+    set_index_.clear();
+    std::vector<const HuffSetDev*> sets;
+    std::vector<StreamHeader> hdrs;
+    hdrs.reserve(n);
+
+    size_t raw_bytes = 0, cmp_bytes = 0, coef_elems = 0, plane_bytes = 0, bounce_bytes = 0;
+    uint32_t n_tiles = 0, n_sub = 0, n_seq = 0, n_bnd = 0, n_idct = 0, n_color = 0;
+    comp_bytes_ = n_coefs_ = out_bytes_ = 0;
+
+    for (int i = 0; i < n; ++i) {
+        StreamHeader hd;
+        const StreamStatus ss = data[i] ? parse_stream(static_cast<const uint8_t*>(data[i]), len[i], &hd) : kStreamNotJpeg;
+        if (ss != kStreamOk) {
+            host_status_[i] = ss == kStreamNotJpeg ? B200JPEG_ERR_NOT_JPEG : (ss == kStreamUnsupported ? B200JPEG_ERR_UNSUPPORTED : B200JPEG_ERR_CORRUPT);
+            continue;
+        }
+        const b200jpegOutput_t& o = outs[i];
+        int x0 = o.roi_x0, y0 = o.roi_y0, x1 = o.roi_x1, y1 = o.roi_y1;
+        if (x0 == 0 && y0 == 0 && x1 == 0 && y1 == 0) {
+            x1 = hd.width;
+            y1 = hd.height;
+        }
+        if (!o.buffer || o.format < 0 || o.format > B200JPEG_FMT_Y || x0 < 0 || y0 < 0 || x1 > hd.width || y1 > hd.height || x0 >= x1 || y0 >= y1) {
+            host_status_[i] = B200JPEG_ERR_ARG;
+            continue;
+        }
+        const size_t rw = size_t(x1 - x0), rh = size_t(y1 - y0);
+        const bool planar = (o.format == B200JPEG_FMT_P_RGB || o.format == B200JPEG_FMT_P_BGR);
+        const size_t nch = o.format == B200JPEG_FMT_Y ? 1 : 3;
+        const size_t tight = planar ? rw : rw * nch;
+        const size_t stride = o.row_stride ? o.row_stride : tight;
+        if (stride < tight || stride > 0xFFFFFFFFull) {
+            host_status_[i] = B200JPEG_ERR_ARG;
+            continue;
+        }
+        if (hd.scan_length >= (size_t(1) << 29)) { // bit positions are 32-bit
+            host_status_[i] = B200JPEG_ERR_TOO_LARGE;
+            continue;
+        }
+        ImageDev im;
+        std::memset(&im, 0, sizeof(im));
+        im.raw_off = raw_bytes;
+        im.raw_len = uint32_t(hd.scan_length);
+        raw_bytes += align_up(hd.scan_length, 16) + 16;
+        im.cmp_off = cmp_bytes;
+        cmp_bytes += align_up(hd.scan_length, 16) + 32;
+        im.tile_off = n_tiles;
+        im.n_tiles = uint32_t((hd.scan_length + kScanTileBytes - 1) / kScanTileBytes);
+        n_tiles += im.n_tiles;
+        im.sub_off = n_sub;
+        im.n_sub_max = uint32_t((hd.scan_length + kSubseqBytes - 1) / kSubseqBytes);
+        n_sub += im.n_sub_max;
+        im.seq_off = n_seq;
+        im.n_seq = (im.n_sub_max + kSeqStride - 1) / kSeqStride;
+        n_seq += im.n_seq;
+        const uint32_t n_mcu = uint32_t(hd.mcus_x) * uint32_t(hd.mcus_y);
+        im.restart_interval = uint32_t(hd.restart_interval);
+        im.n_rst_expected = hd.restart_interval ? (n_mcu + hd.restart_interval - 1) / hd.restart_interval - 1 : 0;
+        im.bnd_off = n_bnd;
+        im.n_bnd_cap = im.n_rst_expected + 1;
+        n_bnd += im.n_bnd_cap;
+        im.total_blocks = n_mcu * uint32_t(hd.blocks_per_mcu);
+        im.coef_off = coef_elems;
+        coef_elems += size_t(im.total_blocks) * 64;
+        im.width = uint16_t(hd.width);
+        im.height = uint16_t(hd.height);
+        im.mcus_x = uint16_t(hd.mcus_x);
+        im.mcus_y = uint16_t(hd.mcus_y);
+        im.ncomp = uint8_t(hd.ncomp);
+        im.hmax = uint8_t(hd.hmax);
+        im.vmax = uint8_t(hd.vmax);
+        im.bpm = uint8_t(hd.blocks_per_mcu);
+        im.fmt = uint8_t(o.format);
+        im.fancy = opt_.fancy_upsampling ? 1 : 0;
+        im.ncomp_needed = (o.format == B200JPEG_FMT_Y || hd.ncomp == 1) ? 1 : 3;
+        int b = 0;
+        uint32_t idct_blocks = 0;
+        for (int c = 0; c < hd.ncomp; ++c) {
+            im.h[c] = uint8_t(hd.h[c]);
+            im.v[c] = uint8_t(hd.v[c]);
+            im.blk_first[c] = uint8_t(b);
+            for (int k = 0; k < hd.h[c] * hd.v[c]; ++k, ++b) {
+                im.blk_comp |= uint32_t(c) << (2 * b);
+                im.blk_tab |= uint32_t(hd.td[c]) << b;
+                im.blk_tab |= uint32_t(hd.ta[c]) << (16 + b);
+            }
+            std::memcpy(im.qt[c], hd.qt[hd.tq[c]], sizeof(im.qt[c]));
+            const size_t pw = size_t(hd.mcus_x) * hd.h[c] * 8, ph = size_t(hd.mcus_y) * hd.v[c] * 8;
+            if (c < im.ncomp_needed) {
+                im.plane_off[c] = plane_bytes;
+                plane_bytes += align_up(pw * ph, 256);
+                idct_blocks += uint32_t(pw / 8 * (ph / 8));
+            }
+        }
+        im.idct_cta_off = n_idct;
+        im.n_idct_cta = (idct_blocks + 127) / 128;
+        n_idct += im.n_idct_cta;
+        im.roi_x0 = uint16_t(x0);
+        im.roi_y0 = uint16_t(y0);
+        im.roi_x1 = uint16_t(x1);
+        im.roi_y1 = uint16_t(y1);
+        im.row_stride = uint32_t(stride);
+        im.plane_stride = stride * rh;
+        const size_t obytes = planar ? 3 * stride * rh : stride * rh;
+        im.color_cta_off = n_color;
+        im.n_color_cta_x = uint32_t((rw + 255) / 256);
+        im.n_color_cta_y = uint32_t((rh + 3) / 4);
+        n_color += im.n_color_cta_x * im.n_color_cta_y;
+        HostOut ho{nullptr, 0, obytes};
+        if (o.buffer_is_host) {
+            ho.host_ptr = o.buffer;
+            ho.bounce_off = bounce_bytes;
+            bounce_bytes += align_up(obytes, 256);
+            im.out = reinterpret_cast<uint8_t*>(ho.bounce_off); // rebased once the bounce arena exists
+        } else {
+            im.out = static_cast<uint8_t*>(o.buffer);
+        }
+        // huffman set (deduplicated by content hash)
+        const uint64_t hsh = hash_huff_set(hd);
+        auto it = set_index_.find(hsh);
+        if (it == set_index_.end()) {
+            auto ci = set_cache_.find(hsh);
+            if (ci == set_cache_.end()) {
+                if (set_cache_.size() > 4096)
+                    set_cache_.clear();
+                HuffSetDev hs;
+                build_huff_set(hd, &hs);
+                ci = set_cache_.emplace(hsh, hs).first;
+            }
+            it = set_index_.emplace(hsh, int(sets.size())).first;
+            sets.push_back(&ci->second);
+        }
+        im.huff_set = uint32_t(it->second);
+
+        comp_bytes_ += int64_t(len[i]);
+        n_coefs_ += int64_t(im.total_blocks) * 64;
+        out_bytes_ += int64_t(rw * rh * nch);
+        dev_index_[i] = int(imgs_.size());
+        in_index_.push_back(i);
+        imgs_.push_back(im);
+        host_outs_.push_back(ho);
+        hdrs.push_back(hd);
+    }
+    algo_bytes_ = comp_bytes_ + 4 * n_coefs_ + out_bytes_;
+    const int nd = int(imgs_.size());
+
+    // ---- upload arena: descriptors | cta->image maps | huffman sets | raw scan bytes
+    size_t off = 0;
+    const size_t off_img = off;
+    off = align_up(off + sizeof(ImageDev) * nd, 256);
+    const size_t off_tile = off;
+    off = align_up(off + 4ull * n_tiles, 256);
+    const size_t off_seq = off;
+    off = align_up(off + 4ull * n_seq, 256);
+    const size_t off_idct = off;
+    off = align_up(off + 4ull * n_idct, 256);
+    const size_t off_color = off;
+    off = align_up(off + 4ull * n_color, 256);
+    const size_t off_huff = off;
+    off = align_up(off + sizeof(HuffSetDev) * sets.size(), 256);
+    const size_t off_raw = off;
+    off += raw_bytes + 256;
+    const size_t upload_bytes = off;
+
+    // ---- scratch arena
+    size_t so = 0;
+    const size_t so_state = so;
+    so = align_up(so + sizeof(ImageState) * nd, 256);
+    const size_t so_tinfo = so;
+    so = align_up(so + 8ull * n_tiles, 256);
+    const size_t so_tbase = so;
+    so = align_up(so + 8ull * n_tiles, 256);
+    const size_t so_bnd = so;
+    so = align_up(so + 4ull * n_bnd, 256);
+    const size_t so_in = so;
+    so = align_up(so + 4ull * n_sub, 256);
+    const size_t so_out = so;
+    so = align_up(so + 4ull * n_sub, 256);
+    const size_t so_info = so;
+    so = align_up(so + 16ull * n_sub, 256);
+    const size_t so_start = so;
+    so = align_up(so + 16ull * n_sub, 256);
+
+    coef_bytes_ = coef_elems * sizeof(int16_t);
+    if (!upload_host_.ensure(upload_bytes) || !state_host_.ensure(sizeof(ImageState) * std::max(nd, 1)))
+        return fail(B200JPEG_ERR_CUDA, "pinned host allocation failed");
+    if (!upload_.ensure(upload_bytes, &device_bytes_) || !scratch_.ensure(so + 256, &device_bytes_) ||
+        !cmp_.ensure(cmp_bytes + 256, &device_bytes_) || !coef_.ensure(coef_bytes_ + 256, &device_bytes_) ||
+        !planes_.ensure(plane_bytes + 256, &device_bytes_) || !bounce_.ensure(bounce_bytes + 256, &device_bytes_))
+        return fail(B200JPEG_ERR_CUDA, "device allocation failed");
+
+    uint8_t* up = upload_host_.as<uint8_t>();
+    uint32_t* tile_img = reinterpret_cast<uint32_t*>(up + off_tile);
+    uint32_t* seq_img = reinterpret_cast<uint32_t*>(up + off_seq);
+    uint32_t* idct_img = reinterpret_cast<uint32_t*>(up + off_idct);
+    uint32_t* color_img = reinterpret_cast<uint32_t*>(up + off_color);
+    for (int d = 0; d < nd; ++d) {
+        ImageDev& im = imgs_[d];
+        if (host_outs_[d].host_ptr)
+            im.out = bounce_.as<uint8_t>() + host_outs_[d].bounce_off;
+        std::fill(tile_img + im.tile_off, tile_img + im.tile_off + im.n_tiles, uint32_t(d));
+        std::fill(seq_img + im.seq_off, seq_img + im.seq_off + im.n_seq, uint32_t(d));
+        std::fill(idct_img + im.idct_cta_off, idct_img + im.idct_cta_off + im.n_idct_cta, uint32_t(d));
+        std::fill(color_img + im.color_cta_off, color_img + im.color_cta_off + im.n_color_cta_x * im.n_color_cta_y, uint32_t(d));
+        const int i = in_index_[d];
+        uint8_t* dst = up + off_raw + im.raw_off;
+        std::memcpy(dst, static_cast<const uint8_t*>(data[i]) + hdrs[d].scan_offset, im.raw_len);
+        std::memset(dst + im.raw_len, 0, align_up(im.raw_len, 16) + 16 - im.raw_len);
+    }
+    if (nd)
+        std::memcpy(up + off_img, imgs_.data(), sizeof(ImageDev) * nd);
+    for (size_t s = 0; s < sets.size(); ++s)
+        std::memcpy(up + off_huff + s * sizeof(HuffSetDev), sets[s], sizeof(HuffSetDev));
+
+    if (nd && !cuda_ok(cudaMemcpyAsync(upload_.ptr, up, upload_bytes, cudaMemcpyHostToDevice, stream), "upload"))
+        return B200JPEG_ERR_CUDA;
+
+    uint8_t* dv = upload_.as<uint8_t>();
+    uint8_t* sc = scratch_.as<uint8_t>();
+    bd_.n_images = nd;
+    bd_.img = reinterpret_cast<const ImageDev*>(dv + off_img);
+    bd_.tile_img = reinterpret_cast<const uint32_t*>(dv + off_tile);
+    bd_.seq_img = reinterpret_cast<const uint32_t*>(dv + off_seq);
+    bd_.idct_cta_img = reinterpret_cast<const uint32_t*>(dv + off_idct);
+    bd_.color_cta_img = reinterpret_cast<const uint32_t*>(dv + off_color);
+    bd_.huff = reinterpret_cast<const HuffSetDev*>(dv + off_huff);
+    bd_.raw = dv + off_raw;
+    bd_.state = reinterpret_cast<ImageState*>(sc + so_state);
+    bd_.tile_info = reinterpret_cast<uint2*>(sc + so_tinfo);
+    bd_.tile_base = reinterpret_cast<uint2*>(sc + so_tbase);
+    bd_.bnd = reinterpret_cast<uint32_t*>(sc + so_bnd);
+    bd_.sub_in = reinterpret_cast<uint32_t*>(sc + so_in);
+    bd_.sub_out = reinterpret_cast<uint32_t*>(sc + so_out);
+    bd_.sub_info = reinterpret_cast<int4*>(sc + so_info);
+    bd_.sub_start = reinterpret_cast<int4*>(sc + so_start);
+    bd_.cmp = cmp_.as<uint32_t>();
+    bd_.coef = coef_.as<int16_t>();
+    bd_.planes = planes_.as<uint8_t>();
+    bd_.n_tiles = int(n_tiles);
+    bd_.n_seq = int(n_seq);
+    bd_.n_sub = int(n_sub);
+    bd_.n_idct_cta = int(n_idct);
+    bd_.n_color_cta = int(n_color);
+    states_.assign(nd, ImageState{0, 0, 0, 0});
+    if (profiling_ && !ev_valid_) {
+        for (auto& e : ev_)
+            cudaEventCreate(&e);
+        ev_valid_ = true;
+    }
+    prepared_ = true;
+    return B200JPEG_OK;
+}
+
+int Decoder::execute(cudaStream_t stream)
+{
+    if (!prepared_)
+        return fail(B200JPEG_ERR_STATE, "execute without a prepared batch");
+    if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
+        return B200JPEG_ERR_CUDA;
+    launches_ = 0;
+    executed_ = true;
+    ev_recorded_ = false;
+    if (bd_.n_images == 0)
+        return B200JPEG_OK;
+    mark(0, stream);
+    launches_ += launch_scan(bd_, stream);
+    mark(1, stream);
+    launches_ += launch_sync(bd_, false, opt_.debug_no_warm, stream);
+    mark(2, stream);
+    launches_ += launch_verify_scan(bd_, false, stream);
+    mark(3, stream);
+    if (coef_bytes_) {
+        cudaMemsetAsync(coef_.ptr, 0, coef_bytes_, stream);
+        launches_ += 1;
+    }
+    mark(4, stream);
+    launches_ += launch_write(bd_, false, stream);
+    mark(5, stream);
+    launches_ += launch_idct(bd_, false, stream);
+    mark(6, stream);
+    launches_ += launch_color(bd_, false, stream);
+    mark(7, stream);
+    ev_recorded_ = profiling_ && ev_valid_;
+    if (!cuda_ok(cudaGetLastError(), "kernel launch"))
+        return B200JPEG_ERR_CUDA;
+    return B200JPEG_OK;
+}
+
+int Decoder::finish(int* status, cudaStream_t stream)
+{
+    if (!executed_)
+        return fail(B200JPEG_ERR_STATE, "finish without an executed batch");
+    if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
+        return B200JPEG_ERR_CUDA;
+    const int nd = bd_.n_images;
+    resync_images_ = 0;
+    auto read_states = [&]() -> bool {
+        if (nd == 0)
+            return true;
+        if (!cuda_ok(cudaMemcpyAsync(state_host_.ptr, bd_.state, sizeof(ImageState) * nd, cudaMemcpyDeviceToHost, stream), "state read-back"))
+            return false;
+        if (!cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
+            return false;
+        std::memcpy(states_.data(), state_host_.ptr, sizeof(ImageState) * nd);
+        return true;
+    };
+    if (!read_states())
+        return B200JPEG_ERR_CUDA;
+    auto count_dirty = [&]() {
+        int c = 0;
+        for (const auto& s : states_)
+            c += (s.flags & kFlagDirty) ? 1 : 0;
+        return c;
+    };
+    int dirty = count_dirty();
+    if (dirty) {
+        // Rare path: some sequence of some image did not enter with the state its predecessor left.
+        // Propagate corrected entry states one sequence per round until K2 finds every image consistent.
+        resync_images_ = dirty;
+        int rounds = 0;
+        while (dirty && rounds < opt_.max_fix_rounds) {
+            launches_ += launch_sync(bd_, true, false, stream);
+            launches_ += launch_verify_scan(bd_, true, stream);
+            if (!read_states())
+                return B200JPEG_ERR_CUDA;
+            dirty = count_dirty();
+            ++rounds;
+        }
+        for (int d = 0; d < nd; ++d)
+            if ((states_[d].flags & kFlagRedo) && !(states_[d].flags & kFlagDirty))
+                cudaMemsetAsync(bd_.coef + imgs_[d].coef_off, 0, size_t(imgs_[d].total_blocks) * 128, stream);
+        launches_ += launch_write(bd_, true, stream);
+        launches_ += launch_idct(bd_, true, stream);
+        launches_ += launch_color(bd_, true, stream);
+        if (!read_states())
+            return B200JPEG_ERR_CUDA;
+    }
+    // host outputs: one D2H per image out of the bounce arena
+    bool any_host = false;
+    for (int d = 0; d < nd; ++d) {
+        const HostOut& ho = host_outs_[d];
+        if (!ho.host_ptr)
+            continue;
+        any_host = true;
+        if (!cuda_ok(cudaMemcpyAsync(ho.host_ptr, bounce_.as<uint8_t>() + ho.bounce_off, ho.bytes, cudaMemcpyDeviceToHost, stream), "output copy"))
+            return B200JPEG_ERR_CUDA;
+    }
+    if (any_host && !cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
+        return B200JPEG_ERR_CUDA;
+    if (status) {
+        for (int i = 0; i < n_in_; ++i) {
+            int st = host_status_[i];
+            const int d = dev_index_[i];
+            if (st == B200JPEG_OK && d >= 0) {
+                const uint32_t f = states_[d].flags;
+                if (f & kFlagDirty)
+                    st = B200JPEG_ERR_UNSUPPORTED;
+                else if (f & (kFlagBadMarker | kFlagBadHuffman | kFlagOverrun | kFlagPhase))
+                    st = B200JPEG_ERR_CORRUPT;
+            }
+            status[i] = st;
+        }
+    }
+    return B200JPEG_OK;
+}
+
+int64_t Decoder::stat(int which) const
+{
+    switch (which) {
+    case B200JPEG_STAT_KERNEL_LAUNCHES: return launches_;
+    case B200JPEG_STAT_ALGO_BYTES: return algo_bytes_;
+    case B200JPEG_STAT_COMPRESSED_BYTES: return comp_bytes_;
+    case B200JPEG_STAT_NUM_COEFS: return n_coefs_;
+    case B200JPEG_STAT_OUTPUT_BYTES: return out_bytes_;
+    case B200JPEG_STAT_RESYNC_IMAGES: return resync_images_;
+    case B200JPEG_STAT_DEVICE_BYTES: return int64_t(device_bytes_);
+    case B200JPEG_STAT_NUM_SUBSEQ: return bd_.n_sub;
+    default: return -1;
+    }
+}
+
+int Decoder::stage_times(float* ms, const char** names, int cap)
+{
+    if (!ev_recorded_)
+        return 0;
+    cudaEventSynchronize(ev_[kStages - 1]);
+    int n = 0;
+    for (int i = 0; i < kStages - 1 && n < cap; ++i, ++n) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, ev_[i], ev_[i + 1]);
+        ms[n] = t;
+        if (names)
+            names[n] = kStageNames[i];
+    }
+    return n;
+}
+
+int Decoder::copy_coefficients(int index, int16_t* host_out, size_t cap_elems)
+{
+    if (!executed_ || index < 0 || index >= n_in_ || dev_index_[index] < 0)
+        return fail(B200JPEG_ERR_ARG, "no such decoded image");
+    const ImageDev& im = imgs_[dev_index_[index]];
+    const size_t elems = size_t(im.total_blocks) * 64;
+    if (cap_elems < elems)
+        return fail(B200JPEG_ERR_ARG, "buffer too small");
+    cudaSetDevice(device_);
+    if (!cuda_ok(cudaMemcpy(host_out, bd_.coef + im.coef_off, elems * sizeof(int16_t), cudaMemcpyDeviceToHost), "coefficient copy"))
+        return B200JPEG_ERR_CUDA;
+    return B200JPEG_OK;
+}
+
+} // namespace b200jpeg

@@ -1,0 +1,106 @@
+// Batch orchestration of the b200 JPEG decode path: host marker walk, one staging
+// upload per batch, kernel sequence, the rare re-synchronisation path, statuses.
+// Mirrors the role of DecoderImpl in the reference's batched plugin
+// (extensions/nvjpeg/hw_decoder.cpp:636-888) for a single device.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "b200jpeg.h"
+#include "jpeg_stream.h"
+#include "kernels.cuh"
+
+namespace b200jpeg {
+
+struct DeviceBuffer {
+    void* ptr = nullptr;
+    size_t cap = 0;
+    bool ensure(size_t bytes, size_t* total); // grow-only
+    void release();
+    template <typename T>
+    T* as() const { return static_cast<T*>(ptr); }
+};
+
+struct PinnedBuffer {
+    void* ptr = nullptr;
+    size_t cap = 0;
+    bool ensure(size_t bytes);
+    void release();
+    template <typename T>
+    T* as() const { return static_cast<T*>(ptr); }
+};
+
+struct Options {
+    bool fancy_upsampling = true; // libjpeg_turbo_ext default (libjpeg_turbo_decoder.cpp:223-249)
+    bool debug_no_warm = false;   // test hook: forces the re-synchronisation path
+    int max_fix_rounds = 1 << 20;
+};
+
+Options parse_options(const char* options, const char* decoder_id);
+
+class Decoder {
+  public:
+    Decoder(int device_id, const Options& opt);
+    ~Decoder();
+
+    int prepare(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, cudaStream_t stream);
+    int execute(cudaStream_t stream);
+    int finish(int* status, cudaStream_t stream);
+
+    int64_t stat(int which) const;
+    void set_profiling(bool on) { profiling_ = on; }
+    int stage_times(float* ms, const char** names, int cap);
+    int copy_coefficients(int index, int16_t* host_out, size_t cap_elems);
+    const char* last_error() const { return err_.c_str(); }
+    int device() const { return device_; }
+
+  private:
+    int fail(int code, const std::string& msg);
+    bool cuda_ok(cudaError_t e, const char* what);
+    void mark(int stage, cudaStream_t s);
+
+    int device_;
+    Options opt_;
+    std::string err_;
+
+    // batch bookkeeping (host)
+    int n_in_ = 0;                      // images passed to prepare
+    std::vector<int> host_status_;      // per input image, B200JPEG_*
+    std::vector<int> dev_index_;        // input index -> device batch index or -1
+    std::vector<int> in_index_;         // device batch index -> input index
+    std::vector<ImageDev> imgs_;        // host copy of descriptors
+    std::vector<ImageState> states_;
+    struct HostOut {
+        void* host_ptr;
+        size_t bounce_off, bytes;
+    };
+    std::vector<HostOut> host_outs_;    // per device image; host_ptr == nullptr if output is a device buffer
+    bool prepared_ = false, executed_ = false;
+
+    // device memory
+    DeviceBuffer upload_, scratch_, cmp_, coef_, planes_, bounce_;
+    PinnedBuffer upload_host_, state_host_;
+    size_t device_bytes_ = 0;
+    size_t coef_bytes_ = 0;
+    BatchDev bd_{};
+
+    // huffman set cache (content keyed by hash)
+    std::unordered_map<uint64_t, int> set_index_; // per batch
+    std::unordered_map<uint64_t, HuffSetDev> set_cache_;
+
+    // stats
+    int64_t launches_ = 0, algo_bytes_ = 0, comp_bytes_ = 0, n_coefs_ = 0, out_bytes_ = 0, resync_images_ = 0;
+
+    // profiling
+    bool profiling_ = false;
+    static constexpr int kStages = 8;
+    cudaEvent_t ev_[kStages + 1] = {};
+    bool ev_valid_ = false;
+    bool ev_recorded_ = false;
+};
+
+} // namespace b200jpeg

@@ -1,0 +1,258 @@
+// Host marker walk + Huffman lookup-table construction (see jpeg_stream.h).
+#include "jpeg_stream.h"
+
+#include <cstring>
+
+namespace b200jpeg {
+
+namespace {
+
+const uint8_t kZigzag[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20,
+    13, 6, 7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46,
+    53, 60, 61, 54, 47, 55, 62, 63};
+
+inline unsigned be16(const uint8_t* p) { return (unsigned(p[0]) << 8) | p[1]; }
+
+bool read_dqt(const uint8_t* s, size_t n, StreamHeader* hdr)
+{
+    size_t q = 0;
+    while (q < n) {
+        const int pq = s[q] >> 4, tq = s[q] & 15;
+        ++q;
+        if (tq > 3 || pq > 1)
+            return false;
+        const size_t need = pq ? 128 : 64;
+        if (q + need > n)
+            return false;
+        for (int i = 0; i < 64; ++i) {
+            hdr->qt[tq][kZigzag[i]] = pq ? uint16_t(be16(s + q + 2 * i)) : uint16_t(s[q + i]);
+        }
+        q += need;
+        hdr->qt_present[tq] = true;
+    }
+    return true;
+}
+
+bool read_dht(const uint8_t* s, size_t n, StreamHeader* hdr)
+{
+    size_t q = 0;
+    while (q < n) {
+        if (q + 17 > n)
+            return false;
+        const int tc = s[q] >> 4, th = s[q] & 15;
+        if (tc > 1 || th > 3)
+            return false;
+        HuffSpec& hs = hdr->huff[tc][th];
+        int total = 0;
+        hs.bits[0] = 0;
+        for (int l = 1; l <= 16; ++l) {
+            hs.bits[l] = s[q + l];
+            total += s[q + l];
+        }
+        q += 17;
+        if (total > 256 || q + size_t(total) > n)
+            return false;
+        std::memset(hs.vals, 0, sizeof(hs.vals));
+        std::memcpy(hs.vals, s + q, size_t(total));
+        q += size_t(total);
+        // Kraft check: a canonical code must not overflow any length
+        int code = 0;
+        for (int l = 1; l <= 16; ++l) {
+            code += hs.bits[l];
+            if (code > (1 << l))
+                return false;
+            code <<= 1;
+        }
+        hs.present = true;
+    }
+    return true;
+}
+
+} // namespace
+
+StreamStatus parse_stream(const uint8_t* d, size_t n, StreamHeader* hdr)
+{
+    for (int c = 0; c < 2; ++c)
+        for (int t = 0; t < 4; ++t)
+            hdr->huff[c][t].present = false;
+    if (n < 4 || d[0] != 0xFF || d[1] != 0xD8)
+        return kStreamNotJpeg;
+    size_t p = 2;
+    bool have_sof = false;
+    StreamStatus verdict = kStreamOk;
+    for (;;) {
+        if (p + 2 > n || d[p] != 0xFF)
+            return kStreamCorrupt;
+        while (p < n && d[p] == 0xFF)
+            ++p; // optional fill bytes before a marker (test/parsers/jpeg_test.cpp:361 exercises them)
+        if (p >= n)
+            return kStreamCorrupt;
+        const int m = d[p++];
+        if (m == 0xD8 || m == 0x01 || (m >= 0xD0 && m <= 0xD7))
+            continue;
+        if (m == 0xD9)
+            return kStreamCorrupt;
+        if (p + 2 > n)
+            return kStreamCorrupt;
+        const size_t len = be16(d + p);
+        if (len < 2 || p + len > n)
+            return kStreamCorrupt;
+        const uint8_t* s = d + p + 2;
+        const size_t sl = len - 2;
+        if (m == 0xDB) {
+            if (!read_dqt(s, sl, hdr))
+                return kStreamCorrupt;
+        } else if (m == 0xC4) {
+            if (!read_dht(s, sl, hdr))
+                return kStreamCorrupt;
+        } else if (m == 0xDD) {
+            if (sl < 2)
+                return kStreamCorrupt;
+            hdr->restart_interval = int(be16(s));
+        } else if (m == 0xE0) {
+            if (sl >= 5 && std::memcmp(s, "JFIF", 5) == 0)
+                hdr->has_jfif = true;
+        } else if (m == 0xEE) {
+            if (sl >= 12 && std::memcmp(s, "Adobe", 5) == 0)
+                hdr->adobe_transform = s[11];
+        } else if (m >= 0xC0 && m <= 0xCF && m != 0xC8 && m != 0xCC) {
+            if (have_sof || sl < 6)
+                return kStreamCorrupt;
+            have_sof = true;
+            hdr->sof = m;
+            hdr->precision = s[0];
+            hdr->height = int(be16(s + 1));
+            hdr->width = int(be16(s + 3));
+            hdr->ncomp = s[5];
+            if (hdr->ncomp < 1 || hdr->ncomp > kMaxComp || sl < 6 + 3 * size_t(hdr->ncomp))
+                return hdr->ncomp > kMaxComp ? kStreamUnsupported : kStreamCorrupt;
+            for (int c = 0; c < hdr->ncomp; ++c) {
+                hdr->comp_id[c] = s[6 + 3 * c];
+                hdr->h[c] = s[7 + 3 * c] >> 4;
+                hdr->v[c] = s[7 + 3 * c] & 15;
+                hdr->tq[c] = s[8 + 3 * c];
+                if (hdr->h[c] < 1 || hdr->h[c] > 4 || hdr->v[c] < 1 || hdr->v[c] > 4 || hdr->tq[c] > 3)
+                    return kStreamCorrupt;
+            }
+            if (m != 0xC0 || hdr->precision != 8)
+                verdict = kStreamUnsupported; // progressive / extended / lossless / arithmetic / 12-bit
+            if (hdr->width == 0 || hdr->height == 0)
+                verdict = kStreamUnsupported; // DNL-defined height
+        } else if (m == 0xDA) {
+            if (!have_sof || sl < 1)
+                return kStreamCorrupt;
+            const int ns = s[0];
+            if (ns < 1 || ns > 4 || sl < 1 + 2 * size_t(ns) + 3)
+                return kStreamCorrupt;
+            hdr->nscans = 1;
+            hdr->scan_offset = p + len;
+            hdr->scan_length = n - hdr->scan_offset;
+            if (verdict != kStreamOk)
+                return verdict;
+            if (ns != hdr->ncomp)
+                return kStreamUnsupported; // non-interleaved multi-scan baseline
+            for (int c = 0; c < ns; ++c) {
+                if (s[1 + 2 * c] != hdr->comp_id[c])
+                    return kStreamUnsupported; // scan order differs from frame order
+                hdr->td[c] = s[2 + 2 * c] >> 4;
+                hdr->ta[c] = s[2 + 2 * c] & 15;
+                if (hdr->td[c] > 1 || hdr->ta[c] > 1)
+                    return kStreamUnsupported; // baseline allows table ids 0 and 1 only
+            }
+            break;
+        }
+        p += len;
+    }
+    if (hdr->ncomp != 1 && hdr->ncomp != 3)
+        return kStreamUnsupported; // CMYK / YCCK / 2-component
+    if (hdr->ncomp == 3) {
+        // libjpeg's colour-space guess (jdapimin.c default_decompress_parms): components tagged R,G,B
+        // or an Adobe transform of 0 mean "already RGB" -- not produced by the encoders in scope.
+        if (hdr->adobe_transform == 0)
+            return kStreamUnsupported;
+        if (!hdr->has_jfif && hdr->adobe_transform < 0 && hdr->comp_id[0] == 'R' && hdr->comp_id[1] == 'G' && hdr->comp_id[2] == 'B')
+            return kStreamUnsupported;
+    }
+    if (hdr->ncomp == 1) {
+        hdr->h[0] = hdr->v[0] = 1; // a one-component scan is never interleaved: MCU == one block
+    }
+    hdr->hmax = hdr->vmax = 1;
+    hdr->blocks_per_mcu = 0;
+    for (int c = 0; c < hdr->ncomp; ++c) {
+        if (hdr->h[c] > hdr->hmax)
+            hdr->hmax = hdr->h[c];
+        if (hdr->v[c] > hdr->vmax)
+            hdr->vmax = hdr->v[c];
+        hdr->blocks_per_mcu += hdr->h[c] * hdr->v[c];
+    }
+    if (hdr->blocks_per_mcu > kMaxBlocksPerMcu)
+        return kStreamCorrupt;
+    for (int c = 0; c < hdr->ncomp; ++c) {
+        if (!hdr->qt_present[hdr->tq[c]] || !hdr->huff[0][hdr->td[c]].present || !hdr->huff[1][hdr->ta[c]].present)
+            return kStreamCorrupt;
+        if (hdr->h[c] == 3 || hdr->v[c] == 3 || hdr->hmax % hdr->h[c] || hdr->vmax % hdr->v[c])
+            return kStreamUnsupported; // fractional upsampling ratios
+    }
+    hdr->mcus_x = (hdr->width + 8 * hdr->hmax - 1) / (8 * hdr->hmax);
+    hdr->mcus_y = (hdr->height + 8 * hdr->vmax - 1) / (8 * hdr->vmax);
+    if (hdr->scan_length == 0)
+        return kStreamCorrupt;
+    return kStreamOk;
+}
+
+void build_huff_table(const HuffSpec& spec, HuffTableDev* out)
+{
+    std::memset(out, 0, sizeof(*out));
+    std::memcpy(out->vals, spec.vals, 256);
+    int code = 0, k = 0;
+    for (int l = 1; l <= 16; ++l) {
+        out->valoff[l] = k - code;
+        const int cnt = spec.present ? spec.bits[l] : 0;
+        for (int i = 0; i < cnt; ++i, ++code, ++k) {
+            if (l <= kLutBits) {
+                const int first = code << (kLutBits - l);
+                const int span = 1 << (kLutBits - l);
+                const uint16_t e = uint16_t((l << 8) | spec.vals[k]);
+                for (int j = 0; j < span; ++j)
+                    out->lut[first + j] = e;
+            }
+        }
+        out->maxcode[l] = cnt ? code - 1 : -1;
+        code <<= 1;
+    }
+    out->maxcode[0] = -1;
+    out->maxcode[17] = 0x7fffffff;
+    out->valoff[0] = 0;
+    out->valoff[17] = 0;
+}
+
+uint64_t hash_huff_set(const StreamHeader& hdr)
+{
+    uint64_t hsh = 1469598103934665603ull;
+    auto mix = [&](const uint8_t* p, size_t n) {
+        for (size_t i = 0; i < n; ++i) {
+            hsh ^= p[i];
+            hsh *= 1099511628211ull;
+        }
+    };
+    for (int cls = 0; cls < 2; ++cls)
+        for (int id = 0; id < 2; ++id) {
+            const HuffSpec& s = hdr.huff[cls][id];
+            const uint8_t tag = s.present ? 1 : 0;
+            mix(&tag, 1);
+            if (s.present) {
+                mix(s.bits, 17);
+                mix(s.vals, 256);
+            }
+        }
+    return hsh;
+}
+
+void build_huff_set(const StreamHeader& hdr, HuffSetDev* out)
+{
+    for (int cls = 0; cls < 2; ++cls)
+        for (int id = 0; id < 2; ++id)
+            build_huff_table(hdr.huff[cls][id], &out->t[cls * 2 + id]);
+}
+
+} // namespace b200jpeg

@@ -1,0 +1,58 @@
+// Host-side JPEG marker walk and Huffman table preparation for the b200 decoder.
+//
+// The reference's built-in parser (src/parsers/jpeg.cpp:269-345) stops at SOS and
+// never reads DQT / DHT / DRI / the SOS component selectors, so the plugin does its
+// own walk here (T.81 B.2).  Nothing in this file touches the GPU.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+
+namespace b200jpeg {
+
+constexpr int kMaxComp = 4;
+constexpr int kMaxBlocksPerMcu = 10;
+constexpr int kLutBits = 12; // first-level Huffman lookup width
+
+enum StreamStatus { kStreamOk = 0, kStreamNotJpeg, kStreamUnsupported, kStreamCorrupt };
+
+struct HuffSpec {
+    uint8_t bits[17]; // bits[l] = number of codes of length l (1..16)
+    uint8_t vals[256];
+    bool present;
+};
+
+struct StreamHeader {
+    int width = 0, height = 0, ncomp = 0, precision = 0, sof = 0;
+    int comp_id[kMaxComp] = {0, 0, 0, 0};
+    int h[kMaxComp] = {0, 0, 0, 0}, v[kMaxComp] = {0, 0, 0, 0}, tq[kMaxComp] = {0, 0, 0, 0};
+    int td[kMaxComp] = {0, 0, 0, 0}, ta[kMaxComp] = {0, 0, 0, 0};
+    int hmax = 0, vmax = 0, mcus_x = 0, mcus_y = 0, blocks_per_mcu = 0;
+    int restart_interval = 0;
+    int nscans = 0;
+    size_t scan_offset = 0, scan_length = 0;
+    uint16_t qt[4][64]; // natural order
+    bool qt_present[4] = {false, false, false, false};
+    HuffSpec huff[2][4]; // [class][id]
+    int adobe_transform = -1;
+    bool has_jfif = false;
+};
+
+// Walks SOI..SOS, fills hdr, and decides whether the CUDA path handles the stream.
+StreamStatus parse_stream(const uint8_t* data, size_t len, StreamHeader* hdr);
+
+// Device-side Huffman table image (one per table; a "set" is DC0, DC1, AC0, AC1).
+struct alignas(16) HuffTableDev {
+    uint16_t lut[1 << kLutBits]; // (code_len << 8) | symbol ; 0 = longer than kLutBits or invalid
+    int32_t maxcode[18];         // maxcode[l] for l in 1..16 (canonical), -1 if none; [17] = sentinel
+    int32_t valoff[18];          // vals index = valoff[l] + code
+    uint8_t vals[256];
+};
+struct alignas(16) HuffSetDev {
+    HuffTableDev t[4]; // 0: DC id0, 1: DC id1, 2: AC id0, 3: AC id1
+};
+
+void build_huff_table(const HuffSpec& spec, HuffTableDev* out);
+uint64_t hash_huff_set(const StreamHeader& hdr);
+void build_huff_set(const StreamHeader& hdr, HuffSetDev* out);
+
+} // namespace b200jpeg

@@ -1,0 +1,990 @@
+// Hand-written sm_100a kernels of the b200 baseline-JPEG decode path.
+//
+//   K0  scan_count / scan_prefix / scan_scatter : marker + restart-interval scan, byte un-stuffing
+//   K1  huff_sync   : self-synchronising Huffman decode (state only), intra-sequence fixed point
+//   K2  verify_scan : sequence-boundary verification + segmented prefix pass (block index, DC predictors)
+//   K3  huff_write  : re-decode from verified states, scatter int16 coefficients
+//   K4a idct        : de-zigzag + dequantise + ISLOW 8x8 integer IDCT -> component planes
+//   K4b color       : chroma upsampling (fancy / box) + YCbCr->RGB + store into the caller's buffer
+//
+// They replace what the reference gets from libjpeg-turbo behind
+// extensions/libjpeg_turbo/jpeg_mem.cpp:102-463 (jdhuff / jidctint / jdsample / jdcolor);
+// the arithmetic is the one written out in SURVEY.md 8(c) and checked by oracle/jpeg_oracle.c.
+// No tensor cores: the work is bit-serial entropy decode and 8x8 integer butterflies.
+#include "kernels.cuh"
+
+namespace b200jpeg {
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// K0: marker scan + un-stuffing
+// ------------------------------------------------------------------------------------------------
+// Byte classes inside the entropy-coded segment (T.81 B.1.1.5, F.1.2.3):
+//   FF 00        -> data byte FF (the 00 is dropped)
+//   FF FF        -> the first FF is a fill byte (dropped)
+//   FF D0..D7    -> RSTm: both bytes dropped, a restart boundary sits here
+//   FF xx other  -> a real marker (EOI, ...): end of the entropy-coded segment
+struct ByteMasks {
+    uint32_t kept, rst, end;
+};
+
+__device__ __forceinline__ ByteMasks classify16(const uint8_t* __restrict__ raw, uint32_t len, uint32_t i0)
+{
+    ByteMasks m{0u, 0u, 0u};
+    if (i0 >= len)
+        return m;
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(raw + i0));
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t prv = i0 ? __ldg(raw + i0 - 1) : 0u;
+    const uint32_t after = (i0 + 16 < len) ? __ldg(raw + i0 + 16) : 0xD9u;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        const uint32_t cur = (w[j >> 2] >> (8 * (j & 3))) & 0xFFu;
+        uint32_t nxt = (j < 15) ? ((w[(j + 1) >> 2] >> (8 * ((j + 1) & 3))) & 0xFFu) : after;
+        if (i0 + j + 1 >= len)
+            nxt = 0xD9u;
+        const bool in = (i0 + j) < len;
+        const bool after_ff = (prv == 0xFFu);
+        const bool keep = (cur == 0xFFu) ? (nxt == 0u) : !after_ff;
+        const bool is_rst = after_ff && ((cur & 0xF8u) == 0xD0u);
+        const bool is_end = after_ff && cur != 0u && cur != 0xFFu && !is_rst;
+        if (in) {
+            m.kept |= uint32_t(keep) << j;
+            m.rst |= uint32_t(is_rst) << j;
+            m.end |= uint32_t(is_end) << j;
+        }
+        prv = cur;
+    }
+    return m;
+}
+
+__device__ __forceinline__ uint32_t block_min_u32(uint32_t v, uint32_t* s_tmp)
+{
+    v = __reduce_min_sync(0xffffffffu, v);
+    if (threadIdx.x == 0)
+        *s_tmp = 0xFFFFFFFFu;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0)
+        atomicMin(s_tmp, v);
+    __syncthreads();
+    return *s_tmp;
+}
+
+__global__ void __launch_bounds__(kScanThreads) scan_count_kernel(BatchDev bd)
+{
+    __shared__ uint32_t s_min, s_kept, s_rst;
+    const uint32_t tile = blockIdx.x;
+    const ImageDev& im = bd.img[bd.tile_img[tile]];
+    const uint8_t* raw = bd.raw + im.raw_off;
+    const uint32_t i0 = (tile - im.tile_off) * kScanTileBytes + threadIdx.x * 16;
+    const ByteMasks m = classify16(raw, im.raw_len, i0);
+    const uint32_t my_end = m.end ? (i0 + __ffs(m.end) - 1) : 0xFFFFFFFFu;
+    if (threadIdx.x == 0) {
+        s_kept = 0;
+        s_rst = 0;
+    }
+    const uint32_t e = block_min_u32(my_end, &s_min); // includes the barriers that publish s_kept/s_rst
+    uint32_t valid = 0xFFFFu;
+    if (e != 0xFFFFFFFFu)
+        valid = (e <= i0) ? 0u : ((e - i0 >= 16) ? 0xFFFFu : ((1u << (e - i0)) - 1u));
+    uint32_t k = __popc(m.kept & valid), r = __popc(m.rst & valid);
+    k = __reduce_add_sync(0xffffffffu, k);
+    r = __reduce_add_sync(0xffffffffu, r);
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&s_kept, k);
+        atomicAdd(&s_rst, r);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+        bd.tile_info[tile] = make_uint2(s_kept | (e != 0xFFFFFFFFu ? 0x80000000u : 0u), s_rst);
+}
+
+// One warp per image: exclusive prefix over its tiles, stops at the tile holding the end marker.
+__global__ void __launch_bounds__(128) scan_prefix_kernel(BatchDev bd)
+{
+    const int img = blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (img >= bd.n_images)
+        return;
+    const ImageDev& im = bd.img[img];
+    uint32_t carry_k = 0, carry_r = 0;
+    bool ended = false;
+    for (uint32_t c = 0; c < im.n_tiles; c += 32) {
+        const uint32_t t = c + lane;
+        uint2 info = make_uint2(0u, 0u);
+        if (t < im.n_tiles)
+            info = bd.tile_info[im.tile_off + t];
+        uint32_t k = info.x & 0x7FFFFFFFu, r = info.y;
+        const uint32_t endmask = __ballot_sync(0xffffffffu, (info.x >> 31) != 0u);
+        const int first_end = endmask ? (__ffs(endmask) - 1) : 32;
+        const bool live = !ended && lane <= first_end;
+        if (!live) {
+            k = 0;
+            r = 0;
+        }
+        uint32_t ik = k, ir = r;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t a = __shfl_up_sync(0xffffffffu, ik, d);
+            const uint32_t b = __shfl_up_sync(0xffffffffu, ir, d);
+            if (lane >= d) {
+                ik += a;
+                ir += b;
+            }
+        }
+        if (t < im.n_tiles)
+            bd.tile_base[im.tile_off + t] = live ? make_uint2(carry_k + ik - k, carry_r + ir - r) : make_uint2(0xFFFFFFFFu, 0u);
+        carry_k += __shfl_sync(0xffffffffu, ik, 31);
+        carry_r += __shfl_sync(0xffffffffu, ir, 31);
+        if (endmask)
+            ended = true;
+    }
+    if (lane == 0) {
+        ImageState st;
+        st.cmp_len = carry_k;
+        st.n_rst = carry_r;
+        st.flags = (carry_r != im.n_rst_expected) ? kFlagBadMarker : 0u;
+        st.n_sub = st.flags ? 0u : (carry_k * 8u + kSubseqBits - 1u) / kSubseqBits;
+        bd.state[img] = st;
+        const uint32_t slot = carry_r < im.n_bnd_cap ? carry_r : im.n_bnd_cap - 1;
+        bd.bnd[im.bnd_off + slot] = carry_k; // end of stream closes the last restart interval
+    }
+}
+
+__global__ void __launch_bounds__(kScanThreads) scan_scatter_kernel(BatchDev bd)
+{
+    __shared__ uint32_t s_min;
+    __shared__ uint32_t s_warp[kScanThreads / 32];
+    __shared__ __align__(16) uint8_t s_stage[kScanTileBytes];
+    const uint32_t tile = blockIdx.x;
+    const uint32_t img = bd.tile_img[tile];
+    const ImageDev& im = bd.img[img];
+    const uint2 base = bd.tile_base[tile];
+    if (base.x == 0xFFFFFFFFu)
+        return; // past the end marker
+    const uint8_t* raw = bd.raw + im.raw_off;
+    const uint32_t i0 = (tile - im.tile_off) * kScanTileBytes + threadIdx.x * 16;
+    const ByteMasks m = classify16(raw, im.raw_len, i0);
+    const uint32_t my_end = m.end ? (i0 + __ffs(m.end) - 1) : 0xFFFFFFFFu;
+    const uint32_t e = block_min_u32(my_end, &s_min);
+    uint32_t valid = 0xFFFFu;
+    if (e != 0xFFFFFFFFu)
+        valid = (e <= i0) ? 0u : ((e - i0 >= 16) ? 0xFFFFu : ((1u << (e - i0)) - 1u));
+    const uint32_t kept = m.kept & valid, rst = m.rst & valid;
+    // block-wide exclusive scan of (kept count | rst count << 16)
+    const uint32_t mine = __popc(kept) | (__popc(rst) << 16);
+    uint32_t inc = mine;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t a = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d)
+            inc += a;
+    }
+    if (lane == 31)
+        s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0, total = 0;
+#pragma unroll
+    for (int i = 0; i < kScanThreads / 32; ++i) {
+        const uint32_t v = s_warp[i];
+        if (i < warp)
+            woff += v;
+        total += v;
+    }
+    const uint32_t excl = woff + inc - mine;
+    uint32_t lk = excl & 0xFFFFu, lr = excl >> 16;
+    const uint32_t tile_kept = total & 0xFFFFu;
+    // stage kept bytes, record restart boundaries
+    if (kept | rst) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(raw + i0));
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const uint32_t cur = (w[j >> 2] >> (8 * (j & 3))) & 0xFFu;
+            if ((kept >> j) & 1u)
+                s_stage[lk++] = uint8_t(cur);
+            if ((rst >> j) & 1u) {
+                const uint32_t idx = base.y + lr++;
+                if (idx + 1 < im.n_bnd_cap)
+                    bd.bnd[im.bnd_off + idx] = base.x + lk;
+                if (cur != 0xD0u + (idx & 7u))
+                    atomicOr(&bd.state[img].flags, kFlagBadMarker);
+            }
+        }
+    }
+    __syncthreads();
+    // write out as big-endian 32-bit words (a little-endian word load then yields MSB-first bits)
+    uint32_t* dst32 = bd.cmp + im.cmp_off / 4;
+    uint8_t* dst8 = reinterpret_cast<uint8_t*>(dst32);
+    const uint32_t g0 = base.x, g1 = base.x + tile_kept;
+    const uint32_t w0 = (g0 + 3) / 4, w1 = g1 / 4;
+    if (w1 > w0) {
+        for (uint32_t wi = w0 + threadIdx.x; wi < w1; wi += kScanThreads) {
+            const uint32_t li = wi * 4 - g0;
+            dst32[wi] = (uint32_t(s_stage[li]) << 24) | (uint32_t(s_stage[li + 1]) << 16) | (uint32_t(s_stage[li + 2]) << 8) |
+                        uint32_t(s_stage[li + 3]);
+        }
+        const uint32_t head = w0 * 4 - g0, tail = g1 - w1 * 4; // < 4 each
+        if (threadIdx.x < head)
+            dst8[(g0 + threadIdx.x) ^ 3u] = s_stage[threadIdx.x];
+        if (threadIdx.x >= 32 && threadIdx.x - 32 < tail)
+            dst8[(w1 * 4 + threadIdx.x - 32) ^ 3u] = s_stage[w1 * 4 - g0 + threadIdx.x - 32];
+    } else {
+        for (uint32_t i = threadIdx.x; i < tile_kept; i += kScanThreads)
+            dst8[(g0 + i) ^ 3u] = s_stage[i];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1 / K3: Huffman decode of one subsequence
+// ------------------------------------------------------------------------------------------------
+// Decoder state at a subsequence boundary, packed in 32 bits:
+//   [0,6)  bit offset of the first code word past the boundary   [6,12) zig-zag index z
+//   [12,16) block-in-MCU index b                                  bit 16: end of stream reached
+constexpr uint32_t kStateDone = 1u << 16;
+
+struct DecodeResult {
+    uint32_t state;     // exit state
+    int32_t blk;        // block index at exit (relative to entry unless restarted, then absolute)
+    int32_t restarted;  // crossed at least one restart boundary
+    int32_t dc0, dc1, dc2;
+    uint32_t err;
+};
+
+struct StreamView {
+    const uint32_t* words;   // unstuffed stream (big-endian words)
+    const uint32_t* bnd;     // restart boundaries as byte positions, then end of stream
+    uint32_t nb;             // entries in bnd (>= 1)
+    uint32_t total_bits;
+    uint32_t bpm, blk_comp, blk_tab;
+    uint32_t ri_blocks;      // restart_interval * bpm
+    uint32_t total_blocks;
+};
+
+template <bool kWrite>
+__device__ __forceinline__ void decode_subsequence(const StreamView& sv, const HuffSetDev* __restrict__ hs, uint32_t k, uint32_t in_state,
+    int32_t blk, int32_t dc0, int32_t dc1, int32_t dc2, int16_t* __restrict__ coef, DecodeResult& out)
+{
+    out.err = 0;
+    out.restarted = 0;
+    if (in_state & kStateDone) {
+        out.state = kStateDone;
+        out.blk = blk;
+        out.dc0 = dc0;
+        out.dc1 = dc1;
+        out.dc2 = dc2;
+        return;
+    }
+    uint32_t p = k * kSubseqBits + (in_state & 63u);
+    uint32_t z = (in_state >> 6) & 63u;
+    uint32_t b = (in_state >> 12) & 15u;
+    const uint32_t end_bit = (k + 1) * kSubseqBits;
+    // first boundary strictly after p
+    uint32_t r = 0;
+    if (sv.nb > 1) {
+        uint32_t lo = 0, hi = sv.nb - 1; // bnd[nb-1]*8 == total_bits > p for every live thread
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(sv.bnd + mid) * 8u > p)
+                hi = mid;
+            else
+                lo = mid + 1;
+        }
+        r = lo;
+    }
+    uint32_t next_bnd = (r == sv.nb - 1) ? sv.total_bits : __ldg(sv.bnd + r) * 8u;
+    uint32_t widx = p >> 5;
+    uint32_t whi = __ldg(sv.words + widx), wlo = __ldg(sv.words + widx + 1);
+    uint32_t comp = (sv.blk_comp >> (2 * b)) & 3u;
+    const uint8_t* hbase = reinterpret_cast<const uint8_t*>(hs);
+    const HuffTableDev* dc_tab = reinterpret_cast<const HuffTableDev*>(hbase + ((sv.blk_tab >> b) & 1u) * sizeof(HuffTableDev));
+    const HuffTableDev* ac_tab = reinterpret_cast<const HuffTableDev*>(hbase + (2u + ((sv.blk_tab >> (16 + b)) & 1u)) * sizeof(HuffTableDev));
+    bool done = false;
+    for (;;) {
+        const uint32_t win = __funnelshift_l(wlo, whi, p & 31u);
+        // End of a restart interval (or of the stream): either the decoder already ran across the
+        // boundary (only an unsynchronised one can), or fewer than 8 bits remain and they are all
+        // 1-bits, i.e. the byte-alignment padding T.81 F.1.2.3 prescribes -- no complete code word
+        // fits there, because the all-ones code is never assigned.
+        if (p + 7u >= next_bnd) {
+            const uint32_t rem = next_bnd - p; // meaningful only when p < next_bnd
+            if (p >= next_bnd || (win >> (32u - rem)) == ((1u << rem) - 1u)) {
+                if (r == sv.nb - 1) {
+                    done = true;
+                    break;
+                }
+                p = next_bnd;
+                ++r;
+                next_bnd = (r == sv.nb - 1) ? sv.total_bits : __ldg(sv.bnd + r) * 8u;
+                if (kWrite && (z != 0u || b != 0u || uint32_t(blk) != r * sv.ri_blocks))
+                    out.err |= kFlagOverrun;
+                blk = int32_t(r * sv.ri_blocks);
+                out.restarted = 1;
+                z = 0;
+                b = 0;
+                dc0 = dc1 = dc2 = 0;
+                comp = sv.blk_comp & 3u;
+                dc_tab = reinterpret_cast<const HuffTableDev*>(hbase + (sv.blk_tab & 1u) * sizeof(HuffTableDev));
+                ac_tab = reinterpret_cast<const HuffTableDev*>(hbase + (2u + ((sv.blk_tab >> 16) & 1u)) * sizeof(HuffTableDev));
+                widx = p >> 5;
+                whi = __ldg(sv.words + widx);
+                wlo = __ldg(sv.words + widx + 1);
+                continue;
+            }
+        }
+        if (p >= end_bit)
+            break;
+        const HuffTableDev* tab = (z == 0u) ? dc_tab : ac_tab;
+        uint32_t e = tab->lut[win >> (32 - kLutBits)];
+        uint32_t len = e >> 8, sym = e & 0xFFu;
+        if (len == 0u) {
+            // code longer than the first-level table: canonical search (T.81 F.2.2.3)
+            len = 16;
+            sym = 0;
+            bool found = false;
+#pragma unroll
+            for (int l = kLutBits + 1; l <= 16; ++l) {
+                const int32_t code = int32_t(win >> (32 - l));
+                if (!found && code <= tab->maxcode[l]) {
+                    found = true;
+                    len = l;
+                    sym = tab->vals[(tab->valoff[l] + code) & 255];
+                }
+            }
+            if (!found)
+                out.err |= kFlagBadHuffman;
+        }
+        const uint32_t size = sym & 15u;
+        const uint32_t rest = win << len;
+        const uint32_t mag = __funnelshift_l(rest, 0u, size); // top `size` bits, 0 when size == 0
+        p += len + size;
+        if ((p >> 5) != widx) {
+            ++widx;
+            whi = wlo;
+            wlo = __ldg(sv.words + widx + 1);
+        }
+        if (z == 0u) {
+            const int32_t val = (rest >> 31) ? int32_t(mag) : int32_t(mag) - int32_t((1u << size) - 1u);
+            if (comp == 0u)
+                dc0 += val;
+            else if (comp == 1u)
+                dc1 += val;
+            else
+                dc2 += val;
+            if (kWrite) {
+                if (uint32_t(blk) < sv.total_blocks)
+                    coef[size_t(blk) * 64] = int16_t(comp == 0u ? dc0 : (comp == 1u ? dc1 : dc2));
+                else
+                    out.err |= kFlagOverrun;
+            }
+            z = 1;
+        } else {
+            const uint32_t run = sym >> 4;
+            if (size == 0u) {
+                z = (run == 15u) ? z + 16u : 64u;
+            } else {
+                z += run;
+                if (z > 63u) {
+                    out.err |= kFlagBadHuffman;
+                } else if (kWrite) {
+                    const int32_t val = (rest >> 31) ? int32_t(mag) : int32_t(mag) - int32_t((1u << size) - 1u);
+                    if (uint32_t(blk) < sv.total_blocks)
+                        coef[size_t(blk) * 64 + z] = int16_t(val);
+                }
+                ++z;
+            }
+        }
+        if (z > 63u) {
+            z = 0;
+            ++blk;
+            b = (b + 1u == sv.bpm) ? 0u : b + 1u;
+            comp = (sv.blk_comp >> (2 * b)) & 3u;
+            dc_tab = reinterpret_cast<const HuffTableDev*>(hbase + ((sv.blk_tab >> b) & 1u) * sizeof(HuffTableDev));
+            ac_tab = reinterpret_cast<const HuffTableDev*>(hbase + (2u + ((sv.blk_tab >> (16 + b)) & 1u)) * sizeof(HuffTableDev));
+        }
+    }
+    if (done) {
+        out.state = kStateDone;
+        if (kWrite && (z != 0u || uint32_t(blk) != sv.total_blocks))
+            out.err |= kFlagOverrun;
+    } else {
+        out.state = (p - end_bit) | (z << 6) | (b << 12);
+    }
+    out.blk = blk;
+    out.dc0 = dc0;
+    out.dc1 = dc1;
+    out.dc2 = dc2;
+}
+
+__device__ __forceinline__ void load_huff_set(HuffSetDev* s_hs, const HuffSetDev* g_hs)
+{
+    const uint4* src = reinterpret_cast<const uint4*>(g_hs);
+    uint4* dst = reinterpret_cast<uint4*>(s_hs);
+    for (uint32_t i = threadIdx.x; i < sizeof(HuffSetDev) / 16; i += blockDim.x)
+        dst[i] = __ldg(src + i);
+}
+
+__device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageDev& im, const ImageState& st)
+{
+    StreamView sv;
+    sv.words = bd.cmp + im.cmp_off / 4;
+    sv.bnd = bd.bnd + im.bnd_off;
+    sv.nb = st.n_rst + 1;
+    sv.total_bits = st.cmp_len * 8u;
+    sv.bpm = im.bpm;
+    sv.blk_comp = im.blk_comp;
+    sv.blk_tab = im.blk_tab;
+    sv.ri_blocks = im.restart_interval * im.bpm;
+    sv.total_blocks = im.total_blocks;
+    return sv;
+}
+
+// K1.  One CTA = kSeqStride consecutive subsequences of one image (+ kSeqWarm warm-up threads that
+// start earlier so the CTA's entry state is right with high probability).  Every thread decodes
+// its subsequence from a guessed state, then the CTA iterates "take the predecessor's exit state
+// as my entry state; re-decode if it changed" to a fixed point.  fix_mode: the first thread takes
+// the stored exit state of the previous sequence instead (used only for images K2 found dirty).
+__global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int mode)
+{
+    const bool fix_mode = (mode & 1) != 0;
+    const bool no_warm = (mode & 2) != 0; // test hook: start every sequence from the bare guess
+    extern __shared__ uint4 s_raw[];
+    HuffSetDev* s_hs = reinterpret_cast<HuffSetDev*>(s_raw);
+    uint32_t* s_out = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev));
+    const uint32_t seq = blockIdx.x;
+    const uint32_t img = bd.seq_img[seq];
+    const ImageDev& im = bd.img[img];
+    const ImageState st = bd.state[img];
+    if (st.n_sub == 0u || (fix_mode && !(st.flags & kFlagDirty)))
+        return;
+    const uint32_t first_k = (seq - im.seq_off) * kSeqStride;
+    if (first_k >= st.n_sub)
+        return;
+    load_huff_set(s_hs, bd.huff + im.huff_set);
+    const StreamView sv = make_view(bd, im, st);
+    const int t = threadIdx.x;
+    const int k = int(first_k) - kSeqWarm + t;
+    const bool skip_warm = fix_mode || no_warm;
+    const bool active = k >= 0 && k < int(st.n_sub) && (!skip_warm || t >= kSeqWarm);
+    const bool has_pred = active && t > 0 && k > 0 && (!skip_warm || t > kSeqWarm);
+    const uint32_t g = im.sub_off + uint32_t(k);
+    uint32_t in = 0; // true start state for k == 0, the guess "code word starts here, block start" otherwise
+    DecodeResult res;
+    res.state = kStateDone;
+    res.blk = 0;
+    res.restarted = 0;
+    res.dc0 = res.dc1 = res.dc2 = 0;
+    res.err = 0;
+    bool need = active;
+    bool decoded = false;
+    if (fix_mode && active) {
+        const uint32_t stored_in = bd.sub_in[g];
+        res.state = bd.sub_out[g];
+        if (t == kSeqWarm) {
+            in = (k > 0) ? bd.sub_out[g - 1] : 0u;
+            need = (in != stored_in);
+        } else {
+            in = stored_in;
+            need = false;
+        }
+    }
+    __syncthreads(); // tables loaded
+    for (;;) {
+        if (need) {
+            decode_subsequence<false>(sv, s_hs, uint32_t(k), in, 0, 0, 0, 0, nullptr, res);
+            decoded = true;
+        }
+        s_out[t] = res.state;
+        __syncthreads();
+        bool chg = false;
+        if (has_pred) {
+            const uint32_t nin = s_out[t - 1];
+            if (nin != in) {
+                in = nin;
+                chg = true;
+            }
+        }
+        need = chg;
+        if (!__syncthreads_or(chg))
+            break;
+    }
+    if (active && t >= kSeqWarm) {
+        if (decoded || !fix_mode) {
+            bd.sub_in[g] = in;
+            bd.sub_out[g] = res.state;
+            bd.sub_info[g] = make_int4(res.blk | (res.restarted ? int32_t(0x80000000u) : 0), res.dc0, res.dc1, res.dc2);
+        }
+    }
+}
+
+// K2.  One CTA per image: (a) every subsequence's entry state must equal its predecessor's exit
+// state (else the image is dirty and goes through the fix-up path), (b) segmented exclusive scan
+// of (block count, DC sums) where a restart boundary resets the running value.
+struct ScanElem {
+    int32_t f, blk, d0, d1, d2;
+};
+__device__ __forceinline__ ScanElem scan_combine(const ScanElem& a, const ScanElem& b)
+{
+    ScanElem r;
+    r.f = a.f | b.f;
+    r.blk = b.f ? b.blk : a.blk + b.blk;
+    r.d0 = b.f ? b.d0 : a.d0 + b.d0;
+    r.d1 = b.f ? b.d1 : a.d1 + b.d1;
+    r.d2 = b.f ? b.d2 : a.d2 + b.d2;
+    return r;
+}
+__device__ __forceinline__ ScanElem scan_shfl_up(const ScanElem& a, int d)
+{
+    ScanElem r;
+    r.f = __shfl_up_sync(0xffffffffu, a.f, d);
+    r.blk = __shfl_up_sync(0xffffffffu, a.blk, d);
+    r.d0 = __shfl_up_sync(0xffffffffu, a.d0, d);
+    r.d1 = __shfl_up_sync(0xffffffffu, a.d1, d);
+    r.d2 = __shfl_up_sync(0xffffffffu, a.d2, d);
+    return r;
+}
+
+__global__ void __launch_bounds__(256) verify_scan_kernel(BatchDev bd, int fix_mode)
+{
+    __shared__ ScanElem s_warp[8];
+    __shared__ ScanElem s_carry;
+    __shared__ uint32_t s_dirty;
+    const uint32_t img = blockIdx.x;
+    const ImageDev& im = bd.img[img];
+    const ImageState st = bd.state[img];
+    if (st.n_sub == 0u || (fix_mode && !(st.flags & kFlagDirty)))
+        return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) {
+        s_carry = ScanElem{0, 0, 0, 0, 0};
+        s_dirty = 0;
+    }
+    __syncthreads();
+    for (uint32_t c = 0; c < st.n_sub; c += 256) {
+        const uint32_t k = c + threadIdx.x;
+        ScanElem e{0, 0, 0, 0, 0};
+        if (k < st.n_sub) {
+            const uint32_t g = im.sub_off + k;
+            const uint32_t in = bd.sub_in[g];
+            const uint32_t want = k ? bd.sub_out[g - 1] : 0u;
+            if (in != want)
+                atomicOr(&s_dirty, 1u);
+            const int4 info = bd.sub_info[g];
+            e.f = (info.x < 0) ? 1 : 0;
+            e.blk = info.x & 0x7FFFFFFF;
+            e.d0 = info.y;
+            e.d1 = info.z;
+            e.d2 = info.w;
+        }
+        const ScanElem own = e;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const ScanElem o = scan_shfl_up(e, d);
+            if (lane >= d)
+                e = scan_combine(o, e);
+        }
+        if (lane == 31)
+            s_warp[warp] = e;
+        __syncthreads();
+        ScanElem pre = s_carry;
+        for (int i = 0; i < warp; ++i)
+            pre = scan_combine(pre, s_warp[i]);
+        // exclusive value = pre (+) inclusive-of-previous-lane
+        ScanElem prev = scan_shfl_up(e, 1);
+        ScanElem ex = (lane == 0) ? pre : scan_combine(pre, prev);
+        (void)own;
+        if (k < st.n_sub)
+            bd.sub_start[im.sub_off + k] = make_int4(ex.blk, ex.d0, ex.d1, ex.d2);
+        __syncthreads();
+        if (threadIdx.x == 255)
+            s_carry = scan_combine(pre, e);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        uint32_t f = st.flags & ~kFlagDirty;
+        if (s_dirty)
+            f |= kFlagDirty;
+        if (fix_mode)
+            f |= kFlagRedo; // its coefficients and pixels have to be produced again once it is clean
+        bd.state[img].flags = f;
+    }
+}
+
+// K3.  Same CTA shape as K1; every thread re-decodes its subsequence from the verified entry
+// state, now knowing its absolute block index and DC predictors, and scatters coefficients
+// (zig-zag order, MCU decode order, absolute DC) into the zeroed coefficient buffer.
+__global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, int redo_only)
+{
+    extern __shared__ uint4 s_raw[];
+    HuffSetDev* s_hs = reinterpret_cast<HuffSetDev*>(s_raw);
+    const uint32_t seq = blockIdx.x;
+    const uint32_t img = bd.seq_img[seq];
+    const ImageDev& im = bd.img[img];
+    const ImageState st = bd.state[img];
+    if (st.n_sub == 0u || (st.flags & kFlagDirty) || (redo_only && !(st.flags & kFlagRedo)))
+        return;
+    const uint32_t first_k = (seq - im.seq_off) * kSeqStride;
+    if (first_k >= st.n_sub)
+        return;
+    load_huff_set(s_hs, bd.huff + im.huff_set);
+    __syncthreads();
+    const int t = threadIdx.x;
+    const uint32_t k = first_k + uint32_t(t) - kSeqWarm;
+    if (t < kSeqWarm || k >= st.n_sub)
+        return;
+    const StreamView sv = make_view(bd, im, st);
+    const uint32_t g = im.sub_off + k;
+    const uint32_t in = bd.sub_in[g];
+    const int4 start = bd.sub_start[g];
+    DecodeResult res;
+    uint32_t err = 0;
+    if (!(in & kStateDone) && (uint32_t(start.x) % im.bpm) != ((in >> 12) & 15u)) {
+        err |= kFlagPhase;
+    } else {
+        decode_subsequence<true>(sv, s_hs, k, in, start.x, start.y, start.z, start.w, bd.coef + im.coef_off, res);
+        err |= res.err;
+    }
+    if (err)
+        atomicOr(&bd.state[img].flags, err);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4a: dequantise + ISLOW IDCT (jidctint.c arithmetic), one thread per 8x8 block
+// ------------------------------------------------------------------------------------------------
+template <int kShift>
+__device__ __forceinline__ void idct8(int32_t i0, int32_t i1, int32_t i2, int32_t i3, int32_t i4, int32_t i5, int32_t i6, int32_t i7,
+    int32_t* o)
+{
+    int32_t z1 = (i2 + i6) * 4433;
+    int32_t t2 = z1 - i6 * 15137;
+    int32_t t3 = z1 + i2 * 6270;
+    int32_t t0 = (i0 + i4) * 8192;
+    int32_t t1 = (i0 - i4) * 8192;
+    const int32_t a10 = t0 + t3, a13 = t0 - t3, a11 = t1 + t2, a12 = t1 - t2;
+    t0 = i7;
+    t1 = i5;
+    t2 = i3;
+    t3 = i1;
+    z1 = t0 + t3;
+    int32_t z2 = t1 + t2, z3 = t0 + t2, z4 = t1 + t3;
+    const int32_t z5 = (z3 + z4) * 9633;
+    t0 *= 2446;
+    t1 *= 16819;
+    t2 *= 25172;
+    t3 *= 12299;
+    z1 *= -7373;
+    z2 *= -20995;
+    z3 = z3 * -16069 + z5;
+    z4 = z4 * -3196 + z5;
+    t0 += z1 + z3;
+    t1 += z2 + z4;
+    t2 += z2 + z3;
+    t3 += z1 + z4;
+    constexpr int32_t rnd = 1 << (kShift - 1);
+    o[0] = (a10 + t3 + rnd) >> kShift;
+    o[7] = (a10 - t3 + rnd) >> kShift;
+    o[1] = (a11 + t2 + rnd) >> kShift;
+    o[6] = (a11 - t2 + rnd) >> kShift;
+    o[2] = (a12 + t1 + rnd) >> kShift;
+    o[5] = (a12 - t1 + rnd) >> kShift;
+    o[3] = (a13 + t0 + rnd) >> kShift;
+    o[4] = (a13 - t0 + rnd) >> kShift;
+}
+
+// libjpeg's range_limit table indexed with (x & 1023): clamp(x + 128) with a 10-bit wrap
+__device__ __forceinline__ uint32_t range_limit(int32_t x)
+{
+    const int32_t i = x & 1023;
+    return uint32_t(i < 128 ? i + 128 : (i < 512 ? 255 : (i < 896 ? 0 : i - 896)));
+}
+
+__global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
+{
+    __shared__ uint16_t s_q[3][64];
+    const uint32_t cta = blockIdx.x;
+    const uint32_t img = bd.idct_cta_img[cta];
+    const ImageDev& im = bd.img[img];
+    const uint32_t flags = bd.state[img].flags;
+    if ((flags & (kFlagDirty | kFlagBadMarker)) || (redo_only && !(flags & kFlagRedo)))
+        return;
+    for (int i = threadIdx.x; i < 3 * 64; i += blockDim.x)
+        s_q[i / 64][i % 64] = im.qt[i / 64][i % 64];
+    __syncthreads();
+    // block index over the planes of the needed components, row-major per plane
+    uint32_t idx = (cta - im.idct_cta_off) * blockDim.x + threadIdx.x;
+    int c = 0;
+    uint32_t bw = 0, bh = 0;
+    for (; c < im.ncomp_needed; ++c) {
+        bw = uint32_t(im.mcus_x) * im.h[c];
+        bh = uint32_t(im.mcus_y) * im.v[c];
+        if (idx < bw * bh)
+            break;
+        idx -= bw * bh;
+    }
+    if (c >= im.ncomp_needed)
+        return;
+    const uint32_t by = idx / bw, bx = idx - by * bw;
+    const uint32_t mx = bx / im.h[c], my = by / im.v[c];
+    const uint32_t bim = im.blk_first[c] + (by - my * im.v[c]) * im.h[c] + (bx - mx * im.h[c]);
+    const int16_t* src = bd.coef + im.coef_off + (size_t(my * im.mcus_x + mx) * im.bpm + bim) * 64;
+    // 64 coefficients, zig-zag order
+    int32_t zz[64];
+    {
+        const uint4* s4 = reinterpret_cast<const uint4*>(src);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint4 v = __ldg(s4 + i);
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                zz[i * 8 + 2 * j] = int32_t(int16_t(w[j] & 0xFFFFu));
+                zz[i * 8 + 2 * j + 1] = int32_t(int16_t(w[j] >> 16));
+            }
+        }
+    }
+    // zig-zag position of each natural-order index (inverse of T.81 Figure A.6)
+    constexpr int kZzPos[64] = {0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43, 9, 11, 18, 24,
+        31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60, 21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48,
+        49, 57, 58, 62, 63};
+    const uint16_t* q = s_q[c];
+    int32_t ws[64];
+    // pass 1: columns, results scaled up by 2^PASS1_BITS
+#pragma unroll
+    for (int x = 0; x < 8; ++x) {
+        int32_t col[8], o[8];
+#pragma unroll
+        for (int y = 0; y < 8; ++y)
+            col[y] = zz[kZzPos[y * 8 + x]] * int32_t(q[y * 8 + x]);
+        idct8<11>(col[0], col[1], col[2], col[3], col[4], col[5], col[6], col[7], o);
+#pragma unroll
+        for (int y = 0; y < 8; ++y)
+            ws[y * 8 + x] = o[y];
+    }
+    // pass 2: rows, descale by CONST_BITS + PASS1_BITS + 3, range-limit, store 8 bytes per row
+    uint8_t* dst = bd.planes + im.plane_off[c] + size_t(by) * 8 * (bw * 8) + bx * 8;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) {
+        int32_t o[8];
+        idct8<18>(ws[y * 8 + 0], ws[y * 8 + 1], ws[y * 8 + 2], ws[y * 8 + 3], ws[y * 8 + 4], ws[y * 8 + 5], ws[y * 8 + 6], ws[y * 8 + 7], o);
+        uint2 pk;
+        pk.x = range_limit(o[0]) | (range_limit(o[1]) << 8) | (range_limit(o[2]) << 16) | (range_limit(o[3]) << 24);
+        pk.y = range_limit(o[4]) | (range_limit(o[5]) << 8) | (range_limit(o[6]) << 16) | (range_limit(o[7]) << 24);
+        *reinterpret_cast<uint2*>(dst + size_t(y) * (bw * 8)) = pk;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4b: upsample + colour convert + store
+// ------------------------------------------------------------------------------------------------
+struct PlaneView {
+    const uint8_t* p;
+    int stride, dw, dh, hx, vx, fancy_h, fancy_v;
+};
+
+// libjpeg jdsample.c semantics: which of the triangle filters applies is decided
+// per component from its expansion factors; everything else replicates.
+__device__ __forceinline__ PlaneView make_plane(const BatchDev& bd, const ImageDev& im, int c)
+{
+    PlaneView pv;
+    pv.p = bd.planes + im.plane_off[c];
+    pv.stride = int(im.mcus_x) * im.h[c] * 8;
+    pv.dw = (int(im.width) * im.h[c] + im.hmax - 1) / im.hmax;
+    pv.dh = (int(im.height) * im.v[c] + im.vmax - 1) / im.vmax;
+    pv.hx = im.hmax / im.h[c];
+    pv.vx = im.vmax / im.v[c];
+    const bool f = im.fancy != 0;
+    const bool h2v1 = f && pv.hx == 2 && pv.vx == 1 && pv.dw > 2;
+    const bool h1v2 = f && pv.hx == 1 && pv.vx == 2;
+    const bool h2v2 = f && pv.hx == 2 && pv.vx == 2 && pv.dw > 2;
+    pv.fancy_h = h2v1 || h2v2;
+    pv.fancy_v = h1v2 || h2v2;
+    return pv;
+}
+
+__device__ __forceinline__ int sample_plane(const PlaneView& pv, int x, int y)
+{
+    if (pv.hx == 1 && pv.vx == 1)
+        return pv.p[size_t(y) * pv.stride + x];
+    if (!pv.fancy_h && !pv.fancy_v)
+        return pv.p[size_t(y / pv.vx) * pv.stride + x / pv.hx];
+    if (pv.fancy_h && !pv.fancy_v) { // h2v1
+        const uint8_t* s = pv.p + size_t(y) * pv.stride;
+        const int i = x >> 1, c = s[i];
+        if (x & 1)
+            return (i == pv.dw - 1) ? c : (3 * c + s[i + 1] + 2) >> 2;
+        return (i == 0) ? c : (3 * c + s[i - 1] + 1) >> 2;
+    }
+    const int i = y >> 1;
+    int nb = (y & 1) ? i + 1 : i - 1;
+    nb = nb < 0 ? 0 : (nb > pv.dh - 1 ? pv.dh - 1 : nb);
+    const uint8_t* s0 = pv.p + size_t(i) * pv.stride;
+    const uint8_t* s1 = pv.p + size_t(nb) * pv.stride;
+    if (!pv.fancy_h) // h1v2
+        return (3 * s0[x] + s1[x] + ((y & 1) ? 2 : 1)) >> 2;
+    const int j = x >> 1; // h2v2
+    const int cur = 3 * s0[j] + s1[j];
+    if (x & 1) {
+        if (j == pv.dw - 1)
+            return (cur * 4 + 7) >> 4;
+        return (3 * cur + 3 * s0[j + 1] + s1[j + 1] + 7) >> 4;
+    }
+    if (j == 0)
+        return (cur * 4 + 8) >> 4;
+    return (3 * cur + 3 * s0[j - 1] + s1[j - 1] + 8) >> 4;
+}
+
+__device__ __forceinline__ uint32_t clamp255(int v) { return uint32_t(v < 0 ? 0 : (v > 255 ? 255 : v)); }
+
+// jdcolor.c fixed-point YCbCr -> RGB (SURVEY.md 8c "Colour")
+__device__ __forceinline__ void ycc_to_rgb(int y, int cb, int cr, uint32_t& r, uint32_t& g, uint32_t& b)
+{
+    cb -= 128;
+    cr -= 128;
+    r = clamp255(y + ((91881 * cr + 32768) >> 16));
+    g = clamp255(y + ((-22554 * cb - 46802 * cr + 32768) >> 16));
+    b = clamp255(y + ((116130 * cb + 32768) >> 16));
+}
+
+constexpr int kColorTx = 64; // threads in x, 4 pixels each
+constexpr int kColorTy = 4;
+
+__global__ void __launch_bounds__(kColorTx* kColorTy) color_kernel(BatchDev bd, int redo_only)
+{
+    const uint32_t cta = blockIdx.x;
+    const uint32_t img = bd.color_cta_img[cta];
+    const ImageDev& im = bd.img[img];
+    const uint32_t flags = bd.state[img].flags;
+    if ((flags & (kFlagDirty | kFlagBadMarker)) || (redo_only && !(flags & kFlagRedo)))
+        return;
+    const uint32_t local = cta - im.color_cta_off;
+    const uint32_t cy = local / im.n_color_cta_x, cx = local - cy * im.n_color_cta_x;
+    const int rw = int(im.roi_x1) - int(im.roi_x0), rh = int(im.roi_y1) - int(im.roi_y0);
+    const int ox = (cx * kColorTx + (threadIdx.x % kColorTx)) * 4;
+    const int oy = cy * kColorTy + threadIdx.x / kColorTx;
+    if (ox >= rw || oy >= rh)
+        return;
+    const int n = (rw - ox) < 4 ? (rw - ox) : 4;
+    const int y = oy + im.roi_y0;
+    const PlaneView p0 = make_plane(bd, im, 0);
+    uint32_t px[4][3];
+    if (im.fmt == kFmtY || im.ncomp == 1) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t v = (i < n) ? uint32_t(sample_plane(p0, ox + i + im.roi_x0, y)) : 0u;
+            px[i][0] = px[i][1] = px[i][2] = v;
+        }
+    } else {
+        const PlaneView p1 = make_plane(bd, im, 1), p2 = make_plane(bd, im, 2);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int x = ox + (i < n ? i : 0) + im.roi_x0;
+            ycc_to_rgb(sample_plane(p0, x, y), sample_plane(p1, x, y), sample_plane(p2, x, y), px[i][0], px[i][1], px[i][2]);
+        }
+    }
+    const bool swap = (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR);
+    if (swap) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t t = px[i][0];
+            px[i][0] = px[i][2];
+            px[i][2] = t;
+        }
+    }
+    if (im.fmt == kFmtY || im.fmt == kFmtPRGB || im.fmt == kFmtPBGR) {
+        const int nch = (im.fmt == kFmtY) ? 1 : 3;
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            if (ch < nch) {
+                uint8_t* o = im.out + size_t(ch) * im.plane_stride + size_t(oy) * im.row_stride + ox;
+                if (n == 4 && ((reinterpret_cast<uintptr_t>(o) & 3u) == 0)) {
+                    *reinterpret_cast<uint32_t*>(o) = px[0][ch] | (px[1][ch] << 8) | (px[2][ch] << 16) | (px[3][ch] << 24);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if (i < n)
+                            o[i] = uint8_t(px[i][ch]);
+                }
+            }
+        }
+        return;
+    }
+    uint8_t* o = im.out + size_t(oy) * im.row_stride + size_t(ox) * 3;
+    if (n == 4 && ((reinterpret_cast<uintptr_t>(o) & 3u) == 0)) {
+        uint32_t* o32 = reinterpret_cast<uint32_t*>(o);
+        o32[0] = px[0][0] | (px[0][1] << 8) | (px[0][2] << 16) | (px[1][0] << 24);
+        o32[1] = px[1][1] | (px[1][2] << 8) | (px[2][0] << 16) | (px[2][1] << 24);
+        o32[2] = px[2][2] | (px[3][0] << 8) | (px[3][1] << 16) | (px[3][2] << 24);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (i < n) {
+                o[3 * i + 0] = uint8_t(px[i][0]);
+                o[3 * i + 1] = uint8_t(px[i][1]);
+                o[3 * i + 2] = uint8_t(px[i][2]);
+            }
+    }
+}
+
+constexpr size_t kSyncSmem = sizeof(HuffSetDev) + kSeqThreads * sizeof(uint32_t);
+
+} // namespace
+
+int launch_scan(const BatchDev& b, cudaStream_t s)
+{
+    if (b.n_tiles == 0)
+        return 0;
+    scan_count_kernel<<<b.n_tiles, kScanThreads, 0, s>>>(b);
+    scan_prefix_kernel<<<(b.n_images + 3) / 4, 128, 0, s>>>(b);
+    scan_scatter_kernel<<<b.n_tiles, kScanThreads, 0, s>>>(b);
+    return 3;
+}
+
+int launch_sync(const BatchDev& b, bool fix_mode, bool no_warm, cudaStream_t s)
+{
+    if (b.n_seq == 0)
+        return 0;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(huff_sync_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSyncSmem));
+        cudaFuncSetAttribute(huff_write_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HuffSetDev)));
+        attr_set = true;
+    }
+    huff_sync_kernel<<<b.n_seq, kSeqThreads, kSyncSmem, s>>>(b, (fix_mode ? 1 : 0) | (no_warm ? 2 : 0));
+    return 1;
+}
+
+int launch_verify_scan(const BatchDev& b, bool fix_mode, cudaStream_t s)
+{
+    if (b.n_images == 0)
+        return 0;
+    verify_scan_kernel<<<b.n_images, 256, 0, s>>>(b, fix_mode ? 1 : 0);
+    return 1;
+}
+
+int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s)
+{
+    if (b.n_seq == 0)
+        return 0;
+    huff_write_kernel<<<b.n_seq, kSeqThreads, sizeof(HuffSetDev), s>>>(b, redo_only ? 1 : 0);
+    return 1;
+}
+
+int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s)
+{
+    if (b.n_idct_cta == 0)
+        return 0;
+    idct_kernel<<<b.n_idct_cta, 128, 0, s>>>(b, redo_only ? 1 : 0);
+    return 1;
+}
+
+int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s)
+{
+    if (b.n_color_cta == 0)
+        return 0;
+    color_kernel<<<b.n_color_cta, kColorTx * kColorTy, 0, s>>>(b, redo_only ? 1 : 0);
+    return 1;
+}
+
+} // namespace b200jpeg

@@ -1,0 +1,106 @@
+// Device-side data layout shared by the kernels (kernels.cu) and the batch
+// orchestration (decoder.cpp).  See DESIGN.md "Data layout in HBM".
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "jpeg_stream.h"
+
+namespace b200jpeg {
+
+// ---- entropy-stage geometry
+constexpr int kScanTileBytes = 4096;  // K0: bytes of byte-stuffed scan data per CTA
+constexpr int kScanThreads = 256;     // 16 B per thread
+constexpr int kSubseqBits = 1024;     // K1-K3: bits of unstuffed stream per thread ("subsequence")
+constexpr int kSubseqBytes = kSubseqBits / 8;
+constexpr int kSeqThreads = 256;      // threads per CTA ("sequence")
+constexpr int kSeqWarm = 8;           // leading threads that only warm up the entry state
+constexpr int kSeqStride = kSeqThreads - kSeqWarm;
+
+// ---- per-image error / state flags (ImageState::flags)
+enum : uint32_t {
+    kFlagBadMarker = 1u << 0,   // RST out of sequence / wrong restart count
+    kFlagBadHuffman = 1u << 1,  // invalid code met by a synchronised decoder
+    kFlagOverrun = 1u << 2,     // coefficient positions ran past the image or ended short
+    kFlagDirty = 1u << 3,       // sequence entry states not yet consistent (needs the fix-up path)
+    kFlagPhase = 1u << 4,       // prefix-summed block index disagrees with the decoder's MCU phase
+    kFlagRedo = 1u << 5         // went through the fix-up path: coefficients / pixels must be produced again
+};
+
+// Output formats (same values as include/b200jpeg.h)
+enum : int { kFmtIRGB = 0, kFmtIBGR = 1, kFmtPRGB = 2, kFmtPBGR = 3, kFmtY = 4 };
+
+struct ImageDev {
+    // stream geometry
+    uint64_t raw_off;   // bytes into the raw (byte-stuffed) arena, 16-aligned
+    uint64_t cmp_off;   // bytes into the unstuffed arena, 16-aligned
+    uint64_t coef_off;  // int16 elements into the coefficient arena
+    uint64_t plane_off[3]; // bytes into the plane arena
+    uint32_t raw_len;
+    uint32_t tile_off, n_tiles;     // K0 tiles
+    uint32_t sub_off, n_sub_max;    // subsequences (upper bound from the stuffed length)
+    uint32_t seq_off, n_seq;        // sequences (CTAs of the entropy kernels)
+    uint32_t bnd_off, n_bnd_cap;    // restart boundaries (+ end of stream)
+    uint32_t restart_interval;      // MCUs, 0 = none
+    uint32_t n_rst_expected;
+    uint32_t total_blocks;          // n_mcu * blocks_per_mcu
+    uint32_t huff_set;
+    uint32_t blk_comp;              // 2 bits per block-in-MCU: component
+    uint32_t blk_tab;               // bit b: DC table id of block b, bit 16+b: AC table id
+    uint32_t idct_cta_off, n_idct_cta;
+    uint32_t color_cta_off, n_color_cta_x, n_color_cta_y;
+    uint16_t width, height, mcus_x, mcus_y;
+    uint8_t ncomp, hmax, vmax, bpm;
+    uint8_t h[3], v[3];
+    uint8_t blk_first[3];           // first block-in-MCU index of each component
+    uint8_t ncomp_needed;           // 1 when only luma is consumed (Y output)
+    uint16_t qt[3][64];             // natural order, per component
+    // output
+    uint8_t* out;
+    uint64_t plane_stride;          // bytes between planes of planar output
+    uint32_t row_stride;
+    uint16_t roi_x0, roi_y0, roi_x1, roi_y1;
+    uint8_t fmt, fancy;
+};
+
+struct ImageState {
+    uint32_t cmp_len;  // unstuffed bytes
+    uint32_t n_rst;    // RST markers found
+    uint32_t n_sub;    // ceil(cmp_len*8 / kSubseqBits)
+    uint32_t flags;
+};
+
+// All device pointers of one prepared batch.
+struct BatchDev {
+    int n_images;
+    const ImageDev* img;
+    ImageState* state;
+    const uint8_t* raw;
+    uint32_t* cmp;          // unstuffed stream, big-endian 32-bit words
+    uint2* tile_info;       // K0a: x = kept | end<<31, y = rst count
+    uint2* tile_base;       // K0b: exclusive prefix (x = kept or 0xFFFFFFFF if past the end, y = rst)
+    const uint32_t* tile_img; // tile -> image
+    uint32_t* bnd;          // restart boundaries (unstuffed byte positions) then end of stream
+    const uint32_t* seq_img;  // sequence -> image
+    uint32_t* sub_in;       // entry state per subsequence
+    uint32_t* sub_out;      // exit state per subsequence
+    int4* sub_info;         // x = block delta (or absolute | 1<<31 after a restart), yzw = DC diff sums
+    int4* sub_start;        // exclusive scan: x = absolute block index at entry, yzw = DC predictors
+    const HuffSetDev* huff;
+    int16_t* coef;
+    uint8_t* planes;
+    const uint32_t* idct_cta_img;
+    const uint32_t* color_cta_img;
+    int n_tiles, n_seq, n_sub, n_idct_cta, n_color_cta;
+};
+
+// Kernel launchers (kernels.cu).  Each returns the number of kernels it launched.
+int launch_scan(const BatchDev& b, cudaStream_t s);                 // K0a, K0b, K0c
+int launch_sync(const BatchDev& b, bool fix_mode, bool no_warm, cudaStream_t s); // K1 (first pass or fix-up pass)
+int launch_verify_scan(const BatchDev& b, bool fix_mode, cudaStream_t s); // K2
+int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s);  // K3
+int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s);   // K4a
+int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s);  // K4b
+
+} // namespace b200jpeg
