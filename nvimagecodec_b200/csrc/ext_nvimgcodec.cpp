@@ -1,0 +1,427 @@
+// nvImageCodec extension adapter: registers the b200 JPEG decoder through the reference's
+// C extension ABI so that nvimgcodecDecoderDecode / nvimgcodec.Decoder / nvimtrans pick it up
+// by codec priority with no caller changes.
+//
+//   entry point        nvimgcodecExtensionModuleEntry            include/nvimgcodec.h:1696
+//   extension desc     nvimgcodecExtensionDesc_t                 include/nvimgcodec.h:1652-1680
+//   decoder desc       nvimgcodecDecoderDesc_t                   include/nvimgcodec.h:1438-1542
+//   behaviour mirrored extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:110-212 (canDecode),
+//                      :295-420 (decode); batched shape as extensions/nvjpeg/hw_decoder.cpp:636-888
+//
+// The adapter only translates descriptors; all work happens in b200jpeg::Decoder (decoder.cpp),
+// the same object the plain C ABI (include/b200jpeg.h) drives.
+#include <nvimgcodec.h>
+
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <sstream>
+#include <string>
+#include <vector>
+
+#include "b200jpeg.h"
+#include "decoder.h"
+
+namespace {
+
+constexpr const char* kExtensionId = "b200_jpeg_ext";
+constexpr const char* kDecoderId = "b200_jpeg_decoder";
+constexpr float kPriority = 50.0f;      // ahead of nvjpeg HW (100), nvjpeg CUDA (200), libjpeg_turbo (300)
+constexpr int kMiniBatch = 65536;       // keeps the framework's first-batch share cap from ever biting
+
+void log_msg(const nvimgcodecFrameworkDesc_t* fw, nvimgcodecDebugMessageSeverity_t sev, const std::string& msg)
+{
+    if (!fw || !fw->log)
+        return;
+    nvimgcodecDebugMessageData_t data{};
+    data.struct_type = NVIMGCODEC_STRUCTURE_TYPE_DEBUG_MESSAGE_DATA;
+    data.struct_size = sizeof(data);
+    data.message = msg.c_str();
+    data.codec_id = kDecoderId;
+    data.codec_version = NVIMGCODEC_VER;
+    fw->log(fw->instance, sev, NVIMGCODEC_DEBUG_MESSAGE_CATEGORY_GENERAL, &data);
+}
+
+struct MappedStream {
+    const uint8_t* data = nullptr;
+    size_t size = 0;
+    std::vector<uint8_t> owned; // used when the io stream cannot be mapped
+};
+
+bool map_stream(const nvimgcodecCodeStreamDesc_t* cs, MappedStream* out)
+{
+    nvimgcodecIoStreamDesc_t* io = cs ? cs->io_stream : nullptr;
+    if (!io)
+        return false;
+    size_t size = 0;
+    if (io->size(io->instance, &size) != NVIMGCODEC_STATUS_SUCCESS || size == 0)
+        return false;
+    void* ptr = nullptr;
+    if (io->map && io->map(io->instance, &ptr, 0, size) == NVIMGCODEC_STATUS_SUCCESS && ptr) {
+        out->data = static_cast<const uint8_t*>(ptr);
+        out->size = size;
+        return true;
+    }
+    out->owned.resize(size);
+    size_t got = 0;
+    if (io->seek(io->instance, 0, SEEK_SET) != NVIMGCODEC_STATUS_SUCCESS)
+        return false;
+    if (io->read(io->instance, &got, out->owned.data(), size) != NVIMGCODEC_STATUS_SUCCESS || got != size)
+        return false;
+    out->data = out->owned.data();
+    out->size = size;
+    return true;
+}
+
+// Translate the requested nvimgcodecImageInfo_t into a b200jpegOutput_t.  Returns a processing
+// status: SUCCESS or an OR of the *_UNSUPPORTED bits (include/nvimgcodec.h:735-768).
+nvimgcodecProcessingStatus_t translate_output(const nvimgcodecImageInfo_t& info, const nvimgcodecRegion_t* region, int img_w, int img_h,
+    b200jpegOutput_t* out)
+{
+    nvimgcodecProcessingStatus_t st = NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+    std::memset(out, 0, sizeof(*out));
+    int want_planes = 1, want_channels = 3;
+    switch (info.sample_format) {
+    case NVIMGCODEC_SAMPLEFORMAT_I_RGB: out->format = B200JPEG_FMT_I_RGB; break;
+    case NVIMGCODEC_SAMPLEFORMAT_I_BGR: out->format = B200JPEG_FMT_I_BGR; break;
+    case NVIMGCODEC_SAMPLEFORMAT_P_RGB:
+        out->format = B200JPEG_FMT_P_RGB;
+        want_planes = 3;
+        want_channels = 1;
+        break;
+    case NVIMGCODEC_SAMPLEFORMAT_P_BGR:
+        out->format = B200JPEG_FMT_P_BGR;
+        want_planes = 3;
+        want_channels = 1;
+        break;
+    case NVIMGCODEC_SAMPLEFORMAT_P_Y:
+    case NVIMGCODEC_SAMPLEFORMAT_I_Y:
+        out->format = B200JPEG_FMT_Y;
+        want_channels = 1;
+        break;
+    case NVIMGCODEC_SAMPLEFORMAT_I_UNCHANGED: // "as stored": RGB for colour streams, Y for gray ones
+        out->format = info.plane_info[0].num_channels == 1 ? B200JPEG_FMT_Y : B200JPEG_FMT_I_RGB;
+        want_channels = info.plane_info[0].num_channels == 1 ? 1 : 3;
+        break;
+    case NVIMGCODEC_SAMPLEFORMAT_P_UNCHANGED:
+        out->format = info.num_planes == 1 ? B200JPEG_FMT_Y : B200JPEG_FMT_P_RGB;
+        want_planes = info.num_planes == 1 ? 1 : 3;
+        want_channels = 1;
+        break;
+    default: st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLE_FORMAT_UNSUPPORTED; break;
+    }
+    if (info.num_planes != uint32_t(want_planes))
+        st |= NVIMGCODEC_PROCESSING_STATUS_NUM_PLANES_UNSUPPORTED;
+    if (info.plane_info[0].num_channels != uint32_t(want_channels))
+        st |= NVIMGCODEC_PROCESSING_STATUS_NUM_CHANNELS_UNSUPPORTED;
+    if (info.plane_info[0].sample_type != NVIMGCODEC_SAMPLE_DATA_TYPE_UINT8)
+        st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLE_TYPE_UNSUPPORTED;
+    int rw = img_w, rh = img_h;
+    if (region && region->ndim != 0) {
+        if (region->ndim != 2) {
+            st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED;
+        } else {
+            // start/end are [y, x] (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:359-362)
+            const int y0 = region->start[0], x0 = region->start[1], y1 = region->end[0], x1 = region->end[1];
+            if (y0 < 0 || x0 < 0 || y1 > img_h || x1 > img_w || y0 >= y1 || x0 >= x1) {
+                st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED; // out-of-bounds ROI: declined like libjpeg_turbo_ext (:154-157)
+            } else {
+                out->roi_x0 = x0;
+                out->roi_y0 = y0;
+                out->roi_x1 = x1;
+                out->roi_y1 = y1;
+                rw = x1 - x0;
+                rh = y1 - y0;
+            }
+        }
+    }
+    if (int(info.plane_info[0].width) < rw || int(info.plane_info[0].height) < rh)
+        st |= NVIMGCODEC_PROCESSING_STATUS_RESOLUTION_UNSUPPORTED;
+    out->buffer = info.buffer;
+    out->buffer_is_host = (info.buffer_kind == NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_HOST) ? 1 : 0;
+    out->row_stride = info.plane_info[0].row_stride;
+    // planes of a planar image lie back to back at row_stride*height (extensions/nvjpeg/cuda_decoder.cpp:716-722);
+    // the kernels assume exactly that with height == ROI height
+    if (want_planes == 3 && int(info.plane_info[0].height) != rh)
+        st |= NVIMGCODEC_PROCESSING_STATUS_RESOLUTION_UNSUPPORTED;
+    return st;
+}
+
+nvimgcodecProcessingStatus_t to_processing_status(int b200_status)
+{
+    switch (b200_status) {
+    case B200JPEG_OK: return NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+    case B200JPEG_ERR_UNSUPPORTED:
+    case B200JPEG_ERR_TOO_LARGE: return NVIMGCODEC_PROCESSING_STATUS_CODESTREAM_UNSUPPORTED;
+    case B200JPEG_ERR_CORRUPT:
+    case B200JPEG_ERR_NOT_JPEG: return NVIMGCODEC_PROCESSING_STATUS_IMAGE_CORRUPTED;
+    default: return NVIMGCODEC_PROCESSING_STATUS_FAIL;
+    }
+}
+
+class DecoderImpl {
+  public:
+    DecoderImpl(const nvimgcodecFrameworkDesc_t* fw, const nvimgcodecExecutionParams_t* ep, const char* options)
+        : fw_(fw)
+        , ep_(ep)
+        , opt_(b200jpeg::parse_options(options, kDecoderId))
+    {
+        int n = 1;
+        if (ep_->executor && ep_->executor->getNumThreads)
+            n = ep_->executor->getNumThreads(ep_->executor->instance) + 1;
+        cores_.resize(size_t(n) + 1);
+    }
+
+    nvimgcodecProcessingStatus_t can_decode(const nvimgcodecImageDesc_t* image, const nvimgcodecCodeStreamDesc_t* cs,
+        const nvimgcodecDecodeParams_t* params)
+    {
+        if (!image || !cs || !params)
+            return NVIMGCODEC_PROCESSING_STATUS_FAIL;
+        nvimgcodecJpegImageInfo_t jpeg_info{NVIMGCODEC_STRUCTURE_TYPE_JPEG_IMAGE_INFO, sizeof(nvimgcodecJpegImageInfo_t), nullptr};
+        nvimgcodecImageInfo_t cs_info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), &jpeg_info};
+        if (cs->getImageInfo(cs->instance, &cs_info) != NVIMGCODEC_STATUS_SUCCESS)
+            return NVIMGCODEC_PROCESSING_STATUS_FAIL;
+        if (std::strcmp(cs_info.codec_name, "jpeg") != 0)
+            return NVIMGCODEC_PROCESSING_STATUS_CODEC_UNSUPPORTED;
+        if (jpeg_info.encoding != NVIMGCODEC_JPEG_ENCODING_BASELINE_DCT)
+            return NVIMGCODEC_PROCESSING_STATUS_ENCODING_UNSUPPORTED;
+        nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
+        if (image->getImageInfo(image->instance, &info) != NVIMGCODEC_STATUS_SUCCESS)
+            return NVIMGCODEC_PROCESSING_STATUS_FAIL;
+        nvimgcodecCodeStreamInfo_t csi{NVIMGCODEC_STRUCTURE_TYPE_CODE_STREAM_INFO, sizeof(nvimgcodecCodeStreamInfo_t), nullptr};
+        if (cs->getCodeStreamInfo(cs->instance, &csi) != NVIMGCODEC_STATUS_SUCCESS)
+            return NVIMGCODEC_PROCESSING_STATUS_FAIL;
+        nvimgcodecProcessingStatus_t st = NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+        const nvimgcodecRegion_t* region = nullptr;
+        if (csi.code_stream_view) {
+            if (csi.code_stream_view->image_idx != 0)
+                st |= NVIMGCODEC_PROCESSING_STATUS_NUM_IMAGES_UNSUPPORTED;
+            region = &csi.code_stream_view->region;
+        }
+        b200jpegOutput_t out;
+        st |= translate_output(info, region, int(cs_info.plane_info[0].width), int(cs_info.plane_info[0].height), &out);
+        if (params->apply_exif_orientation && (info.orientation.flip_x || info.orientation.flip_y || info.orientation.rotated != 0))
+            st |= NVIMGCODEC_PROCESSING_STATUS_ORIENTATION_UNSUPPORTED;
+        if (st != NVIMGCODEC_PROCESSING_STATUS_SUCCESS)
+            return st;
+        // stream-level acceptance: our own marker walk (the built-in parser stops before DQT/DHT/DRI/SOS)
+        MappedStream ms;
+        if (!map_stream(cs, &ms))
+            return NVIMGCODEC_PROCESSING_STATUS_FAIL;
+        b200jpegStreamInfo_t si;
+        const int rc = b200jpegProbe(ms.data, ms.size, &si);
+        if (rc == B200JPEG_OK)
+            return NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+        if (rc == B200JPEG_ERR_CORRUPT || rc == B200JPEG_ERR_NOT_JPEG)
+            return NVIMGCODEC_PROCESSING_STATUS_IMAGE_CORRUPTED;
+        return NVIMGCODEC_PROCESSING_STATUS_CODESTREAM_UNSUPPORTED;
+    }
+
+    // Shared by decodeBatch (thread_idx 0, whole batch on one framework stream) and the per-sample
+    // decode safety net (one core per executor thread).
+    nvimgcodecStatus_t decode_batch(const nvimgcodecImageDesc_t** images, const nvimgcodecCodeStreamDesc_t** css, int n, int thread_idx)
+    {
+        if (n <= 0)
+            return NVIMGCODEC_STATUS_SUCCESS;
+        b200jpeg::Decoder* core = core_for(thread_idx);
+        if (!core) {
+            for (int i = 0; i < n; ++i)
+                images[i]->imageReady(images[i]->instance, NVIMGCODEC_PROCESSING_STATUS_FAIL);
+            return NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+        }
+        std::vector<MappedStream> streams(n);
+        std::vector<const void*> data(n, nullptr);
+        std::vector<size_t> len(n, 0);
+        std::vector<b200jpegOutput_t> outs(n);
+        std::vector<nvimgcodecProcessingStatus_t> pre(n, NVIMGCODEC_PROCESSING_STATUS_SUCCESS);
+        std::vector<int> status(n, B200JPEG_ERR_STATE);
+        cudaStream_t stream = nullptr;
+        bool have_stream = false;
+        for (int i = 0; i < n; ++i) {
+            nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
+            nvimgcodecImageInfo_t cs_info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
+            nvimgcodecCodeStreamInfo_t csi{NVIMGCODEC_STRUCTURE_TYPE_CODE_STREAM_INFO, sizeof(nvimgcodecCodeStreamInfo_t), nullptr};
+            if (images[i]->getImageInfo(images[i]->instance, &info) != NVIMGCODEC_STATUS_SUCCESS ||
+                css[i]->getImageInfo(css[i]->instance, &cs_info) != NVIMGCODEC_STATUS_SUCCESS ||
+                css[i]->getCodeStreamInfo(css[i]->instance, &csi) != NVIMGCODEC_STATUS_SUCCESS || !map_stream(css[i], &streams[i])) {
+                pre[i] = NVIMGCODEC_PROCESSING_STATUS_FAIL;
+                std::memset(&outs[i], 0, sizeof(outs[i]));
+                continue;
+            }
+            if (!have_stream) {
+                stream = info.cuda_stream; // every sample of a batch shares the framework's stream (hw_decoder.cpp:687-697)
+                have_stream = true;
+            }
+            const nvimgcodecRegion_t* region = csi.code_stream_view ? &csi.code_stream_view->region : nullptr;
+            pre[i] = translate_output(info, region, int(cs_info.plane_info[0].width), int(cs_info.plane_info[0].height), &outs[i]);
+            if (pre[i] == NVIMGCODEC_PROCESSING_STATUS_SUCCESS) {
+                data[i] = streams[i].data;
+                len[i] = streams[i].size;
+            }
+        }
+        int rc = core->prepare(n, data.data(), len.data(), outs.data(), stream);
+        if (rc == B200JPEG_OK)
+            rc = core->execute(stream);
+        if (rc == B200JPEG_OK)
+            rc = core->finish(status.data(), stream);
+        if (rc != B200JPEG_OK)
+            log_msg(fw_, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_ERROR, std::string("b200 jpeg batch decode failed: ") + core->last_error());
+        for (int i = 0; i < n; ++i) {
+            nvimgcodecProcessingStatus_t ps = pre[i];
+            if (ps == NVIMGCODEC_PROCESSING_STATUS_SUCCESS)
+                ps = (rc == B200JPEG_OK) ? to_processing_status(status[i]) : NVIMGCODEC_PROCESSING_STATUS_FAIL;
+            images[i]->imageReady(images[i]->instance, ps);
+        }
+        return rc == B200JPEG_OK ? NVIMGCODEC_STATUS_SUCCESS : NVIMGCODEC_STATUS_EXTENSION_EXECUTION_FAILED;
+    }
+
+  private:
+    b200jpeg::Decoder* core_for(int thread_idx)
+    {
+        std::lock_guard<std::mutex> lock(mu_);
+        size_t slot = thread_idx < 0 ? cores_.size() - 1 : size_t(thread_idx);
+        if (slot >= cores_.size())
+            cores_.resize(slot + 1);
+        if (!cores_[slot])
+            cores_[slot] = std::make_unique<b200jpeg::Decoder>(ep_->device_id, opt_);
+        return cores_[slot].get();
+    }
+
+    const nvimgcodecFrameworkDesc_t* fw_;
+    const nvimgcodecExecutionParams_t* ep_;
+    b200jpeg::Options opt_;
+    std::mutex mu_;
+    std::vector<std::unique_ptr<b200jpeg::Decoder>> cores_;
+};
+
+// ---- C trampolines of nvimgcodecDecoderDesc_t (never let an exception cross the ABI)
+struct PluginCtx {
+    const nvimgcodecFrameworkDesc_t* framework = nullptr;
+    nvimgcodecDecoderDesc_t desc{};
+};
+
+nvimgcodecStatus_t dec_create(void* instance, nvimgcodecDecoder_t* decoder, const nvimgcodecExecutionParams_t* ep, const char* options)
+{
+    auto* ctx = static_cast<PluginCtx*>(instance);
+    if (!ctx || !decoder || !ep)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER;
+    if (ep->device_id == NVIMGCODEC_DEVICE_CPU_ONLY)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER; // a GPU-only decoder (same refusal as cuda_decoder.cpp:333-334)
+    try {
+        *decoder = reinterpret_cast<nvimgcodecDecoder_t>(new DecoderImpl(ctx->framework, ep, options));
+    } catch (...) {
+        return NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+    }
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t dec_destroy(nvimgcodecDecoder_t decoder)
+{
+    delete reinterpret_cast<DecoderImpl*>(decoder);
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t dec_get_metadata(nvimgcodecDecoder_t, const nvimgcodecCodeStreamDesc_t*, nvimgcodecMetadata_t**, int*)
+{
+    return NVIMGCODEC_STATUS_IMPLEMENTATION_UNSUPPORTED; // as libjpeg_turbo_decoder.cpp:105-108
+}
+
+nvimgcodecProcessingStatus_t dec_can_decode(nvimgcodecDecoder_t decoder, const nvimgcodecImageDesc_t* image,
+    const nvimgcodecCodeStreamDesc_t* cs, const nvimgcodecDecodeParams_t* params, int)
+{
+    try {
+        return reinterpret_cast<DecoderImpl*>(decoder)->can_decode(image, cs, params);
+    } catch (...) {
+        return NVIMGCODEC_PROCESSING_STATUS_FAIL;
+    }
+}
+
+nvimgcodecStatus_t dec_decode(nvimgcodecDecoder_t decoder, const nvimgcodecImageDesc_t* image, const nvimgcodecCodeStreamDesc_t* cs,
+    const nvimgcodecDecodeParams_t*, int thread_idx)
+{
+    try {
+        // +1: slot 0 belongs to decodeBatch, which the framework calls with thread_idx 0 on the caller thread
+        return reinterpret_cast<DecoderImpl*>(decoder)->decode_batch(&image, &cs, 1, thread_idx < 0 ? -1 : thread_idx + 1);
+    } catch (...) {
+        if (image)
+            image->imageReady(image->instance, NVIMGCODEC_PROCESSING_STATUS_FAIL);
+        return NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+    }
+}
+
+nvimgcodecStatus_t dec_decode_batch(nvimgcodecDecoder_t decoder, const nvimgcodecImageDesc_t** images,
+    const nvimgcodecCodeStreamDesc_t** css, int batch_size, const nvimgcodecDecodeParams_t*, int)
+{
+    try {
+        return reinterpret_cast<DecoderImpl*>(decoder)->decode_batch(images, css, batch_size, 0);
+    } catch (...) {
+        for (int i = 0; i < batch_size; ++i)
+            images[i]->imageReady(images[i]->instance, NVIMGCODEC_PROCESSING_STATUS_FAIL);
+        return NVIMGCODEC_STATUS_EXTENSION_INTERNAL_ERROR;
+    }
+}
+
+nvimgcodecStatus_t dec_mini_batch(nvimgcodecDecoder_t, int* batch_size)
+{
+    if (batch_size)
+        *batch_size = kMiniBatch;
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t ext_create(void*, nvimgcodecExtension_t* extension, const nvimgcodecFrameworkDesc_t* framework)
+{
+    if (!extension || !framework)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER;
+    auto* ctx = new (std::nothrow) PluginCtx;
+    if (!ctx)
+        return NVIMGCODEC_STATUS_ALLOCATOR_FAILURE;
+    ctx->framework = framework;
+    ctx->desc = nvimgcodecDecoderDesc_t{NVIMGCODEC_STRUCTURE_TYPE_DECODER_DESC, sizeof(nvimgcodecDecoderDesc_t), nullptr, ctx, kDecoderId, "jpeg",
+        NVIMGCODEC_BACKEND_KIND_GPU_ONLY, dec_create, dec_destroy, dec_get_metadata, dec_can_decode, dec_decode, dec_decode_batch,
+        dec_mini_batch};
+    const nvimgcodecStatus_t st = framework->registerDecoder(framework->instance, &ctx->desc, kPriority);
+    if (st != NVIMGCODEC_STATUS_SUCCESS) {
+        delete ctx;
+        return st;
+    }
+    log_msg(framework, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_INFO, "b200 jpeg decoder registered");
+    *extension = reinterpret_cast<nvimgcodecExtension_t>(ctx);
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+nvimgcodecStatus_t ext_destroy(nvimgcodecExtension_t extension)
+{
+    auto* ctx = reinterpret_cast<PluginCtx*>(extension);
+    if (!ctx)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER;
+    ctx->framework->unregisterDecoder(ctx->framework->instance, &ctx->desc);
+    delete ctx;
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+const nvimgcodecExtensionDesc_t kExtensionDesc = {NVIMGCODEC_STRUCTURE_TYPE_EXTENSION_DESC, sizeof(nvimgcodecExtensionDesc_t), nullptr, nullptr,
+    kExtensionId, 100 /* 0.1.0 */, NVIMGCODEC_VER, ext_create, ext_destroy};
+
+} // namespace
+
+extern "C" {
+
+// For in-process registration through nvimgcodecExtensionCreate, as the reference's own tests do
+// (test/extensions/libjpeg_turbo_ext_decoder_test.cpp:49-52).
+B200JPEG_API nvimgcodecStatus_t get_b200_jpeg_extension_desc(nvimgcodecExtensionDesc_t* ext_desc)
+{
+    if (!ext_desc)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER;
+    if (ext_desc->struct_type != NVIMGCODEC_STRUCTURE_TYPE_EXTENSION_DESC)
+        return NVIMGCODEC_STATUS_INVALID_PARAMETER;
+    *ext_desc = kExtensionDesc;
+    return NVIMGCODEC_STATUS_SUCCESS;
+}
+
+// Found by dlsym when the framework scans its extensions directory (src/plugin_framework.cpp:338-372).
+B200JPEG_API nvimgcodecStatus_t nvimgcodecExtensionModuleEntry(nvimgcodecExtensionDesc_t* ext_desc)
+{
+    return get_b200_jpeg_extension_desc(ext_desc);
+}
+
+} // extern "C"

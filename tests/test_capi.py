@@ -1,0 +1,98 @@
+"""CPU tests: the C-ABI library loads, exports what include/b200jpeg.h declares, and its host logic
+(marker walk / acceptance predicate) agrees with the oracle.  No compute calls: no GPU here."""
+import ctypes
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle
+from nvimagecodec_b200 import _lib, jpeg_host, sharding
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "b200jpeg.h")).read()
+    return sorted(set(re.findall(r"B200JPEG_API\s+[\w\s\*]+?\b(b200jpeg\w+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    L = _lib.load()
+    names = _declared()
+    assert len(names) >= 12
+    for n in names:
+        assert hasattr(L, n), n
+    assert sorted(names) == sorted(_lib.EXPORTS)
+    assert b"sm_100a" in L.b200jpegVersion()
+
+
+def test_extension_entry_point_is_exported_when_built():
+    L = _lib.load()
+    if not os.path.isdir("/root/reference/include") and not hasattr(L, "nvimgcodecExtensionModuleEntry"):
+        pytest.skip("extension adapter not built in this tree")
+    assert hasattr(L, "nvimgcodecExtensionModuleEntry")
+    assert hasattr(L, "get_b200_jpeg_extension_desc")
+
+
+def test_probe_agrees_with_oracle_on_goldens():
+    with open(os.path.join(GOLD, "golden.json")) as f:
+        entries = json.load(f)["entries"]
+    for e in entries:
+        data = open(os.path.join(GOLD, "jpeg", e["name"] + ".jpg"), "rb").read()
+        info = jpeg_host.probe(data)
+        ref = oracle.info(data)
+        assert info.supported == 1, e["name"]
+        assert (info.width, info.height, info.num_components) == (ref["width"], ref["height"], ref["ncomp"])
+        assert info.restart_interval == ref["restart_interval"]
+        assert (info.mcus_x, info.mcus_y, info.blocks_per_mcu) == (ref["mcus_x"], ref["mcus_y"], ref["blocks_per_mcu"])
+        assert info.scan_offset == ref["scan_offset"]
+        assert [(info.h[c], info.v[c]) for c in range(ref["ncomp"])] == ref["sampling"]
+
+
+def test_probe_rejects_what_the_kernels_do_not_handle():
+    cv2 = pytest.importorskip("cv2")
+    from PIL import Image
+    import io
+    from nvimagecodec_b200 import corpus
+
+    img = corpus.synth(40, 56, 3)
+    ok, prog = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_PROGRESSIVE, 1])
+    info = jpeg_host.probe(prog.tobytes())
+    assert info.supported == 0 and info.reason == _lib.ERR_UNSUPPORTED and info.sof_marker == 0xC2
+    buf = io.BytesIO()
+    Image.fromarray(np.dstack([img, img[..., 0]])).convert("CMYK").save(buf, format="JPEG")
+    info = jpeg_host.probe(buf.getvalue())
+    assert info.supported == 0 and info.reason == _lib.ERR_UNSUPPORTED and info.num_components == 4
+    assert jpeg_host.probe(b"\x89PNG\r\n\x1a\n....").reason == _lib.ERR_NOT_JPEG
+    good = corpus.encode(img, 90, "420")
+    assert jpeg_host.probe(good[:100]).reason == _lib.ERR_CORRUPT
+    assert jpeg_host.probe(good).supported == 1
+
+
+def test_create_fails_loudly_without_gpu():
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    L = _lib.load()
+    h = ctypes.c_void_p()
+    assert L.b200jpegCreate(ctypes.byref(h), 0, b"") == _lib.ERR_CUDA
+    with pytest.raises(Exception):
+        from nvimagecodec_b200 import Decoder
+
+        Decoder(0)
+
+
+def test_partition_by_bytes_is_balanced_and_complete():
+    rng = np.random.default_rng(0)
+    sizes = [int(x) for x in rng.integers(10_000, 600_000, size=8192)]
+    parts = sharding.partition_by_bytes(sizes, 8)
+    assert sorted(i for p in parts for i in p) == list(range(8192))
+    assert sharding.imbalance(sizes, parts) < 1.01
+    assert sharding.partition_by_bytes(sizes, 8) == parts  # deterministic
+    assert sharding.partition_by_bytes([5, 1, 1], 2) == [[0], [1, 2]]
+    assert sharding.partition_by_bytes([], 3) == [[], [], []]

@@ -1,0 +1,223 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the oracle and the
+committed libjpeg-turbo golden vectors.  Bar: bit-exact (integer / byte work)."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+OFMT = {"I_RGB": oracle.FMT_I_RGB, "I_BGR": oracle.FMT_I_BGR, "P_RGB": oracle.FMT_P_RGB, "P_BGR": oracle.FMT_P_BGR,
+        "I_Y": oracle.FMT_Y, "P_Y": oracle.FMT_Y}
+
+
+def _gold():
+    with open(os.path.join(GOLD, "golden.json")) as f:
+        entries = json.load(f)["entries"]
+    return entries, [open(os.path.join(GOLD, "jpeg", e["name"] + ".jpg"), "rb").read() for e in entries]
+
+
+def _sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.fixture(scope="module")
+def dec_fancy(decoder_cls):
+    d = decoder_cls(0, options=":fancy_upsampling=1")
+    yield d
+    d.close()
+
+
+@pytest.fixture(scope="module")
+def dec_plain(decoder_cls):
+    d = decoder_cls(0)  # binding default ":fancy_upsampling=0"
+    yield d
+    d.close()
+
+
+def test_native_library_is_what_runs(dec_fancy):
+    from nvimagecodec_b200 import _lib
+
+    assert os.path.exists(_lib.LIB_PATH)
+    with open("/proc/self/maps") as f:
+        assert "libb200jpeg_ext.so" in f.read()
+
+
+def test_golden_vectors_bit_exact(dec_fancy):
+    """Every committed libjpeg-turbo vector (config #1 substitutes + edge cases), one batch."""
+    from nvimagecodec_b200 import _lib
+
+    entries, datas = _gold()
+    outs = dec_fancy.decode(datas, "I_RGB")
+    assert dec_fancy.last_status == [_lib.OK] * len(datas)
+    assert dec_fancy.stat(_lib.STAT_KERNEL_LAUNCHES) >= 8
+    for e, o in zip(entries, outs):
+        got = o.cpu().numpy()
+        assert got.shape == (e["height"], e["width"], 3), e["name"]
+        assert _sha(got) == e["sha256_rgb_fancy"], e["name"]
+    outs = dec_fancy.decode(datas, "I_Y")
+    for e, o in zip(entries, outs):
+        assert _sha(o.cpu().numpy()) == e["sha256_y"], e["name"]
+
+
+@pytest.mark.parametrize("fmt", ["I_RGB", "I_BGR", "P_RGB", "P_BGR", "I_Y"])
+@pytest.mark.parametrize("fancy", [True, False])
+def test_formats_and_upsampling_modes_vs_oracle(decoder_cls, dec_fancy, dec_plain, fmt, fancy):
+    from nvimagecodec_b200 import _lib
+
+    entries, datas = _gold()
+    pick = [i for i, e in enumerate(entries) if e["name"].startswith("syn_") or "padlock_4" in e["name"]]
+    srcs = [datas[i] for i in pick]
+    dec = dec_fancy if fancy else dec_plain
+    outs = dec.decode(srcs, fmt)
+    assert dec.last_status == [_lib.OK] * len(srcs)
+    for d, o in zip(srcs, outs):
+        ref = oracle.decode(d, OFMT[fmt], fancy=fancy)
+        assert np.array_equal(o.cpu().numpy(), ref)
+
+
+def test_coefficients_match_oracle(dec_fancy):
+    from nvimagecodec_b200 import corpus
+
+    srcs = [corpus.encode(corpus.synth(120, 200, 11), 92, "420", rst_interval=5),
+            corpus.encode(corpus.synth(96, 80, 12), 60, "444", optimize=True),
+            corpus.encode(corpus.synth(70, 70, 13), 85, gray=True)]
+    dec_fancy.decode(srcs, "I_RGB")
+    for i, d in enumerate(srcs):
+        ref = oracle.coefficients(d)
+        got = dec_fancy.coefficients(i, ref.size).reshape(ref.shape)
+        assert np.array_equal(got, ref)
+
+
+def test_roi_equals_crop_and_mixed_requests(dec_plain):
+    """ROI == crop of the full decode (test/python/test_decode.py:381), mixed formats in one batch."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    rng = np.random.default_rng(3)
+    srcs, fmts, rois = [], [], []
+    for i in range(24):
+        h, w = int(rng.integers(20, 300)), int(rng.integers(20, 300))
+        samp = ["444", "422", "420", "440", "411"][i % 5]
+        srcs.append(corpus.encode(corpus.synth(h, w, 40 + i), 85, samp, rst_interval=int(rng.integers(0, 9))))
+        y0, x0 = int(rng.integers(0, h)), int(rng.integers(0, w))
+        y1, x1 = int(rng.integers(y0 + 1, h + 1)), int(rng.integers(x0 + 1, w + 1))
+        rois.append((y0, x0, y1, x1) if i % 4 else None)
+        fmts.append(["I_RGB", "I_Y", "P_RGB", "I_BGR"][i % 4])
+    outs = dec_plain.decode(srcs, fmts, rois)
+    assert dec_plain.last_status == [_lib.OK] * len(srcs)
+    for d, f, r, o in zip(srcs, fmts, rois, outs):
+        assert np.array_equal(o.cpu().numpy(), oracle.decode(d, OFMT[f], fancy=False, roi=r))
+
+
+def test_host_output_and_padded_stride(dec_fancy):
+    from nvimagecodec_b200 import _lib, corpus
+    import torch
+
+    srcs = [corpus.encode(corpus.synth(61, 45, 5), 90, "420"), corpus.encode(corpus.synth(33, 130, 6), 90, "422", 2)]
+    outs = dec_fancy.decode(srcs, "I_RGB", to_host=True)
+    for d, o in zip(srcs, outs):
+        assert not o.is_cuda
+        assert np.array_equal(o.numpy(), oracle.decode(d, oracle.FMT_I_RGB, True))
+    with torch.cuda.device(0):
+        b = dec_fancy.make_batch(srcs, ["P_RGB", "I_RGB"], row_align=64)
+        b.storage.fill_(7)
+        assert dec_fancy.run(b) == [_lib.OK, _lib.OK]
+    assert np.array_equal(b.images[0].cpu().numpy(), oracle.decode(srcs[0], oracle.FMT_P_RGB, True))
+    assert np.array_equal(b.images[1].cpu().numpy(), oracle.decode(srcs[1], oracle.FMT_I_RGB, True))
+
+
+def test_bad_and_unsupported_streams_report_per_image_status(dec_fancy):
+    cv2 = pytest.importorskip("cv2")
+    from nvimagecodec_b200 import _lib, corpus
+
+    img = corpus.synth(90, 120, 9)
+    good = corpus.encode(img, 90, "420", rst_interval=3)
+    ok, prog = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_PROGRESSIVE, 1])
+    info = oracle.info(good)
+    cut = bytearray(good)
+    mid = info["scan_offset"] + (len(good) - info["scan_offset"]) // 2
+    trunc = bytes(cut[:mid]) + b"\xff\xd9"
+    # damage the entropy data: the decoder must flag it, never crash or write out of bounds
+    noisy = bytearray(good)
+    rng = np.random.default_rng(1)
+    for p in rng.integers(info["scan_offset"] + 10, len(good) - 10, size=40):
+        if noisy[p] != 0xFF and noisy[p - 1] != 0xFF:
+            noisy[p] = (noisy[p] ^ 0x5A) if (noisy[p] ^ 0x5A) != 0xFF else 0x11
+    badrst = good.replace(b"\xff\xd1", b"\xff\xd5", 1)
+    srcs = [good, prog.tobytes(), b"garbage", trunc, bytes(noisy), badrst, good]
+    outs = dec_fancy.decode(srcs, "I_RGB")
+    st = dec_fancy.last_status
+    assert st[0] == _lib.OK and st[6] == _lib.OK
+    assert st[1] == _lib.ERR_UNSUPPORTED
+    assert st[2] == _lib.ERR_NOT_JPEG
+    assert st[3] == _lib.ERR_CORRUPT
+    assert st[5] == _lib.ERR_CORRUPT
+    assert st[4] in (_lib.ERR_CORRUPT, _lib.OK)  # random damage may still parse; it must not take the batch down
+    ref = oracle.decode(good, oracle.FMT_I_RGB, True)
+    assert np.array_equal(outs[0].cpu().numpy(), ref) and np.array_equal(outs[6].cpu().numpy(), ref)
+
+
+def test_resync_path_and_no_rst_large_stream(decoder_cls):
+    """Config #4 shape (4:4:4, q95, no RST, large scan): relies on self-synchronisation only.  The
+    debug_no_warm hook starts every sequence from a bare guess, which forces the fix-up path."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    big = corpus.encode(corpus.synth(1080, 1920, 21), 95, "444")
+    flat = np.zeros((1200, 1600, 3), np.uint8)
+    flat[:, :] = (12, 200, 90)
+    flat[500:520, 300:900] = 255
+    srcs = [big, corpus.encode(flat, 90, "420"), corpus.encode(corpus.synth(600, 800, 22), 90, "420", optimize=True)]
+    refs = [oracle.decode(d, oracle.FMT_I_RGB, True) for d in srcs]
+    for opts, expect_resync in [(":fancy_upsampling=1", False), (":fancy_upsampling=1 b200_jpeg_decoder:debug_no_warm=1", True)]:
+        dec = decoder_cls(0, options=opts)
+        outs = dec.decode(srcs, "I_RGB")
+        assert dec.last_status == [_lib.OK] * len(srcs)
+        if expect_resync:
+            assert dec.stat(_lib.STAT_RESYNC_IMAGES) >= 1
+        for o, r in zip(outs, refs):
+            assert np.array_equal(o.cpu().numpy(), r)
+        dec.close()
+
+
+def test_deterministic_and_reusable(dec_plain):
+    """Sequential reuse of one decoder gives byte-identical results (the reference's
+    concurrent_decode_test.cpp demands equality with a sequential decode)."""
+    from nvimagecodec_b200 import corpus
+
+    a = [corpus.encode(corpus.synth(200, 300, 70 + i), 80, ["420", "444", "422"][i % 3], i) for i in range(9)]
+    b = [corpus.encode(corpus.synth(50, 60, 80 + i), 90, "420") for i in range(3)]
+    first = [o.cpu().numpy().copy() for o in dec_plain.decode(a, "I_RGB")]
+    dec_plain.decode(b, "I_RGB")
+    dec_plain.decode([], "I_RGB")
+    second = [o.cpu().numpy() for o in dec_plain.decode(a, "I_RGB")]
+    for x, y in zip(first, second):
+        assert np.array_equal(x, y)
+
+
+def test_full_size_properties_c2_shape(dec_plain, dec_fancy):
+    """BASELINE config #2 shape (1920x1080 4:2:0 q90): size-independent properties plus the oracle
+    on a couple of images (the scalar oracle needs ~0.1 s per image at this size)."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    srcs = [corpus.encode(corpus.synth(1080, 1920, s), 90, "420") for s in range(4)]
+    rgb = [o.cpu().numpy() for o in dec_plain.decode(srcs, "I_RGB")]
+    assert dec_plain.last_status == [_lib.OK] * 4
+    prgb = [o.cpu().numpy() for o in dec_plain.decode(srcs, "P_RGB")]
+    bgr = [o.cpu().numpy() for o in dec_plain.decode(srcs, "I_BGR")]
+    roi = (100, 37, 1001, 1900)
+    crop = [o.cpu().numpy() for o in dec_plain.decode(srcs, "I_RGB", [roi] * 4)]
+    for i in range(4):
+        assert np.array_equal(prgb[i], rgb[i].transpose(2, 0, 1))
+        assert np.array_equal(bgr[i], rgb[i][..., ::-1])
+        assert np.array_equal(crop[i], rgb[i][roi[0]:roi[2], roi[1]:roi[3]])
+    for i in range(2):
+        assert np.array_equal(rgb[i], oracle.decode(srcs[i], oracle.FMT_I_RGB, fancy=False))
+    f = dec_fancy.decode(srcs[:1], "I_RGB")[0].cpu().numpy()
+    assert np.array_equal(f, oracle.decode(srcs[0], oracle.FMT_I_RGB, fancy=True))
+    algo = dec_plain.stat(_lib.STAT_ALGO_BYTES)
+    assert algo > 0
