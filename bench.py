@@ -267,7 +267,7 @@ def main():
         # algorithmic bytes per launch of each kernel (DESIGN.md "Kernels"), for the N=1 shard of rank 0
         kbytes = {
             "scan(K0)": 2 * comp_bytes, "huff_sync(K1)": comp_bytes, "verify_scan(K2)": 40 * dec.stat(_lib.STAT_NUM_SUBSEQ),
-            "coef_clear": 2 * n_coefs, "huff_write(K3)": comp_bytes, "idct(K4a)": 2 * n_coefs + planes_bytes,
+            "huff_write(K3)": comp_bytes + 2 * n_coefs, "idct(K4a)": 2 * n_coefs + planes_bytes,
             "color(K4b)": planes_bytes + out_bytes,
         }
         top = max(stages, key=stages.get) if stages else None

@@ -10,7 +10,7 @@ namespace b200jpeg {
 
 namespace {
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-const char* kStageNames[] = {"scan(K0)", "huff_sync(K1)", "verify_scan(K2)", "coef_clear", "huff_write(K3)", "idct(K4a)", "color(K4b)", "fixup"};
+const char* kStageNames[] = {"scan(K0)", "huff_sync(K1)", "verify_scan(K2)", "huff_write(K3)", "idct(K4a)", "color(K4b)"};
 } // namespace
 
 bool DeviceBuffer::ensure(size_t bytes, size_t* total)
@@ -264,9 +264,28 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.row_stride = uint32_t(stride);
         im.plane_stride = stride * rh;
         const size_t obytes = planar ? 3 * stride * rh : stride * rh;
-        im.color_cta_off = n_color;
-        im.n_color_cta_x = uint32_t((rw + 255) / 256);
-        im.n_color_cta_y = uint32_t((rh + 3) / 4);
+        // K4b specialisation (kernels.cu color_kernel): fast paths need full-resolution luma and
+        // both chroma components subsampled alike by 1 or 2 in each direction
+        im.color_mode = 0;
+        im.color_unit_rows = 1;
+        const bool luma_full = hd.h[0] == hd.hmax && hd.v[0] == hd.vmax;
+        if (im.ncomp_needed == 1) {
+            if (luma_full)
+                im.color_mode = 1;
+        } else if (luma_full && hd.h[1] == hd.h[2] && hd.v[1] == hd.v[2]) {
+            const int hx = hd.hmax / hd.h[1], vx = hd.vmax / hd.v[1];
+            if ((hx == 1 || hx == 2) && (vx == 1 || vx == 2)) {
+                im.color_mode = uint8_t(2 + (hx - 1) + 2 * (vx - 1));
+                im.color_unit_rows = uint8_t(vx);
+            }
+        }
+        {
+            const int ur = im.color_unit_rows;
+            const size_t ax0 = size_t(x0) & ~size_t(7), ay0 = size_t(y0) / ur * ur; // units are aligned in image coordinates
+            im.color_cta_off = n_color;
+            im.n_color_cta_x = uint32_t((size_t(x1) - ax0 + 255) / 256);
+            im.n_color_cta_y = uint32_t((size_t(y1) - ay0 + 8 * ur - 1) / (8 * ur));
+        }
         n_color += im.n_color_cta_x * im.n_color_cta_y;
         HostOut ho{nullptr, 0, obytes};
         if (o.buffer_is_host) {
@@ -431,17 +450,12 @@ int Decoder::execute(cudaStream_t stream)
     mark(2, stream);
     launches_ += launch_verify_scan(bd_, false, stream);
     mark(3, stream);
-    if (coef_bytes_) {
-        cudaMemsetAsync(coef_.ptr, 0, coef_bytes_, stream);
-        launches_ += 1;
-    }
+    launches_ += launch_write(bd_, false, stream); // writes every coefficient exactly once: no clearing pass
     mark(4, stream);
-    launches_ += launch_write(bd_, false, stream);
-    mark(5, stream);
     launches_ += launch_idct(bd_, false, stream);
-    mark(6, stream);
+    mark(5, stream);
     launches_ += launch_color(bd_, false, stream);
-    mark(7, stream);
+    mark(6, stream);
     ev_recorded_ = profiling_ && ev_valid_;
     if (!cuda_ok(cudaGetLastError(), "kernel launch"))
         return B200JPEG_ERR_CUDA;
@@ -488,9 +502,6 @@ int Decoder::finish(int* status, cudaStream_t stream)
             dirty = count_dirty();
             ++rounds;
         }
-        for (int d = 0; d < nd; ++d)
-            if ((states_[d].flags & kFlagRedo) && !(states_[d].flags & kFlagDirty))
-                cudaMemsetAsync(bd_.coef + imgs_[d].coef_off, 0, size_t(imgs_[d].total_blocks) * 128, stream);
         launches_ += launch_write(bd_, true, stream);
         launches_ += launch_idct(bd_, true, stream);
         launches_ += launch_color(bd_, true, stream);
@@ -545,9 +556,9 @@ int Decoder::stage_times(float* ms, const char** names, int cap)
 {
     if (!ev_recorded_)
         return 0;
-    cudaEventSynchronize(ev_[kStages - 1]);
+    cudaEventSynchronize(ev_[kStages]);
     int n = 0;
-    for (int i = 0; i < kStages - 1 && n < cap; ++i, ++n) {
+    for (int i = 0; i < kStages && n < cap; ++i, ++n) {
         float t = 0.f;
         cudaEventElapsedTime(&t, ev_[i], ev_[i + 1]);
         ms[n] = t;

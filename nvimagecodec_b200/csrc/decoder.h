@@ -97,7 +97,7 @@ class Decoder {
 
     // profiling
     bool profiling_ = false;
-    static constexpr int kStages = 8;
+    static constexpr int kStages = 6;
     cudaEvent_t ev_[kStages + 1] = {};
     bool ev_valid_ = false;
     bool ev_recorded_ = false;

@@ -200,21 +200,38 @@ StreamStatus parse_stream(const uint8_t* d, size_t n, StreamHeader* hdr)
     return kStreamOk;
 }
 
-void build_huff_table(const HuffSpec& spec, HuffTableDev* out)
+// What a decoded symbol does, packed for the device (kernels.cu decode_subsequence):
+//   bits [0,5)  code length, 0 = not in the first-level table
+//   bits [5,9)  number of magnitude bits that follow the code
+//   bits [9,16) how far the zig-zag index advances: DC -> 1; AC run/size -> run + 1;
+//               ZRL (0xF0) -> 16; EOB (0x00) -> 64 (ends the block)
+uint16_t pack_symbol(bool is_dc, int len, int sym)
+{
+    const int size = sym & 15;
+    int skip;
+    if (is_dc)
+        skip = 1;
+    else if (size)
+        skip = (sym >> 4) + 1;
+    else
+        skip = ((sym >> 4) == 15) ? 16 : 64;
+    return uint16_t(len | (size << 5) | (skip << 9));
+}
+
+void build_huff_table(const HuffSpec& spec, bool is_dc, HuffTableDev* out)
 {
     std::memset(out, 0, sizeof(*out));
-    std::memcpy(out->vals, spec.vals, 256);
     int code = 0, k = 0;
     for (int l = 1; l <= 16; ++l) {
         out->valoff[l] = k - code;
         const int cnt = spec.present ? spec.bits[l] : 0;
         for (int i = 0; i < cnt; ++i, ++code, ++k) {
+            out->sym[k] = pack_symbol(is_dc, l, spec.vals[k]);
             if (l <= kLutBits) {
                 const int first = code << (kLutBits - l);
                 const int span = 1 << (kLutBits - l);
-                const uint16_t e = uint16_t((l << 8) | spec.vals[k]);
                 for (int j = 0; j < span; ++j)
-                    out->lut[first + j] = e;
+                    out->lut[first + j] = out->sym[k];
             }
         }
         out->maxcode[l] = cnt ? code - 1 : -1;
@@ -252,7 +269,7 @@ void build_huff_set(const StreamHeader& hdr, HuffSetDev* out)
 {
     for (int cls = 0; cls < 2; ++cls)
         for (int id = 0; id < 2; ++id)
-            build_huff_table(hdr.huff[cls][id], &out->t[cls * 2 + id]);
+            build_huff_table(hdr.huff[cls][id], cls == 0, &out->t[cls * 2 + id]);
 }
 
 } // namespace b200jpeg

@@ -42,16 +42,16 @@ StreamStatus parse_stream(const uint8_t* data, size_t len, StreamHeader* hdr);
 
 // Device-side Huffman table image (one per table; a "set" is DC0, DC1, AC0, AC1).
 struct alignas(16) HuffTableDev {
-    uint16_t lut[1 << kLutBits]; // (code_len << 8) | symbol ; 0 = longer than kLutBits or invalid
+    uint16_t lut[1 << kLutBits]; // packed symbol action (see pack_symbol); 0 = longer than kLutBits or invalid
     int32_t maxcode[18];         // maxcode[l] for l in 1..16 (canonical), -1 if none; [17] = sentinel
-    int32_t valoff[18];          // vals index = valoff[l] + code
-    uint8_t vals[256];
+    int32_t valoff[18];          // sym index = valoff[l] + code
+    uint16_t sym[256];           // packed symbol actions in canonical order (slow path for long codes)
 };
 struct alignas(16) HuffSetDev {
     HuffTableDev t[4]; // 0: DC id0, 1: DC id1, 2: AC id0, 3: AC id1
 };
 
-void build_huff_table(const HuffSpec& spec, HuffTableDev* out);
+void build_huff_table(const HuffSpec& spec, bool is_dc, HuffTableDev* out);
 uint64_t hash_huff_set(const StreamHeader& hdr);
 void build_huff_set(const StreamHeader& hdr, HuffSetDev* out);
 

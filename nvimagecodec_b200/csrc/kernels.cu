@@ -244,6 +244,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_scatter_kernel(BatchDev bd)
 //   [0,6)  bit offset of the first code word past the boundary   [6,12) zig-zag index z
 //   [12,16) block-in-MCU index b                                  bit 16: end of stream reached
 constexpr uint32_t kStateDone = 1u << 16;
+constexpr int kProbeBits = 256; // K1: how far before its subsequence a thread starts to guess its entry state
 
 struct DecodeResult {
     uint32_t state;     // exit state
@@ -263,9 +264,44 @@ struct StreamView {
     uint32_t total_blocks;
 };
 
+// Coefficient block assembly for K3: the 64 int16 of the block being decoded are emitted as eight
+// 16-byte groups, in order, straight from registers -- every byte of the coefficient buffer is
+// written exactly once (no clearing pass, no partial-sector read-modify-write in L2).
+struct BlockWriter {
+    uint64_t lo, hi; // coefficients 0..3 and 4..7 of the current group
+    uint32_t g;      // current group, 0..7
+    __device__ __forceinline__ void reset()
+    {
+        lo = hi = 0;
+        g = 0;
+    }
+    __device__ __forceinline__ void flush_to(int16_t* __restrict__ blk_base, uint32_t upto)
+    {
+        while (g < upto) {
+            *reinterpret_cast<uint4*>(blk_base + g * 8) = make_uint4(uint32_t(lo), uint32_t(lo >> 32), uint32_t(hi), uint32_t(hi >> 32));
+            lo = hi = 0;
+            ++g;
+        }
+    }
+    __device__ __forceinline__ void put(int16_t* __restrict__ blk_base, uint32_t pos, int32_t val)
+    {
+        flush_to(blk_base, pos >> 3);
+        const uint64_t v = uint64_t(uint32_t(val) & 0xFFFFu) << (16 * (pos & 3u));
+        if (pos & 4u)
+            hi |= v;
+        else
+            lo |= v;
+    }
+};
+
+// Decodes the code words that start in [start bit given by in_state, end_bit).
+//   kWrite == false (K1): only the decoder state, the block count and the DC sums are tracked.
+//   kWrite == true  (K3): the thread OWNS every block that starts inside its range: a block already
+//     under way at entry is skipped (its owner, the previous thread, finishes it), and the block
+//     under way at end_bit is decoded to its end.
 template <bool kWrite>
-__device__ __forceinline__ void decode_subsequence(const StreamView& sv, const HuffSetDev* __restrict__ hs, uint32_t k, uint32_t in_state,
-    int32_t blk, int32_t dc0, int32_t dc1, int32_t dc2, int16_t* __restrict__ coef, DecodeResult& out)
+__device__ __forceinline__ void decode_subsequence(const StreamView& sv, const HuffSetDev* __restrict__ hs, uint32_t base_bit, uint32_t end_bit,
+    uint32_t in_state, int32_t blk, int32_t dc0, int32_t dc1, int32_t dc2, int16_t* __restrict__ coef, DecodeResult& out)
 {
     out.err = 0;
     out.restarted = 0;
@@ -277,10 +313,9 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
         out.dc2 = dc2;
         return;
     }
-    uint32_t p = k * kSubseqBits + (in_state & 63u);
+    uint32_t p = base_bit + (in_state & 63u);
     uint32_t z = (in_state >> 6) & 63u;
     uint32_t b = (in_state >> 12) & 15u;
-    const uint32_t end_bit = (k + 1) * kSubseqBits;
     // first boundary strictly after p
     uint32_t r = 0;
     if (sv.nb > 1) {
@@ -297,10 +332,14 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
     uint32_t next_bnd = (r == sv.nb - 1) ? sv.total_bits : __ldg(sv.bnd + r) * 8u;
     uint32_t widx = p >> 5;
     uint32_t whi = __ldg(sv.words + widx), wlo = __ldg(sv.words + widx + 1);
-    uint32_t comp = (sv.blk_comp >> (2 * b)) & 3u;
     const uint8_t* hbase = reinterpret_cast<const uint8_t*>(hs);
-    const HuffTableDev* dc_tab = reinterpret_cast<const HuffTableDev*>(hbase + ((sv.blk_tab >> b) & 1u) * sizeof(HuffTableDev));
-    const HuffTableDev* ac_tab = reinterpret_cast<const HuffTableDev*>(hbase + (2u + ((sv.blk_tab >> (16 + b)) & 1u)) * sizeof(HuffTableDev));
+    // per-block constants: component, DC table, AC table (byte offsets into the table set)
+    uint32_t comp = (sv.blk_comp >> (2 * b)) & 3u;
+    uint32_t dc_off = ((sv.blk_tab >> b) & 1u) * uint32_t(sizeof(HuffTableDev));
+    uint32_t ac_off = (2u + ((sv.blk_tab >> (16 + b)) & 1u)) * uint32_t(sizeof(HuffTableDev));
+    bool owned = (z == 0u); // kWrite: am I writing the block under way?
+    BlockWriter bw;
+    bw.reset();
     bool done = false;
     for (;;) {
         const uint32_t win = __funnelshift_l(wlo, whi, p & 31u);
@@ -324,85 +363,74 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
                 out.restarted = 1;
                 z = 0;
                 b = 0;
+                owned = true;
+                bw.reset();
                 dc0 = dc1 = dc2 = 0;
                 comp = sv.blk_comp & 3u;
-                dc_tab = reinterpret_cast<const HuffTableDev*>(hbase + (sv.blk_tab & 1u) * sizeof(HuffTableDev));
-                ac_tab = reinterpret_cast<const HuffTableDev*>(hbase + (2u + ((sv.blk_tab >> 16) & 1u)) * sizeof(HuffTableDev));
+                dc_off = (sv.blk_tab & 1u) * uint32_t(sizeof(HuffTableDev));
+                ac_off = (2u + ((sv.blk_tab >> 16) & 1u)) * uint32_t(sizeof(HuffTableDev));
                 widx = p >> 5;
                 whi = __ldg(sv.words + widx);
                 wlo = __ldg(sv.words + widx + 1);
                 continue;
             }
         }
-        if (p >= end_bit)
+        if (p >= end_bit && (!kWrite || z == 0u || !owned))
             break;
-        const HuffTableDev* tab = (z == 0u) ? dc_tab : ac_tab;
+        const bool is_dc = (z == 0u);
+        const HuffTableDev* tab = reinterpret_cast<const HuffTableDev*>(hbase + (is_dc ? dc_off : ac_off));
         uint32_t e = tab->lut[win >> (32 - kLutBits)];
-        uint32_t len = e >> 8, sym = e & 0xFFu;
-        if (len == 0u) {
+        if ((e & 31u) == 0u) {
             // code longer than the first-level table: canonical search (T.81 F.2.2.3)
-            len = 16;
-            sym = 0;
+            e = 16u | (1u << 9); // an invalid code consumes 16 bits (only an unsynchronised decoder gets here on a valid stream)
             bool found = false;
 #pragma unroll
             for (int l = kLutBits + 1; l <= 16; ++l) {
                 const int32_t code = int32_t(win >> (32 - l));
                 if (!found && code <= tab->maxcode[l]) {
                     found = true;
-                    len = l;
-                    sym = tab->vals[(tab->valoff[l] + code) & 255];
+                    e = tab->sym[(tab->valoff[l] + code) & 255];
                 }
             }
             if (!found)
                 out.err |= kFlagBadHuffman;
         }
-        const uint32_t size = sym & 15u;
+        const uint32_t len = e & 31u, size = (e >> 5) & 15u, skip = e >> 9;
         const uint32_t rest = win << len;
         const uint32_t mag = __funnelshift_l(rest, 0u, size); // top `size` bits, 0 when size == 0
+        const int32_t val = (rest >> 31) ? int32_t(mag) : int32_t(mag) - int32_t((1u << size) - 1u);
         p += len + size;
         if ((p >> 5) != widx) {
             ++widx;
             whi = wlo;
             wlo = __ldg(sv.words + widx + 1);
         }
-        if (z == 0u) {
-            const int32_t val = (rest >> 31) ? int32_t(mag) : int32_t(mag) - int32_t((1u << size) - 1u);
-            if (comp == 0u)
-                dc0 += val;
-            else if (comp == 1u)
-                dc1 += val;
-            else
-                dc2 += val;
-            if (kWrite) {
-                if (uint32_t(blk) < sv.total_blocks)
-                    coef[size_t(blk) * 64] = int16_t(comp == 0u ? dc0 : (comp == 1u ? dc1 : dc2));
-                else
-                    out.err |= kFlagOverrun;
-            }
-            z = 1;
-        } else {
-            const uint32_t run = sym >> 4;
-            if (size == 0u) {
-                z = (run == 15u) ? z + 16u : 64u;
-            } else {
-                z += run;
-                if (z > 63u) {
-                    out.err |= kFlagBadHuffman;
-                } else if (kWrite) {
-                    const int32_t val = (rest >> 31) ? int32_t(mag) : int32_t(mag) - int32_t((1u << size) - 1u);
-                    if (uint32_t(blk) < sv.total_blocks)
-                        coef[size_t(blk) * 64 + z] = int16_t(val);
-                }
-                ++z;
-            }
+        if (is_dc) {
+            dc0 += (comp == 0u) ? val : 0;
+            dc1 += (comp == 1u) ? val : 0;
+            dc2 += (comp == 2u) ? val : 0;
         }
+        const uint32_t pos = z + skip - 1u; // zig-zag position of the coefficient this symbol carries (if any)
+        if (kWrite && owned && (is_dc || size != 0u)) {
+            if (pos > 63u)
+                out.err |= kFlagBadHuffman;
+            else if (uint32_t(blk) < sv.total_blocks)
+                bw.put(coef + size_t(blk) * 64, pos, is_dc ? (comp == 0u ? dc0 : (comp == 1u ? dc1 : dc2)) : val);
+            else
+                out.err |= kFlagOverrun;
+        }
+        z += skip;
         if (z > 63u) {
+            if (kWrite && owned && uint32_t(blk) < sv.total_blocks)
+                bw.flush_to(coef + size_t(blk) * 64, 8u);
+            bw.reset();
+            owned = true;
             z = 0;
             ++blk;
             b = (b + 1u == sv.bpm) ? 0u : b + 1u;
             comp = (sv.blk_comp >> (2 * b)) & 3u;
-            dc_tab = reinterpret_cast<const HuffTableDev*>(hbase + ((sv.blk_tab >> b) & 1u) * sizeof(HuffTableDev));
-            ac_tab = reinterpret_cast<const HuffTableDev*>(hbase + (2u + ((sv.blk_tab >> (16 + b)) & 1u)) * sizeof(HuffTableDev));
+            dc_off = ((sv.blk_tab >> b) & 1u) * uint32_t(sizeof(HuffTableDev));
+            ac_off = (2u + ((sv.blk_tab >> (16 + b)) & 1u)) * uint32_t(sizeof(HuffTableDev));
         }
     }
     if (done) {
@@ -410,7 +438,7 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
         if (kWrite && (z != 0u || uint32_t(blk) != sv.total_blocks))
             out.err |= kFlagOverrun;
     } else {
-        out.state = (p - end_bit) | (z << 6) | (b << 12);
+        out.state = ((p - end_bit) & 63u) | (z << 6) | (b << 12);
     }
     out.blk = blk;
     out.dc0 = dc0;
@@ -441,18 +469,38 @@ __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageD
     return sv;
 }
 
-// K1.  One CTA = kSeqStride consecutive subsequences of one image (+ kSeqWarm warm-up threads that
-// start earlier so the CTA's entry state is right with high probability).  Every thread decodes
-// its subsequence from a guessed state, then the CTA iterates "take the predecessor's exit state
-// as my entry state; re-decode if it changed" to a fixed point.  fix_mode: the first thread takes
-// the stored exit state of the previous sequence instead (used only for images K2 found dirty).
+// K1.  One CTA = kSeqStride consecutive subsequences of one image (+ kSeqWarm leading threads whose
+// only job is to make the CTA's entry state right with high probability).
+//   round 0  every thread decodes the last kProbeBits bits BEFORE its subsequence from the bare guess
+//            "a code word starts here, at a block start": JPEG Huffman streams self-synchronise
+//            within a few dozen symbols, so this usually lands on the true entry state;
+//   round 1  every thread decodes its subsequence from that entry state (exit state, block count, DC sums);
+//   round 2+ "my entry state := my predecessor's exit state; re-decode if it changed", to a fixed
+//            point; the few threads that changed are compacted into the leading warps so the sparse
+//            rounds do not burn issue slots of 8 mostly idle warps.
+// fix mode (images K2 found dirty): the first thread takes the stored exit state of the previous
+// sequence as entry state and only the fixed-point rounds run.
+struct SyncShared {
+    uint32_t in[kSeqThreads];
+    uint32_t out[kSeqThreads];
+    int4 info[kSeqThreads];
+    uint32_t queue[kSeqThreads];
+    uint8_t fresh[kSeqThreads]; // (re)computed by this CTA -> has to be written back
+    uint32_t count;
+};
+
+__device__ __forceinline__ int4 pack_info(const DecodeResult& r)
+{
+    return make_int4(r.blk | (r.restarted ? int32_t(0x80000000u) : 0), r.dc0, r.dc1, r.dc2);
+}
+
 __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int mode)
 {
-    const bool fix_mode = (mode & 1) != 0;
-    const bool no_warm = (mode & 2) != 0; // test hook: start every sequence from the bare guess
     extern __shared__ uint4 s_raw[];
     HuffSetDev* s_hs = reinterpret_cast<HuffSetDev*>(s_raw);
-    uint32_t* s_out = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev));
+    SyncShared& sh = *reinterpret_cast<SyncShared*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev));
+    const bool fix_mode = (mode & 1) != 0;
+    const bool no_warm = (mode & 2) != 0; // test hook: bare guesses, no warm-up threads, no probe
     const uint32_t seq = blockIdx.x;
     const uint32_t img = bd.seq_img[seq];
     const ImageDev& im = bd.img[img];
@@ -465,57 +513,90 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     load_huff_set(s_hs, bd.huff + im.huff_set);
     const StreamView sv = make_view(bd, im, st);
     const int t = threadIdx.x;
-    const int k = int(first_k) - kSeqWarm + t;
+    const int k0 = int(first_k) - kSeqWarm; // subsequence of thread 0 (may be negative)
+    const int k = k0 + t;
     const bool skip_warm = fix_mode || no_warm;
     const bool active = k >= 0 && k < int(st.n_sub) && (!skip_warm || t >= kSeqWarm);
     const bool has_pred = active && t > 0 && k > 0 && (!skip_warm || t > kSeqWarm);
     const uint32_t g = im.sub_off + uint32_t(k);
-    uint32_t in = 0; // true start state for k == 0, the guess "code word starts here, block start" otherwise
+    if (t == 0)
+        sh.count = 0;
+    sh.fresh[t] = 0;
+    __syncthreads(); // tables loaded, counters cleared
     DecodeResult res;
-    res.state = kStateDone;
-    res.blk = 0;
-    res.restarted = 0;
-    res.dc0 = res.dc1 = res.dc2 = 0;
-    res.err = 0;
-    bool need = active;
-    bool decoded = false;
-    if (fix_mode && active) {
-        const uint32_t stored_in = bd.sub_in[g];
-        res.state = bd.sub_out[g];
-        if (t == kSeqWarm) {
-            in = (k > 0) ? bd.sub_out[g - 1] : 0u;
-            need = (in != stored_in);
-        } else {
-            in = stored_in;
-            need = false;
-        }
-    }
-    __syncthreads(); // tables loaded
-    for (;;) {
-        if (need) {
-            decode_subsequence<false>(sv, s_hs, uint32_t(k), in, 0, 0, 0, 0, nullptr, res);
-            decoded = true;
-        }
-        s_out[t] = res.state;
-        __syncthreads();
-        bool chg = false;
-        if (has_pred) {
-            const uint32_t nin = s_out[t - 1];
-            if (nin != in) {
-                in = nin;
-                chg = true;
+    if (fix_mode) {
+        uint32_t in = 0;
+        sh.out[t] = active ? bd.sub_out[g] : kStateDone;
+        if (active) {
+            in = bd.sub_in[g];
+            if (t == kSeqWarm) {
+                const uint32_t want = (k > 0) ? bd.sub_out[g - 1] : 0u;
+                if (want != in) {
+                    in = want;
+                    sh.fresh[t] = 1;
+                    sh.queue[atomicAdd(&sh.count, 1u)] = uint32_t(t);
+                }
             }
         }
-        need = chg;
-        if (!__syncthreads_or(chg))
-            break;
-    }
-    if (active && t >= kSeqWarm) {
-        if (decoded || !fix_mode) {
-            bd.sub_in[g] = in;
-            bd.sub_out[g] = res.state;
-            bd.sub_info[g] = make_int4(res.blk | (res.restarted ? int32_t(0x80000000u) : 0), res.dc0, res.dc1, res.dc2);
+        sh.in[t] = in;
+    } else {
+        uint32_t in = 0; // k == 0: the true start state; otherwise the bare guess
+        if (active && k > 0 && !no_warm) {
+            // round 0: probe the tail of the previous subsequence
+            const uint32_t pb = uint32_t(k) * kSubseqBits - kProbeBits;
+            decode_subsequence<false>(sv, s_hs, pb, uint32_t(k) * kSubseqBits, 0u, 0, 0, 0, 0, nullptr, res);
+            in = res.state;
         }
+        // round 1: everybody
+        res.state = kStateDone;
+        if (active) {
+            decode_subsequence<false>(sv, s_hs, uint32_t(k) * kSubseqBits, uint32_t(k + 1) * kSubseqBits, in, 0, 0, 0, 0, nullptr, res);
+            sh.info[t] = pack_info(res);
+            sh.fresh[t] = 1;
+        }
+        sh.in[t] = in;
+        sh.out[t] = res.state;
+        __syncthreads();
+        if (has_pred && sh.out[t - 1] != in) {
+            sh.in[t] = sh.out[t - 1];
+            sh.queue[atomicAdd(&sh.count, 1u)] = uint32_t(t);
+        }
+    }
+    // fixed-point rounds over the compacted work list.  Invariant: in[t] == out[t-1] for every t,
+    // and out[t] == decode(in[t]) for every t that is not queued.
+    for (;;) {
+        __syncthreads();
+        const uint32_t n = sh.count;
+        if (n == 0u)
+            break;
+        uint32_t item = 0;
+        if (uint32_t(t) < n) {
+            item = sh.queue[t];
+            const uint32_t kk = uint32_t(k0 + int(item));
+            decode_subsequence<false>(sv, s_hs, kk * kSubseqBits, (kk + 1) * kSubseqBits, sh.in[item], 0, 0, 0, 0, nullptr, res);
+        }
+        __syncthreads(); // everyone has read count and queue
+        if (t == 0)
+            sh.count = 0;
+        if (uint32_t(t) < n) {
+            sh.out[item] = res.state;
+            sh.info[item] = pack_info(res);
+        }
+        __syncthreads();
+        if (uint32_t(t) < n) {
+            const uint32_t succ = item + 1;
+            if (succ < uint32_t(kSeqThreads) && k0 + int(succ) < int(st.n_sub) && sh.in[succ] != res.state) {
+                sh.in[succ] = res.state;
+                sh.fresh[succ] = 1;
+                sh.queue[atomicAdd(&sh.count, 1u)] = succ;
+            }
+        }
+    }
+    // results of the real (non warm-up) subsequences
+    if (active && t >= kSeqWarm && sh.fresh[t]) {
+        bd.sub_in[g] = sh.in[t];
+        bd.sub_out[g] = sh.out[t];
+        bd.sub_info[g] = sh.info[t];
     }
 }
 
@@ -613,8 +694,8 @@ __global__ void __launch_bounds__(256) verify_scan_kernel(BatchDev bd, int fix_m
 }
 
 // K3.  Same CTA shape as K1; every thread re-decodes its subsequence from the verified entry
-// state, now knowing its absolute block index and DC predictors, and scatters coefficients
-// (zig-zag order, MCU decode order, absolute DC) into the zeroed coefficient buffer.
+// state, now knowing its absolute block index and DC predictors, and writes the coefficient
+// blocks it owns (zig-zag order, MCU decode order, absolute DC) as whole 16-byte groups.
 __global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, int redo_only)
 {
     extern __shared__ uint4 s_raw[];
@@ -643,7 +724,8 @@ __global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, in
     if (!(in & kStateDone) && (uint32_t(start.x) % im.bpm) != ((in >> 12) & 15u)) {
         err |= kFlagPhase;
     } else {
-        decode_subsequence<true>(sv, s_hs, k, in, start.x, start.y, start.z, start.w, bd.coef + im.coef_off, res);
+        decode_subsequence<true>(sv, s_hs, k * kSubseqBits, (k + 1) * kSubseqBits, in, start.x, start.y, start.z, start.w,
+            bd.coef + im.coef_off, res);
         err |= res.err;
     }
     if (err)
@@ -847,10 +929,238 @@ __device__ __forceinline__ void ycc_to_rgb(int y, int cb, int cr, uint32_t& r, u
     b = clamp255(y + ((116130 * cb + 32768) >> 16));
 }
 
-constexpr int kColorTx = 64; // threads in x, 4 pixels each
-constexpr int kColorTy = 4;
+constexpr int kColorTx = 32; // threads in x, 8 pixels each
+constexpr int kColorTy = 8;  // thread rows, color_unit_rows output rows each
 
-__global__ void __launch_bounds__(kColorTx* kColorTy) color_kernel(BatchDev bd, int redo_only)
+// Generic (any sampling, any alignment) path: one pixel at a time through sample_plane().
+__device__ __forceinline__ void color_pixel_generic(const BatchDev& bd, const ImageDev& im, int x, int y)
+{
+    const PlaneView p0 = make_plane(bd, im, 0);
+    uint32_t r, g, b;
+    if (im.fmt == kFmtY || im.ncomp == 1) {
+        r = g = b = uint32_t(sample_plane(p0, x, y));
+    } else {
+        const PlaneView p1 = make_plane(bd, im, 1), p2 = make_plane(bd, im, 2);
+        ycc_to_rgb(sample_plane(p0, x, y), sample_plane(p1, x, y), sample_plane(p2, x, y), r, g, b);
+    }
+    const int ox = x - im.roi_x0, oy = y - im.roi_y0;
+    if (im.fmt == kFmtY) {
+        im.out[size_t(oy) * im.row_stride + ox] = uint8_t(r);
+        return;
+    }
+    if (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR) {
+        const uint32_t t = r;
+        r = b;
+        b = t;
+    }
+    if (im.fmt == kFmtPRGB || im.fmt == kFmtPBGR) {
+        uint8_t* o = im.out + size_t(oy) * im.row_stride + ox;
+        o[0] = uint8_t(r);
+        o[im.plane_stride] = uint8_t(g);
+        o[2 * im.plane_stride] = uint8_t(b);
+    } else {
+        uint8_t* o = im.out + size_t(oy) * im.row_stride + size_t(ox) * 3;
+        o[0] = uint8_t(r);
+        o[1] = uint8_t(g);
+        o[2] = uint8_t(b);
+    }
+}
+
+__device__ __forceinline__ void unpack8(uint2 v, int* o)
+{
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        o[i] = int((v.x >> (8 * i)) & 0xFFu);
+        o[4 + i] = int((v.y >> (8 * i)) & 0xFFu);
+    }
+}
+
+// Chroma samples for 8 output pixels of one chroma row: HX == 2 -> 6 values (left neighbour, 4
+// centres, right neighbour, all clamped to [0, dw-1] which reproduces libjpeg's edge formulas);
+// HX == 1 -> 8 values.
+template <int HX>
+__device__ __forceinline__ void load_chroma_row(const uint8_t* row, int j0, int dw, int* c)
+{
+    if (HX == 2) {
+        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(row + j0));
+        c[0] = __ldg(row + (j0 > 0 ? j0 - 1 : 0));
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            c[1 + k] = int((w >> (8 * k)) & 0xFFu);
+        c[5] = __ldg(row + (j0 + 4 < dw ? j0 + 4 : dw - 1));
+        if (j0 + 3 > dw - 1) { // right image edge inside this unit: replicate the last real sample
+            int last = c[1];
+#pragma unroll
+            for (int k = 1; k < 4; ++k)
+                if (j0 + k <= dw - 1)
+                    last = c[1 + k];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (j0 + k > dw - 1)
+                    c[1 + k] = last;
+        }
+    } else {
+        unpack8(__ldg(reinterpret_cast<const uint2*>(row + j0)), c);
+    }
+}
+
+// Upsampled chroma for the 8 output pixels of output row `r` (0 or 1 inside the unit).
+//   cur / nbr: chroma row samples as loaded by load_chroma_row (nbr = vertical neighbour, or == cur)
+template <int HX, int VX>
+__device__ __forceinline__ void upsample8(const int* cur, const int* nbr, int r, bool fancy_h, bool fancy_v, int* out)
+{
+    if (HX == 2) {
+        if (VX == 2 && fancy_v) { // h2v2 triangle (jdsample.c h2v2_fancy_upsample)
+            int s[6];
+#pragma unroll
+            for (int k = 0; k < 6; ++k)
+                s[k] = 3 * cur[k] + nbr[k];
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                out[2 * m] = (3 * s[m + 1] + s[m] + 8) >> 4;
+                out[2 * m + 1] = (3 * s[m + 1] + s[m + 2] + 7) >> 4;
+            }
+        } else if (VX == 1 && fancy_h) { // h2v1 triangle
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                out[2 * m] = (3 * cur[m + 1] + cur[m] + 1) >> 2;
+                out[2 * m + 1] = (3 * cur[m + 1] + cur[m + 2] + 2) >> 2;
+            }
+        } else { // box
+#pragma unroll
+            for (int m = 0; m < 4; ++m)
+                out[2 * m] = out[2 * m + 1] = cur[m + 1];
+        }
+    } else {
+        if (VX == 2 && fancy_v) { // h1v2 triangle
+#pragma unroll
+            for (int m = 0; m < 8; ++m)
+                out[m] = (3 * cur[m] + nbr[m] + (r ? 2 : 1)) >> 2;
+        } else {
+#pragma unroll
+            for (int m = 0; m < 8; ++m)
+                out[m] = cur[m];
+        }
+    }
+}
+
+// One unit = 8 pixels x VX rows at image position (X0, Y0), X0 % 8 == 0, Y0 % VX == 0.
+// kLumaOnly: grayscale stream or Y output.
+template <int HX, int VX, bool kLumaOnly>
+__device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& im, int X0, int Y0)
+{
+    const int W = im.width, H = im.height;
+    const uint8_t* p0 = bd.planes + im.plane_off[0];
+    const int stride0 = int(im.mcus_x) * im.h[0] * 8;
+    int cb[VX][8], cr[VX][8];
+    if (!kLumaOnly) {
+        const int stride_c = int(im.mcus_x) * im.h[1] * 8;
+        const int dw = (W * im.h[1] + im.hmax - 1) / im.hmax, dh = (H * im.v[1] + im.vmax - 1) / im.vmax;
+        const bool fancy = im.fancy != 0;
+        const bool fancy_h = fancy && HX == 2 && dw > 2;
+        const bool fancy_v = fancy && VX == 2 && (HX == 1 || dw > 2);
+        const int j0 = X0 / HX;
+        const int ci = Y0 / VX;
+        constexpr int NC = (HX == 2) ? 6 : 8;
+#pragma unroll
+        for (int comp = 1; comp <= 2; ++comp) {
+            const uint8_t* pc = bd.planes + im.plane_off[comp];
+            int cur[NC], up[NC] = {}, dn[NC] = {};
+            load_chroma_row<HX>(pc + size_t(ci) * stride_c, j0, dw, cur);
+            if (VX == 2 && fancy_v) {
+                load_chroma_row<HX>(pc + size_t(ci > 0 ? ci - 1 : 0) * stride_c, j0, dw, up);
+                load_chroma_row<HX>(pc + size_t(ci + 1 < dh ? ci + 1 : dh - 1) * stride_c, j0, dw, dn);
+            }
+#pragma unroll
+            for (int r = 0; r < VX; ++r) {
+                int nb[NC], res[8];
+#pragma unroll
+                for (int k = 0; k < NC; ++k)
+                    nb[k] = (VX == 2 && fancy_v) ? (r == 0 ? up[k] : dn[k]) : cur[k];
+                upsample8<HX, VX>(cur, nb, r, fancy_h, fancy_v, res);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    if (comp == 1)
+                        cb[r][k] = res[k];
+                    else
+                        cr[r][k] = res[k];
+                }
+            }
+        }
+    }
+    const bool swap = (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR);
+    const bool full_x = X0 >= int(im.roi_x0) && X0 + 8 <= int(im.roi_x1);
+#pragma unroll
+    for (int r = 0; r < VX; ++r) {
+        const int y = Y0 + r;
+        if (y < int(im.roi_y0) || y >= int(im.roi_y1))
+            continue;
+        int yy[8];
+        unpack8(__ldg(reinterpret_cast<const uint2*>(p0 + size_t(y) * stride0 + X0)), yy);
+        uint32_t c0[8], c1[8], c2[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (kLumaOnly) {
+                c0[i] = c1[i] = c2[i] = uint32_t(yy[i]);
+            } else {
+                uint32_t rr, gg, bb;
+                ycc_to_rgb(yy[i], cb[r][i], cr[r][i], rr, gg, bb);
+                c0[i] = swap ? bb : rr;
+                c1[i] = gg;
+                c2[i] = swap ? rr : bb;
+            }
+        }
+        const int oy = y - im.roi_y0, ox = X0 - int(im.roi_x0);
+        if (im.fmt == kFmtY || im.fmt == kFmtPRGB || im.fmt == kFmtPBGR) {
+            const int nch = (im.fmt == kFmtY) ? 1 : 3;
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) {
+                if (ch >= nch)
+                    break;
+                const uint32_t* v = ch == 0 ? c0 : (ch == 1 ? c1 : c2);
+                uint8_t* o = im.out + size_t(ch) * im.plane_stride + size_t(oy) * im.row_stride + ox;
+                if (full_x && (reinterpret_cast<uintptr_t>(o) & 7u) == 0) {
+                    uint2 pk;
+                    pk.x = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
+                    pk.y = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
+                    *reinterpret_cast<uint2*>(o) = pk;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        if (X0 + i >= int(im.roi_x0) && X0 + i < int(im.roi_x1))
+                            o[i] = uint8_t(v[i]);
+                }
+            }
+        } else {
+            uint8_t* o = im.out + size_t(oy) * im.row_stride + ptrdiff_t(ox) * 3;
+            if (full_x && (reinterpret_cast<uintptr_t>(o) & 7u) == 0) {
+                uint2 a, b, c;
+                a.x = c0[0] | (c1[0] << 8) | (c2[0] << 16) | (c0[1] << 24);
+                a.y = c1[1] | (c2[1] << 8) | (c0[2] << 16) | (c1[2] << 24);
+                b.x = c2[2] | (c0[3] << 8) | (c1[3] << 16) | (c2[3] << 24);
+                b.y = c0[4] | (c1[4] << 8) | (c2[4] << 16) | (c0[5] << 24);
+                c.x = c1[5] | (c2[5] << 8) | (c0[6] << 16) | (c1[6] << 24);
+                c.y = c2[6] | (c0[7] << 8) | (c1[7] << 16) | (c2[7] << 24);
+                uint2* o8 = reinterpret_cast<uint2*>(o);
+                o8[0] = a;
+                o8[1] = b;
+                o8[2] = c;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    if (X0 + i >= int(im.roi_x0) && X0 + i < int(im.roi_x1)) {
+                        o[3 * i + 0] = uint8_t(c0[i]);
+                        o[3 * i + 1] = uint8_t(c1[i]);
+                        o[3 * i + 2] = uint8_t(c2[i]);
+                    }
+            }
+        }
+    }
+}
+
+// K4b.  CTA = 32 x 8 threads; a thread owns one unit of 8 pixels x unit_rows rows, aligned in image
+// coordinates so that every plane load is a naturally aligned 4- or 8-byte word.
+__global__ void __launch_bounds__(kColorTx* kColorTy, 2) color_kernel(BatchDev bd, int redo_only)
 {
     const uint32_t cta = blockIdx.x;
     const uint32_t img = bd.color_cta_img[cta];
@@ -860,74 +1170,30 @@ __global__ void __launch_bounds__(kColorTx* kColorTy) color_kernel(BatchDev bd, 
         return;
     const uint32_t local = cta - im.color_cta_off;
     const uint32_t cy = local / im.n_color_cta_x, cx = local - cy * im.n_color_cta_x;
-    const int rw = int(im.roi_x1) - int(im.roi_x0), rh = int(im.roi_y1) - int(im.roi_y0);
-    const int ox = (cx * kColorTx + (threadIdx.x % kColorTx)) * 4;
-    const int oy = cy * kColorTy + threadIdx.x / kColorTx;
-    if (ox >= rw || oy >= rh)
+    const int tx = threadIdx.x % kColorTx, ty = threadIdx.x / kColorTx;
+    const int urows = im.color_unit_rows;
+    const int X0 = (int(im.roi_x0) & ~7) + (int(cx) * kColorTx + tx) * 8;
+    const int Y0 = (int(im.roi_y0) / urows) * urows + (int(cy) * kColorTy + ty) * urows;
+    if (X0 >= int(im.roi_x1) || Y0 >= int(im.roi_y1))
         return;
-    const int n = (rw - ox) < 4 ? (rw - ox) : 4;
-    const int y = oy + im.roi_y0;
-    const PlaneView p0 = make_plane(bd, im, 0);
-    uint32_t px[4][3];
-    if (im.fmt == kFmtY || im.ncomp == 1) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const uint32_t v = (i < n) ? uint32_t(sample_plane(p0, ox + i + im.roi_x0, y)) : 0u;
-            px[i][0] = px[i][1] = px[i][2] = v;
-        }
-    } else {
-        const PlaneView p1 = make_plane(bd, im, 1), p2 = make_plane(bd, im, 2);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int x = ox + (i < n ? i : 0) + im.roi_x0;
-            ycc_to_rgb(sample_plane(p0, x, y), sample_plane(p1, x, y), sample_plane(p2, x, y), px[i][0], px[i][1], px[i][2]);
-        }
-    }
-    const bool swap = (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR);
-    if (swap) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const uint32_t t = px[i][0];
-            px[i][0] = px[i][2];
-            px[i][2] = t;
-        }
-    }
-    if (im.fmt == kFmtY || im.fmt == kFmtPRGB || im.fmt == kFmtPBGR) {
-        const int nch = (im.fmt == kFmtY) ? 1 : 3;
-#pragma unroll
-        for (int ch = 0; ch < 3; ++ch) {
-            if (ch < nch) {
-                uint8_t* o = im.out + size_t(ch) * im.plane_stride + size_t(oy) * im.row_stride + ox;
-                if (n == 4 && ((reinterpret_cast<uintptr_t>(o) & 3u) == 0)) {
-                    *reinterpret_cast<uint32_t*>(o) = px[0][ch] | (px[1][ch] << 8) | (px[2][ch] << 16) | (px[3][ch] << 24);
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        if (i < n)
-                            o[i] = uint8_t(px[i][ch]);
-                }
+    switch (im.color_mode) {
+    case 1: color_unit<1, 1, true>(bd, im, X0, Y0); break;
+    case 2: color_unit<1, 1, false>(bd, im, X0, Y0); break;
+    case 3: color_unit<2, 1, false>(bd, im, X0, Y0); break;
+    case 4: color_unit<1, 2, false>(bd, im, X0, Y0); break;
+    case 5: color_unit<2, 2, false>(bd, im, X0, Y0); break;
+    default:
+        for (int r = 0; r < urows; ++r)
+            for (int i = 0; i < 8; ++i) {
+                const int x = X0 + i, y = Y0 + r;
+                if (x >= int(im.roi_x0) && x < int(im.roi_x1) && y >= int(im.roi_y0) && y < int(im.roi_y1))
+                    color_pixel_generic(bd, im, x, y);
             }
-        }
-        return;
-    }
-    uint8_t* o = im.out + size_t(oy) * im.row_stride + size_t(ox) * 3;
-    if (n == 4 && ((reinterpret_cast<uintptr_t>(o) & 3u) == 0)) {
-        uint32_t* o32 = reinterpret_cast<uint32_t*>(o);
-        o32[0] = px[0][0] | (px[0][1] << 8) | (px[0][2] << 16) | (px[1][0] << 24);
-        o32[1] = px[1][1] | (px[1][2] << 8) | (px[2][0] << 16) | (px[2][1] << 24);
-        o32[2] = px[2][2] | (px[3][0] << 8) | (px[3][1] << 16) | (px[3][2] << 24);
-    } else {
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-            if (i < n) {
-                o[3 * i + 0] = uint8_t(px[i][0]);
-                o[3 * i + 1] = uint8_t(px[i][1]);
-                o[3 * i + 2] = uint8_t(px[i][2]);
-            }
+        break;
     }
 }
 
-constexpr size_t kSyncSmem = sizeof(HuffSetDev) + kSeqThreads * sizeof(uint32_t);
+constexpr size_t kSyncSmem = sizeof(HuffSetDev) + sizeof(SyncShared);
 
 } // namespace
 

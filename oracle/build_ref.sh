@@ -1,0 +1,59 @@
+#!/usr/bin/env bash
+# Builds, from the reference's OWN sources where they lie under /root/reference, the pieces the
+# tests and the CPU baseline need.  Outputs go only to oracle/_ref/ (git-ignored, shipped to the
+# GPU box).  Nothing is copied into the repository; the reference's CMake build is not run
+# (it needs zstd/OpenCV/network, see DESIGN.md "Reference builds").
+#
+#   oracle/_ref/libnvimgcodec.so   the unmodified nvImageCodec core (src/*.cpp, src/parsers, src/imgproc)
+#                                  -- the host framework that loads our extension in tests/
+#   oracle/_ref/host_driver        tests/host/host_driver.cpp linked against it (our own file)
+set -euo pipefail
+HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
+REF="${REFERENCE_ROOT:-/root/reference}"
+OUT="$HERE/_ref"
+OBJ="$OUT/obj"
+GEN="$OUT/gen"
+CUDA="${CUDA_HOME:-/usr/local/cuda}"
+JOBS="${JOBS:-$(nproc)}"
+[ -d "$REF/src" ] || { echo "reference tree not found at $REF; keeping prebuilt oracle/_ref" >&2; exit 0; }
+mkdir -p "$OBJ" "$GEN"
+
+sed -e 's/@PROJECT_VERSION_MAJOR@/0/;s/@PROJECT_VERSION_MINOR@/8/;s/@PROJECT_VERSION_PATCH@/0/;s/@PROJECT_VERSION_TWEAK@/0/' \
+    "$REF/include/nvimgcodec_version.h.in" > "$GEN/nvimgcodec_version.h.tmp"
+cmp -s "$GEN/nvimgcodec_version.h.tmp" "$GEN/nvimgcodec_version.h" 2>/dev/null || mv "$GEN/nvimgcodec_version.h.tmp" "$GEN/nvimgcodec_version.h"
+rm -f "$GEN/nvimgcodec_version.h.tmp"
+
+INC="-I$GEN -I$REF/include -I$REF/src -I$REF -I$REF/external/NVTX/c/include -I$REF/external/boost/preprocessor/include -I$CUDA/include"
+CXXFLAGS="-std=c++20 -O2 -fPIC -DNDEBUG -w"
+
+SRCS="nvimgcodec_capi plugin_framework codec_registry codec image_decoder image_encoder image_parser code_stream file_io_stream
+ std_file_io_stream mmaped_file_io_stream image image_parser_factory image_encoder_factory image_decoder_factory image_generic_decoder
+ image_generic_encoder nvimgcodec_director processing_results decode_state_batch encode_state_batch thread_pool default_executor
+ builtin_modules parsers/bmp parsers/exif parsers/jpeg parsers/jpeg2k parsers/tiff parsers/png parsers/pnm parsers/webp
+ parsers/parsers_ext_module imgproc/pinned_buffer imgproc/device_buffer imgproc/exception imgproc/out_of_bound_roi_fill
+ imgproc/stream_device dynlink/dynlink_cuda"
+
+{
+  echo "all: objs"
+  OBJS=""
+  for s in $SRCS; do
+    [ -f "$REF/src/$s.cpp" ] || continue
+    o="$OBJ/$(echo "$s" | tr '/' '_').o"
+    OBJS="$OBJS $o"
+    printf '%s: %s\n\tg++ %s %s -c $< -o $@\n' "$o" "$REF/src/$s.cpp" "$CXXFLAGS" "$INC"
+  done
+  o="$OBJ/imgproc_convert_kernel_gpu.o"
+  OBJS="$OBJS $o"
+  printf '%s: %s\n\tnvcc -gencode arch=compute_100a,code=sm_100a -std=c++20 -O2 -Xcompiler -fPIC -DNDEBUG -w %s -c $< -o $@\n' \
+      "$o" "$REF/src/imgproc/convert_kernel_gpu.cu" "$INC"
+  echo "objs:$OBJS"
+} > "$OUT/ref.mk"
+make -s -j"$JOBS" -f "$OUT/ref.mk"
+
+OBJS=$(ls "$OBJ"/*.o)
+g++ -shared -o "$OUT/libnvimgcodec.so" $OBJS -L"$CUDA/lib64" -L"$CUDA/lib64/stubs" -lcudart_static -lcuda -ldl -lpthread -lrt
+if [ -f "$HERE/../tests/host/host_driver.cpp" ]; then
+  g++ -std=c++17 -O2 -I"$GEN" -I"$REF/include" -I"$CUDA/include" "$HERE/../tests/host/host_driver.cpp" -o "$OUT/host_driver" \
+      -L"$OUT" -lnvimgcodec -Wl,-rpath,'$ORIGIN' -L"$CUDA/lib64" -lcudart_static -ldl -lpthread -lrt
+fi
+echo "built $(ls "$OUT" | grep -v -E '^(obj|gen|ref.mk)$' | tr '\n' ' ')"
