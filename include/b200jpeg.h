@@ -109,6 +109,28 @@ B200JPEG_API int b200jpegPrepareBatch(b200jpegDecoder_t decoder, int batch_size,
 B200JPEG_API int b200jpegExecuteBatch(b200jpegDecoder_t decoder, void* cuda_stream);
 B200JPEG_API int b200jpegFinishBatch(b200jpegDecoder_t decoder, int* status, void* cuda_stream);
 
+/* Kernel-level entry: the marker + restart-interval scan (K0) of ONE entropy-coded segment that is
+ * already in device memory.  Drops the stuffed 0x00 after 0xFF, fill bytes and RSTn markers, stops at
+ * the first other marker, and records where each restart interval starts.  What the reference gets
+ * from libjpeg-turbo's bit reader + restart handling (jdhuff.c / jdmarker.c behind
+ * extensions/libjpeg_turbo/jpeg_mem.cpp:311-379); exposed so the kernel can be tested on its own.
+ *   dev_raw            device pointer, 16-byte aligned, readable for length + 16 bytes
+ *   dev_out_words      device buffer of at least round_up(length, 16) + 32 bytes: the unstuffed stream as
+ *                      big-endian 32-bit words (byte i of the stream is at byte address i ^ 3)
+ *   dev_out_boundaries device uint32[boundary_capacity], boundary_capacity >= expected_restart_markers + 1:
+ *                      unstuffed byte offset of the start of restart interval 1, 2, ...; the entry
+ *                      after the last one is the unstuffed length
+ *   dev_result         device pointer, filled asynchronously on cuda_stream
+ * The decoder's own (cudaMalloc'ed, grow-only) scratch is used for the per-tile counts. */
+typedef struct {
+    uint32_t unstuffed_bytes;
+    uint32_t num_restart_markers;
+    uint32_t num_subsequences; /* ceil(unstuffed bits / 1024), 0 if flags != 0 */
+    uint32_t flags;            /* bit 0: restart markers out of sequence or not the expected number */
+} b200jpegScanResult_t;
+B200JPEG_API int b200jpegScanSegment(b200jpegDecoder_t decoder, const void* dev_raw, size_t length, uint32_t expected_restart_markers,
+    void* dev_out_words, uint32_t* dev_out_boundaries, uint32_t boundary_capacity, b200jpegScanResult_t* dev_result, void* cuda_stream);
+
 /* Introspection for benchmarks and tests. */
 enum {
     B200JPEG_STAT_KERNEL_LAUNCHES = 0, /* kernels launched by the last Execute */

@@ -25,6 +25,11 @@ class StreamInfo(ctypes.Structure):
                 ("mcus_x", ctypes.c_int), ("mcus_y", ctypes.c_int), ("blocks_per_mcu", ctypes.c_int)]
 
 
+class ScanResult(ctypes.Structure):
+    _fields_ = [("unstuffed_bytes", ctypes.c_uint32), ("num_restart_markers", ctypes.c_uint32),
+                ("num_subsequences", ctypes.c_uint32), ("flags", ctypes.c_uint32)]
+
+
 class Output(ctypes.Structure):
     _fields_ = [("buffer", ctypes.c_void_p), ("format", ctypes.c_int), ("buffer_is_host", ctypes.c_int),
                 ("row_stride", ctypes.c_size_t), ("roi_x0", ctypes.c_int), ("roi_y0", ctypes.c_int),
@@ -33,7 +38,7 @@ class Output(ctypes.Structure):
 
 EXPORTS = ["b200jpegProbe", "b200jpegCreate", "b200jpegDestroy", "b200jpegDecodeBatch", "b200jpegPrepareBatch",
            "b200jpegExecuteBatch", "b200jpegFinishBatch", "b200jpegGetStat", "b200jpegSetProfiling", "b200jpegGetStageTimes",
-           "b200jpegDebugCopyCoefficients", "b200jpegGetLastError", "b200jpegVersion"]
+           "b200jpegDebugCopyCoefficients", "b200jpegGetLastError", "b200jpegVersion", "b200jpegScanSegment"]
 
 _lib = None
 
@@ -71,6 +76,8 @@ def load():
     L.b200jpegGetStageTimes.restype = ci
     L.b200jpegDebugCopyCoefficients.argtypes = [vp, ci, vp, sz]
     L.b200jpegDebugCopyCoefficients.restype = ci
+    L.b200jpegScanSegment.argtypes = [vp, vp, sz, ctypes.c_uint32, vp, vp, ctypes.c_uint32, vp, vp]
+    L.b200jpegScanSegment.restype = ci
     L.b200jpegGetLastError.argtypes = [vp]
     L.b200jpegGetLastError.restype = ctypes.c_char_p
     L.b200jpegVersion.argtypes = []

@@ -139,6 +139,20 @@ int b200jpegDecodeBatch(b200jpegDecoder_t decoder, int batch_size, const void* c
     return b200jpegFinishBatch(decoder, status, cuda_stream);
 }
 
+int b200jpegScanSegment(b200jpegDecoder_t decoder, const void* dev_raw, size_t length, uint32_t expected_restart_markers, void* dev_out_words,
+    uint32_t* dev_out_boundaries, uint32_t boundary_capacity, b200jpegScanResult_t* dev_result, void* cuda_stream)
+{
+    if (!decoder)
+        return B200JPEG_ERR_ARG;
+    static_assert(sizeof(b200jpegScanResult_t) == sizeof(b200jpeg::ImageState), "result layout");
+    try {
+        return decoder->impl->scan_segment(dev_raw, length, expected_restart_markers, dev_out_words, dev_out_boundaries, boundary_capacity,
+            dev_result, static_cast<cudaStream_t>(cuda_stream));
+    } catch (...) {
+        return B200JPEG_ERR_STATE;
+    }
+}
+
 int64_t b200jpegGetStat(b200jpegDecoder_t decoder, int which) { return decoder ? decoder->impl->stat(which) : -1; }
 
 int b200jpegSetProfiling(b200jpegDecoder_t decoder, int enable)

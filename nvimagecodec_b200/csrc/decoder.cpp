@@ -123,6 +123,8 @@ Decoder::~Decoder()
     coef_.release();
     planes_.release();
     bounce_.release();
+    scan_scratch_.release();
+    scan_host_.release();
     upload_host_.release();
     state_host_.release();
 }
@@ -578,6 +580,57 @@ int Decoder::copy_coefficients(int index, int16_t* host_out, size_t cap_elems)
         return fail(B200JPEG_ERR_ARG, "buffer too small");
     cudaSetDevice(device_);
     if (!cuda_ok(cudaMemcpy(host_out, bd_.coef + im.coef_off, elems * sizeof(int16_t), cudaMemcpyDeviceToHost), "coefficient copy"))
+        return B200JPEG_ERR_CUDA;
+    return B200JPEG_OK;
+}
+
+// Kernel-level K0 entry (b200jpegScanSegment): one segment, descriptors and per-tile counts in
+// decoder-owned scratch, everything else supplied by the caller.
+int Decoder::scan_segment(const void* dev_raw, size_t length, uint32_t expected_rst, void* dev_words, uint32_t* dev_bnd, uint32_t bnd_cap,
+    void* dev_result, cudaStream_t stream)
+{
+    if (!dev_raw || !dev_words || !dev_bnd || !dev_result || length == 0 || (reinterpret_cast<uintptr_t>(dev_raw) & 15u) ||
+        (reinterpret_cast<uintptr_t>(dev_words) & 3u) || bnd_cap < expected_rst + 1)
+        return fail(B200JPEG_ERR_ARG, "bad argument");
+    if (length >= (size_t(1) << 29))
+        return fail(B200JPEG_ERR_TOO_LARGE, "segment too large");
+    if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
+        return B200JPEG_ERR_CUDA;
+    const uint32_t n_tiles = uint32_t((length + kScanTileBytes - 1) / kScanTileBytes);
+    const size_t off_tile = align_up(sizeof(ImageDev), 256);
+    const size_t off_info = align_up(off_tile + 4ull * n_tiles, 256);
+    const size_t off_base = align_up(off_info + 8ull * n_tiles, 256);
+    const size_t total = off_base + 8ull * n_tiles;
+    if (!scan_scratch_.ensure(total, &device_bytes_) || !scan_host_.ensure(off_info))
+        return fail(B200JPEG_ERR_CUDA, "allocation failed");
+    // the previous call's upload may still be in flight out of the pinned staging block
+    if (!cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
+        return B200JPEG_ERR_CUDA;
+    uint8_t* hp = scan_host_.as<uint8_t>();
+    ImageDev im;
+    std::memset(&im, 0, sizeof(im));
+    im.raw_len = uint32_t(length);
+    im.n_tiles = n_tiles;
+    im.n_rst_expected = expected_rst;
+    im.n_bnd_cap = bnd_cap;
+    std::memcpy(hp, &im, sizeof(im));
+    std::memset(hp + off_tile, 0, 4ull * n_tiles);
+    uint8_t* dp = scan_scratch_.as<uint8_t>();
+    if (!cuda_ok(cudaMemcpyAsync(dp, hp, off_tile + 4ull * n_tiles, cudaMemcpyHostToDevice, stream), "upload"))
+        return B200JPEG_ERR_CUDA;
+    BatchDev b{};
+    b.n_images = 1;
+    b.img = reinterpret_cast<const ImageDev*>(dp);
+    b.tile_img = reinterpret_cast<const uint32_t*>(dp + off_tile);
+    b.tile_info = reinterpret_cast<uint2*>(dp + off_info);
+    b.tile_base = reinterpret_cast<uint2*>(dp + off_base);
+    b.state = static_cast<ImageState*>(dev_result);
+    b.raw = static_cast<const uint8_t*>(dev_raw);
+    b.cmp = static_cast<uint32_t*>(dev_words);
+    b.bnd = dev_bnd;
+    b.n_tiles = int(n_tiles);
+    launch_scan(b, stream);
+    if (!cuda_ok(cudaGetLastError(), "kernel launch"))
         return B200JPEG_ERR_CUDA;
     return B200JPEG_OK;
 }

@@ -55,6 +55,8 @@ class Decoder {
     void set_profiling(bool on) { profiling_ = on; }
     int stage_times(float* ms, const char** names, int cap);
     int copy_coefficients(int index, int16_t* host_out, size_t cap_elems);
+    int scan_segment(const void* dev_raw, size_t length, uint32_t expected_rst, void* dev_words, uint32_t* dev_bnd, uint32_t bnd_cap,
+        void* dev_result, cudaStream_t stream);
     const char* last_error() const { return err_.c_str(); }
     int device() const { return device_; }
 
@@ -82,8 +84,8 @@ class Decoder {
     bool prepared_ = false, executed_ = false;
 
     // device memory
-    DeviceBuffer upload_, scratch_, cmp_, coef_, planes_, bounce_;
-    PinnedBuffer upload_host_, state_host_;
+    DeviceBuffer upload_, scratch_, cmp_, coef_, planes_, bounce_, scan_scratch_;
+    PinnedBuffer upload_host_, state_host_, scan_host_;
     size_t device_bytes_ = 0;
     size_t coef_bytes_ = 0;
     BatchDev bd_{};
