@@ -131,6 +131,36 @@ typedef struct {
 B200JPEG_API int b200jpegScanSegment(b200jpegDecoder_t decoder, const void* dev_raw, size_t length, uint32_t expected_restart_markers,
     void* dev_out_words, uint32_t* dev_out_boundaries, uint32_t boundary_capacity, b200jpegScanResult_t* dev_result, void* cuda_stream);
 
+/* The same scan for callers that cannot allocate.  (No counterpart in the reference: nvImageCodec
+ * plugins always go through an allocator.)
+ *
+ * Who this is for: code that runs after the process has handed all of its device memory to something
+ * else -- a training framework's caching pool, a fixed up-front budget in an ingest service -- so that
+ * a later cudaMalloc can fail outright, and code on a latency-critical path where the device-wide
+ * synchronisation cudaMalloc / cudaFree imply is not acceptable.  b200jpegScanSegment grows the
+ * decoder's scratch with cudaMalloc the first time it sees a larger segment; this entry point never
+ * calls cudaMalloc, cudaFree or any other allocating routine, and needs no decoder handle.
+ *
+ * How: the per-tile counts, the tile map and the segment descriptor that K0 needs live in one fixed
+ * 41 KiB array inside the library (a static __device__ array; every GPU that loads the library
+ * holds it until the process exits).  That bounds the segment: length must not exceed
+ * B200JPEG_NOALLOC_MAX_SEGMENT_BYTES (8 MiB of byte-stuffed scan data); longer segments are refused
+ * with B200JPEG_ERR_TOO_LARGE and nothing is launched.  Inputs and outputs are the caller's, with the
+ * same requirements as b200jpegScanSegment, on the device that is current when the call is made.
+ *
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ * that device current); make that first call before starting any stream capture.  All calls on a
+ * device share the one array, and it keeps whatever the previous call left: the entry point
+ * rewrites the parts that must start clean on the given stream, but two calls whose GPU work can
+ * overlap (different streams, different host threads) race on it -- serialise them.
+ *
+ * message (optional, may be NULL) receives a human-readable reason when the return value is not
+ * B200JPEG_OK. */
+#define B200JPEG_NOALLOC_MAX_SEGMENT_BYTES (8u << 20)
+B200JPEG_API int b200jpegScanSegmentNoAlloc(const void* dev_raw, size_t length, uint32_t expected_restart_markers, void* dev_out_words,
+    uint32_t* dev_out_boundaries, uint32_t boundary_capacity, b200jpegScanResult_t* dev_result, void* cuda_stream, char* message,
+    size_t message_capacity);
+
 /* Introspection for benchmarks and tests. */
 enum {
     B200JPEG_STAT_KERNEL_LAUNCHES = 0, /* kernels launched by the last Execute */

@@ -13,6 +13,8 @@ OK, ERR_ARG, ERR_NOT_JPEG, ERR_UNSUPPORTED, ERR_CORRUPT, ERR_CUDA, ERR_STATE, ER
 STATUS_NAMES = ["OK", "ERR_ARG", "ERR_NOT_JPEG", "ERR_UNSUPPORTED", "ERR_CORRUPT", "ERR_CUDA", "ERR_STATE", "ERR_TOO_LARGE"]
 FMT = {"I_RGB": 0, "I_BGR": 1, "P_RGB": 2, "P_BGR": 3, "P_Y": 4, "I_Y": 4, "Y": 4}
 
+NOALLOC_MAX_SEGMENT_BYTES = 8 << 20
+
 (STAT_KERNEL_LAUNCHES, STAT_ALGO_BYTES, STAT_COMPRESSED_BYTES, STAT_NUM_COEFS, STAT_OUTPUT_BYTES, STAT_RESYNC_IMAGES,
  STAT_DEVICE_BYTES, STAT_NUM_SUBSEQ) = range(8)
 
@@ -38,7 +40,8 @@ class Output(ctypes.Structure):
 
 EXPORTS = ["b200jpegProbe", "b200jpegCreate", "b200jpegDestroy", "b200jpegDecodeBatch", "b200jpegPrepareBatch",
            "b200jpegExecuteBatch", "b200jpegFinishBatch", "b200jpegGetStat", "b200jpegSetProfiling", "b200jpegGetStageTimes",
-           "b200jpegDebugCopyCoefficients", "b200jpegGetLastError", "b200jpegVersion", "b200jpegScanSegment"]
+           "b200jpegDebugCopyCoefficients", "b200jpegGetLastError", "b200jpegVersion", "b200jpegScanSegment",
+           "b200jpegScanSegmentNoAlloc"]
 
 _lib = None
 
@@ -78,6 +81,8 @@ def load():
     L.b200jpegDebugCopyCoefficients.restype = ci
     L.b200jpegScanSegment.argtypes = [vp, vp, sz, ctypes.c_uint32, vp, vp, ctypes.c_uint32, vp, vp]
     L.b200jpegScanSegment.restype = ci
+    L.b200jpegScanSegmentNoAlloc.argtypes = [vp, sz, ctypes.c_uint32, vp, vp, ctypes.c_uint32, vp, vp, ctypes.c_char_p, sz]
+    L.b200jpegScanSegmentNoAlloc.restype = ci
     L.b200jpegGetLastError.argtypes = [vp]
     L.b200jpegGetLastError.restype = ctypes.c_char_p
     L.b200jpegVersion.argtypes = []

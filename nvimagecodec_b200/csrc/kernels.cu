@@ -13,6 +13,11 @@
 // No tensor cores: the work is bit-serial entropy decode and 8x8 integer butterflies.
 #include "kernels.cuh"
 
+#include <cstring>
+#include <mutex>
+
+#include "b200jpeg.h"
+
 namespace b200jpeg {
 
 namespace {
@@ -1254,3 +1259,130 @@ int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s)
 }
 
 } // namespace b200jpeg
+
+// ------------------------------------------------------------------------------------------------
+// b200jpegScanSegmentNoAlloc: the K0 scan for callers that must not allocate
+// ------------------------------------------------------------------------------------------------
+// Everything K0 needs besides the caller's input and outputs -- the segment descriptor, the
+// tile->segment map and the per-tile counts / prefixes -- lives in this fixed array, which every
+// GPU that loads the library carries until the process exits.
+namespace b200jpeg {
+namespace {
+
+constexpr size_t kNoAllocMaxTiles = B200JPEG_NOALLOC_MAX_SEGMENT_BYTES / kScanTileBytes;
+constexpr size_t kNoAllocDescBytes = 1024;
+static_assert(sizeof(ImageDev) <= kNoAllocDescBytes, "descriptor slot too small");
+constexpr size_t kNoAllocOffTileImg = kNoAllocDescBytes;
+constexpr size_t kNoAllocOffInfo = kNoAllocOffTileImg + 4 * kNoAllocMaxTiles;
+constexpr size_t kNoAllocOffBase = kNoAllocOffInfo + 8 * kNoAllocMaxTiles;
+constexpr size_t kNoAllocScratchBytes = kNoAllocOffBase + 8 * kNoAllocMaxTiles; // 1 KiB + 20 B per 4 KiB tile = 41 KiB
+
+static __device__ __align__(256) unsigned char g_noalloc_scan_scratch[kNoAllocScratchBytes];
+
+struct NoAllocParams {
+    uint32_t raw_len, n_tiles, n_rst_expected, n_bnd_cap;
+};
+
+// Rewrites the part of the shared scratch that has to start from a known value: the descriptor
+// (all fields; the array still holds the previous call's) and the tile->segment map (all zero).
+__global__ void noalloc_scan_setup_kernel(unsigned char* scratch, NoAllocParams p)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t* desc_words = reinterpret_cast<uint32_t*>(scratch);
+    if (i < kNoAllocDescBytes / 4)
+        desc_words[i] = 0u;
+    if (i < p.n_tiles)
+        reinterpret_cast<uint32_t*>(scratch + kNoAllocOffTileImg)[i] = 0u;
+    __syncthreads();
+    if (i == 0) {
+        ImageDev* im = reinterpret_cast<ImageDev*>(scratch);
+        im->raw_len = p.raw_len;
+        im->n_tiles = p.n_tiles;
+        im->n_rst_expected = p.n_rst_expected;
+        im->n_bnd_cap = p.n_bnd_cap;
+    }
+}
+
+// Device address of the scratch array, resolved once per device (the array's name is only a
+// host-side handle; kernels need the address cudaGetSymbolAddress reports for the current device).
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[64] = {};
+
+int noalloc_scratch_for_current_device(unsigned char** out)
+{
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+        return B200JPEG_ERR_CUDA;
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        unsigned char* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_scan_scratch);
+        if (e != cudaSuccess || !ptr) {
+            cudaGetLastError();
+            return B200JPEG_ERR_CUDA;
+        }
+        g_noalloc_ptr[dev] = ptr;
+    }
+    *out = g_noalloc_ptr[dev];
+    return B200JPEG_OK;
+}
+
+void noalloc_message(char* message, size_t capacity, const char* text)
+{
+    if (message && capacity) {
+        std::strncpy(message, text, capacity - 1);
+        message[capacity - 1] = '\0';
+    }
+}
+
+} // namespace
+} // namespace b200jpeg
+
+extern "C" B200JPEG_API int b200jpegScanSegmentNoAlloc(const void* dev_raw, size_t length, uint32_t expected_restart_markers,
+    void* dev_out_words, uint32_t* dev_out_boundaries, uint32_t boundary_capacity, b200jpegScanResult_t* dev_result, void* cuda_stream,
+    char* message, size_t message_capacity)
+{
+    using namespace b200jpeg;
+    noalloc_message(message, message_capacity, "");
+    if (!dev_raw || !dev_out_words || !dev_out_boundaries || !dev_result || length == 0 || (reinterpret_cast<uintptr_t>(dev_raw) & 15u) ||
+        (reinterpret_cast<uintptr_t>(dev_out_words) & 3u) || boundary_capacity < expected_restart_markers + 1) {
+        noalloc_message(message, message_capacity, "b200jpegScanSegmentNoAlloc: null / misaligned pointer, empty segment or boundary array too small");
+        return B200JPEG_ERR_ARG;
+    }
+    if (length > size_t(B200JPEG_NOALLOC_MAX_SEGMENT_BYTES)) {
+        noalloc_message(message, message_capacity,
+            "b200jpegScanSegmentNoAlloc: segment longer than B200JPEG_NOALLOC_MAX_SEGMENT_BYTES (8 MiB); the fixed scratch cannot hold its tile counts");
+        return B200JPEG_ERR_TOO_LARGE;
+    }
+    unsigned char* scratch = nullptr;
+    if (noalloc_scratch_for_current_device(&scratch) != B200JPEG_OK) {
+        noalloc_message(message, message_capacity, "b200jpegScanSegmentNoAlloc: cudaGetSymbolAddress failed on the current device");
+        return B200JPEG_ERR_CUDA;
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    NoAllocParams p;
+    p.raw_len = uint32_t(length);
+    p.n_tiles = uint32_t((length + kScanTileBytes - 1) / kScanTileBytes);
+    p.n_rst_expected = expected_restart_markers;
+    p.n_bnd_cap = boundary_capacity;
+    // block 0 clears and refills the descriptor (one barrier apart); all blocks clear the tile map
+    const uint32_t setup_threads = p.n_tiles > uint32_t(kNoAllocDescBytes / 4) ? p.n_tiles : uint32_t(kNoAllocDescBytes / 4);
+    noalloc_scan_setup_kernel<<<(setup_threads + 1023) / 1024, 1024, 0, stream>>>(scratch, p);
+    BatchDev b{};
+    b.n_images = 1;
+    b.img = reinterpret_cast<const ImageDev*>(scratch);
+    b.tile_img = reinterpret_cast<const uint32_t*>(scratch + kNoAllocOffTileImg);
+    b.tile_info = reinterpret_cast<uint2*>(scratch + kNoAllocOffInfo);
+    b.tile_base = reinterpret_cast<uint2*>(scratch + kNoAllocOffBase);
+    b.state = reinterpret_cast<ImageState*>(dev_result);
+    b.raw = static_cast<const uint8_t*>(dev_raw);
+    b.cmp = static_cast<uint32_t*>(dev_out_words);
+    b.bnd = dev_out_boundaries;
+    b.n_tiles = int(p.n_tiles);
+    launch_scan(b, stream);
+    if (cudaGetLastError() != cudaSuccess) {
+        noalloc_message(message, message_capacity, "b200jpegScanSegmentNoAlloc: kernel launch failed");
+        return B200JPEG_ERR_CUDA;
+    }
+    return B200JPEG_OK;
+}
