@@ -6,9 +6,12 @@
 #include "decoder.h"
 
 using b200jpeg::Decoder;
+using b200jpeg::Pipeline;
 
 struct b200jpegDecoder_st {
-    Decoder* impl;
+    Pipeline* pipe;
+    Decoder* impl; // lane 0 of the pipeline: Prepare / Execute / Finish, kernel-level entry points, introspection
+    bool last_was_pipeline;
 };
 
 namespace {
@@ -75,11 +78,13 @@ int b200jpegCreate(b200jpegDecoder_t* decoder, int device_id, const char* option
     auto* h = new (std::nothrow) b200jpegDecoder_st;
     if (!h)
         return B200JPEG_ERR_ARG;
-    h->impl = new (std::nothrow) Decoder(device_id, b200jpeg::parse_options(options, kDecoderId));
-    if (!h->impl) {
+    h->pipe = new (std::nothrow) Pipeline(device_id, b200jpeg::parse_options(options, kDecoderId));
+    if (!h->pipe) {
         delete h;
         return B200JPEG_ERR_ARG;
     }
+    h->impl = &h->pipe->lane0();
+    h->last_was_pipeline = false;
     *decoder = h;
     return B200JPEG_OK;
 }
@@ -88,7 +93,7 @@ int b200jpegDestroy(b200jpegDecoder_t decoder)
 {
     if (!decoder)
         return B200JPEG_OK;
-    delete decoder->impl;
+    delete decoder->pipe;
     delete decoder;
     return B200JPEG_OK;
 }
@@ -99,6 +104,7 @@ int b200jpegPrepareBatch(b200jpegDecoder_t decoder, int batch_size, const void* 
     if (!decoder)
         return B200JPEG_ERR_ARG;
     try {
+        decoder->last_was_pipeline = false;
         return decoder->impl->prepare(batch_size, data, lengths, outputs, static_cast<cudaStream_t>(cuda_stream));
     } catch (...) {
         return B200JPEG_ERR_STATE;
@@ -130,13 +136,14 @@ int b200jpegFinishBatch(b200jpegDecoder_t decoder, int* status, void* cuda_strea
 int b200jpegDecodeBatch(b200jpegDecoder_t decoder, int batch_size, const void* const* data, const size_t* lengths,
     const b200jpegOutput_t* outputs, int* status, void* cuda_stream)
 {
-    int rc = b200jpegPrepareBatch(decoder, batch_size, data, lengths, outputs, cuda_stream);
-    if (rc != B200JPEG_OK)
-        return rc;
-    rc = b200jpegExecuteBatch(decoder, cuda_stream);
-    if (rc != B200JPEG_OK)
-        return rc;
-    return b200jpegFinishBatch(decoder, status, cuda_stream);
+    if (!decoder)
+        return B200JPEG_ERR_ARG;
+    try {
+        decoder->last_was_pipeline = true;
+        return decoder->pipe->decode(batch_size, data, lengths, outputs, status, static_cast<cudaStream_t>(cuda_stream));
+    } catch (...) {
+        return B200JPEG_ERR_STATE;
+    }
 }
 
 int b200jpegScanSegment(b200jpegDecoder_t decoder, const void* dev_raw, size_t length, uint32_t expected_restart_markers, void* dev_out_words,
@@ -153,7 +160,16 @@ int b200jpegScanSegment(b200jpegDecoder_t decoder, const void* dev_raw, size_t l
     }
 }
 
-int64_t b200jpegGetStat(b200jpegDecoder_t decoder, int which) { return decoder ? decoder->impl->stat(which) : -1; }
+int64_t b200jpegGetStat(b200jpegDecoder_t decoder, int which)
+{
+    if (!decoder)
+        return -1;
+    if (decoder->last_was_pipeline && which == B200JPEG_STAT_KERNEL_LAUNCHES)
+        return decoder->pipe->last_launches();
+    if (decoder->last_was_pipeline && which == B200JPEG_STAT_RESYNC_IMAGES)
+        return decoder->pipe->last_resync();
+    return decoder->impl->stat(which);
+}
 
 int b200jpegSetProfiling(b200jpegDecoder_t decoder, int enable)
 {
@@ -177,7 +193,12 @@ int b200jpegDebugCopyCoefficients(b200jpegDecoder_t decoder, int index, int16_t*
     return decoder->impl->copy_coefficients(index, host_out, capacity_elems);
 }
 
-const char* b200jpegGetLastError(b200jpegDecoder_t decoder) { return decoder ? decoder->impl->last_error() : g_err; }
+const char* b200jpegGetLastError(b200jpegDecoder_t decoder)
+{
+    if (!decoder)
+        return g_err;
+    return decoder->last_was_pipeline ? decoder->pipe->last_error() : decoder->impl->last_error();
+}
 
 const char* b200jpegVersion(void) { return "b200jpeg 0.1.0 (sm_100a)"; }
 

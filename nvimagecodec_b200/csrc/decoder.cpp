@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <thread>
 
 namespace b200jpeg {
 
@@ -377,6 +378,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     uint32_t* seq_img = reinterpret_cast<uint32_t*>(up + off_seq);
     uint32_t* idct_img = reinterpret_cast<uint32_t*>(up + off_idct);
     uint32_t* color_img = reinterpret_cast<uint32_t*>(up + off_color);
+    std::vector<uint8_t> direct(size_t(nd), 0); // source is pinned / registered host memory: copy without staging
+    size_t staged_bytes = 0;
     for (int d = 0; d < nd; ++d) {
         ImageDev& im = imgs_[d];
         if (host_outs_[d].host_ptr)
@@ -385,18 +388,53 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         std::fill(seq_img + im.seq_off, seq_img + im.seq_off + im.n_seq, uint32_t(d));
         std::fill(idct_img + im.idct_cta_off, idct_img + im.idct_cta_off + im.n_idct_cta, uint32_t(d));
         std::fill(color_img + im.color_cta_off, color_img + im.color_cta_off + im.n_color_cta_x * im.n_color_cta_y, uint32_t(d));
-        const int i = in_index_[d];
-        uint8_t* dst = up + off_raw + im.raw_off;
-        std::memcpy(dst, static_cast<const uint8_t*>(data[i]) + hdrs[d].scan_offset, im.raw_len);
-        std::memset(dst + im.raw_len, 0, align_up(im.raw_len, 16) + 16 - im.raw_len);
+        cudaPointerAttributes attr{};
+        if (cudaPointerGetAttributes(&attr, data[in_index_[d]]) == cudaSuccess && attr.type == cudaMemoryTypeHost)
+            direct[d] = 1;
+        else {
+            cudaGetLastError();
+            staged_bytes += im.raw_len;
+        }
+    }
+    if (staged_bytes) {
+        // pageable sources: copy into the pinned staging block, a few threads when it is worth it
+        auto stage = [&](int d0, int d1) {
+            for (int d = d0; d < d1; ++d) {
+                if (direct[d])
+                    continue;
+                const ImageDev& im = imgs_[d];
+                std::memcpy(up + off_raw + im.raw_off, static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[d].scan_offset, im.raw_len);
+            }
+        };
+        const int nthreads = staged_bytes > (size_t(8) << 20) ? std::min(4, std::max(1, int(std::thread::hardware_concurrency()) / 2)) : 1;
+        if (nthreads <= 1) {
+            stage(0, nd);
+        } else {
+            std::vector<std::thread> pool;
+            for (int t = 0; t < nthreads; ++t)
+                pool.emplace_back(stage, nd * t / nthreads, nd * (t + 1) / nthreads);
+            for (auto& th : pool)
+                th.join();
+        }
     }
     if (nd)
         std::memcpy(up + off_img, imgs_.data(), sizeof(ImageDev) * nd);
-    for (size_t s = 0; s < sets.size(); ++s)
-        std::memcpy(up + off_huff + s * sizeof(HuffSetDev), sets[s], sizeof(HuffSetDev));
+    for (size_t si = 0; si < sets.size(); ++si)
+        std::memcpy(up + off_huff + si * sizeof(HuffSetDev), sets[si], sizeof(HuffSetDev));
 
-    if (nd && !cuda_ok(cudaMemcpyAsync(upload_.ptr, up, upload_bytes, cudaMemcpyHostToDevice, stream), "upload"))
+    // one H2D for descriptors + maps + tables (+ the staged raw bytes), then one per directly copied image
+    const size_t first_copy = staged_bytes ? upload_bytes : off_raw;
+    if (nd && !cuda_ok(cudaMemcpyAsync(upload_.ptr, up, first_copy, cudaMemcpyHostToDevice, stream), "upload"))
         return B200JPEG_ERR_CUDA;
+    for (int d = 0; d < nd; ++d) {
+        if (!direct[d])
+            continue;
+        const ImageDev& im = imgs_[d];
+        if (!cuda_ok(cudaMemcpyAsync(upload_.as<uint8_t>() + off_raw + im.raw_off,
+                         static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[d].scan_offset, im.raw_len, cudaMemcpyHostToDevice, stream),
+                "bitstream upload"))
+            return B200JPEG_ERR_CUDA;
+    }
 
     uint8_t* dv = upload_.as<uint8_t>();
     uint8_t* sc = scratch_.as<uint8_t>();
@@ -464,17 +502,41 @@ int Decoder::execute(cudaStream_t stream)
     return B200JPEG_OK;
 }
 
-int Decoder::finish(int* status, cudaStream_t stream)
+// Finish, part 1 (asynchronous): queue the state read-back and the copies of host outputs.
+int Decoder::finish_async(cudaStream_t stream)
 {
     if (!executed_)
         return fail(B200JPEG_ERR_STATE, "finish without an executed batch");
     if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
         return B200JPEG_ERR_CUDA;
     const int nd = bd_.n_images;
+    if (nd && !cuda_ok(cudaMemcpyAsync(state_host_.ptr, bd_.state, sizeof(ImageState) * nd, cudaMemcpyDeviceToHost, stream), "state read-back"))
+        return B200JPEG_ERR_CUDA;
+    for (int d = 0; d < nd; ++d) {
+        const HostOut& ho = host_outs_[d];
+        if (ho.host_ptr &&
+            !cuda_ok(cudaMemcpyAsync(ho.host_ptr, bounce_.as<uint8_t>() + ho.bounce_off, ho.bytes, cudaMemcpyDeviceToHost, stream), "output copy"))
+            return B200JPEG_ERR_CUDA;
+    }
+    finish_queued_ = true;
+    return B200JPEG_OK;
+}
+
+// Finish, part 2: wait, run the rare re-synchronisation path, report statuses.
+int Decoder::finish_wait(int* status, cudaStream_t stream)
+{
+    if (!finish_queued_)
+        return fail(B200JPEG_ERR_STATE, "finish_wait without finish_async");
+    finish_queued_ = false;
+    if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
+        return B200JPEG_ERR_CUDA;
+    const int nd = bd_.n_images;
     resync_images_ = 0;
+    if (!cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
+        return B200JPEG_ERR_CUDA;
+    if (nd)
+        std::memcpy(states_.data(), state_host_.ptr, sizeof(ImageState) * nd);
     auto read_states = [&]() -> bool {
-        if (nd == 0)
-            return true;
         if (!cuda_ok(cudaMemcpyAsync(state_host_.ptr, bd_.state, sizeof(ImageState) * nd, cudaMemcpyDeviceToHost, stream), "state read-back"))
             return false;
         if (!cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
@@ -482,18 +544,17 @@ int Decoder::finish(int* status, cudaStream_t stream)
         std::memcpy(states_.data(), state_host_.ptr, sizeof(ImageState) * nd);
         return true;
     };
-    if (!read_states())
-        return B200JPEG_ERR_CUDA;
     auto count_dirty = [&]() {
         int c = 0;
-        for (const auto& s : states_)
-            c += (s.flags & kFlagDirty) ? 1 : 0;
+        for (const auto& st : states_)
+            c += (st.flags & kFlagDirty) ? 1 : 0;
         return c;
     };
     int dirty = count_dirty();
     if (dirty) {
         // Rare path: some sequence of some image did not enter with the state its predecessor left.
-        // Propagate corrected entry states one sequence per round until K2 finds every image consistent.
+        // Propagate corrected entry states one sequence per round until K2 finds every image consistent,
+        // then produce coefficients and pixels of those images again.
         resync_images_ = dirty;
         int rounds = 0;
         while (dirty && rounds < opt_.max_fix_rounds) {
@@ -509,19 +570,18 @@ int Decoder::finish(int* status, cudaStream_t stream)
         launches_ += launch_color(bd_, true, stream);
         if (!read_states())
             return B200JPEG_ERR_CUDA;
-    }
-    // host outputs: one D2H per image out of the bounce arena
-    bool any_host = false;
-    for (int d = 0; d < nd; ++d) {
-        const HostOut& ho = host_outs_[d];
-        if (!ho.host_ptr)
-            continue;
-        any_host = true;
-        if (!cuda_ok(cudaMemcpyAsync(ho.host_ptr, bounce_.as<uint8_t>() + ho.bounce_off, ho.bytes, cudaMemcpyDeviceToHost, stream), "output copy"))
+        bool any_host = false;
+        for (int d = 0; d < nd; ++d) {
+            const HostOut& ho = host_outs_[d];
+            if (!ho.host_ptr || !(states_[d].flags & kFlagRedo))
+                continue;
+            any_host = true;
+            if (!cuda_ok(cudaMemcpyAsync(ho.host_ptr, bounce_.as<uint8_t>() + ho.bounce_off, ho.bytes, cudaMemcpyDeviceToHost, stream), "output copy"))
+                return B200JPEG_ERR_CUDA;
+        }
+        if (any_host && !cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
             return B200JPEG_ERR_CUDA;
     }
-    if (any_host && !cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
-        return B200JPEG_ERR_CUDA;
     if (status) {
         for (int i = 0; i < n_in_; ++i) {
             int st = host_status_[i];
@@ -537,6 +597,12 @@ int Decoder::finish(int* status, cudaStream_t stream)
         }
     }
     return B200JPEG_OK;
+}
+
+int Decoder::finish(int* status, cudaStream_t stream)
+{
+    const int rc = finish_async(stream);
+    return rc == B200JPEG_OK ? finish_wait(status, stream) : rc;
 }
 
 int64_t Decoder::stat(int which) const
@@ -633,6 +699,115 @@ int Decoder::scan_segment(const void* dev_raw, size_t length, uint32_t expected_
     if (!cuda_ok(cudaGetLastError(), "kernel launch"))
         return B200JPEG_ERR_CUDA;
     return B200JPEG_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Pipeline: the batch is cut into chunks that rotate over a few lanes (decoder + stream each), so
+// that the host marker walk / staging of chunk i+1, the H2D of its bitstreams, the kernels of chunk
+// i and the D2H of chunk i-1 overlap.  Chunk results are identical to an unchunked decode: images
+// are independent.
+// ------------------------------------------------------------------------------------------------
+Pipeline::Pipeline(int device_id, const Options& opt, int n_lanes)
+    : device_(device_id)
+    , opt_(opt)
+{
+    lanes_.resize(size_t(std::max(1, n_lanes)));
+    for (auto& l : lanes_)
+        l.dec = std::make_unique<Decoder>(device_id, opt);
+}
+
+Pipeline::~Pipeline()
+{
+    cudaSetDevice(device_);
+    for (auto& l : lanes_) {
+        if (l.stream)
+            cudaStreamDestroy(l.stream);
+    }
+    if (user_event_)
+        cudaEventDestroy(user_event_);
+}
+
+int Pipeline::decode(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, int* status, cudaStream_t user_stream)
+{
+    if (n < 0 || (n > 0 && (!data || !len || !outs)))
+        return B200JPEG_ERR_ARG;
+    if (cudaSetDevice(device_) != cudaSuccess)
+        return B200JPEG_ERR_CUDA;
+    last_launches_ = 0;
+    last_resync_ = 0;
+    // chunk boundaries: about 24 MB of bitstream or 64 images, whichever comes first; small batches stay whole
+    std::vector<int> cuts{0};
+    {
+        size_t acc = 0;
+        int cnt = 0;
+        size_t total = 0;
+        for (int i = 0; i < n; ++i)
+            total += len[i];
+        const bool split = lanes_.size() > 1 && (total > (size_t(32) << 20) || n > 128);
+        for (int i = 0; i < n; ++i) {
+            acc += len[i];
+            ++cnt;
+            if (split && (acc >= (size_t(24) << 20) || cnt >= 64) && i + 1 < n) {
+                cuts.push_back(i + 1);
+                acc = 0;
+                cnt = 0;
+            }
+        }
+        cuts.push_back(n);
+    }
+    const int n_chunks = int(cuts.size()) - 1;
+    if (n_chunks > 1 || lanes_[0].stream) {
+        // lanes run on their own streams, ordered after whatever the caller already queued
+        if (!user_event_ && cudaEventCreateWithFlags(&user_event_, cudaEventDisableTiming) != cudaSuccess)
+            return B200JPEG_ERR_CUDA;
+        cudaEventRecord(user_event_, user_stream);
+    }
+    int rc_all = B200JPEG_OK;
+    auto drain = [&](Lane& l) {
+        if (!l.busy)
+            return;
+        const int rc = l.dec->finish_wait(status ? status + l.first : nullptr, l.active_stream);
+        if (rc != B200JPEG_OK && rc_all == B200JPEG_OK) {
+            rc_all = rc;
+            err_ = l.dec->last_error();
+        }
+        last_launches_ += l.dec->stat(B200JPEG_STAT_KERNEL_LAUNCHES);
+        last_resync_ += l.dec->stat(B200JPEG_STAT_RESYNC_IMAGES);
+        l.busy = false;
+    };
+    for (int c = 0; c < n_chunks; ++c) {
+        Lane& l = lanes_[size_t(c) % lanes_.size()];
+        drain(l);
+        const int first = cuts[c], cnt = cuts[c + 1] - cuts[c];
+        cudaStream_t s = user_stream;
+        if (n_chunks > 1) {
+            if (!l.stream && cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking) != cudaSuccess)
+                return B200JPEG_ERR_CUDA;
+            s = l.stream;
+            cudaStreamWaitEvent(s, user_event_, 0);
+        }
+        int rc = l.dec->prepare(cnt, data + first, len + first, outs + first, s);
+        if (rc == B200JPEG_OK)
+            rc = l.dec->execute(s);
+        if (rc == B200JPEG_OK)
+            rc = l.dec->finish_async(s);
+        if (rc != B200JPEG_OK) {
+            if (rc_all == B200JPEG_OK) {
+                rc_all = rc;
+                err_ = l.dec->last_error();
+            }
+            if (status)
+                for (int i = 0; i < cnt; ++i)
+                    status[first + i] = rc;
+            continue;
+        }
+        l.first = first;
+        l.active_stream = s;
+        l.busy = true;
+    }
+    for (auto& l : lanes_)
+        drain(l);
+    return rc_all;
 }
 
 } // namespace b200jpeg

@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <memory>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -50,6 +51,8 @@ class Decoder {
     int prepare(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, cudaStream_t stream);
     int execute(cudaStream_t stream);
     int finish(int* status, cudaStream_t stream);
+    int finish_async(cudaStream_t stream);          // queue read-backs / host-output copies
+    int finish_wait(int* status, cudaStream_t stream); // wait, fix-up path, statuses
 
     int64_t stat(int which) const;
     void set_profiling(bool on) { profiling_ = on; }
@@ -81,7 +84,7 @@ class Decoder {
         size_t bounce_off, bytes;
     };
     std::vector<HostOut> host_outs_;    // per device image; host_ptr == nullptr if output is a device buffer
-    bool prepared_ = false, executed_ = false;
+    bool prepared_ = false, executed_ = false, finish_queued_ = false;
 
     // device memory
     DeviceBuffer upload_, scratch_, cmp_, coef_, planes_, bounce_, scan_scratch_;
@@ -103,6 +106,34 @@ class Decoder {
     cudaEvent_t ev_[kStages + 1] = {};
     bool ev_valid_ = false;
     bool ev_recorded_ = false;
+};
+
+// Chunked, overlapped decode of a whole batch (what b200jpegDecodeBatch and the extension's decodeBatch use).
+class Pipeline {
+  public:
+    Pipeline(int device_id, const Options& opt, int n_lanes = 3);
+    ~Pipeline();
+    int decode(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, int* status, cudaStream_t user_stream);
+    Decoder& lane0() { return *lanes_[0].dec; } // Prepare / Execute / Finish and the kernel-level entry points use this one
+    int64_t last_launches() const { return last_launches_; }
+    int64_t last_resync() const { return last_resync_; }
+    const char* last_error() const { return err_.c_str(); }
+    int device() const { return device_; }
+
+  private:
+    struct Lane {
+        std::unique_ptr<Decoder> dec;
+        cudaStream_t stream = nullptr;
+        cudaStream_t active_stream = nullptr;
+        int first = 0;
+        bool busy = false;
+    };
+    int device_;
+    Options opt_;
+    std::vector<Lane> lanes_;
+    cudaEvent_t user_event_ = nullptr;
+    int64_t last_launches_ = 0, last_resync_ = 0;
+    std::string err_;
 };
 
 } // namespace b200jpeg

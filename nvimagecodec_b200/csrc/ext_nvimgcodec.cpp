@@ -223,7 +223,7 @@ class DecoderImpl {
     {
         if (n <= 0)
             return NVIMGCODEC_STATUS_SUCCESS;
-        b200jpeg::Decoder* core = core_for(thread_idx);
+        b200jpeg::Pipeline* core = core_for(thread_idx);
         if (!core) {
             for (int i = 0; i < n; ++i)
                 images[i]->imageReady(images[i]->instance, NVIMGCODEC_PROCESSING_STATUS_FAIL);
@@ -259,11 +259,7 @@ class DecoderImpl {
                 len[i] = streams[i].size;
             }
         }
-        int rc = core->prepare(n, data.data(), len.data(), outs.data(), stream);
-        if (rc == B200JPEG_OK)
-            rc = core->execute(stream);
-        if (rc == B200JPEG_OK)
-            rc = core->finish(status.data(), stream);
+        const int rc = core->decode(n, data.data(), len.data(), outs.data(), status.data(), stream);
         if (rc != B200JPEG_OK)
             log_msg(fw_, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_ERROR, std::string("b200 jpeg batch decode failed: ") + core->last_error());
         for (int i = 0; i < n; ++i) {
@@ -276,14 +272,14 @@ class DecoderImpl {
     }
 
   private:
-    b200jpeg::Decoder* core_for(int thread_idx)
+    b200jpeg::Pipeline* core_for(int thread_idx)
     {
         std::lock_guard<std::mutex> lock(mu_);
         size_t slot = thread_idx < 0 ? cores_.size() - 1 : size_t(thread_idx);
         if (slot >= cores_.size())
             cores_.resize(slot + 1);
         if (!cores_[slot])
-            cores_[slot] = std::make_unique<b200jpeg::Decoder>(ep_->device_id, opt_);
+            cores_[slot] = std::make_unique<b200jpeg::Pipeline>(ep_->device_id, opt_, slot == 0 ? 3 : 1);
         return cores_[slot].get();
     }
 
@@ -291,7 +287,7 @@ class DecoderImpl {
     const nvimgcodecExecutionParams_t* ep_;
     b200jpeg::Options opt_;
     std::mutex mu_;
-    std::vector<std::unique_ptr<b200jpeg::Decoder>> cores_;
+    std::vector<std::unique_ptr<b200jpeg::Pipeline>> cores_;
 };
 
 // ---- C trampolines of nvimgcodecDecoderDesc_t (never let an exception cross the ABI)
