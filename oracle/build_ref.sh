@@ -54,6 +54,6 @@ OBJS=$(ls "$OBJ"/*.o)
 g++ -shared -o "$OUT/libnvimgcodec.so" $OBJS -L"$CUDA/lib64" -L"$CUDA/lib64/stubs" -lcudart_static -lcuda -ldl -lpthread -lrt
 if [ -f "$HERE/../tests/host/host_driver.cpp" ]; then
   g++ -std=c++17 -O2 -I"$GEN" -I"$REF/include" -I"$CUDA/include" "$HERE/../tests/host/host_driver.cpp" -o "$OUT/host_driver" \
-      -L"$OUT" -lnvimgcodec -Wl,-rpath,'$ORIGIN' -L"$CUDA/lib64" -lcudart_static -ldl -lpthread -lrt
+      -L"$OUT" -lnvimgcodec -Wl,-rpath,'$ORIGIN' -Wl,--allow-shlib-undefined -L"$CUDA/lib64" -lcudart_static -ldl -lpthread -lrt
 fi
 echo "built $(ls "$OUT" | grep -v -E '^(obj|gen|ref.mk)$' | tr '\n' ' ')"

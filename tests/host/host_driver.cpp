@@ -1,0 +1,180 @@
+// host_driver -- drives the UNMODIFIED nvImageCodec core (built by oracle/build_ref.sh from the
+// reference sources) through its public C API, with our extension discovered from a directory,
+// exactly as nvimgcodec.Decoder / nvimtrans would (include/nvimgcodec.h:1733, 1973, 2030).
+// Test infrastructure: reads a manifest, decodes the whole list as ONE batch, dumps raw pixels.
+//
+//   host_driver <extension dir> <manifest> <out dir> [decoder options]
+//   manifest line: <jpeg path> <I_RGB|I_BGR|P_RGB|P_BGR|I_Y> <y0> <x0> <y1> <x1> <device|host>
+//                  (all-zero ROI = whole image)
+#include <cuda_runtime_api.h>
+#include <nvimgcodec.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <vector>
+
+#define CHECK(x)                                                                  \
+    do {                                                                          \
+        auto _s = (x);                                                            \
+        if (_s != NVIMGCODEC_STATUS_SUCCESS) {                                    \
+            std::fprintf(stderr, "%s failed: %d (line %d)\n", #x, int(_s), __LINE__); \
+            return 2;                                                             \
+        }                                                                         \
+    } while (0)
+
+struct Item {
+    std::string path, fmt, where;
+    int y0, x0, y1, x1;
+    std::vector<unsigned char> bytes;
+    void* buffer = nullptr;
+    size_t out_bytes = 0;
+    int w = 0, h = 0;
+};
+
+int main(int argc, char** argv)
+{
+    if (argc < 4) {
+        std::fprintf(stderr, "usage: host_driver <ext dir> <manifest> <out dir> [options]\n");
+        return 1;
+    }
+    const std::string ext_dir = argv[1], manifest = argv[2], out_dir = argv[3];
+    const char* options = argc > 4 ? argv[4] : "";
+    std::vector<Item> items;
+    {
+        std::ifstream f(manifest);
+        std::string line;
+        while (std::getline(f, line)) {
+            if (line.empty())
+                continue;
+            std::istringstream ss(line);
+            Item it;
+            ss >> it.path >> it.fmt >> it.y0 >> it.x0 >> it.y1 >> it.x1 >> it.where;
+            std::ifstream j(it.path, std::ios::binary);
+            it.bytes.assign(std::istreambuf_iterator<char>(j), std::istreambuf_iterator<char>());
+            items.push_back(std::move(it));
+        }
+    }
+    const int n = int(items.size());
+
+    nvimgcodecInstance_t instance = nullptr;
+    nvimgcodecInstanceCreateInfo_t ci{NVIMGCODEC_STRUCTURE_TYPE_INSTANCE_CREATE_INFO, sizeof(nvimgcodecInstanceCreateInfo_t), nullptr};
+    ci.load_builtin_modules = 1;
+    ci.load_extension_modules = 1;
+    ci.extension_modules_path = ext_dir.c_str();
+    ci.create_debug_messenger = 1;
+    ci.message_severity = NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_INFO | NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_WARNING |
+                          NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_ERROR | NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_FATAL;
+    ci.message_category = NVIMGCODEC_DEBUG_MESSAGE_CATEGORY_ALL;
+    CHECK(nvimgcodecInstanceCreate(&instance, &ci));
+
+    nvimgcodecExecutionParams_t ep{NVIMGCODEC_STRUCTURE_TYPE_EXECUTION_PARAMS, sizeof(nvimgcodecExecutionParams_t), nullptr};
+    ep.device_id = 0;
+    ep.max_num_cpu_threads = 4;
+    nvimgcodecDecoder_t decoder = nullptr;
+    CHECK(nvimgcodecDecoderCreate(instance, &decoder, &ep, options));
+
+    cudaStream_t stream;
+    cudaStreamCreate(&stream);
+    std::vector<nvimgcodecCodeStream_t> parents(n, nullptr), streams(n, nullptr);
+    std::vector<nvimgcodecImage_t> images(n, nullptr);
+    for (int i = 0; i < n; ++i) {
+        Item& it = items[i];
+        CHECK(nvimgcodecCodeStreamCreateFromHostMem(instance, &parents[i], it.bytes.data(), it.bytes.size(), nullptr));
+        nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
+        CHECK(nvimgcodecCodeStreamGetImageInfo(parents[i], &info));
+        it.w = int(info.plane_info[0].width);
+        it.h = int(info.plane_info[0].height);
+        streams[i] = parents[i];
+        const bool roi = it.y1 > it.y0 && it.x1 > it.x0;
+        if (roi) {
+            nvimgcodecCodeStreamView_t view{NVIMGCODEC_STRUCTURE_TYPE_CODE_STREAM_VIEW, sizeof(nvimgcodecCodeStreamView_t), nullptr};
+            view.image_idx = 0;
+            view.region.struct_type = NVIMGCODEC_STRUCTURE_TYPE_REGION;
+            view.region.struct_size = sizeof(nvimgcodecRegion_t);
+            view.region.ndim = 2;
+            view.region.start[0] = it.y0;
+            view.region.start[1] = it.x0;
+            view.region.end[0] = it.y1;
+            view.region.end[1] = it.x1;
+            CHECK(nvimgcodecCodeStreamGetSubCodeStream(parents[i], &streams[i], &view));
+            it.w = it.x1 - it.x0;
+            it.h = it.y1 - it.y0;
+        }
+        const bool planar = it.fmt == "P_RGB" || it.fmt == "P_BGR";
+        const bool gray = it.fmt == "I_Y";
+        info.sample_format = it.fmt == "I_RGB" ? NVIMGCODEC_SAMPLEFORMAT_I_RGB
+                             : it.fmt == "I_BGR" ? NVIMGCODEC_SAMPLEFORMAT_I_BGR
+                             : it.fmt == "P_RGB" ? NVIMGCODEC_SAMPLEFORMAT_P_RGB
+                             : it.fmt == "P_BGR" ? NVIMGCODEC_SAMPLEFORMAT_P_BGR
+                                                 : NVIMGCODEC_SAMPLEFORMAT_I_Y;
+        info.color_spec = gray ? NVIMGCODEC_COLORSPEC_GRAY : NVIMGCODEC_COLORSPEC_SRGB;
+        info.chroma_subsampling = NVIMGCODEC_SAMPLING_NONE;
+        info.num_planes = planar ? 3 : 1;
+        const int channels = planar || gray ? 1 : 3;
+        it.out_bytes = 0;
+        for (uint32_t p = 0; p < info.num_planes; ++p) {
+            info.plane_info[p].struct_type = NVIMGCODEC_STRUCTURE_TYPE_IMAGE_PLANE_INFO;
+            info.plane_info[p].struct_size = sizeof(nvimgcodecImagePlaneInfo_t);
+            info.plane_info[p].width = uint32_t(it.w);
+            info.plane_info[p].height = uint32_t(it.h);
+            info.plane_info[p].num_channels = uint32_t(channels);
+            info.plane_info[p].row_stride = size_t(it.w) * channels;
+            info.plane_info[p].sample_type = NVIMGCODEC_SAMPLE_DATA_TYPE_UINT8;
+            info.plane_info[p].precision = 8;
+            it.out_bytes += size_t(it.w) * channels * it.h;
+        }
+        if (it.where == "host") {
+            it.buffer = std::malloc(it.out_bytes);
+            info.buffer_kind = NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_HOST;
+        } else {
+            cudaMalloc(&it.buffer, it.out_bytes);
+            info.buffer_kind = NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_DEVICE;
+        }
+        info.buffer = it.buffer;
+        info.cuda_stream = stream;
+        CHECK(nvimgcodecImageCreate(instance, &images[i], &info));
+    }
+
+    nvimgcodecDecodeParams_t dp{NVIMGCODEC_STRUCTURE_TYPE_DECODE_PARAMS, sizeof(nvimgcodecDecodeParams_t), nullptr};
+    dp.apply_exif_orientation = 0;
+    nvimgcodecFuture_t future = nullptr;
+    CHECK(nvimgcodecDecoderDecode(decoder, streams.data(), images.data(), n, &dp, &future));
+    CHECK(nvimgcodecFutureWaitForAll(future));
+    std::vector<nvimgcodecProcessingStatus_t> st(n, NVIMGCODEC_PROCESSING_STATUS_UNKNOWN);
+    size_t st_n = 0;
+    CHECK(nvimgcodecFutureGetProcessingStatus(future, st.data(), &st_n));
+    cudaStreamSynchronize(stream);
+    cudaDeviceSynchronize();
+
+    std::ofstream sf(out_dir + "/status.txt");
+    for (int i = 0; i < n; ++i) {
+        Item& it = items[i];
+        sf << int(st[i]) << " " << it.w << " " << it.h << "\n";
+        std::vector<unsigned char> host(it.out_bytes);
+        if (it.where == "host")
+            std::memcpy(host.data(), it.buffer, it.out_bytes);
+        else
+            cudaMemcpy(host.data(), it.buffer, it.out_bytes, cudaMemcpyDeviceToHost);
+        std::ofstream o(out_dir + "/" + std::to_string(i) + ".raw", std::ios::binary);
+        o.write(reinterpret_cast<const char*>(host.data()), std::streamsize(host.size()));
+    }
+    nvimgcodecFutureDestroy(future);
+    for (int i = 0; i < n; ++i) {
+        nvimgcodecImageDestroy(images[i]);
+        if (streams[i] != parents[i])
+            nvimgcodecCodeStreamDestroy(streams[i]);
+        nvimgcodecCodeStreamDestroy(parents[i]);
+        if (items[i].where == "host")
+            std::free(items[i].buffer);
+        else
+            cudaFree(items[i].buffer);
+    }
+    nvimgcodecDecoderDestroy(decoder);
+    nvimgcodecInstanceDestroy(instance);
+    std::printf("decoded %d images through nvimgcodecDecoderDecode\n", n);
+    return 0;
+}
