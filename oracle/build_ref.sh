@@ -7,6 +7,9 @@
 #   oracle/_ref/libnvimgcodec.so   the unmodified nvImageCodec core (src/*.cpp, src/parsers, src/imgproc)
 #                                  -- the host framework that loads our extension in tests/
 #   oracle/_ref/host_driver        tests/host/host_driver.cpp linked against it (our own file)
+#   oracle/_ref/libref_turbo.so    the reference's CPU JPEG glue (extensions/libjpeg_turbo/jpeg_mem.cpp, jpeg_handle.cpp)
+#                                  + oracle/ref_turbo_shim.cpp, compiled against the reconstructed libjpeg62 ABI header
+#                                  (oracle/turbo_abi/) and linked to the libjpeg-turbo binary bundled with Pillow
 set -euo pipefail
 HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
 REF="${REFERENCE_ROOT:-/root/reference}"
@@ -50,10 +53,32 @@ SRCS="nvimgcodec_capi plugin_framework codec_registry codec image_decoder image_
 } > "$OUT/ref.mk"
 make -s -j"$JOBS" -f "$OUT/ref.mk"
 
-OBJS=$(ls "$OBJ"/*.o)
+OBJS=$(ls "$OBJ"/*.o)   # (the turbo glue objects use the .to suffix so they stay out of libnvimgcodec.so)
 g++ -shared -o "$OUT/libnvimgcodec.so" $OBJS -L"$CUDA/lib64" -L"$CUDA/lib64/stubs" -lcudart_static -lcuda -ldl -lpthread -lrt
 if [ -f "$HERE/../tests/host/host_driver.cpp" ]; then
   g++ -std=c++17 -O2 -I"$GEN" -I"$REF/include" -I"$CUDA/include" "$HERE/../tests/host/host_driver.cpp" -o "$OUT/host_driver" \
       -L"$OUT" -lnvimgcodec -Wl,-rpath,'$ORIGIN' -Wl,--allow-shlib-undefined -L"$CUDA/lib64" -lcudart_static -ldl -lpthread -lrt
+fi
+# ---- the reference's own CPU JPEG path over the libjpeg-turbo binary that ships with Pillow
+TURBO_SO="$(python - <<'PY'
+import glob, os, sys
+try:
+    import PIL
+    c = sorted(glob.glob(os.path.join(os.path.dirname(PIL.__file__), "..", "pillow.libs", "libjpeg-*.so.62*")))
+    print(os.path.realpath(c[0]) if c else "")
+except Exception:
+    print("")
+PY
+)"
+if [ -n "$TURBO_SO" ] && [ -f "$HERE/ref_turbo_shim.cpp" ]; then
+  TINC="-I$HERE/turbo_abi $INC -I$REF/extensions/libjpeg_turbo"
+  g++ $CXXFLAGS -fvisibility=hidden $TINC -c "$REF/extensions/libjpeg_turbo/jpeg_mem.cpp" -o "$OBJ/turbo_jpeg_mem.to"
+  g++ $CXXFLAGS -fvisibility=hidden $TINC -c "$REF/extensions/libjpeg_turbo/jpeg_handle.cpp" -o "$OBJ/turbo_jpeg_handle.to"
+  g++ $CXXFLAGS -fvisibility=hidden $TINC -c "$HERE/ref_turbo_shim.cpp" -o "$OBJ/turbo_shim.to"
+  g++ -shared -o "$OUT/libref_turbo.so" "$OBJ/turbo_jpeg_mem.to" "$OBJ/turbo_jpeg_handle.to" "$OBJ/turbo_shim.to" "$TURBO_SO" \
+      -Wl,-rpath,"$(dirname "$TURBO_SO")" -lpthread
+  echo "$TURBO_SO" > "$OUT/libref_turbo.engine"
+else
+  echo "Pillow's libjpeg-turbo not found: libref_turbo.so not built" >&2
 fi
 echo "built $(ls "$OUT" | grep -v -E '^(obj|gen|ref.mk)$' | tr '\n' ' ')"

@@ -23,6 +23,7 @@ from PIL import Image
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 from nvimagecodec_b200 import corpus  # noqa: E402
+from oracle import turbo  # noqa: E402  (the reference's own jpeg_mem.cpp over Pillow's libjpeg-turbo; oracle/build_ref.sh)
 
 REF = "/root/reference/resources/ref/jpeg"
 
@@ -57,8 +58,15 @@ def main():
         gray = turbo_gray(data)
         with open(os.path.join(HERE, "jpeg", name + ".jpg"), "wb") as f:
             f.write(data)
+        # the reference's libjpeg_turbo::Uncompress, both upsampling modes (fancy must equal Pillow/OpenCV)
+        ref_fancy = turbo.decode(data, "I_RGB", fancy=True)
+        assert np.array_equal(ref_fancy, rgb), "reference glue disagrees with Pillow"
+        ref_box = turbo.decode(data, "I_RGB", fancy=False)
+        h_, w_ = rgb.shape[:2]
+        roi = (h_ // 3, w_ // 4, max(h_ // 3 + 1, h_ - h_ // 5), max(w_ // 4 + 1, w_ - w_ // 7))
+        ref_roi = turbo.decode(data, "I_RGB", fancy=False, roi=roi)
         e = dict(name=name, note=note, bytes=len(data), height=int(rgb.shape[0]), width=int(rgb.shape[1]),
-                 sha256_rgb_fancy=sha(rgb), sha256_y=sha(gray))
+                 sha256_rgb_fancy=sha(rgb), sha256_y=sha(gray), sha256_rgb_box=sha(ref_box), roi=list(roi), sha256_roi_box=sha(ref_roi))
         if rgb.size <= 6000:
             e["rgb_fancy"] = rgb.reshape(-1).tolist()
         entries.append(e)
@@ -85,7 +93,9 @@ def main():
         add("syn_%dx%d_gray" % (h, w), corpus.encode(img, 90, gray=True), "synthetic grayscale")
     with open(os.path.join(HERE, "golden.json"), "w") as f:
         json.dump(dict(generator="tests/golden/make_golden.py",
-                       engines="Pillow libjpeg-turbo 3.1.4.1 == OpenCV libjpeg-turbo 3.1.2 (ISLOW, fancy upsampling)",
+                       engines="Pillow libjpeg-turbo 3.1.4.1 == OpenCV libjpeg-turbo 3.1.2 (ISLOW, fancy upsampling); "
+                               "fancy_upsampling=0 and ROI vectors from the reference's libjpeg_turbo::Uncompress "
+                               "(extensions/libjpeg_turbo/jpeg_mem.cpp) over the same Pillow binary",
                        entries=entries), f, indent=0)
     print(len(entries), "fixtures,", sum(e["bytes"] for e in entries), "jpeg bytes")
 

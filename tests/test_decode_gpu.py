@@ -65,6 +65,21 @@ def test_golden_vectors_bit_exact(dec_fancy):
         assert _sha(o.cpu().numpy()) == e["sha256_y"], e["name"]
 
 
+def test_golden_vectors_box_upsampling_and_roi_bit_exact(dec_plain):
+    """fancy_upsampling=0 (the Python binding / nvimtrans default) and cropped decodes against the
+    vectors produced by the reference's own libjpeg_turbo::Uncompress."""
+    from nvimagecodec_b200 import _lib
+
+    entries, datas = _gold()
+    outs = dec_plain.decode(datas, "I_RGB")
+    assert dec_plain.last_status == [_lib.OK] * len(datas)
+    for e, o in zip(entries, outs):
+        assert _sha(o.cpu().numpy()) == e["sha256_rgb_box"], e["name"]
+    outs = dec_plain.decode(datas, "I_RGB", [tuple(e["roi"]) for e in entries])
+    for e, o in zip(entries, outs):
+        assert _sha(o.cpu().numpy()) == e["sha256_roi_box"], e["name"]
+
+
 @pytest.mark.parametrize("fmt", ["I_RGB", "I_BGR", "P_RGB", "P_BGR", "I_Y"])
 @pytest.mark.parametrize("fancy", [True, False])
 def test_formats_and_upsampling_modes_vs_oracle(decoder_cls, dec_fancy, dec_plain, fmt, fancy):

@@ -45,6 +45,9 @@ def test_oracle_matches_libjpeg_turbo_golden(e):
         assert np.array_equal(rgb.reshape(-1), np.asarray(e["rgb_fancy"], dtype=np.uint8))
     y = oracle.decode(data, oracle.FMT_Y, fancy=True)
     assert _sha(y) == e["sha256_y"]
+    # fancy_upsampling=0 and a cropped decode, as produced by the reference's own jpeg_mem.cpp
+    assert _sha(oracle.decode(data, oracle.FMT_I_RGB, fancy=False)) == e["sha256_rgb_box"]
+    assert _sha(oracle.decode(data, oracle.FMT_I_RGB, fancy=False, roi=tuple(e["roi"]))) == e["sha256_roi_box"]
 
 
 def test_formats_are_permutations_of_rgb():
@@ -103,3 +106,27 @@ def test_live_against_pillow_when_available():
         data = corpus.encode(corpus.synth(h, w, 900 + i), int(rng.integers(30, 100)), samp, int(rng.integers(0, 5)), bool(i & 1))
         ref = np.asarray(PIL.open(io.BytesIO(data)).convert("RGB"))
         assert np.array_equal(oracle.decode(data, oracle.FMT_I_RGB, fancy=True), ref)
+
+
+def test_live_against_reference_glue_when_built():
+    """oracle/_ref/libref_turbo.so = the reference's libjpeg_turbo::Uncompress compiled from its own
+    sources (oracle/build_ref.sh); it can switch fancy upsampling off and crop, which Pillow cannot."""
+    from oracle import turbo
+
+    if not turbo.available():
+        pytest.skip("oracle/_ref/libref_turbo.so not built")
+    pytest.importorskip("cv2")
+    from nvimagecodec_b200 import corpus
+
+    rng = np.random.default_rng(11)
+    for i in range(10):
+        h, w = int(rng.integers(9, 120)), int(rng.integers(9, 120))
+        samp = ["444", "422", "420", "440", "411"][i % 5]
+        data = corpus.encode(corpus.synth(h, w, 700 + i), int(rng.integers(30, 100)), samp, int(rng.integers(0, 5)), bool(i & 1))
+        y0, x0 = int(rng.integers(0, h - 1)), int(rng.integers(0, w - 1))
+        roi = (y0, x0, int(rng.integers(y0 + 1, h + 1)), int(rng.integers(x0 + 1, w + 1)))
+        for fancy in (True, False):
+            assert np.array_equal(oracle.decode(data, oracle.FMT_I_RGB, fancy), turbo.decode(data, "I_RGB", fancy))
+            assert np.array_equal(oracle.decode(data, oracle.FMT_I_BGR, fancy), turbo.decode(data, "I_BGR", fancy))
+            assert np.array_equal(oracle.decode(data, oracle.FMT_Y, fancy), turbo.decode(data, "I_Y", fancy))
+            assert np.array_equal(oracle.decode(data, oracle.FMT_I_RGB, fancy, roi), turbo.decode(data, "I_RGB", fancy, roi))
