@@ -170,7 +170,11 @@ enum {
     B200JPEG_STAT_OUTPUT_BYTES = 4,
     B200JPEG_STAT_RESYNC_IMAGES = 5,   /* images that needed the re-synchronisation path in the last Finish */
     B200JPEG_STAT_DEVICE_BYTES = 6,    /* device memory currently held */
-    B200JPEG_STAT_NUM_SUBSEQ = 7
+    B200JPEG_STAT_NUM_SUBSEQ = 7,
+    B200JPEG_STAT_SYNC_CTAS = 8,          /* K1 counters of the last Execute (lane 0): CTAs, */
+    B200JPEG_STAT_SYNC_REPAIR_ROUNDS = 9, /*   fixed-point rounds after the first full pass (summed over CTAs), */
+    B200JPEG_STAT_SYNC_REPAIRED = 10,     /*   subsequences re-decoded in those rounds, */
+    B200JPEG_STAT_SYNC_MAX_ROUNDS = 11    /*   most rounds any CTA needed */
 };
 B200JPEG_API int64_t b200jpegGetStat(b200jpegDecoder_t decoder, int which);
 

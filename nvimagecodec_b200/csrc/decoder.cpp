@@ -100,7 +100,11 @@ Options parse_options(const char* options, const char* decoder_id)
             o.fancy_upsampling = std::atoi(value.c_str()) != 0;
         else if (name == "debug_no_warm")
             o.debug_no_warm = std::atoi(value.c_str()) != 0;
-        else if (name == "max_fix_rounds")
+        else if (name == "subseq_bits") {
+            const int v = std::atoi(value.c_str());
+            if (v == 1024 || v == 2048 || v == 4096)
+                o.subseq_bits = v;
+        } else if (name == "max_fix_rounds")
             o.max_fix_rounds = std::atoi(value.c_str());
     }
     return o;
@@ -168,6 +172,23 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     std::vector<StreamHeader> hdrs;
     hdrs.reserve(n);
 
+    // Subsequence length for this batch: longer subsequences cost fewer re-synchronisation rounds
+    // (the block-in-MCU phase of a 4:2:0 stream needs a few MCUs to lock), shorter ones give more
+    // threads; pick the longest that still fills the GPU.
+    {
+        uint64_t total_bits = 0;
+        for (int i = 0; i < n; ++i)
+            total_bits += uint64_t(len[i]) * 8;
+        uint32_t sb = kMinSubseqBits;
+        if (opt_.subseq_bits)
+            sb = uint32_t(opt_.subseq_bits);
+        else if (total_bits / 4096 >= 400000)
+            sb = 4096;
+        else if (total_bits / 2048 >= 50000)
+            sb = 2048;
+        bd_.sub_bits = sb;
+    }
+    const size_t sub_bytes = bd_.sub_bits / 8;
     size_t raw_bytes = 0, cmp_bytes = 0, coef_elems = 0, plane_bytes = 0, bounce_bytes = 0;
     uint32_t n_tiles = 0, n_sub = 0, n_seq = 0, n_bnd = 0, n_idct = 0, n_color = 0;
     comp_bytes_ = n_coefs_ = out_bytes_ = 0;
@@ -213,7 +234,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.n_tiles = uint32_t((hd.scan_length + kScanTileBytes - 1) / kScanTileBytes);
         n_tiles += im.n_tiles;
         im.sub_off = n_sub;
-        im.n_sub_max = uint32_t((hd.scan_length + kSubseqBytes - 1) / kSubseqBytes);
+        im.n_sub_max = uint32_t((hd.scan_length + sub_bytes - 1) / sub_bytes);
         n_sub += im.n_sub_max;
         im.seq_off = n_seq;
         im.n_seq = (im.n_sub_max + kSeqStride - 1) / kSeqStride;
@@ -364,6 +385,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     so = align_up(so + 16ull * n_sub, 256);
     const size_t so_start = so;
     so = align_up(so + 16ull * n_sub, 256);
+    const size_t so_stats = so;
+    so += 256;
 
     coef_bytes_ = coef_elems * sizeof(int16_t);
     if (!upload_host_.ensure(upload_bytes) || !state_host_.ensure(sizeof(ImageState) * std::max(nd, 1)))
@@ -454,6 +477,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.sub_out = reinterpret_cast<uint32_t*>(sc + so_out);
     bd_.sub_info = reinterpret_cast<int4*>(sc + so_info);
     bd_.sub_start = reinterpret_cast<int4*>(sc + so_start);
+    bd_.sync_stats = reinterpret_cast<uint32_t*>(sc + so_stats);
     bd_.cmp = cmp_.as<uint32_t>();
     bd_.coef = coef_.as<int16_t>();
     bd_.planes = planes_.as<uint8_t>();
@@ -483,6 +507,7 @@ int Decoder::execute(cudaStream_t stream)
     ev_recorded_ = false;
     if (bd_.n_images == 0)
         return B200JPEG_OK;
+    cudaMemsetAsync(bd_.sync_stats, 0, 16, stream);
     mark(0, stream);
     launches_ += launch_scan(bd_, stream);
     mark(1, stream);
@@ -616,6 +641,15 @@ int64_t Decoder::stat(int which) const
     case B200JPEG_STAT_RESYNC_IMAGES: return resync_images_;
     case B200JPEG_STAT_DEVICE_BYTES: return int64_t(device_bytes_);
     case B200JPEG_STAT_NUM_SUBSEQ: return bd_.n_sub;
+    case B200JPEG_STAT_SYNC_CTAS:
+    case B200JPEG_STAT_SYNC_REPAIR_ROUNDS:
+    case B200JPEG_STAT_SYNC_REPAIRED:
+    case B200JPEG_STAT_SYNC_MAX_ROUNDS: {
+        uint32_t v[4] = {0, 0, 0, 0};
+        if (!bd_.sync_stats || cudaMemcpy(v, bd_.sync_stats, sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess)
+            return -1;
+        return v[which - B200JPEG_STAT_SYNC_CTAS];
+    }
     default: return -1;
     }
 }
@@ -695,6 +729,7 @@ int Decoder::scan_segment(const void* dev_raw, size_t length, uint32_t expected_
     b.cmp = static_cast<uint32_t*>(dev_words);
     b.bnd = dev_bnd;
     b.n_tiles = int(n_tiles);
+    b.sub_bits = kMinSubseqBits;
     launch_scan(b, stream);
     if (!cuda_ok(cudaGetLastError(), "kernel launch"))
         return B200JPEG_ERR_CUDA;

@@ -39,6 +39,7 @@ struct Options {
     bool fancy_upsampling = true; // libjpeg_turbo_ext default (libjpeg_turbo_decoder.cpp:223-249)
     bool debug_no_warm = false;   // test hook: forces the re-synchronisation path
     int max_fix_rounds = 1 << 20;
+    int subseq_bits = 0;          // 0 = choose per batch; else 1024 / 2048 / 4096
 };
 
 Options parse_options(const char* options, const char* decoder_id);

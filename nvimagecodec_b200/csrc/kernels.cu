@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(128) scan_prefix_kernel(BatchDev bd)
         st.cmp_len = carry_k;
         st.n_rst = carry_r;
         st.flags = (carry_r != im.n_rst_expected) ? kFlagBadMarker : 0u;
-        st.n_sub = st.flags ? 0u : (carry_k * 8u + kSubseqBits - 1u) / kSubseqBits;
+        st.n_sub = st.flags ? 0u : (carry_k * 8u + bd.sub_bits - 1u) / bd.sub_bits;
         bd.state[img] = st;
         const uint32_t slot = carry_r < im.n_bnd_cap ? carry_r : im.n_bnd_cap - 1;
         bd.bnd[im.bnd_off + slot] = carry_k; // end of stream closes the last restart interval
@@ -249,7 +249,6 @@ __global__ void __launch_bounds__(kScanThreads) scan_scatter_kernel(BatchDev bd)
 //   [0,6)  bit offset of the first code word past the boundary   [6,12) zig-zag index z
 //   [12,16) block-in-MCU index b                                  bit 16: end of stream reached
 constexpr uint32_t kStateDone = 1u << 16;
-constexpr int kProbeBits = 256; // K1: how far before its subsequence a thread starts to guess its entry state
 
 struct DecodeResult {
     uint32_t state;     // exit state
@@ -476,7 +475,7 @@ __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageD
 
 // K1.  One CTA = kSeqStride consecutive subsequences of one image (+ kSeqWarm leading threads whose
 // only job is to make the CTA's entry state right with high probability).
-//   round 0  every thread decodes the last kProbeBits bits BEFORE its subsequence from the bare guess
+//   round 0  every thread decodes the last quarter subsequence BEFORE its own from the bare guess
 //            "a code word starts here, at a block start": JPEG Huffman streams self-synchronise
 //            within a few dozen symbols, so this usually lands on the true entry state;
 //   round 1  every thread decodes its subsequence from that entry state (exit state, block count, DC sums);
@@ -506,6 +505,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     SyncShared& sh = *reinterpret_cast<SyncShared*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev));
     const bool fix_mode = (mode & 1) != 0;
     const bool no_warm = (mode & 2) != 0; // test hook: bare guesses, no warm-up threads, no probe
+    const uint32_t S = bd.sub_bits;
     const uint32_t seq = blockIdx.x;
     const uint32_t img = bd.seq_img[seq];
     const ImageDev& im = bd.img[img];
@@ -548,14 +548,14 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
         uint32_t in = 0; // k == 0: the true start state; otherwise the bare guess
         if (active && k > 0 && !no_warm) {
             // round 0: probe the tail of the previous subsequence
-            const uint32_t pb = uint32_t(k) * kSubseqBits - kProbeBits;
-            decode_subsequence<false>(sv, s_hs, pb, uint32_t(k) * kSubseqBits, 0u, 0, 0, 0, 0, nullptr, res);
+            const uint32_t pb = uint32_t(k) * S - S / 4;
+            decode_subsequence<false>(sv, s_hs, pb, uint32_t(k) * S, 0u, 0, 0, 0, 0, nullptr, res);
             in = res.state;
         }
         // round 1: everybody
         res.state = kStateDone;
         if (active) {
-            decode_subsequence<false>(sv, s_hs, uint32_t(k) * kSubseqBits, uint32_t(k + 1) * kSubseqBits, in, 0, 0, 0, 0, nullptr, res);
+            decode_subsequence<false>(sv, s_hs, uint32_t(k) * S, uint32_t(k + 1) * S, in, 0, 0, 0, 0, nullptr, res);
             sh.info[t] = pack_info(res);
             sh.fresh[t] = 1;
         }
@@ -569,16 +569,19 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     }
     // fixed-point rounds over the compacted work list.  Invariant: in[t] == out[t-1] for every t,
     // and out[t] == decode(in[t]) for every t that is not queued.
+    uint32_t dbg_rounds = 0, dbg_items = 0;
     for (;;) {
         __syncthreads();
         const uint32_t n = sh.count;
         if (n == 0u)
             break;
+        ++dbg_rounds;
+        dbg_items += n;
         uint32_t item = 0;
         if (uint32_t(t) < n) {
             item = sh.queue[t];
             const uint32_t kk = uint32_t(k0 + int(item));
-            decode_subsequence<false>(sv, s_hs, kk * kSubseqBits, (kk + 1) * kSubseqBits, sh.in[item], 0, 0, 0, 0, nullptr, res);
+            decode_subsequence<false>(sv, s_hs, kk * S, (kk + 1) * S, sh.in[item], 0, 0, 0, 0, nullptr, res);
         }
         __syncthreads(); // everyone has read count and queue
         if (t == 0)
@@ -596,6 +599,12 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
                 sh.queue[atomicAdd(&sh.count, 1u)] = succ;
             }
         }
+    }
+    if (t == 0 && bd.sync_stats) { // [0] CTAs, [1] repair rounds, [2] repaired subsequences, [3] max rounds in one CTA
+        atomicAdd(bd.sync_stats + 0, 1u);
+        atomicAdd(bd.sync_stats + 1, dbg_rounds);
+        atomicAdd(bd.sync_stats + 2, dbg_items);
+        atomicMax(bd.sync_stats + 3, dbg_rounds);
     }
     // results of the real (non warm-up) subsequences
     if (active && t >= kSeqWarm && sh.fresh[t]) {
@@ -729,7 +738,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, in
     if (!(in & kStateDone) && (uint32_t(start.x) % im.bpm) != ((in >> 12) & 15u)) {
         err |= kFlagPhase;
     } else {
-        decode_subsequence<true>(sv, s_hs, k * kSubseqBits, (k + 1) * kSubseqBits, in, start.x, start.y, start.z, start.w,
+        decode_subsequence<true>(sv, s_hs, k * bd.sub_bits, (k + 1) * bd.sub_bits, in, start.x, start.y, start.z, start.w,
             bd.coef + im.coef_off, res);
         err |= res.err;
     }
@@ -1379,6 +1388,7 @@ extern "C" B200JPEG_API int b200jpegScanSegmentNoAlloc(const void* dev_raw, size
     b.cmp = static_cast<uint32_t*>(dev_out_words);
     b.bnd = dev_out_boundaries;
     b.n_tiles = int(p.n_tiles);
+    b.sub_bits = kMinSubseqBits;
     launch_scan(b, stream);
     if (cudaGetLastError() != cudaSuccess) {
         noalloc_message(message, message_capacity, "b200jpegScanSegmentNoAlloc: kernel launch failed");

@@ -12,8 +12,8 @@ namespace b200jpeg {
 // ---- entropy-stage geometry
 constexpr int kScanTileBytes = 4096;  // K0: bytes of byte-stuffed scan data per CTA
 constexpr int kScanThreads = 256;     // 16 B per thread
-constexpr int kSubseqBits = 1024;     // K1-K3: bits of unstuffed stream per thread ("subsequence")
-constexpr int kSubseqBytes = kSubseqBits / 8;
+constexpr int kMinSubseqBits = 1024;  // K1-K3: bits of unstuffed stream per thread ("subsequence"); the host picks
+constexpr int kMaxSubseqBits = 4096;  //   1024, 2048 or 4096 per batch (BatchDev::sub_bits) so the GPU stays filled
 constexpr int kSeqThreads = 256;      // threads per CTA ("sequence")
 constexpr int kSeqWarm = 8;           // leading threads that only warm up the entry state
 constexpr int kSeqStride = kSeqThreads - kSeqWarm;
@@ -69,7 +69,7 @@ struct ImageDev {
 struct ImageState {
     uint32_t cmp_len;  // unstuffed bytes
     uint32_t n_rst;    // RST markers found
-    uint32_t n_sub;    // ceil(cmp_len*8 / kSubseqBits)
+    uint32_t n_sub;    // ceil(cmp_len*8 / sub_bits)
     uint32_t flags;
 };
 
@@ -95,6 +95,8 @@ struct BatchDev {
     const uint32_t* idct_cta_img;
     const uint32_t* color_cta_img;
     int n_tiles, n_seq, n_sub, n_idct_cta, n_color_cta;
+    uint32_t* sync_stats;   // optional K1 counters (4 x uint32), may be null
+    uint32_t sub_bits;      // subsequence length in bits for this batch
 };
 
 // Kernel launchers (kernels.cu).  Each returns the number of kernels it launched.

@@ -199,6 +199,24 @@ def test_resync_path_and_no_rst_large_stream(decoder_cls):
         dec.close()
 
 
+@pytest.mark.parametrize("bits", [1024, 2048, 4096])
+def test_every_subsequence_length_is_bit_exact(decoder_cls, bits):
+    """The host picks 1024 / 2048 / 4096-bit subsequences per batch; force each, with and without the
+    warm-up / probe heuristics, on streams with and without restart markers."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    srcs = [corpus.encode(corpus.synth(700, 900, 31), 93, "420"), corpus.encode(corpus.synth(500, 640, 32), 96, "444"),
+            corpus.encode(corpus.synth(480, 360, 33), 80, "422", rst_interval=7), corpus.encode(corpus.synth(90, 90, 34), 90, gray=True)]
+    refs = [oracle.decode(d, oracle.FMT_I_RGB, True) for d in srcs]
+    for extra in ("", " b200_jpeg_decoder:debug_no_warm=1"):
+        dec = decoder_cls(0, options=f":fancy_upsampling=1 b200_jpeg_decoder:subseq_bits={bits}" + extra)
+        outs = dec.decode(srcs, "I_RGB")
+        assert dec.last_status == [_lib.OK] * len(srcs)
+        for o, r in zip(outs, refs):
+            assert np.array_equal(o.cpu().numpy(), r)
+        dec.close()
+
+
 def test_deterministic_and_reusable(dec_plain):
     """Sequential reuse of one decoder gives byte-identical results (the reference's
     concurrent_decode_test.cpp demands equality with a sequential decode)."""
