@@ -301,6 +301,12 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             if ((hx == 1 || hx == 2) && (vx == 1 || vx == 2)) {
                 im.color_mode = uint8_t(2 + (hx - 1) + 2 * (vx - 1));
                 im.color_unit_rows = uint8_t(vx);
+                // libjpeg's choice of the triangle filter (jdsample.c jinit_upsampler): h2v1 and h2v2 need
+                // downsampled_width > 2, h1v2 does not
+                const int dw = (hd.width * hd.h[1] + hd.hmax - 1) / hd.hmax;
+                const bool tri = opt_.fancy_upsampling && ((hx == 2 && dw > 2) || (hx == 1 && vx == 2));
+                if (tri && im.color_mode >= 3)
+                    im.color_mode = uint8_t(im.color_mode + 3); // 6: h2v1, 7: h1v2, 8: h2v2 with the triangle filter
             }
         }
         {

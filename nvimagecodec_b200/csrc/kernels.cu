@@ -303,9 +303,33 @@ struct BlockWriter {
 //   kWrite == true  (K3): the thread OWNS every block that starts inside its range: a block already
 //     under way at entry is skipped (its owner, the previous thread, finishes it), and the block
 //     under way at end_bit is decoded to its end.
+// Per-block-in-MCU constants, one 64-bit word per block index, built once per CTA in shared memory:
+//   .x = byte offset of the block's DC table inside the table set
+//   .y = byte offset of its AC table | component << 24 | next block index << 28
+struct BlockTable {
+    uint2 e[kMaxBlocksPerMcu];
+};
+__device__ __forceinline__ void build_block_table(BlockTable* bt, const ImageDev& im)
+{
+    if (threadIdx.x < im.bpm) {
+        const uint32_t b = threadIdx.x;
+        const uint32_t comp = (im.blk_comp >> (2 * b)) & 3u;
+        const uint32_t dc = ((im.blk_tab >> b) & 1u) * uint32_t(sizeof(HuffTableDev));
+        const uint32_t ac = (2u + ((im.blk_tab >> (16 + b)) & 1u)) * uint32_t(sizeof(HuffTableDev));
+        const uint32_t next = (b + 1u == im.bpm) ? 0u : b + 1u;
+        bt->e[b] = make_uint2(dc, ac | (comp << 24) | (next << 28));
+    }
+}
+
+// Decodes the code words that start in [start bit given by in_state, end_bit).
+//   kWrite == false (K1): only the decoder state, the block count and the DC sums are tracked.
+//   kWrite == true  (K3): the thread OWNS every block that starts inside its range: a block already
+//     under way at entry is skipped (its owner, the previous thread, finishes it), and the block
+//     under way at end_bit is decoded to its end.
 template <bool kWrite>
-__device__ __forceinline__ void decode_subsequence(const StreamView& sv, const HuffSetDev* __restrict__ hs, uint32_t base_bit, uint32_t end_bit,
-    uint32_t in_state, int32_t blk, int32_t dc0, int32_t dc1, int32_t dc2, int16_t* __restrict__ coef, DecodeResult& out)
+__device__ __forceinline__ void decode_subsequence(const StreamView& sv, const HuffSetDev* __restrict__ hs, const BlockTable* __restrict__ bt,
+    uint32_t base_bit, uint32_t end_bit, uint32_t in_state, int32_t blk, int32_t dc0, int32_t dc1, int32_t dc2, int16_t* __restrict__ coef,
+    DecodeResult& out)
 {
     out.err = 0;
     out.restarted = 0;
@@ -334,26 +358,29 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
         r = lo;
     }
     uint32_t next_bnd = (r == sv.nb - 1) ? sv.total_bits : __ldg(sv.bnd + r) * 8u;
+    // one comparison per symbol covers both "subsequence finished" and "restart boundary close"
+    uint32_t limit = min(end_bit, max(next_bnd, 7u) - 7u);
     uint32_t widx = p >> 5;
     uint32_t whi = __ldg(sv.words + widx), wlo = __ldg(sv.words + widx + 1);
     const uint8_t* hbase = reinterpret_cast<const uint8_t*>(hs);
-    // per-block constants: component, DC table, AC table (byte offsets into the table set)
-    uint32_t comp = (sv.blk_comp >> (2 * b)) & 3u;
-    uint32_t dc_off = ((sv.blk_tab >> b) & 1u) * uint32_t(sizeof(HuffTableDev));
-    uint32_t ac_off = (2u + ((sv.blk_tab >> (16 + b)) & 1u)) * uint32_t(sizeof(HuffTableDev));
+    uint2 binfo = bt->e[b]; // .x: DC table offset, .y: AC table offset | comp << 24 | next b << 28
     bool owned = (z == 0u); // kWrite: am I writing the block under way?
     BlockWriter bw;
     bw.reset();
     bool done = false;
     for (;;) {
         const uint32_t win = __funnelshift_l(wlo, whi, p & 31u);
-        // End of a restart interval (or of the stream): either the decoder already ran across the
-        // boundary (only an unsynchronised one can), or fewer than 8 bits remain and they are all
-        // 1-bits, i.e. the byte-alignment padding T.81 F.1.2.3 prescribes -- no complete code word
-        // fits there, because the all-ones code is never assigned.
-        if (p + 7u >= next_bnd) {
-            const uint32_t rem = next_bnd - p; // meaningful only when p < next_bnd
-            if (p >= next_bnd || (win >> (32u - rem)) == ((1u << rem) - 1u)) {
+        if (p >= limit) {
+            // End of a restart interval (or of the stream): either the decoder already ran across the
+            // boundary (only an unsynchronised one can), or fewer than 8 bits remain and they are all
+            // 1-bits, i.e. the byte-alignment padding T.81 F.1.2.3 prescribes -- no complete code word
+            // fits there, because the all-ones code is never assigned.
+            bool at_boundary = false;
+            if (p + 7u >= next_bnd) {
+                const uint32_t rem = next_bnd - p; // meaningful only when p < next_bnd
+                at_boundary = p >= next_bnd || (win >> (32u - rem)) == ((1u << rem) - 1u);
+            }
+            if (at_boundary) {
                 if (r == sv.nb - 1) {
                     done = true;
                     break;
@@ -361,6 +388,7 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
                 p = next_bnd;
                 ++r;
                 next_bnd = (r == sv.nb - 1) ? sv.total_bits : __ldg(sv.bnd + r) * 8u;
+                limit = min(end_bit, max(next_bnd, 7u) - 7u);
                 if (kWrite && (z != 0u || b != 0u || uint32_t(blk) != r * sv.ri_blocks))
                     out.err |= kFlagOverrun;
                 blk = int32_t(r * sv.ri_blocks);
@@ -370,19 +398,19 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
                 owned = true;
                 bw.reset();
                 dc0 = dc1 = dc2 = 0;
-                comp = sv.blk_comp & 3u;
-                dc_off = (sv.blk_tab & 1u) * uint32_t(sizeof(HuffTableDev));
-                ac_off = (2u + ((sv.blk_tab >> 16) & 1u)) * uint32_t(sizeof(HuffTableDev));
+                binfo = bt->e[0];
                 widx = p >> 5;
                 whi = __ldg(sv.words + widx);
                 wlo = __ldg(sv.words + widx + 1);
                 continue;
             }
+            if (p >= end_bit && (!kWrite || z == 0u || !owned))
+                break;
+            // otherwise: real code words within 7 bits of a boundary, or K3 finishing the block it
+            // owns past its range -- keep taking this path until one of the exits above fires
         }
-        if (p >= end_bit && (!kWrite || z == 0u || !owned))
-            break;
         const bool is_dc = (z == 0u);
-        const HuffTableDev* tab = reinterpret_cast<const HuffTableDev*>(hbase + (is_dc ? dc_off : ac_off));
+        const HuffTableDev* tab = reinterpret_cast<const HuffTableDev*>(hbase + (is_dc ? binfo.x : (binfo.y & 0xFFFFFFu)));
         uint32_t e = tab->lut[win >> (32 - kLutBits)];
         if ((e & 31u) == 0u) {
             // code longer than the first-level table: canonical search (T.81 F.2.2.3)
@@ -401,27 +429,32 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
         }
         const uint32_t len = e & 31u, size = (e >> 5) & 15u, skip = e >> 9;
         const uint32_t rest = win << len;
-        const uint32_t mag = __funnelshift_l(rest, 0u, size); // top `size` bits, 0 when size == 0
-        const int32_t val = (rest >> 31) ? int32_t(mag) : int32_t(mag) - int32_t((1u << size) - 1u);
         p += len + size;
         if ((p >> 5) != widx) {
             ++widx;
             whi = wlo;
             wlo = __ldg(sv.words + widx + 1);
         }
-        if (is_dc) {
-            dc0 += (comp == 0u) ? val : 0;
-            dc1 += (comp == 1u) ? val : 0;
-            dc2 += (comp == 2u) ? val : 0;
-        }
-        const uint32_t pos = z + skip - 1u; // zig-zag position of the coefficient this symbol carries (if any)
-        if (kWrite && owned && (is_dc || size != 0u)) {
-            if (pos > 63u)
-                out.err |= kFlagBadHuffman;
-            else if (uint32_t(blk) < sv.total_blocks)
-                bw.put(coef + size_t(blk) * 64, pos, is_dc ? (comp == 0u ? dc0 : (comp == 1u ? dc1 : dc2)) : val);
-            else
-                out.err |= kFlagOverrun;
+        if (kWrite || is_dc) {
+            const uint32_t mag = __funnelshift_l(rest, 0u, size); // top `size` bits, 0 when size == 0
+            const int32_t val = (rest >> 31) ? int32_t(mag) : int32_t(mag) - int32_t((1u << size) - 1u);
+            const uint32_t comp = (binfo.y >> 24) & 3u;
+            int32_t put_val = val;
+            if (is_dc) {
+                dc0 += (comp == 0u) ? val : 0;
+                dc1 += (comp == 1u) ? val : 0;
+                dc2 += (comp == 2u) ? val : 0;
+                put_val = comp == 0u ? dc0 : (comp == 1u ? dc1 : dc2);
+            }
+            if (kWrite && owned && (is_dc || size != 0u)) {
+                const uint32_t pos = z + skip - 1u; // zig-zag position of the coefficient this symbol carries
+                if (pos > 63u)
+                    out.err |= kFlagBadHuffman;
+                else if (uint32_t(blk) < sv.total_blocks)
+                    bw.put(coef + size_t(blk) * 64, pos, put_val);
+                else
+                    out.err |= kFlagOverrun;
+            }
         }
         z += skip;
         if (z > 63u) {
@@ -431,10 +464,8 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
             owned = true;
             z = 0;
             ++blk;
-            b = (b + 1u == sv.bpm) ? 0u : b + 1u;
-            comp = (sv.blk_comp >> (2 * b)) & 3u;
-            dc_off = ((sv.blk_tab >> b) & 1u) * uint32_t(sizeof(HuffTableDev));
-            ac_off = (2u + ((sv.blk_tab >> (16 + b)) & 1u)) * uint32_t(sizeof(HuffTableDev));
+            b = binfo.y >> 28;
+            binfo = bt->e[b];
         }
     }
     if (done) {
@@ -502,7 +533,8 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
 {
     extern __shared__ uint4 s_raw[];
     HuffSetDev* s_hs = reinterpret_cast<HuffSetDev*>(s_raw);
-    SyncShared& sh = *reinterpret_cast<SyncShared*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev));
+    BlockTable* s_bt = reinterpret_cast<BlockTable*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev));
+    SyncShared& sh = *reinterpret_cast<SyncShared*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev) + sizeof(BlockTable));
     const bool fix_mode = (mode & 1) != 0;
     const bool no_warm = (mode & 2) != 0; // test hook: bare guesses, no warm-up threads, no probe
     const uint32_t S = bd.sub_bits;
@@ -516,6 +548,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     if (first_k >= st.n_sub)
         return;
     load_huff_set(s_hs, bd.huff + im.huff_set);
+    build_block_table(s_bt, im);
     const StreamView sv = make_view(bd, im, st);
     const int t = threadIdx.x;
     const int k0 = int(first_k) - kSeqWarm; // subsequence of thread 0 (may be negative)
@@ -549,13 +582,13 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
         if (active && k > 0 && !no_warm) {
             // round 0: probe the tail of the previous subsequence
             const uint32_t pb = uint32_t(k) * S - S / 4;
-            decode_subsequence<false>(sv, s_hs, pb, uint32_t(k) * S, 0u, 0, 0, 0, 0, nullptr, res);
+            decode_subsequence<false>(sv, s_hs, s_bt, pb, uint32_t(k) * S, 0u, 0, 0, 0, 0, nullptr, res);
             in = res.state;
         }
         // round 1: everybody
         res.state = kStateDone;
         if (active) {
-            decode_subsequence<false>(sv, s_hs, uint32_t(k) * S, uint32_t(k + 1) * S, in, 0, 0, 0, 0, nullptr, res);
+            decode_subsequence<false>(sv, s_hs, s_bt, uint32_t(k) * S, uint32_t(k + 1) * S, in, 0, 0, 0, 0, nullptr, res);
             sh.info[t] = pack_info(res);
             sh.fresh[t] = 1;
         }
@@ -581,7 +614,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
         if (uint32_t(t) < n) {
             item = sh.queue[t];
             const uint32_t kk = uint32_t(k0 + int(item));
-            decode_subsequence<false>(sv, s_hs, kk * S, (kk + 1) * S, sh.in[item], 0, 0, 0, 0, nullptr, res);
+            decode_subsequence<false>(sv, s_hs, s_bt, kk * S, (kk + 1) * S, sh.in[item], 0, 0, 0, 0, nullptr, res);
         }
         __syncthreads(); // everyone has read count and queue
         if (t == 0)
@@ -714,6 +747,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, in
 {
     extern __shared__ uint4 s_raw[];
     HuffSetDev* s_hs = reinterpret_cast<HuffSetDev*>(s_raw);
+    BlockTable* s_bt = reinterpret_cast<BlockTable*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev));
     const uint32_t seq = blockIdx.x;
     const uint32_t img = bd.seq_img[seq];
     const ImageDev& im = bd.img[img];
@@ -724,6 +758,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, in
     if (first_k >= st.n_sub)
         return;
     load_huff_set(s_hs, bd.huff + im.huff_set);
+    build_block_table(s_bt, im);
     __syncthreads();
     const int t = threadIdx.x;
     const uint32_t k = first_k + uint32_t(t) - kSeqWarm;
@@ -738,7 +773,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, in
     if (!(in & kStateDone) && (uint32_t(start.x) % im.bpm) != ((in >> 12) & 15u)) {
         err |= kFlagPhase;
     } else {
-        decode_subsequence<true>(sv, s_hs, k * bd.sub_bits, (k + 1) * bd.sub_bits, in, start.x, start.y, start.z, start.w,
+        decode_subsequence<true>(sv, s_hs, s_bt, k * bd.sub_bits, (k + 1) * bd.sub_bits, in, start.x, start.y, start.z, start.w,
             bd.coef + im.coef_off, res);
         err |= res.err;
     }
@@ -931,16 +966,17 @@ __device__ __forceinline__ int sample_plane(const PlaneView& pv, int x, int y)
     return (3 * cur + 3 * s0[j - 1] + s1[j - 1] + 8) >> 4;
 }
 
-__device__ __forceinline__ uint32_t clamp255(int v) { return uint32_t(v < 0 ? 0 : (v > 255 ? 255 : v)); }
+__device__ __forceinline__ uint32_t clamp255(int v) { return uint32_t(__vimin_s32_relu(v, 255)); }
 
-// jdcolor.c fixed-point YCbCr -> RGB (SURVEY.md 8c "Colour")
+// jdcolor.c fixed-point YCbCr -> RGB (SURVEY.md 8c "Colour"); __viaddmin_s32_relu(a, b, c) is
+// max(min(a + b, c), 0) in one instruction, i.e. the add and the [0,255] clamp together.
 __device__ __forceinline__ void ycc_to_rgb(int y, int cb, int cr, uint32_t& r, uint32_t& g, uint32_t& b)
 {
     cb -= 128;
     cr -= 128;
-    r = clamp255(y + ((91881 * cr + 32768) >> 16));
-    g = clamp255(y + ((-22554 * cb - 46802 * cr + 32768) >> 16));
-    b = clamp255(y + ((116130 * cb + 32768) >> 16));
+    r = uint32_t(__viaddmin_s32_relu(y, (91881 * cr + 32768) >> 16, 255));
+    g = uint32_t(__viaddmin_s32_relu(y, (-22554 * cb - 46802 * cr + 32768) >> 16, 255));
+    b = uint32_t(__viaddmin_s32_relu(y, (116130 * cb + 32768) >> 16, 255));
 }
 
 constexpr int kColorTx = 32; // threads in x, 8 pixels each
@@ -1020,9 +1056,10 @@ __device__ __forceinline__ void load_chroma_row(const uint8_t* row, int j0, int 
 
 // Upsampled chroma for the 8 output pixels of output row `r` (0 or 1 inside the unit).
 //   cur / nbr: chroma row samples as loaded by load_chroma_row (nbr = vertical neighbour, or == cur)
-template <int HX, int VX>
-__device__ __forceinline__ void upsample8(const int* cur, const int* nbr, int r, bool fancy_h, bool fancy_v, int* out)
+template <int HX, int VX, bool kFancy>
+__device__ __forceinline__ void upsample8(const int* cur, const int* nbr, int r, int* out)
 {
+    constexpr bool fancy_h = kFancy, fancy_v = kFancy;
     if (HX == 2) {
         if (VX == 2 && fancy_v) { // h2v2 triangle (jdsample.c h2v2_fancy_upsample)
             int s[6];
@@ -1060,7 +1097,9 @@ __device__ __forceinline__ void upsample8(const int* cur, const int* nbr, int r,
 
 // One unit = 8 pixels x VX rows at image position (X0, Y0), X0 % 8 == 0, Y0 % VX == 0.
 // kLumaOnly: grayscale stream or Y output.
-template <int HX, int VX, bool kLumaOnly>
+// kFancy: the triangle filter applies (decided on the host: fancy_upsampling option, the expansion
+// factors and libjpeg's downsampled_width > 2 condition).
+template <int HX, int VX, bool kFancy, bool kLumaOnly>
 __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& im, int X0, int Y0)
 {
     const int W = im.width, H = im.height;
@@ -1070,9 +1109,7 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
     if (!kLumaOnly) {
         const int stride_c = int(im.mcus_x) * im.h[1] * 8;
         const int dw = (W * im.h[1] + im.hmax - 1) / im.hmax, dh = (H * im.v[1] + im.vmax - 1) / im.vmax;
-        const bool fancy = im.fancy != 0;
-        const bool fancy_h = fancy && HX == 2 && dw > 2;
-        const bool fancy_v = fancy && VX == 2 && (HX == 1 || dw > 2);
+        constexpr bool fancy_v = kFancy && VX == 2;
         const int j0 = X0 / HX;
         const int ci = Y0 / VX;
         constexpr int NC = (HX == 2) ? 6 : 8;
@@ -1091,7 +1128,7 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
 #pragma unroll
                 for (int k = 0; k < NC; ++k)
                     nb[k] = (VX == 2 && fancy_v) ? (r == 0 ? up[k] : dn[k]) : cur[k];
-                upsample8<HX, VX>(cur, nb, r, fancy_h, fancy_v, res);
+                upsample8<HX, VX, kFancy>(cur, nb, r, res);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
                     if (comp == 1)
@@ -1174,7 +1211,7 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
 
 // K4b.  CTA = 32 x 8 threads; a thread owns one unit of 8 pixels x unit_rows rows, aligned in image
 // coordinates so that every plane load is a naturally aligned 4- or 8-byte word.
-__global__ void __launch_bounds__(kColorTx* kColorTy, 2) color_kernel(BatchDev bd, int redo_only)
+__global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev bd, int redo_only)
 {
     const uint32_t cta = blockIdx.x;
     const uint32_t img = bd.color_cta_img[cta];
@@ -1191,11 +1228,14 @@ __global__ void __launch_bounds__(kColorTx* kColorTy, 2) color_kernel(BatchDev b
     if (X0 >= int(im.roi_x1) || Y0 >= int(im.roi_y1))
         return;
     switch (im.color_mode) {
-    case 1: color_unit<1, 1, true>(bd, im, X0, Y0); break;
-    case 2: color_unit<1, 1, false>(bd, im, X0, Y0); break;
-    case 3: color_unit<2, 1, false>(bd, im, X0, Y0); break;
-    case 4: color_unit<1, 2, false>(bd, im, X0, Y0); break;
-    case 5: color_unit<2, 2, false>(bd, im, X0, Y0); break;
+    case 1: color_unit<1, 1, false, true>(bd, im, X0, Y0); break;
+    case 2: color_unit<1, 1, false, false>(bd, im, X0, Y0); break;
+    case 3: color_unit<2, 1, false, false>(bd, im, X0, Y0); break;
+    case 4: color_unit<1, 2, false, false>(bd, im, X0, Y0); break;
+    case 5: color_unit<2, 2, false, false>(bd, im, X0, Y0); break;
+    case 6: color_unit<2, 1, true, false>(bd, im, X0, Y0); break;
+    case 7: color_unit<1, 2, true, false>(bd, im, X0, Y0); break;
+    case 8: color_unit<2, 2, true, false>(bd, im, X0, Y0); break;
     default:
         for (int r = 0; r < urows; ++r)
             for (int i = 0; i < 8; ++i) {
@@ -1207,7 +1247,8 @@ __global__ void __launch_bounds__(kColorTx* kColorTy, 2) color_kernel(BatchDev b
     }
 }
 
-constexpr size_t kSyncSmem = sizeof(HuffSetDev) + sizeof(SyncShared);
+constexpr size_t kSyncSmem = sizeof(HuffSetDev) + sizeof(BlockTable) + sizeof(SyncShared);
+constexpr size_t kWriteSmem = sizeof(HuffSetDev) + sizeof(BlockTable);
 
 } // namespace
 
@@ -1228,7 +1269,7 @@ int launch_sync(const BatchDev& b, bool fix_mode, bool no_warm, cudaStream_t s)
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(huff_sync_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSyncSmem));
-        cudaFuncSetAttribute(huff_write_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HuffSetDev)));
+        cudaFuncSetAttribute(huff_write_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kWriteSmem));
         attr_set = true;
     }
     huff_sync_kernel<<<b.n_seq, kSeqThreads, kSyncSmem, s>>>(b, (fix_mode ? 1 : 0) | (no_warm ? 2 : 0));
@@ -1247,7 +1288,7 @@ int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s)
 {
     if (b.n_seq == 0)
         return 0;
-    huff_write_kernel<<<b.n_seq, kSeqThreads, sizeof(HuffSetDev), s>>>(b, redo_only ? 1 : 0);
+    huff_write_kernel<<<b.n_seq, kSeqThreads, kWriteSmem, s>>>(b, redo_only ? 1 : 0);
     return 1;
 }
 

@@ -62,7 +62,7 @@ struct ImageDev {
     uint32_t row_stride;
     uint16_t roi_x0, roi_y0, roi_x1, roi_y1;
     uint8_t fmt, fancy;
-    uint8_t color_mode;      // K4b specialisation: 0 generic, 1 luma only, 2..5 chroma (hx,vx) = (1,1),(2,1),(1,2),(2,2)
+    uint8_t color_mode;      // K4b specialisation: 0 generic, 1 luma only, 2..5 chroma (hx,vx) = (1,1),(2,1),(1,2),(2,2) replicated, 6..8 = 3..5 with the triangle filter
     uint8_t color_unit_rows; // output rows per K4b thread (the chroma vertical factor on the fast paths)
 };
 
