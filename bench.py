@@ -22,25 +22,90 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-WORKLOAD = "C2: 256 x 1920x1080 baseline JPEG 4:2:0 q90 (no RST) -> I_RGB uint8"
+WORKLOADS = {
+    "c2": "C2: 256 x 1920x1080 baseline JPEG 4:2:0 q90 (no RST) -> I_RGB uint8",
+    "c3": "C3: 256 ImageNet-shaped (~500x375, 15% spread) JPEGs, mixed 4:4:4/4:2:2/4:2:0, q75-95, with RST markers -> I_RGB",
+    "c4": "C4: 64 x 3840x2160 baseline JPEG 4:4:4 q95, no restart markers -> I_RGB",
+    "c5": "C5: 8192 mixed images (C3 distribution + 10% 1080p), 50% with ROI, 30% grayscale output",
+}
+WORKLOAD = WORKLOADS["c2"]
 HEIGHT, WIDTH, PER_GPU = 1080, 1920, 256
 
 
-def _gen_one(seed):
+def _gen_spec(spec):
     from nvimagecodec_b200 import corpus
 
-    return corpus.encode(corpus.synth(HEIGHT, WIDTH, seed), 90, "420")
+    h, w, seed, q, samp, rst = spec
+    return corpus.encode(corpus.synth(h, w, seed), q, samp, rst_interval=rst)
+
+
+def _gen_one(seed):
+    return _gen_spec((HEIGHT, WIDTH, seed, 90, "420", 0))
+
+
+def _pmap(fn, items, workers):
+    from concurrent.futures import ProcessPoolExecutor
+
+    workers = max(1, min(workers, len(items)))
+    if workers == 1:
+        return [fn(x) for x in items]
+    with ProcessPoolExecutor(max_workers=workers) as ex:
+        return list(ex.map(fn, items, chunksize=max(1, len(items) // (workers * 4))))
 
 
 def make_corpus(n, workers):
     """n distinct seeded 1080p JPEGs, generated in parallel on the host (outside any timed region)."""
-    from concurrent.futures import ProcessPoolExecutor
+    return _pmap(_gen_one, list(range(n)), workers)
 
-    workers = max(1, min(workers, n))
-    if workers == 1:
-        return [_gen_one(s) for s in range(n)]
-    with ProcessPoolExecutor(max_workers=workers) as ex:
-        return list(ex.map(_gen_one, range(n), chunksize=max(1, n // (workers * 4))))
+
+def c3_specs(n, seed=1234):
+    import numpy as np
+
+    rng = np.random.default_rng(seed)
+    specs = []
+    for i in range(n):
+        h = int(np.clip(rng.normal(375, 0.15 * 375), 64, 1024))
+        w = int(np.clip(rng.normal(500, 0.15 * 500), 64, 1024))
+        samp = ["444", "422", "420"][i % 3]
+        q = [75, 85, 95][(i // 3) % 3]
+        hmax = 2 if samp in ("422", "420") else 1
+        row = (w + 8 * hmax - 1) // (8 * hmax)
+        specs.append((h, w, seed * 100003 + i, q, samp, [row, 8, 32][(i // 9) % 3]))
+    return specs
+
+
+def make_workload(name, n, workers):
+    """Returns (jpegs, formats, rois, output pixel count) for one GPU's share of the named config."""
+    import numpy as np
+
+    from nvimagecodec_b200 import jpeg_host
+
+    if name == "c2":
+        jp = make_corpus(n, workers)
+        return jp, ["I_RGB"] * n, [None] * n
+    if name == "c3":
+        jp = _pmap(_gen_spec, c3_specs(n), workers)
+        return jp, ["I_RGB"] * n, [None] * n
+    if name == "c4":
+        jp = _pmap(_gen_spec, [(2160, 3840, 5000 + s, 95, "444", 0) for s in range(n)], workers)
+        return jp, ["I_RGB"] * n, [None] * n
+    # c5: a pool of distinct streams cycled to n images, random in-bounds ROI on half, gray output on 30%
+    small = _pmap(_gen_spec, c3_specs(min(n, 461), seed=77), workers)
+    big = _pmap(_gen_spec, [(1080, 1920, 9000 + s, 90, "420", 0) for s in range(max(1, min(n, 512) // 10))], workers)
+    rng = np.random.default_rng(77)
+    jp, fmts, rois = [], [], []
+    for i in range(n):
+        d = big[(i // 10) % len(big)] if i % 10 == 9 else small[i % len(small)]
+        info = jpeg_host.probe(d)
+        roi = None
+        if rng.uniform() < 0.5:
+            rh, rw = max(1, int(info.height * rng.uniform(0.25, 0.75))), max(1, int(info.width * rng.uniform(0.25, 0.75)))
+            y0, x0 = int(rng.integers(0, info.height - rh + 1)), int(rng.integers(0, info.width - rw + 1))
+            roi = (y0, x0, y0 + rh, x0 + rw)
+        jp.append(d)
+        fmts.append("I_Y" if rng.uniform() < 0.3 else "I_RGB")
+        rois.append(roi)
+    return jp, fmts, rois
 
 
 class ClockSampler:
@@ -148,6 +213,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=PER_GPU, help="images per GPU (256 = the configuration the metric is quoted on)")
     ap.add_argument("--fancy", type=int, default=1, help="upsampling mode; 1 = libjpeg_turbo_ext default, what the CPU arm uses")
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="c2 is the configuration the metric is quoted on; "
+                    "the others are the remaining BASELINE.json configs, for extra lines only")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
@@ -164,7 +231,9 @@ def main():
     cores = os.cpu_count() or 1
     # ---- corpus: 256 distinct seeded images (worker processes are forked before CUDA is touched);
     # the N-GPU global batch is N copies, LPT-sharded by compressed bytes
-    base = make_corpus(args.batch, max(1, cores // world))
+    if args.workload != "c2" and args.batch == PER_GPU:
+        args.batch = {"c3": 256, "c4": 64, "c5": 8192 // max(world, 1)}[args.workload]
+    base, base_fmt, base_roi = make_workload(args.workload, args.batch, max(1, cores // world))
     assert torch.cuda.is_available(), "bench.py needs a GPU (the decoder has no CPU path)"
     torch.cuda.set_device(local)
     if world > 1:
@@ -172,8 +241,9 @@ def main():
     global_sizes = [len(base[i % args.batch]) for i in range(args.batch * world)]
     mine = sharding.shard_for_rank(global_sizes, rank, world)
     jpegs = [base[i % args.batch] for i in mine]
+    fmts = [base_fmt[i % args.batch] for i in mine]
+    rois = [base_roi[i % args.batch] for i in mine]
     n_img = len(jpegs)
-    mpix_step = n_img * HEIGHT * WIDTH / 1e6
 
     dec = Decoder(local, options=f":fancy_upsampling={args.fancy}")
     pinned_in = [torch.frombuffer(bytearray(j), dtype=torch.uint8).pin_memory() for j in jpegs]
@@ -187,7 +257,13 @@ def main():
         torch.cuda.synchronize()
 
     # ---- device-resident: Prepare once (H2D), then time Execute only
-    dev_batch = dec.make_batch(srcs, "I_RGB", to_host=False)
+    dev_batch = dec.make_batch(srcs, fmts, rois, to_host=False)
+    # MPix counts OUTPUT pixels (ROI pixels where a ROI is requested)
+    mpix_step = sum((r[2] - r[0]) * (r[3] - r[1]) if r else inf.width * inf.height for inf, r in zip(dev_batch.infos, rois)) / 1e6
+    planes_bytes = 0
+    for inf, f in zip(dev_batch.infos, fmts):
+        ncomp = 1 if f in ("I_Y", "P_Y") else inf.num_components
+        planes_bytes += sum(inf.mcus_x * inf.h[c] * 8 * inf.mcus_y * inf.v[c] * 8 for c in range(ncomp))
     dec.prepare(dev_batch)
     for _ in range(args.warmup):
         dec.execute()
@@ -224,7 +300,7 @@ def main():
     stages = {k: v / args.steps for k, v in stage_acc.items()}
 
     # ---- e2e: host pinned bitstreams in, host pinned pixels out, through the public call
-    host_batch = dec.make_batch(srcs, "I_RGB", to_host=True)
+    host_batch = dec.make_batch(srcs, fmts, rois, to_host=True)
     for _ in range(args.warmup):
         dec.run(host_batch)
     barrier()
@@ -263,7 +339,6 @@ def main():
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
-        planes_bytes = n_img * (1920 * 1088 + 2 * 960 * 544)
         # algorithmic bytes per launch of each kernel (DESIGN.md "Kernels"), for the N=1 shard of rank 0
         kbytes = {
             "scan(K0)": 2 * comp_bytes, "huff_sync(K1)": comp_bytes, "verify_scan(K2)": 40 * dec.stat(_lib.STAT_NUM_SUBSEQ),
@@ -284,17 +359,19 @@ def main():
         # bounded CPU sample on rank 0 only: 64 of the images, 2 passes, all host threads
         cpu = None
         if world == 1:
-            sample = jpegs[:64]
+            sample = jpegs[:64] if args.workload != "c5" else jpegs[:512]
             dt, how = cpu_reference_decode(sample, cores, 2)
-            cpu = {"value": 2 * len(sample) * HEIGHT * WIDTH / 1e6 / dt, "unit": "MPix/s", "cores": cores, "kind": "reference",
+            sample_mpix = sum(i.width * i.height for i in dev_batch.infos[:len(sample)]) / 1e6  # the CPU arm decodes whole images to RGB
+            cpu = {"value": 2 * sample_mpix / dt, "unit": "MPix/s", "cores": cores, "kind": "reference",
                    "sample": f"{len(sample)} of the batch's images x 2 passes on {cores} threads; {how}"}
         line = {
             "metric": "decoded_mpix_per_s", "value": job_mpix * args.steps / (ms_dev * 1e-3), "unit": "MPix/s",
             "images_per_s": job_imgs * args.steps / (ms_dev * 1e-3),
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "images_per_gpu": n_img, "upsampling": "fancy" if args.fancy else "box",
-                       "l2": "inputs larger than L2 (125 MB bitstreams + 3.2 GB coefficients per step), no flush needed",
+            "config": {"workload": WORKLOADS[args.workload], "images_per_gpu": n_img, "upsampling": "fancy" if args.fancy else "box",
+                       "l2": "working set per step (bitstreams + %.1f GB coefficients + planes + pixels) is larger than the 126 MB L2, no flush needed"
+                             % (2 * n_coefs / 1e9),
                        "sharding": "LPT by compressed bytes, one process per GPU, no collective"},
             "e2e": {"value": job_mpix * args.steps / (ms_e2e * 1e-3), "unit": "MPix/s", "images_per_s": job_imgs * args.steps / (ms_e2e * 1e-3),
                     "h2d_bytes_per_step": host_batch.h2d_bytes, "d2h_bytes_per_step": host_batch.d2h_bytes,

@@ -418,7 +418,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         std::fill(idct_img + im.idct_cta_off, idct_img + im.idct_cta_off + im.n_idct_cta, uint32_t(d));
         std::fill(color_img + im.color_cta_off, color_img + im.color_cta_off + im.n_color_cta_x * im.n_color_cta_y, uint32_t(d));
         cudaPointerAttributes attr{};
-        if (cudaPointerGetAttributes(&attr, data[in_index_[d]]) == cudaSuccess && attr.type == cudaMemoryTypeHost)
+        // small streams are cheaper to gather into the staging block (one big copy) than to copy one by one
+        if (im.raw_len >= (128u << 10) && cudaPointerGetAttributes(&attr, data[in_index_[d]]) == cudaSuccess && attr.type == cudaMemoryTypeHost)
             direct[d] = 1;
         else {
             cudaGetLastError();
