@@ -393,6 +393,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     so = align_up(so + 16ull * n_sub, 256);
     const size_t so_stats = so;
     so += 256;
+    const size_t so_mask = so;
+    so = align_up(so + coef_elems / 64, 256);
 
     coef_bytes_ = coef_elems * sizeof(int16_t);
     if (!upload_host_.ensure(upload_bytes) || !state_host_.ensure(sizeof(ImageState) * std::max(nd, 1)))
@@ -485,6 +487,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.sub_info = reinterpret_cast<int4*>(sc + so_info);
     bd_.sub_start = reinterpret_cast<int4*>(sc + so_start);
     bd_.sync_stats = reinterpret_cast<uint32_t*>(sc + so_stats);
+    bd_.blkmask = sc + so_mask;
     bd_.cmp = cmp_.as<uint32_t>();
     bd_.coef = coef_.as<int16_t>();
     bd_.planes = planes_.as<uint8_t>();
@@ -688,6 +691,14 @@ int Decoder::copy_coefficients(int index, int16_t* host_out, size_t cap_elems)
     cudaSetDevice(device_);
     if (!cuda_ok(cudaMemcpy(host_out, bd_.coef + im.coef_off, elems * sizeof(int16_t), cudaMemcpyDeviceToHost), "coefficient copy"))
         return B200JPEG_ERR_CUDA;
+    // groups K3 skipped (all zero) hold stale bytes on the device: blank them using the per-block masks
+    std::vector<uint8_t> masks(im.total_blocks);
+    if (!cuda_ok(cudaMemcpy(masks.data(), bd_.blkmask + im.coef_off / 64, masks.size(), cudaMemcpyDeviceToHost), "mask copy"))
+        return B200JPEG_ERR_CUDA;
+    for (size_t b = 0; b < masks.size(); ++b)
+        for (int g = 0; g < 8; ++g)
+            if (!((masks[b] >> g) & 1))
+                std::memset(host_out + b * 64 + g * 8, 0, 16);
     return B200JPEG_OK;
 }
 

@@ -268,41 +268,50 @@ struct StreamView {
     uint32_t total_blocks;
 };
 
-// Coefficient block assembly for K3: the 64 int16 of the block being decoded are emitted as eight
-// 16-byte groups, in order, straight from registers -- every byte of the coefficient buffer is
-// written exactly once (no clearing pass, no partial-sector read-modify-write in L2).
+// Coefficient block assembly for K3: the 64 int16 of the block being decoded are emitted as
+// 16-byte groups (8 coefficients in zig-zag order) straight from registers; groups that are all zero
+// -- most of them at photographic qualities -- are not written at all, a one-byte mask per block says
+// which groups exist.  No clearing pass, no partial-sector read-modify-write in L2.
 struct BlockWriter {
     uint64_t lo, hi; // coefficients 0..3 and 4..7 of the current group
     uint32_t g;      // current group, 0..7
+    uint32_t mask;   // groups of this block that hold a non-zero coefficient (and were stored)
     __device__ __forceinline__ void reset()
     {
         lo = hi = 0;
         g = 0;
+        mask = 0;
     }
-    __device__ __forceinline__ void flush_to(int16_t* __restrict__ blk_base, uint32_t upto)
+    __device__ __forceinline__ void store_group(int16_t* __restrict__ blk_base)
     {
-        while (g < upto) {
+        if (lo | hi) {
             *reinterpret_cast<uint4*>(blk_base + g * 8) = make_uint4(uint32_t(lo), uint32_t(lo >> 32), uint32_t(hi), uint32_t(hi >> 32));
+            mask |= 1u << g;
             lo = hi = 0;
-            ++g;
         }
     }
     __device__ __forceinline__ void put(int16_t* __restrict__ blk_base, uint32_t pos, int32_t val)
     {
-        flush_to(blk_base, pos >> 3);
+        const uint32_t ng = pos >> 3;
+        if (ng != g) { // positions only grow inside a block: the previous group is complete
+            store_group(blk_base);
+            g = ng;
+        }
         const uint64_t v = uint64_t(uint32_t(val) & 0xFFFFu) << (16 * (pos & 3u));
         if (pos & 4u)
             hi |= v;
         else
             lo |= v;
     }
+    // end of block: last group out, then the presence mask (all-zero groups are never written;
+    // K4a substitutes zeros for them)
+    __device__ __forceinline__ void finish(int16_t* __restrict__ blk_base, uint8_t* __restrict__ mask_out)
+    {
+        store_group(blk_base);
+        *mask_out = uint8_t(mask);
+    }
 };
 
-// Decodes the code words that start in [start bit given by in_state, end_bit).
-//   kWrite == false (K1): only the decoder state, the block count and the DC sums are tracked.
-//   kWrite == true  (K3): the thread OWNS every block that starts inside its range: a block already
-//     under way at entry is skipped (its owner, the previous thread, finishes it), and the block
-//     under way at end_bit is decoded to its end.
 // Per-block-in-MCU constants, one 64-bit word per block index, built once per CTA in shared memory:
 //   .x = byte offset of the block's DC table inside the table set
 //   .y = byte offset of its AC table | component << 24 | next block index << 28
@@ -329,7 +338,7 @@ __device__ __forceinline__ void build_block_table(BlockTable* bt, const ImageDev
 template <bool kWrite>
 __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const HuffSetDev* __restrict__ hs, const BlockTable* __restrict__ bt,
     uint32_t base_bit, uint32_t end_bit, uint32_t in_state, int32_t blk, int32_t dc0, int32_t dc1, int32_t dc2, int16_t* __restrict__ coef,
-    DecodeResult& out)
+    uint8_t* __restrict__ blkmask, DecodeResult& out)
 {
     out.err = 0;
     out.restarted = 0;
@@ -459,7 +468,7 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
         z += skip;
         if (z > 63u) {
             if (kWrite && owned && uint32_t(blk) < sv.total_blocks)
-                bw.flush_to(coef + size_t(blk) * 64, 8u);
+                bw.finish(coef + size_t(blk) * 64, blkmask + blk);
             bw.reset();
             owned = true;
             z = 0;
@@ -582,13 +591,13 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
         if (active && k > 0 && !no_warm) {
             // round 0: probe the tail of the previous subsequence
             const uint32_t pb = uint32_t(k) * S - S / 4;
-            decode_subsequence<false>(sv, s_hs, s_bt, pb, uint32_t(k) * S, 0u, 0, 0, 0, 0, nullptr, res);
+            decode_subsequence<false>(sv, s_hs, s_bt, pb, uint32_t(k) * S, 0u, 0, 0, 0, 0, nullptr, nullptr, res);
             in = res.state;
         }
         // round 1: everybody
         res.state = kStateDone;
         if (active) {
-            decode_subsequence<false>(sv, s_hs, s_bt, uint32_t(k) * S, uint32_t(k + 1) * S, in, 0, 0, 0, 0, nullptr, res);
+            decode_subsequence<false>(sv, s_hs, s_bt, uint32_t(k) * S, uint32_t(k + 1) * S, in, 0, 0, 0, 0, nullptr, nullptr, res);
             sh.info[t] = pack_info(res);
             sh.fresh[t] = 1;
         }
@@ -614,7 +623,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
         if (uint32_t(t) < n) {
             item = sh.queue[t];
             const uint32_t kk = uint32_t(k0 + int(item));
-            decode_subsequence<false>(sv, s_hs, s_bt, kk * S, (kk + 1) * S, sh.in[item], 0, 0, 0, 0, nullptr, res);
+            decode_subsequence<false>(sv, s_hs, s_bt, kk * S, (kk + 1) * S, sh.in[item], 0, 0, 0, 0, nullptr, nullptr, res);
         }
         __syncthreads(); // everyone has read count and queue
         if (t == 0)
@@ -774,7 +783,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, in
         err |= kFlagPhase;
     } else {
         decode_subsequence<true>(sv, s_hs, s_bt, k * bd.sub_bits, (k + 1) * bd.sub_bits, in, start.x, start.y, start.z, start.w,
-            bd.coef + im.coef_off, res);
+            bd.coef + im.coef_off, bd.blkmask + im.coef_off / 64, res);
         err |= res.err;
     }
     if (err)
@@ -864,9 +873,12 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
     int32_t zz[64];
     {
         const uint4* s4 = reinterpret_cast<const uint4*>(src);
+        const uint32_t mask = __ldg(bd.blkmask + im.coef_off / 64 + (size_t(my * im.mcus_x + mx) * im.bpm + bim));
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const uint4 v = __ldg(s4 + i);
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if ((mask >> i) & 1u) // groups K3 did not write are all zero
+                v = __ldg(s4 + i);
             const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
             for (int j = 0; j < 4; ++j) {

@@ -91,6 +91,7 @@ struct BatchDev {
     int4* sub_start;        // exclusive scan: x = absolute block index at entry, yzw = DC predictors
     const HuffSetDev* huff;
     int16_t* coef;
+    uint8_t* blkmask;       // per coefficient block: which of its eight 16-byte groups K3 wrote (bit g = group g)
     uint8_t* planes;
     const uint32_t* idct_cta_img;
     const uint32_t* color_cta_img;
