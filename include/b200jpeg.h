@@ -142,7 +142,7 @@ B200JPEG_API int b200jpegScanSegment(b200jpegDecoder_t decoder, const void* dev_
  * calls cudaMalloc, cudaFree or any other allocating routine, and needs no decoder handle.
  *
  * How: the per-tile counts, the tile map and the segment descriptor that K0 needs live in one fixed
- * 41 KiB array inside the library (a static __device__ array; every GPU that loads the library
+ * 11 KiB array inside the library (a static __device__ array; every GPU that loads the library
  * holds it until the process exits).  That bounds the segment: length must not exceed
  * B200JPEG_NOALLOC_MAX_SEGMENT_BYTES (8 MiB of byte-stuffed scan data); longer segments are refused
  * with B200JPEG_ERR_TOO_LARGE and nothing is launched.  Inputs and outputs are the caller's, with the

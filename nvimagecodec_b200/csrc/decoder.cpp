@@ -271,6 +271,9 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 im.blk_tab |= uint32_t(hd.ta[c]) << (16 + b);
             }
             std::memcpy(im.qt[c], hd.qt[hd.tq[c]], sizeof(im.qt[c]));
+            im.plane_stride_px[c] = uint32_t(hd.mcus_x) * hd.h[c] * 8;
+            im.comp_w[c] = uint16_t((hd.width * hd.h[c] + hd.hmax - 1) / hd.hmax);
+            im.comp_h[c] = uint16_t((hd.height * hd.v[c] + hd.vmax - 1) / hd.vmax);
             const size_t pw = size_t(hd.mcus_x) * hd.h[c] * 8, ph = size_t(hd.mcus_y) * hd.v[c] * 8;
             if (c < im.ncomp_needed) {
                 im.plane_off[c] = plane_bytes;
@@ -315,6 +318,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             im.color_cta_off = n_color;
             im.n_color_cta_x = uint32_t((size_t(x1) - ax0 + 255) / 256);
             im.n_color_cta_y = uint32_t((size_t(y1) - ay0 + 8 * ur - 1) / (8 * ur));
+            im.color_cta_x_rcp = im.n_color_cta_x > 1 ? uint32_t((uint64_t(1) << 32) / im.n_color_cta_x + 1) : 0u;
         }
         n_color += im.n_color_cta_x * im.n_color_cta_y;
         HostOut ho{nullptr, 0, obytes};

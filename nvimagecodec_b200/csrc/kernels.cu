@@ -76,24 +76,48 @@ __device__ __forceinline__ uint32_t block_min_u32(uint32_t v, uint32_t* s_tmp)
     return *s_tmp;
 }
 
+// Staging-buffer swizzle for K0c: a thread compacts 64 consecutive input bytes, so without it the
+// 32 lanes of a byte store would hit two shared-memory banks (16-way conflict).  XOR-ing the
+// word-in-row index with the 128-byte row number spreads them over all 32 banks; the sequential
+// read-out stays conflict-free because lanes of one row see the same XOR constant.
+__device__ __forceinline__ uint32_t stage_swz(uint32_t byte_index) { return byte_index ^ (((byte_index >> 7) & 15u) << 2); }
+
+__device__ __forceinline__ uint32_t valid_mask16(uint32_t e, uint32_t i0)
+{
+    if (e == 0xFFFFFFFFu)
+        return 0xFFFFu;
+    return (e <= i0) ? 0u : ((e - i0 >= 16) ? 0xFFFFu : ((1u << (e - i0)) - 1u));
+}
+
+// K0a: per-tile counts.  A thread owns kScanChunks consecutive 16-byte chunks (64 contiguous bytes),
+// so a CTA streams 16 KiB with four independent 128-bit loads in flight per thread.
 __global__ void __launch_bounds__(kScanThreads) scan_count_kernel(BatchDev bd)
 {
     __shared__ uint32_t s_min, s_kept, s_rst;
     const uint32_t tile = blockIdx.x;
     const ImageDev& im = bd.img[bd.tile_img[tile]];
     const uint8_t* raw = bd.raw + im.raw_off;
-    const uint32_t i0 = (tile - im.tile_off) * kScanTileBytes + threadIdx.x * 16;
-    const ByteMasks m = classify16(raw, im.raw_len, i0);
-    const uint32_t my_end = m.end ? (i0 + __ffs(m.end) - 1) : 0xFFFFFFFFu;
+    const uint32_t i0 = (tile - im.tile_off) * kScanTileBytes + threadIdx.x * (16 * kScanChunks);
+    ByteMasks m[kScanChunks];
+    uint32_t my_end = 0xFFFFFFFFu;
+#pragma unroll
+    for (int c = 0; c < kScanChunks; ++c) {
+        m[c] = classify16(raw, im.raw_len, i0 + 16 * c);
+        if (m[c].end && my_end == 0xFFFFFFFFu)
+            my_end = i0 + 16 * c + __ffs(m[c].end) - 1;
+    }
     if (threadIdx.x == 0) {
         s_kept = 0;
         s_rst = 0;
     }
     const uint32_t e = block_min_u32(my_end, &s_min); // includes the barriers that publish s_kept/s_rst
-    uint32_t valid = 0xFFFFu;
-    if (e != 0xFFFFFFFFu)
-        valid = (e <= i0) ? 0u : ((e - i0 >= 16) ? 0xFFFFu : ((1u << (e - i0)) - 1u));
-    uint32_t k = __popc(m.kept & valid), r = __popc(m.rst & valid);
+    uint32_t k = 0, r = 0;
+#pragma unroll
+    for (int c = 0; c < kScanChunks; ++c) {
+        const uint32_t valid = valid_mask16(e, i0 + 16 * c);
+        k += __popc(m[c].kept & valid);
+        r += __popc(m[c].rst & valid);
+    }
     k = __reduce_add_sync(0xffffffffu, k);
     r = __reduce_add_sync(0xffffffffu, r);
     if ((threadIdx.x & 31) == 0) {
@@ -169,16 +193,25 @@ __global__ void __launch_bounds__(kScanThreads) scan_scatter_kernel(BatchDev bd)
     if (base.x == 0xFFFFFFFFu)
         return; // past the end marker
     const uint8_t* raw = bd.raw + im.raw_off;
-    const uint32_t i0 = (tile - im.tile_off) * kScanTileBytes + threadIdx.x * 16;
-    const ByteMasks m = classify16(raw, im.raw_len, i0);
-    const uint32_t my_end = m.end ? (i0 + __ffs(m.end) - 1) : 0xFFFFFFFFu;
+    const uint32_t i0 = (tile - im.tile_off) * kScanTileBytes + threadIdx.x * (16 * kScanChunks);
+    ByteMasks m[kScanChunks];
+    uint32_t my_end = 0xFFFFFFFFu;
+#pragma unroll
+    for (int c = 0; c < kScanChunks; ++c) {
+        m[c] = classify16(raw, im.raw_len, i0 + 16 * c);
+        if (m[c].end && my_end == 0xFFFFFFFFu)
+            my_end = i0 + 16 * c + __ffs(m[c].end) - 1;
+    }
     const uint32_t e = block_min_u32(my_end, &s_min);
-    uint32_t valid = 0xFFFFu;
-    if (e != 0xFFFFFFFFu)
-        valid = (e <= i0) ? 0u : ((e - i0 >= 16) ? 0xFFFFu : ((1u << (e - i0)) - 1u));
-    const uint32_t kept = m.kept & valid, rst = m.rst & valid;
+    uint32_t mine = 0;
+#pragma unroll
+    for (int c = 0; c < kScanChunks; ++c) {
+        const uint32_t valid = valid_mask16(e, i0 + 16 * c);
+        m[c].kept &= valid;
+        m[c].rst &= valid;
+        mine += __popc(m[c].kept) | (__popc(m[c].rst) << 16);
+    }
     // block-wide exclusive scan of (kept count | rst count << 16)
-    const uint32_t mine = __popc(kept) | (__popc(rst) << 16);
     uint32_t inc = mine;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -202,20 +235,24 @@ __global__ void __launch_bounds__(kScanThreads) scan_scatter_kernel(BatchDev bd)
     uint32_t lk = excl & 0xFFFFu, lr = excl >> 16;
     const uint32_t tile_kept = total & 0xFFFFu;
     // stage kept bytes, record restart boundaries
-    if (kept | rst) {
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(raw + i0));
-        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            const uint32_t cur = (w[j >> 2] >> (8 * (j & 3))) & 0xFFu;
-            if ((kept >> j) & 1u)
-                s_stage[lk++] = uint8_t(cur);
-            if ((rst >> j) & 1u) {
-                const uint32_t idx = base.y + lr++;
-                if (idx + 1 < im.n_bnd_cap)
-                    bd.bnd[im.bnd_off + idx] = base.x + lk;
-                if (cur != 0xD0u + (idx & 7u))
-                    atomicOr(&bd.state[img].flags, kFlagBadMarker);
+    for (int c = 0; c < kScanChunks; ++c) {
+        const uint32_t kept = m[c].kept, rst = m[c].rst;
+        if (kept | rst) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(raw + i0 + 16 * c));
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const uint32_t cur = (w[j >> 2] >> (8 * (j & 3))) & 0xFFu;
+                if ((kept >> j) & 1u)
+                    s_stage[stage_swz(lk++)] = uint8_t(cur);
+                if ((rst >> j) & 1u) {
+                    const uint32_t idx = base.y + lr++;
+                    if (idx + 1 < im.n_bnd_cap)
+                        bd.bnd[im.bnd_off + idx] = base.x + lk;
+                    if (cur != 0xD0u + (idx & 7u))
+                        atomicOr(&bd.state[img].flags, kFlagBadMarker);
+                }
             }
         }
     }
@@ -228,17 +265,17 @@ __global__ void __launch_bounds__(kScanThreads) scan_scatter_kernel(BatchDev bd)
     if (w1 > w0) {
         for (uint32_t wi = w0 + threadIdx.x; wi < w1; wi += kScanThreads) {
             const uint32_t li = wi * 4 - g0;
-            dst32[wi] = (uint32_t(s_stage[li]) << 24) | (uint32_t(s_stage[li + 1]) << 16) | (uint32_t(s_stage[li + 2]) << 8) |
-                        uint32_t(s_stage[li + 3]);
+            dst32[wi] = (uint32_t(s_stage[stage_swz(li)]) << 24) | (uint32_t(s_stage[stage_swz(li + 1)]) << 16) |
+                        (uint32_t(s_stage[stage_swz(li + 2)]) << 8) | uint32_t(s_stage[stage_swz(li + 3)]);
         }
         const uint32_t head = w0 * 4 - g0, tail = g1 - w1 * 4; // < 4 each
         if (threadIdx.x < head)
-            dst8[(g0 + threadIdx.x) ^ 3u] = s_stage[threadIdx.x];
+            dst8[(g0 + threadIdx.x) ^ 3u] = s_stage[stage_swz(threadIdx.x)];
         if (threadIdx.x >= 32 && threadIdx.x - 32 < tail)
-            dst8[(w1 * 4 + threadIdx.x - 32) ^ 3u] = s_stage[w1 * 4 - g0 + threadIdx.x - 32];
+            dst8[(w1 * 4 + threadIdx.x - 32) ^ 3u] = s_stage[stage_swz(w1 * 4 - g0 + threadIdx.x - 32)];
     } else {
         for (uint32_t i = threadIdx.x; i < tile_kept; i += kScanThreads)
-            dst8[(g0 + i) ^ 3u] = s_stage[i];
+            dst8[(g0 + i) ^ 3u] = s_stage[stage_swz(i)];
     }
 }
 
@@ -932,9 +969,9 @@ __device__ __forceinline__ PlaneView make_plane(const BatchDev& bd, const ImageD
 {
     PlaneView pv;
     pv.p = bd.planes + im.plane_off[c];
-    pv.stride = int(im.mcus_x) * im.h[c] * 8;
-    pv.dw = (int(im.width) * im.h[c] + im.hmax - 1) / im.hmax;
-    pv.dh = (int(im.height) * im.v[c] + im.vmax - 1) / im.vmax;
+    pv.stride = int(im.plane_stride_px[c]);
+    pv.dw = int(im.comp_w[c]);
+    pv.dh = int(im.comp_h[c]);
     pv.hx = im.hmax / im.h[c];
     pv.vx = im.vmax / im.v[c];
     const bool f = im.fancy != 0;
@@ -1111,16 +1148,15 @@ __device__ __forceinline__ void upsample8(const int* cur, const int* nbr, int r,
 // kLumaOnly: grayscale stream or Y output.
 // kFancy: the triangle filter applies (decided on the host: fancy_upsampling option, the expansion
 // factors and libjpeg's downsampled_width > 2 condition).
-template <int HX, int VX, bool kFancy, bool kLumaOnly>
+template <int HX, int VX, bool kFancy, bool kLumaOnly, bool kSwap>
 __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& im, int X0, int Y0)
 {
-    const int W = im.width, H = im.height;
     const uint8_t* p0 = bd.planes + im.plane_off[0];
-    const int stride0 = int(im.mcus_x) * im.h[0] * 8;
+    const int stride0 = int(im.plane_stride_px[0]);
     int cb[VX][8], cr[VX][8];
     if (!kLumaOnly) {
-        const int stride_c = int(im.mcus_x) * im.h[1] * 8;
-        const int dw = (W * im.h[1] + im.hmax - 1) / im.hmax, dh = (H * im.v[1] + im.vmax - 1) / im.vmax;
+        const int stride_c = int(im.plane_stride_px[1]);
+        const int dw = int(im.comp_w[1]), dh = int(im.comp_h[1]); // real (not MCU-padded) chroma size: edges replicate there
         constexpr bool fancy_v = kFancy && VX == 2;
         const int j0 = X0 / HX;
         const int ci = Y0 / VX;
@@ -1151,7 +1187,7 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
             }
         }
     }
-    const bool swap = (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR);
+    constexpr bool swap = kSwap; // BGR orders
     const bool full_x = X0 >= int(im.roi_x0) && X0 + 8 <= int(im.roi_x1);
 #pragma unroll
     for (int r = 0; r < VX; ++r) {
@@ -1232,22 +1268,32 @@ __global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev b
     if ((flags & (kFlagDirty | kFlagBadMarker)) || (redo_only && !(flags & kFlagRedo)))
         return;
     const uint32_t local = cta - im.color_cta_off;
-    const uint32_t cy = local / im.n_color_cta_x, cx = local - cy * im.n_color_cta_x;
+    const uint32_t cy = im.n_color_cta_x == 1u ? local : __umulhi(local, im.color_cta_x_rcp); // exact for local < 2^16 * n_color_cta_x
+    const uint32_t cx = local - cy * im.n_color_cta_x;
     const int tx = threadIdx.x % kColorTx, ty = threadIdx.x / kColorTx;
     const int urows = im.color_unit_rows;
     const int X0 = (int(im.roi_x0) & ~7) + (int(cx) * kColorTx + tx) * 8;
-    const int Y0 = (int(im.roi_y0) / urows) * urows + (int(cy) * kColorTy + ty) * urows;
+    const int Y0 = (int(im.roi_y0) & ~(urows - 1)) + (int(cy) * kColorTy + ty) * urows; // urows is 1 or 2
     if (X0 >= int(im.roi_x1) || Y0 >= int(im.roi_y1))
         return;
+    const bool swap = (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR);
+#define B200_COLOR_CASE(mode, HX, VX, FANCY, LUMA)                  \
+    case mode:                                                      \
+        if (swap)                                                   \
+            color_unit<HX, VX, FANCY, LUMA, true>(bd, im, X0, Y0);  \
+        else                                                        \
+            color_unit<HX, VX, FANCY, LUMA, false>(bd, im, X0, Y0); \
+        break;
     switch (im.color_mode) {
-    case 1: color_unit<1, 1, false, true>(bd, im, X0, Y0); break;
-    case 2: color_unit<1, 1, false, false>(bd, im, X0, Y0); break;
-    case 3: color_unit<2, 1, false, false>(bd, im, X0, Y0); break;
-    case 4: color_unit<1, 2, false, false>(bd, im, X0, Y0); break;
-    case 5: color_unit<2, 2, false, false>(bd, im, X0, Y0); break;
-    case 6: color_unit<2, 1, true, false>(bd, im, X0, Y0); break;
-    case 7: color_unit<1, 2, true, false>(bd, im, X0, Y0); break;
-    case 8: color_unit<2, 2, true, false>(bd, im, X0, Y0); break;
+        B200_COLOR_CASE(1, 1, 1, false, true)
+        B200_COLOR_CASE(2, 1, 1, false, false)
+        B200_COLOR_CASE(3, 2, 1, false, false)
+        B200_COLOR_CASE(4, 1, 2, false, false)
+        B200_COLOR_CASE(5, 2, 2, false, false)
+        B200_COLOR_CASE(6, 2, 1, true, false)
+        B200_COLOR_CASE(7, 1, 2, true, false)
+        B200_COLOR_CASE(8, 2, 2, true, false)
+#undef B200_COLOR_CASE
     default:
         for (int r = 0; r < urows; ++r)
             for (int i = 0; i < 8; ++i) {
@@ -1337,7 +1383,7 @@ static_assert(sizeof(ImageDev) <= kNoAllocDescBytes, "descriptor slot too small"
 constexpr size_t kNoAllocOffTileImg = kNoAllocDescBytes;
 constexpr size_t kNoAllocOffInfo = kNoAllocOffTileImg + 4 * kNoAllocMaxTiles;
 constexpr size_t kNoAllocOffBase = kNoAllocOffInfo + 8 * kNoAllocMaxTiles;
-constexpr size_t kNoAllocScratchBytes = kNoAllocOffBase + 8 * kNoAllocMaxTiles; // 1 KiB + 20 B per 4 KiB tile = 41 KiB
+constexpr size_t kNoAllocScratchBytes = kNoAllocOffBase + 8 * kNoAllocMaxTiles; // 1 KiB + 20 B per 16 KiB tile = 11 KiB
 
 static __device__ __align__(256) unsigned char g_noalloc_scan_scratch[kNoAllocScratchBytes];
 

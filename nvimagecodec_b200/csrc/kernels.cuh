@@ -10,8 +10,9 @@
 namespace b200jpeg {
 
 // ---- entropy-stage geometry
-constexpr int kScanTileBytes = 4096;  // K0: bytes of byte-stuffed scan data per CTA
-constexpr int kScanThreads = 256;     // 16 B per thread
+constexpr int kScanThreads = 256;     // K0: 64 B (four 16-byte chunks) of byte-stuffed scan data per thread,
+constexpr int kScanChunks = 4;        //     16 KiB per CTA
+constexpr int kScanTileBytes = kScanThreads * 16 * kScanChunks;
 constexpr int kMinSubseqBits = 1024;  // K1-K3: bits of unstuffed stream per thread ("subsequence"); the host picks
 constexpr int kMaxSubseqBits = 4096;  //   1024, 2048 or 4096 per batch (BatchDev::sub_bits) so the GPU stays filled
 constexpr int kSeqThreads = 256;      // threads per CTA ("sequence")
@@ -50,6 +51,9 @@ struct ImageDev {
     uint32_t blk_tab;               // bit b: DC table id of block b, bit 16+b: AC table id
     uint32_t idct_cta_off, n_idct_cta;
     uint32_t color_cta_off, n_color_cta_x, n_color_cta_y;
+    uint32_t color_cta_x_rcp;       // ceil(2^32 / n_color_cta_x): cta -> (row, column) without a division
+    uint32_t plane_stride_px[3];    // row pitch of each MCU-padded component plane
+    uint16_t comp_w[3], comp_h[3];  // real component size ceil(W*h/hmax) x ceil(H*v/vmax): where edges replicate
     uint16_t width, height, mcus_x, mcus_y;
     uint8_t ncomp, hmax, vmax, bpm;
     uint8_t h[3], v[3];
