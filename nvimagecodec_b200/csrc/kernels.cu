@@ -870,11 +870,13 @@ __device__ __forceinline__ void idct8(int32_t i0, int32_t i1, int32_t i2, int32_
     o[4] = (a13 - t0 + rnd) >> kShift;
 }
 
-// libjpeg's range_limit table indexed with (x & 1023): clamp(x + 128) with a 10-bit wrap
+// libjpeg's range_limit table indexed with (x & 1023), i.e. clamp(x + 128) with a 10-bit wrap:
+//   i = x & 1023;  i < 128 -> i + 128;  i < 512 -> 255;  i < 896 -> 0;  else i - 896.
+// With u = (x + 128) & 1023 that is u for u < 256, 255 for u < 640, 0 above; shifting the wrap
+// point to 640 turns it into one clamp: t = ((x + 512) & 1023) - 384, result = min(max(t, 0), 255).
 __device__ __forceinline__ uint32_t range_limit(int32_t x)
 {
-    const int32_t i = x & 1023;
-    return uint32_t(i < 128 ? i + 128 : (i < 512 ? 255 : (i < 896 ? 0 : i - 896)));
+    return uint32_t(__vimin_s32_relu(((x + 512) & 1023) - 384, 255));
 }
 
 __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
