@@ -259,6 +259,14 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.fmt = uint8_t(o.format);
         im.fancy = opt_.fancy_upsampling ? 1 : 0;
         im.ncomp_needed = (o.format == B200JPEG_FMT_Y || hd.ncomp == 1) ? 1 : 3;
+        // MCU rows the ROI needs: its own rows plus one MCU row of context on each side (the vertical
+        // triangle filter looks one chroma row up / down)
+        const int mcu_h = 8 * hd.vmax;
+        const int mcu_row_lo = std::max(0, y0 / mcu_h - 1), mcu_row_hi = std::min(hd.mcus_y, (y1 + mcu_h - 1) / mcu_h + 1);
+        im.mcu_row_lo = uint16_t(mcu_row_lo);
+        im.mcu_row_hi = uint16_t(mcu_row_hi);
+        im.write_blk_lo = uint32_t(mcu_row_lo) * uint32_t(hd.mcus_x) * uint32_t(hd.blocks_per_mcu);
+        im.write_blk_hi = uint32_t(mcu_row_hi) * uint32_t(hd.mcus_x) * uint32_t(hd.blocks_per_mcu);
         int b = 0;
         uint32_t idct_blocks = 0;
         for (int c = 0; c < hd.ncomp; ++c) {
@@ -278,7 +286,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             if (c < im.ncomp_needed) {
                 im.plane_off[c] = plane_bytes;
                 plane_bytes += align_up(pw * ph, 256);
-                idct_blocks += uint32_t(pw / 8 * (ph / 8));
+                idct_blocks += uint32_t(pw / 8) * uint32_t(mcu_row_hi - mcu_row_lo) * hd.v[c];
             }
         }
         im.idct_cta_off = n_idct;
@@ -348,7 +356,14 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.huff_set = uint32_t(it->second);
 
         comp_bytes_ += int64_t(len[i]);
-        n_coefs_ += int64_t(im.total_blocks) * 64;
+        {
+            // coefficients are counted for the MCU rows actually decoded and, for Y output
+            // of a colour stream, for luma only
+            int64_t blocks_per_mcu_needed = 0;
+            for (int c = 0; c < im.ncomp_needed; ++c)
+                blocks_per_mcu_needed += hd.h[c] * hd.v[c];
+            n_coefs_ += int64_t(mcu_row_hi - mcu_row_lo) * hd.mcus_x * blocks_per_mcu_needed * 64;
+        }
         out_bytes_ += int64_t(rw * rh * nch);
         dev_index_[i] = int(imgs_.size());
         in_index_.push_back(i);

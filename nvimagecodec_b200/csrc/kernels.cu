@@ -303,6 +303,8 @@ struct StreamView {
     uint32_t bpm, blk_comp, blk_tab;
     uint32_t ri_blocks;      // restart_interval * bpm
     uint32_t total_blocks;
+    uint32_t write_lo, write_hi; // K3: only blocks in [write_lo, write_hi) are wanted (MCU rows a ROI touches)
+    uint32_t comp_mask;          // K3: bit c set = component c is wanted (luma only for Y output)
 };
 
 // Coefficient block assembly for K3: the 64 int16 of the block being decoded are emitted as
@@ -410,7 +412,9 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
     uint32_t whi = __ldg(sv.words + widx), wlo = __ldg(sv.words + widx + 1);
     const uint8_t* hbase = reinterpret_cast<const uint8_t*>(hs);
     uint2 binfo = bt->e[b]; // .x: DC table offset, .y: AC table offset | comp << 24 | next b << 28
-    bool owned = (z == 0u); // kWrite: am I writing the block under way?
+    bool owned = (z == 0u); // kWrite: is the block under way mine (it started inside my range)?
+    // ... and is it wanted at all (inside the ROI's MCU rows, component needed)?
+    bool wanted = kWrite && uint32_t(blk) - sv.write_lo < sv.write_hi - sv.write_lo && ((sv.comp_mask >> ((binfo.y >> 24) & 3u)) & 1u);
     BlockWriter bw;
     bw.reset();
     bool done = false;
@@ -445,6 +449,7 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
                 bw.reset();
                 dc0 = dc1 = dc2 = 0;
                 binfo = bt->e[0];
+                wanted = kWrite && uint32_t(blk) - sv.write_lo < sv.write_hi - sv.write_lo && (sv.comp_mask & 1u);
                 widx = p >> 5;
                 whi = __ldg(sv.words + widx);
                 wlo = __ldg(sv.words + widx + 1);
@@ -492,7 +497,7 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
                 dc2 += (comp == 2u) ? val : 0;
                 put_val = comp == 0u ? dc0 : (comp == 1u ? dc1 : dc2);
             }
-            if (kWrite && owned && (is_dc || size != 0u)) {
+            if (kWrite && owned && wanted && (is_dc || size != 0u)) {
                 const uint32_t pos = z + skip - 1u; // zig-zag position of the coefficient this symbol carries
                 if (pos > 63u)
                     out.err |= kFlagBadHuffman;
@@ -504,7 +509,7 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
         }
         z += skip;
         if (z > 63u) {
-            if (kWrite && owned && uint32_t(blk) < sv.total_blocks)
+            if (kWrite && owned && wanted && uint32_t(blk) < sv.total_blocks)
                 bw.finish(coef + size_t(blk) * 64, blkmask + blk);
             bw.reset();
             owned = true;
@@ -512,6 +517,7 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
             ++blk;
             b = binfo.y >> 28;
             binfo = bt->e[b];
+            wanted = kWrite && uint32_t(blk) - sv.write_lo < sv.write_hi - sv.write_lo && ((sv.comp_mask >> ((binfo.y >> 24) & 3u)) & 1u);
         }
     }
     if (done) {
@@ -547,6 +553,9 @@ __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageD
     sv.blk_tab = im.blk_tab;
     sv.ri_blocks = im.restart_interval * im.bpm;
     sv.total_blocks = im.total_blocks;
+    sv.write_lo = im.write_blk_lo;
+    sv.write_hi = im.write_blk_hi;
+    sv.comp_mask = im.ncomp_needed >= 3 ? 7u : 1u;
     return sv;
 }
 
@@ -816,6 +825,12 @@ __global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, in
     const int4 start = bd.sub_start[g];
     DecodeResult res;
     uint32_t err = 0;
+    // ROI: nothing to write if every block this thread can own lies outside the wanted MCU rows.  (The
+    // end-of-stream consistency check then falls to whoever decodes the tail; a ROI that excludes the
+    // last MCU row skips it, like libjpeg's jpeg_skip_scanlines does.)
+    const uint32_t next_start = (k + 1 < st.n_sub) ? uint32_t(bd.sub_start[g + 1].x) : im.total_blocks;
+    if (uint32_t(start.x) >= im.write_blk_hi || next_start < im.write_blk_lo)
+        return;
     if (!(in & kStateDone) && (uint32_t(start.x) % im.bpm) != ((in >> 12) & 15u)) {
         err |= kFlagPhase;
     } else {
@@ -891,20 +906,21 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
     for (int i = threadIdx.x; i < 3 * 64; i += blockDim.x)
         s_q[i / 64][i % 64] = im.qt[i / 64][i % 64];
     __syncthreads();
-    // block index over the planes of the needed components, row-major per plane
+    // block index over the wanted rows of the planes of the needed components, row-major per plane
     uint32_t idx = (cta - im.idct_cta_off) * blockDim.x + threadIdx.x;
     int c = 0;
-    uint32_t bw = 0, bh = 0;
+    uint32_t bw = 0, by0 = 0;
     for (; c < im.ncomp_needed; ++c) {
         bw = uint32_t(im.mcus_x) * im.h[c];
-        bh = uint32_t(im.mcus_y) * im.v[c];
-        if (idx < bw * bh)
+        by0 = uint32_t(im.mcu_row_lo) * im.v[c];
+        const uint32_t rows = uint32_t(im.mcu_row_hi - im.mcu_row_lo) * im.v[c];
+        if (idx < bw * rows)
             break;
-        idx -= bw * bh;
+        idx -= bw * rows;
     }
     if (c >= im.ncomp_needed)
         return;
-    const uint32_t by = idx / bw, bx = idx - by * bw;
+    const uint32_t by = by0 + idx / bw, bx = idx % bw;
     const uint32_t mx = bx / im.h[c], my = by / im.v[c];
     const uint32_t bim = im.blk_first[c] + (by - my * im.v[c]) * im.h[c] + (bx - mx * im.h[c]);
     const int16_t* src = bd.coef + im.coef_off + (size_t(my * im.mcus_x + mx) * im.bpm + bim) * 64;

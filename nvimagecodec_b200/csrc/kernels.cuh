@@ -46,6 +46,8 @@ struct ImageDev {
     uint32_t restart_interval;      // MCUs, 0 = none
     uint32_t n_rst_expected;
     uint32_t total_blocks;          // n_mcu * blocks_per_mcu
+    uint32_t write_blk_lo, write_blk_hi; // blocks (MCU decode order) of the MCU rows the requested ROI needs, incl. one row of context
+    uint16_t mcu_row_lo, mcu_row_hi;     // the same window as MCU rows
     uint32_t huff_set;
     uint32_t blk_comp;              // 2 bits per block-in-MCU: component
     uint32_t blk_tab;               // bit b: DC table id of block b, bit 16+b: AC table id
