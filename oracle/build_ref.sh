@@ -7,6 +7,7 @@
 #   oracle/_ref/libnvimgcodec.so   the unmodified nvImageCodec core (src/*.cpp, src/parsers, src/imgproc)
 #                                  -- the host framework that loads our extension in tests/
 #   oracle/_ref/host_driver        tests/host/host_driver.cpp linked against it (our own file)
+#   oracle/_ref/nvimtrans          example/nvimtrans/main.cpp, unmodified, + oracle/_ref/extensions/libnvbmp_ext.so (extensions/nvbmp)
 #   oracle/_ref/libref_turbo.so    the reference's CPU JPEG glue (extensions/libjpeg_turbo/jpeg_mem.cpp, jpeg_handle.cpp)
 #                                  + oracle/ref_turbo_shim.cpp, compiled against the reconstructed libjpeg62 ABI header
 #                                  (oracle/turbo_abi/) and linked to the libjpeg-turbo binary bundled with Pillow
@@ -59,6 +60,16 @@ if [ -f "$HERE/../tests/host/host_driver.cpp" ]; then
   g++ -std=c++17 -O2 -I"$GEN" -I"$REF/include" -I"$CUDA/include" "$HERE/../tests/host/host_driver.cpp" -o "$OUT/host_driver" \
       -L"$OUT" -lnvimgcodec -Wl,-rpath,'$ORIGIN' -Wl,--allow-shlib-undefined -L"$CUDA/lib64" -lcudart_static -ldl -lpthread -lrt
 fi
+# ---- the nvimtrans sample and the dependency-free nvbmp extension (its output encoder), both unmodified:
+#      the named drop-in consumer of SURVEY.md 8(f) n1
+mkdir -p "$OUT/extensions"
+for f in nvbmp_ext encoder decoder ext_module; do
+  g++ $CXXFLAGS $INC -I"$REF/extensions/nvbmp" -c "$REF/extensions/nvbmp/$f.cpp" -o "$OBJ/nvbmp_$f.bo"
+done
+g++ -shared -o "$OUT/extensions/libnvbmp_ext.so" "$OBJ"/nvbmp_*.bo -lpthread
+g++ -std=c++20 -O2 -w $INC -I"$REF/example/nvimtrans" "$REF/example/nvimtrans/main.cpp" -o "$OUT/nvimtrans" \
+    -L"$OUT" -lnvimgcodec -Wl,-rpath,'$ORIGIN' -Wl,--allow-shlib-undefined -L"$CUDA/lib64" -lcudart_static -ldl -lpthread -lrt
+
 # ---- the reference's own CPU JPEG path over the libjpeg-turbo binary that ships with Pillow
 TURBO_SO="$(python - <<'PY'
 import glob, os, sys

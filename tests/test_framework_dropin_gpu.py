@@ -83,3 +83,59 @@ def test_unsupported_streams_are_declined_not_crashed(tmp_path):
     assert status[1][0] != 1
     ref = oracle.decode(good, oracle.FMT_I_RGB, fancy=True)
     assert np.array_equal(raws[0], ref.reshape(-1)) and np.array_equal(raws[2], ref.reshape(-1))
+
+
+NVIMTRANS = os.path.join(ROOT, "oracle", "_ref", "nvimtrans")
+NVBMP = os.path.join(ROOT, "oracle", "_ref", "extensions", "libnvbmp_ext.so")
+
+
+def _read_bmp(path):
+    """24-bit uncompressed BMP -> HxWx3 RGB (what the reference's nvbmp encoder writes)."""
+    raw = open(path, "rb").read()
+    assert raw[:2] == b"BM"
+    off = int.from_bytes(raw[10:14], "little")
+    w = int.from_bytes(raw[18:22], "little", signed=True)
+    h = int.from_bytes(raw[22:26], "little", signed=True)
+    bpp = int.from_bytes(raw[28:30], "little")
+    assert bpp == 24
+    stride = (w * 3 + 3) // 4 * 4
+    rows = np.frombuffer(raw, dtype=np.uint8, count=stride * abs(h), offset=off).reshape(abs(h), stride)[:, :w * 3].reshape(abs(h), w, 3)
+    if h > 0:
+        rows = rows[::-1]
+    return rows[..., ::-1]
+
+
+@pytest.mark.skipif(not (os.path.exists(NVIMTRANS) and os.path.exists(NVBMP)), reason="nvimtrans not built (oracle/build_ref.sh)")
+def test_nvimtrans_sample_uses_the_extension(tmp_path):
+    """the reference's own CLI sample, unmodified, transcodes a directory of JPEGs
+    to BMP.  The only JPEG decoder in its extension directory is ours (found by codec priority through
+    NVIMGCODEC_EXTENSIONS_PATH); nvimtrans asks for planar RGB with ":fancy_upsampling=0"
+    (example/nvimtrans/main.cpp:275, 516)."""
+    import shutil
+
+    from nvimagecodec_b200 import corpus
+
+    ext = tmp_path / "extensions"
+    ext.mkdir()
+    shutil.copy(os.path.join(EXT_DIR, "libb200jpeg_ext.so"), ext / "libb200jpeg_ext.so")
+    shutil.copy(NVBMP, ext / "libnvbmp_ext.so")
+    src, dst = tmp_path / "in", tmp_path / "out"
+    src.mkdir()
+    dst.mkdir()
+    datas = {}
+    for i, (h, w, samp, rst) in enumerate([(240, 320, "420", 0), (199, 301, "444", 5), (128, 96, "422", 2), (375, 500, "420", 16)]):
+        datas[f"img{i}"] = corpus.encode(corpus.synth(h, w, 640 + i), 88, samp, rst)
+        (src / f"img{i}.jpg").write_bytes(datas[f"img{i}"])
+    env = dict(os.environ)
+    env["NVIMGCODEC_EXTENSIONS_PATH"] = str(ext)
+    env["LD_LIBRARY_PATH"] = os.path.dirname(NVIMTRANS) + ":" + env.get("LD_LIBRARY_PATH", "")
+    # One file per invocation: the sample's directory mode cannot work against this revision of the core
+    # (example/nvimtrans/main.cpp:689 passes a NULL status array, src/nvimgcodec_capi.cpp:950 rejects NULL),
+    # whichever decoder is installed.
+    for name, data in datas.items():
+        r = subprocess.run([NVIMTRANS, "-i", str(src / (name + ".jpg")), "-o", str(dst / (name + ".bmp"))],
+                           capture_output=True, text=True, env=env, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        got = _read_bmp(dst / (name + ".bmp"))
+        ref = oracle.decode(data, oracle.FMT_I_RGB, fancy=False)
+        assert np.array_equal(got, ref), name
