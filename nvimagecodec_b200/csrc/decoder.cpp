@@ -100,6 +100,10 @@ Options parse_options(const char* options, const char* decoder_id)
             o.fancy_upsampling = std::atoi(value.c_str()) != 0;
         else if (name == "debug_no_warm")
             o.debug_no_warm = std::atoi(value.c_str()) != 0;
+        else if (name == "chunk_mb")
+            o.chunk_mb = std::max(1, std::atoi(value.c_str()));
+        else if (name == "chunk_images")
+            o.chunk_images = std::max(1, std::atoi(value.c_str()));
         else if (name == "subseq_bits") {
             const int v = std::atoi(value.c_str());
             if (v == 1024 || v == 2048 || v == 4096)
@@ -807,7 +811,7 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         return B200JPEG_ERR_CUDA;
     last_launches_ = 0;
     last_resync_ = 0;
-    // chunk boundaries: about 24 MB of bitstream or 64 images, whichever comes first; small batches stay whole
+    // chunk boundaries: chunk_mb of bitstream or chunk_images images, whichever comes first; small batches stay whole
     std::vector<int> cuts{0};
     {
         size_t acc = 0;
@@ -815,11 +819,13 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         size_t total = 0;
         for (int i = 0; i < n; ++i)
             total += len[i];
-        const bool split = lanes_.size() > 1 && (total > (size_t(32) << 20) || n > 128);
+        const size_t chunk_bytes = size_t(opt_.chunk_mb) << 20;
+        const int chunk_images = opt_.chunk_images;
+        const bool split = lanes_.size() > 1 && (total > chunk_bytes + chunk_bytes / 3 || n > 2 * chunk_images);
         for (int i = 0; i < n; ++i) {
             acc += len[i];
             ++cnt;
-            if (split && (acc >= (size_t(24) << 20) || cnt >= 64) && i + 1 < n) {
+            if (split && (acc >= chunk_bytes || cnt >= chunk_images) && i + 1 < n) {
                 cuts.push_back(i + 1);
                 acc = 0;
                 cnt = 0;

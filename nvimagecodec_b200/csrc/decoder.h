@@ -40,6 +40,8 @@ struct Options {
     bool debug_no_warm = false;   // test hook: forces the re-synchronisation path
     int max_fix_rounds = 1 << 20;
     int subseq_bits = 0;          // 0 = choose per batch; else 1024 / 2048 / 4096
+    int chunk_mb = 24;            // pipeline chunk: this much bitstream ...
+    int chunk_images = 64;        // ... or this many images, whichever comes first
 };
 
 Options parse_options(const char* options, const char* decoder_id);

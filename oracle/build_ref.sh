@@ -8,6 +8,7 @@
 #                                  -- the host framework that loads our extension in tests/
 #   oracle/_ref/host_driver        tests/host/host_driver.cpp linked against it (our own file)
 #   oracle/_ref/nvimtrans          example/nvimtrans/main.cpp, unmodified, + oracle/_ref/extensions/libnvbmp_ext.so (extensions/nvbmp)
+#   oracle/_ref/extensions_nvjpeg/libnvjpeg_ext.so   extensions/nvjpeg (unmodified) over the toolkit's libnvjpeg: GPU comparison point
 #   oracle/_ref/libref_turbo.so    the reference's CPU JPEG glue (extensions/libjpeg_turbo/jpeg_mem.cpp, jpeg_handle.cpp)
 #                                  + oracle/ref_turbo_shim.cpp, compiled against the reconstructed libjpeg62 ABI header
 #                                  (oracle/turbo_abi/) and linked to the libjpeg-turbo binary bundled with Pillow
@@ -69,6 +70,19 @@ done
 g++ -shared -o "$OUT/extensions/libnvbmp_ext.so" "$OBJ"/nvbmp_*.bo -lpthread
 g++ -std=c++20 -O2 -w $INC -I"$REF/example/nvimtrans" "$REF/example/nvimtrans/main.cpp" -o "$OUT/nvimtrans" \
     -L"$OUT" -lnvimgcodec -Wl,-rpath,'$ORIGIN' -Wl,--allow-shlib-undefined -L"$CUDA/lib64" -lcudart_static -ldl -lpthread -lrt
+
+# ---- the reference's nvjpeg_ext (wrapper over the closed nvJPEG library of the CUDA toolkit), unmodified: the GPU
+#      comparison point of SURVEY.md 8(d).  Linked directly against libnvjpeg (no dlopen stubs: those need libclang).
+if [ -f "$CUDA/include/nvjpeg.h" ] && ls "$CUDA"/lib64/libnvjpeg.so* >/dev/null 2>&1; then
+  mkdir -p "$OUT/extensions_nvjpeg"
+  NVJ_DEFS="-DNVJPEG_LOSSLESS_SUPPORTED=0 -DNVJPEG_HW_ENCODER_SUPPORTED=0 -DCUDA_VERSION_MAJOR=12 -DCUDA_VERSION_MINOR=9"
+  for f in cuda_decoder hw_decoder cuda_encoder type_convert nvjpeg_ext nvjpeg_utils exception ext_module; do
+    g++ $CXXFLAGS $NVJ_DEFS $INC -I"$REF/extensions" -I"$REF/extensions/nvjpeg" -c "$REF/extensions/nvjpeg/$f.cpp" -o "$OBJ/nvjpeg_$f.jo" &
+  done
+  wait
+  g++ -shared -o "$OUT/extensions_nvjpeg/libnvjpeg_ext.so" "$OBJ"/nvjpeg_*.jo "$OBJ"/imgproc_*.o "$OBJ/dynlink_dynlink_cuda.o" \
+      -L"$CUDA/lib64" -L"$CUDA/lib64/stubs" -lnvjpeg -lcudart_static -lcuda -ldl -lpthread -lrt
+fi
 
 # ---- the reference's own CPU JPEG path over the libjpeg-turbo binary that ships with Pillow
 TURBO_SO="$(python - <<'PY'

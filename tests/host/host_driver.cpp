@@ -3,12 +3,16 @@
 // exactly as nvimgcodec.Decoder / nvimtrans would (include/nvimgcodec.h:1733, 1973, 2030).
 // Test infrastructure: reads a manifest, decodes the whole list as ONE batch, dumps raw pixels.
 //
-//   host_driver <extension dir> <manifest> <out dir> [decoder options]
+//   host_driver <extension dir> <manifest> <out dir> [decoder options] [repeat] [backend: any|gpu|hybrid|hw|cpu]
+//   repeat > 0: after the first (checked, dumped) decode, time `repeat` more decodes of the same batch
+//   through nvimgcodecDecoderDecode + future wait + device sync and print images/s (used to compare
+//   decoders -- ours vs the reference's nvjpeg_ext -- through the very same framework path).
 //   manifest line: <jpeg path> <I_RGB|I_BGR|P_RGB|P_BGR|I_Y> <y0> <x0> <y1> <x1> <device|host>
 //                  (all-zero ROI = whole image)
 #include <cuda_runtime_api.h>
 #include <nvimgcodec.h>
 
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -43,6 +47,8 @@ int main(int argc, char** argv)
     }
     const std::string ext_dir = argv[1], manifest = argv[2], out_dir = argv[3];
     const char* options = argc > 4 ? argv[4] : "";
+    const int repeat = argc > 5 ? std::atoi(argv[5]) : 0;
+    const std::string backend = argc > 6 ? argv[6] : "any";
     std::vector<Item> items;
     {
         std::ifstream f(manifest);
@@ -73,7 +79,17 @@ int main(int argc, char** argv)
 
     nvimgcodecExecutionParams_t ep{NVIMGCODEC_STRUCTURE_TYPE_EXECUTION_PARAMS, sizeof(nvimgcodecExecutionParams_t), nullptr};
     ep.device_id = 0;
-    ep.max_num_cpu_threads = 4;
+    ep.max_num_cpu_threads = repeat > 0 ? 0 : 4; // timing runs: all host cores, like the default executor
+    nvimgcodecBackend_t be{NVIMGCODEC_STRUCTURE_TYPE_BACKEND, sizeof(nvimgcodecBackend_t), nullptr};
+    be.params = {NVIMGCODEC_STRUCTURE_TYPE_BACKEND_PARAMS, sizeof(nvimgcodecBackendParams_t), nullptr, 1.0f, NVIMGCODEC_LOAD_HINT_POLICY_FIXED};
+    if (backend != "any") {
+        be.kind = backend == "gpu"      ? NVIMGCODEC_BACKEND_KIND_GPU_ONLY
+                  : backend == "hybrid" ? NVIMGCODEC_BACKEND_KIND_HYBRID_CPU_GPU
+                  : backend == "hw"     ? NVIMGCODEC_BACKEND_KIND_HW_GPU_ONLY
+                                        : NVIMGCODEC_BACKEND_KIND_CPU_ONLY;
+        ep.num_backends = 1;
+        ep.backends = &be;
+    }
     nvimgcodecDecoder_t decoder = nullptr;
     CHECK(nvimgcodecDecoderCreate(instance, &decoder, &ep, options));
 
@@ -149,6 +165,38 @@ int main(int argc, char** argv)
     CHECK(nvimgcodecFutureGetProcessingStatus(future, st.data(), &st_n));
     cudaStreamSynchronize(stream);
     cudaDeviceSynchronize();
+
+    if (repeat > 0) {
+        int ok = 0;
+        for (int i = 0; i < n; ++i)
+            ok += st[i] == NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        auto run_once = [&]() -> int {
+            nvimgcodecFuture_t f = nullptr;
+            if (nvimgcodecDecoderDecode(decoder, streams.data(), images.data(), n, &dp, &f) != NVIMGCODEC_STATUS_SUCCESS)
+                return 1;
+            nvimgcodecFutureWaitForAll(f);
+            nvimgcodecFutureDestroy(f);
+            cudaStreamSynchronize(stream);
+            return 0;
+        };
+        for (int w = 0; w < 2; ++w)
+            run_once();
+        cudaDeviceSynchronize();
+        const auto t0 = std::chrono::steady_clock::now();
+        for (int r = 0; r < repeat; ++r)
+            if (run_once())
+                return 3;
+        cudaDeviceSynchronize();
+        const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        double mpix = 0;
+        for (int i = 0; i < n; ++i)
+            mpix += double(items[i].w) * items[i].h / 1e6;
+        std::printf("BENCH images=%d ok=%d repeat=%d seconds=%.6f images_per_s=%.1f mpix_per_s=%.1f\n", n, ok, repeat, dt, n * repeat / dt,
+            mpix * repeat / dt);
+    }
 
     std::ofstream sf(out_dir + "/status.txt");
     for (int i = 0; i < n; ++i) {
