@@ -11,7 +11,7 @@ namespace b200jpeg {
 
 constexpr int kMaxComp = 4;
 constexpr int kMaxBlocksPerMcu = 10;
-constexpr int kLutBits = 12; // first-level Huffman lookup width
+constexpr int kLutBits = 11; // first-level Huffman lookup width
 
 enum StreamStatus { kStreamOk = 0, kStreamNotJpeg, kStreamUnsupported, kStreamCorrupt };
 
