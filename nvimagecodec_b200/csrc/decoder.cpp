@@ -194,7 +194,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     }
     const size_t sub_bytes = bd_.sub_bits / 8;
     size_t raw_bytes = 0, cmp_bytes = 0, coef_elems = 0, plane_bytes = 0, bounce_bytes = 0;
-    uint32_t n_tiles = 0, n_sub = 0, n_seq = 0, n_bnd = 0, n_idct = 0, n_color = 0;
+    uint32_t n_tiles = 0, n_sub = 0, n_seq = 0, n_wseq = 0, n_bnd = 0, n_idct = 0, n_color = 0;
     comp_bytes_ = n_coefs_ = out_bytes_ = 0;
 
     for (int i = 0; i < n; ++i) {
@@ -243,6 +243,9 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.seq_off = n_seq;
         im.n_seq = (im.n_sub_max + kSeqStride - 1) / kSeqStride;
         n_seq += im.n_seq;
+        im.wseq_off = n_wseq;
+        im.n_wseq = (im.n_sub_max + kSeqThreads - 1) / kSeqThreads;
+        n_wseq += im.n_wseq;
         const uint32_t n_mcu = uint32_t(hd.mcus_x) * uint32_t(hd.mcus_y);
         im.restart_interval = uint32_t(hd.restart_interval);
         im.n_rst_expected = hd.restart_interval ? (n_mcu + hd.restart_interval - 1) / hd.restart_interval - 1 : 0;
@@ -386,6 +389,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     off = align_up(off + 4ull * n_tiles, 256);
     const size_t off_seq = off;
     off = align_up(off + 4ull * n_seq, 256);
+    const size_t off_wseq = off;
+    off = align_up(off + 4ull * n_wseq, 256);
     const size_t off_idct = off;
     off = align_up(off + 4ull * n_idct, 256);
     const size_t off_color = off;
@@ -430,6 +435,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     uint8_t* up = upload_host_.as<uint8_t>();
     uint32_t* tile_img = reinterpret_cast<uint32_t*>(up + off_tile);
     uint32_t* seq_img = reinterpret_cast<uint32_t*>(up + off_seq);
+    uint32_t* wseq_img = reinterpret_cast<uint32_t*>(up + off_wseq);
     uint32_t* idct_img = reinterpret_cast<uint32_t*>(up + off_idct);
     uint32_t* color_img = reinterpret_cast<uint32_t*>(up + off_color);
     std::vector<uint8_t> direct(size_t(nd), 0); // source is pinned / registered host memory: copy without staging
@@ -440,6 +446,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             im.out = bounce_.as<uint8_t>() + host_outs_[d].bounce_off;
         std::fill(tile_img + im.tile_off, tile_img + im.tile_off + im.n_tiles, uint32_t(d));
         std::fill(seq_img + im.seq_off, seq_img + im.seq_off + im.n_seq, uint32_t(d));
+        std::fill(wseq_img + im.wseq_off, wseq_img + im.wseq_off + im.n_wseq, uint32_t(d));
         std::fill(idct_img + im.idct_cta_off, idct_img + im.idct_cta_off + im.n_idct_cta, uint32_t(d));
         std::fill(color_img + im.color_cta_off, color_img + im.color_cta_off + im.n_color_cta_x * im.n_color_cta_y, uint32_t(d));
         cudaPointerAttributes attr{};
@@ -497,6 +504,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.img = reinterpret_cast<const ImageDev*>(dv + off_img);
     bd_.tile_img = reinterpret_cast<const uint32_t*>(dv + off_tile);
     bd_.seq_img = reinterpret_cast<const uint32_t*>(dv + off_seq);
+    bd_.wseq_img = reinterpret_cast<const uint32_t*>(dv + off_wseq);
     bd_.idct_cta_img = reinterpret_cast<const uint32_t*>(dv + off_idct);
     bd_.color_cta_img = reinterpret_cast<const uint32_t*>(dv + off_color);
     bd_.huff = reinterpret_cast<const HuffSetDev*>(dv + off_huff);
@@ -516,6 +524,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.planes = planes_.as<uint8_t>();
     bd_.n_tiles = int(n_tiles);
     bd_.n_seq = int(n_seq);
+    bd_.n_wseq = int(n_wseq);
     bd_.n_sub = int(n_sub);
     bd_.n_idct_cta = int(n_idct);
     bd_.n_color_cta = int(n_color);

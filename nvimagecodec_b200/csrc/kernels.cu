@@ -571,12 +571,12 @@ __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageD
 // fix mode (images K2 found dirty): the first thread takes the stored exit state of the previous
 // sequence as entry state and only the fixed-point rounds run.
 struct SyncShared {
-    uint32_t in[kSeqThreads];
-    uint32_t out[kSeqThreads];
-    int4 info[kSeqThreads];
-    uint32_t queue[kSeqThreads];
-    uint8_t fresh[kSeqThreads]; // (re)computed by this CTA -> has to be written back
-    uint32_t count;
+    uint32_t in[kSeqLogical];
+    uint32_t out[kSeqLogical];
+    int4 info[kSeqLogical];
+    uint32_t queue[2][kSeqLogical]; // work lists of the current and the next fixed-point round
+    uint8_t fresh[kSeqLogical];     // (re)computed by this CTA -> has to be written back
+    uint32_t count[2];
 };
 
 __device__ __forceinline__ int4 pack_info(const DecodeResult& r)
@@ -584,6 +584,10 @@ __device__ __forceinline__ int4 pack_info(const DecodeResult& r)
     return make_int4(r.blk | (r.restarted ? int32_t(0x80000000u) : 0), r.dc0, r.dc1, r.dc2);
 }
 
+// A CTA of kSeqThreads threads owns kSeqLogical = kSeqMult * kSeqThreads consecutive subsequences
+// ("logical threads" l = m * kSeqThreads + t): the full pass runs kSeqMult times back to back, and the
+// repair rounds batch the work of the whole range, so they run with (nearly) full warps instead of
+// idling most of the CTA at the round barriers.
 __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int mode)
 {
     extern __shared__ uint4 s_raw[];
@@ -606,87 +610,96 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     build_block_table(s_bt, im);
     const StreamView sv = make_view(bd, im, st);
     const int t = threadIdx.x;
-    const int k0 = int(first_k) - kSeqWarm; // subsequence of thread 0 (may be negative)
-    const int k = k0 + t;
+    const int k0 = int(first_k) - kSeqWarm; // subsequence of logical thread 0 (may be negative)
     const bool skip_warm = fix_mode || no_warm;
-    const bool active = k >= 0 && k < int(st.n_sub) && (!skip_warm || t >= kSeqWarm);
-    const bool has_pred = active && t > 0 && k > 0 && (!skip_warm || t > kSeqWarm);
-    const uint32_t g = im.sub_off + uint32_t(k);
+    auto is_active = [&](int l) { return k0 + l >= 0 && k0 + l < int(st.n_sub) && (!skip_warm || l >= kSeqWarm); };
+    auto has_pred = [&](int l) { return is_active(l) && l > 0 && k0 + l > 0 && (!skip_warm || l > kSeqWarm); };
     if (t == 0)
-        sh.count = 0;
-    sh.fresh[t] = 0;
+        sh.count[0] = sh.count[1] = 0;
+    for (int l = t; l < kSeqLogical; l += kSeqThreads)
+        sh.fresh[l] = 0;
     __syncthreads(); // tables loaded, counters cleared
     DecodeResult res;
     if (fix_mode) {
-        uint32_t in = 0;
-        sh.out[t] = active ? bd.sub_out[g] : kStateDone;
-        if (active) {
-            in = bd.sub_in[g];
-            if (t == kSeqWarm) {
-                const uint32_t want = (k > 0) ? bd.sub_out[g - 1] : 0u;
-                if (want != in) {
-                    in = want;
-                    sh.fresh[t] = 1;
-                    sh.queue[atomicAdd(&sh.count, 1u)] = uint32_t(t);
+        for (int l = t; l < kSeqLogical; l += kSeqThreads) {
+            const bool active = is_active(l);
+            const uint32_t g = im.sub_off + uint32_t(k0 + l);
+            uint32_t in = 0;
+            sh.out[l] = active ? bd.sub_out[g] : kStateDone;
+            if (active) {
+                in = bd.sub_in[g];
+                if (l == kSeqWarm) {
+                    const uint32_t want = (k0 + l > 0) ? bd.sub_out[g - 1] : 0u;
+                    if (want != in) {
+                        in = want;
+                        sh.fresh[l] = 1;
+                        sh.queue[0][atomicAdd(&sh.count[0], 1u)] = uint32_t(l);
+                    }
                 }
             }
+            sh.in[l] = in;
         }
-        sh.in[t] = in;
     } else {
-        uint32_t in = 0; // k == 0: the true start state; otherwise the bare guess
-        if (active && k > 0 && !no_warm) {
-            // round 0: probe the tail of the previous subsequence
-            const uint32_t pb = uint32_t(k) * S - S / 4;
-            decode_subsequence<false>(sv, s_hs, s_bt, pb, uint32_t(k) * S, 0u, 0, 0, 0, 0, nullptr, nullptr, res);
-            in = res.state;
+        for (int l = t; l < kSeqLogical; l += kSeqThreads) {
+            const bool active = is_active(l);
+            const int k = k0 + l;
+            uint32_t in = 0; // k == 0: the true start state; otherwise the bare guess
+            if (active && k > 0 && !no_warm) {
+                // round 0: probe the tail of the previous subsequence
+                const uint32_t pb = uint32_t(k) * S - S / 4;
+                decode_subsequence<false>(sv, s_hs, s_bt, pb, uint32_t(k) * S, 0u, 0, 0, 0, 0, nullptr, nullptr, res);
+                in = res.state;
+            }
+            // round 1: everybody
+            res.state = kStateDone;
+            if (active) {
+                decode_subsequence<false>(sv, s_hs, s_bt, uint32_t(k) * S, uint32_t(k + 1) * S, in, 0, 0, 0, 0, nullptr, nullptr, res);
+                sh.info[l] = pack_info(res);
+                sh.fresh[l] = 1;
+            }
+            sh.in[l] = in;
+            sh.out[l] = res.state;
         }
-        // round 1: everybody
-        res.state = kStateDone;
-        if (active) {
-            decode_subsequence<false>(sv, s_hs, s_bt, uint32_t(k) * S, uint32_t(k + 1) * S, in, 0, 0, 0, 0, nullptr, nullptr, res);
-            sh.info[t] = pack_info(res);
-            sh.fresh[t] = 1;
-        }
-        sh.in[t] = in;
-        sh.out[t] = res.state;
         __syncthreads();
-        if (has_pred && sh.out[t - 1] != in) {
-            sh.in[t] = sh.out[t - 1];
-            sh.queue[atomicAdd(&sh.count, 1u)] = uint32_t(t);
+        for (int l = t; l < kSeqLogical; l += kSeqThreads) {
+            if (has_pred(l) && sh.out[l - 1] != sh.in[l]) {
+                sh.in[l] = sh.out[l - 1];
+                sh.queue[0][atomicAdd(&sh.count[0], 1u)] = uint32_t(l);
+            }
         }
     }
-    // fixed-point rounds over the compacted work list.  Invariant: in[t] == out[t-1] for every t,
-    // and out[t] == decode(in[t]) for every t that is not queued.
+    // fixed-point rounds over the compacted work list.  Invariant: in[l] == out[l-1] for every l,
+    // and out[l] == decode(in[l]) for every l that is not queued.
     uint32_t dbg_rounds = 0, dbg_items = 0;
-    for (;;) {
+    for (uint32_t cur = 0;; cur ^= 1u) {
         __syncthreads();
-        const uint32_t n = sh.count;
+        const uint32_t n = sh.count[cur];
         if (n == 0u)
             break;
         ++dbg_rounds;
         dbg_items += n;
-        uint32_t item = 0;
-        if (uint32_t(t) < n) {
-            item = sh.queue[t];
+        for (uint32_t i = uint32_t(t); i < n; i += kSeqThreads) {
+            const uint32_t item = sh.queue[cur][i];
             const uint32_t kk = uint32_t(k0 + int(item));
             decode_subsequence<false>(sv, s_hs, s_bt, kk * S, (kk + 1) * S, sh.in[item], 0, 0, 0, 0, nullptr, nullptr, res);
-        }
-        __syncthreads(); // everyone has read count and queue
-        if (t == 0)
-            sh.count = 0;
-        if (uint32_t(t) < n) {
-            sh.out[item] = res.state;
+            sh.out[item] = res.state; // nobody reads out[] before the barrier below
             sh.info[item] = pack_info(res);
         }
+        if (t == 0)
+            sh.count[cur ^ 1u] = 0; // the other list was drained in the previous round
         __syncthreads();
-        if (uint32_t(t) < n) {
+        for (uint32_t i = uint32_t(t); i < n; i += kSeqThreads) {
+            const uint32_t item = sh.queue[cur][i];
             const uint32_t succ = item + 1;
-            if (succ < uint32_t(kSeqThreads) && k0 + int(succ) < int(st.n_sub) && sh.in[succ] != res.state) {
-                sh.in[succ] = res.state;
+            const uint32_t state = sh.out[item];
+            if (succ < uint32_t(kSeqLogical) && k0 + int(succ) < int(st.n_sub) && sh.in[succ] != state) {
+                sh.in[succ] = state;
                 sh.fresh[succ] = 1;
-                sh.queue[atomicAdd(&sh.count, 1u)] = succ;
+                sh.queue[cur ^ 1u][atomicAdd(&sh.count[cur ^ 1u], 1u)] = succ;
             }
         }
+        if (t == 0)
+            sh.count[cur] = 0;
     }
     if (t == 0 && bd.sync_stats) { // [0] CTAs, [1] repair rounds, [2] repaired subsequences, [3] max rounds in one CTA
         atomicAdd(bd.sync_stats + 0, 1u);
@@ -695,10 +708,13 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
         atomicMax(bd.sync_stats + 3, dbg_rounds);
     }
     // results of the real (non warm-up) subsequences
-    if (active && t >= kSeqWarm && sh.fresh[t]) {
-        bd.sub_in[g] = sh.in[t];
-        bd.sub_out[g] = sh.out[t];
-        bd.sub_info[g] = sh.info[t];
+    for (int l = t; l < kSeqLogical; l += kSeqThreads) {
+        if (is_active(l) && l >= kSeqWarm && sh.fresh[l]) {
+            const uint32_t g = im.sub_off + uint32_t(k0 + l);
+            bd.sub_in[g] = sh.in[l];
+            bd.sub_out[g] = sh.out[l];
+            bd.sub_info[g] = sh.info[l];
+        }
     }
 }
 
@@ -803,21 +819,20 @@ __global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, in
     extern __shared__ uint4 s_raw[];
     HuffSetDev* s_hs = reinterpret_cast<HuffSetDev*>(s_raw);
     BlockTable* s_bt = reinterpret_cast<BlockTable*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev));
-    const uint32_t seq = blockIdx.x;
-    const uint32_t img = bd.seq_img[seq];
+    const uint32_t cta = blockIdx.x;
+    const uint32_t img = bd.wseq_img[cta];
     const ImageDev& im = bd.img[img];
     const ImageState st = bd.state[img];
     if (st.n_sub == 0u || (st.flags & kFlagDirty) || (redo_only && !(st.flags & kFlagRedo)))
         return;
-    const uint32_t first_k = (seq - im.seq_off) * kSeqStride;
+    const uint32_t first_k = (cta - im.wseq_off) * kSeqThreads;
     if (first_k >= st.n_sub)
         return;
     load_huff_set(s_hs, bd.huff + im.huff_set);
     build_block_table(s_bt, im);
     __syncthreads();
-    const int t = threadIdx.x;
-    const uint32_t k = first_k + uint32_t(t) - kSeqWarm;
-    if (t < kSeqWarm || k >= st.n_sub)
+    const uint32_t k = first_k + threadIdx.x;
+    if (k >= st.n_sub)
         return;
     const StreamView sv = make_view(bd, im, st);
     const uint32_t g = im.sub_off + k;
@@ -1362,9 +1377,9 @@ int launch_verify_scan(const BatchDev& b, bool fix_mode, cudaStream_t s)
 
 int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s)
 {
-    if (b.n_seq == 0)
+    if (b.n_wseq == 0)
         return 0;
-    huff_write_kernel<<<b.n_seq, kSeqThreads, kWriteSmem, s>>>(b, redo_only ? 1 : 0);
+    huff_write_kernel<<<b.n_wseq, kSeqThreads, kWriteSmem, s>>>(b, redo_only ? 1 : 0);
     return 1;
 }
 

@@ -15,9 +15,11 @@ constexpr int kScanChunks = 4;        //     16 KiB per CTA
 constexpr int kScanTileBytes = kScanThreads * 16 * kScanChunks;
 constexpr int kMinSubseqBits = 1024;  // K1-K3: bits of unstuffed stream per thread ("subsequence"); the host picks
 constexpr int kMaxSubseqBits = 4096;  //   1024, 2048 or 4096 per batch (BatchDev::sub_bits) so the GPU stays filled
-constexpr int kSeqThreads = 256;      // threads per CTA ("sequence")
-constexpr int kSeqWarm = 8;           // leading threads that only warm up the entry state
-constexpr int kSeqStride = kSeqThreads - kSeqWarm;
+constexpr int kSeqThreads = 256;      // threads per CTA of the entropy kernels
+constexpr int kSeqMult = 1;           // K1: subsequences per thread ...
+constexpr int kSeqLogical = kSeqThreads * kSeqMult; // ... i.e. per CTA ("sequence"), of which the
+constexpr int kSeqWarm = 8;           // leading ones only warm up the entry state
+constexpr int kSeqStride = kSeqLogical - kSeqWarm;
 
 // ---- per-image error / state flags (ImageState::flags)
 enum : uint32_t {
@@ -41,7 +43,8 @@ struct ImageDev {
     uint32_t raw_len;
     uint32_t tile_off, n_tiles;     // K0 tiles
     uint32_t sub_off, n_sub_max;    // subsequences (upper bound from the stuffed length)
-    uint32_t seq_off, n_seq;        // sequences (CTAs of the entropy kernels)
+    uint32_t seq_off, n_seq;        // sequences (CTAs of K1)
+    uint32_t wseq_off, n_wseq;      // CTAs of K3 (kSeqThreads subsequences each)
     uint32_t bnd_off, n_bnd_cap;    // restart boundaries (+ end of stream)
     uint32_t restart_interval;      // MCUs, 0 = none
     uint32_t n_rst_expected;
@@ -91,6 +94,7 @@ struct BatchDev {
     const uint32_t* tile_img; // tile -> image
     uint32_t* bnd;          // restart boundaries (unstuffed byte positions) then end of stream
     const uint32_t* seq_img;  // sequence -> image
+    const uint32_t* wseq_img; // K3 CTA -> image
     uint32_t* sub_in;       // entry state per subsequence
     uint32_t* sub_out;      // exit state per subsequence
     int4* sub_info;         // x = block delta (or absolute | 1<<31 after a restart), yzw = DC diff sums
@@ -101,7 +105,7 @@ struct BatchDev {
     uint8_t* planes;
     const uint32_t* idct_cta_img;
     const uint32_t* color_cta_img;
-    int n_tiles, n_seq, n_sub, n_idct_cta, n_color_cta;
+    int n_tiles, n_seq, n_wseq, n_sub, n_idct_cta, n_color_cta;
     uint32_t* sync_stats;   // optional K1 counters (4 x uint32), may be null
     uint32_t sub_bits;      // subsequence length in bits for this batch
 };
