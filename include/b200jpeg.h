@@ -161,6 +161,22 @@ B200JPEG_API int b200jpegScanSegmentNoAlloc(const void* dev_raw, size_t length, 
     uint32_t* dev_out_boundaries, uint32_t boundary_capacity, b200jpegScanResult_t* dev_result, void* cuda_stream, char* message,
     size_t message_capacity);
 
+/* One batch across several GPUs of one box.  Images are independent, so there is no
+ * collective: the host partitions the batch by compressed byte count (greedy longest-processing-time,
+ * deterministic), and every device decodes its share from its own pinned staging on its own stream,
+ * driven by its own host thread.  The reference has no multi-GPU notion (one decoder == one
+ * exec_params.device_id, include/nvimgcodec.h:1101); this is the thin driver above the decoder that
+ * its users would otherwise write themselves.
+ *   Plan        : device_of_image[i] = index (into device_ids) of the device that will decode image i
+ *   DecodeBatch : outputs[i].buffer must be host memory (buffer_is_host = 1) or device memory on the
+ *                 planned device of image i; returns when every device has finished. */
+typedef struct b200jpegMultiDecoder_st* b200jpegMultiDecoder_t;
+B200JPEG_API int b200jpegMultiCreate(b200jpegMultiDecoder_t* multi, const int* device_ids, int num_devices, const char* options);
+B200JPEG_API int b200jpegMultiDestroy(b200jpegMultiDecoder_t multi);
+B200JPEG_API int b200jpegMultiPlan(b200jpegMultiDecoder_t multi, int batch_size, const size_t* lengths, int* device_of_image);
+B200JPEG_API int b200jpegMultiDecodeBatch(b200jpegMultiDecoder_t multi, int batch_size, const void* const* data, const size_t* lengths,
+    const b200jpegOutput_t* outputs, const int* device_of_image, int* status);
+
 /* Introspection for benchmarks and tests. */
 enum {
     B200JPEG_STAT_KERNEL_LAUNCHES = 0, /* kernels launched by the last Execute */

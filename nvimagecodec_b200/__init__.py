@@ -5,11 +5,11 @@ a ctypes loader and the Python mirror of the reference's decoder object.
 """
 from . import _lib  # noqa: F401
 
-__all__ = ["Decoder", "DecodeError"]
+__all__ = ["Decoder", "MultiGpuDecoder", "DecodeError"]
 
 
 def __getattr__(name):
-    if name in ("Decoder", "DecodeError"):
+    if name in ("Decoder", "MultiGpuDecoder", "DecodeError"):
         from . import decoder
 
         return getattr(decoder, name)

@@ -41,7 +41,7 @@ class Output(ctypes.Structure):
 EXPORTS = ["b200jpegProbe", "b200jpegCreate", "b200jpegDestroy", "b200jpegDecodeBatch", "b200jpegPrepareBatch",
            "b200jpegExecuteBatch", "b200jpegFinishBatch", "b200jpegGetStat", "b200jpegSetProfiling", "b200jpegGetStageTimes",
            "b200jpegDebugCopyCoefficients", "b200jpegGetLastError", "b200jpegVersion", "b200jpegScanSegment",
-           "b200jpegScanSegmentNoAlloc"]
+           "b200jpegScanSegmentNoAlloc", "b200jpegMultiCreate", "b200jpegMultiDestroy", "b200jpegMultiPlan", "b200jpegMultiDecodeBatch"]
 
 _lib = None
 
@@ -83,6 +83,15 @@ def load():
     L.b200jpegScanSegment.restype = ci
     L.b200jpegScanSegmentNoAlloc.argtypes = [vp, sz, ctypes.c_uint32, vp, vp, ctypes.c_uint32, vp, vp, ctypes.c_char_p, sz]
     L.b200jpegScanSegmentNoAlloc.restype = ci
+    L.b200jpegMultiCreate.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(ci), ci, ctypes.c_char_p]
+    L.b200jpegMultiCreate.restype = ci
+    L.b200jpegMultiDestroy.argtypes = [vp]
+    L.b200jpegMultiDestroy.restype = ci
+    L.b200jpegMultiPlan.argtypes = [vp, ci, ctypes.POINTER(sz), ctypes.POINTER(ci)]
+    L.b200jpegMultiPlan.restype = ci
+    L.b200jpegMultiDecodeBatch.argtypes = [vp, ci, ctypes.POINTER(vp), ctypes.POINTER(sz), ctypes.POINTER(Output), ctypes.POINTER(ci),
+                                           ctypes.POINTER(ci)]
+    L.b200jpegMultiDecodeBatch.restype = ci
     L.b200jpegGetLastError.argtypes = [vp]
     L.b200jpegGetLastError.restype = ctypes.c_char_p
     L.b200jpegVersion.argtypes = []

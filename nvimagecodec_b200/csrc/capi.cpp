@@ -1,6 +1,11 @@
 // extern "C" surface declared in include/b200jpeg.h.
+#include <algorithm>
 #include <cstring>
+#include <memory>
 #include <new>
+#include <queue>
+#include <thread>
+#include <vector>
 
 #include "b200jpeg.h"
 #include "decoder.h"
@@ -158,6 +163,123 @@ int b200jpegScanSegment(b200jpegDecoder_t decoder, const void* dev_raw, size_t l
     } catch (...) {
         return B200JPEG_ERR_STATE;
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// multi-GPU driver: LPT partition by compressed bytes, one pipeline + stream + host thread per device
+// ------------------------------------------------------------------------------------------------
+struct b200jpegMultiDecoder_st {
+    std::vector<int> devices;
+    std::vector<std::unique_ptr<Pipeline>> pipes;
+    std::vector<cudaStream_t> streams;
+};
+
+int b200jpegMultiCreate(b200jpegMultiDecoder_t* multi, const int* device_ids, int num_devices, const char* options)
+{
+    if (!multi || !device_ids || num_devices <= 0)
+        return B200JPEG_ERR_ARG;
+    *multi = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        return B200JPEG_ERR_CUDA;
+    }
+    auto m = std::make_unique<b200jpegMultiDecoder_st>();
+    const b200jpeg::Options opt = b200jpeg::parse_options(options, kDecoderId);
+    for (int i = 0; i < num_devices; ++i) {
+        if (device_ids[i] < 0 || device_ids[i] >= count)
+            return B200JPEG_ERR_ARG;
+        m->devices.push_back(device_ids[i]);
+        m->pipes.push_back(std::make_unique<Pipeline>(device_ids[i], opt));
+        cudaStream_t s = nullptr;
+        if (cudaSetDevice(device_ids[i]) != cudaSuccess || cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess)
+            return B200JPEG_ERR_CUDA;
+        m->streams.push_back(s);
+    }
+    *multi = m.release();
+    return B200JPEG_OK;
+}
+
+int b200jpegMultiDestroy(b200jpegMultiDecoder_t multi)
+{
+    if (!multi)
+        return B200JPEG_OK;
+    for (size_t i = 0; i < multi->streams.size(); ++i) {
+        cudaSetDevice(multi->devices[i]);
+        cudaStreamDestroy(multi->streams[i]);
+    }
+    delete multi;
+    return B200JPEG_OK;
+}
+
+int b200jpegMultiPlan(b200jpegMultiDecoder_t multi, int batch_size, const size_t* lengths, int* device_of_image)
+{
+    if (!multi || batch_size < 0 || (batch_size > 0 && (!lengths || !device_of_image)))
+        return B200JPEG_ERR_ARG;
+    // longest-processing-time first: biggest stream to the least loaded device; ties by index -> deterministic
+    std::vector<int> order(static_cast<size_t>(batch_size));
+    for (int i = 0; i < batch_size; ++i)
+        order[size_t(i)] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return lengths[a] > lengths[b]; });
+    using Load = std::pair<uint64_t, int>;
+    std::priority_queue<Load, std::vector<Load>, std::greater<Load>> heap;
+    for (int d = 0; d < int(multi->devices.size()); ++d)
+        heap.push({0, d});
+    for (int i : order) {
+        Load l = heap.top();
+        heap.pop();
+        device_of_image[i] = l.second;
+        heap.push({l.first + lengths[i], l.second});
+    }
+    return B200JPEG_OK;
+}
+
+int b200jpegMultiDecodeBatch(b200jpegMultiDecoder_t multi, int batch_size, const void* const* data, const size_t* lengths,
+    const b200jpegOutput_t* outputs, const int* device_of_image, int* status)
+{
+    if (!multi || batch_size < 0 || (batch_size > 0 && (!data || !lengths || !outputs || !device_of_image)))
+        return B200JPEG_ERR_ARG;
+    const int nd = int(multi->devices.size());
+    std::vector<std::vector<int>> share(static_cast<size_t>(nd));
+    for (int i = 0; i < batch_size; ++i) {
+        if (device_of_image[i] < 0 || device_of_image[i] >= nd)
+            return B200JPEG_ERR_ARG;
+        share[size_t(device_of_image[i])].push_back(i);
+    }
+    std::vector<int> rc(static_cast<size_t>(nd), B200JPEG_OK);
+    auto work = [&](int d) {
+        const std::vector<int>& idx = share[size_t(d)];
+        const int n = int(idx.size());
+        if (n == 0)
+            return;
+        std::vector<const void*> dd(static_cast<size_t>(n));
+        std::vector<size_t> ll(static_cast<size_t>(n));
+        std::vector<b200jpegOutput_t> oo(static_cast<size_t>(n));
+        std::vector<int> st(static_cast<size_t>(n), B200JPEG_ERR_STATE);
+        for (int j = 0; j < n; ++j) {
+            dd[size_t(j)] = data[idx[size_t(j)]];
+            ll[size_t(j)] = lengths[idx[size_t(j)]];
+            oo[size_t(j)] = outputs[idx[size_t(j)]];
+        }
+        try {
+            rc[size_t(d)] = multi->pipes[size_t(d)]->decode(n, dd.data(), ll.data(), oo.data(), st.data(), multi->streams[size_t(d)]);
+        } catch (...) {
+            rc[size_t(d)] = B200JPEG_ERR_STATE;
+        }
+        if (status)
+            for (int j = 0; j < n; ++j)
+                status[idx[size_t(j)]] = st[size_t(j)];
+    };
+    std::vector<std::thread> threads;
+    for (int d = 1; d < nd; ++d)
+        threads.emplace_back(work, d);
+    work(0);
+    for (auto& t : threads)
+        t.join();
+    for (int d = 0; d < nd; ++d)
+        if (rc[size_t(d)] != B200JPEG_OK)
+            return rc[size_t(d)];
+    return B200JPEG_OK;
 }
 
 int64_t b200jpegGetStat(b200jpegDecoder_t decoder, int which)

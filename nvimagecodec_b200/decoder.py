@@ -190,3 +190,67 @@ class Decoder:
         out = np.empty(n_elems, dtype=np.int16)
         self._check(self._L.b200jpegDebugCopyCoefficients(self._h, index, ctypes.c_void_p(out.ctypes.data), out.size), "coefficients")
         return out
+
+
+class MultiGpuDecoder:
+    """One batch across several GPUs of one box: LPT partition by compressed bytes, one pipeline, stream and
+    host thread per device, no collective (b200jpegMulti* in include/b200jpeg.h)."""
+
+    def __init__(self, device_ids, options=":fancy_upsampling=0"):
+        self._L = _lib.load()
+        if not torch.cuda.is_available():
+            raise DecodeError("nvimagecodec_b200 needs a CUDA device (there is no CPU fallback)")
+        self.device_ids = [int(d) for d in device_ids]
+        ids = (ctypes.c_int * len(self.device_ids))(*self.device_ids)
+        h = ctypes.c_void_p()
+        rc = self._L.b200jpegMultiCreate(ctypes.byref(h), ids, len(self.device_ids), (options or "").encode())
+        if rc != _lib.OK:
+            raise DecodeError(f"b200jpegMultiCreate failed: {_lib.STATUS_NAMES[rc]}")
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.b200jpegMultiDestroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def plan(self, srcs):
+        arrs = [_as_u8(s) for s in srcs]
+        n = len(arrs)
+        lens = (ctypes.c_size_t * max(n, 1))(*[a.size for a in arrs])
+        dev = (ctypes.c_int * max(n, 1))()
+        rc = self._L.b200jpegMultiPlan(self._h, n, lens, dev)
+        if rc != _lib.OK:
+            raise DecodeError(f"b200jpegMultiPlan failed: {_lib.STATUS_NAMES[rc]}")
+        return arrs, lens, dev
+
+    def decode(self, srcs, fmt="I_RGB"):
+        """Returns (images, statuses, device index per image); every image lives on the device that decoded it."""
+        arrs, lens, dev = self.plan(srcs)
+        n = len(arrs)
+        ptrs = (ctypes.c_void_p * max(n, 1))(*[a.ctypes.data for a in arrs])
+        outs = (_lib.Output * max(n, 1))()
+        status = (ctypes.c_int * max(n, 1))()
+        images = []
+        for i, a in enumerate(arrs):
+            info = _lib.StreamInfo()
+            self._L.b200jpegProbe(ctypes.c_void_p(a.ctypes.data), a.size, ctypes.byref(info))
+            shape = (info.height, info.width, 3) if fmt in ("I_RGB", "I_BGR") else ((3, info.height, info.width) if fmt.startswith("P_R") or fmt.startswith("P_B") else (info.height, info.width))
+            t = torch.empty(shape if info.supported else (1,), dtype=torch.uint8, device=torch.device("cuda", self.device_ids[dev[i]]))
+            images.append(t)
+            outs[i].buffer = t.data_ptr()
+            outs[i].format = _lib.FMT[fmt]
+            outs[i].buffer_is_host = 0
+            outs[i].row_stride = 0
+        for d in set(self.device_ids):
+            torch.cuda.synchronize(d)  # the outputs were allocated on torch's streams
+        rc = self._L.b200jpegMultiDecodeBatch(self._h, n, ptrs, lens, outs, dev, status)
+        if rc != _lib.OK:
+            raise DecodeError(f"b200jpegMultiDecodeBatch failed: {_lib.STATUS_NAMES[rc]}")
+        st = [status[i] for i in range(n)]
+        return [im if s == _lib.OK else None for im, s in zip(images, st)], st, [dev[i] for i in range(n)]
