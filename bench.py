@@ -349,9 +349,19 @@ def main():
         stage_list = [{"kernel": k, "ms": round(v, 4), "share": round(v / max(sum(stages.values()), 1e-9), 4),
                        "algo_gbs": round(kbytes.get(k, 0) / (v * 1e-3) / 1e9, 1) if v > 0 else None} for k, v in stages.items()]
         roofline = None
+        # DRAM bytes per launch of each kernel from the committed `ncu --set full` capture of this workload
+        traffic = {}
+        try:
+            with open(os.path.join(ROOT, "profiles", "r1f_dram_traffic.json")) as f:
+                traffic = {k.replace("_kernel", ""): v["dram_bytes"] for k, v in json.load(f)["kernels"].items()}
+        except Exception:
+            pass
+        ncu_name = {"scan(K0)": "scan_scatter", "huff_sync(K1)": "huff_sync", "verify_scan(K2)": "verify_scan", "huff_write(K3)": "huff_write",
+                    "idct(K4a)": "idct", "color(K4b)": "color"}
         if top:
             ach = kbytes[top] / (stages[top] * 1e-3) / 1e9
-            roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+            roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                        "traffic": traffic.get(ncu_name.get(top, "")) if args.workload == "c2" and n_img == 256 else None,
                         "peak_source": peak_src,
                         "note": "dominant kernel by CUDA-event time; the entropy kernels are issue-bound, see profiles/ for warp-issue efficiency"}
         step_s = ms_dev / args.steps * 1e-3
