@@ -1357,11 +1357,14 @@ int launch_sync(const BatchDev& b, bool fix_mode, bool no_warm, cudaStream_t s)
 {
     if (b.n_seq == 0)
         return 0;
-    static bool attr_set = false;
-    if (!attr_set) {
+    // dynamic shared memory opt-in is per device
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
         cudaFuncSetAttribute(huff_sync_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSyncSmem));
         cudaFuncSetAttribute(huff_write_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kWriteSmem));
-        attr_set = true;
+        attr_set[dev] = true;
     }
     huff_sync_kernel<<<b.n_seq, kSeqThreads, kSyncSmem, s>>>(b, (fix_mode ? 1 : 0) | (no_warm ? 2 : 0));
     return 1;

@@ -254,3 +254,44 @@ def test_full_size_properties_c2_shape(dec_plain, dec_fancy):
     assert np.array_equal(f, oracle.decode(srcs[0], oracle.FMT_I_RGB, fancy=True))
     algo = dec_plain.stat(_lib.STAT_ALGO_BYTES)
     assert algo > 0
+
+
+def test_concurrent_decoders_equal_sequential(decoder_cls):
+    """Several decoders driven from several host threads at once (one decoder per thread, like the reference's
+    test/python/test_decode_concurrent.py) must reproduce the sequential result byte for byte
+    (test/api/concurrent_decode_test.cpp demands the same of the reference's decoders)."""
+    import threading
+
+    import torch
+    from nvimagecodec_b200 import _lib, corpus
+
+    sets = []
+    for s in range(4):
+        sets.append([corpus.encode(corpus.synth(150 + 40 * s + 7 * i, 210 + 13 * i, 2000 + 10 * s + i), 70 + 5 * s,
+                                   ["420", "444", "422"][(s + i) % 3], (s + i) % 6) for i in range(10)])
+    seq = decoder_cls(0, options=":fancy_upsampling=1")
+    want = [[o.cpu().numpy().copy() for o in seq.decode(srcs, "I_RGB")] for srcs in sets]
+    seq.close()
+    results, errors = [None] * len(sets), []
+
+    def work(j):
+        try:
+            with torch.cuda.stream(torch.cuda.Stream()):
+                dec = decoder_cls(0, options=":fancy_upsampling=1")
+                for _ in range(3):
+                    outs = dec.decode(sets[j], "I_RGB")
+                    assert dec.last_status == [_lib.OK] * len(sets[j])
+                results[j] = [o.cpu().numpy() for o in outs]
+                dec.close()
+        except Exception as e:  # surfaced below: an assert in a thread would otherwise vanish
+            errors.append(e)
+
+    threads = [threading.Thread(target=work, args=(j,)) for j in range(len(sets))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for got, ref in zip(results, want):
+        for a, b in zip(got, ref):
+            assert np.array_equal(a, b)
