@@ -295,3 +295,43 @@ def test_concurrent_decoders_equal_sequential(decoder_cls):
     for got, ref in zip(results, want):
         for a, b in zip(got, ref):
             assert np.array_equal(a, b)
+
+
+def _add_fill_bytes(data):
+    """Insert optional 0xFF fill bytes before every RSTn marker and before EOI (T.81 B.1.1.2 allows them;
+    the reference's parser tests exercise the same in headers, test/parsers/jpeg_test.cpp:361)."""
+    off = oracle.info(data)["scan_offset"]
+    head, scan = bytearray(data[:off]), data[off:]
+    out = bytearray()
+    i = 0
+    while i < len(scan):
+        if scan[i] == 0xFF and i + 1 < len(scan) and (0xD0 <= scan[i + 1] <= 0xD7 or scan[i + 1] == 0xD9):
+            out += b"\xff" * (1 + (i % 3))
+        out.append(scan[i])
+        i += 1
+    return bytes(head + out)
+
+
+def test_awkward_but_valid_streams(dec_fancy, dec_plain):
+    """Restart interval of one MCU (a boundary every few bytes), fill bytes before markers, gray with RST,
+    very wide / very tall strips, 4:1:1 and 4:4:0 through the generic and the specialised colour paths."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    srcs = [corpus.encode(corpus.synth(300, 400, 51), 92, "420", rst_interval=1),
+            corpus.encode(corpus.synth(240, 320, 52), 85, "444", rst_interval=1),
+            _add_fill_bytes(corpus.encode(corpus.synth(200, 300, 53), 90, "422", rst_interval=4)),
+            _add_fill_bytes(corpus.encode(corpus.synth(64, 64, 54), 75, "420", rst_interval=2)),
+            corpus.encode(corpus.synth(8, 16000, 55), 90, "420"),
+            corpus.encode(corpus.synth(12000, 9, 56), 90, "422", rst_interval=3),
+            corpus.encode(corpus.synth(333, 777, 57), 88, "411", rst_interval=5),
+            corpus.encode(corpus.synth(333, 777, 58), 88, "440")]
+    import cv2
+
+    ok, g = cv2.imencode(".jpg", cv2.cvtColor(corpus.synth(150, 222, 59), cv2.COLOR_RGB2GRAY), [cv2.IMWRITE_JPEG_QUALITY, 90, cv2.IMWRITE_JPEG_RST_INTERVAL, 3])
+    srcs.append(g.tobytes())
+    for dec, fancy in ((dec_fancy, True), (dec_plain, False)):
+        for fmt in ("I_RGB", "P_BGR", "I_Y"):
+            outs = dec.decode(srcs, fmt)
+            assert dec.last_status == [_lib.OK] * len(srcs), dec.last_status
+            for d, o in zip(srcs, outs):
+                assert np.array_equal(o.cpu().numpy(), oracle.decode(d, OFMT[fmt], fancy=fancy))
