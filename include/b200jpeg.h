@@ -46,7 +46,9 @@ enum {
     B200JPEG_FMT_I_BGR = 1,
     B200JPEG_FMT_P_RGB = 2,
     B200JPEG_FMT_P_BGR = 3,
-    B200JPEG_FMT_Y = 4 /* single plane: P_Y / I_Y */
+    B200JPEG_FMT_Y = 4,     /* single plane: P_Y / I_Y */
+    B200JPEG_FMT_I_YUV = 5, /* Y, Cb, Cr samples (chroma upsampled, no colour transform), interleaved */
+    B200JPEG_FMT_P_YUV = 6  /* ... planar */
 };
 
 /* What the host marker walk found.  Superset of what the reference's header

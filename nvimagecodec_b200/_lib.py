@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libb200jpeg_ext.so")
 
 OK, ERR_ARG, ERR_NOT_JPEG, ERR_UNSUPPORTED, ERR_CORRUPT, ERR_CUDA, ERR_STATE, ERR_TOO_LARGE = range(8)
 STATUS_NAMES = ["OK", "ERR_ARG", "ERR_NOT_JPEG", "ERR_UNSUPPORTED", "ERR_CORRUPT", "ERR_CUDA", "ERR_STATE", "ERR_TOO_LARGE"]
-FMT = {"I_RGB": 0, "I_BGR": 1, "P_RGB": 2, "P_BGR": 3, "P_Y": 4, "I_Y": 4, "Y": 4}
+FMT = {"I_RGB": 0, "I_BGR": 1, "P_RGB": 2, "P_BGR": 3, "P_Y": 4, "I_Y": 4, "Y": 4, "I_YUV": 5, "P_YUV": 6}
 
 NOALLOC_MAX_SEGMENT_BYTES = 8 << 20
 

@@ -210,12 +210,12 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             x1 = hd.width;
             y1 = hd.height;
         }
-        if (!o.buffer || o.format < 0 || o.format > B200JPEG_FMT_Y || x0 < 0 || y0 < 0 || x1 > hd.width || y1 > hd.height || x0 >= x1 || y0 >= y1) {
+        if (!o.buffer || o.format < 0 || o.format > B200JPEG_FMT_P_YUV || x0 < 0 || y0 < 0 || x1 > hd.width || y1 > hd.height || x0 >= x1 || y0 >= y1) {
             host_status_[i] = B200JPEG_ERR_ARG;
             continue;
         }
         const size_t rw = size_t(x1 - x0), rh = size_t(y1 - y0);
-        const bool planar = (o.format == B200JPEG_FMT_P_RGB || o.format == B200JPEG_FMT_P_BGR);
+        const bool planar = (o.format == B200JPEG_FMT_P_RGB || o.format == B200JPEG_FMT_P_BGR || o.format == B200JPEG_FMT_P_YUV);
         const size_t nch = o.format == B200JPEG_FMT_Y ? 1 : 3;
         const size_t tight = planar ? rw : rw * nch;
         const size_t stride = o.row_stride ? o.row_stride : tight;

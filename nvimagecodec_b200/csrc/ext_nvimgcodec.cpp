@@ -99,6 +99,12 @@ nvimgcodecProcessingStatus_t translate_output(const nvimgcodecImageInfo_t& info,
         out->format = B200JPEG_FMT_Y;
         want_channels = 1;
         break;
+    case NVIMGCODEC_SAMPLEFORMAT_I_YUV: out->format = B200JPEG_FMT_I_YUV; break;
+    case NVIMGCODEC_SAMPLEFORMAT_P_YUV:
+        out->format = B200JPEG_FMT_P_YUV;
+        want_planes = 3;
+        want_channels = 1;
+        break;
     case NVIMGCODEC_SAMPLEFORMAT_I_UNCHANGED: // "as stored": RGB for colour streams, Y for gray ones
         out->format = info.plane_info[0].num_channels == 1 ? B200JPEG_FMT_Y : B200JPEG_FMT_I_RGB;
         want_channels = info.plane_info[0].num_channels == 1 ? 1 : 3;
@@ -183,7 +189,8 @@ class DecoderImpl {
             return NVIMGCODEC_PROCESSING_STATUS_FAIL;
         if (std::strcmp(cs_info.codec_name, "jpeg") != 0)
             return NVIMGCODEC_PROCESSING_STATUS_CODEC_UNSUPPORTED;
-        if (jpeg_info.encoding != NVIMGCODEC_JPEG_ENCODING_BASELINE_DCT)
+        if (jpeg_info.encoding != NVIMGCODEC_JPEG_ENCODING_BASELINE_DCT &&
+            jpeg_info.encoding != NVIMGCODEC_JPEG_ENCODING_EXTENDED_SEQUENTIAL_DCT_HUFFMAN)
             return NVIMGCODEC_PROCESSING_STATUS_ENCODING_UNSUPPORTED;
         nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
         if (image->getImageInfo(image->instance, &info) != NVIMGCODEC_STATUS_SUCCESS)
@@ -202,6 +209,10 @@ class DecoderImpl {
         st |= translate_output(info, region, int(cs_info.plane_info[0].width), int(cs_info.plane_info[0].height), &out);
         if (params->apply_exif_orientation && (info.orientation.flip_x || info.orientation.flip_y || info.orientation.rotated != 0))
             st |= NVIMGCODEC_PROCESSING_STATUS_ORIENTATION_UNSUPPORTED;
+        // YCbCr output only for YCbCr streams without subsampling, as libjpeg_turbo_decoder.cpp:180-189
+        if ((info.sample_format == NVIMGCODEC_SAMPLEFORMAT_I_YUV || info.sample_format == NVIMGCODEC_SAMPLEFORMAT_P_YUV) &&
+            (cs_info.color_spec != NVIMGCODEC_COLORSPEC_SYCC || cs_info.chroma_subsampling != NVIMGCODEC_SAMPLING_444))
+            st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLE_FORMAT_UNSUPPORTED;
         if (st != NVIMGCODEC_PROCESSING_STATUS_SUCCESS)
             return st;
         // stream-level acceptance: our own marker walk (the built-in parser stops before DQT/DHT/DRI/SOS)

@@ -134,8 +134,10 @@ StreamStatus parse_stream(const uint8_t* d, size_t n, StreamHeader* hdr)
                 if (hdr->h[c] < 1 || hdr->h[c] > 4 || hdr->v[c] < 1 || hdr->v[c] > 4 || hdr->tq[c] > 3)
                     return kStreamCorrupt;
             }
-            if (m != 0xC0 || hdr->precision != 8)
-                verdict = kStreamUnsupported; // progressive / extended / lossless / arithmetic / 12-bit
+            // SOF0 baseline and SOF1 extended-sequential Huffman decode identically at 8 bits (SOF1 merely
+            // allows 4 tables per class and 12-bit samples; those are declined below / here)
+            if ((m != 0xC0 && m != 0xC1) || hdr->precision != 8)
+                verdict = kStreamUnsupported; // progressive / lossless / arithmetic / 12-bit
             if (hdr->width == 0 || hdr->height == 0)
                 verdict = kStreamUnsupported; // DNL-defined height
         } else if (m == 0xDA) {
@@ -157,7 +159,7 @@ StreamStatus parse_stream(const uint8_t* d, size_t n, StreamHeader* hdr)
                 hdr->td[c] = s[2 + 2 * c] >> 4;
                 hdr->ta[c] = s[2 + 2 * c] & 15;
                 if (hdr->td[c] > 1 || hdr->ta[c] > 1)
-                    return kStreamUnsupported; // baseline allows table ids 0 and 1 only
+                    return kStreamUnsupported; // table ids 2 and 3 (legal in SOF1 only) are not carried to the device
             }
             break;
         }

@@ -1073,7 +1073,13 @@ __device__ __forceinline__ void color_pixel_generic(const BatchDev& bd, const Im
         r = g = b = uint32_t(sample_plane(p0, x, y));
     } else {
         const PlaneView p1 = make_plane(bd, im, 1), p2 = make_plane(bd, im, 2);
-        ycc_to_rgb(sample_plane(p0, x, y), sample_plane(p1, x, y), sample_plane(p2, x, y), r, g, b);
+        if (im.fmt == kFmtIYUV || im.fmt == kFmtPYUV) {
+            r = uint32_t(sample_plane(p0, x, y));
+            g = uint32_t(sample_plane(p1, x, y));
+            b = uint32_t(sample_plane(p2, x, y));
+        } else {
+            ycc_to_rgb(sample_plane(p0, x, y), sample_plane(p1, x, y), sample_plane(p2, x, y), r, g, b);
+        }
     }
     const int ox = x - im.roi_x0, oy = y - im.roi_y0;
     if (im.fmt == kFmtY) {
@@ -1085,7 +1091,7 @@ __device__ __forceinline__ void color_pixel_generic(const BatchDev& bd, const Im
         r = b;
         b = t;
     }
-    if (im.fmt == kFmtPRGB || im.fmt == kFmtPBGR) {
+    if (im.fmt == kFmtPRGB || im.fmt == kFmtPBGR || im.fmt == kFmtPYUV) {
         uint8_t* o = im.out + size_t(oy) * im.row_stride + ox;
         o[0] = uint8_t(r);
         o[im.plane_stride] = uint8_t(g);
@@ -1181,7 +1187,7 @@ __device__ __forceinline__ void upsample8(const int* cur, const int* nbr, int r,
 // kLumaOnly: grayscale stream or Y output.
 // kFancy: the triangle filter applies (decided on the host: fancy_upsampling option, the expansion
 // factors and libjpeg's downsampled_width > 2 condition).
-template <int HX, int VX, bool kFancy, bool kLumaOnly, bool kSwap>
+template <int HX, int VX, bool kFancy, bool kLumaOnly, int kOrder>
 __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& im, int X0, int Y0)
 {
     const uint8_t* p0 = bd.planes + im.plane_off[0];
@@ -1220,7 +1226,7 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
             }
         }
     }
-    constexpr bool swap = kSwap; // BGR orders
+    constexpr bool swap = (kOrder == 1); // BGR orders; kOrder == 2: Y, Cb, Cr written as they are
     const bool full_x = X0 >= int(im.roi_x0) && X0 + 8 <= int(im.roi_x1);
 #pragma unroll
     for (int r = 0; r < VX; ++r) {
@@ -1236,14 +1242,20 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
                 c0[i] = c1[i] = c2[i] = uint32_t(yy[i]);
             } else {
                 uint32_t rr, gg, bb;
-                ycc_to_rgb(yy[i], cb[r][i], cr[r][i], rr, gg, bb);
+                if (kOrder == 2) {
+                    rr = uint32_t(yy[i]);
+                    gg = uint32_t(cb[r][i]);
+                    bb = uint32_t(cr[r][i]);
+                } else {
+                    ycc_to_rgb(yy[i], cb[r][i], cr[r][i], rr, gg, bb);
+                }
                 c0[i] = swap ? bb : rr;
                 c1[i] = gg;
                 c2[i] = swap ? rr : bb;
             }
         }
         const int oy = y - im.roi_y0, ox = X0 - int(im.roi_x0);
-        if (im.fmt == kFmtY || im.fmt == kFmtPRGB || im.fmt == kFmtPBGR) {
+        if (im.fmt == kFmtY || im.fmt == kFmtPRGB || im.fmt == kFmtPBGR || im.fmt == kFmtPYUV) {
             const int nch = (im.fmt == kFmtY) ? 1 : 3;
 #pragma unroll
             for (int ch = 0; ch < 3; ++ch) {
@@ -1309,13 +1321,15 @@ __global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev b
     const int Y0 = (int(im.roi_y0) & ~(urows - 1)) + (int(cy) * kColorTy + ty) * urows; // urows is 1 or 2
     if (X0 >= int(im.roi_x1) || Y0 >= int(im.roi_y1))
         return;
-    const bool swap = (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR);
-#define B200_COLOR_CASE(mode, HX, VX, FANCY, LUMA)                  \
-    case mode:                                                      \
-        if (swap)                                                   \
-            color_unit<HX, VX, FANCY, LUMA, true>(bd, im, X0, Y0);  \
-        else                                                        \
-            color_unit<HX, VX, FANCY, LUMA, false>(bd, im, X0, Y0); \
+    const int order = (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR) ? 1 : ((im.fmt == kFmtIYUV || im.fmt == kFmtPYUV) ? 2 : 0);
+#define B200_COLOR_CASE(mode, HX, VX, FANCY, LUMA)               \
+    case mode:                                                   \
+        if (order == 0)                                          \
+            color_unit<HX, VX, FANCY, LUMA, 0>(bd, im, X0, Y0);  \
+        else if (order == 1)                                     \
+            color_unit<HX, VX, FANCY, LUMA, 1>(bd, im, X0, Y0);  \
+        else                                                     \
+            color_unit<HX, VX, FANCY, LUMA, 2>(bd, im, X0, Y0);  \
         break;
     switch (im.color_mode) {
         B200_COLOR_CASE(1, 1, 1, false, true)

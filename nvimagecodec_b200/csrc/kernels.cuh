@@ -32,7 +32,7 @@ enum : uint32_t {
 };
 
 // Output formats (same values as include/b200jpeg.h)
-enum : int { kFmtIRGB = 0, kFmtIBGR = 1, kFmtPRGB = 2, kFmtPBGR = 3, kFmtY = 4 };
+enum : int { kFmtIRGB = 0, kFmtIBGR = 1, kFmtPRGB = 2, kFmtPBGR = 3, kFmtY = 4, kFmtIYUV = 5, kFmtPYUV = 6 };
 
 struct ImageDev {
     // stream geometry

@@ -91,9 +91,9 @@ class Decoder:
                 y0, x0, y1, x1 = rois[i]
                 hgt, wid = y1 - y0, x1 - x0
             f = fmts[i]
-            if f in ("I_RGB", "I_BGR"):
+            if f in ("I_RGB", "I_BGR", "I_YUV"):
                 shape, stride = (hgt, wid, 3), wid * 3
-            elif f in ("P_RGB", "P_BGR"):
+            elif f in ("P_RGB", "P_BGR", "P_YUV"):
                 shape, stride = (3, hgt, wid), wid
             else:
                 shape, stride = (hgt, wid), wid
@@ -121,10 +121,10 @@ class Decoder:
                 o.roi_x0, o.roi_y0, o.roi_x1, o.roi_y1 = x0, y0, x1, y1
             if infos[i].supported and nbytes > 0:
                 flat = out_storage[off:off + nbytes]
-                if f in ("I_RGB", "I_BGR"):
+                if f in ("I_RGB", "I_BGR", "I_YUV"):
                     img = flat.view(shape[0], stride)[:, :shape[1] * 3].view(shape[0], shape[1], 3) if stride == shape[1] * 3 else \
                         flat.view(shape[0], stride)[:, :shape[1] * 3].unflatten(1, (shape[1], 3))
-                elif f in ("P_RGB", "P_BGR"):
+                elif f in ("P_RGB", "P_BGR", "P_YUV"):
                     img = flat.view(3, shape[1], stride)[:, :, :shape[2]]
                 else:
                     img = flat.view(shape[0], stride)[:, :shape[1]]

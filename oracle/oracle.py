@@ -13,7 +13,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "liboracle_jpeg.so")
 
-FMT_I_RGB, FMT_I_BGR, FMT_P_RGB, FMT_P_BGR, FMT_Y = 0, 1, 2, 3, 4
+FMT_I_RGB, FMT_I_BGR, FMT_P_RGB, FMT_P_BGR, FMT_Y, FMT_I_YUV, FMT_P_YUV = 0, 1, 2, 3, 4, 5, 6
 _lib = None
 
 
@@ -74,7 +74,7 @@ def decode(data, fmt=FMT_I_RGB, fancy=True, roi=None):
     h, w = y1 - y0, x1 - x0
     if fmt == FMT_Y:
         out = np.empty((h, w), dtype=np.uint8)
-    elif fmt in (FMT_P_RGB, FMT_P_BGR):
+    elif fmt in (FMT_P_RGB, FMT_P_BGR, FMT_P_YUV):
         out = np.empty((3, h, w), dtype=np.uint8)
     else:
         out = np.empty((h, w, 3), dtype=np.uint8)

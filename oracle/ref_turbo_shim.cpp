@@ -14,7 +14,7 @@
 
 extern "C" {
 
-// fmt: 0 = I_RGB, 1 = I_BGR, 4 = Y (grayscale).  crop: x, y, w, h (w == 0 -> whole image).
+// fmt: 0 = I_RGB, 1 = I_BGR, 4 = Y (grayscale), 5 = I_YUV (YCbCr samples, no colour transform).  crop: x, y, w, h (w == 0 -> whole image).
 // out must hold w*h*components bytes.  Returns 0 on success.
 __attribute__((visibility("default"))) int ref_turbo_decode(const unsigned char* data, int len, int fancy, int fmt, int crop_x, int crop_y,
     int crop_w, int crop_h, unsigned char* out, int* out_w, int* out_h)
@@ -24,7 +24,10 @@ __attribute__((visibility("default"))) int ref_turbo_decode(const unsigned char*
         return 1;
     libjpeg_turbo::UncompressFlags flags;
     flags.components = (fmt == 4) ? 1 : 3;
-    flags.sample_format = fmt == 0 ? NVIMGCODEC_SAMPLEFORMAT_I_RGB : (fmt == 1 ? NVIMGCODEC_SAMPLEFORMAT_I_BGR : NVIMGCODEC_SAMPLEFORMAT_I_Y);
+    flags.sample_format = fmt == 0 ? NVIMGCODEC_SAMPLEFORMAT_I_RGB
+                          : fmt == 1 ? NVIMGCODEC_SAMPLEFORMAT_I_BGR
+                          : fmt == 5 ? NVIMGCODEC_SAMPLEFORMAT_I_YUV
+                                     : NVIMGCODEC_SAMPLEFORMAT_I_Y;
     flags.dct_method = JDCT_DEFAULT;
     flags.fancy_upscaling = fancy != 0;
     if (crop_w > 0) {

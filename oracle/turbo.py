@@ -42,7 +42,7 @@ def decode(data, fmt="I_RGB", fancy=True, roi=None):
     """roi = (y0, x0, y1, x1).  Returns HxWx3 (I_RGB / I_BGR) or HxW (I_Y)."""
     a = np.frombuffer(bytes(data), dtype=np.uint8)
     w, h = ctypes.c_int(), ctypes.c_int()
-    code = {"I_RGB": 0, "I_BGR": 1, "I_Y": 4}[fmt]
+    code = {"I_RGB": 0, "I_BGR": 1, "I_Y": 4, "I_YUV": 5}[fmt]
     crop = (0, 0, 0, 0) if roi is None else (roi[1], roi[0], roi[3] - roi[1], roi[2] - roi[0])
     rc = lib().ref_turbo_decode(a.ctypes.data, a.size, int(bool(fancy)), code, *crop, None, ctypes.byref(w), ctypes.byref(h))
     if rc:

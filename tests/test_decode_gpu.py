@@ -335,3 +335,31 @@ def test_awkward_but_valid_streams(dec_fancy, dec_plain):
             assert dec.last_status == [_lib.OK] * len(srcs), dec.last_status
             for d, o in zip(srcs, outs):
                 assert np.array_equal(o.cpu().numpy(), oracle.decode(d, OFMT[fmt], fancy=fancy))
+
+
+def _as_sof1(data):
+    """Relabel a baseline stream as extended-sequential Huffman (SOF1): every baseline stream is a valid SOF1 stream."""
+    i = data.index(b"\xff\xc0")
+    return data[:i] + b"\xff\xc1" + data[i + 2:]
+
+
+def test_ycbcr_output_and_extended_sequential(dec_fancy, dec_plain):
+    """I_YUV / P_YUV (libjpeg's out_color_space = JCS_YCbCr: upsampled samples, no colour transform;
+    the reference allows it for 4:4:4 streams, libjpeg_turbo_decoder.cpp:180-189) and SOF1 streams."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    srcs = [corpus.encode(corpus.synth(120, 200, 91), 90, "444"), corpus.encode(corpus.synth(97, 131, 92), 80, "444", 4),
+            corpus.encode(corpus.synth(64, 80, 93), 90, "420"), corpus.encode(corpus.synth(50, 70, 94), 90, "422", 2)]
+    for dec, fancy in ((dec_fancy, True), (dec_plain, False)):
+        for fmt, ofmt in (("I_YUV", oracle.FMT_I_YUV), ("P_YUV", oracle.FMT_P_YUV)):
+            outs = dec.decode(srcs, fmt)
+            assert dec.last_status == [_lib.OK] * len(srcs)
+            for d, o in zip(srcs, outs):
+                assert np.array_equal(o.cpu().numpy(), oracle.decode(d, ofmt, fancy=fancy))
+    sof1 = [_as_sof1(d) for d in srcs]
+    outs = dec_fancy.decode(sof1, "I_RGB")
+    assert dec_fancy.last_status == [_lib.OK] * len(sof1)
+    for d, s1, o in zip(srcs, sof1, outs):
+        ref = oracle.decode(d, oracle.FMT_I_RGB, fancy=True)
+        assert np.array_equal(oracle.decode(s1, oracle.FMT_I_RGB, fancy=True), ref)
+        assert np.array_equal(o.cpu().numpy(), ref)
