@@ -56,7 +56,7 @@ int b200jpegProbe(const void* data, size_t length, b200jpegStreamInfo_t* info)
     case b200jpeg::kStreamUnsupported: info->reason = B200JPEG_ERR_UNSUPPORTED; break;
     default: info->reason = B200JPEG_ERR_CORRUPT; break;
     }
-    if (st == b200jpeg::kStreamOk && hd.scan_length >= (size_t(1) << 29)) {
+    if (st == b200jpeg::kStreamOk && hd.scan_length >= (size_t(1) << 28)) {
         info->supported = 0;
         info->reason = B200JPEG_ERR_TOO_LARGE;
     }

@@ -223,7 +223,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             host_status_[i] = B200JPEG_ERR_ARG;
             continue;
         }
-        if (hd.scan_length >= (size_t(1) << 29)) { // bit positions are 32-bit
+        if (hd.scan_length >= (size_t(1) << 28)) { // bit positions (and the bit after the last subsequence) must fit 32 bits
             host_status_[i] = B200JPEG_ERR_TOO_LARGE;
             continue;
         }
@@ -742,7 +742,7 @@ int Decoder::scan_segment(const void* dev_raw, size_t length, uint32_t expected_
     if (!dev_raw || !dev_words || !dev_bnd || !dev_result || length == 0 || (reinterpret_cast<uintptr_t>(dev_raw) & 15u) ||
         (reinterpret_cast<uintptr_t>(dev_words) & 3u) || bnd_cap < expected_rst + 1)
         return fail(B200JPEG_ERR_ARG, "bad argument");
-    if (length >= (size_t(1) << 29))
+    if (length >= (size_t(1) << 28))
         return fail(B200JPEG_ERR_TOO_LARGE, "segment too large");
     if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
         return B200JPEG_ERR_CUDA;
