@@ -224,9 +224,12 @@ void build_huff_table(const HuffSpec& spec, bool is_dc, HuffTableDev* out)
 {
     std::memset(out, 0, sizeof(*out));
     int code = 0, k = 0;
+    uint32_t first16 = 0x10000u;
     for (int l = 1; l <= 16; ++l) {
         out->valoff[l] = k - code;
         const int cnt = spec.present ? spec.bits[l] : 0;
+        if (cnt && l > kLutBits && first16 == 0x10000u)
+            first16 = uint32_t(code) << (16 - l);
         for (int i = 0; i < cnt; ++i, ++code, ++k) {
             out->sym[k] = pack_symbol(is_dc, l, spec.vals[k]);
             if (l <= kLutBits) {
@@ -243,6 +246,26 @@ void build_huff_table(const HuffSpec& spec, bool is_dc, HuffTableDev* out)
     out->maxcode[17] = 0x7fffffff;
     out->valoff[0] = 0;
     out->valoff[17] = 0;
+    // second level: every 16-bit window >= first16 belongs to a long code (or is unassigned: entry 0)
+    out->first16 = first16;
+    out->n2 = 0;
+    if (first16 < 0x10000u && 0x10000u - first16 <= uint32_t(kLut2Size)) {
+        out->n2 = 0x10000u - first16;
+        code = 0;
+        k = 0;
+        for (int l = 1; l <= 16; ++l) {
+            const int cnt = spec.present ? spec.bits[l] : 0;
+            for (int i = 0; i < cnt; ++i, ++code, ++k) {
+                if (l <= kLutBits)
+                    continue;
+                const uint32_t left = uint32_t(code) << (16 - l);
+                for (uint32_t j = 0; j < (1u << (16 - l)); ++j)
+                    if (left + j >= first16 && left + j - first16 < out->n2)
+                        out->lut2[left + j - first16] = out->sym[k];
+            }
+            code <<= 1;
+        }
+    }
 }
 
 uint64_t hash_huff_set(const StreamHeader& hdr)

@@ -11,7 +11,8 @@ namespace b200jpeg {
 
 constexpr int kMaxComp = 4;
 constexpr int kMaxBlocksPerMcu = 10;
-constexpr int kLutBits = 11; // first-level Huffman lookup width
+constexpr int kLutBits = 11;    // first-level Huffman lookup width
+constexpr int kLut2Size = 256;  // second-level entries (16-bit windows of the codes longer than kLutBits)
 
 enum StreamStatus { kStreamOk = 0, kStreamNotJpeg, kStreamUnsupported, kStreamCorrupt };
 
@@ -45,7 +46,12 @@ struct alignas(16) HuffTableDev {
     uint16_t lut[1 << kLutBits]; // packed symbol action (see pack_symbol); 0 = longer than kLutBits or invalid
     int32_t maxcode[18];         // maxcode[l] for l in 1..16 (canonical), -1 if none; [17] = sentinel
     int32_t valoff[18];          // sym index = valoff[l] + code
-    uint16_t sym[256];           // packed symbol actions in canonical order (slow path for long codes)
+    uint16_t sym[256];           // packed symbol actions in canonical order (last-resort canonical search)
+    // Second level for codes longer than kLutBits: in a canonical code they are exactly the 16-bit windows
+    // >= first16 (the first long code, left-aligned), usually a hundred-odd values, so one more lookup
+    // indexed by (window16 - first16) resolves them; n2 == 0 means "too many, use the canonical search".
+    uint32_t first16, n2;
+    uint16_t lut2[kLut2Size];
 };
 struct alignas(16) HuffSetDev {
     HuffTableDev t[4]; // 0: DC id0, 1: DC id1, 2: AC id0, 3: AC id1

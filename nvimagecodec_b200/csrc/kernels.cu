@@ -464,19 +464,24 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
         const HuffTableDev* tab = reinterpret_cast<const HuffTableDev*>(hbase + (is_dc ? binfo.x : (binfo.y & 0xFFFFFFu)));
         uint32_t e = tab->lut[win >> (32 - kLutBits)];
         if ((e & 31u) == 0u) {
-            // code longer than the first-level table: canonical search (T.81 F.2.2.3)
-            e = 16u | (1u << 9); // an invalid code consumes 16 bits (only an unsynchronised decoder gets here on a valid stream)
-            bool found = false;
-#pragma unroll
-            for (int l = kLutBits + 1; l <= 16; ++l) {
-                const int32_t code = int32_t(win >> (32 - l));
-                if (!found && code <= tab->maxcode[l]) {
-                    found = true;
-                    e = tab->sym[(tab->valoff[l] + code) & 255];
+            // code longer than the first-level table: second-level lookup on the 16-bit window
+            const uint32_t i2 = (win >> 16) - tab->first16; // wraps to a huge value below first16
+            e = (i2 < tab->n2) ? tab->lut2[i2] : 0u;
+            if (tab->n2 == 0u && (win >> 16) >= tab->first16) {
+                // table with too many long codes for the second level: canonical search (T.81 F.2.2.3)
+#pragma unroll 1
+                for (int l = kLutBits + 1; l <= 16; ++l) {
+                    const int32_t code = int32_t(win >> (32 - l));
+                    if (code <= tab->maxcode[l]) {
+                        e = tab->sym[(tab->valoff[l] + code) & 255];
+                        break;
+                    }
                 }
             }
-            if (!found)
+            if ((e & 31u) == 0u) {
+                e = 16u | (1u << 9); // unassigned code: consumes 16 bits (only an unsynchronised decoder gets here on a valid stream)
                 out.err |= kFlagBadHuffman;
+            }
         }
         const uint32_t len = e & 31u, size = (e >> 5) & 15u, skip = e >> 9;
         const uint32_t rest = win << len;
@@ -814,7 +819,7 @@ __global__ void __launch_bounds__(256) verify_scan_kernel(BatchDev bd, int fix_m
 // K3.  Same CTA shape as K1; every thread re-decodes its subsequence from the verified entry
 // state, now knowing its absolute block index and DC predictors, and writes the coefficient
 // blocks it owns (zig-zag order, MCU decode order, absolute DC) as whole 16-byte groups.
-__global__ void __launch_bounds__(kSeqThreads) huff_write_kernel(BatchDev bd, int redo_only)
+__global__ void __launch_bounds__(kSeqThreads, 5) huff_write_kernel(BatchDev bd, int redo_only)
 {
     extern __shared__ uint4 s_raw[];
     HuffSetDev* s_hs = reinterpret_cast<HuffSetDev*>(s_raw);
