@@ -236,6 +236,17 @@ def main():
     base, base_fmt, base_roi = make_workload(args.workload, args.batch, max(1, cores // world))
     assert torch.cuda.is_available(), "bench.py needs a GPU (the decoder has no CPU path)"
     torch.cuda.set_device(local)
+    numa = "unset"
+    if world > 1:
+        # keep this rank's host threads (and, by first touch, its pinned staging) on the CPUs next to its GPU
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local))
+            numa = "nvml cpu affinity, %d cpus" % len(os.sched_getaffinity(0))
+        except Exception as e:  # affinity is an optimisation only
+            numa = "unavailable (%s)" % type(e).__name__
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     global_sizes = [len(base[i % args.batch]) for i in range(args.batch * world)]
@@ -382,7 +393,7 @@ def main():
             "config": {"workload": WORKLOADS[args.workload], "images_per_gpu": n_img, "upsampling": "fancy" if args.fancy else "box",
                        "l2": "working set per step (bitstreams + %.1f GB coefficients + planes + pixels) is larger than the 126 MB L2, no flush needed"
                              % (2 * n_coefs / 1e9),
-                       "sharding": "LPT by compressed bytes, one process per GPU, no collective"},
+                       "sharding": "LPT by compressed bytes, one process per GPU, no collective", "host_affinity": numa},
             "e2e": {"value": job_mpix * args.steps / (ms_e2e * 1e-3), "unit": "MPix/s", "images_per_s": job_imgs * args.steps / (ms_e2e * 1e-3),
                     "h2d_bytes_per_step": host_batch.h2d_bytes, "d2h_bytes_per_step": host_batch.d2h_bytes,
                     "call": "Decoder.run(batch) == b200jpegDecodeBatch, pinned host in, pinned host out"},
