@@ -76,6 +76,10 @@ typedef struct {
     int buffer_is_host; /* 0 = device (kernels store straight into it), 1 = host (decoder bounces + D2H) */
     size_t row_stride;  /* bytes per row of a plane; 0 = tight */
     int roi_x0, roi_y0, roi_x1, roi_y1; /* all zero = full image; else [x0,x1) x [y0,y1) inside the image */
+    int orientation;    /* EXIF orientation code 1..8 to apply to the (cropped) result, 0 or 1 = none.  Codes 5..8
+                           swap width and height: the buffer then holds roi_width rows of roi_height pixels.  What
+                           nvimgcodecDecodeParams_t::apply_exif_orientation asks of a decoder (include/nvimgcodec.h:784);
+                           the reference's CPU plugin declines it (libjpeg_turbo_decoder.cpp:206-209), nvjpeg_ext applies it. */
 } b200jpegOutput_t;
 
 /* Host-only marker walk (SOI .. SOS): tables present, sampling, restart interval,

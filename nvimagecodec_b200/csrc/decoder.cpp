@@ -217,7 +217,13 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         const size_t rw = size_t(x1 - x0), rh = size_t(y1 - y0);
         const bool planar = (o.format == B200JPEG_FMT_P_RGB || o.format == B200JPEG_FMT_P_BGR || o.format == B200JPEG_FMT_P_YUV);
         const size_t nch = o.format == B200JPEG_FMT_Y ? 1 : 3;
-        const size_t tight = planar ? rw : rw * nch;
+        if (o.orientation < 0 || o.orientation > 8) {
+            host_status_[i] = B200JPEG_ERR_ARG;
+            continue;
+        }
+        const bool transposed = o.orientation >= 5;       // EXIF 5..8: output rows run along the source columns
+        const size_t out_w = transposed ? rh : rw, out_h = transposed ? rw : rh;
+        const size_t tight = planar ? out_w : out_w * nch;
         const size_t stride = o.row_stride ? o.row_stride : tight;
         if (stride < tight || stride > 0xFFFFFFFFull) {
             host_status_[i] = B200JPEG_ERR_ARG;
@@ -304,8 +310,9 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.roi_x1 = uint16_t(x1);
         im.roi_y1 = uint16_t(y1);
         im.row_stride = uint32_t(stride);
-        im.plane_stride = stride * rh;
-        const size_t obytes = planar ? 3 * stride * rh : stride * rh;
+        im.plane_stride = stride * out_h;
+        im.orient = uint8_t(o.orientation);
+        const size_t obytes = planar ? 3 * stride * out_h : stride * out_h;
         // K4b specialisation (kernels.cu color_kernel): fast paths need full-resolution luma and
         // both chroma components subsampled alike by 1 or 2 in each direction
         im.color_mode = 0;

@@ -12,6 +12,7 @@
 // the same object the plain C ABI (include/b200jpeg.h) drives.
 #include <nvimgcodec.h>
 
+#include <algorithm>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -73,10 +74,12 @@ bool map_stream(const nvimgcodecCodeStreamDesc_t* cs, MappedStream* out)
     return true;
 }
 
+int to_exif_code(const nvimgcodecOrientation_t& o);
+
 // Translate the requested nvimgcodecImageInfo_t into a b200jpegOutput_t.  Returns a processing
 // status: SUCCESS or an OR of the *_UNSUPPORTED bits (include/nvimgcodec.h:735-768).
 nvimgcodecProcessingStatus_t translate_output(const nvimgcodecImageInfo_t& info, const nvimgcodecRegion_t* region, int img_w, int img_h,
-    b200jpegOutput_t* out)
+    bool apply_orientation, b200jpegOutput_t* out)
 {
     nvimgcodecProcessingStatus_t st = NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
     std::memset(out, 0, sizeof(*out));
@@ -141,6 +144,19 @@ nvimgcodecProcessingStatus_t translate_output(const nvimgcodecImageInfo_t& info,
             }
         }
     }
+    // EXIF orientation (nvimgcodecDecodeParams_t::apply_exif_orientation): applied while storing; the caller's image
+    // already has the oriented size (python/decoder.cpp and example/nvimtrans/main.cpp:487-490 swap it for 90/270)
+    int exif = 1;
+    if (apply_orientation) {
+        exif = to_exif_code(info.orientation);
+        if (exif == 0)
+            st |= NVIMGCODEC_PROCESSING_STATUS_ORIENTATION_UNSUPPORTED;
+        else if (exif > 1 && region && region->ndim != 0)
+            st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED; // which frame a region refers to is not defined by the API
+    }
+    out->orientation = exif;
+    if (exif >= 5)
+        std::swap(rw, rh);
     if (int(info.plane_info[0].width) < rw || int(info.plane_info[0].height) < rh)
         st |= NVIMGCODEC_PROCESSING_STATUS_RESOLUTION_UNSUPPORTED;
     out->buffer = info.buffer;
@@ -151,6 +167,30 @@ nvimgcodecProcessingStatus_t translate_output(const nvimgcodecImageInfo_t& info,
     if (want_planes == 3 && int(info.plane_info[0].height) != rh)
         st |= NVIMGCODEC_PROCESSING_STATUS_RESOLUTION_UNSUPPORTED;
     return st;
+}
+
+// nvimgcodecOrientation_t (rotation counter-clockwise in degrees + flips, as src/parsers/exif_orientation.h builds it from
+// the EXIF tag) back to the EXIF code the decoder applies.  Returns 0 for combinations the parser never produces.
+int to_exif_code(const nvimgcodecOrientation_t& o)
+{
+    const int rot = ((o.rotated % 360) + 360) % 360;
+    if (rot == 0 && !o.flip_x && !o.flip_y)
+        return 1;
+    if (rot == 0 && o.flip_x && !o.flip_y)
+        return 2;
+    if (rot == 180 && !o.flip_x && !o.flip_y)
+        return 3;
+    if (rot == 0 && !o.flip_x && o.flip_y)
+        return 4;
+    if (rot == 90 && !o.flip_x && o.flip_y)
+        return 5;
+    if (rot == 270 && !o.flip_x && !o.flip_y)
+        return 6;
+    if (rot == 270 && !o.flip_x && o.flip_y)
+        return 7;
+    if (rot == 90 && !o.flip_x && !o.flip_y)
+        return 8;
+    return 0;
 }
 
 nvimgcodecProcessingStatus_t to_processing_status(int b200_status)
@@ -206,9 +246,8 @@ class DecoderImpl {
             region = &csi.code_stream_view->region;
         }
         b200jpegOutput_t out;
-        st |= translate_output(info, region, int(cs_info.plane_info[0].width), int(cs_info.plane_info[0].height), &out);
-        if (params->apply_exif_orientation && (info.orientation.flip_x || info.orientation.flip_y || info.orientation.rotated != 0))
-            st |= NVIMGCODEC_PROCESSING_STATUS_ORIENTATION_UNSUPPORTED;
+        st |= translate_output(info, region, int(cs_info.plane_info[0].width), int(cs_info.plane_info[0].height),
+            params->apply_exif_orientation != 0, &out);
         // YCbCr output only for YCbCr streams without subsampling, as libjpeg_turbo_decoder.cpp:180-189
         if ((info.sample_format == NVIMGCODEC_SAMPLEFORMAT_I_YUV || info.sample_format == NVIMGCODEC_SAMPLEFORMAT_P_YUV) &&
             (cs_info.color_spec != NVIMGCODEC_COLORSPEC_SYCC || cs_info.chroma_subsampling != NVIMGCODEC_SAMPLING_444))
@@ -230,7 +269,8 @@ class DecoderImpl {
 
     // Shared by decodeBatch (thread_idx 0, whole batch on one framework stream) and the per-sample
     // decode safety net (one core per executor thread).
-    nvimgcodecStatus_t decode_batch(const nvimgcodecImageDesc_t** images, const nvimgcodecCodeStreamDesc_t** css, int n, int thread_idx)
+    nvimgcodecStatus_t decode_batch(const nvimgcodecImageDesc_t** images, const nvimgcodecCodeStreamDesc_t** css, int n, int thread_idx,
+        bool apply_orientation)
     {
         if (n <= 0)
             return NVIMGCODEC_STATUS_SUCCESS;
@@ -264,7 +304,8 @@ class DecoderImpl {
                 have_stream = true;
             }
             const nvimgcodecRegion_t* region = csi.code_stream_view ? &csi.code_stream_view->region : nullptr;
-            pre[i] = translate_output(info, region, int(cs_info.plane_info[0].width), int(cs_info.plane_info[0].height), &outs[i]);
+            pre[i] = translate_output(info, region, int(cs_info.plane_info[0].width), int(cs_info.plane_info[0].height), apply_orientation,
+                &outs[i]);
             if (pre[i] == NVIMGCODEC_PROCESSING_STATUS_SUCCESS) {
                 data[i] = streams[i].data;
                 len[i] = streams[i].size;
@@ -344,11 +385,12 @@ nvimgcodecProcessingStatus_t dec_can_decode(nvimgcodecDecoder_t decoder, const n
 }
 
 nvimgcodecStatus_t dec_decode(nvimgcodecDecoder_t decoder, const nvimgcodecImageDesc_t* image, const nvimgcodecCodeStreamDesc_t* cs,
-    const nvimgcodecDecodeParams_t*, int thread_idx)
+    const nvimgcodecDecodeParams_t* params, int thread_idx)
 {
     try {
         // +1: slot 0 belongs to decodeBatch, which the framework calls with thread_idx 0 on the caller thread
-        return reinterpret_cast<DecoderImpl*>(decoder)->decode_batch(&image, &cs, 1, thread_idx < 0 ? -1 : thread_idx + 1);
+        return reinterpret_cast<DecoderImpl*>(decoder)->decode_batch(&image, &cs, 1, thread_idx < 0 ? -1 : thread_idx + 1,
+            params && params->apply_exif_orientation);
     } catch (...) {
         if (image)
             image->imageReady(image->instance, NVIMGCODEC_PROCESSING_STATUS_FAIL);
@@ -357,10 +399,10 @@ nvimgcodecStatus_t dec_decode(nvimgcodecDecoder_t decoder, const nvimgcodecImage
 }
 
 nvimgcodecStatus_t dec_decode_batch(nvimgcodecDecoder_t decoder, const nvimgcodecImageDesc_t** images,
-    const nvimgcodecCodeStreamDesc_t** css, int batch_size, const nvimgcodecDecodeParams_t*, int)
+    const nvimgcodecCodeStreamDesc_t** css, int batch_size, const nvimgcodecDecodeParams_t* params, int)
 {
     try {
-        return reinterpret_cast<DecoderImpl*>(decoder)->decode_batch(images, css, batch_size, 0);
+        return reinterpret_cast<DecoderImpl*>(decoder)->decode_batch(images, css, batch_size, 0, params && params->apply_exif_orientation);
     } catch (...) {
         for (int i = 0; i < batch_size; ++i)
             images[i]->imageReady(images[i]->instance, NVIMGCODEC_PROCESSING_STATUS_FAIL);

@@ -1069,6 +1069,42 @@ __device__ __forceinline__ void ycc_to_rgb(int y, int cb, int cr, uint32_t& r, u
 constexpr int kColorTx = 32; // threads in x, 8 pixels each
 constexpr int kColorTy = 8;  // thread rows, color_unit_rows output rows each
 
+// EXIF orientation: where pixel (sx, sy) of the rw x rh (cropped) decode lands in the stored image.
+// Codes as in the EXIF standard / src/parsers/exif_orientation.h; checked against OpenCV and Pillow.
+__device__ __forceinline__ void orient_xy(uint32_t code, int sx, int sy, int rw, int rh, int& dx, int& dy)
+{
+    switch (code) {
+    case 2: dx = rw - 1 - sx; dy = sy; break;            // mirror horizontal
+    case 3: dx = rw - 1 - sx; dy = rh - 1 - sy; break;   // rotate 180
+    case 4: dx = sx; dy = rh - 1 - sy; break;            // mirror vertical
+    case 5: dx = sy; dy = sx; break;                     // transpose
+    case 6: dx = rh - 1 - sy; dy = sx; break;            // rotate 90 CW
+    case 7: dx = rh - 1 - sy; dy = rw - 1 - sx; break;   // transverse
+    case 8: dx = sy; dy = rw - 1 - sx; break;            // rotate 270 CW
+    default: dx = sx; dy = sy; break;
+    }
+}
+
+// Stores one pixel (three channel values, already in output channel order) at its oriented position.
+__device__ __forceinline__ void store_pixel_oriented(const ImageDev& im, int sx, int sy, uint32_t v0, uint32_t v1, uint32_t v2)
+{
+    int dx, dy;
+    orient_xy(im.orient, sx, sy, int(im.roi_x1) - int(im.roi_x0), int(im.roi_y1) - int(im.roi_y0), dx, dy);
+    if (im.fmt == kFmtY) {
+        im.out[size_t(dy) * im.row_stride + dx] = uint8_t(v0);
+    } else if (im.fmt == kFmtPRGB || im.fmt == kFmtPBGR || im.fmt == kFmtPYUV) {
+        uint8_t* o = im.out + size_t(dy) * im.row_stride + dx;
+        o[0] = uint8_t(v0);
+        o[im.plane_stride] = uint8_t(v1);
+        o[2 * im.plane_stride] = uint8_t(v2);
+    } else {
+        uint8_t* o = im.out + size_t(dy) * im.row_stride + size_t(dx) * 3;
+        o[0] = uint8_t(v0);
+        o[1] = uint8_t(v1);
+        o[2] = uint8_t(v2);
+    }
+}
+
 // Generic (any sampling, any alignment) path: one pixel at a time through sample_plane().
 __device__ __forceinline__ void color_pixel_generic(const BatchDev& bd, const ImageDev& im, int x, int y)
 {
@@ -1087,14 +1123,18 @@ __device__ __forceinline__ void color_pixel_generic(const BatchDev& bd, const Im
         }
     }
     const int ox = x - im.roi_x0, oy = y - im.roi_y0;
-    if (im.fmt == kFmtY) {
-        im.out[size_t(oy) * im.row_stride + ox] = uint8_t(r);
-        return;
-    }
     if (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR) {
         const uint32_t t = r;
         r = b;
         b = t;
+    }
+    if (im.orient > 1) {
+        store_pixel_oriented(im, ox, oy, r, g, b);
+        return;
+    }
+    if (im.fmt == kFmtY) {
+        im.out[size_t(oy) * im.row_stride + ox] = uint8_t(r);
+        return;
     }
     if (im.fmt == kFmtPRGB || im.fmt == kFmtPBGR || im.fmt == kFmtPYUV) {
         uint8_t* o = im.out + size_t(oy) * im.row_stride + ox;
@@ -1260,6 +1300,13 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
             }
         }
         const int oy = y - im.roi_y0, ox = X0 - int(im.roi_x0);
+        if (im.orient > 1) { // flipped / rotated output: the values are the same, only the addresses differ
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (X0 + i >= int(im.roi_x0) && X0 + i < int(im.roi_x1))
+                    store_pixel_oriented(im, ox + i, oy, c0[i], c1[i], c2[i]);
+            continue;
+        }
         if (im.fmt == kFmtY || im.fmt == kFmtPRGB || im.fmt == kFmtPBGR || im.fmt == kFmtPYUV) {
             const int nch = (im.fmt == kFmtY) ? 1 : 3;
 #pragma unroll

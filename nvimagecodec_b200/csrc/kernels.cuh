@@ -73,6 +73,7 @@ struct ImageDev {
     uint8_t fmt, fancy;
     uint8_t color_mode;      // K4b specialisation: 0 generic, 1 luma only, 2..5 chroma (hx,vx) = (1,1),(2,1),(1,2),(2,2) replicated, 6..8 = 3..5 with the triangle filter
     uint8_t color_unit_rows; // output rows per K4b thread (the chroma vertical factor on the fast paths)
+    uint8_t orient;          // EXIF orientation code applied when storing (0/1 = none; 5..8 transpose)
 };
 
 struct ImageState {

@@ -65,7 +65,7 @@ class Decoder:
             pass
 
     # ------------------------------------------------------------------ batch construction
-    def make_batch(self, srcs, fmt="I_RGB", rois=None, to_host=False, out_storage=None, row_align=1):
+    def make_batch(self, srcs, fmt="I_RGB", rois=None, to_host=False, out_storage=None, row_align=1, orientations=None):
         """srcs: list of bytes / uint8 arrays.  fmt: one name or a list of names per image.
         rois: None or list of None | (y0, x0, y1, x1) (nvimgcodecRegion_t order).
         to_host: write into pinned host tensors (decoder bounces through HBM + D2H)."""
@@ -73,6 +73,7 @@ class Decoder:
         b = Batch(n)
         fmts = [fmt] * n if isinstance(fmt, str) else list(fmt)
         rois = [None] * n if rois is None else list(rois)
+        orientations = [0] * n if orientations is None else list(orientations)  # EXIF codes; 5..8 swap width and height
         infos = []
         total = 0
         shapes = []
@@ -90,6 +91,8 @@ class Decoder:
             else:
                 y0, x0, y1, x1 = rois[i]
                 hgt, wid = y1 - y0, x1 - x0
+            if orientations[i] >= 5:
+                hgt, wid = wid, hgt
             f = fmts[i]
             if f in ("I_RGB", "I_BGR", "I_YUV"):
                 shape, stride = (hgt, wid, 3), wid * 3
@@ -116,6 +119,7 @@ class Decoder:
             o.format = _lib.FMT[f]
             o.buffer_is_host = 1 if to_host else 0
             o.row_stride = stride
+            o.orientation = int(orientations[i])
             if rois[i] is not None:
                 y0, x0, y1, x1 = rois[i]
                 o.roi_x0, o.roi_y0, o.roi_x1, o.roi_y1 = x0, y0, x1, y1
@@ -160,7 +164,7 @@ class Decoder:
         return [batch.status[i] for i in range(batch.n)]
 
     # ------------------------------------------------------------------ the user-facing call
-    def decode(self, srcs, fmt="I_RGB", rois=None, to_host=False, stream=None):
+    def decode(self, srcs, fmt="I_RGB", rois=None, to_host=False, stream=None, orientations=None):
         """Decode a batch.  Returns a list with one uint8 tensor per source (None where the
         stream was rejected; the per-image status codes are in ``self.last_status``)."""
         single = isinstance(srcs, (bytes, bytearray, np.ndarray))
@@ -168,7 +172,7 @@ class Decoder:
             srcs = [srcs]
             rois = None if rois is None else [rois]
         with torch.cuda.device(self.device):
-            batch = self.make_batch(srcs, fmt, rois, to_host)
+            batch = self.make_batch(srcs, fmt, rois, to_host, orientations=orientations)
             self.last_status = self.run(batch, stream)
         out = [img if st == _lib.OK else None for img, st in zip(batch.images, self.last_status)]
         return out[0] if single else out

@@ -84,6 +84,19 @@ def decode(data, fmt=FMT_I_RGB, fancy=True, roi=None):
     return out
 
 
+def apply_orientation(img, code, planar=False):
+    """EXIF orientation 1..8 applied to an HxW[xC] (or CxHxW when planar) array, as OpenCV's imread and
+    Pillow's ImageOps.exif_transpose do (tests/test_oracle.py checks both)."""
+    if code in (0, 1):
+        return img
+    a = np.moveaxis(img, 0, -1) if planar else img
+    t = (lambda x: x.swapaxes(0, 1))
+    out = {2: lambda x: x[:, ::-1], 3: lambda x: x[::-1, ::-1], 4: lambda x: x[::-1], 5: t, 6: lambda x: t(x)[:, ::-1],
+           7: lambda x: t(x)[::-1, ::-1], 8: lambda x: t(x)[::-1]}[code](a)
+    out = np.ascontiguousarray(out)
+    return np.ascontiguousarray(np.moveaxis(out, -1, 0)) if planar else out
+
+
 def coefficients(data):
     """int16 [n_mcu, blocks_per_mcu, 64], zig-zag order, MCU decode order, absolute DC."""
     a = _buf(data)

@@ -3,7 +3,8 @@
 // exactly as nvimgcodec.Decoder / nvimtrans would (include/nvimgcodec.h:1733, 1973, 2030).
 // Test infrastructure: reads a manifest, decodes the whole list as ONE batch, dumps raw pixels.
 //
-//   host_driver <extension dir> <manifest> <out dir> [decoder options] [repeat] [backend: any|gpu|hybrid|hw|cpu]
+//   host_driver <extension dir> <manifest> <out dir> [decoder options] [repeat] [backend: any|gpu|hybrid|hw|cpu] [exif]
+//   exif: decode with apply_exif_orientation = 1; images take the oriented size, as python/decoder.cpp does
 //   repeat > 0: after the first (checked, dumped) decode, time `repeat` more decodes of the same batch
 //   through nvimgcodecDecoderDecode + future wait + device sync and print images/s (used to compare
 //   decoders -- ours vs the reference's nvjpeg_ext -- through the very same framework path).
@@ -12,6 +13,7 @@
 #include <cuda_runtime_api.h>
 #include <nvimgcodec.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -49,6 +51,7 @@ int main(int argc, char** argv)
     const char* options = argc > 4 ? argv[4] : "";
     const int repeat = argc > 5 ? std::atoi(argv[5]) : 0;
     const std::string backend = argc > 6 ? argv[6] : "any";
+    const bool apply_exif = argc > 7 && std::string(argv[7]) == "exif";
     std::vector<Item> items;
     {
         std::ifstream f(manifest);
@@ -104,6 +107,8 @@ int main(int argc, char** argv)
         CHECK(nvimgcodecCodeStreamGetImageInfo(parents[i], &info));
         it.w = int(info.plane_info[0].width);
         it.h = int(info.plane_info[0].height);
+        if (apply_exif && (info.orientation.rotated / 90) % 2)
+            std::swap(it.w, it.h);
         streams[i] = parents[i];
         const bool roi = it.y1 > it.y0 && it.x1 > it.x0;
         if (roi) {
@@ -156,7 +161,7 @@ int main(int argc, char** argv)
     }
 
     nvimgcodecDecodeParams_t dp{NVIMGCODEC_STRUCTURE_TYPE_DECODE_PARAMS, sizeof(nvimgcodecDecodeParams_t), nullptr};
-    dp.apply_exif_orientation = 0;
+    dp.apply_exif_orientation = apply_exif ? 1 : 0;
     nvimgcodecFuture_t future = nullptr;
     CHECK(nvimgcodecDecoderDecode(decoder, streams.data(), images.data(), n, &dp, &future));
     CHECK(nvimgcodecFutureWaitForAll(future));

@@ -363,3 +363,20 @@ def test_ycbcr_output_and_extended_sequential(dec_fancy, dec_plain):
         ref = oracle.decode(d, oracle.FMT_I_RGB, fancy=True)
         assert np.array_equal(oracle.decode(s1, oracle.FMT_I_RGB, fancy=True), ref)
         assert np.array_equal(o.cpu().numpy(), ref)
+
+
+def test_exif_orientations_applied_while_storing(dec_fancy):
+    """All eight EXIF orientations, every output layout, with and without a crop: the stored image must be the
+    oriented crop of the plain decode (semantics pinned against OpenCV / Pillow in tests/test_oracle.py)."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    srcs = [corpus.encode(corpus.synth(75, 131, 301), 90, "420"), corpus.encode(corpus.synth(64, 40, 302), 85, "444", 3),
+            corpus.encode(corpus.synth(33, 90, 303), 90, "422"), corpus.encode(corpus.synth(50, 50, 304), 90, "411")]
+    rois = [None, (5, 3, 60, 31), None, (10, 0, 41, 50)]
+    for fmt in ("I_RGB", "P_BGR", "I_Y", "P_YUV"):
+        for code in range(1, 9):
+            outs = dec_fancy.decode(srcs, fmt, rois, orientations=[code] * len(srcs))
+            assert dec_fancy.last_status == [_lib.OK] * len(srcs)
+            for d, r, o in zip(srcs, rois, outs):
+                ref = oracle.apply_orientation(oracle.decode(d, OFMT.get(fmt, oracle.FMT_P_YUV), fancy=True, roi=r), code, planar=fmt.startswith("P_"))
+                assert np.array_equal(o.cpu().numpy(), ref), (fmt, code)

@@ -19,7 +19,7 @@ EXT_DIR = os.path.join(ROOT, "nvimagecodec_b200", "lib")
 OFMT = {"I_RGB": oracle.FMT_I_RGB, "I_BGR": oracle.FMT_I_BGR, "P_RGB": oracle.FMT_P_RGB, "P_BGR": oracle.FMT_P_BGR, "I_Y": oracle.FMT_Y}
 
 
-def _run(tmp_path, entries, options):
+def _run(tmp_path, entries, options, extra=()):
     man = tmp_path / "manifest.txt"
     lines = []
     for i, (data, fmt, roi, where) in enumerate(entries):
@@ -32,7 +32,7 @@ def _run(tmp_path, entries, options):
     out.mkdir()
     env = dict(os.environ)
     env["LD_LIBRARY_PATH"] = os.path.dirname(DRIVER) + ":" + env.get("LD_LIBRARY_PATH", "")
-    r = subprocess.run([DRIVER, EXT_DIR, str(man), str(out), options], capture_output=True, text=True, env=env, timeout=300)
+    r = subprocess.run([DRIVER, EXT_DIR, str(man), str(out), options, *extra], capture_output=True, text=True, env=env, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     status = [tuple(int(v) for v in l.split()) for l in (out / "status.txt").read_text().splitlines()]
     raws = [np.fromfile(out / f"{i}.raw", dtype=np.uint8) for i in range(len(entries))]
@@ -83,6 +83,31 @@ def test_unsupported_streams_are_declined_not_crashed(tmp_path):
     assert status[1][0] != 1
     ref = oracle.decode(good, oracle.FMT_I_RGB, fancy=True)
     assert np.array_equal(raws[0], ref.reshape(-1)) and np.array_equal(raws[2], ref.reshape(-1))
+
+
+@pytest.mark.skipif(not os.path.exists(DRIVER), reason="reference core not built (oracle/build_ref.sh)")
+def test_exif_orientation_through_the_framework(tmp_path):
+    """apply_exif_orientation = 1: the reference's parser reads the EXIF tag (src/parsers/jpeg.cpp + exif.cpp), the framework
+    hands the orientation to the decoder, the extension applies it while storing (libjpeg_turbo_ext would decline it)."""
+    import io
+
+    from PIL import Image
+    from nvimagecodec_b200 import corpus
+
+    entries, codes = [], []
+    for code in range(1, 9):
+        img = corpus.synth(45 + code, 80 - code, 400 + code)
+        ex = Image.Exif()
+        ex[0x0112] = code
+        buf = io.BytesIO()
+        Image.fromarray(img).save(buf, "JPEG", quality=88, subsampling=[0, 1, 2][code % 3], exif=ex.tobytes())
+        entries.append((buf.getvalue(), ["I_RGB", "P_RGB", "I_Y"][code % 3], None, "device" if code % 2 else "host"))
+        codes.append(code)
+    status, raws, log = _run(tmp_path, entries, ":fancy_upsampling=1", extra=("0", "any", "exif"))
+    for (data, fmt, _, _), code, st, raw in zip(entries, codes, status, raws):
+        assert st[0] == 1, (code, st, log[-1500:])
+        ref = oracle.apply_orientation(oracle.decode(data, OFMT[fmt], fancy=True), code, planar=fmt.startswith("P_"))
+        assert raw.size == ref.size and np.array_equal(raw, ref.reshape(-1)), code
 
 
 NVIMTRANS = os.path.join(ROOT, "oracle", "_ref", "nvimtrans")

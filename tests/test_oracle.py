@@ -130,3 +130,23 @@ def test_live_against_reference_glue_when_built():
             assert np.array_equal(oracle.decode(data, oracle.FMT_I_BGR, fancy), turbo.decode(data, "I_BGR", fancy))
             assert np.array_equal(oracle.decode(data, oracle.FMT_Y, fancy), turbo.decode(data, "I_Y", fancy))
             assert np.array_equal(oracle.decode(data, oracle.FMT_I_RGB, fancy, roi), turbo.decode(data, "I_RGB", fancy, roi))
+
+
+def test_orientation_helper_matches_opencv_and_pillow():
+    """oracle.apply_orientation is what the GPU path is compared with when EXIF orientation is applied."""
+    cv2 = pytest.importorskip("cv2")
+    from PIL import Image, ImageOps
+    from nvimagecodec_b200 import corpus
+
+    img = corpus.synth(40, 64, 5)
+    for code in range(1, 9):
+        ex = Image.Exif()
+        ex[0x0112] = code
+        buf = io.BytesIO()
+        Image.fromarray(img).save(buf, "JPEG", quality=90, subsampling=2, exif=ex.tobytes())
+        data = buf.getvalue()
+        want = oracle.apply_orientation(oracle.decode(data, oracle.FMT_I_RGB, True), code)
+        assert np.array_equal(want, cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR)[..., ::-1])
+        assert np.array_equal(want, np.asarray(ImageOps.exif_transpose(Image.open(io.BytesIO(data))).convert("RGB")))
+        planar = oracle.apply_orientation(oracle.decode(data, oracle.FMT_P_RGB, True), code, planar=True)
+        assert np.array_equal(planar, want.transpose(2, 0, 1))
