@@ -8,6 +8,7 @@
 #                                  -- the host framework that loads our extension in tests/
 #   oracle/_ref/host_driver        tests/host/host_driver.cpp linked against it (our own file)
 #   oracle/_ref/nvimtrans          example/nvimtrans/main.cpp, unmodified, + oracle/_ref/extensions/libnvbmp_ext.so (extensions/nvbmp)
+#   oracle/_ref/python/nvidia/nvimgcodec/           the reference's pybind11 module (python/*.cpp), unmodified: `from nvidia import nvimgcodec`
 #   oracle/_ref/extensions_nvjpeg/libnvjpeg_ext.so   extensions/nvjpeg (unmodified) over the toolkit's libnvjpeg: GPU comparison point
 #   oracle/_ref/libref_turbo.so    the reference's CPU JPEG glue (extensions/libjpeg_turbo/jpeg_mem.cpp, jpeg_handle.cpp)
 #                                  + oracle/ref_turbo_shim.cpp, compiled against the reconstructed libjpeg62 ABI header
@@ -29,7 +30,8 @@ cmp -s "$GEN/nvimgcodec_version.h.tmp" "$GEN/nvimgcodec_version.h" 2>/dev/null |
 rm -f "$GEN/nvimgcodec_version.h.tmp"
 
 INC="-I$GEN -I$REF/include -I$REF/src -I$REF -I$REF/external/NVTX/c/include -I$REF/external/boost/preprocessor/include -I$CUDA/include"
-CXXFLAGS="-std=c++20 -O2 -fPIC -DNDEBUG -w"
+# -fvisibility=hidden as in the reference's CMakeLists.txt:314 (the core and the Python binding both define nvimgcodec::Image)
+CXXFLAGS="-std=c++20 -O2 -fPIC -fvisibility=hidden -DNDEBUG -w"
 
 SRCS="nvimgcodec_capi plugin_framework codec_registry codec image_decoder image_encoder image_parser code_stream file_io_stream
  std_file_io_stream mmaped_file_io_stream image image_parser_factory image_encoder_factory image_decoder_factory image_generic_decoder
@@ -49,7 +51,7 @@ SRCS="nvimgcodec_capi plugin_framework codec_registry codec image_decoder image_
   done
   o="$OBJ/imgproc_convert_kernel_gpu.o"
   OBJS="$OBJS $o"
-  printf '%s: %s\n\tnvcc -gencode arch=compute_100a,code=sm_100a -std=c++20 -O2 -Xcompiler -fPIC -DNDEBUG -w %s -c $< -o $@\n' \
+  printf '%s: %s\n\tnvcc -gencode arch=compute_100a,code=sm_100a -std=c++20 -O2 -Xcompiler -fPIC -Xcompiler -fvisibility=hidden -DNDEBUG -w %s -c $< -o $@\n' \
       "$o" "$REF/src/imgproc/convert_kernel_gpu.cu" "$INC"
   echo "objs:$OBJS"
 } > "$OUT/ref.mk"
@@ -70,6 +72,39 @@ done
 g++ -shared -o "$OUT/extensions/libnvbmp_ext.so" "$OBJ"/nvbmp_*.bo -lpthread
 g++ -std=c++20 -O2 -w $INC -I"$REF/example/nvimtrans" "$REF/example/nvimtrans/main.cpp" -o "$OUT/nvimtrans" \
     -L"$OUT" -lnvimgcodec -Wl,-rpath,'$ORIGIN' -Wl,--allow-shlib-undefined -L"$CUDA/lib64" -lcudart_static -ldl -lpthread -lrt
+
+# ---- the reference's Python binding (python/*.cpp, pybind11 from external/pybind11, unmodified).  Its dlpack submodule is
+#      absent from the tree; the same public header ships with tvm_ffi in this image.
+PYINC="$(python - <<'PY'
+import sysconfig
+print(sysconfig.get_paths()["include"])
+PY
+)"
+PYEXT="$(python - <<'PY'
+import sysconfig
+print(sysconfig.get_config_var("EXT_SUFFIX"))
+PY
+)"
+DLPACK="$(python - <<'PY'
+import glob, os, sys
+c = glob.glob(os.path.join(sys.prefix, "lib", "python*", "site-packages", "tvm_ffi", "3rdparty", "dlpack", "include"))
+print(c[0] if c else "")
+PY
+)"
+if [ -n "$DLPACK" ] && [ -f "$PYINC/Python.h" ] && [ -d "$REF/external/pybind11/include/pybind11" ]; then
+  PYOUT="$OUT/python/nvidia/nvimgcodec"
+  mkdir -p "$PYOUT" "$OBJ/py"
+  for f in "$REF"/python/*.cpp; do
+    b="$(basename "$f" .cpp)"
+    [ "$OBJ/py/$b.po" -nt "$f" ] && continue
+    g++ -std=c++20 -O1 -fPIC -fvisibility=hidden -w -DNDEBUG $INC -I"$REF/python" -I"$REF/external/pybind11/include" -I"$DLPACK" -I"$PYINC" -c "$f" -o "$OBJ/py/$b.po" &
+  done
+  wait
+  g++ -shared -o "$PYOUT/nvimgcodec_impl$PYEXT" "$OBJ"/py/*.po "$OBJ"/imgproc_*.o "$OBJ/dynlink_dynlink_cuda.o" -L"$OUT" -lnvimgcodec \
+      -Wl,-rpath,'$ORIGIN/../../..' -Wl,--allow-shlib-undefined -L"$CUDA/lib64" -L"$CUDA/lib64/stubs" -lcudart_static -lcuda -ldl -lpthread -lrt
+  sed -e 's/@GIT_SHA@/36b4ee8/' "$REF/python/__init__.py.in" > "$PYOUT/__init__.py"
+  cp "$REF/python/nvidia/__init__.py" "$OUT/python/nvidia/__init__.py"
+fi
 
 # ---- the reference's nvjpeg_ext (wrapper over the closed nvJPEG library of the CUDA toolkit), unmodified: the GPU
 #      comparison point of SURVEY.md 8(d).  Linked directly against libnvjpeg (no dlopen stubs: those need libclang).

@@ -164,3 +164,53 @@ def test_nvimtrans_sample_uses_the_extension(tmp_path):
         got = _read_bmp(dst / (name + ".bmp"))
         ref = oracle.decode(data, oracle.FMT_I_RGB, fancy=False)
         assert np.array_equal(got, ref), name
+
+
+PYMOD = os.path.join(ROOT, "oracle", "_ref", "python")
+
+_PY_SCRIPT = r'''
+import sys, glob, numpy as np
+from nvidia import nvimgcodec
+files = sorted(glob.glob(sys.argv[1] + "/*.jpg"))
+dec = nvimgcodec.Decoder()                      # binding default options: ":fancy_upsampling=0"
+imgs = dec.decode([open(f, "rb").read() for f in files])
+for f, im in zip(files, imgs):
+    assert im is not None, f
+    assert im.buffer_kind == nvimgcodec.ImageBufferKind.STRIDED_DEVICE
+    np.save(f[:-4] + "_rgb.npy", np.asarray(im.cpu()))
+gray = dec.decode([open(f, "rb").read() for f in files], params=nvimgcodec.DecodeParams(color_spec=nvimgcodec.ColorSpec.GRAY))
+for f, im in zip(files, gray):
+    np.save(f[:-4] + "_gray.npy", np.asarray(im.cpu()))
+print("decoded", len(files), "with nvidia.nvimgcodec", nvimgcodec.__version__)
+'''
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(PYMOD, "nvidia", "nvimgcodec")), reason="reference python binding not built")
+def test_reference_python_binding_picks_the_extension(tmp_path):
+    """SURVEY.md 8(f) n1, second half: `from nvidia import nvimgcodec; nvimgcodec.Decoder().decode(...)` -- the reference's own
+    pybind11 module (python/*.cpp, unmodified) over the unmodified core.  The extension directory holds only our decoder,
+    so these pixels come from the CUDA path; the binding asks for I_RGB / I_Y with ":fancy_upsampling=0"."""
+    import shutil
+    import sys
+
+    from nvimagecodec_b200 import corpus
+
+    ext = tmp_path / "extensions"
+    ext.mkdir()
+    shutil.copy(os.path.join(EXT_DIR, "libb200jpeg_ext.so"), ext / "libb200jpeg_ext.so")
+    datas = {}
+    for i, (h, w, samp, rst) in enumerate([(240, 320, "420", 0), (199, 301, "444", 5), (128, 96, "422", 2), (1080, 1920, "420", 0)]):
+        datas[f"img{i}"] = corpus.encode(corpus.synth(h, w, 740 + i), 88, samp, rst)
+        (tmp_path / f"img{i}.jpg").write_bytes(datas[f"img{i}"])
+    (tmp_path / "run.py").write_text(_PY_SCRIPT)
+    env = dict(os.environ)
+    env["NVIMGCODEC_EXTENSIONS_PATH"] = str(ext)
+    env["PYTHONPATH"] = PYMOD + ":" + env.get("PYTHONPATH", "")
+    env["LD_LIBRARY_PATH"] = os.path.join(ROOT, "oracle", "_ref") + ":" + env.get("LD_LIBRARY_PATH", "")
+    r = subprocess.run([sys.executable, str(tmp_path / "run.py"), str(tmp_path)], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    for name, data in datas.items():
+        rgb = np.load(tmp_path / (name + "_rgb.npy"))
+        assert np.array_equal(rgb, oracle.decode(data, oracle.FMT_I_RGB, fancy=False)), name
+        gray = np.load(tmp_path / (name + "_gray.npy"))
+        assert np.array_equal(gray.reshape(gray.shape[0], gray.shape[1]), oracle.decode(data, oracle.FMT_Y, fancy=False)), name
