@@ -352,8 +352,8 @@ def main():
         peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
         # algorithmic bytes per launch of each kernel (DESIGN.md "Kernels"), for the N=1 shard of rank 0
         kbytes = {
-            "scan(K0)": 2 * comp_bytes, "huff_sync(K1)": comp_bytes, "verify_scan(K2)": 40 * dec.stat(_lib.STAT_NUM_SUBSEQ),
-            "huff_write(K3)": comp_bytes + 2 * n_coefs, "idct(K4a)": 2 * n_coefs + planes_bytes,
+            "scan(K0)": 2 * comp_bytes, "huff_sync(K1)": comp_bytes, "verify_scan(K2)": 16 * dec.stat(_lib.STAT_NUM_SUBSEQ),
+            "huff_write(K3)": comp_bytes + 2 * n_coefs, "dc_scan(K3b)": 8 * (n_coefs // 64), "idct(K4a)": 2 * n_coefs + planes_bytes,
             "color(K4b)": planes_bytes + out_bytes,
         }
         top = max(stages, key=stages.get) if stages else None
@@ -367,7 +367,7 @@ def main():
                 traffic = {k.replace("_kernel", ""): v["dram_bytes"] for k, v in json.load(f)["kernels"].items()}
         except Exception:
             pass
-        ncu_name = {"scan(K0)": "scan_scatter", "huff_sync(K1)": "huff_sync", "verify_scan(K2)": "verify_scan", "huff_write(K3)": "huff_write",
+        ncu_name = {"scan(K0)": "scan_scatter", "huff_sync(K1)": "huff_sync", "verify_scan(K2)": "verify_scan", "huff_write(K3)": "huff_write", "dc_scan(K3b)": "dc_scan",
                     "idct(K4a)": "idct", "color(K4b)": "color"}
         if top:
             ach = kbytes[top] / (stages[top] * 1e-3) / 1e9

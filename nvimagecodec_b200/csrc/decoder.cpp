@@ -11,7 +11,7 @@ namespace b200jpeg {
 
 namespace {
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-const char* kStageNames[] = {"scan(K0)", "huff_sync(K1)", "verify_scan(K2)", "huff_write(K3)", "idct(K4a)", "color(K4b)"};
+const char* kStageNames[] = {"scan(K0)", "huff_sync(K1)", "verify_scan(K2)", "huff_write(K3)", "dc_scan(K3b)", "idct(K4a)", "color(K4b)"};
 } // namespace
 
 bool DeviceBuffer::ensure(size_t bytes, size_t* total)
@@ -280,6 +280,10 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.mcu_row_hi = uint16_t(mcu_row_hi);
         im.write_blk_lo = uint32_t(mcu_row_lo) * uint32_t(hd.mcus_x) * uint32_t(hd.blocks_per_mcu);
         im.write_blk_hi = uint32_t(mcu_row_hi) * uint32_t(hd.mcus_x) * uint32_t(hd.blocks_per_mcu);
+        {   // DC differences are needed from the last predictor reset at or before the first wanted block
+            const uint32_t ri_blocks = uint32_t(hd.restart_interval) * uint32_t(hd.blocks_per_mcu);
+            im.dc_blk_lo = ri_blocks ? im.write_blk_lo / ri_blocks * ri_blocks : 0u;
+        }
         int b = 0;
         uint32_t idct_blocks = 0;
         for (int c = 0; c < hd.ncomp; ++c) {
@@ -423,13 +427,13 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     const size_t so_out = so;
     so = align_up(so + 4ull * n_sub, 256);
     const size_t so_info = so;
-    so = align_up(so + 16ull * n_sub, 256);
+    so = align_up(so + 4ull * n_sub, 256);
     const size_t so_start = so;
-    so = align_up(so + 16ull * n_sub, 256);
+    so = align_up(so + 4ull * n_sub, 256);
     const size_t so_stats = so;
     so += 256;
     const size_t so_mask = so;
-    so = align_up(so + coef_elems / 64, 256);
+    so = align_up(so + 4ull * (coef_elems / 64), 256);
 
     coef_bytes_ = coef_elems * sizeof(int16_t);
     if (!upload_host_.ensure(upload_bytes) || !state_host_.ensure(sizeof(ImageState) * std::max(nd, 1)))
@@ -522,10 +526,10 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.bnd = reinterpret_cast<uint32_t*>(sc + so_bnd);
     bd_.sub_in = reinterpret_cast<uint32_t*>(sc + so_in);
     bd_.sub_out = reinterpret_cast<uint32_t*>(sc + so_out);
-    bd_.sub_info = reinterpret_cast<int4*>(sc + so_info);
-    bd_.sub_start = reinterpret_cast<int4*>(sc + so_start);
+    bd_.sub_info = reinterpret_cast<uint32_t*>(sc + so_info);
+    bd_.sub_start = reinterpret_cast<uint32_t*>(sc + so_start);
     bd_.sync_stats = reinterpret_cast<uint32_t*>(sc + so_stats);
-    bd_.blkmask = sc + so_mask;
+    bd_.blkrec = reinterpret_cast<uint32_t*>(sc + so_mask);
     bd_.cmp = cmp_.as<uint32_t>();
     bd_.coef = coef_.as<int16_t>();
     bd_.planes = planes_.as<uint8_t>();
@@ -566,10 +570,12 @@ int Decoder::execute(cudaStream_t stream)
     mark(3, stream);
     launches_ += launch_write(bd_, false, stream); // writes every coefficient exactly once: no clearing pass
     mark(4, stream);
-    launches_ += launch_idct(bd_, false, stream);
+    launches_ += launch_dc_scan(bd_, false, stream);
     mark(5, stream);
-    launches_ += launch_color(bd_, false, stream);
+    launches_ += launch_idct(bd_, false, stream);
     mark(6, stream);
+    launches_ += launch_color(bd_, false, stream);
+    mark(7, stream);
     ev_recorded_ = profiling_ && ev_valid_;
     if (!cuda_ok(cudaGetLastError(), "kernel launch"))
         return B200JPEG_ERR_CUDA;
@@ -640,6 +646,7 @@ int Decoder::finish_wait(int* status, cudaStream_t stream)
             ++rounds;
         }
         launches_ += launch_write(bd_, true, stream);
+        launches_ += launch_dc_scan(bd_, true, stream);
         launches_ += launch_idct(bd_, true, stream);
         launches_ += launch_color(bd_, true, stream);
         if (!read_states())
@@ -730,14 +737,17 @@ int Decoder::copy_coefficients(int index, int16_t* host_out, size_t cap_elems)
     cudaSetDevice(device_);
     if (!cuda_ok(cudaMemcpy(host_out, bd_.coef + im.coef_off, elems * sizeof(int16_t), cudaMemcpyDeviceToHost), "coefficient copy"))
         return B200JPEG_ERR_CUDA;
-    // groups K3 skipped (all zero) hold stale bytes on the device: blank them using the per-block masks
-    std::vector<uint8_t> masks(im.total_blocks);
-    if (!cuda_ok(cudaMemcpy(masks.data(), bd_.blkmask + im.coef_off / 64, masks.size(), cudaMemcpyDeviceToHost), "mask copy"))
+    // groups K3 skipped (all zero) hold stale bytes on the device: blank them using the per-block records,
+    // which also carry the DC value (K3 never stores it into the coefficient array)
+    std::vector<uint32_t> recs(im.total_blocks);
+    if (!cuda_ok(cudaMemcpy(recs.data(), bd_.blkrec + im.coef_off / 64, recs.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost), "record copy"))
         return B200JPEG_ERR_CUDA;
-    for (size_t b = 0; b < masks.size(); ++b)
+    for (size_t b = 0; b < recs.size(); ++b) {
         for (int g = 0; g < 8; ++g)
-            if (!((masks[b] >> g) & 1))
+            if (!((recs[b] >> g) & 1))
                 std::memset(host_out + b * 64 + g * 8, 0, 16);
+        host_out[b * 64] = int16_t(recs[b] >> 16);
+    }
     return B200JPEG_OK;
 }
 

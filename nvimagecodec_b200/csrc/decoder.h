@@ -105,7 +105,7 @@ class Decoder {
 
     // profiling
     bool profiling_ = false;
-    static constexpr int kStages = 6;
+    static constexpr int kStages = 7;
     cudaEvent_t ev_[kStages + 1] = {};
     bool ev_valid_ = false;
     bool ev_recorded_ = false;

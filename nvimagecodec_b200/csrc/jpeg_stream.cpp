@@ -203,7 +203,8 @@ StreamStatus parse_stream(const uint8_t* d, size_t n, StreamHeader* hdr)
 }
 
 // What a decoded symbol does, packed for the device (kernels.cu decode_subsequence):
-//   bits [0,5)  code length, 0 = not in the first-level table
+//   bits [0,5)  code length + magnitude bits = how far the bit position advances (<= 31);
+//               0 = not in the first-level table
 //   bits [5,9)  number of magnitude bits that follow the code
 //   bits [9,16) how far the zig-zag index advances: DC -> 1; AC run/size -> run + 1;
 //               ZRL (0xF0) -> 16; EOB (0x00) -> 64 (ends the block)
@@ -217,7 +218,7 @@ uint16_t pack_symbol(bool is_dc, int len, int sym)
         skip = (sym >> 4) + 1;
     else
         skip = ((sym >> 4) == 15) ? 16 : 64;
-    return uint16_t(len | (size << 5) | (skip << 9));
+    return uint16_t((len + size) | (size << 5) | (skip << 9));
 }
 
 void build_huff_table(const HuffSpec& spec, bool is_dc, HuffTableDev* out)

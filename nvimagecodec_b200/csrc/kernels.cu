@@ -291,7 +291,6 @@ struct DecodeResult {
     uint32_t state;     // exit state
     int32_t blk;        // block index at exit (relative to entry unless restarted, then absolute)
     int32_t restarted;  // crossed at least one restart boundary
-    int32_t dc0, dc1, dc2;
     uint32_t err;
 };
 
@@ -303,7 +302,8 @@ struct StreamView {
     uint32_t bpm, blk_comp, blk_tab;
     uint32_t ri_blocks;      // restart_interval * bpm
     uint32_t total_blocks;
-    uint32_t write_lo, write_hi; // K3: only blocks in [write_lo, write_hi) are wanted (MCU rows a ROI touches)
+    uint32_t write_lo, write_hi; // K3: only blocks in [write_lo, write_hi) are wanted (MCU rows a ROI touches) ...
+    uint32_t dc_lo;              //     ... but DC differences from dc_lo on: the predictor chain K3b integrates
     uint32_t comp_mask;          // K3: bit c set = component c is wanted (luma only for Y output)
 };
 
@@ -342,56 +342,101 @@ struct BlockWriter {
         else
             lo |= v;
     }
-    // end of block: last group out, then the presence mask (all-zero groups are never written;
-    // K4a substitutes zeros for them)
-    __device__ __forceinline__ void finish(int16_t* __restrict__ blk_base, uint8_t* __restrict__ mask_out)
+    // end of block: last group out, then the block record = presence mask (all-zero groups are never
+    // written; K4a substitutes zeros for them) | DC difference << 16 (K3b turns it into the DC value)
+    __device__ __forceinline__ void finish(int16_t* __restrict__ blk_base, uint32_t* __restrict__ rec_out, int32_t dc_diff)
     {
         store_group(blk_base);
-        *mask_out = uint8_t(mask);
+        *rec_out = mask | (uint32_t(dc_diff) << 16);
     }
 };
 
-// Per-block-in-MCU constants, one 64-bit word per block index, built once per CTA in shared memory:
-//   .x = byte offset of the block's DC table inside the table set
-//   .y = byte offset of its AC table | component << 24 | next block index << 28
+// Per-block-in-MCU constants, one 16-byte entry per block index, built once per CTA in shared memory.
+// The addresses are 32-bit shared-window addresses, so the decode loop forms every table access with
+// one add:
+//   .x = address of the block's DC table      .y = address of its AC table
+//   .z = address of the NEXT block's entry    .w = component | block index << 8 | (1 << component) << 16
 struct BlockTable {
-    uint2 e[kMaxBlocksPerMcu];
+    uint4 e[kMaxBlocksPerMcu];
 };
-__device__ __forceinline__ void build_block_table(BlockTable* bt, const ImageDev& im)
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a)
+{
+    uint16_t v;
+    asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint4 lds_v4(uint32_t a)
+{
+    uint4 v;
+    asm("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void build_block_table(BlockTable* bt, const HuffSetDev* s_hs, const ImageDev& im)
 {
     if (threadIdx.x < im.bpm) {
         const uint32_t b = threadIdx.x;
         const uint32_t comp = (im.blk_comp >> (2 * b)) & 3u;
-        const uint32_t dc = ((im.blk_tab >> b) & 1u) * uint32_t(sizeof(HuffTableDev));
-        const uint32_t ac = (2u + ((im.blk_tab >> (16 + b)) & 1u)) * uint32_t(sizeof(HuffTableDev));
+        const uint32_t dc = (im.blk_tab >> b) & 1u;
+        const uint32_t ac = 2u + ((im.blk_tab >> (16 + b)) & 1u);
         const uint32_t next = (b + 1u == im.bpm) ? 0u : b + 1u;
-        bt->e[b] = make_uint2(dc, ac | (comp << 24) | (next << 28));
+        bt->e[b] = make_uint4(smem_addr(&s_hs->t[dc]), smem_addr(&s_hs->t[ac]), smem_addr(&bt->e[next]), comp | (b << 8) | ((1u << comp) << 16));
     }
 }
 
+// Bit reader of the decode loop: the 64 bits at the read position in (whi, wlo), the following word
+// prefetched in wnx, wp -> the word held in whi.  A symbol advances the position by at most 31 bits,
+// i.e. across at most one word boundary; the refill is predicated, not branched: a branch here is taken
+// by some lane of the warp in nearly every iteration and then costs every lane its issue slots.
+struct BitReader {
+    uint32_t whi, wlo, wnx;
+    const uint32_t* wp;
+    __device__ __forceinline__ void seek(const uint32_t* words, uint32_t p)
+    {
+        wp = words + (p >> 5);
+        whi = __ldg(wp);
+        wlo = __ldg(wp + 1);
+        wnx = __ldg(wp + 2);
+    }
+    __device__ __forceinline__ uint32_t window(uint32_t p) const { return __funnelshift_l(wlo, whi, p & 31u); }
+    // p_old -> p_new crossed a word boundary?  then shift the words up and fetch the next one
+    __device__ __forceinline__ void advance(uint32_t p_old, uint32_t p_new)
+    {
+        asm("{\n\t.reg .pred q;\n\t"
+            "setp.gt.u32 q, %4, 31;\n\t"
+            "@q mov.b32 %0, %1;\n\t"
+            "@q mov.b32 %1, %2;\n\t"
+            "@q add.u64 %3, %3, 4;\n\t"
+            "@q ld.global.nc.u32 %2, [%3+8];\n\t}"
+            : "+r"(whi), "+r"(wlo), "+r"(wnx), "+l"(wp)
+            : "r"(p_old ^ p_new));
+    }
+};
+
 // Decodes the code words that start in [start bit given by in_state, end_bit).
-//   kWrite == false (K1): only the decoder state, the block count and the DC sums are tracked.
+//   kWrite == false (K1): only the decoder state and the block count are tracked -- no symbol values.
 //   kWrite == true  (K3): the thread OWNS every block that starts inside its range: a block already
 //     under way at entry is skipped (its owner, the previous thread, finishes it), and the block
-//     under way at end_bit is decoded to its end.
+//     under way at end_bit is decoded to its end.  AC coefficients go out as 16-byte groups, the DC
+//     DIFFERENCE goes into the block record; K3b integrates the differences afterwards, so neither
+//     kernel carries DC predictors.
+// The per-symbol path is straight-line: table address kept in a register, word refill and (K1) the
+// switch to the next block's tables predicated.  Only the rare events branch (restart boundary, code
+// longer than the first-level table, K3's group / block stores).
 template <bool kWrite>
 __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const HuffSetDev* __restrict__ hs, const BlockTable* __restrict__ bt,
-    uint32_t base_bit, uint32_t end_bit, uint32_t in_state, int32_t blk, int32_t dc0, int32_t dc1, int32_t dc2, int16_t* __restrict__ coef,
-    uint8_t* __restrict__ blkmask, DecodeResult& out)
+    uint32_t base_bit, uint32_t end_bit, uint32_t in_state, int32_t blk, int16_t* __restrict__ coef, uint32_t* __restrict__ blkrec,
+    DecodeResult& out)
 {
     out.err = 0;
     out.restarted = 0;
     if (in_state & kStateDone) {
         out.state = kStateDone;
         out.blk = blk;
-        out.dc0 = dc0;
-        out.dc1 = dc1;
-        out.dc2 = dc2;
         return;
     }
     uint32_t p = base_bit + (in_state & 63u);
     uint32_t z = (in_state >> 6) & 63u;
-    uint32_t b = (in_state >> 12) & 15u;
     // first boundary strictly after p
     uint32_t r = 0;
     if (sv.nb > 1) {
@@ -408,18 +453,23 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
     uint32_t next_bnd = (r == sv.nb - 1) ? sv.total_bits : __ldg(sv.bnd + r) * 8u;
     // one comparison per symbol covers both "subsequence finished" and "restart boundary close"
     uint32_t limit = min(end_bit, max(next_bnd, 7u) - 7u);
-    uint32_t widx = p >> 5;
-    uint32_t whi = __ldg(sv.words + widx), wlo = __ldg(sv.words + widx + 1);
-    const uint8_t* hbase = reinterpret_cast<const uint8_t*>(hs);
-    uint2 binfo = bt->e[b]; // .x: DC table offset, .y: AC table offset | comp << 24 | next b << 28
+    const uint32_t s_hs = smem_addr(hs), s_bt = smem_addr(bt);
+    BitReader br;
+    br.seek(sv.words, p);
+    uint4 bi = lds_v4(s_bt + ((in_state >> 12) & 15u) * 16u); // tables / component of the block under way
+    uint32_t taddr = (z == 0u) ? bi.x : bi.y;                 // table of the next symbol
     bool owned = (z == 0u); // kWrite: is the block under way mine (it started inside my range)?
-    // ... and is it wanted at all (inside the ROI's MCU rows, component needed)?
-    bool wanted = kWrite && uint32_t(blk) - sv.write_lo < sv.write_hi - sv.write_lo && ((sv.comp_mask >> ((binfo.y >> 24) & 3u)) & 1u);
+    // ... and is it wanted at all: its DC difference (component needed, not past the ROI's MCU rows), its AC
+    // coefficients (inside those rows)?  Both imply blk < total_blocks.
+    auto want_dc = [&](int32_t k, uint32_t w) { return uint32_t(k) - sv.dc_lo < sv.write_hi - sv.dc_lo && ((sv.comp_mask >> (w & 3u)) & 1u); };
+    bool w_dc = kWrite && owned && want_dc(blk, bi.w);
+    bool w_ac = w_dc && uint32_t(blk) >= sv.write_lo;
+    int32_t dc_diff = 0;
     BlockWriter bw;
     bw.reset();
     bool done = false;
     for (;;) {
-        const uint32_t win = __funnelshift_l(wlo, whi, p & 31u);
+        const uint32_t win = br.window(p);
         if (p >= limit) {
             // End of a restart interval (or of the stream): either the decoder already ran across the
             // boundary (only an unsynchronised one can), or fewer than 8 bits remain and they are all
@@ -439,20 +489,18 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
                 ++r;
                 next_bnd = (r == sv.nb - 1) ? sv.total_bits : __ldg(sv.bnd + r) * 8u;
                 limit = min(end_bit, max(next_bnd, 7u) - 7u);
-                if (kWrite && (z != 0u || b != 0u || uint32_t(blk) != r * sv.ri_blocks))
+                if (kWrite && (z != 0u || ((bi.w >> 8) & 15u) != 0u || uint32_t(blk) != r * sv.ri_blocks))
                     out.err |= kFlagOverrun;
                 blk = int32_t(r * sv.ri_blocks);
                 out.restarted = 1;
                 z = 0;
-                b = 0;
                 owned = true;
                 bw.reset();
-                dc0 = dc1 = dc2 = 0;
-                binfo = bt->e[0];
-                wanted = kWrite && uint32_t(blk) - sv.write_lo < sv.write_hi - sv.write_lo && (sv.comp_mask & 1u);
-                widx = p >> 5;
-                whi = __ldg(sv.words + widx);
-                wlo = __ldg(sv.words + widx + 1);
+                bi = lds_v4(s_bt);
+                taddr = bi.x;
+                w_dc = kWrite && want_dc(blk, bi.w);
+                w_ac = w_dc && uint32_t(blk) >= sv.write_lo;
+                br.seek(sv.words, p);
                 continue;
             }
             if (p >= end_bit && (!kWrite || z == 0u || !owned))
@@ -461,10 +509,10 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
             // owns past its range -- keep taking this path until one of the exits above fires
         }
         const bool is_dc = (z == 0u);
-        const HuffTableDev* tab = reinterpret_cast<const HuffTableDev*>(hbase + (is_dc ? binfo.x : (binfo.y & 0xFFFFFFu)));
-        uint32_t e = tab->lut[win >> (32 - kLutBits)];
+        uint32_t e = lds_u16(taddr + ((win >> (31 - kLutBits)) & ((2u << kLutBits) - 2u)));
         if ((e & 31u) == 0u) {
             // code longer than the first-level table: second-level lookup on the 16-bit window
+            const HuffTableDev* tab = reinterpret_cast<const HuffTableDev*>(reinterpret_cast<const uint8_t*>(hs) + (taddr - s_hs));
             const uint32_t i2 = (win >> 16) - tab->first16; // wraps to a huge value below first16
             e = (i2 < tab->n2) ? tab->lut2[i2] : 0u;
             if (tab->n2 == 0u && (win >> 16) >= tab->first16) {
@@ -483,59 +531,55 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
                 out.err |= kFlagBadHuffman;
             }
         }
-        const uint32_t len = e & 31u, size = (e >> 5) & 15u, skip = e >> 9;
-        const uint32_t rest = win << len;
-        p += len + size;
-        if ((p >> 5) != widx) {
-            ++widx;
-            whi = wlo;
-            wlo = __ldg(sv.words + widx + 1);
-        }
-        if (kWrite || is_dc) {
+        const uint32_t tot = e & 31u, size = (e >> 5) & 15u, skip = e >> 9;
+        br.advance(p, p + tot);
+        p += tot;
+        if (kWrite) {
+            // the value the symbol carries (T.81 F.2.2.1 EXTEND)
+            const uint32_t rest = win << (tot - size);
             const uint32_t mag = __funnelshift_l(rest, 0u, size); // top `size` bits, 0 when size == 0
             const int32_t val = (rest >> 31) ? int32_t(mag) : int32_t(mag) - int32_t((1u << size) - 1u);
-            const uint32_t comp = (binfo.y >> 24) & 3u;
-            int32_t put_val = val;
-            if (is_dc) {
-                dc0 += (comp == 0u) ? val : 0;
-                dc1 += (comp == 1u) ? val : 0;
-                dc2 += (comp == 2u) ? val : 0;
-                put_val = comp == 0u ? dc0 : (comp == 1u ? dc1 : dc2);
-            }
-            if (kWrite && owned && wanted && (is_dc || size != 0u)) {
+            dc_diff = is_dc ? val : dc_diff;
+            if (w_ac && !is_dc && size != 0u) {
                 const uint32_t pos = z + skip - 1u; // zig-zag position of the coefficient this symbol carries
                 if (pos > 63u)
                     out.err |= kFlagBadHuffman;
-                else if (uint32_t(blk) < sv.total_blocks)
-                    bw.put(coef + size_t(blk) * 64, pos, put_val);
                 else
-                    out.err |= kFlagOverrun;
+                    bw.put(coef + size_t(blk) * 64, pos, val);
             }
+            z += skip;
+            if (z > 63u) {
+                if (w_dc)
+                    bw.finish(coef + size_t(blk) * 64, blkrec + blk, dc_diff);
+                bw.reset();
+                owned = true;
+                z = 0;
+                ++blk;
+                bi = lds_v4(bi.z);
+                w_dc = want_dc(blk, bi.w);
+                w_ac = w_dc && uint32_t(blk) >= sv.write_lo;
+            }
+        } else {
+            z += skip;
+            // end of block: next block's entry, predicated (some lane ends a block in most iterations)
+            asm("{\n\t.reg .pred q;\n\t"
+                "setp.gt.u32 q, %4, 63;\n\t"
+                "@q ld.shared.v4.u32 {%0,%1,%2,%3}, [%2];\n\t}"
+                : "+r"(bi.x), "+r"(bi.y), "+r"(bi.z), "+r"(bi.w)
+                : "r"(z));
+            blk += (z > 63u) ? 1 : 0;
+            z = (z > 63u) ? 0u : z;
         }
-        z += skip;
-        if (z > 63u) {
-            if (kWrite && owned && wanted && uint32_t(blk) < sv.total_blocks)
-                bw.finish(coef + size_t(blk) * 64, blkmask + blk);
-            bw.reset();
-            owned = true;
-            z = 0;
-            ++blk;
-            b = binfo.y >> 28;
-            binfo = bt->e[b];
-            wanted = kWrite && uint32_t(blk) - sv.write_lo < sv.write_hi - sv.write_lo && ((sv.comp_mask >> ((binfo.y >> 24) & 3u)) & 1u);
-        }
+        taddr = (z == 0u) ? bi.x : bi.y;
     }
     if (done) {
         out.state = kStateDone;
         if (kWrite && (z != 0u || uint32_t(blk) != sv.total_blocks))
             out.err |= kFlagOverrun;
     } else {
-        out.state = ((p - end_bit) & 63u) | (z << 6) | (b << 12);
+        out.state = ((p - end_bit) & 63u) | (z << 6) | (((bi.w >> 8) & 15u) << 12);
     }
     out.blk = blk;
-    out.dc0 = dc0;
-    out.dc1 = dc1;
-    out.dc2 = dc2;
 }
 
 __device__ __forceinline__ void load_huff_set(HuffSetDev* s_hs, const HuffSetDev* g_hs)
@@ -560,6 +604,7 @@ __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageD
     sv.total_blocks = im.total_blocks;
     sv.write_lo = im.write_blk_lo;
     sv.write_hi = im.write_blk_hi;
+    sv.dc_lo = im.dc_blk_lo;
     sv.comp_mask = im.ncomp_needed >= 3 ? 7u : 1u;
     return sv;
 }
@@ -578,16 +623,13 @@ __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageD
 struct SyncShared {
     uint32_t in[kSeqLogical];
     uint32_t out[kSeqLogical];
-    int4 info[kSeqLogical];
+    uint32_t info[kSeqLogical];     // block count (or absolute index | 1 << 31 after a restart)
     uint32_t queue[2][kSeqLogical]; // work lists of the current and the next fixed-point round
     uint8_t fresh[kSeqLogical];     // (re)computed by this CTA -> has to be written back
     uint32_t count[2];
 };
 
-__device__ __forceinline__ int4 pack_info(const DecodeResult& r)
-{
-    return make_int4(r.blk | (r.restarted ? int32_t(0x80000000u) : 0), r.dc0, r.dc1, r.dc2);
-}
+__device__ __forceinline__ uint32_t pack_info(const DecodeResult& r) { return uint32_t(r.blk) | (r.restarted ? 0x80000000u : 0u); }
 
 // A CTA of kSeqThreads threads owns kSeqLogical = kSeqMult * kSeqThreads consecutive subsequences
 // ("logical threads" l = m * kSeqThreads + t): the full pass runs kSeqMult times back to back, and the
@@ -612,7 +654,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     if (first_k >= st.n_sub)
         return;
     load_huff_set(s_hs, bd.huff + im.huff_set);
-    build_block_table(s_bt, im);
+    build_block_table(s_bt, s_hs, im);
     const StreamView sv = make_view(bd, im, st);
     const int t = threadIdx.x;
     const int k0 = int(first_k) - kSeqWarm; // subsequence of logical thread 0 (may be negative)
@@ -652,13 +694,13 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
             if (active && k > 0 && !no_warm) {
                 // round 0: probe the tail of the previous subsequence
                 const uint32_t pb = uint32_t(k) * S - S / 4;
-                decode_subsequence<false>(sv, s_hs, s_bt, pb, uint32_t(k) * S, 0u, 0, 0, 0, 0, nullptr, nullptr, res);
+                decode_subsequence<false>(sv, s_hs, s_bt, pb, uint32_t(k) * S, 0u, 0, nullptr, nullptr, res);
                 in = res.state;
             }
             // round 1: everybody
             res.state = kStateDone;
             if (active) {
-                decode_subsequence<false>(sv, s_hs, s_bt, uint32_t(k) * S, uint32_t(k + 1) * S, in, 0, 0, 0, 0, nullptr, nullptr, res);
+                decode_subsequence<false>(sv, s_hs, s_bt, uint32_t(k) * S, uint32_t(k + 1) * S, in, 0, nullptr, nullptr, res);
                 sh.info[l] = pack_info(res);
                 sh.fresh[l] = 1;
             }
@@ -686,7 +728,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
         for (uint32_t i = uint32_t(t); i < n; i += kSeqThreads) {
             const uint32_t item = sh.queue[cur][i];
             const uint32_t kk = uint32_t(k0 + int(item));
-            decode_subsequence<false>(sv, s_hs, s_bt, kk * S, (kk + 1) * S, sh.in[item], 0, 0, 0, 0, nullptr, nullptr, res);
+            decode_subsequence<false>(sv, s_hs, s_bt, kk * S, (kk + 1) * S, sh.in[item], 0, nullptr, nullptr, res);
             sh.out[item] = res.state; // nobody reads out[] before the barrier below
             sh.info[item] = pack_info(res);
         }
@@ -725,18 +767,15 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
 
 // K2.  One CTA per image: (a) every subsequence's entry state must equal its predecessor's exit
 // state (else the image is dirty and goes through the fix-up path), (b) segmented exclusive scan
-// of (block count, DC sums) where a restart boundary resets the running value.
+// of the block counts where a restart boundary resets the running value to the absolute index.
 struct ScanElem {
-    int32_t f, blk, d0, d1, d2;
+    int32_t f, blk;
 };
 __device__ __forceinline__ ScanElem scan_combine(const ScanElem& a, const ScanElem& b)
 {
     ScanElem r;
     r.f = a.f | b.f;
     r.blk = b.f ? b.blk : a.blk + b.blk;
-    r.d0 = b.f ? b.d0 : a.d0 + b.d0;
-    r.d1 = b.f ? b.d1 : a.d1 + b.d1;
-    r.d2 = b.f ? b.d2 : a.d2 + b.d2;
     return r;
 }
 __device__ __forceinline__ ScanElem scan_shfl_up(const ScanElem& a, int d)
@@ -744,9 +783,6 @@ __device__ __forceinline__ ScanElem scan_shfl_up(const ScanElem& a, int d)
     ScanElem r;
     r.f = __shfl_up_sync(0xffffffffu, a.f, d);
     r.blk = __shfl_up_sync(0xffffffffu, a.blk, d);
-    r.d0 = __shfl_up_sync(0xffffffffu, a.d0, d);
-    r.d1 = __shfl_up_sync(0xffffffffu, a.d1, d);
-    r.d2 = __shfl_up_sync(0xffffffffu, a.d2, d);
     return r;
 }
 
@@ -762,27 +798,23 @@ __global__ void __launch_bounds__(256) verify_scan_kernel(BatchDev bd, int fix_m
         return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
-        s_carry = ScanElem{0, 0, 0, 0, 0};
+        s_carry = ScanElem{0, 0};
         s_dirty = 0;
     }
     __syncthreads();
     for (uint32_t c = 0; c < st.n_sub; c += 256) {
         const uint32_t k = c + threadIdx.x;
-        ScanElem e{0, 0, 0, 0, 0};
+        ScanElem e{0, 0};
         if (k < st.n_sub) {
             const uint32_t g = im.sub_off + k;
             const uint32_t in = bd.sub_in[g];
             const uint32_t want = k ? bd.sub_out[g - 1] : 0u;
             if (in != want)
                 atomicOr(&s_dirty, 1u);
-            const int4 info = bd.sub_info[g];
-            e.f = (info.x < 0) ? 1 : 0;
-            e.blk = info.x & 0x7FFFFFFF;
-            e.d0 = info.y;
-            e.d1 = info.z;
-            e.d2 = info.w;
+            const uint32_t info = bd.sub_info[g];
+            e.f = int32_t(info >> 31);
+            e.blk = int32_t(info & 0x7FFFFFFFu);
         }
-        const ScanElem own = e;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const ScanElem o = scan_shfl_up(e, d);
@@ -798,9 +830,8 @@ __global__ void __launch_bounds__(256) verify_scan_kernel(BatchDev bd, int fix_m
         // exclusive value = pre (+) inclusive-of-previous-lane
         ScanElem prev = scan_shfl_up(e, 1);
         ScanElem ex = (lane == 0) ? pre : scan_combine(pre, prev);
-        (void)own;
         if (k < st.n_sub)
-            bd.sub_start[im.sub_off + k] = make_int4(ex.blk, ex.d0, ex.d1, ex.d2);
+            bd.sub_start[im.sub_off + k] = uint32_t(ex.blk);
         __syncthreads();
         if (threadIdx.x == 255)
             s_carry = scan_combine(pre, e);
@@ -817,8 +848,8 @@ __global__ void __launch_bounds__(256) verify_scan_kernel(BatchDev bd, int fix_m
 }
 
 // K3.  Same CTA shape as K1; every thread re-decodes its subsequence from the verified entry
-// state, now knowing its absolute block index and DC predictors, and writes the coefficient
-// blocks it owns (zig-zag order, MCU decode order, absolute DC) as whole 16-byte groups.
+// state, now knowing its absolute block index, and writes the coefficient blocks it owns (zig-zag
+// order, MCU decode order) as whole 16-byte groups plus one record per block (group mask, DC difference).
 __global__ void __launch_bounds__(kSeqThreads, 5) huff_write_kernel(BatchDev bd, int redo_only)
 {
     extern __shared__ uint4 s_raw[];
@@ -834,7 +865,7 @@ __global__ void __launch_bounds__(kSeqThreads, 5) huff_write_kernel(BatchDev bd,
     if (first_k >= st.n_sub)
         return;
     load_huff_set(s_hs, bd.huff + im.huff_set);
-    build_block_table(s_bt, im);
+    build_block_table(s_bt, s_hs, im);
     __syncthreads();
     const uint32_t k = first_k + threadIdx.x;
     if (k >= st.n_sub)
@@ -842,24 +873,133 @@ __global__ void __launch_bounds__(kSeqThreads, 5) huff_write_kernel(BatchDev bd,
     const StreamView sv = make_view(bd, im, st);
     const uint32_t g = im.sub_off + k;
     const uint32_t in = bd.sub_in[g];
-    const int4 start = bd.sub_start[g];
+    const uint32_t start = bd.sub_start[g];
     DecodeResult res;
     uint32_t err = 0;
-    // ROI: nothing to write if every block this thread can own lies outside the wanted MCU rows.  (The
-    // end-of-stream consistency check then falls to whoever decodes the tail; a ROI that excludes the
-    // last MCU row skips it, like libjpeg's jpeg_skip_scanlines does.)
-    const uint32_t next_start = (k + 1 < st.n_sub) ? uint32_t(bd.sub_start[g + 1].x) : im.total_blocks;
-    if (uint32_t(start.x) >= im.write_blk_hi || next_start < im.write_blk_lo)
+    // ROI: nothing to write if every block this thread can own lies past the wanted MCU rows or before the
+    // restart interval they start in (DC differences are needed from there on).  (The end-of-stream
+    // consistency check then falls to whoever decodes the tail; a ROI that excludes the last MCU row skips
+    // it, like libjpeg's jpeg_skip_scanlines does.)
+    const uint32_t next_start = (k + 1 < st.n_sub) ? bd.sub_start[g + 1] : im.total_blocks;
+    if (start >= im.write_blk_hi || next_start < im.dc_blk_lo)
         return;
-    if (!(in & kStateDone) && (uint32_t(start.x) % im.bpm) != ((in >> 12) & 15u)) {
+    if (!(in & kStateDone) && (start % im.bpm) != ((in >> 12) & 15u)) {
         err |= kFlagPhase;
     } else {
-        decode_subsequence<true>(sv, s_hs, s_bt, k * bd.sub_bits, (k + 1) * bd.sub_bits, in, start.x, start.y, start.z, start.w,
-            bd.coef + im.coef_off, bd.blkmask + im.coef_off / 64, res);
+        decode_subsequence<true>(sv, s_hs, s_bt, k * bd.sub_bits, (k + 1) * bd.sub_bits, in, int32_t(start), bd.coef + im.coef_off,
+            bd.blkrec + im.coef_off / 64, res);
         err |= res.err;
     }
     if (err)
         atomicOr(&bd.state[img].flags, err);
+}
+
+// K3b.  DC differences -> DC values, in place in the block records K3 wrote (T.81 F.2.1.3.1: every DC is coded
+// as the difference from the previous block of the same component; restart intervals reset the predictors).
+// One CTA per image; a thread takes kDcPer consecutive blocks (MCU decode order), the CTA combines the
+// per-thread sums with a segmented scan, a carry runs from tile to tile.  Arithmetic is int32 with the
+// low 16 bits kept, exactly what storing into a 16-bit coefficient does.
+constexpr int kDcThreads = 512;
+constexpr int kDcPer = 8;
+struct DcElem {
+    int32_t f, d0, d1, d2; // f: a predictor reset lies inside -> the sums are absolute
+};
+__device__ __forceinline__ DcElem dc_combine(const DcElem& a, const DcElem& b)
+{
+    DcElem r;
+    r.f = a.f | b.f;
+    r.d0 = b.f ? b.d0 : a.d0 + b.d0;
+    r.d1 = b.f ? b.d1 : a.d1 + b.d1;
+    r.d2 = b.f ? b.d2 : a.d2 + b.d2;
+    return r;
+}
+__device__ __forceinline__ DcElem dc_shfl_up(const DcElem& a, int d)
+{
+    DcElem r;
+    r.f = __shfl_up_sync(0xffffffffu, a.f, d);
+    r.d0 = __shfl_up_sync(0xffffffffu, a.d0, d);
+    r.d1 = __shfl_up_sync(0xffffffffu, a.d1, d);
+    r.d2 = __shfl_up_sync(0xffffffffu, a.d2, d);
+    return r;
+}
+
+__global__ void __launch_bounds__(kDcThreads) dc_scan_kernel(BatchDev bd, int redo_only)
+{
+    __shared__ DcElem s_warp[kDcThreads / 32];
+    __shared__ DcElem s_carry;
+    const uint32_t img = blockIdx.x;
+    const ImageDev& im = bd.img[img];
+    const uint32_t flags = bd.state[img].flags;
+    if ((flags & (kFlagDirty | kFlagBadMarker)) || (redo_only && !(flags & kFlagRedo)))
+        return;
+    uint32_t* rec = bd.blkrec + im.coef_off / 64;
+    const uint32_t lo = im.dc_blk_lo, hi = im.write_blk_hi;
+    const uint32_t bpm = im.bpm, ri = im.restart_interval * bpm, blk_comp = im.blk_comp;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0)
+        s_carry = DcElem{0, 0, 0, 0};
+    __syncthreads();
+    for (uint32_t base = lo; base < hi; base += kDcThreads * kDcPer) {
+        const uint32_t j0 = base + threadIdx.x * kDcPer;
+        uint32_t bim = j0 % bpm;
+        uint32_t rim = ri ? j0 % ri : 1u; // position inside the restart interval (never 0 without restarts ...
+        if (!ri && j0 == 0u)
+            rim = 0u;                     // ... except at the very first block)
+        uint32_t r[kDcPer];
+        int32_t v[kDcPer];
+        DcElem e{0, 0, 0, 0};
+        uint32_t reset_at = kDcPer; // first i at which this thread's sums became absolute
+#pragma unroll
+        for (int i = 0; i < kDcPer; ++i) {
+            const uint32_t j = j0 + i;
+            r[i] = (j < hi) ? rec[j] : 0u;
+            if (rim == 0u && j < hi) {
+                e = DcElem{1, 0, 0, 0};
+                reset_at = min(reset_at, uint32_t(i));
+            }
+            const uint32_t c = (blk_comp >> (2u * bim)) & 3u;
+            const int32_t diff = int32_t(r[i]) >> 16;
+            e.d0 += (c == 0u) ? diff : 0;
+            e.d1 += (c == 1u) ? diff : 0;
+            e.d2 += (c == 2u) ? diff : 0;
+            v[i] = (c == 0u) ? e.d0 : (c == 1u ? e.d1 : e.d2);
+            bim = (bim + 1u == bpm) ? 0u : bim + 1u;
+            ++rim;
+            if (ri && rim == ri)
+                rim = 0u;
+        }
+        // inclusive scan over the CTA
+        DcElem inc = e;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const DcElem o = dc_shfl_up(inc, d);
+            if (lane >= d)
+                inc = dc_combine(o, inc);
+        }
+        if (lane == 31)
+            s_warp[warp] = inc;
+        __syncthreads();
+        DcElem pre = s_carry;
+        for (int i = 0; i < warp; ++i)
+            pre = dc_combine(pre, s_warp[i]);
+        const DcElem prev = dc_shfl_up(inc, 1);
+        const DcElem ex = (lane == 0) ? pre : dc_combine(pre, prev); // everything before this thread's blocks
+        // second walk: add the incoming predictors to the blocks that precede this thread's first reset
+        bim = j0 % bpm;
+#pragma unroll
+        for (int i = 0; i < kDcPer; ++i) {
+            const uint32_t j = j0 + i;
+            const uint32_t c = (blk_comp >> (2u * bim)) & 3u;
+            const int32_t add = (uint32_t(i) < reset_at) ? (c == 0u ? ex.d0 : (c == 1u ? ex.d1 : ex.d2)) : 0;
+            if (j < hi)
+                rec[j] = (r[i] & 0xFFFFu) | (uint32_t(v[i] + add) << 16);
+            bim = (bim + 1u == bpm) ? 0u : bim + 1u;
+        }
+        __syncthreads();
+        if (threadIdx.x == kDcThreads - 1)
+            s_carry = dc_combine(pre, inc);
+        __syncthreads();
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -948,7 +1088,8 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
     int32_t zz[64];
     {
         const uint4* s4 = reinterpret_cast<const uint4*>(src);
-        const uint32_t mask = __ldg(bd.blkmask + im.coef_off / 64 + (size_t(my * im.mcus_x + mx) * im.bpm + bim));
+        const uint32_t rec = __ldg(bd.blkrec + im.coef_off / 64 + (size_t(my * im.mcus_x + mx) * im.bpm + bim));
+        const uint32_t mask = rec & 0xFFu; // which groups K3 wrote; the DC value (K3b) sits in the upper half
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             uint4 v = make_uint4(0u, 0u, 0u, 0u);
@@ -961,6 +1102,7 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
                 zz[i * 8 + 2 * j + 1] = int32_t(int16_t(w[j] >> 16));
             }
         }
+        zz[0] = int32_t(rec) >> 16;
     }
     // zig-zag position of each natural-order index (inverse of T.81 Figure A.6)
     constexpr int kZzPos[64] = {0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43, 9, 11, 18, 24,
@@ -1449,6 +1591,14 @@ int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s)
     if (b.n_wseq == 0)
         return 0;
     huff_write_kernel<<<b.n_wseq, kSeqThreads, kWriteSmem, s>>>(b, redo_only ? 1 : 0);
+    return 1;
+}
+
+int launch_dc_scan(const BatchDev& b, bool redo_only, cudaStream_t s)
+{
+    if (b.n_images == 0 || b.n_wseq == 0)
+        return 0;
+    dc_scan_kernel<<<b.n_images, kDcThreads, 0, s>>>(b, redo_only ? 1 : 0);
     return 1;
 }
 

@@ -50,6 +50,7 @@ struct ImageDev {
     uint32_t n_rst_expected;
     uint32_t total_blocks;          // n_mcu * blocks_per_mcu
     uint32_t write_blk_lo, write_blk_hi; // blocks (MCU decode order) of the MCU rows the requested ROI needs, incl. one row of context
+    uint32_t dc_blk_lo;                  // start of the restart interval write_blk_lo lies in (0 without restarts): DC chain start
     uint16_t mcu_row_lo, mcu_row_hi;     // the same window as MCU rows
     uint32_t huff_set;
     uint32_t blk_comp;              // 2 bits per block-in-MCU: component
@@ -98,11 +99,12 @@ struct BatchDev {
     const uint32_t* wseq_img; // K3 CTA -> image
     uint32_t* sub_in;       // entry state per subsequence
     uint32_t* sub_out;      // exit state per subsequence
-    int4* sub_info;         // x = block delta (or absolute | 1<<31 after a restart), yzw = DC diff sums
-    int4* sub_start;        // exclusive scan: x = absolute block index at entry, yzw = DC predictors
+    uint32_t* sub_info;     // blocks that end inside the subsequence (or absolute index | 1<<31 after a restart)
+    uint32_t* sub_start;    // exclusive scan: absolute block index at entry
     const HuffSetDev* huff;
     int16_t* coef;
-    uint8_t* blkmask;       // per coefficient block: which of its eight 16-byte groups K3 wrote (bit g = group g)
+    uint32_t* blkrec;       // per coefficient block: bits 0-7 which of its eight 16-byte groups K3 wrote (bit g = group g),
+                            // bits 16-31 its DC: the coded difference out of K3, the value after K3b
     uint8_t* planes;
     const uint32_t* idct_cta_img;
     const uint32_t* color_cta_img;
@@ -116,6 +118,7 @@ int launch_scan(const BatchDev& b, cudaStream_t s);                 // K0a, K0b,
 int launch_sync(const BatchDev& b, bool fix_mode, bool no_warm, cudaStream_t s); // K1 (first pass or fix-up pass)
 int launch_verify_scan(const BatchDev& b, bool fix_mode, cudaStream_t s); // K2
 int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s);  // K3
+int launch_dc_scan(const BatchDev& b, bool redo_only, cudaStream_t s); // K3b
 int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s);   // K4a
 int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s);  // K4b
 
