@@ -213,6 +213,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=PER_GPU, help="images per GPU (256 = the configuration the metric is quoted on)")
     ap.add_argument("--fancy", type=int, default=1, help="upsampling mode; 1 = libjpeg_turbo_ext default, what the CPU arm uses")
+    ap.add_argument("--options", default="", help="extra decoder options, e.g. ' :subseq_bits=4096' (space-separated) (experiments only)")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="c2 is the configuration the metric is quoted on; "
                     "the others are the remaining BASELINE.json configs, for extra lines only")
     args = ap.parse_args()
@@ -256,7 +257,7 @@ def main():
     rois = [base_roi[i % args.batch] for i in mine]
     n_img = len(jpegs)
 
-    dec = Decoder(local, options=f":fancy_upsampling={args.fancy}")
+    dec = Decoder(local, options=f":fancy_upsampling={args.fancy}{args.options}")
     pinned_in = [torch.frombuffer(bytearray(j), dtype=torch.uint8).pin_memory() for j in jpegs]
     srcs = [t.numpy() for t in pinned_in]
     stream = torch.cuda.current_stream()

@@ -302,9 +302,10 @@ struct StreamView {
     uint32_t bpm, blk_comp, blk_tab;
     uint32_t ri_blocks;      // restart_interval * bpm
     uint32_t total_blocks;
-    uint32_t write_lo, write_hi; // K3: only blocks in [write_lo, write_hi) are wanted (MCU rows a ROI touches) ...
-    uint32_t dc_lo;              //     ... but DC differences from dc_lo on: the predictor chain K3b integrates
-    uint32_t comp_mask;          // K3: bit c set = component c is wanted (luma only for Y output)
+    // K3 counts blocks in the batch's coefficient arena (blk_base = first block of this image; 0 in K1):
+    uint32_t blk_base;
+    uint32_t write_lo;           // AC coefficients are wanted from here (first MCU row a ROI touches) ...
+    uint32_t dc_lo, dc_span;     // ... DC differences in [dc_lo, dc_lo + dc_span): the chain K3b integrates, up to the last wanted row
 };
 
 // Coefficient block assembly for K3: the 64 int16 of the block being decoded are emitted as
@@ -312,42 +313,56 @@ struct StreamView {
 // -- most of them at photographic qualities -- are not written at all, a one-byte mask per block says
 // which groups exist.  No clearing pass, no partial-sector read-modify-write in L2.
 struct BlockWriter {
-    uint64_t lo, hi; // coefficients 0..3 and 4..7 of the current group
-    uint32_t g;      // current group, 0..7
-    uint32_t mask;   // groups of this block that hold a non-zero coefficient (and were stored)
+    uint32_t r0, r1, r2, r3; // the eight coefficients of the current group, zig-zag order, two per register
+    uint32_t g;              // current group, 0..7
+    uint32_t mask;           // groups of this block that hold a non-zero coefficient (and were stored)
     __device__ __forceinline__ void reset()
     {
-        lo = hi = 0;
+        r0 = r1 = r2 = r3 = 0;
         g = 0;
         mask = 0;
     }
-    __device__ __forceinline__ void store_group(int16_t* __restrict__ blk_base)
+    // next block: the group registers are zero already (store_group clears what it stores, and a block
+    // that is not wanted never put anything)
+    __device__ __forceinline__ void next_block()
     {
-        if (lo | hi) {
-            *reinterpret_cast<uint4*>(blk_base + g * 8) = make_uint4(uint32_t(lo), uint32_t(lo >> 32), uint32_t(hi), uint32_t(hi >> 32));
+        g = 0;
+        mask = 0;
+    }
+    // coef: the batch's coefficient arena, blk: block index in it
+    __device__ __forceinline__ void store_group(int16_t* __restrict__ coef, uint32_t blk)
+    {
+        if ((r0 | r1) | (r2 | r3)) {
+            reinterpret_cast<uint4*>(coef)[blk * 8u + g] = make_uint4(r0, r1, r2, r3);
             mask |= 1u << g;
-            lo = hi = 0;
+            r0 = r1 = r2 = r3 = 0;
         }
     }
-    __device__ __forceinline__ void put(int16_t* __restrict__ blk_base, uint32_t pos, int32_t val)
+    __device__ __forceinline__ void put(int16_t* __restrict__ coef, uint32_t blk, uint32_t pos, int32_t val)
     {
         const uint32_t ng = pos >> 3;
         if (ng != g) { // positions only grow inside a block: the previous group is complete
-            store_group(blk_base);
+            store_group(coef, blk);
             g = ng;
         }
-        const uint64_t v = uint64_t(uint32_t(val) & 0xFFFFu) << (16 * (pos & 3u));
-        if (pos & 4u)
-            hi |= v;
-        else
-            lo |= v;
+        // 16-bit value to halfword (pos & 7) of r0..r3: a 64-bit shift by the position inside the half, then
+        // predicated ORs into the lower or the upper pair
+        const uint64_t v = uint64_t(uint32_t(val) & 0xFFFFu) << (16u * (pos & 3u));
+        asm("{\n\t.reg .pred q;\n\t"
+            "setp.ne.u32 q, %4, 0;\n\t"
+            "@!q or.b32 %0, %0, %5;\n\t"
+            "@!q or.b32 %1, %1, %6;\n\t"
+            "@q or.b32 %2, %2, %5;\n\t"
+            "@q or.b32 %3, %3, %6;\n\t}"
+            : "+r"(r0), "+r"(r1), "+r"(r2), "+r"(r3)
+            : "r"(pos & 4u), "r"(uint32_t(v)), "r"(uint32_t(v >> 32)));
     }
     // end of block: last group out, then the block record = presence mask (all-zero groups are never
     // written; K4a substitutes zeros for them) | DC difference << 16 (K3b turns it into the DC value)
-    __device__ __forceinline__ void finish(int16_t* __restrict__ blk_base, uint32_t* __restrict__ rec_out, int32_t dc_diff)
+    __device__ __forceinline__ void finish(int16_t* __restrict__ coef, uint32_t* __restrict__ rec, uint32_t blk, int32_t dc_diff)
     {
-        store_group(blk_base);
-        *rec_out = mask | (uint32_t(dc_diff) << 16);
+        store_group(coef, blk);
+        rec[blk] = mask | (uint32_t(dc_diff) << 16);
     }
 };
 
@@ -355,7 +370,7 @@ struct BlockWriter {
 // The addresses are 32-bit shared-window addresses, so the decode loop forms every table access with
 // one add:
 //   .x = address of the block's DC table      .y = address of its AC table
-//   .z = address of the NEXT block's entry    .w = component | block index << 8 | (1 << component) << 16
+//   .z = address of the NEXT block's entry    .w = component | block index << 8 | component consumed << 24
 struct BlockTable {
     uint4 e[kMaxBlocksPerMcu];
 };
@@ -380,7 +395,8 @@ __device__ __forceinline__ void build_block_table(BlockTable* bt, const HuffSetD
         const uint32_t dc = (im.blk_tab >> b) & 1u;
         const uint32_t ac = 2u + ((im.blk_tab >> (16 + b)) & 1u);
         const uint32_t next = (b + 1u == im.bpm) ? 0u : b + 1u;
-        bt->e[b] = make_uint4(smem_addr(&s_hs->t[dc]), smem_addr(&s_hs->t[ac]), smem_addr(&bt->e[next]), comp | (b << 8) | ((1u << comp) << 16));
+        const uint32_t used = (comp == 0u || im.ncomp_needed >= 3) ? 1u : 0u; // Y output consumes luma only
+        bt->e[b] = make_uint4(smem_addr(&s_hs->t[dc]), smem_addr(&s_hs->t[ac]), smem_addr(&bt->e[next]), comp | (b << 8) | (used << 24));
     }
 }
 
@@ -388,6 +404,8 @@ __device__ __forceinline__ void build_block_table(BlockTable* bt, const HuffSetD
 // prefetched in wnx, wp -> the word held in whi.  A symbol advances the position by at most 31 bits,
 // i.e. across at most one word boundary; the refill is predicated, not branched: a branch here is taken
 // by some lane of the warp in nearly every iteration and then costs every lane its issue slots.
+// (Measured and dropped: an L2 prefetch ahead of the refill, and a subsequence-interleaved stream layout
+// that makes a warp's refills share cache lines -- neither shortens the kernels, profiles/README.md.)
 struct BitReader {
     uint32_t whi, wlo, wnx;
     const uint32_t* wp;
@@ -461,15 +479,18 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
     bool owned = (z == 0u); // kWrite: is the block under way mine (it started inside my range)?
     // ... and is it wanted at all: its DC difference (component needed, not past the ROI's MCU rows), its AC
     // coefficients (inside those rows)?  Both imply blk < total_blocks.
-    auto want_dc = [&](int32_t k, uint32_t w) { return uint32_t(k) - sv.dc_lo < sv.write_hi - sv.dc_lo && ((sv.comp_mask >> (w & 3u)) & 1u); };
+    auto want_dc = [&](int32_t k, uint32_t w) { return uint32_t(k) - sv.dc_lo < sv.dc_span && (w & (1u << 24)); };
     bool w_dc = kWrite && owned && want_dc(blk, bi.w);
     bool w_ac = w_dc && uint32_t(blk) >= sv.write_lo;
     int32_t dc_diff = 0;
     BlockWriter bw;
     bw.reset();
     bool done = false;
+    // The 32 bits at the read position are carried around the loop (computed at the end of an iteration for
+    // the next one): the word refill issued in iteration i is then first needed by the register moves of
+    // iteration i+1, a whole iteration later, instead of at the loop head.
+    uint32_t win = br.window(p);
     for (;;) {
-        const uint32_t win = br.window(p);
         if (p >= limit) {
             // End of a restart interval (or of the stream): either the decoder already ran across the
             // boundary (only an unsynchronised one can), or fewer than 8 bits remain and they are all
@@ -489,9 +510,9 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
                 ++r;
                 next_bnd = (r == sv.nb - 1) ? sv.total_bits : __ldg(sv.bnd + r) * 8u;
                 limit = min(end_bit, max(next_bnd, 7u) - 7u);
-                if (kWrite && (z != 0u || ((bi.w >> 8) & 15u) != 0u || uint32_t(blk) != r * sv.ri_blocks))
+                if (kWrite && (z != 0u || ((bi.w >> 8) & 15u) != 0u || uint32_t(blk) != sv.blk_base + r * sv.ri_blocks))
                     out.err |= kFlagOverrun;
-                blk = int32_t(r * sv.ri_blocks);
+                blk = int32_t(sv.blk_base + r * sv.ri_blocks);
                 out.restarted = 1;
                 z = 0;
                 owned = true;
@@ -501,6 +522,7 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
                 w_dc = kWrite && want_dc(blk, bi.w);
                 w_ac = w_dc && uint32_t(blk) >= sv.write_lo;
                 br.seek(sv.words, p);
+                win = br.window(p);
                 continue;
             }
             if (p >= end_bit && (!kWrite || z == 0u || !owned))
@@ -542,16 +564,14 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
             dc_diff = is_dc ? val : dc_diff;
             if (w_ac && !is_dc && size != 0u) {
                 const uint32_t pos = z + skip - 1u; // zig-zag position of the coefficient this symbol carries
-                if (pos > 63u)
-                    out.err |= kFlagBadHuffman;
-                else
-                    bw.put(coef + size_t(blk) * 64, pos, val);
+                out.err |= (pos > 63u) ? uint32_t(kFlagBadHuffman) : 0u;
+                bw.put(coef, uint32_t(blk), pos & 63u, val);
             }
             z += skip;
             if (z > 63u) {
                 if (w_dc)
-                    bw.finish(coef + size_t(blk) * 64, blkrec + blk, dc_diff);
-                bw.reset();
+                    bw.finish(coef, blkrec, uint32_t(blk), dc_diff);
+                bw.next_block();
                 owned = true;
                 z = 0;
                 ++blk;
@@ -571,10 +591,11 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
             z = (z > 63u) ? 0u : z;
         }
         taddr = (z == 0u) ? bi.x : bi.y;
+        win = br.window(p);
     }
     if (done) {
         out.state = kStateDone;
-        if (kWrite && (z != 0u || uint32_t(blk) != sv.total_blocks))
+        if (kWrite && (z != 0u || uint32_t(blk) != sv.blk_base + sv.total_blocks))
             out.err |= kFlagOverrun;
     } else {
         out.state = ((p - end_bit) & 63u) | (z << 6) | (((bi.w >> 8) & 15u) << 12);
@@ -602,10 +623,10 @@ __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageD
     sv.blk_tab = im.blk_tab;
     sv.ri_blocks = im.restart_interval * im.bpm;
     sv.total_blocks = im.total_blocks;
+    sv.blk_base = 0;
     sv.write_lo = im.write_blk_lo;
-    sv.write_hi = im.write_blk_hi;
     sv.dc_lo = im.dc_blk_lo;
-    sv.comp_mask = im.ncomp_needed >= 3 ? 7u : 1u;
+    sv.dc_span = im.write_blk_hi - im.dc_blk_lo;
     return sv;
 }
 
@@ -870,7 +891,10 @@ __global__ void __launch_bounds__(kSeqThreads, 5) huff_write_kernel(BatchDev bd,
     const uint32_t k = first_k + threadIdx.x;
     if (k >= st.n_sub)
         return;
-    const StreamView sv = make_view(bd, im, st);
+    StreamView sv = make_view(bd, im, st);
+    sv.blk_base = uint32_t(im.coef_off / 64); // blocks are counted in the batch's arena from here on
+    sv.write_lo += sv.blk_base;
+    sv.dc_lo += sv.blk_base;
     const uint32_t g = im.sub_off + k;
     const uint32_t in = bd.sub_in[g];
     const uint32_t start = bd.sub_start[g];
@@ -886,8 +910,7 @@ __global__ void __launch_bounds__(kSeqThreads, 5) huff_write_kernel(BatchDev bd,
     if (!(in & kStateDone) && (start % im.bpm) != ((in >> 12) & 15u)) {
         err |= kFlagPhase;
     } else {
-        decode_subsequence<true>(sv, s_hs, s_bt, k * bd.sub_bits, (k + 1) * bd.sub_bits, in, int32_t(start), bd.coef + im.coef_off,
-            bd.blkrec + im.coef_off / 64, res);
+        decode_subsequence<true>(sv, s_hs, s_bt, k * bd.sub_bits, (k + 1) * bd.sub_bits, in, int32_t(sv.blk_base + start), bd.coef, bd.blkrec, res);
         err |= res.err;
     }
     if (err)
