@@ -1028,7 +1028,7 @@ __global__ void __launch_bounds__(kDcThreads) dc_scan_kernel(BatchDev bd, int re
 // ------------------------------------------------------------------------------------------------
 // K4a: dequantise + ISLOW IDCT (jidctint.c arithmetic), one thread per 8x8 block
 // ------------------------------------------------------------------------------------------------
-template <int kShift>
+template <int kShift, uint32_t kBias>
 __device__ __forceinline__ void idct8(int32_t i0, int32_t i1, int32_t i2, int32_t i3, int32_t i4, int32_t i5, int32_t i6, int32_t i7,
     int32_t* o)
 {
@@ -1057,24 +1057,28 @@ __device__ __forceinline__ void idct8(int32_t i0, int32_t i1, int32_t i2, int32_
     t1 += z2 + z4;
     t2 += z2 + z3;
     t3 += z1 + z4;
-    constexpr int32_t rnd = 1 << (kShift - 1);
-    o[0] = (a10 + t3 + rnd) >> kShift;
-    o[7] = (a10 - t3 + rnd) >> kShift;
-    o[1] = (a11 + t2 + rnd) >> kShift;
-    o[6] = (a11 - t2 + rnd) >> kShift;
-    o[2] = (a12 + t1 + rnd) >> kShift;
-    o[5] = (a12 - t1 + rnd) >> kShift;
-    o[3] = (a13 + t0 + rnd) >> kShift;
-    o[4] = (a13 - t0 + rnd) >> kShift;
+    // DESCALE; kBias (a multiple of 1 << kShift) rides along with the rounding constant.  Unsigned adds: with the
+    // bias the sum may wrap, and only bits kShift.. of it are used by the caller then.
+    constexpr uint32_t rnd = (1u << (kShift - 1)) + kBias;
+    auto descale = [](int32_t a, int32_t b) { return int32_t(uint32_t(a) + uint32_t(b) + rnd) >> kShift; };
+    o[0] = descale(a10, t3);
+    o[7] = descale(a10, -t3);
+    o[1] = descale(a11, t2);
+    o[6] = descale(a11, -t2);
+    o[2] = descale(a12, t1);
+    o[5] = descale(a12, -t1);
+    o[3] = descale(a13, t0);
+    o[4] = descale(a13, -t0);
 }
 
 // libjpeg's range_limit table indexed with (x & 1023), i.e. clamp(x + 128) with a 10-bit wrap:
 //   i = x & 1023;  i < 128 -> i + 128;  i < 512 -> 255;  i < 896 -> 0;  else i - 896.
 // With u = (x + 128) & 1023 that is u for u < 256, 255 for u < 640, 0 above; shifting the wrap
 // point to 640 turns it into one clamp: t = ((x + 512) & 1023) - 384, result = min(max(t, 0), 255).
+// The + 512 is added by the caller: pass 2 of the IDCT folds 512 << 18 into its rounding constant.
 __device__ __forceinline__ uint32_t range_limit(int32_t x)
 {
-    return uint32_t(__vimin_s32_relu(((x + 512) & 1023) - 384, 255));
+    return uint32_t(__vimin_s32_relu((x & 1023) - 384, 255)); // x already carries the + 512
 }
 
 __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
@@ -1140,7 +1144,7 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
 #pragma unroll
         for (int y = 0; y < 8; ++y)
             col[y] = zz[kZzPos[y * 8 + x]] * int32_t(q[y * 8 + x]);
-        idct8<11>(col[0], col[1], col[2], col[3], col[4], col[5], col[6], col[7], o);
+        idct8<11, 0u>(col[0], col[1], col[2], col[3], col[4], col[5], col[6], col[7], o);
 #pragma unroll
         for (int y = 0; y < 8; ++y)
             ws[y * 8 + x] = o[y];
@@ -1150,7 +1154,7 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
 #pragma unroll
     for (int y = 0; y < 8; ++y) {
         int32_t o[8];
-        idct8<18>(ws[y * 8 + 0], ws[y * 8 + 1], ws[y * 8 + 2], ws[y * 8 + 3], ws[y * 8 + 4], ws[y * 8 + 5], ws[y * 8 + 6], ws[y * 8 + 7], o);
+        idct8<18, (512u << 18)>(ws[y * 8 + 0], ws[y * 8 + 1], ws[y * 8 + 2], ws[y * 8 + 3], ws[y * 8 + 4], ws[y * 8 + 5], ws[y * 8 + 6], ws[y * 8 + 7], o);
         uint2 pk;
         pk.x = range_limit(o[0]) | (range_limit(o[1]) << 8) | (range_limit(o[2]) << 16) | (range_limit(o[3]) << 24);
         pk.y = range_limit(o[4]) | (range_limit(o[5]) << 8) | (range_limit(o[6]) << 16) | (range_limit(o[7]) << 24);
@@ -1229,6 +1233,35 @@ __device__ __forceinline__ void ycc_to_rgb(int y, int cb, int cr, uint32_t& r, u
     r = uint32_t(__viaddmin_s32_relu(y, (91881 * cr + 32768) >> 16, 255));
     g = uint32_t(__viaddmin_s32_relu(y, (-22554 * cb - 46802 * cr + 32768) >> 16, 255));
     b = uint32_t(__viaddmin_s32_relu(y, (116130 * cb + 32768) >> 16, 255));
+}
+
+// The same transform 16 bits up, for the 8-pixel units: with y16 = y << 16 the sample is byte 2 of
+//   clamp(y16 + C * (c - 128) + 32768, 0, 0xFFFFFF)      (floor((y16 + t) / 65536) == y + floor(t / 65536)),
+// the -128 folded into the constant, so a channel costs one multiply-add and one add-clamp, no shift; the
+// byte permutes that pack the output words pick byte 2 instead of byte 0.
+__device__ __forceinline__ void ycc_to_rgb16(int y16, int cb, int cr, uint32_t& r, uint32_t& g, uint32_t& b)
+{
+    constexpr int kR = 32768 - 128 * 91881, kG = 32768 + 128 * (22554 + 46802), kB = 32768 - 128 * 116130;
+    r = uint32_t(__viaddmin_s32_relu(y16, 91881 * cr + kR, 0xFFFFFF));
+    g = uint32_t(__viaddmin_s32_relu(y16, -22554 * cb + (-46802 * cr + kG), 0xFFFFFF));
+    b = uint32_t(__viaddmin_s32_relu(y16, 116130 * cb + kB, 0xFFFFFF));
+}
+// byte 2 of a, b, c, d -> one little-endian word
+__device__ __forceinline__ uint32_t pack_b2(uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+{
+    return __byte_perm(__byte_perm(a, b, 0x0062), __byte_perm(c, d, 0x0062), 0x5410);
+}
+// the eight bytes of v, each moved to byte 2 of its own word
+__device__ __forceinline__ void unpack8_b2(uint2 v, uint32_t* o)
+{
+    o[0] = __byte_perm(v.x, 0u, 0x4044);
+    o[1] = __byte_perm(v.x, 0u, 0x4144);
+    o[2] = __byte_perm(v.x, 0u, 0x4244);
+    o[3] = __byte_perm(v.x, 0u, 0x4344);
+    o[4] = __byte_perm(v.y, 0u, 0x4044);
+    o[5] = __byte_perm(v.y, 0u, 0x4144);
+    o[6] = __byte_perm(v.y, 0u, 0x4244);
+    o[7] = __byte_perm(v.y, 0u, 0x4344);
 }
 
 constexpr int kColorTx = 32; // threads in x, 8 pixels each
@@ -1366,8 +1399,9 @@ __device__ __forceinline__ void upsample8(const int* cur, const int* nbr, int r,
                 s[k] = 3 * cur[k] + nbr[k];
 #pragma unroll
             for (int m = 0; m < 4; ++m) {
-                out[2 * m] = (3 * s[m + 1] + s[m] + 8) >> 4;
-                out[2 * m + 1] = (3 * s[m + 1] + s[m + 2] + 7) >> 4;
+                const int t = 3 * s[m + 1] + 8;
+                out[2 * m] = (t + s[m]) >> 4;
+                out[2 * m + 1] = (t + s[m + 2] - 1) >> 4;
             }
         } else if (VX == 1 && fancy_h) { // h2v1 triangle
 #pragma unroll
@@ -1391,6 +1425,41 @@ __device__ __forceinline__ void upsample8(const int* cur, const int* nbr, int r,
                 out[m] = cur[m];
         }
     }
+}
+
+// Stores 4 * NW contiguous bytes (little-endian words w[0..NW)) at ANY byte address.  Tightly pitched rows of
+// odd widths put most rows of an image off the 8-byte grid: aligned words go out as words (funnel-shifted by
+// the misalignment, which is the same for every lane of the warp), only the 4 bytes of head and tail singly.
+template <int NW>
+__device__ __forceinline__ void store_words_any(uint8_t* o, const uint32_t* w)
+{
+    const uint32_t a = uint32_t(reinterpret_cast<uintptr_t>(o)) & 3u;
+    if (a == 0u) {
+        if ((NW % 2) == 0 && (reinterpret_cast<uintptr_t>(o) & 7u) == 0) {
+#pragma unroll
+            for (int k = 0; k < NW / 2; ++k)
+                reinterpret_cast<uint2*>(o)[k] = make_uint2(w[2 * k], w[2 * k + 1]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < NW; ++k)
+                reinterpret_cast<uint32_t*>(o)[k] = w[k];
+        }
+        return;
+    }
+    const uint32_t head = 4u - a, sh = 8u * head; // bytes before the first aligned word; its position in w[0]
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+        if (uint32_t(j) < head)
+            o[j] = uint8_t(w[0] >> (8 * j));
+    uint32_t* o32 = reinterpret_cast<uint32_t*>(o + head);
+#pragma unroll
+    for (int k = 0; k + 1 < NW; ++k)
+        o32[k] = __funnelshift_r(w[k], w[k + 1], sh);
+    uint8_t* tail = o + head + 4 * (NW - 1);
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+        if (uint32_t(j) < a)
+            tail[j] = uint8_t(w[NW - 1] >> (sh + 8 * j));
 }
 
 // One unit = 8 pixels x VX rows at image position (X0, Y0), X0 % 8 == 0, Y0 % VX == 0.
@@ -1443,21 +1512,21 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
         const int y = Y0 + r;
         if (y < int(im.roi_y0) || y >= int(im.roi_y1))
             continue;
-        int yy[8];
-        unpack8(__ldg(reinterpret_cast<const uint2*>(p0 + size_t(y) * stride0 + X0)), yy);
+        uint32_t yy[8]; // luma << 16; every channel value below sits in byte 2 of its word
+        unpack8_b2(__ldg(reinterpret_cast<const uint2*>(p0 + size_t(y) * stride0 + X0)), yy);
         uint32_t c0[8], c1[8], c2[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             if (kLumaOnly) {
-                c0[i] = c1[i] = c2[i] = uint32_t(yy[i]);
+                c0[i] = c1[i] = c2[i] = yy[i];
             } else {
                 uint32_t rr, gg, bb;
                 if (kOrder == 2) {
-                    rr = uint32_t(yy[i]);
-                    gg = uint32_t(cb[r][i]);
-                    bb = uint32_t(cr[r][i]);
+                    rr = yy[i];
+                    gg = uint32_t(cb[r][i]) << 16;
+                    bb = uint32_t(cr[r][i]) << 16;
                 } else {
-                    ycc_to_rgb(yy[i], cb[r][i], cr[r][i], rr, gg, bb);
+                    ycc_to_rgb16(int(yy[i]), cb[r][i], cr[r][i], rr, gg, bb);
                 }
                 c0[i] = swap ? bb : rr;
                 c1[i] = gg;
@@ -1469,7 +1538,7 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
 #pragma unroll
             for (int i = 0; i < 8; ++i)
                 if (X0 + i >= int(im.roi_x0) && X0 + i < int(im.roi_x1))
-                    store_pixel_oriented(im, ox + i, oy, c0[i], c1[i], c2[i]);
+                    store_pixel_oriented(im, ox + i, oy, c0[i] >> 16, c1[i] >> 16, c2[i] >> 16);
             continue;
         }
         if (im.fmt == kFmtY || im.fmt == kFmtPRGB || im.fmt == kFmtPBGR || im.fmt == kFmtPYUV) {
@@ -1480,39 +1549,30 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
                     break;
                 const uint32_t* v = ch == 0 ? c0 : (ch == 1 ? c1 : c2);
                 uint8_t* o = im.out + size_t(ch) * im.plane_stride + size_t(oy) * im.row_stride + ox;
-                if (full_x && (reinterpret_cast<uintptr_t>(o) & 7u) == 0) {
-                    uint2 pk;
-                    pk.x = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
-                    pk.y = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
-                    *reinterpret_cast<uint2*>(o) = pk;
+                if (full_x) {
+                    const uint32_t pk[2] = {pack_b2(v[0], v[1], v[2], v[3]), pack_b2(v[4], v[5], v[6], v[7])};
+                    store_words_any<2>(o, pk);
                 } else {
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
                         if (X0 + i >= int(im.roi_x0) && X0 + i < int(im.roi_x1))
-                            o[i] = uint8_t(v[i]);
+                            o[i] = uint8_t(v[i] >> 16);
                 }
             }
         } else {
             uint8_t* o = im.out + size_t(oy) * im.row_stride + ptrdiff_t(ox) * 3;
-            if (full_x && (reinterpret_cast<uintptr_t>(o) & 7u) == 0) {
-                uint2 a, b, c;
-                a.x = c0[0] | (c1[0] << 8) | (c2[0] << 16) | (c0[1] << 24);
-                a.y = c1[1] | (c2[1] << 8) | (c0[2] << 16) | (c1[2] << 24);
-                b.x = c2[2] | (c0[3] << 8) | (c1[3] << 16) | (c2[3] << 24);
-                b.y = c0[4] | (c1[4] << 8) | (c2[4] << 16) | (c0[5] << 24);
-                c.x = c1[5] | (c2[5] << 8) | (c0[6] << 16) | (c1[6] << 24);
-                c.y = c2[6] | (c0[7] << 8) | (c1[7] << 16) | (c2[7] << 24);
-                uint2* o8 = reinterpret_cast<uint2*>(o);
-                o8[0] = a;
-                o8[1] = b;
-                o8[2] = c;
+            if (full_x) {
+                const uint32_t pk[6] = {pack_b2(c0[0], c1[0], c2[0], c0[1]), pack_b2(c1[1], c2[1], c0[2], c1[2]),
+                    pack_b2(c2[2], c0[3], c1[3], c2[3]), pack_b2(c0[4], c1[4], c2[4], c0[5]), pack_b2(c1[5], c2[5], c0[6], c1[6]),
+                    pack_b2(c2[6], c0[7], c1[7], c2[7])};
+                store_words_any<6>(o, pk);
             } else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i)
                     if (X0 + i >= int(im.roi_x0) && X0 + i < int(im.roi_x1)) {
-                        o[3 * i + 0] = uint8_t(c0[i]);
-                        o[3 * i + 1] = uint8_t(c1[i]);
-                        o[3 * i + 2] = uint8_t(c2[i]);
+                        o[3 * i + 0] = uint8_t(c0[i] >> 16);
+                        o[3 * i + 1] = uint8_t(c1[i] >> 16);
+                        o[3 * i + 2] = uint8_t(c2[i] >> 16);
                     }
             }
         }

@@ -380,3 +380,20 @@ def test_exif_orientations_applied_while_storing(dec_fancy):
             for d, r, o in zip(srcs, rois, outs):
                 ref = oracle.apply_orientation(oracle.decode(d, OFMT.get(fmt, oracle.FMT_P_YUV), fancy=True, roi=r), code, planar=fmt.startswith("P_"))
                 assert np.array_equal(o.cpu().numpy(), ref), (fmt, code)
+
+
+@pytest.mark.parametrize("fmt", ["I_RGB", "P_RGB", "I_Y"])
+def test_tight_rows_at_every_byte_alignment(dec_fancy, fmt):
+    """Tightly pitched outputs of odd widths start their rows at every address mod 8; the 8-pixel units of the
+    colour kernel then store through the funnel-shifted word path.  Also with a ROI whose left edge is odd."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    srcs, rois = [], []
+    for i, w in enumerate(range(65, 81)):  # 16 widths: 3*w and w cover all residues mod 8 over the rows
+        samp = ["420", "422", "444"][i % 3]
+        srcs.append(corpus.encode(corpus.synth(40 + i, w, 900 + i), 85, samp))
+        rois.append(None if i % 2 == 0 else (3, 5 + i % 7, 35, w - 2))
+    outs = dec_fancy.decode(srcs, fmt, rois=rois)
+    assert dec_fancy.last_status == [_lib.OK] * len(srcs)
+    for d, roi, o in zip(srcs, rois, outs):
+        assert np.array_equal(o.cpu().numpy(), oracle.decode(d, OFMT[fmt], fancy=True, roi=roi))
