@@ -364,7 +364,10 @@ def main():
         # DRAM bytes per launch of each kernel from the committed `ncu --set full` capture of this workload
         traffic = {}
         try:
-            with open(os.path.join(ROOT, "profiles", "r1f_dram_traffic.json")) as f:
+            import glob
+
+            newest = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_dram_traffic.json")))[-1]
+            with open(newest) as f:
                 traffic = {k.replace("_kernel", ""): v["dram_bytes"] for k, v in json.load(f)["kernels"].items()}
         except Exception:
             pass

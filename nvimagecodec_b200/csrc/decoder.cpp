@@ -194,7 +194,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     }
     const size_t sub_bytes = bd_.sub_bits / 8;
     size_t raw_bytes = 0, cmp_bytes = 0, coef_elems = 0, plane_bytes = 0, bounce_bytes = 0;
-    uint32_t n_tiles = 0, n_sub = 0, n_seq = 0, n_wseq = 0, n_bnd = 0, n_idct = 0, n_color = 0;
+    uint32_t n_tiles = 0, n_sub = 0, n_seq = 0, n_wseq = 0, n_bnd = 0, n_dc = 0, n_idct = 0, n_color = 0;
     comp_bytes_ = n_coefs_ = out_bytes_ = 0;
 
     for (int i = 0; i < n; ++i) {
@@ -283,6 +283,9 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         {   // DC differences are needed from the last predictor reset at or before the first wanted block
             const uint32_t ri_blocks = uint32_t(hd.restart_interval) * uint32_t(hd.blocks_per_mcu);
             im.dc_blk_lo = ri_blocks ? im.write_blk_lo / ri_blocks * ri_blocks : 0u;
+            im.dc_cta_off = n_dc;
+            im.n_dc_cta = (im.write_blk_hi - im.dc_blk_lo + kDcChunk - 1) / kDcChunk;
+            n_dc += im.n_dc_cta;
         }
         int b = 0;
         uint32_t idct_blocks = 0;
@@ -402,6 +405,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     off = align_up(off + 4ull * n_seq, 256);
     const size_t off_wseq = off;
     off = align_up(off + 4ull * n_wseq, 256);
+    const size_t off_dc = off;
+    off = align_up(off + 4ull * n_dc, 256);
     const size_t off_idct = off;
     off = align_up(off + 4ull * n_idct, 256);
     const size_t off_color = off;
@@ -430,6 +435,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     so = align_up(so + 4ull * n_sub, 256);
     const size_t so_start = so;
     so = align_up(so + 4ull * n_sub, 256);
+    const size_t so_dcsum = so;
+    so = align_up(so + 16ull * n_dc, 256);
     const size_t so_stats = so;
     so += 256;
     const size_t so_mask = so;
@@ -447,6 +454,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     uint32_t* tile_img = reinterpret_cast<uint32_t*>(up + off_tile);
     uint32_t* seq_img = reinterpret_cast<uint32_t*>(up + off_seq);
     uint32_t* wseq_img = reinterpret_cast<uint32_t*>(up + off_wseq);
+    uint32_t* dc_img = reinterpret_cast<uint32_t*>(up + off_dc);
     uint32_t* idct_img = reinterpret_cast<uint32_t*>(up + off_idct);
     uint32_t* color_img = reinterpret_cast<uint32_t*>(up + off_color);
     std::vector<uint8_t> direct(size_t(nd), 0); // source is pinned / registered host memory: copy without staging
@@ -458,6 +466,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         std::fill(tile_img + im.tile_off, tile_img + im.tile_off + im.n_tiles, uint32_t(d));
         std::fill(seq_img + im.seq_off, seq_img + im.seq_off + im.n_seq, uint32_t(d));
         std::fill(wseq_img + im.wseq_off, wseq_img + im.wseq_off + im.n_wseq, uint32_t(d));
+        std::fill(dc_img + im.dc_cta_off, dc_img + im.dc_cta_off + im.n_dc_cta, uint32_t(d));
         std::fill(idct_img + im.idct_cta_off, idct_img + im.idct_cta_off + im.n_idct_cta, uint32_t(d));
         std::fill(color_img + im.color_cta_off, color_img + im.color_cta_off + im.n_color_cta_x * im.n_color_cta_y, uint32_t(d));
         cudaPointerAttributes attr{};
@@ -516,6 +525,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.tile_img = reinterpret_cast<const uint32_t*>(dv + off_tile);
     bd_.seq_img = reinterpret_cast<const uint32_t*>(dv + off_seq);
     bd_.wseq_img = reinterpret_cast<const uint32_t*>(dv + off_wseq);
+    bd_.dc_cta_img = reinterpret_cast<const uint32_t*>(dv + off_dc);
     bd_.idct_cta_img = reinterpret_cast<const uint32_t*>(dv + off_idct);
     bd_.color_cta_img = reinterpret_cast<const uint32_t*>(dv + off_color);
     bd_.huff = reinterpret_cast<const HuffSetDev*>(dv + off_huff);
@@ -537,6 +547,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.n_seq = int(n_seq);
     bd_.n_wseq = int(n_wseq);
     bd_.n_sub = int(n_sub);
+    bd_.n_dc_cta = int(n_dc);
+    bd_.dc_sum = reinterpret_cast<int4*>(sc + so_dcsum);
     bd_.n_idct_cta = int(n_idct);
     bd_.n_color_cta = int(n_color);
     states_.assign(nd, ImageState{0, 0, 0, 0});

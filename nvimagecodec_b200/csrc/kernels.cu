@@ -919,11 +919,10 @@ __global__ void __launch_bounds__(kSeqThreads, 5) huff_write_kernel(BatchDev bd,
 
 // K3b.  DC differences -> DC values, in place in the block records K3 wrote (T.81 F.2.1.3.1: every DC is coded
 // as the difference from the previous block of the same component; restart intervals reset the predictors).
-// One CTA per image; a thread takes kDcPer consecutive blocks (MCU decode order), the CTA combines the
-// per-thread sums with a segmented scan, a carry runs from tile to tile.  Arithmetic is int32 with the
-// low 16 bits kept, exactly what storing into a 16-bit coefficient does.
-constexpr int kDcThreads = 512;
-constexpr int kDcPer = 8;
+// A CTA takes one chunk of kDcChunk consecutive blocks (MCU decode order) of one image, a thread kDcPer of
+// them.  Two launches: (a) per-chunk sums, (b) every chunk combines the sums of the chunks before it in its
+// image (one warp, a few loads) and integrates its own blocks.  Arithmetic is int32 with the low 16 bits
+// kept, exactly what storing into a 16-bit coefficient does.
 struct DcElem {
     int32_t f, d0, d1, d2; // f: a predictor reset lies inside -> the sums are absolute
 };
@@ -945,83 +944,135 @@ __device__ __forceinline__ DcElem dc_shfl_up(const DcElem& a, int d)
     r.d2 = __shfl_up_sync(0xffffffffu, a.d2, d);
     return r;
 }
+__device__ __forceinline__ DcElem dc_warp_scan(DcElem e, int lane)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const DcElem o = dc_shfl_up(e, d);
+        if (lane >= d)
+            e = dc_combine(o, e);
+    }
+    return e;
+}
 
-__global__ void __launch_bounds__(kDcThreads) dc_scan_kernel(BatchDev bd, int redo_only)
+// The thread's kDcPer blocks starting at j0: records r[], running per-component sums v[] (inclusive, restarted at
+// a predictor reset), the thread's element, and the first i at which the sums became absolute.
+struct DcLocal {
+    uint32_t r[kDcPer];
+    int32_t v[kDcPer];
+    DcElem e;
+    uint32_t reset_at;
+};
+__device__ __forceinline__ void dc_local(const uint32_t* __restrict__ rec, uint32_t j0, uint32_t hi, uint32_t bpm, uint32_t ri, uint32_t blk_comp,
+    DcLocal& L)
+{
+    uint32_t bim = j0 % bpm;
+    uint32_t rim = ri ? j0 % ri : (j0 == 0u ? 0u : 1u); // position inside the restart interval; without restarts only block 0 resets
+    L.e = DcElem{0, 0, 0, 0};
+    L.reset_at = kDcPer;
+#pragma unroll
+    for (int i = 0; i < kDcPer; ++i) {
+        const uint32_t j = j0 + i;
+        L.r[i] = (j < hi) ? rec[j] : 0u;
+        if (rim == 0u && j < hi) {
+            L.e = DcElem{1, 0, 0, 0};
+            L.reset_at = min(L.reset_at, uint32_t(i));
+        }
+        const uint32_t c = (blk_comp >> (2u * bim)) & 3u;
+        const int32_t diff = int32_t(L.r[i]) >> 16;
+        L.e.d0 += (c == 0u) ? diff : 0;
+        L.e.d1 += (c == 1u) ? diff : 0;
+        L.e.d2 += (c == 2u) ? diff : 0;
+        L.v[i] = (c == 0u) ? L.e.d0 : (c == 1u ? L.e.d1 : L.e.d2);
+        bim = (bim + 1u == bpm) ? 0u : bim + 1u;
+        ++rim;
+        if (ri && rim == ri)
+            rim = 0u;
+    }
+}
+
+__global__ void __launch_bounds__(kDcThreads) dc_sum_kernel(BatchDev bd, int redo_only)
+{
+    __shared__ DcElem s_warp[kDcThreads / 32];
+    const uint32_t cta = blockIdx.x;
+    const uint32_t img = bd.dc_cta_img[cta];
+    const ImageDev& im = bd.img[img];
+    const uint32_t flags = bd.state[img].flags;
+    if ((flags & (kFlagDirty | kFlagBadMarker)) || (redo_only && !(flags & kFlagRedo)))
+        return;
+    const uint32_t* rec = bd.blkrec + im.coef_off / 64;
+    const uint32_t j0 = im.dc_blk_lo + (cta - im.dc_cta_off) * kDcChunk + threadIdx.x * kDcPer;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    DcLocal L;
+    dc_local(rec, j0, im.write_blk_hi, im.bpm, im.restart_interval * im.bpm, im.blk_comp, L);
+    const DcElem inc = dc_warp_scan(L.e, lane);
+    if (lane == 31)
+        s_warp[warp] = inc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        DcElem t = s_warp[0];
+        for (int i = 1; i < kDcThreads / 32; ++i)
+            t = dc_combine(t, s_warp[i]);
+        bd.dc_sum[cta] = make_int4(t.f, t.d0, t.d1, t.d2);
+    }
+}
+
+__global__ void __launch_bounds__(kDcThreads, 2) dc_apply_kernel(BatchDev bd, int redo_only)
 {
     __shared__ DcElem s_warp[kDcThreads / 32];
     __shared__ DcElem s_carry;
-    const uint32_t img = blockIdx.x;
+    const uint32_t cta = blockIdx.x;
+    const uint32_t img = bd.dc_cta_img[cta];
     const ImageDev& im = bd.img[img];
     const uint32_t flags = bd.state[img].flags;
     if ((flags & (kFlagDirty | kFlagBadMarker)) || (redo_only && !(flags & kFlagRedo)))
         return;
     uint32_t* rec = bd.blkrec + im.coef_off / 64;
-    const uint32_t lo = im.dc_blk_lo, hi = im.write_blk_hi;
-    const uint32_t bpm = im.bpm, ri = im.restart_interval * bpm, blk_comp = im.blk_comp;
+    const uint32_t chunk = cta - im.dc_cta_off;
+    const uint32_t j0 = im.dc_blk_lo + chunk * kDcChunk + threadIdx.x * kDcPer;
+    const uint32_t hi = im.write_blk_hi, bpm = im.bpm, blk_comp = im.blk_comp;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0)
-        s_carry = DcElem{0, 0, 0, 0};
-    __syncthreads();
-    for (uint32_t base = lo; base < hi; base += kDcThreads * kDcPer) {
-        const uint32_t j0 = base + threadIdx.x * kDcPer;
-        uint32_t bim = j0 % bpm;
-        uint32_t rim = ri ? j0 % ri : 1u; // position inside the restart interval (never 0 without restarts ...
-        if (!ri && j0 == 0u)
-            rim = 0u;                     // ... except at the very first block)
-        uint32_t r[kDcPer];
-        int32_t v[kDcPer];
-        DcElem e{0, 0, 0, 0};
-        uint32_t reset_at = kDcPer; // first i at which this thread's sums became absolute
-#pragma unroll
-        for (int i = 0; i < kDcPer; ++i) {
-            const uint32_t j = j0 + i;
-            r[i] = (j < hi) ? rec[j] : 0u;
-            if (rim == 0u && j < hi) {
-                e = DcElem{1, 0, 0, 0};
-                reset_at = min(reset_at, uint32_t(i));
+    // predictors at the start of this chunk: the sums of the chunks before it, combined in order by warp 0
+    if (warp == 0) {
+        DcElem carry{0, 0, 0, 0};
+        for (uint32_t c0 = 0; c0 < chunk; c0 += 32) {
+            DcElem e{0, 0, 0, 0};
+            if (c0 + lane < chunk) {
+                const int4 t = bd.dc_sum[im.dc_cta_off + c0 + lane];
+                e = DcElem{t.x, t.y, t.z, t.w};
             }
-            const uint32_t c = (blk_comp >> (2u * bim)) & 3u;
-            const int32_t diff = int32_t(r[i]) >> 16;
-            e.d0 += (c == 0u) ? diff : 0;
-            e.d1 += (c == 1u) ? diff : 0;
-            e.d2 += (c == 2u) ? diff : 0;
-            v[i] = (c == 0u) ? e.d0 : (c == 1u ? e.d1 : e.d2);
-            bim = (bim + 1u == bpm) ? 0u : bim + 1u;
-            ++rim;
-            if (ri && rim == ri)
-                rim = 0u;
+            e = dc_warp_scan(e, lane);
+            DcElem last;
+            last.f = __shfl_sync(0xffffffffu, e.f, 31);
+            last.d0 = __shfl_sync(0xffffffffu, e.d0, 31);
+            last.d1 = __shfl_sync(0xffffffffu, e.d1, 31);
+            last.d2 = __shfl_sync(0xffffffffu, e.d2, 31);
+            carry = dc_combine(carry, last);
         }
-        // inclusive scan over the CTA
-        DcElem inc = e;
+        if (lane == 0)
+            s_carry = carry;
+    }
+    DcLocal L;
+    dc_local(rec, j0, hi, bpm, im.restart_interval * bpm, blk_comp, L);
+    const DcElem inc = dc_warp_scan(L.e, lane);
+    if (lane == 31)
+        s_warp[warp] = inc;
+    __syncthreads();
+    DcElem pre = s_carry;
+    for (int i = 0; i < warp; ++i)
+        pre = dc_combine(pre, s_warp[i]);
+    const DcElem prev = dc_shfl_up(inc, 1);
+    const DcElem ex = (lane == 0) ? pre : dc_combine(pre, prev); // everything before this thread's blocks
+    // second walk: add the incoming predictors to the blocks that precede this thread's first reset
+    uint32_t bim = j0 % bpm;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const DcElem o = dc_shfl_up(inc, d);
-            if (lane >= d)
-                inc = dc_combine(o, inc);
-        }
-        if (lane == 31)
-            s_warp[warp] = inc;
-        __syncthreads();
-        DcElem pre = s_carry;
-        for (int i = 0; i < warp; ++i)
-            pre = dc_combine(pre, s_warp[i]);
-        const DcElem prev = dc_shfl_up(inc, 1);
-        const DcElem ex = (lane == 0) ? pre : dc_combine(pre, prev); // everything before this thread's blocks
-        // second walk: add the incoming predictors to the blocks that precede this thread's first reset
-        bim = j0 % bpm;
-#pragma unroll
-        for (int i = 0; i < kDcPer; ++i) {
-            const uint32_t j = j0 + i;
-            const uint32_t c = (blk_comp >> (2u * bim)) & 3u;
-            const int32_t add = (uint32_t(i) < reset_at) ? (c == 0u ? ex.d0 : (c == 1u ? ex.d1 : ex.d2)) : 0;
-            if (j < hi)
-                rec[j] = (r[i] & 0xFFFFu) | (uint32_t(v[i] + add) << 16);
-            bim = (bim + 1u == bpm) ? 0u : bim + 1u;
-        }
-        __syncthreads();
-        if (threadIdx.x == kDcThreads - 1)
-            s_carry = dc_combine(pre, inc);
-        __syncthreads();
+    for (int i = 0; i < kDcPer; ++i) {
+        const uint32_t j = j0 + i;
+        const uint32_t c = (blk_comp >> (2u * bim)) & 3u;
+        const int32_t add = (uint32_t(i) < L.reset_at) ? (c == 0u ? ex.d0 : (c == 1u ? ex.d1 : ex.d2)) : 0;
+        if (j < hi)
+            rec[j] = (L.r[i] & 0xFFFFu) | (uint32_t(L.v[i] + add) << 16);
+        bim = (bim + 1u == bpm) ? 0u : bim + 1u;
     }
 }
 
@@ -1679,10 +1730,11 @@ int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s)
 
 int launch_dc_scan(const BatchDev& b, bool redo_only, cudaStream_t s)
 {
-    if (b.n_images == 0 || b.n_wseq == 0)
+    if (b.n_dc_cta == 0)
         return 0;
-    dc_scan_kernel<<<b.n_images, kDcThreads, 0, s>>>(b, redo_only ? 1 : 0);
-    return 1;
+    dc_sum_kernel<<<b.n_dc_cta, kDcThreads, 0, s>>>(b, redo_only ? 1 : 0);
+    dc_apply_kernel<<<b.n_dc_cta, kDcThreads, 0, s>>>(b, redo_only ? 1 : 0);
+    return 2;
 }
 
 int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s)

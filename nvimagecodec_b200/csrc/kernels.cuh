@@ -20,6 +20,9 @@ constexpr int kSeqMult = 1;           // K1: subsequences per thread ...
 constexpr int kSeqLogical = kSeqThreads * kSeqMult; // ... i.e. per CTA ("sequence"), of which the
 constexpr int kSeqWarm = 8;           // leading ones only warm up the entry state
 constexpr int kSeqStride = kSeqLogical - kSeqWarm;
+constexpr int kDcThreads = 512;       // K3b: threads per CTA, ...
+constexpr int kDcPer = 8;             //      blocks per thread,
+constexpr int kDcChunk = kDcThreads * kDcPer; // blocks per CTA
 
 // ---- per-image error / state flags (ImageState::flags)
 enum : uint32_t {
@@ -55,6 +58,7 @@ struct ImageDev {
     uint32_t huff_set;
     uint32_t blk_comp;              // 2 bits per block-in-MCU: component
     uint32_t blk_tab;               // bit b: DC table id of block b, bit 16+b: AC table id
+    uint32_t dc_cta_off, n_dc_cta;  // K3b chunks of kDcChunk blocks covering [dc_blk_lo, write_blk_hi)
     uint32_t idct_cta_off, n_idct_cta;
     uint32_t color_cta_off, n_color_cta_x, n_color_cta_y;
     uint32_t color_cta_x_rcp;       // ceil(2^32 / n_color_cta_x): cta -> (row, column) without a division
@@ -106,9 +110,11 @@ struct BatchDev {
     uint32_t* blkrec;       // per coefficient block: bits 0-7 which of its eight 16-byte groups K3 wrote (bit g = group g),
                             // bits 16-31 its DC: the coded difference out of K3, the value after K3b
     uint8_t* planes;
+    const uint32_t* dc_cta_img;   // K3b CTA -> image
+    int4* dc_sum;                 // K3b: per chunk (reset seen, DC sums of the three components)
     const uint32_t* idct_cta_img;
     const uint32_t* color_cta_img;
-    int n_tiles, n_seq, n_wseq, n_sub, n_idct_cta, n_color_cta;
+    int n_tiles, n_seq, n_wseq, n_sub, n_dc_cta, n_idct_cta, n_color_cta;
     uint32_t* sync_stats;   // optional K1 counters (4 x uint32), may be null
     uint32_t sub_bits;      // subsequence length in bits for this batch
 };
