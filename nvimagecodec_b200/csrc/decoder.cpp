@@ -106,7 +106,7 @@ Options parse_options(const char* options, const char* decoder_id)
             o.chunk_images = std::max(1, std::atoi(value.c_str()));
         else if (name == "subseq_bits") {
             const int v = std::atoi(value.c_str());
-            if (v == 1024 || v == 2048 || v == 4096)
+            if (v == 512 || v == 1024 || v == 2048 || v == 4096)
                 o.subseq_bits = v;
         } else if (name == "max_fix_rounds")
             o.max_fix_rounds = std::atoi(value.c_str());
@@ -183,14 +183,19 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         uint64_t total_bits = 0;
         for (int i = 0; i < n; ++i)
             total_bits += uint64_t(len[i]) * 8;
-        uint32_t sb = kMinSubseqBits;
+        // Measured on B200 (profiles/README.md): full-size batches decode fastest with 2048-bit subsequences,
+        // smaller ones with shorter subsequences, i.e. more threads, until the GPU is filled again.
+        uint32_t sb = 512;
         if (opt_.subseq_bits)
             sb = uint32_t(opt_.subseq_bits);
-        else if (total_bits / 4096 >= 400000)
+        else if (total_bits >= (uint64_t(1600) << 20))
             sb = 4096;
-        else if (total_bits / 2048 >= 50000)
+        else if (total_bits >= (uint64_t(400) << 20))
             sb = 2048;
+        else if (total_bits >= (uint64_t(48) << 20))
+            sb = 1024;
         bd_.sub_bits = sb;
+        bd_.seq_warm = std::max<uint32_t>(kSeqWarmMin, kSeqWarmBits / sb);
     }
     const size_t sub_bytes = bd_.sub_bits / 8;
     size_t raw_bytes = 0, cmp_bytes = 0, coef_elems = 0, plane_bytes = 0, bounce_bytes = 0;
@@ -247,7 +252,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.n_sub_max = uint32_t((hd.scan_length + sub_bytes - 1) / sub_bytes);
         n_sub += im.n_sub_max;
         im.seq_off = n_seq;
-        im.n_seq = (im.n_sub_max + kSeqStride - 1) / kSeqStride;
+        im.n_seq = (im.n_sub_max + (kSeqLogical - bd_.seq_warm) - 1) / (kSeqLogical - bd_.seq_warm);
         n_seq += im.n_seq;
         im.wseq_off = n_wseq;
         im.n_wseq = (im.n_sub_max + kSeqThreads - 1) / kSeqThreads;
@@ -808,7 +813,7 @@ int Decoder::scan_segment(const void* dev_raw, size_t length, uint32_t expected_
     b.cmp = static_cast<uint32_t*>(dev_words);
     b.bnd = dev_bnd;
     b.n_tiles = int(n_tiles);
-    b.sub_bits = kMinSubseqBits;
+    b.sub_bits = 1024; // only sizes the n_sub field of the result (documented as 1024-bit units)
     launch_scan(b, stream);
     if (!cuda_ok(cudaGetLastError(), "kernel launch"))
         return B200JPEG_ERR_CUDA;

@@ -630,7 +630,7 @@ __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageD
     return sv;
 }
 
-// K1.  One CTA = kSeqStride consecutive subsequences of one image (+ kSeqWarm leading threads whose
+// K1.  One CTA = kSeqLogical - seq_warm consecutive subsequences of one image (+ seq_warm leading threads whose
 // only job is to make the CTA's entry state right with high probability).
 //   round 0  every thread decodes the last quarter subsequence BEFORE its own from the bare guess
 //            "a code word starts here, at a block start": JPEG Huffman streams self-synchronise
@@ -671,17 +671,18 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     const ImageState st = bd.state[img];
     if (st.n_sub == 0u || (fix_mode && !(st.flags & kFlagDirty)))
         return;
-    const uint32_t first_k = (seq - im.seq_off) * kSeqStride;
+    const int warm = int(bd.seq_warm); // leading subsequences of the CTA that only warm up its entry state (host: by subsequence length)
+    const uint32_t first_k = (seq - im.seq_off) * uint32_t(kSeqLogical - warm);
     if (first_k >= st.n_sub)
         return;
     load_huff_set(s_hs, bd.huff + im.huff_set);
     build_block_table(s_bt, s_hs, im);
     const StreamView sv = make_view(bd, im, st);
     const int t = threadIdx.x;
-    const int k0 = int(first_k) - kSeqWarm; // subsequence of logical thread 0 (may be negative)
+    const int k0 = int(first_k) - warm; // subsequence of logical thread 0 (may be negative)
     const bool skip_warm = fix_mode || no_warm;
-    auto is_active = [&](int l) { return k0 + l >= 0 && k0 + l < int(st.n_sub) && (!skip_warm || l >= kSeqWarm); };
-    auto has_pred = [&](int l) { return is_active(l) && l > 0 && k0 + l > 0 && (!skip_warm || l > kSeqWarm); };
+    auto is_active = [&](int l) { return k0 + l >= 0 && k0 + l < int(st.n_sub) && (!skip_warm || l >= warm); };
+    auto has_pred = [&](int l) { return is_active(l) && l > 0 && k0 + l > 0 && (!skip_warm || l > warm); };
     if (t == 0)
         sh.count[0] = sh.count[1] = 0;
     for (int l = t; l < kSeqLogical; l += kSeqThreads)
@@ -696,7 +697,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
             sh.out[l] = active ? bd.sub_out[g] : kStateDone;
             if (active) {
                 in = bd.sub_in[g];
-                if (l == kSeqWarm) {
+                if (l == warm) {
                     const uint32_t want = (k0 + l > 0) ? bd.sub_out[g - 1] : 0u;
                     if (want != in) {
                         in = want;
@@ -777,7 +778,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     }
     // results of the real (non warm-up) subsequences
     for (int l = t; l < kSeqLogical; l += kSeqThreads) {
-        if (is_active(l) && l >= kSeqWarm && sh.fresh[l]) {
+        if (is_active(l) && l >= warm && sh.fresh[l]) {
             const uint32_t g = im.sub_off + uint32_t(k0 + l);
             bd.sub_in[g] = sh.in[l];
             bd.sub_out[g] = sh.out[l];
@@ -1874,7 +1875,7 @@ extern "C" B200JPEG_API int b200jpegScanSegmentNoAlloc(const void* dev_raw, size
     b.cmp = static_cast<uint32_t*>(dev_out_words);
     b.bnd = dev_out_boundaries;
     b.n_tiles = int(p.n_tiles);
-    b.sub_bits = kMinSubseqBits;
+    b.sub_bits = 1024; // only sizes the n_sub field of the result (documented as 1024-bit units)
     launch_scan(b, stream);
     if (cudaGetLastError() != cudaSuccess) {
         noalloc_message(message, message_capacity, "b200jpegScanSegmentNoAlloc: kernel launch failed");

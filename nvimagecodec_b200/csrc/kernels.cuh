@@ -13,13 +13,13 @@ namespace b200jpeg {
 constexpr int kScanThreads = 256;     // K0: 64 B (four 16-byte chunks) of byte-stuffed scan data per thread,
 constexpr int kScanChunks = 4;        //     16 KiB per CTA
 constexpr int kScanTileBytes = kScanThreads * 16 * kScanChunks;
-constexpr int kMinSubseqBits = 1024;  // K1-K3: bits of unstuffed stream per thread ("subsequence"); the host picks
-constexpr int kMaxSubseqBits = 4096;  //   1024, 2048 or 4096 per batch (BatchDev::sub_bits) so the GPU stays filled
+constexpr int kMinSubseqBits = 512;   // K1-K3: bits of unstuffed stream per thread ("subsequence"); the host picks
+constexpr int kMaxSubseqBits = 4096;  //   512 .. 4096 per batch (BatchDev::sub_bits) so the GPU stays filled
 constexpr int kSeqThreads = 256;      // threads per CTA of the entropy kernels
 constexpr int kSeqMult = 1;           // K1: subsequences per thread ...
 constexpr int kSeqLogical = kSeqThreads * kSeqMult; // ... i.e. per CTA ("sequence"), of which the
-constexpr int kSeqWarm = 8;           // leading ones only warm up the entry state
-constexpr int kSeqStride = kSeqLogical - kSeqWarm;
+constexpr int kSeqWarmBits = 8192;    // leading ones only warm up the entry state: this many bits of them (BatchDev::seq_warm),
+constexpr int kSeqWarmMin = 8;        // at least this many subsequences
 constexpr int kDcThreads = 512;       // K3b: threads per CTA, ...
 constexpr int kDcPer = 8;             //      blocks per thread,
 constexpr int kDcChunk = kDcThreads * kDcPer; // blocks per CTA
@@ -117,6 +117,7 @@ struct BatchDev {
     int n_tiles, n_seq, n_wseq, n_sub, n_dc_cta, n_idct_cta, n_color_cta;
     uint32_t* sync_stats;   // optional K1 counters (4 x uint32), may be null
     uint32_t sub_bits;      // subsequence length in bits for this batch
+    uint32_t seq_warm;      // warm-up subsequences at the head of every K1 CTA
 };
 
 // Kernel launchers (kernels.cu).  Each returns the number of kernels it launched.

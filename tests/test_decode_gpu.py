@@ -199,7 +199,7 @@ def test_resync_path_and_no_rst_large_stream(decoder_cls):
         dec.close()
 
 
-@pytest.mark.parametrize("bits", [1024, 2048, 4096])
+@pytest.mark.parametrize("bits", [512, 1024, 2048, 4096])
 def test_every_subsequence_length_is_bit_exact(decoder_cls, bits):
     """The host picks 1024 / 2048 / 4096-bit subsequences per batch; force each, with and without the
     warm-up / probe heuristics, on streams with and without restart markers."""
