@@ -656,6 +656,7 @@ __device__ __forceinline__ uint32_t pack_info(const DecodeResult& r) { return ui
 // ("logical threads" l = m * kSeqThreads + t): the full pass runs kSeqMult times back to back, and the
 // repair rounds batch the work of the whole range, so they run with (nearly) full warps instead of
 // idling most of the CTA at the round barriers.
+template <int kWarm>
 __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int mode)
 {
     extern __shared__ uint4 s_raw[];
@@ -671,7 +672,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     const ImageState st = bd.state[img];
     if (st.n_sub == 0u || (fix_mode && !(st.flags & kFlagDirty)))
         return;
-    const int warm = int(bd.seq_warm); // leading subsequences of the CTA that only warm up its entry state (host: by subsequence length)
+    constexpr int warm = kWarm; // leading subsequences of the CTA that only warm up its entry state (BatchDev::seq_warm)
     const uint32_t first_k = (seq - im.seq_off) * uint32_t(kSeqLogical - warm);
     if (first_k >= st.n_sub)
         return;
@@ -1705,11 +1706,16 @@ int launch_sync(const BatchDev& b, bool fix_mode, bool no_warm, cudaStream_t s)
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        cudaFuncSetAttribute(huff_sync_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSyncSmem));
+        cudaFuncSetAttribute(huff_sync_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSyncSmem));
+        cudaFuncSetAttribute(huff_sync_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSyncSmem));
         cudaFuncSetAttribute(huff_write_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kWriteSmem));
         attr_set[dev] = true;
     }
-    huff_sync_kernel<<<b.n_seq, kSeqThreads, kSyncSmem, s>>>(b, (fix_mode ? 1 : 0) | (no_warm ? 2 : 0));
+    const int mode = (fix_mode ? 1 : 0) | (no_warm ? 2 : 0);
+    if (b.seq_warm == 16) // the two values the host uses (decoder.cpp: 8 Kbit of warm-up, at least 8 subsequences)
+        huff_sync_kernel<16><<<b.n_seq, kSeqThreads, kSyncSmem, s>>>(b, mode);
+    else
+        huff_sync_kernel<8><<<b.n_seq, kSeqThreads, kSyncSmem, s>>>(b, mode);
     return 1;
 }
 
