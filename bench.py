@@ -371,7 +371,7 @@ def main():
                 traffic = {k.replace("_kernel", ""): v["dram_bytes"] for k, v in json.load(f)["kernels"].items()}
         except Exception:
             pass
-        ncu_name = {"scan(K0)": "scan_scatter", "huff_sync(K1)": "huff_sync", "verify_scan(K2)": "verify_scan", "huff_write(K3)": "huff_write", "dc_scan(K3b)": "dc_scan",
+        ncu_name = {"scan(K0)": "scan_scatter", "huff_sync(K1)": "huff_sync", "verify_scan(K2)": "verify_scan", "huff_write(K3)": "huff_write", "dc_scan(K3b)": "dc_apply",
                     "idct(K4a)": "idct", "color(K4b)": "color"}
         if top:
             ach = kbytes[top] / (stages[top] * 1e-3) / 1e9

@@ -13,7 +13,7 @@ def val(r, k, table):
     return float(r[idx[k]].replace(",", "")) * table.get(units[idx[k]], 1.0)
 out = {"source": "%s (ncu --set full --clock-control none), %s" % (os.path.basename(rep), what), "kernels": {}}
 for r in rows[2:]:
-    name = r[idx["Kernel Name"]].split("(")[0].split("::")[-1]
+    name = r[idx["Kernel Name"]].split("(")[0].split("::")[-1].split("<")[0]
     if name in out["kernels"]:
         continue  # first launch of each kernel
     rd, wr = val(r, "dram__bytes_read.sum", scale), val(r, "dram__bytes_write.sum", scale)
