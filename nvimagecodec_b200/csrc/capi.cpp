@@ -83,7 +83,10 @@ int b200jpegCreate(b200jpegDecoder_t* decoder, int device_id, const char* option
     auto* h = new (std::nothrow) b200jpegDecoder_st;
     if (!h)
         return B200JPEG_ERR_ARG;
-    h->pipe = new (std::nothrow) Pipeline(device_id, b200jpeg::parse_options(options, kDecoderId));
+    {
+        const b200jpeg::Options opt = b200jpeg::parse_options(options, kDecoderId);
+        h->pipe = new (std::nothrow) Pipeline(device_id, opt, opt.lanes);
+    }
     if (!h->pipe) {
         delete h;
         return B200JPEG_ERR_ARG;

@@ -101,7 +101,11 @@ Options parse_options(const char* options, const char* decoder_id)
         else if (name == "debug_no_warm")
             o.debug_no_warm = std::atoi(value.c_str()) != 0;
         else if (name == "chunk_mb")
-            o.chunk_mb = std::max(1, std::atoi(value.c_str()));
+            o.chunk_mb = std::max(0, std::atoi(value.c_str()));
+        else if (name == "direct_kb")
+            o.direct_kb = std::max(1, std::atoi(value.c_str()));
+        else if (name == "lanes")
+            o.lanes = std::min(8, std::max(1, std::atoi(value.c_str())));
         else if (name == "chunk_images")
             o.chunk_images = std::max(1, std::atoi(value.c_str()));
         else if (name == "subseq_bits") {
@@ -476,7 +480,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         std::fill(color_img + im.color_cta_off, color_img + im.color_cta_off + im.n_color_cta_x * im.n_color_cta_y, uint32_t(d));
         cudaPointerAttributes attr{};
         // small streams are cheaper to gather into the staging block (one big copy) than to copy one by one
-        if (im.raw_len >= (128u << 10) && cudaPointerGetAttributes(&attr, data[in_index_[d]]) == cudaSuccess && attr.type == cudaMemoryTypeHost)
+        if (im.raw_len >= (uint32_t(opt_.direct_kb) << 10) && cudaPointerGetAttributes(&attr, data[in_index_[d]]) == cudaSuccess && attr.type == cudaMemoryTypeHost)
             direct[d] = 1;
         else {
             cudaGetLastError();
@@ -493,7 +497,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 std::memcpy(up + off_raw + im.raw_off, static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[d].scan_offset, im.raw_len);
             }
         };
-        const int nthreads = staged_bytes > (size_t(8) << 20) ? std::min(4, std::max(1, int(std::thread::hardware_concurrency()) / 2)) : 1;
+        const int nthreads = staged_bytes > (size_t(2) << 20) ? std::min(4, std::max(1, int(std::thread::hardware_concurrency()) / 2)) : 1;
         if (nthreads <= 1) {
             stage(0, nd);
         } else {
@@ -862,7 +866,15 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         size_t total = 0;
         for (int i = 0; i < n; ++i)
             total += len[i];
-        const size_t chunk_bytes = size_t(opt_.chunk_mb) << 20;
+        size_t chunk_bytes = size_t(opt_.chunk_mb) << 20;
+        if (!chunk_bytes) {
+            // Pinned bitstreams are copied straight from the caller's buffers: small chunks start the GPU early.  Pageable ones
+            // are gathered into a pinned staging block first (a few threads per chunk): that wants bigger chunks.
+            cudaPointerAttributes attr{};
+            const bool pinned = n > 0 && data[0] && cudaPointerGetAttributes(&attr, data[0]) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+            cudaGetLastError();
+            chunk_bytes = size_t(pinned ? 8 : 24) << 20;
+        }
         const int chunk_images = opt_.chunk_images;
         const bool split = lanes_.size() > 1 && (total > chunk_bytes + chunk_bytes / 3 || n > 2 * chunk_images);
         for (int i = 0; i < n; ++i) {

@@ -40,7 +40,9 @@ struct Options {
     bool debug_no_warm = false;   // test hook: forces the re-synchronisation path
     int max_fix_rounds = 1 << 20;
     int subseq_bits = 0;          // 0 = choose per batch; else 1024 / 2048 / 4096
-    int chunk_mb = 24;            // pipeline chunk: this much bitstream ...
+    int chunk_mb = 0;             // pipeline chunk: this much bitstream (0 = 8 MB for pinned sources, 24 MB for pageable ones, which are staged by a few threads) ...
+    int direct_kb = 128;          // pinned bitstreams of at least this many KiB are copied straight from the caller's buffer
+    int lanes = 6;                // pipeline lanes (decoder + stream each) the chunks rotate over
     int chunk_images = 64;        // ... or this many images, whichever comes first
 };
 
@@ -114,7 +116,7 @@ class Decoder {
 // Chunked, overlapped decode of a whole batch (what b200jpegDecodeBatch and the extension's decodeBatch use).
 class Pipeline {
   public:
-    Pipeline(int device_id, const Options& opt, int n_lanes = 3);
+    Pipeline(int device_id, const Options& opt, int n_lanes = 6);
     ~Pipeline();
     int decode(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, int* status, cudaStream_t user_stream);
     Decoder& lane0() { return *lanes_[0].dec; } // Prepare / Execute / Finish and the kernel-level entry points use this one
