@@ -248,6 +248,11 @@ def main():
             numa = "nvml cpu affinity, %d cpus" % len(os.sched_getaffinity(0))
         except Exception as e:  # affinity is an optimisation only
             numa = "unavailable (%s)" % type(e).__name__
+    # stdout carries exactly one JSON line: whatever native libraries print meanwhile (NCCL's version banner under
+    # NCCL_DEBUG=VERSION, for one) goes to stderr
+    sys.stdout.flush()
+    stdout_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     global_sizes = [len(base[i % args.batch]) for i in range(args.batch * world)]
@@ -412,7 +417,10 @@ def main():
             "cpu_baseline": cpu,
             "clocks": clocks,
         }
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.dup2(stdout_fd, 1)
+        print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
     if world > 1:
         dist.destroy_process_group()
     return 0
