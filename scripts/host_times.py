@@ -1,10 +1,11 @@
-"""Host-side cost of the three phases of a batch (C2, 256 images, pinned bitstreams, pixels left in HBM)."""
+"""Host-side cost of the three phases of a batch (256 images of the named config, pinned bitstreams, pixels left in HBM)."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from nvimagecodec_b200 import Decoder
 import bench
-jp = bench.make_corpus(256, os.cpu_count())
+wl = sys.argv[1] if len(sys.argv) > 1 else 'c2'
+jp = bench.make_workload(wl, 256, os.cpu_count())[0]
 pinned = [torch.frombuffer(bytearray(j), dtype=torch.uint8).pin_memory() for j in jp]
 srcs = [t.numpy() for t in pinned]
 dec = Decoder(0, options=":fancy_upsampling=1")

@@ -397,3 +397,56 @@ def test_tight_rows_at_every_byte_alignment(dec_fancy, fmt):
     assert dec_fancy.last_status == [_lib.OK] * len(srcs)
     for d, roi, o in zip(srcs, rois, outs):
         assert np.array_equal(o.cpu().numpy(), oracle.decode(d, OFMT[fmt], fancy=True, roi=roi))
+
+
+@pytest.mark.parametrize("extra", ["", " b200_jpeg_decoder:debug_no_warm=1", " b200_jpeg_decoder:subseq_bits=512"])
+def test_fuzzed_entropy_data_never_takes_the_batch_down(decoder_cls, extra):
+    """A few hundred damaged variants (byte flips anywhere in the scan incl. fresh FF xx pairs, truncations, stray and
+    missing RSTn, tail garbage) share batches with pristine images: the call returns, every pristine image stays
+    bit-exact (no out-of-bounds write reached a neighbour's coefficients, planes or pixels), and the decoder is reusable."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    rng = np.random.default_rng(20261107)
+    base = [corpus.encode(corpus.synth(96, 128, 70), 90, "420"), corpus.encode(corpus.synth(120, 88, 71), 75, "444", rst_interval=2),
+            corpus.encode(corpus.synth(64, 200, 72), 95, "422", rst_interval=5), corpus.encode(corpus.synth(72, 72, 73), 85, gray=True),
+            corpus.encode(corpus.synth(300, 420, 74), 92, "420")]
+    refs = [oracle.decode(d, oracle.FMT_I_RGB, True) for d in base]
+    dec = decoder_cls(0, options=":fancy_upsampling=1" + extra)
+    for rnd in range(4):
+        srcs, clean = [], []
+        for k in range(60):
+            b = int(rng.integers(0, len(base)))
+            d = bytearray(base[b])
+            so = oracle.info(base[b])["scan_offset"]
+            kind = int(rng.integers(0, 6))
+            if kind == 0:  # flips, any value (may create markers, stuffing, fill bytes)
+                for p in rng.integers(so, len(d) - 2, size=int(rng.integers(1, 30))):
+                    d[p] = int(rng.integers(0, 256))
+            elif kind == 1:  # truncation, with or without an EOI
+                d = d[:int(rng.integers(so + 1, len(d)))] + (bytearray(b"\xff\xd9") if rng.integers(0, 2) else bytearray())
+            elif kind == 2:  # stray restart markers
+                for p in sorted(rng.integers(so, len(d) - 2, size=3), reverse=True):
+                    d[p:p] = bytes([0xFF, 0xD0 + int(rng.integers(0, 8))])
+            elif kind == 3:  # a run of FF / 00
+                p = int(rng.integers(so, len(d) - 40))
+                d[p:p + 32] = bytes([0xFF if rng.integers(0, 2) else 0x00]) * 32
+            elif kind == 4:  # garbage behind the data, no EOI
+                d = d[:-2] + bytearray(rng.integers(0, 256, size=64, dtype=np.uint8).tobytes())
+            else:  # a chunk cut out of the middle
+                p = int(rng.integers(so, len(d) - 50))
+                del d[p:p + int(rng.integers(1, 40))]
+            srcs.append(bytes(d))
+            if k % 4 == 0:
+                clean.append((len(srcs), b))
+                srcs.append(base[b])
+        outs = dec.decode(srcs, "I_RGB")
+        st = dec.last_status
+        assert len(st) == len(srcs)
+        for pos, b in clean:
+            assert st[pos] == _lib.OK
+            assert np.array_equal(outs[pos].cpu().numpy(), refs[b])
+    outs = dec.decode(base, "I_RGB")
+    assert dec.last_status == [_lib.OK] * len(base)
+    for o, r in zip(outs, refs):
+        assert np.array_equal(o.cpu().numpy(), r)
+    dec.close()
