@@ -91,6 +91,11 @@ B200JPEG_API int b200jpegProbe(const void* data, size_t length, b200jpegStreamIn
 /* Create / destroy a decoder bound to one GPU.  options is the nvImageCodec
  * option string ("<id>:<name>=<value>" tokens, include/nvimgcodec.h:1967-1971);
  * understood: fancy_upsampling=<0|1> (default 1, as libjpeg_turbo_decoder.cpp:223-249).
+ * Tuning knobs (defaults are measured choices, results do not depend on them): subseq_bits=<512|1024|2048|4096>
+ * (bits of entropy-coded data per GPU thread; default by batch size), lanes=<1..8> (pipeline lanes, default 6),
+ * chunk_mb / chunk_images (pipeline chunk, default 8 MB for pinned bitstreams, 24 MB for pageable ones, 64 images),
+ * direct_kb (pinned bitstreams of at least this size are copied without staging, default 128), max_fix_rounds;
+ * debug_no_warm=1 is a test hook that forces the re-synchronisation path.
  * Replaces nvimgcodecDecoderDesc_t::create / destroy (include/nvimgcodec.h:1466-1482). */
 B200JPEG_API int b200jpegCreate(b200jpegDecoder_t* decoder, int device_id, const char* options);
 B200JPEG_API int b200jpegDestroy(b200jpegDecoder_t decoder);
