@@ -32,7 +32,17 @@ int b200jpegProbe(const void* data, size_t length, b200jpegStreamInfo_t* info)
         return B200JPEG_ERR_ARG;
     std::memset(info, 0, sizeof(*info));
     b200jpeg::StreamHeader hd;
-    const b200jpeg::StreamStatus st = b200jpeg::parse_stream(static_cast<const uint8_t*>(data), length, &hd);
+    b200jpeg::StreamStatus st = b200jpeg::parse_stream(static_cast<const uint8_t*>(data), length, &hd);
+    if (st == b200jpeg::kStreamMultiScan) { // three scans of one component each: decoded as three one-component images
+        b200jpeg::StreamHeader sc[3];
+        st = b200jpeg::parse_multiscan(static_cast<const uint8_t*>(data), length, &hd, sc);
+        if (st == b200jpeg::kStreamOk) {
+            hd.scan_offset = sc[0].scan_offset;
+            for (int c = 0; c < 3; ++c)
+                if (sc[c].scan_length >= (size_t(1) << 28))
+                    hd.scan_length = sc[c].scan_length;
+        }
+    }
     info->width = hd.width;
     info->height = hd.height;
     info->num_components = hd.ncomp;

@@ -173,12 +173,14 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     host_status_.assign(n, B200JPEG_OK);
     dev_index_.assign(n, -1);
     in_index_.clear();
+    gates_.clear();
     imgs_.clear();
     host_outs_.clear();
     set_index_.clear();
     std::vector<const HuffSetDev*> sets;
     std::vector<StreamHeader> hdrs;
     hdrs.reserve(n);
+    std::vector<size_t> item_of_dev; // device image -> its entry in hdrs
 
     // Subsequence length for this batch: longer subsequences cost fewer re-synchronisation rounds
     // (the block-in-MCU phase of a 4:2:0 stream needs a few MCUs to lock), shorter ones give more
@@ -206,14 +208,62 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     uint32_t n_tiles = 0, n_sub = 0, n_seq = 0, n_wseq = 0, n_bnd = 0, n_dc = 0, n_idct = 0, n_color = 0;
     comp_bytes_ = n_coefs_ = out_bytes_ = 0;
 
+    // Work list: one entry per device image.  A stream whose three components come in three scans becomes up to three
+    // one-component images (kChild; each decodes like a grayscale image of the component's size) plus the image itself
+    // (kParent: no entropy data of its own, its colour stage reads the children's planes).
+    enum { kNormal = 0, kChild = 1, kParent = 2 };
+    struct Item {
+        int i, role;
+    };
+    std::vector<Item> items;
+    items.reserve(n);
+    auto status_of = [](StreamStatus ss) {
+        return ss == kStreamNotJpeg ? B200JPEG_ERR_NOT_JPEG : (ss == kStreamUnsupported ? B200JPEG_ERR_UNSUPPORTED : B200JPEG_ERR_CORRUPT);
+    };
+    b200jpegOutput_t child_out;
+    std::memset(&child_out, 0, sizeof(child_out));
+    child_out.buffer = &child_out; // never written: a child has no colour stage
+    child_out.format = B200JPEG_FMT_Y;
     for (int i = 0; i < n; ++i) {
         StreamHeader hd;
         const StreamStatus ss = data[i] ? parse_stream(static_cast<const uint8_t*>(data[i]), len[i], &hd) : kStreamNotJpeg;
-        if (ss != kStreamOk) {
-            host_status_[i] = ss == kStreamNotJpeg ? B200JPEG_ERR_NOT_JPEG : (ss == kStreamUnsupported ? B200JPEG_ERR_UNSUPPORTED : B200JPEG_ERR_CORRUPT);
-            continue;
+        if (ss == kStreamOk) {
+            hdrs.push_back(hd);
+            items.push_back({i, kNormal});
+        } else if (ss == kStreamMultiScan) {
+            StreamHeader frame, sc[3];
+            const StreamStatus ms = parse_multiscan(static_cast<const uint8_t*>(data[i]), len[i], &frame, sc);
+            if (ms != kStreamOk) {
+                host_status_[i] = status_of(ms);
+                continue;
+            }
+            const int n_child = outs[i].format == B200JPEG_FMT_Y ? 1 : 3; // Y output consumes luma only
+            for (int c = 0; c < n_child; ++c) {
+                hdrs.push_back(sc[c]);
+                items.push_back({i, kChild});
+            }
+            frame.restart_interval = 0; // the parent has no scan of its own
+            hdrs.push_back(frame);
+            items.push_back({i, kParent});
+        } else {
+            host_status_[i] = status_of(ss);
         }
-        const b200jpegOutput_t& o = outs[i];
+    }
+    int children_ok = 0; // children of the multi-scan stream under way that made it into the batch
+    for (size_t item = 0; item < items.size(); ++item) {
+        const int i = items[item].i, role = items[item].role;
+        const StreamHeader& hd = hdrs[item];
+        if (role == kChild && (item == 0 || items[item - 1].role != kChild || items[item - 1].i != i))
+            children_ok = 0;
+        const b200jpegOutput_t& o = role == kChild ? child_out : outs[i];
+        if (role == kParent) {
+            const int want = o.format == B200JPEG_FMT_Y ? 1 : 3;
+            if (host_status_[i] != B200JPEG_OK || children_ok != want) {
+                if (host_status_[i] == B200JPEG_OK)
+                    host_status_[i] = B200JPEG_ERR_UNSUPPORTED;
+                continue;
+            }
+        }
         int x0 = o.roi_x0, y0 = o.roi_y0, x1 = o.roi_x1, y1 = o.roi_y1;
         if (x0 == 0 && y0 == 0 && x1 == 0 && y1 == 0) {
             x1 = hd.width;
@@ -244,6 +294,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         }
         ImageDev im;
         std::memset(&im, 0, sizeof(im));
+        uint32_t gate[3] = {0, 0, 0};
         im.raw_off = raw_bytes;
         im.raw_len = uint32_t(hd.scan_length);
         raw_bytes += align_up(hd.scan_length, 16) + 16;
@@ -267,7 +318,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.bnd_off = n_bnd;
         im.n_bnd_cap = im.n_rst_expected + 1;
         n_bnd += im.n_bnd_cap;
-        im.total_blocks = n_mcu * uint32_t(hd.blocks_per_mcu);
+        im.total_blocks = role == kParent ? 0u : n_mcu * uint32_t(hd.blocks_per_mcu);
         im.coef_off = coef_elems;
         coef_elems += size_t(im.total_blocks) * 64;
         im.width = uint16_t(hd.width);
@@ -287,8 +338,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         const int mcu_row_lo = std::max(0, y0 / mcu_h - 1), mcu_row_hi = std::min(hd.mcus_y, (y1 + mcu_h - 1) / mcu_h + 1);
         im.mcu_row_lo = uint16_t(mcu_row_lo);
         im.mcu_row_hi = uint16_t(mcu_row_hi);
-        im.write_blk_lo = uint32_t(mcu_row_lo) * uint32_t(hd.mcus_x) * uint32_t(hd.blocks_per_mcu);
-        im.write_blk_hi = uint32_t(mcu_row_hi) * uint32_t(hd.mcus_x) * uint32_t(hd.blocks_per_mcu);
+        im.write_blk_lo = role == kParent ? 0u : uint32_t(mcu_row_lo) * uint32_t(hd.mcus_x) * uint32_t(hd.blocks_per_mcu);
+        im.write_blk_hi = role == kParent ? 0u : uint32_t(mcu_row_hi) * uint32_t(hd.mcus_x) * uint32_t(hd.blocks_per_mcu);
         {   // DC differences are needed from the last predictor reset at or before the first wanted block
             const uint32_t ri_blocks = uint32_t(hd.restart_interval) * uint32_t(hd.blocks_per_mcu);
             im.dc_blk_lo = ri_blocks ? im.write_blk_lo / ri_blocks * ri_blocks : 0u;
@@ -312,7 +363,14 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             im.comp_w[c] = uint16_t((hd.width * hd.h[c] + hd.hmax - 1) / hd.hmax);
             im.comp_h[c] = uint16_t((hd.height * hd.v[c] + hd.vmax - 1) / hd.vmax);
             const size_t pw = size_t(hd.mcus_x) * hd.h[c] * 8, ph = size_t(hd.mcus_y) * hd.v[c] * 8;
-            if (c < im.ncomp_needed) {
+            if (role == kParent) {
+                if (c < im.ncomp_needed) { // the planes are the children's (the last `ncomp_needed` images pushed)
+                    const ImageDev& ch = imgs_[imgs_.size() - size_t(im.ncomp_needed) + size_t(c)];
+                    im.plane_off[c] = ch.plane_off[0];
+                    im.plane_stride_px[c] = ch.plane_stride_px[0];
+                    gate[c] = uint32_t(imgs_.size() - size_t(im.ncomp_needed) + size_t(c));
+                }
+            } else if (c < im.ncomp_needed) {
                 im.plane_off[c] = plane_bytes;
                 plane_bytes += align_up(pw * ph, 256);
                 idct_blocks += uint32_t(pw / 8) * uint32_t(mcu_row_hi - mcu_row_lo) * hd.v[c];
@@ -357,10 +415,14 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             im.n_color_cta_x = uint32_t((size_t(x1) - ax0 + 255) / 256);
             im.n_color_cta_y = uint32_t((size_t(y1) - ay0 + 8 * ur - 1) / (8 * ur));
             im.color_cta_x_rcp = im.n_color_cta_x > 1 ? uint32_t((uint64_t(1) << 32) / im.n_color_cta_x + 1) : 0u;
+            if (role == kChild)
+                im.n_color_cta_x = im.n_color_cta_y = 0; // planes only
         }
         n_color += im.n_color_cta_x * im.n_color_cta_y;
         HostOut ho{nullptr, 0, obytes};
-        if (o.buffer_is_host) {
+        if (role == kChild) {
+            im.out = nullptr;
+        } else if (o.buffer_is_host) {
             ho.host_ptr = o.buffer;
             ho.bounce_off = bounce_bytes;
             bounce_bytes += align_up(obytes, 256);
@@ -369,9 +431,11 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             im.out = static_cast<uint8_t*>(o.buffer);
         }
         // huffman set (deduplicated by content hash)
-        const uint64_t hsh = hash_huff_set(hd);
+        const uint64_t hsh = role == kParent ? 0 : hash_huff_set(hd);
         auto it = set_index_.find(hsh);
-        if (it == set_index_.end()) {
+        if (role == kParent) {
+            im.huff_set = 0;
+        } else if (it == set_index_.end()) {
             auto ci = set_cache_.find(hsh);
             if (ci == set_cache_.end()) {
                 if (set_cache_.size() > 4096)
@@ -383,10 +447,12 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             it = set_index_.emplace(hsh, int(sets.size())).first;
             sets.push_back(&ci->second);
         }
-        im.huff_set = uint32_t(it->second);
+        if (role != kParent)
+            im.huff_set = uint32_t(it->second);
 
-        comp_bytes_ += int64_t(len[i]);
-        {
+        if (role != kChild)
+            comp_bytes_ += int64_t(len[i]);
+        if (role != kParent) {
             // coefficients are counted for the MCU rows actually decoded and, for Y output
             // of a colour stream, for luma only
             int64_t blocks_per_mcu_needed = 0;
@@ -394,12 +460,22 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 blocks_per_mcu_needed += hd.h[c] * hd.v[c];
             n_coefs_ += int64_t(mcu_row_hi - mcu_row_lo) * hd.mcus_x * blocks_per_mcu_needed * 64;
         }
-        out_bytes_ += int64_t(rw * rh * nch);
-        dev_index_[i] = int(imgs_.size());
+        if (role != kChild) {
+            out_bytes_ += int64_t(rw * rh * nch);
+            dev_index_[i] = int(imgs_.size());
+        } else {
+            ++children_ok;
+        }
+        if (role != kParent)
+            gate[0] = gate[1] = gate[2] = uint32_t(imgs_.size());
+        else if (im.ncomp_needed == 1)
+            gate[1] = gate[2] = gate[0];
+        im.multi = role == kParent ? 1 : 0;
+        gates_.insert(gates_.end(), gate, gate + 3);
         in_index_.push_back(i);
+        item_of_dev.push_back(item);
         imgs_.push_back(im);
         host_outs_.push_back(ho);
-        hdrs.push_back(hd);
     }
     algo_bytes_ = comp_bytes_ + 4 * n_coefs_ + out_bytes_;
     const int nd = int(imgs_.size());
@@ -420,6 +496,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     off = align_up(off + 4ull * n_idct, 256);
     const size_t off_color = off;
     off = align_up(off + 4ull * n_color, 256);
+    const size_t off_gate = off;
+    off = align_up(off + 12ull * nd, 256);
     const size_t off_huff = off;
     off = align_up(off + sizeof(HuffSetDev) * sets.size(), 256);
     const size_t off_raw = off;
@@ -494,7 +572,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 if (direct[d])
                     continue;
                 const ImageDev& im = imgs_[d];
-                std::memcpy(up + off_raw + im.raw_off, static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[d].scan_offset, im.raw_len);
+                std::memcpy(up + off_raw + im.raw_off, static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[item_of_dev[d]].scan_offset, im.raw_len);
             }
         };
         const int nthreads = staged_bytes > (size_t(2) << 20) ? std::min(4, std::max(1, int(std::thread::hardware_concurrency()) / 2)) : 1;
@@ -508,8 +586,10 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 th.join();
         }
     }
-    if (nd)
+    if (nd) {
         std::memcpy(up + off_img, imgs_.data(), sizeof(ImageDev) * nd);
+        std::memcpy(up + off_gate, gates_.data(), 12ull * nd);
+    }
     for (size_t si = 0; si < sets.size(); ++si)
         std::memcpy(up + off_huff + si * sizeof(HuffSetDev), sets[si], sizeof(HuffSetDev));
 
@@ -522,7 +602,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             continue;
         const ImageDev& im = imgs_[d];
         if (!cuda_ok(cudaMemcpyAsync(upload_.as<uint8_t>() + off_raw + im.raw_off,
-                         static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[d].scan_offset, im.raw_len, cudaMemcpyHostToDevice, stream),
+                         static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[item_of_dev[d]].scan_offset, im.raw_len, cudaMemcpyHostToDevice, stream),
                 "bitstream upload"))
             return B200JPEG_ERR_CUDA;
     }
@@ -537,6 +617,10 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.dc_cta_img = reinterpret_cast<const uint32_t*>(dv + off_dc);
     bd_.idct_cta_img = reinterpret_cast<const uint32_t*>(dv + off_idct);
     bd_.color_cta_img = reinterpret_cast<const uint32_t*>(dv + off_color);
+    bd_.gate = reinterpret_cast<const uint32_t*>(dv + off_gate);
+    bd_.n_multi = 0;
+    for (const ImageDev& im : imgs_)
+        bd_.n_multi += im.multi;
     bd_.huff = reinterpret_cast<const HuffSetDev*>(dv + off_huff);
     bd_.raw = dv + off_raw;
     bd_.state = reinterpret_cast<ImageState*>(sc + so_state);
@@ -645,10 +729,12 @@ int Decoder::finish_wait(int* status, cudaStream_t stream)
         std::memcpy(states_.data(), state_host_.ptr, sizeof(ImageState) * nd);
         return true;
     };
+    // flags that decide about image d's pixels: its own, or those of the one-component images its planes came from
+    auto flags_of = [&](int d) { return states_[gates_[3 * d]].flags | states_[gates_[3 * d + 1]].flags | states_[gates_[3 * d + 2]].flags; };
     auto count_dirty = [&]() {
         int c = 0;
-        for (const auto& st : states_)
-            c += (st.flags & kFlagDirty) ? 1 : 0;
+        for (int d = 0; d < nd; ++d) // (an image assembled from one-component images only mirrors their flags)
+            c += (!imgs_[d].multi && (states_[d].flags & kFlagDirty)) ? 1 : 0;
         return c;
     };
     int dirty = count_dirty();
@@ -675,7 +761,7 @@ int Decoder::finish_wait(int* status, cudaStream_t stream)
         bool any_host = false;
         for (int d = 0; d < nd; ++d) {
             const HostOut& ho = host_outs_[d];
-            if (!ho.host_ptr || !(states_[d].flags & kFlagRedo))
+            if (!ho.host_ptr || !(flags_of(d) & kFlagRedo))
                 continue;
             any_host = true;
             if (!cuda_ok(cudaMemcpyAsync(ho.host_ptr, bounce_.as<uint8_t>() + ho.bounce_off, ho.bytes, cudaMemcpyDeviceToHost, stream), "output copy"))
@@ -689,7 +775,7 @@ int Decoder::finish_wait(int* status, cudaStream_t stream)
             int st = host_status_[i];
             const int d = dev_index_[i];
             if (st == B200JPEG_OK && d >= 0) {
-                const uint32_t f = states_[d].flags;
+                const uint32_t f = flags_of(d);
                 if (f & kFlagDirty)
                     st = B200JPEG_ERR_UNSUPPORTED;
                 else if (f & (kFlagBadMarker | kFlagBadHuffman | kFlagOverrun | kFlagPhase))

@@ -82,6 +82,7 @@ class Decoder {
     std::vector<int> host_status_;      // per input image, B200JPEG_*
     std::vector<int> dev_index_;        // input index -> device batch index or -1
     std::vector<int> in_index_;         // device batch index -> input index
+    std::vector<uint32_t> gates_;       // three device images per device image whose state flags decide about its pixels
     std::vector<ImageDev> imgs_;        // host copy of descriptors
     std::vector<ImageState> states_;
     struct HostOut {

@@ -1,6 +1,7 @@
 // Host marker walk + Huffman lookup-table construction (see jpeg_stream.h).
 #include "jpeg_stream.h"
 
+#include <algorithm>
 #include <cstring>
 
 namespace b200jpeg {
@@ -152,7 +153,7 @@ StreamStatus parse_stream(const uint8_t* d, size_t n, StreamHeader* hdr)
             if (verdict != kStreamOk)
                 return verdict;
             if (ns != hdr->ncomp)
-                return kStreamUnsupported; // non-interleaved multi-scan baseline
+                return (ns == 1 && hdr->ncomp == 3) ? kStreamMultiScan : kStreamUnsupported; // one scan per component: parse_multiscan
             for (int c = 0; c < ns; ++c) {
                 if (s[1 + 2 * c] != hdr->comp_id[c])
                     return kStreamUnsupported; // scan order differs from frame order
@@ -199,6 +200,166 @@ StreamStatus parse_stream(const uint8_t* d, size_t n, StreamHeader* hdr)
     hdr->mcus_y = (hdr->height + 8 * hdr->vmax - 1) / (8 * hdr->vmax);
     if (hdr->scan_length == 0)
         return kStreamCorrupt;
+    return kStreamOk;
+}
+
+StreamStatus parse_multiscan(const uint8_t* d, size_t n, StreamHeader* frame, StreamHeader* scans)
+{
+    StreamHeader cur; // tables and restart interval as they stand at the current position
+    for (int c = 0; c < 2; ++c)
+        for (int t = 0; t < 4; ++t)
+            cur.huff[c][t].present = false;
+    if (n < 4 || d[0] != 0xFF || d[1] != 0xD8)
+        return kStreamNotJpeg;
+    size_t p = 2;
+    bool have_sof = false, seen[3] = {false, false, false};
+    int n_seen = 0;
+    while (n_seen < 3) {
+        if (p + 2 > n || d[p] != 0xFF)
+            return kStreamCorrupt;
+        while (p < n && d[p] == 0xFF)
+            ++p;
+        if (p >= n)
+            return kStreamCorrupt;
+        const int m = d[p++];
+        if (m == 0xD8 || m == 0x01 || (m >= 0xD0 && m <= 0xD7))
+            continue;
+        if (m == 0xD9 || p + 2 > n)
+            return kStreamCorrupt;
+        const size_t len = be16(d + p);
+        if (len < 2 || p + len > n)
+            return kStreamCorrupt;
+        const uint8_t* s = d + p + 2;
+        const size_t sl = len - 2;
+        if (m == 0xDB) {
+            if (!read_dqt(s, sl, &cur))
+                return kStreamCorrupt;
+        } else if (m == 0xC4) {
+            if (!read_dht(s, sl, &cur))
+                return kStreamCorrupt;
+        } else if (m == 0xDD) {
+            if (sl < 2)
+                return kStreamCorrupt;
+            cur.restart_interval = int(be16(s));
+        } else if (m == 0xE0) {
+            if (sl >= 5 && std::memcmp(s, "JFIF", 5) == 0)
+                cur.has_jfif = true;
+        } else if (m == 0xEE) {
+            if (sl >= 12 && std::memcmp(s, "Adobe", 5) == 0)
+                cur.adobe_transform = s[11];
+        } else if (m == 0xC0 || m == 0xC1) {
+            if (have_sof || sl < 6 + 9 || s[0] != 8 || s[5] != 3)
+                return have_sof ? kStreamCorrupt : kStreamUnsupported;
+            have_sof = true;
+            cur.sof = m;
+            cur.precision = 8;
+            cur.height = int(be16(s + 1));
+            cur.width = int(be16(s + 3));
+            cur.ncomp = 3;
+            if (cur.width == 0 || cur.height == 0)
+                return kStreamUnsupported;
+            for (int c = 0; c < 3; ++c) {
+                cur.comp_id[c] = s[6 + 3 * c];
+                cur.h[c] = s[7 + 3 * c] >> 4;
+                cur.v[c] = s[7 + 3 * c] & 15;
+                cur.tq[c] = s[8 + 3 * c];
+                if (cur.h[c] < 1 || cur.h[c] > 4 || cur.v[c] < 1 || cur.v[c] > 4 || cur.tq[c] > 3)
+                    return kStreamCorrupt;
+            }
+            cur.hmax = std::max(cur.h[0], std::max(cur.h[1], cur.h[2]));
+            cur.vmax = std::max(cur.v[0], std::max(cur.v[1], cur.v[2]));
+        } else if (m >= 0xC2 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC) {
+            return kStreamUnsupported;
+        } else if (m == 0xDA) {
+            if (!have_sof || sl < 1 + 2 + 3)
+                return kStreamCorrupt;
+            if (s[0] != 1)
+                return kStreamUnsupported; // a mix of interleaved and single-component scans
+            int c = -1;
+            for (int k = 0; k < 3; ++k)
+                if (s[1] == cur.comp_id[k])
+                    c = k;
+            if (c < 0)
+                return kStreamCorrupt;
+            if (seen[c])
+                return kStreamUnsupported;
+            const int td = s[2] >> 4, ta = s[2] & 15;
+            if (td > 3 || ta > 3 || !cur.huff[0][td].present || !cur.huff[1][ta].present || !cur.qt_present[cur.tq[c]])
+                return kStreamCorrupt;
+            StreamHeader& sc = scans[c];
+            sc = StreamHeader();
+            for (int cl = 0; cl < 2; ++cl)
+                for (int t = 0; t < 4; ++t)
+                    sc.huff[cl][t].present = false;
+            sc.sof = cur.sof;
+            sc.precision = 8;
+            sc.ncomp = 1;
+            sc.width = (cur.width * cur.h[c] + cur.hmax - 1) / cur.hmax;   // the component's own sample grid (T.81 A.1.1)
+            sc.height = (cur.height * cur.v[c] + cur.vmax - 1) / cur.vmax;
+            sc.comp_id[0] = cur.comp_id[c];
+            sc.h[0] = sc.v[0] = 1;
+            sc.hmax = sc.vmax = 1;
+            sc.blocks_per_mcu = 1;
+            sc.mcus_x = (sc.width + 7) / 8;
+            sc.mcus_y = (sc.height + 7) / 8;
+            sc.tq[0] = 0;
+            std::memcpy(sc.qt[0], cur.qt[cur.tq[c]], sizeof(sc.qt[0]));
+            sc.qt_present[0] = true;
+            sc.td[0] = sc.ta[0] = 0; // the tables in force now, under ids of our own
+            sc.huff[0][0] = cur.huff[0][td];
+            sc.huff[1][0] = cur.huff[1][ta];
+            sc.restart_interval = cur.restart_interval;
+            sc.nscans = 1;
+            sc.scan_offset = p + len;
+            // the entropy-coded segment ends at the first marker that is neither a stuffed FF00, a fill FF nor RSTn
+            size_t q = sc.scan_offset;
+            for (;;) {
+                const void* f = q < n ? std::memchr(d + q, 0xFF, n - q) : nullptr;
+                if (!f) {
+                    q = n;
+                    break;
+                }
+                q = size_t(static_cast<const uint8_t*>(f) - d);
+                if (q + 1 >= n) {
+                    q = n;
+                    break;
+                }
+                const int x = d[q + 1];
+                if (x == 0x00 || (x >= 0xD0 && x <= 0xD7)) {
+                    q += 2;
+                } else if (x == 0xFF) {
+                    q += 1;
+                } else {
+                    break;
+                }
+            }
+            sc.scan_length = std::min(n, q + 2) - sc.scan_offset; // including the marker, which is what stops K0
+            if (q <= sc.scan_offset)
+                return kStreamCorrupt;
+            seen[c] = true;
+            ++n_seen;
+            p = q;
+            continue;
+        }
+        p += len;
+    }
+    *frame = cur;
+    frame->nscans = 3;
+    frame->scan_offset = frame->scan_length = 0;
+    if (frame->adobe_transform == 0)
+        return kStreamUnsupported;
+    if (!frame->has_jfif && frame->adobe_transform < 0 && frame->comp_id[0] == 'R' && frame->comp_id[1] == 'G' && frame->comp_id[2] == 'B')
+        return kStreamUnsupported;
+    frame->blocks_per_mcu = 0;
+    for (int c = 0; c < 3; ++c) {
+        frame->blocks_per_mcu += frame->h[c] * frame->v[c];
+        if (frame->h[c] == 3 || frame->v[c] == 3 || frame->hmax % frame->h[c] || frame->vmax % frame->v[c])
+            return kStreamUnsupported;
+    }
+    if (frame->blocks_per_mcu > kMaxBlocksPerMcu)
+        return kStreamCorrupt;
+    frame->mcus_x = (frame->width + 8 * frame->hmax - 1) / (8 * frame->hmax);
+    frame->mcus_y = (frame->height + 8 * frame->vmax - 1) / (8 * frame->vmax);
     return kStreamOk;
 }
 

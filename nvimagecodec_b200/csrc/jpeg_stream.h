@@ -14,7 +14,7 @@ constexpr int kMaxBlocksPerMcu = 10;
 constexpr int kLutBits = 11;    // first-level Huffman lookup width
 constexpr int kLut2Size = 256;  // second-level entries (16-bit windows of the codes longer than kLutBits)
 
-enum StreamStatus { kStreamOk = 0, kStreamNotJpeg, kStreamUnsupported, kStreamCorrupt };
+enum StreamStatus { kStreamOk = 0, kStreamNotJpeg, kStreamUnsupported, kStreamCorrupt, kStreamMultiScan };
 
 struct HuffSpec {
     uint8_t bits[17]; // bits[l] = number of codes of length l (1..16)
@@ -40,6 +40,13 @@ struct StreamHeader {
 
 // Walks SOI..SOS, fills hdr, and decides whether the CUDA path handles the stream.
 StreamStatus parse_stream(const uint8_t* data, size_t len, StreamHeader* hdr);
+
+// Sequential streams whose three components come in three scans of one component each (T.81 A.2.2, non-interleaved):
+// parse_stream answers kStreamMultiScan for them, and this second walk fills `frame` (geometry of the whole image, no scan)
+// and scans[c] for component c: a self-contained ONE-component stream description -- the component's own size, the
+// quantisation / Huffman tables and the restart interval in force when its scan starts, where its entropy-coded data lies.
+// Each scan then decodes like a grayscale image of the component's size; the colour stage reads the three planes.
+StreamStatus parse_multiscan(const uint8_t* data, size_t len, StreamHeader* frame, StreamHeader* scans /* [3] */);
 
 // Device-side Huffman table image (one per table; a "set" is DC0, DC1, AC0, AC1).
 struct alignas(16) HuffTableDev {

@@ -1634,6 +1634,16 @@ __device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& i
 
 // K4b.  CTA = 32 x 8 threads; a thread owns one unit of 8 pixels x unit_rows rows, aligned in image
 // coordinates so that every plane load is a naturally aligned 4- or 8-byte word.
+// Streams whose components came in three scans: the image proper has no entropy data, its planes were decoded as
+// one-component images of their own (BatchDev::gate).  Their state flags become the image's before K4b looks at them.
+__global__ void gate_flags_kernel(BatchDev bd)
+{
+    const int img = blockIdx.x * blockDim.x + threadIdx.x;
+    if (img >= bd.n_images || !bd.img[img].multi)
+        return;
+    bd.state[img].flags = bd.state[bd.gate[3 * img]].flags | bd.state[bd.gate[3 * img + 1]].flags | bd.state[bd.gate[3 * img + 2]].flags;
+}
+
 __global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev bd, int redo_only)
 {
     const uint32_t cta = blockIdx.x;
@@ -1756,8 +1766,13 @@ int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s)
 {
     if (b.n_color_cta == 0)
         return 0;
+    int launched = 1;
+    if (b.n_multi) {
+        gate_flags_kernel<<<(b.n_images + 127) / 128, 128, 0, s>>>(b);
+        ++launched;
+    }
     color_kernel<<<b.n_color_cta, kColorTx * kColorTy, 0, s>>>(b, redo_only ? 1 : 0);
-    return 1;
+    return launched;
 }
 
 } // namespace b200jpeg

@@ -79,6 +79,8 @@ struct ImageDev {
     uint8_t color_mode;      // K4b specialisation: 0 generic, 1 luma only, 2..5 chroma (hx,vx) = (1,1),(2,1),(1,2),(2,2) replicated, 6..8 = 3..5 with the triangle filter
     uint8_t color_unit_rows; // output rows per K4b thread (the chroma vertical factor on the fast paths)
     uint8_t orient;          // EXIF orientation code applied when storing (0/1 = none; 5..8 transpose)
+    uint8_t multi;           // 1: the components came in three scans and were decoded as one-component images of their own;
+                             //    BatchDev::gate names them (their state flags become this image's before K4b)
 };
 
 struct ImageState {
@@ -114,7 +116,9 @@ struct BatchDev {
     int4* dc_sum;                 // K3b: per chunk (reset seen, DC sums of the three components)
     const uint32_t* idct_cta_img;
     const uint32_t* color_cta_img;
+    const uint32_t* gate;         // three image indices per image, see ImageDev::multi
     int n_tiles, n_seq, n_wseq, n_sub, n_dc_cta, n_idct_cta, n_color_cta;
+    int n_multi;            // images with ImageDev::multi set
     uint32_t* sync_stats;   // optional K1 counters (4 x uint32), may be null
     uint32_t sub_bits;      // subsequence length in bits for this batch
     uint32_t seq_warm;      // warm-up subsequences at the head of every K1 CTA

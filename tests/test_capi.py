@@ -96,3 +96,28 @@ def test_partition_by_bytes_is_balanced_and_complete():
     assert sharding.partition_by_bytes(sizes, 8) == parts  # deterministic
     assert sharding.partition_by_bytes([5, 1, 1], 2) == [[0], [1, 2]]
     assert sharding.partition_by_bytes([], 3) == [[], [], []]
+
+
+def test_probe_accepts_three_scans_of_one_component_each():
+    """Non-interleaved sequential streams (tests/remux.py makes them out of interleaved ones) are accepted; the remuxer
+    itself is pinned against libjpeg-turbo: both files must decode to the same pixels."""
+    PIL = pytest.importorskip("PIL.Image")
+    import io
+    from tests import remux
+    from nvimagecodec_b200 import corpus
+
+    for h, w, samp, rb in [(90, 120, "420", 0), (50, 70, "444", 5), (64, 48, "422", 3), (33, 17, "420", 0), (40, 100, "440", 7)]:
+        d = corpus.encode(corpus.synth(h, w, 7), 90, samp)
+        m = remux.to_three_scans(d, rb, (1, 2, 0) if rb else (0, 1, 2))
+        a = np.asarray(PIL.open(io.BytesIO(d)).convert("RGB"))
+        b = np.asarray(PIL.open(io.BytesIO(m)).convert("RGB"))
+        assert np.array_equal(a, b)
+        info = jpeg_host.probe(m)
+        assert info.supported == 1 and (info.width, info.height, info.num_components) == (w, h, 3)
+    # a mix of an interleaved and a one-component scan is declined
+    d = corpus.encode(corpus.synth(48, 48, 9), 90, "444")
+    m = bytearray(remux.to_three_scans(d))
+    i = m.index(b"\xff\xda")
+    j = m.index(b"\xff\xda", i + 2)
+    m[j + 4] = 2  # second SOS claims two components
+    assert jpeg_host.probe(bytes(m)).supported == 0

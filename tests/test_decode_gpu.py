@@ -450,3 +450,45 @@ def test_fuzzed_entropy_data_never_takes_the_batch_down(decoder_cls, extra):
     for o, r in zip(outs, refs):
         assert np.array_equal(o.cpu().numpy(), r)
     dec.close()
+
+
+def test_three_scans_of_one_component_each(decoder_cls, dec_fancy, dec_plain):
+    """Non-interleaved sequential JPEG (one scan per component, T.81 A.2.2): each scan is decoded as a one-component
+    image of the component's size, the colour stage reads the three planes.  tests/remux.py derives such files from
+    interleaved ones without touching a coefficient, so the reference result is the oracle's decode of the original."""
+    from tests import remux
+    from nvimagecodec_b200 import _lib, corpus
+
+    srcs, origs, fmts, rois = [], [], [], []
+    cases = [(90, 120, "420", 0, (0, 1, 2)), (50, 70, "444", 5, (0, 1, 2)), (64, 48, "422", 3, (2, 0, 1)), (33, 17, "420", 0, (1, 2, 0)),
+             (40, 100, "440", 7, (0, 1, 2)), (48, 64, "411", 0, (0, 1, 2)), (300, 420, "420", 0, (0, 1, 2)), (131, 259, "420", 64, (0, 2, 1))]
+    for k, (h, w, samp, rb, order) in enumerate(cases):
+        d = corpus.encode(corpus.synth(h, w, 50 + k), 88, samp)
+        origs.append(d)
+        srcs.append(remux.to_three_scans(d, rb, order))
+        fmts.append(["I_RGB", "I_Y", "P_RGB", "I_BGR"][k % 4])
+        rois.append(None if k % 3 else (h // 4, w // 5, h - 3, w - 2))
+        if k % 2:  # interleaved neighbours in the same batch
+            origs.append(d)
+            srcs.append(d)
+            fmts.append("I_RGB")
+            rois.append(None)
+    for dec, fancy in ((dec_fancy, True), (dec_plain, False)):
+        outs = dec.decode(srcs, fmts, rois)
+        assert dec.last_status == [_lib.OK] * len(srcs)
+        for d, f, r, o in zip(origs, fmts, rois, outs):
+            assert np.array_equal(o.cpu().numpy(), oracle.decode(d, OFMT[f], fancy=fancy, roi=r))
+    # the re-synchronisation path (forced: no warm-up, no probe) works on the one-component images and redoes the colour stage
+    dec = decoder_cls(0, options=":fancy_upsampling=1 b200_jpeg_decoder:debug_no_warm=1 b200_jpeg_decoder:subseq_bits=512")
+    outs = dec.decode(srcs, fmts, rois)
+    assert dec.last_status == [_lib.OK] * len(srcs) and dec.stat(_lib.STAT_RESYNC_IMAGES) > 0
+    for d, f, r, o in zip(origs, fmts, rois, outs):
+        assert np.array_equal(o.cpu().numpy(), oracle.decode(d, OFMT[f], fancy=True, roi=r))
+    dec.close()
+    # damage in one component's scan is reported for the image, the neighbours are untouched
+    bad = bytearray(srcs[0])
+    j = bad.index(b"\xff\xda", bad.index(b"\xff\xda") + 2)
+    bad[j + 14:j + 30] = bytes(16)
+    outs = dec_fancy.decode([bytes(bad), srcs[1], origs[0]], "I_RGB")
+    assert dec_fancy.last_status[1:] == [_lib.OK, _lib.OK]
+    assert np.array_equal(outs[2].cpu().numpy(), oracle.decode(origs[0], oracle.FMT_I_RGB, True))

@@ -58,11 +58,18 @@ def test_extension_is_picked_up_and_bit_exact(tmp_path, fancy):
         entries.append((data, fmt, roi, "host" if i % 4 == 2 else "device"))
     entries.append((corpus.encode(corpus.synth(1080, 1920, 77), 90, "420"), "I_RGB", None, "device"))
     entries.append((corpus.encode(corpus.synth(90, 60, 78), 90, gray=True), "I_RGB", None, "device"))
+    # one scan per component (non-interleaved): same coefficients as the interleaved original, which is what the oracle decodes
+    from tests import remux
+    orig = {}
+    for k, (h, w, samp, rb) in enumerate([(120, 200, "420", 0), (75, 61, "444", 4), (96, 64, "422", 9)]):
+        d = corpus.encode(corpus.synth(h, w, 560 + k), 90, samp)
+        orig[len(entries)] = d
+        entries.append((remux.to_three_scans(d, rb), ["I_RGB", "P_RGB", "I_Y"][k], (5, 7, h - 9, w - 3) if k == 1 else None, "device"))
     status, raws, log = _run(tmp_path, entries, f":fancy_upsampling={fancy}")
     assert "b200 jpeg decoder registered" in log
-    for (data, fmt, roi, where), st, raw in zip(entries, status, raws):
+    for idx, ((data, fmt, roi, where), st, raw) in enumerate(zip(entries, status, raws)):
         assert st[0] == 1, (st, log[-2000:])  # NVIMGCODEC_PROCESSING_STATUS_SUCCESS
-        ref = oracle.decode(data, OFMT[fmt], fancy=bool(fancy), roi=roi)
+        ref = oracle.decode(orig.get(idx, data), OFMT[fmt], fancy=bool(fancy), roi=roi)
         assert raw.size == ref.size
         assert np.array_equal(raw, ref.reshape(-1))
 
