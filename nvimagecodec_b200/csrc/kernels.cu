@@ -34,7 +34,7 @@ struct ByteMasks {
     uint32_t kept, rst, end;
 };
 
-__device__ __forceinline__ ByteMasks classify16(const uint8_t* __restrict__ raw, uint32_t len, uint32_t i0)
+__device__ __noinline__ ByteMasks classify16_tail(const uint8_t* __restrict__ raw, uint32_t len, uint32_t i0)
 {
     ByteMasks m{0u, 0u, 0u};
     if (i0 >= len)
@@ -60,6 +60,49 @@ __device__ __forceinline__ ByteMasks classify16(const uint8_t* __restrict__ raw,
             m.end |= uint32_t(is_end) << j;
         }
         prv = cur;
+    }
+    return m;
+}
+
+// The same classification four bytes at a time (all but the one chunk of a segment that holds its last byte).
+// flag words carry one bit per byte, in bit 7 of the byte.
+__device__ __forceinline__ uint32_t zero_bytes(uint32_t v) // 0x80 in every byte of v that is 0 (exact, no carries across bytes)
+{
+    const uint32_t t = (v & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;
+    return ~(t | v | 0x7F7F7F7Fu);
+}
+__device__ __forceinline__ uint32_t gather_bit7(uint32_t m) // bit 7 of bytes 0..3 -> bits 0..3
+{
+    return (m * 0x00204081u) >> 28;
+}
+__device__ __forceinline__ ByteMasks classify16(const uint8_t* __restrict__ raw, uint32_t len, uint32_t i0)
+{
+    if (i0 + 16u >= len) // (also i0 >= len)
+        return classify16_tail(raw, len, i0);
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(raw + i0));
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    const uint32_t prv = i0 ? __ldg(raw + i0 - 1) : 0u;
+    const uint32_t after = __ldg(raw + i0 + 16);
+    uint32_t ff[4], zz[4], rs[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        ff[k] = zero_bytes(~w[k]);
+        zz[k] = zero_bytes(w[k]);
+        rs[k] = zero_bytes((w[k] & 0xF8F8F8F8u) ^ 0xD0D0D0D0u);
+    }
+    const uint32_t ff_before = (prv == 0xFFu) ? 0x80000000u : 0u; // flag of the byte before the chunk, in its top byte
+    const uint32_t zz_after = (after == 0u) ? 0x00000080u : 0u;   // flag of the byte after the chunk, in its low byte
+    ByteMasks m{0u, 0u, 0u};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t pf = __funnelshift_l(k ? ff[k - 1] : ff_before, ff[k], 8);  // byte j: was byte j-1 an FF?
+        const uint32_t nz = __funnelshift_r(zz[k], k < 3 ? zz[k + 1] : zz_after, 8); // byte j: is byte j+1 a 00?
+        const uint32_t keep = (ff[k] & nz) | (~ff[k] & ~pf & 0x80808080u);
+        const uint32_t rst = pf & rs[k];
+        const uint32_t end = pf & ~zz[k] & ~ff[k] & ~rs[k];
+        m.kept |= gather_bit7(keep) << (4 * k);
+        m.rst |= gather_bit7(rst) << (4 * k);
+        m.end |= gather_bit7(end) << (4 * k);
     }
     return m;
 }
