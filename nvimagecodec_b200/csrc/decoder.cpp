@@ -413,7 +413,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             const size_t ax0 = size_t(x0) & ~size_t(7), ay0 = size_t(y0) / ur * ur; // units are aligned in image coordinates
             im.color_cta_off = n_color;
             im.n_color_cta_x = uint32_t((size_t(x1) - ax0 + 255) / 256);
-            im.n_color_cta_y = uint32_t((size_t(y1) - ay0 + 8 * ur - 1) / (8 * ur));
+            im.n_color_cta_y = uint32_t((size_t(y1) - ay0 + 8 * ur * kColorUnitsY - 1) / (8 * ur * kColorUnitsY));
             im.color_cta_x_rcp = im.n_color_cta_x > 1 ? uint32_t((uint64_t(1) << 32) / im.n_color_cta_x + 1) : 0u;
             if (role == kChild)
                 im.n_color_cta_x = im.n_color_cta_y = 0; // planes only

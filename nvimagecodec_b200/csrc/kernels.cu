@@ -1701,18 +1701,20 @@ __global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev b
     const int tx = threadIdx.x % kColorTx, ty = threadIdx.x / kColorTx;
     const int urows = im.color_unit_rows;
     const int X0 = (int(im.roi_x0) & ~7) + (int(cx) * kColorTx + tx) * 8;
-    const int Y0 = (int(im.roi_y0) & ~(urows - 1)) + (int(cy) * kColorTy + ty) * urows; // urows is 1 or 2
+    const int Y0 = (int(im.roi_y0) & ~(urows - 1)) + ((int(cy) * kColorTy + ty) * kColorUnitsY) * urows; // urows is 1 or 2; kColorUnitsY units per thread
     if (X0 >= int(im.roi_x1) || Y0 >= int(im.roi_y1))
         return;
     const int order = (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR) ? 1 : ((im.fmt == kFmtIYUV || im.fmt == kFmtPYUV) ? 2 : 0);
 #define B200_COLOR_CASE(mode, HX, VX, FANCY, LUMA)               \
-    case mode:                                                   \
-        if (order == 0)                                          \
-            color_unit<HX, VX, FANCY, LUMA, 0>(bd, im, X0, Y0);  \
-        else if (order == 1)                                     \
-            color_unit<HX, VX, FANCY, LUMA, 1>(bd, im, X0, Y0);  \
-        else                                                     \
-            color_unit<HX, VX, FANCY, LUMA, 2>(bd, im, X0, Y0);  \
+    case mode:                                                                 \
+        for (int u = 0; u < kColorUnitsY && Y0 + u * VX < int(im.roi_y1); ++u) {   \
+            if (order == 0)                                                        \
+                color_unit<HX, VX, FANCY, LUMA, 0>(bd, im, X0, Y0 + u * VX);       \
+            else if (order == 1)                                                   \
+                color_unit<HX, VX, FANCY, LUMA, 1>(bd, im, X0, Y0 + u * VX);       \
+            else                                                                   \
+                color_unit<HX, VX, FANCY, LUMA, 2>(bd, im, X0, Y0 + u * VX);       \
+        }                                                                          \
         break;
     switch (im.color_mode) {
         B200_COLOR_CASE(1, 1, 1, false, true)
@@ -1725,7 +1727,7 @@ __global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev b
         B200_COLOR_CASE(8, 2, 2, true, false)
 #undef B200_COLOR_CASE
     default:
-        for (int r = 0; r < urows; ++r)
+        for (int r = 0; r < urows * kColorUnitsY; ++r)
             for (int i = 0; i < 8; ++i) {
                 const int x = X0 + i, y = Y0 + r;
                 if (x >= int(im.roi_x0) && x < int(im.roi_x1) && y >= int(im.roi_y0) && y < int(im.roi_y1))
