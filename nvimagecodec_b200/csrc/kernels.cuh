@@ -20,7 +20,10 @@ constexpr int kSeqMult = 1;           // K1: subsequences per thread ...
 constexpr int kSeqLogical = kSeqThreads * kSeqMult; // ... i.e. per CTA ("sequence"), of which the
 constexpr int kSeqWarmBits = 8192;    // leading ones only warm up the entry state: this many bits of them (BatchDev::seq_warm),
 constexpr int kSeqWarmMin = 8;        // at least this many subsequences
-constexpr int kColorUnitsY = 2;       // K4b: vertically adjacent units per thread (descriptor reads, index arithmetic and the mode switch amortised)
+#ifndef B200_COLOR_UNITS_Y
+#define B200_COLOR_UNITS_Y 4
+#endif
+constexpr int kColorUnitsY = B200_COLOR_UNITS_Y;       // K4b: vertically adjacent units per thread (descriptor reads, index arithmetic and the mode switch amortised)
 constexpr int kDcThreads = 512;       // K3b: threads per CTA, ...
 constexpr int kDcPer = 8;             //      blocks per thread,
 constexpr int kDcChunk = kDcThreads * kDcPer; // blocks per CTA
