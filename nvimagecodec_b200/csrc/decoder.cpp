@@ -377,7 +377,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             }
         }
         im.idct_cta_off = n_idct;
-        im.n_idct_cta = (idct_blocks + 127) / 128;
+        im.n_idct_cta = (idct_blocks + 128 * kIdctPer - 1) / (128 * kIdctPer);
         n_idct += im.n_idct_cta;
         im.roi_x0 = uint16_t(x0);
         im.roi_y0 = uint16_t(y0);

@@ -1189,23 +1189,36 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
     for (int i = threadIdx.x; i < 3 * 64; i += blockDim.x)
         s_q[i / 64][i % 64] = im.qt[i / 64][i % 64];
     __syncthreads();
-    // block index over the wanted rows of the planes of the needed components, row-major per plane
-    uint32_t idx = (cta - im.idct_cta_off) * blockDim.x + threadIdx.x;
+    // block index over the wanted rows of the planes of the needed components, row-major per plane; a thread takes
+    // kIdctPer blocks, blockDim.x apart (neighbouring threads keep neighbouring blocks: the row stores coalesce)
+    const uint32_t first = (cta - im.idct_cta_off) * (kIdctPer * blockDim.x) + threadIdx.x;
     int c = 0;
-    uint32_t bw = 0, by0 = 0;
-    for (; c < im.ncomp_needed; ++c) {
-        bw = uint32_t(im.mcus_x) * im.h[c];
-        by0 = uint32_t(im.mcu_row_lo) * im.v[c];
-        const uint32_t rows = uint32_t(im.mcu_row_hi - im.mcu_row_lo) * im.v[c];
-        if (idx < bw * rows)
-            break;
-        idx -= bw * rows;
+    uint32_t bw = 0, by_end = 0, by = 0, bx = 0, lh = 0, lv = 0; // component, its width in blocks, end of its wanted rows, position
+    bool locate = true;
+#pragma unroll 1
+    for (int k = 0; k < kIdctPer; ++k) {
+    if (locate) { // from the linear index (first block; later ones only when they cross into the next component)
+        uint32_t idx = first + uint32_t(k) * blockDim.x;
+        for (c = 0; c < im.ncomp_needed; ++c) {
+            bw = uint32_t(im.mcus_x) * im.h[c];
+            const uint32_t rows = uint32_t(im.mcu_row_hi - im.mcu_row_lo) * im.v[c];
+            if (idx < bw * rows) {
+                by = uint32_t(im.mcu_row_lo) * im.v[c];
+                by_end = by + rows;
+                break;
+            }
+            idx -= bw * rows;
+        }
+        if (c >= im.ncomp_needed)
+            return;
+        by += idx / bw;
+        bx = idx % bw;
+        lh = 31u - uint32_t(__clz(int(im.h[c]))); // sampling factors are 1, 2 or 4
+        lv = 31u - uint32_t(__clz(int(im.v[c])));
+        locate = false;
     }
-    if (c >= im.ncomp_needed)
-        return;
-    const uint32_t by = by0 + idx / bw, bx = idx % bw;
-    const uint32_t mx = bx / im.h[c], my = by / im.v[c];
-    const uint32_t bim = im.blk_first[c] + (by - my * im.v[c]) * im.h[c] + (bx - mx * im.h[c]);
+    const uint32_t mx = bx >> lh, my = by >> lv;
+    const uint32_t bim = im.blk_first[c] + ((by - (my << lv)) << lh) + (bx - (mx << lh));
     const int16_t* src = bd.coef + im.coef_off + (size_t(my * im.mcus_x + mx) * im.bpm + bim) * 64;
     // 64 coefficients, zig-zag order
     int32_t zz[64];
@@ -1256,6 +1269,14 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
         pk.y = range_limit(o[4]) | (range_limit(o[5]) << 8) | (range_limit(o[6]) << 16) | (range_limit(o[7]) << 24);
         *reinterpret_cast<uint2*>(dst + size_t(y) * (bw * 8)) = pk;
     }
+    // the next block of this thread lies blockDim.x further on
+    bx += blockDim.x;
+    while (bx >= bw) {
+        bx -= bw;
+        ++by;
+    }
+    locate = by >= by_end;
+    } // blocks of this thread
 }
 
 // ------------------------------------------------------------------------------------------------

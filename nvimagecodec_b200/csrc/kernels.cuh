@@ -20,6 +20,10 @@ constexpr int kSeqMult = 1;           // K1: subsequences per thread ...
 constexpr int kSeqLogical = kSeqThreads * kSeqMult; // ... i.e. per CTA ("sequence"), of which the
 constexpr int kSeqWarmBits = 8192;    // leading ones only warm up the entry state: this many bits of them (BatchDev::seq_warm),
 constexpr int kSeqWarmMin = 8;        // at least this many subsequences
+#ifndef B200_IDCT_PER
+#define B200_IDCT_PER 4
+#endif
+constexpr int kIdctPer = B200_IDCT_PER;        // K4a: blocks per thread (table load, barrier and descriptor reads amortised)
 #ifndef B200_COLOR_UNITS_Y
 #define B200_COLOR_UNITS_Y 4
 #endif
