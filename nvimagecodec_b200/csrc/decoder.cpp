@@ -575,7 +575,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 std::memcpy(up + off_raw + im.raw_off, static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[item_of_dev[d]].scan_offset, im.raw_len);
             }
         };
-        const int nthreads = staged_bytes > (size_t(2) << 20) ? std::min(4, std::max(1, int(std::thread::hardware_concurrency()) / 2)) : 1;
+        const int nthreads = staged_bytes > (size_t(8) << 20) ? std::min(4, std::max(1, int(std::thread::hardware_concurrency()) / 2)) : 1;
         if (nthreads <= 1) {
             stage(0, nd);
         } else {
