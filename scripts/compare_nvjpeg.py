@@ -22,10 +22,6 @@ ours = os.path.join(tmp, "ext_ours"); os.makedirs(ours)
 shutil.copy(os.path.join(ROOT, "nvimagecodec_b200", "lib", "libb200jpeg_ext.so"), ours)
 nvj = os.path.join(ROOT, "oracle", "_ref", "extensions_nvjpeg")
 runs = [("b200_jpeg_decoder", ours, ":fancy_upsampling=1", "any"),
-        ("b200_jpeg_decoder (3 lanes x 24 MB chunks, the earlier default)", ours, ":fancy_upsampling=1 b200_jpeg_decoder:lanes=3 b200_jpeg_decoder:chunk_mb=24", "any"),
-        ("b200 lanes=6 chunk=24", ours, ":fancy_upsampling=1 b200_jpeg_decoder:lanes=6 b200_jpeg_decoder:chunk_mb=24", "any"),
-        ("b200 lanes=6 chunk=16", ours, ":fancy_upsampling=1 b200_jpeg_decoder:lanes=6 b200_jpeg_decoder:chunk_mb=16", "any"),
-        ("b200 lanes=4 chunk=32", ours, ":fancy_upsampling=1 b200_jpeg_decoder:lanes=4 b200_jpeg_decoder:chunk_mb=32 b200_jpeg_decoder:chunk_images=128", "any"),
         ("nvjpeg_cuda_decoder (default: CPU Huffman <= 1 MPix)", nvj, ":fancy_upsampling=1", "hybrid"),
         ("nvjpeg_cuda_decoder hybrid_huffman_threshold=0 (GPU Huffman)", nvj, ":fancy_upsampling=1 nvjpeg_cuda_decoder:hybrid_huffman_threshold=0", "hybrid"),
         ("nvjpeg_hw_decoder", nvj, ":fancy_upsampling=1", "hw")]
