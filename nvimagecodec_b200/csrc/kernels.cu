@@ -344,6 +344,7 @@ struct StreamView {
     uint32_t total_bits;
     uint32_t bpm, blk_comp, blk_tab;
     uint32_t ri_blocks;      // restart_interval * bpm
+    uint32_t pair_off;       // K1: bytes from an AC table of the set in shared memory to its pair table (pair_ac_tables); 0 in K3
     uint32_t total_blocks;
     // K3 counts blocks in the batch's coefficient arena (blk_base = first block of this image; 0 in K1):
     uint32_t blk_base;
@@ -574,7 +575,11 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
             // owns past its range -- keep taking this path until one of the exits above fires
         }
         const bool is_dc = (z == 0u);
-        uint32_t e = lds_u16(taddr + ((win >> (31 - kLutBits)) & ((2u << kLutBits) - 2u)));
+        // K1 has a second first-level table per AC table whose entries cover PAIRS of symbols where two fit the lookup
+        // window (pair_ac_tables; `pair_off` bytes behind the table set, 0 = none).  A pair may be taken only if its second code
+        // word still starts before `limit` and its first one cannot end the block (a run is <= 16).
+        const bool pair = !kWrite && !is_dc && p + uint32_t(kLutBits) <= limit && z <= 47u;
+        uint32_t e = lds_u16(taddr + (pair ? sv.pair_off : 0u) + ((win >> (31 - kLutBits)) & ((2u << kLutBits) - 2u)));
         if ((e & 31u) == 0u) {
             // code longer than the first-level table: second-level lookup on the 16-bit window
             const HuffTableDev* tab = reinterpret_cast<const HuffTableDev*>(reinterpret_cast<const uint8_t*>(hs) + (taddr - s_hs));
@@ -654,6 +659,29 @@ __device__ __forceinline__ void load_huff_set(HuffSetDev* s_hs, const HuffSetDev
         dst[i] = __ldg(src + i);
 }
 
+// K1 only: a second first-level table per AC table whose entries cover TWO symbols wherever the second code word lies
+// entirely inside the lookup window: advance = both symbols' bits, zig-zag advance = both runs (the second may be an EOB).
+// K1 tracks neither values nor magnitude sizes, so a pair is just a longer symbol to it and the loop runs fewer iterations.
+// pair table k sits k * sizeof(HuffTableDev) bytes into `s_pair`, i.e. at one constant offset from AC table k of the set.
+__device__ __forceinline__ void pair_ac_tables(const HuffSetDev* s_hs, uint8_t* s_pair)
+{
+    constexpr uint32_t N = 1u << kLutBits;
+    for (uint32_t idx = threadIdx.x; idx < 2u * N; idx += blockDim.x) {
+        const HuffTableDev& tab = s_hs->t[2 + idx / N];
+        const uint32_t i = idx % N;
+        const uint32_t e1 = tab.lut[i];
+        uint32_t out = e1;
+        const uint32_t tot1 = e1 & 31u, skip1 = e1 >> 9;
+        if (tot1 != 0u && tot1 < uint32_t(kLutBits) && skip1 != 64u) {
+            const uint32_t e2 = tab.lut[(i << tot1) & (N - 1u)]; // the window behind the first symbol, unknown bits as zeros
+            const uint32_t tot2 = e2 & 31u, len2 = tot2 - ((e2 >> 5) & 15u);
+            if (tot2 != 0u && len2 <= uint32_t(kLutBits) - tot1 && tot1 + tot2 <= 31u)
+                out = (tot1 + tot2) | ((skip1 + (e2 >> 9)) << 9);
+        }
+        reinterpret_cast<uint16_t*>(s_pair + (idx / N) * sizeof(HuffTableDev))[i] = uint16_t(out);
+    }
+}
+
 __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageDev& im, const ImageState& st)
 {
     StreamView sv;
@@ -665,6 +693,7 @@ __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageD
     sv.blk_comp = im.blk_comp;
     sv.blk_tab = im.blk_tab;
     sv.ri_blocks = im.restart_interval * im.bpm;
+    sv.pair_off = 0;
     sv.total_blocks = im.total_blocks;
     sv.blk_base = 0;
     sv.write_lo = im.write_blk_lo;
@@ -692,6 +721,7 @@ struct SyncShared {
     uint8_t fresh[kSeqLogical];     // (re)computed by this CTA -> has to be written back
     uint32_t count[2];
 };
+constexpr size_t kSyncPairOffset = (sizeof(HuffSetDev) + sizeof(BlockTable) + sizeof(SyncShared) + 15) / 16 * 16;
 
 __device__ __forceinline__ uint32_t pack_info(const DecodeResult& r) { return uint32_t(r.blk) | (r.restarted ? 0x80000000u : 0u); }
 
@@ -706,6 +736,7 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     HuffSetDev* s_hs = reinterpret_cast<HuffSetDev*>(s_raw);
     BlockTable* s_bt = reinterpret_cast<BlockTable*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev));
     SyncShared& sh = *reinterpret_cast<SyncShared*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev) + sizeof(BlockTable));
+    uint8_t* s_pair = reinterpret_cast<uint8_t*>(s_raw) + kSyncPairOffset;
     const bool fix_mode = (mode & 1) != 0;
     const bool no_warm = (mode & 2) != 0; // test hook: bare guesses, no warm-up threads, no probe
     const uint32_t S = bd.sub_bits;
@@ -721,7 +752,8 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
         return;
     load_huff_set(s_hs, bd.huff + im.huff_set);
     build_block_table(s_bt, s_hs, im);
-    const StreamView sv = make_view(bd, im, st);
+    StreamView sv = make_view(bd, im, st);
+    sv.pair_off = uint32_t(kSyncPairOffset - 2 * sizeof(HuffTableDev)); // AC table k of the set is t[2 + k]
     const int t = threadIdx.x;
     const int k0 = int(first_k) - warm; // subsequence of logical thread 0 (may be negative)
     const bool skip_warm = fix_mode || no_warm;
@@ -732,6 +764,8 @@ __global__ void __launch_bounds__(kSeqThreads) huff_sync_kernel(BatchDev bd, int
     for (int l = t; l < kSeqLogical; l += kSeqThreads)
         sh.fresh[l] = 0;
     __syncthreads(); // tables loaded, counters cleared
+    pair_ac_tables(s_hs, s_pair);
+    __syncthreads();
     DecodeResult res;
     if (fix_mode) {
         for (int l = t; l < kSeqLogical; l += kSeqThreads) {
@@ -1758,7 +1792,7 @@ __global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev b
     }
 }
 
-constexpr size_t kSyncSmem = sizeof(HuffSetDev) + sizeof(BlockTable) + sizeof(SyncShared);
+constexpr size_t kSyncSmem = kSyncPairOffset + 2 * sizeof(HuffTableDev);
 constexpr size_t kWriteSmem = sizeof(HuffSetDev) + sizeof(BlockTable);
 
 } // namespace
