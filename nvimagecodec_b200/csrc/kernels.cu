@@ -18,6 +18,10 @@
 
 #include "b200jpeg.h"
 
+#ifndef B200_K1_CHAIN
+#define B200_K1_CHAIN 3 // symbols per pair-table entry at most (measured 2: 0.714 ms, 3: 0.694 ms on C2)
+#endif
+
 namespace b200jpeg {
 
 namespace {
@@ -575,10 +579,10 @@ __device__ __forceinline__ void decode_subsequence(const StreamView& sv, const H
             // owns past its range -- keep taking this path until one of the exits above fires
         }
         const bool is_dc = (z == 0u);
-        // K1 has a second first-level table per AC table whose entries cover PAIRS of symbols where two fit the lookup
-        // window (pair_ac_tables; `pair_off` bytes behind the table set, 0 = none).  A pair may be taken only if its second code
-        // word still starts before `limit` and its first one cannot end the block (a run is <= 16).
-        const bool pair = !kWrite && !is_dc && p + uint32_t(kLutBits) <= limit && z <= 47u;
+        // K1 has a second first-level table per AC table whose entries cover up to B200_K1_CHAIN symbols where they fit the
+        // lookup window (pair_ac_tables; `pair_off` bytes behind the table set).  Such an entry may be taken only if its last
+        // code word still starts before `limit` and none but the last symbol can end the block (a run is <= 16).
+        const bool pair = !kWrite && !is_dc && p + uint32_t(kLutBits) <= limit && z <= 63u - 16u * (B200_K1_CHAIN - 1);
         uint32_t e = lds_u16(taddr + (pair ? sv.pair_off : 0u) + ((win >> (31 - kLutBits)) & ((2u << kLutBits) - 2u)));
         if ((e & 31u) == 0u) {
             // code longer than the first-level table: second-level lookup on the 16-bit window
@@ -659,8 +663,9 @@ __device__ __forceinline__ void load_huff_set(HuffSetDev* s_hs, const HuffSetDev
         dst[i] = __ldg(src + i);
 }
 
-// K1 only: a second first-level table per AC table whose entries cover TWO symbols wherever the second code word lies
-// entirely inside the lookup window: advance = both symbols' bits, zig-zag advance = both runs (the second may be an EOB).
+// K1 only: a second first-level table per AC table whose entries cover up to B200_K1_CHAIN symbols wherever the code words
+// after the first lie entirely inside the lookup window: advance = all their bits, zig-zag advance = all their runs (the
+// last may be an EOB).
 // K1 tracks neither values nor magnitude sizes, so a pair is just a longer symbol to it and the loop runs fewer iterations.
 // pair table k sits k * sizeof(HuffTableDev) bytes into `s_pair`, i.e. at one constant offset from AC table k of the set.
 __device__ __forceinline__ void pair_ac_tables(const HuffSetDev* s_hs, uint8_t* s_pair)
@@ -671,12 +676,18 @@ __device__ __forceinline__ void pair_ac_tables(const HuffSetDev* s_hs, uint8_t* 
         const uint32_t i = idx % N;
         const uint32_t e1 = tab.lut[i];
         uint32_t out = e1;
-        const uint32_t tot1 = e1 & 31u, skip1 = e1 >> 9;
-        if (tot1 != 0u && tot1 < uint32_t(kLutBits) && skip1 != 64u) {
-            const uint32_t e2 = tab.lut[(i << tot1) & (N - 1u)]; // the window behind the first symbol, unknown bits as zeros
-            const uint32_t tot2 = e2 & 31u, len2 = tot2 - ((e2 >> 5) & 15u);
-            if (tot2 != 0u && len2 <= uint32_t(kLutBits) - tot1 && tot1 + tot2 <= 31u)
-                out = (tot1 + tot2) | ((skip1 + (e2 >> 9)) << 9);
+        uint32_t tot = e1 & 31u, skip = e1 >> 9, last = skip;
+        if (tot != 0u) {
+            for (int n = 1; n < B200_K1_CHAIN && tot < uint32_t(kLutBits) && last != 64u; ++n) {
+                const uint32_t e2 = tab.lut[(i << tot) & (N - 1u)]; // the window behind the symbols so far, unknown bits as zeros
+                const uint32_t tot2 = e2 & 31u, len2 = tot2 - ((e2 >> 5) & 15u);
+                if (tot2 == 0u || len2 > uint32_t(kLutBits) - tot || tot + tot2 > 31u)
+                    break;
+                tot += tot2;
+                last = e2 >> 9;
+                skip += last;
+                out = tot | (skip << 9);
+            }
         }
         reinterpret_cast<uint16_t*>(s_pair + (idx / N) * sizeof(HuffTableDev))[i] = uint16_t(out);
     }
