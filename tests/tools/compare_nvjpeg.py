@@ -1,7 +1,7 @@
 """Same framework, same call (nvimgcodecDecoderDecode on host bitstreams -> device P_RGB/I_RGB buffers), different JPEG
 decoder extension: ours vs the reference's nvjpeg_ext over the toolkit's closed nvJPEG.  Run on the GPU box."""
 import os, subprocess, sys, tempfile, shutil
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import bench
 

@@ -1,5 +1,5 @@
 import sys, time, io
-import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from nvimagecodec_b200 import Decoder, corpus, _lib
 import oracle

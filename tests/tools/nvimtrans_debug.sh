@@ -1,5 +1,5 @@
 #!/bin/bash
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 T=$(mktemp -d); mkdir -p $T/ext $T/in $T/out
 cp nvimagecodec_b200/lib/libb200jpeg_ext.so oracle/_ref/extensions/libnvbmp_ext.so $T/ext/
 python - <<PY

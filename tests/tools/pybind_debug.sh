@@ -1,6 +1,6 @@
 #!/bin/bash
 # Stepwise run of the reference's Python binding (oracle/_ref/python) against this extension, to localise a crash.
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 R=$PWD
 mkdir -p gpurun_out /tmp/extdir
 cp nvimagecodec_b200/lib/libb200jpeg_ext.so /tmp/extdir/

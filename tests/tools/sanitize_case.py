@@ -1,6 +1,6 @@
 """Small mixed batch for compute-sanitizer: every kernel, both upsampling modes, ROI, formats, RST, fix-up path."""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 import oracle
 from nvimagecodec_b200 import Decoder, corpus, _lib
