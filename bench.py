@@ -6,10 +6,17 @@ batch 256 x 1920x1080 baseline 4:2:0 q90 synthetic JPEG -> interleaved RGB, per 
   python bench.py --impl reference --gpus N --steps K ...  # libjpeg-turbo on the host cores
 
 A "step" is one pass of the hot path over one batch.  `value` times the kernels only
-(bitstreams already resident in HBM, outputs left in HBM); `e2e` times the public call with
-HOST buffers: pinned bitstreams in, pinned pixels out, H2D and D2H inside the timed region.
+(bitstreams already resident in HBM, outputs left in HBM).  `e2e` is the same metric through the
+reference-facing plugin call -- nvimgcodecDecoderDecode of the UNMODIFIED nvImageCodec core
+(oracle/_ref/libnvimgcodec.so, built from the reference sources) with this repo's extension picked
+up by priority -- with HOST buffers: pageable bitstreams in, pinned host pixels out, H2D and D2H
+inside the timed region (tests/host/host_driver.cpp drives it; one driver process per rank).
+`e2e_capi` is the same through the plain C ABI (b200jpegDecodeBatch, pinned bitstreams in, pinned
+pixels out); the *_device_out variants leave the pixels in HBM (what a GPU consumer sees).
 Weak scaling: every rank decodes its own 256-image shard of a 256*N batch that is partitioned
-by compressed byte count (nvimagecodec_b200/sharding.py); no data-path collective.
+by compressed byte count (nvimagecodec_b200/sharding.py); no data-path collective.  `strong` is a
+fixed heterogeneous 2048-image batch (C3 distribution + 10 % 1080p) sharded over the N ranks by the
+same rule.  `nvjpeg_ext` is the reference's own CUDA decoder extension through the same framework call.
 """
 import argparse
 import json
@@ -108,6 +115,106 @@ def make_workload(name, n, workers):
     return jp, fmts, rois
 
 
+DRIVER = os.path.join(ROOT, "oracle", "_ref", "host_driver")
+EXT_DIR = os.path.join(ROOT, "nvimagecodec_b200", "lib")
+NVJPEG_EXT_DIR = os.path.join(ROOT, "oracle", "_ref", "extensions_nvjpeg")
+
+
+def reference_pixels(data, fmt="I_RGB", fancy=True, roi=None):
+    """Checker for the parity spot checks (never inside a timed region): the reference's own libjpeg-turbo path when it
+    was built, else the oracle."""
+    try:
+        from oracle import turbo
+
+        if turbo.available():
+            return turbo.decode(data, fmt, fancy, roi)
+    except Exception:
+        pass
+    import oracle
+
+    return oracle.decode(data, {"I_RGB": oracle.FMT_I_RGB, "I_Y": oracle.FMT_Y}[fmt], fancy=fancy, roi=roi)
+
+
+class PluginDriver:
+    """The reference-facing call: tests/host/host_driver.cpp drives nvimgcodecDecoderDecode of the unmodified core
+    (oracle/_ref/libnvimgcodec.so) with an extension directory of our choice, on pageable host bitstreams."""
+
+    def __init__(self, jpegs, device_index):
+        import tempfile
+
+        self.n = len(jpegs)
+        self.dir = tempfile.mkdtemp(prefix="b200bench_")
+        self.device_index = device_index
+        seen = {}
+        self.paths = []
+        for i, d in enumerate(jpegs):
+            if id(d) not in seen:
+                p = os.path.join(self.dir, f"{len(seen)}.jpg")
+                with open(p, "wb") as f:
+                    f.write(d)
+                seen[id(d)] = p
+            self.paths.append(seen[id(d)])
+
+    @staticmethod
+    def available():
+        return os.path.exists(DRIVER) and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libnvimgcodec.so"))
+
+    def run(self, where, options, repeat, ext_dir=EXT_DIR, backend="any", fmts=None, rois=None, crc_every=0, timeout=600):
+        man = os.path.join(self.dir, f"manifest_{where}.txt")
+        with open(man, "w") as f:
+            for i, p in enumerate(self.paths):
+                r = rois[i] if rois and rois[i] else (0, 0, 0, 0)
+                f.write(f"{p} {fmts[i] if fmts else 'I_RGB'} {r[0]} {r[1]} {r[2]} {r[3]} {where}\n")
+        out = os.path.join(self.dir, "out_" + where)
+        os.makedirs(out, exist_ok=True)
+        env = dict(os.environ)
+        env["LD_LIBRARY_PATH"] = os.path.dirname(DRIVER) + ":/usr/local/cuda/lib64:" + env.get("LD_LIBRARY_PATH", "")
+        env["CUDA_VISIBLE_DEVICES"] = str(self.device_index)
+        env["HOST_DRIVER_PINNED"] = "1"
+        env["HOST_DRIVER_CRC"] = str(crc_every if crc_every else 1 << 30)
+        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+            env.pop(k, None)
+        try:
+            r = subprocess.run([DRIVER, ext_dir, man, out, options, str(repeat), backend], capture_output=True, text=True, env=env, timeout=timeout)
+        except Exception as e:
+            return {"error": type(e).__name__}
+        line = [l for l in r.stdout.splitlines() if l.startswith("BENCH")]
+        if r.returncode != 0 or not line:
+            return {"error": "rc=%d %s" % (r.returncode, (r.stdout + r.stderr)[-200:].replace("\n", " | "))}
+        kv = dict(x.split("=") for x in line[0].split()[1:])
+        res = {"images_per_s": float(kv["images_per_s"]), "mpix_per_s": float(kv["mpix_per_s"]), "ms_per_batch": float(kv["ms_per_batch"]),
+               "seconds": float(kv["seconds"]), "ok": int(kv["ok"]), "images": int(kv["images"]), "repeat": int(kv["repeat"])}
+        if crc_every:
+            rows = [l.split() for l in open(os.path.join(out, "status.txt")).read().splitlines()]
+            res["crc"] = {i: int(rows[i][3]) for i in range(0, len(rows), crc_every)}
+        return res
+
+    def close(self):
+        import shutil
+
+        shutil.rmtree(self.dir, ignore_errors=True)
+
+
+def nvjpeg_hw_backend_status():
+    """What NvJpegHwDecoderPlugin::isPlatformSupported() asks (extensions/nvjpeg/hw_decoder.cpp:282-292):
+    nvjpegCreateEx(NVJPEG_BACKEND_HARDWARE).  Returns the nvjpegStatus_t (0 = the hardware engine is usable)."""
+    import ctypes
+
+    try:
+        nv = ctypes.CDLL("libnvjpeg.so.12")
+    except OSError:
+        try:
+            nv = ctypes.CDLL("/usr/local/cuda/lib64/libnvjpeg.so")
+        except OSError:
+            return None
+    h = ctypes.c_void_p()
+    st = nv.nvjpegCreateEx(3, None, None, 0, ctypes.byref(h))
+    if st == 0:
+        nv.nvjpegDestroy(h)
+    return int(st)
+
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
 
@@ -182,7 +289,7 @@ def run_reference(args):
     if rank != 0:
         return 0
     cores = os.cpu_count() or 1
-    n = min(PER_GPU, 128)
+    n = PER_GPU  # the whole batch of the configuration, as the CUDA arm decodes per step
     jpegs = make_corpus(n, cores)
     mpix = n * HEIGHT * WIDTH / 1e6
     for _ in range(args.warmup):
@@ -197,8 +304,9 @@ def run_reference(args):
         "impl": "reference", "metric": "decoded_mpix_per_s", "value": val, "unit": "MPix/s", "images_per_s": n * args.steps / dt,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": f"{n} images per step"},
-        "cpu_baseline": {"value": val, "unit": "MPix/s", "cores": cores, "kind": "reference", "sample": f"{n} of the 256 images per step; {how}"},
+        "config": {"workload": WORKLOAD, "images_per_gpu": n, "upsampling": "fancy",
+                   "note": "host threads are started inside every timed call (oracle/ref_turbo_shim.cpp); at >= 100 ms per step that is noise"},
+        "cpu_baseline": {"value": val, "unit": "MPix/s", "cores": cores, "kind": "reference", "sample": f"all {n} images per step; {how}"},
         "e2e": {"value": val, "unit": "MPix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -214,6 +322,7 @@ def main():
     ap.add_argument("--batch", type=int, default=PER_GPU, help="images per GPU (256 = the configuration the metric is quoted on)")
     ap.add_argument("--fancy", type=int, default=1, help="upsampling mode; 1 = libjpeg_turbo_ext default, what the CPU arm uses")
     ap.add_argument("--options", default="", help="extra decoder options, e.g. ' :subseq_bits=4096' (space-separated) (experiments only)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the strong-scaling, nvjpeg_ext and other-config extras")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS), help="c2 is the configuration the metric is quoted on; "
                     "the others are the remaining BASELINE.json configs, for extra lines only")
     args = ap.parse_args()
@@ -235,6 +344,12 @@ def main():
     if args.workload != "c2" and args.batch == PER_GPU:
         args.batch = {"c3": 256, "c4": 64, "c5": 8192 // max(world, 1)}[args.workload]
     base, base_fmt, base_roi = make_workload(args.workload, args.batch, max(1, cores // world))
+    extra_corpora = {}  # generated here, before CUDA is touched (the generators fork worker processes)
+    if args.workload == "c2" and not args.no_extras:
+        extra_corpora["c5"] = make_workload("c5", 2048, max(1, cores // world))
+        if world == 1:
+            extra_corpora["c3"] = make_workload("c3", 256, cores)
+            extra_corpora["c4"] = make_workload("c4", 32, cores)
     assert torch.cuda.is_available(), "bench.py needs a GPU (the decoder has no CPU path)"
     torch.cuda.set_device(local)
     numa = "unset"
@@ -316,7 +431,22 @@ def main():
     dec.set_profiling(False)
     stages = {k: v / args.steps for k, v in stage_acc.items()}
 
-    # ---- e2e: host pinned bitstreams in, host pinned pixels out, through the public call
+    # ---- e2e_capi: host pinned bitstreams in, host pinned pixels out, through b200jpegDecodeBatch
+    parity_checked = 0
+    check_idx = sorted(set(int(i) for i in __import__("numpy").linspace(0, n_img - 1, 8)))
+
+    def check_pixels(batch, where):
+        import numpy as np
+
+        n_ok = 0
+        for i in check_idx:
+            ref = reference_pixels(jpegs[i], "I_Y" if fmts[i] in ("I_Y", "P_Y") else "I_RGB", bool(args.fancy), rois[i])
+            got = batch.images[i]
+            got = got.numpy() if not got.is_cuda else got.cpu().numpy()
+            assert np.array_equal(got, ref), f"{where}: image {i} differs from the reference decode"
+            n_ok += 1
+        return n_ok
+
     host_batch = dec.make_batch(srcs, fmts, rois, to_host=True)
     for _ in range(args.warmup):
         dec.run(host_batch)
@@ -327,7 +457,9 @@ def main():
     torch.cuda.synchronize()
     t_e2e = time.perf_counter() - t0
     assert all(s == _lib.OK for s in st)
-    # e2e with the pixels left in HBM (what nvImageCodec's GPU backends hand to a GPU consumer)
+    parity_checked += check_pixels(host_batch, "e2e_capi")
+    # the same call with the pixels left in HBM (what nvImageCodec's GPU backends hand to a GPU consumer)
+    dev_batch.storage.zero_()
     for _ in range(2):
         dec.run(dev_batch)
     barrier()
@@ -336,16 +468,71 @@ def main():
         dec.run(dev_batch)
     torch.cuda.synchronize()
     t_e2e_dev = time.perf_counter() - t0
+    parity_checked += check_pixels(dev_batch, "e2e_capi_device_out")
     clocks = sampler.stop()
 
+    # ---- e2e: the plugin call (nvimgcodecDecoderDecode of the unmodified core + this extension), one driver process per rank
+    opts = f":fancy_upsampling={args.fancy}{args.options}"
+    plugin = {"host": None, "device": None}
+    t_plugin = [0.0, 0.0]
+    have_driver = PluginDriver.available()
+    drv = PluginDriver(jpegs, local) if have_driver else None
+    if drv:
+        rep_host = max(3, min(args.steps, int(1.0 / max(t_e2e / args.steps, 1e-3)) + 1))
+        rep_dev = max(5, min(10 * args.steps, int(1.0 / max(t_e2e_dev / args.steps, 1e-4)) + 1))
+        barrier()
+        plugin["host"] = drv.run("host", opts, rep_host, fmts=fmts, rois=rois, crc_every=max(1, n_img // 8))
+        barrier()
+        plugin["device"] = drv.run("device", opts, rep_dev, fmts=fmts, rois=rois, crc_every=max(1, n_img // 8))
+        barrier()
+        import zlib
+
+        import numpy as np
+
+        for leg in ("host", "device"):
+            res = plugin[leg]
+            assert res and "error" not in res and res["ok"] == n_img, f"plugin leg failed: {res}"
+            for i, crc in res["crc"].items():
+                ref = reference_pixels(jpegs[i], "I_Y" if fmts[i] in ("I_Y", "P_Y") else "I_RGB", bool(args.fancy), rois[i])
+                assert zlib.crc32(np.ascontiguousarray(ref).tobytes()) == crc, f"plugin {leg}: image {i} differs from the reference decode"
+                parity_checked += 1
+        t_plugin = [plugin["host"]["seconds"] / plugin["host"]["repeat"], plugin["device"]["seconds"] / plugin["device"]["repeat"]]
+
+    # ---- strong scaling extra: one fixed heterogeneous batch, sharded over the ranks by compressed bytes
+    strong = None
+    if args.workload == "c2" and not args.no_extras:
+        n_strong = 2048
+        sj, sf, sr = extra_corpora["c5"]
+        assert len(sj) == n_strong
+        sizes = [len(j) for j in sj]
+        parts = sharding.partition_by_bytes(sizes, world)
+        mine_s = parts[rank]
+        s_srcs = [torch.frombuffer(bytearray(sj[i]), dtype=torch.uint8).pin_memory() for i in mine_s]
+        s_np = [t.numpy() for t in s_srcs]
+        sb = dec.make_batch(s_np, [sf[i] for i in mine_s], [sr[i] for i in mine_s], to_host=False)
+        s_mpix = sum((r[2] - r[0]) * (r[3] - r[1]) if r else inf.width * inf.height for inf, r in zip(sb.infos, [sr[i] for i in mine_s])) / 1e6
+        for _ in range(2):
+            st = dec.run(sb)
+        assert all(x == _lib.OK for x in st)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            dec.run(sb)
+        torch.cuda.synchronize()
+        t_strong = time.perf_counter() - t0
+        strong = [t_strong * 1e3, s_mpix, float(len(mine_s)), sharding.imbalance(sizes, parts)]
+        del sb, s_srcs
+
     # ---- max over ranks, whole-job aggregate
-    times = torch.tensor([ms_dev, t_e2e * 1e3, t_e2e_dev * 1e3], dtype=torch.float64, device="cuda")
-    total_mpix = torch.tensor([mpix_step, float(n_img)], dtype=torch.float64, device="cuda")
+    times = torch.tensor([ms_dev, t_e2e * 1e3, t_e2e_dev * 1e3, t_plugin[0] * 1e3, t_plugin[1] * 1e3, strong[0] if strong else 0.0],
+                         dtype=torch.float64, device="cuda")
+    total_mpix = torch.tensor([mpix_step, float(n_img), strong[1] if strong else 0.0, strong[2] if strong else 0.0, float(parity_checked)],
+                              dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
         dist.all_reduce(total_mpix, op=dist.ReduceOp.SUM)
-    ms_dev, ms_e2e, ms_e2e_dev = [float(x) for x in times.tolist()]
-    job_mpix, job_imgs = [float(x) for x in total_mpix.tolist()]
+    ms_dev, ms_e2e, ms_e2e_dev, ms_plug_host, ms_plug_dev, ms_strong = [float(x) for x in times.tolist()]
+    job_mpix, job_imgs, strong_mpix, strong_imgs, parity_total = [float(x) for x in total_mpix.tolist()]
 
     if rank == 0:
         peaks = {}
@@ -360,7 +547,7 @@ def main():
         kbytes = {
             "scan(K0)": 2 * comp_bytes, "huff_sync(K1)": comp_bytes, "verify_scan(K2)": 16 * dec.stat(_lib.STAT_NUM_SUBSEQ),
             "huff_write(K3)": comp_bytes + 2 * n_coefs, "dc_scan(K3b)": 8 * (n_coefs // 64), "idct(K4a)": 2 * n_coefs + planes_bytes,
-            "color(K4b)": planes_bytes + out_bytes,
+            "color(K4b)": planes_bytes + out_bytes, "pixels(K4)": 2 * n_coefs + out_bytes,
         }
         top = max(stages, key=stages.get) if stages else None
         stage_list = [{"kernel": k, "ms": round(v, 4), "share": round(v / max(sum(stages.values()), 1e-9), 4),
@@ -377,7 +564,7 @@ def main():
         except Exception:
             pass
         ncu_name = {"scan(K0)": "scan_scatter", "huff_sync(K1)": "huff_sync", "verify_scan(K2)": "verify_scan", "huff_write(K3)": "huff_write", "dc_scan(K3b)": "dc_apply",
-                    "idct(K4a)": "idct", "color(K4b)": "color"}
+                    "idct(K4a)": "idct", "color(K4b)": "color", "pixels(K4)": "pixels"}
         if top:
             ach = kbytes[top] / (stages[top] * 1e-3) / 1e9
             roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
@@ -394,21 +581,36 @@ def main():
             sample_mpix = sum(i.width * i.height for i in dev_batch.infos[:len(sample)]) / 1e6  # the CPU arm decodes whole images to RGB
             cpu = {"value": 2 * sample_mpix / dt, "unit": "MPix/s", "cores": cores, "kind": "reference",
                    "sample": f"{len(sample)} of the batch's images x 2 passes on {cores} threads; {how}"}
+        e2e_capi = {"value": job_mpix * args.steps / (ms_e2e * 1e-3), "unit": "MPix/s", "images_per_s": job_imgs * args.steps / (ms_e2e * 1e-3),
+                    "h2d_bytes_per_step": host_batch.h2d_bytes, "d2h_bytes_per_step": host_batch.d2h_bytes,
+                    "call": "Decoder.run(batch) == b200jpegDecodeBatch, pinned host bitstreams in, pinned host pixels out"}
+        e2e_capi_dev = {"value": job_mpix * args.steps / (ms_e2e_dev * 1e-3), "unit": "MPix/s",
+                        "h2d_bytes_per_step": dev_batch.h2d_bytes, "d2h_bytes_per_step": 16 * n_img,
+                        "note": "same call, pixels left in HBM (what a GPU consumer of nvImageCodec sees); statuses read back"}
+        if drv:
+            e2e = {"value": job_mpix / (ms_plug_host * 1e-3), "unit": "MPix/s", "images_per_s": job_imgs / (ms_plug_host * 1e-3),
+                   "h2d_bytes_per_step": host_batch.h2d_bytes, "d2h_bytes_per_step": host_batch.d2h_bytes,
+                   "call": "nvimgcodecDecoderDecode + future wait + stream sync on the unmodified reference core (oracle/_ref/libnvimgcodec.so) "
+                           "with this extension picked by priority; pageable host bitstreams in, pinned host pixels out; one driver "
+                           "process (tests/host/host_driver.cpp) per rank, wall clock inside the driver, max over ranks",
+                   "steps_timed": plugin["host"]["repeat"]}
+            e2e_dev = {"value": job_mpix / (ms_plug_dev * 1e-3), "unit": "MPix/s", "images_per_s": job_imgs / (ms_plug_dev * 1e-3),
+                       "h2d_bytes_per_step": dev_batch.h2d_bytes, "d2h_bytes_per_step": 0,
+                       "note": "same plugin call, device output buffers", "steps_timed": plugin["device"]["repeat"]}
+        else:
+            e2e = dict(e2e_capi, note="oracle/_ref/host_driver is not built here: the plugin leg falls back to the C ABI")
+            e2e_dev = e2e_capi_dev
         line = {
             "metric": "decoded_mpix_per_s", "value": job_mpix * args.steps / (ms_dev * 1e-3), "unit": "MPix/s",
             "images_per_s": job_imgs * args.steps / (ms_dev * 1e-3),
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": WORKLOADS[args.workload], "images_per_gpu": n_img, "upsampling": "fancy" if args.fancy else "box",
-                       "l2": "working set per step (bitstreams + %.1f GB coefficients + planes + pixels) is larger than the 126 MB L2, no flush needed"
+                       "l2": "working set per step (bitstreams + %.1f GB coefficients + pixels) is larger than the 126 MB L2, no flush needed"
                              % (2 * n_coefs / 1e9),
                        "sharding": "LPT by compressed bytes, one process per GPU, no collective", "host_affinity": numa},
-            "e2e": {"value": job_mpix * args.steps / (ms_e2e * 1e-3), "unit": "MPix/s", "images_per_s": job_imgs * args.steps / (ms_e2e * 1e-3),
-                    "h2d_bytes_per_step": host_batch.h2d_bytes, "d2h_bytes_per_step": host_batch.d2h_bytes,
-                    "call": "Decoder.run(batch) == b200jpegDecodeBatch, pinned host in, pinned host out"},
-            "e2e_device_out": {"value": job_mpix * args.steps / (ms_e2e_dev * 1e-3), "unit": "MPix/s",
-                               "h2d_bytes_per_step": dev_batch.h2d_bytes, "d2h_bytes_per_step": 16 * n_img,
-                               "note": "same call, pixels left in HBM (what a GPU consumer of nvImageCodec sees); statuses read back"},
+            "e2e": e2e, "e2e_device_out": e2e_dev, "e2e_capi": e2e_capi, "e2e_capi_device_out": e2e_capi_dev,
+            "parity_checked": int(parity_total),
             "gpu_launches": int(launches_per_step * args.steps),
             "roofline": roofline,
             "roofline_pipeline": {"bound": "hbm", "achieved": pipe, "peak": peak, "unit": "GB/s", "frac": pipe / peak,
@@ -417,10 +619,68 @@ def main():
             "cpu_baseline": cpu,
             "clocks": clocks,
         }
+        if strong:
+            line["strong"] = {"workload": "2048 mixed images (C3 distribution + 10 % 1080p, 50 % ROI, 30 % gray output), pinned bitstreams in, pixels left in HBM, "
+                                          "b200jpegDecodeBatch per rank", "images": int(strong_imgs), "value": strong_mpix * args.steps / (ms_strong * 1e-3),
+                              "unit": "MPix/s", "images_per_s": strong_imgs * args.steps / (ms_strong * 1e-3), "ms_per_step": ms_strong / args.steps,
+                              "byte_imbalance_max_over_mean": strong[3]}
+        # ---- the reference's own CUDA decoder extension through the same framework call (SURVEY.md 8d "GPU comparison point")
+        if drv and world == 1 and not args.no_extras:
+            nvj = {"nvjpeg_hw_backend_status": nvjpeg_hw_backend_status(),
+                   "note": "nvjpeg_hw_decoder registers only where nvjpegCreateEx(NVJPEG_BACKEND_HARDWARE) returns 0 (hw_decoder.cpp:282-292)"}
+            if os.path.exists(os.path.join(NVJPEG_EXT_DIR, "libnvjpeg_ext.so")):
+                for key, o in (("nvjpeg_cuda_decoder", opts), ("nvjpeg_cuda_decoder_gpu_huffman", opts + " nvjpeg_cuda_decoder:hybrid_huffman_threshold=0")):
+                    r = drv.run("device", o, 3, ext_dir=NVJPEG_EXT_DIR, backend="hybrid", fmts=fmts, rois=rois)
+                    nvj[key] = r if "error" in r else {"mpix_per_s": r["mpix_per_s"], "images_per_s": r["images_per_s"], "ok": r["ok"],
+                                                       "call": "same nvimgcodecDecoderDecode, pageable bitstreams in, device pixels out"}
+                if nvj["nvjpeg_hw_backend_status"] == 0:
+                    r = drv.run("device", opts, 3, ext_dir=NVJPEG_EXT_DIR, backend="hw", fmts=fmts, rois=rois)
+                    nvj["nvjpeg_hw_decoder"] = r if "error" in r else {"mpix_per_s": r["mpix_per_s"], "images_per_s": r["images_per_s"], "ok": r["ok"]}
+            else:
+                nvj["unavailable"] = "oracle/_ref/extensions_nvjpeg/libnvjpeg_ext.so not built"
+            line["nvjpeg_ext"] = nvj
+        # ---- the other BASELINE configs, bounded (N=1 only): kernels-only and C-ABI pixels-in-HBM numbers, statuses checked
+        if world == 1 and args.workload == "c2" and not args.no_extras:
+            others = []
+            for name, nb in (("c3", 256), ("c4", 32), ("c5", 2048)):
+                try:
+                    oj, of, orr = extra_corpora[name]
+                    assert len(oj) == nb
+                    ob = dec.make_batch([torch.frombuffer(bytearray(j), dtype=torch.uint8).pin_memory().numpy() for j in oj], of, orr, to_host=False)
+                    ompix = sum((r[2] - r[0]) * (r[3] - r[1]) if r else inf.width * inf.height for inf, r in zip(ob.infos, orr)) / 1e6
+                    dec.prepare(ob)
+                    for _ in range(3):
+                        dec.execute()
+                    torch.cuda.synchronize()
+                    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    f0.record(stream)
+                    for _ in range(5):
+                        dec.execute()
+                    f1.record(stream)
+                    torch.cuda.synchronize()
+                    ost = dec.finish(ob)
+                    kms = f0.elapsed_time(f1) / 5
+                    for _ in range(2):
+                        dec.run(ob)
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    for _ in range(5):
+                        dec.run(ob)
+                    torch.cuda.synchronize()
+                    pms = (time.perf_counter() - t0) / 5 * 1e3
+                    others.append({"workload": WORKLOADS[name], "images": nb, "all_ok": all(x == _lib.OK for x in ost),
+                                   "kernels_only_mpix_per_s": ompix / (kms * 1e-3), "ms_per_step": kms,
+                                   "e2e_capi_device_out_mpix_per_s": ompix / (pms * 1e-3)})
+                    del ob
+                except Exception as e:  # an extra must not take the headline down
+                    others.append({"workload": WORKLOADS[name], "error": repr(e)[:200]})
+            line["other_configs"] = others
         sys.stdout.flush()
         os.dup2(stdout_fd, 1)
         print(json.dumps(line), flush=True)
         os.dup2(2, 1)
+    if drv:
+        drv.close()
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -94,17 +94,38 @@ B200JPEG_API int b200jpegProbe(const void* data, size_t length, b200jpegStreamIn
  * Tuning knobs (defaults are measured choices, results do not depend on them): subseq_bits=<512|1024|2048|4096>
  * (bits of entropy-coded data per GPU thread; default by batch size), lanes=<1..8> (pipeline lanes, default 6),
  * chunk_mb / chunk_images (pipeline chunk, default 8 MB for pinned bitstreams, 24 MB for pageable ones, 64 images),
- * direct_kb (pinned bitstreams of at least this size are copied without staging, default 128), max_fix_rounds;
+ * direct_kb (pinned bitstreams of at least this size are copied without staging, default 128), host_threads (helper
+ * threads for marker walks and staging copies, default by the CPUs the process may use, at most 8), max_arena_mb (images whose
+ * coefficient + plane arenas would exceed it are refused with B200JPEG_ERR_TOO_LARGE, default 32768), max_fix_rounds;
  * debug_no_warm=1 is a test hook that forces the re-synchronisation path.
  * Replaces nvimgcodecDecoderDesc_t::create / destroy (include/nvimgcodec.h:1466-1482). */
 B200JPEG_API int b200jpegCreate(b200jpegDecoder_t* decoder, int device_id, const char* options);
 B200JPEG_API int b200jpegDestroy(b200jpegDecoder_t decoder);
 
+/* The same with the caller's allocators: every arena the decoder needs (device scratch, pinned staging) is then taken
+ * from and returned to these callbacks, stream-ordered, the size handed back on free -- the contract of
+ * nvimgcodecDeviceAllocator_t / nvimgcodecPinnedAllocator_t (include/nvimgcodec.h:246-318), which the extension
+ * forwards from nvimgcodecExecutionParams_t (include/nvimgcodec.h:1095-1096).  `stream` is a cudaStream_t.  A NULL
+ * struct or a NULL pair falls back to what the reference's own buffers do (src/imgproc/device_buffer.cpp:42-69):
+ * cudaMallocAsync on the batch's stream where the device has memory pools, else cudaMalloc; cudaMallocHost. */
+typedef struct {
+    void* device_ctx;
+    int (*device_malloc)(void* ctx, void** ptr, size_t size, void* stream);
+    int (*device_free)(void* ctx, void* ptr, size_t size, void* stream);
+    void* pinned_ctx;
+    int (*pinned_malloc)(void* ctx, void** ptr, size_t size, void* stream);
+    int (*pinned_free)(void* ctx, void* ptr, size_t size, void* stream);
+} b200jpegAllocators_t;
+B200JPEG_API int b200jpegCreateEx(b200jpegDecoder_t* decoder, int device_id, const char* options, const b200jpegAllocators_t* allocators);
+
 /* Decode a batch: host bitstreams in, pixels out (device or host buffers).
  * Replaces nvimgcodecDecoderDesc_t::decodeBatch (include/nvimgcodec.h:1519-1533) /
  * DecoderImpl::decode (libjpeg_turbo_decoder.cpp:295-420).  status[i] receives
- * B200JPEG_* per image.  cuda_stream is a cudaStream_t.  The call returns after the
- * stream has been synchronised, so statuses reflect entropy-decode errors too. */
+ * B200JPEG_* per image.  cuda_stream is a cudaStream_t.  The call returns once every status is
+ * final, entropy-decode errors included.  When an output is a host buffer that is after its pixels have
+ * arrived; when all outputs are device buffers the last pixel kernels may still be running: they are
+ * ordered on cuda_stream, so work queued on that stream afterwards (or a synchronise on it) sees the
+ * finished pixels, as with any stream-ordered CUDA call.  Option sync_finish=1 waits for the pixels too. */
 B200JPEG_API int b200jpegDecodeBatch(b200jpegDecoder_t decoder, int batch_size, const void* const* data, const size_t* lengths,
     const b200jpegOutput_t* outputs, int* status, void* cuda_stream);
 
@@ -112,7 +133,8 @@ B200JPEG_API int b200jpegDecodeBatch(b200jpegDecoder_t decoder, int batch_size, 
  * part can be timed on its own:
  *   Prepare : host marker walk, staging, async H2D of bitstreams and descriptors
  *   Execute : the CUDA kernels only (everything already in HBM); asynchronous
- *   Finish  : synchronise, run the rare re-synchronisation path, D2H of host outputs, statuses
+ *   Finish  : wait for the statuses (for the pixels too when an output is a host buffer), run the rare
+ *             re-synchronisation path, D2H of host outputs
  * Prepare/Execute/Finish must be called in that order on one decoder; Execute may be
  * repeated on the same prepared batch (it is idempotent). */
 B200JPEG_API int b200jpegPrepareBatch(b200jpegDecoder_t decoder, int batch_size, const void* const* data, const size_t* lengths,
@@ -156,8 +178,11 @@ B200JPEG_API int b200jpegScanSegment(b200jpegDecoder_t decoder, const void* dev_
  * 11 KiB array inside the library (a static __device__ array; every GPU that loads the library
  * holds it until the process exits).  That bounds the segment: length must not exceed
  * B200JPEG_NOALLOC_MAX_SEGMENT_BYTES (8 MiB of byte-stuffed scan data); longer segments are refused
- * with B200JPEG_ERR_TOO_LARGE and nothing is launched.  Inputs and outputs are the caller's, with the
- * same requirements as b200jpegScanSegment, on the device that is current when the call is made.
+ * with B200JPEG_ERR_TOO_LARGE and nothing is launched.  Inputs and outputs are the caller's, on the device
+ * that is current when the call is made, with the same requirements as for b200jpegScanSegment; in
+ * particular dev_raw must be 16-byte aligned and readable for length + 16 bytes (the scan reads whole
+ * 16-byte chunks, the last one past the end of the segment), and dev_out_words must hold
+ * round_up(length, 16) + 32 bytes.
  *
  * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
  * that device current); make that first call before starting any stream capture.  All calls on a

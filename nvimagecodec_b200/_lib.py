@@ -32,13 +32,22 @@ class ScanResult(ctypes.Structure):
                 ("num_subsequences", ctypes.c_uint32), ("flags", ctypes.c_uint32)]
 
 
+ALLOC_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.c_size_t, ctypes.c_void_p)
+FREE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p)
+
+
+class Allocators(ctypes.Structure):
+    _fields_ = [("device_ctx", ctypes.c_void_p), ("device_malloc", ALLOC_FN), ("device_free", FREE_FN),
+                ("pinned_ctx", ctypes.c_void_p), ("pinned_malloc", ALLOC_FN), ("pinned_free", FREE_FN)]
+
+
 class Output(ctypes.Structure):
     _fields_ = [("buffer", ctypes.c_void_p), ("format", ctypes.c_int), ("buffer_is_host", ctypes.c_int),
                 ("row_stride", ctypes.c_size_t), ("roi_x0", ctypes.c_int), ("roi_y0", ctypes.c_int),
                 ("roi_x1", ctypes.c_int), ("roi_y1", ctypes.c_int), ("orientation", ctypes.c_int)]
 
 
-EXPORTS = ["b200jpegProbe", "b200jpegCreate", "b200jpegDestroy", "b200jpegDecodeBatch", "b200jpegPrepareBatch",
+EXPORTS = ["b200jpegProbe", "b200jpegCreate", "b200jpegCreateEx", "b200jpegDestroy", "b200jpegDecodeBatch", "b200jpegPrepareBatch",
            "b200jpegExecuteBatch", "b200jpegFinishBatch", "b200jpegGetStat", "b200jpegSetProfiling", "b200jpegGetStageTimes",
            "b200jpegDebugCopyCoefficients", "b200jpegGetLastError", "b200jpegVersion", "b200jpegScanSegment",
            "b200jpegScanSegmentNoAlloc", "b200jpegMultiCreate", "b200jpegMultiDestroy", "b200jpegMultiPlan", "b200jpegMultiDecodeBatch"]
@@ -60,6 +69,8 @@ def load():
     L.b200jpegProbe.restype = ci
     L.b200jpegCreate.argtypes = [ctypes.POINTER(vp), ci, ctypes.c_char_p]
     L.b200jpegCreate.restype = ci
+    L.b200jpegCreateEx.argtypes = [ctypes.POINTER(vp), ci, ctypes.c_char_p, ctypes.POINTER(Allocators)]
+    L.b200jpegCreateEx.restype = ci
     L.b200jpegDestroy.argtypes = [vp]
     L.b200jpegDestroy.restype = ci
     batch = [vp, ci, ctypes.POINTER(vp), ctypes.POINTER(sz), ctypes.POINTER(Output)]

@@ -73,7 +73,7 @@ int b200jpegProbe(const void* data, size_t length, b200jpegStreamInfo_t* info)
     return info->reason;
 }
 
-int b200jpegCreate(b200jpegDecoder_t* decoder, int device_id, const char* options)
+int b200jpegCreateEx(b200jpegDecoder_t* decoder, int device_id, const char* options, const b200jpegAllocators_t* allocators)
 {
     if (!decoder)
         return B200JPEG_ERR_ARG;
@@ -90,21 +90,38 @@ int b200jpegCreate(b200jpegDecoder_t* decoder, int device_id, const char* option
     }
     if (device_id >= count)
         return B200JPEG_ERR_ARG;
+    b200jpeg::Services sv;
+    if (allocators) {
+        if (allocators->device_malloc && allocators->device_free) {
+            sv.device_ctx = allocators->device_ctx;
+            sv.device_malloc = reinterpret_cast<int (*)(void*, void**, size_t, cudaStream_t)>(allocators->device_malloc);
+            sv.device_free = reinterpret_cast<int (*)(void*, void*, size_t, cudaStream_t)>(allocators->device_free);
+        }
+        if (allocators->pinned_malloc && allocators->pinned_free) {
+            sv.pinned_ctx = allocators->pinned_ctx;
+            sv.pinned_malloc = reinterpret_cast<int (*)(void*, void**, size_t, cudaStream_t)>(allocators->pinned_malloc);
+            sv.pinned_free = reinterpret_cast<int (*)(void*, void*, size_t, cudaStream_t)>(allocators->pinned_free);
+        }
+    }
     auto* h = new (std::nothrow) b200jpegDecoder_st;
     if (!h)
         return B200JPEG_ERR_ARG;
-    {
+    try {
         const b200jpeg::Options opt = b200jpeg::parse_options(options, kDecoderId);
-        h->pipe = new (std::nothrow) Pipeline(device_id, opt, opt.lanes);
-    }
-    if (!h->pipe) {
+        h->pipe = new Pipeline(device_id, opt, opt.lanes, sv);
+    } catch (...) {
         delete h;
-        return B200JPEG_ERR_ARG;
+        return B200JPEG_ERR_STATE;
     }
     h->impl = &h->pipe->lane0();
     h->last_was_pipeline = false;
     *decoder = h;
     return B200JPEG_OK;
+}
+
+int b200jpegCreate(b200jpegDecoder_t* decoder, int device_id, const char* options)
+{
+    return b200jpegCreateEx(decoder, device_id, options, nullptr);
 }
 
 int b200jpegDestroy(b200jpegDecoder_t decoder)
@@ -203,7 +220,7 @@ int b200jpegMultiCreate(b200jpegMultiDecoder_t* multi, const int* device_ids, in
         if (device_ids[i] < 0 || device_ids[i] >= count)
             return B200JPEG_ERR_ARG;
         m->devices.push_back(device_ids[i]);
-        m->pipes.push_back(std::make_unique<Pipeline>(device_ids[i], opt));
+        m->pipes.push_back(std::make_unique<Pipeline>(device_ids[i], opt, opt.lanes));
         cudaStream_t s = nullptr;
         if (cudaSetDevice(device_ids[i]) != cudaSuccess || cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess)
             return B200JPEG_ERR_CUDA;

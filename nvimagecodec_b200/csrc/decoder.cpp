@@ -2,9 +2,15 @@
 // pinned staging arena, ONE host->device copy, a fixed kernel sequence, one status read-back.
 #include "decoder.h"
 
+#include <nvtx3/nvtx3.hpp>
+#include <sched.h>
+
 #include <algorithm>
+#include <atomic>
+#include <condition_variable>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <thread>
 
 namespace b200jpeg {
@@ -14,43 +20,88 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 const char* kStageNames[] = {"scan(K0)", "huff_sync(K1)", "verify_scan(K2)", "huff_write(K3)", "dc_scan(K3b)", "idct(K4a)", "color(K4b)"};
 } // namespace
 
-bool DeviceBuffer::ensure(size_t bytes, size_t* total)
+// ---- memory: the host's allocators when it supplied some, else stream-ordered allocation (cudaMallocAsync) where the
+// device has memory pools, else cudaMalloc -- the order src/imgproc/device_buffer.cpp:42-69 uses.
+namespace {
+bool device_has_pools()
 {
-    if (bytes <= cap)
-        return true;
+    static int cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+        return false;
+    if (cached[dev] == 0) {
+        int v = 0;
+        cudaDeviceGetAttribute(&v, cudaDevAttrMemoryPoolsSupported, dev);
+        cudaGetLastError();
+        cached[dev] = v ? 2 : 1;
+    }
+    return cached[dev] == 2;
+}
+void device_block_free(const Services& sv, void* ptr, size_t cap, cudaStream_t s, bool teardown)
+{
+    if (!ptr)
+        return;
+    if (sv.device_malloc && sv.device_free)
+        sv.device_free(sv.device_ctx, ptr, cap, s);
+    else if (!teardown && device_has_pools())
+        cudaFreeAsync(ptr, s);
+    else
+        cudaFree(ptr); // also valid for stream-ordered allocations; synchronises, which is what teardown wants
+}
+} // namespace
+
+bool DeviceBuffer::ensure(size_t bytes, size_t* total, const Services& sv, cudaStream_t s)
+{
+    if (bytes <= cap) {
+        // an outlier batch must not pin HBM for good: after a run of batches that need less than a quarter of a
+        // large block it is given back and re-allocated at the size in use
+        idle = (cap > (size_t(256) << 20) && bytes < cap / 4) ? idle + 1 : 0;
+        if (idle < 16)
+            return true;
+    }
     if (ptr) {
-        cudaFree(ptr);
+        device_block_free(sv, ptr, cap, s, false);
         *total -= cap;
         ptr = nullptr;
         cap = 0;
     }
+    idle = 0;
     const size_t want = align_up(bytes + bytes / 8, size_t(2) << 20);
-    if (cudaMalloc(&ptr, want) != cudaSuccess) {
+    bool ok;
+    if (sv.device_malloc && sv.device_free)
+        ok = sv.device_malloc(sv.device_ctx, &ptr, want, s) == 0 && ptr;
+    else if (device_has_pools())
+        ok = cudaMallocAsync(&ptr, want, s) == cudaSuccess;
+    else
+        ok = cudaMalloc(&ptr, want) == cudaSuccess;
+    if (!ok) {
         ptr = nullptr;
         cudaGetLastError();
         return false;
     }
     cap = want;
+    stream = s;
     *total += cap;
     return true;
 }
-void DeviceBuffer::release()
+void DeviceBuffer::release(const Services& sv)
 {
-    if (ptr)
-        cudaFree(ptr);
+    device_block_free(sv, ptr, cap, nullptr, true);
     ptr = nullptr;
     cap = 0;
 }
-bool PinnedBuffer::ensure(size_t bytes)
+bool PinnedBuffer::ensure(size_t bytes, const Services& sv, cudaStream_t s)
 {
     if (bytes <= cap)
         return true;
-    if (ptr)
-        cudaFreeHost(ptr);
-    ptr = nullptr;
-    cap = 0;
+    release(sv);
     const size_t want = align_up(bytes + bytes / 8, size_t(2) << 20);
-    if (cudaMallocHost(&ptr, want) != cudaSuccess) {
+    bool ok;
+    if (sv.pinned_malloc && sv.pinned_free)
+        ok = sv.pinned_malloc(sv.pinned_ctx, &ptr, want, s) == 0 && ptr;
+    else
+        ok = cudaMallocHost(&ptr, want) == cudaSuccess;
+    if (!ok) {
         ptr = nullptr;
         cudaGetLastError();
         return false;
@@ -58,12 +109,91 @@ bool PinnedBuffer::ensure(size_t bytes)
     cap = want;
     return true;
 }
-void PinnedBuffer::release()
+void PinnedBuffer::release(const Services& sv)
 {
-    if (ptr)
-        cudaFreeHost(ptr);
+    if (ptr) {
+        if (sv.pinned_malloc && sv.pinned_free)
+            sv.pinned_free(sv.pinned_ctx, ptr, cap, nullptr);
+        else
+            cudaFreeHost(ptr);
+    }
     ptr = nullptr;
     cap = 0;
+}
+
+// ---- helper threads
+struct HostPool::Impl {
+    std::mutex mu;
+    std::condition_variable cv_work, cv_done;
+    void (*fn)(int, void*) = nullptr;
+    void* arg = nullptr;
+    int n = 0;
+    std::atomic<int> next{0};
+    int pending = 0;      // helpers still inside the current job
+    uint64_t job = 0;
+    bool stop = false;
+};
+
+HostPool::HostPool(int n_threads)
+    : impl_(new Impl)
+{
+    for (int t = 0; t < n_threads; ++t)
+        threads_.emplace_back([this]() {
+            Impl& m = *impl_;
+            uint64_t seen = 0;
+            for (;;) {
+                std::unique_lock<std::mutex> lk(m.mu);
+                m.cv_work.wait(lk, [&] { return m.stop || m.job != seen; });
+                if (m.stop)
+                    return;
+                seen = m.job;
+                auto fn = m.fn;
+                void* arg = m.arg;
+                const int n = m.n;
+                lk.unlock();
+                for (int i; (i = m.next.fetch_add(1)) < n;)
+                    fn(i, arg);
+                lk.lock();
+                if (--m.pending == 0)
+                    m.cv_done.notify_one();
+            }
+        });
+}
+
+HostPool::~HostPool()
+{
+    {
+        std::lock_guard<std::mutex> lk(impl_->mu);
+        impl_->stop = true;
+    }
+    impl_->cv_work.notify_all();
+    for (auto& t : threads_)
+        t.join();
+    delete impl_;
+}
+
+void HostPool::run(int n, void (*fn)(int, void*), void* arg)
+{
+    Impl& m = *impl_;
+    if (n <= 1 || threads_.empty()) {
+        for (int i = 0; i < n; ++i)
+            fn(i, arg);
+        return;
+    }
+    {
+        std::lock_guard<std::mutex> lk(m.mu);
+        m.fn = fn;
+        m.arg = arg;
+        m.n = n;
+        m.next.store(0);
+        m.pending = int(threads_.size());
+        ++m.job;
+    }
+    m.cv_work.notify_all();
+    for (int i; (i = m.next.fetch_add(1)) < n;)
+        fn(i, arg);
+    std::unique_lock<std::mutex> lk(m.mu);
+    m.cv_done.wait(lk, [&] { return m.pending == 0; });
 }
 
 // "<decoder_id>:<name>=<value>" tokens separated by spaces; an empty id addresses every decoder
@@ -108,6 +238,12 @@ Options parse_options(const char* options, const char* decoder_id)
             o.lanes = std::min(8, std::max(1, std::atoi(value.c_str())));
         else if (name == "chunk_images")
             o.chunk_images = std::max(1, std::atoi(value.c_str()));
+        else if (name == "sync_finish")
+            o.sync_finish = std::atoi(value.c_str()) != 0;
+        else if (name == "host_threads")
+            o.host_threads = std::min(64, std::max(1, std::atoi(value.c_str())));
+        else if (name == "max_arena_mb")
+            o.max_arena_mb = std::max(1, std::atoi(value.c_str()));
         else if (name == "subseq_bits") {
             const int v = std::atoi(value.c_str());
             if (v == 512 || v == 1024 || v == 2048 || v == 4096)
@@ -118,28 +254,31 @@ Options parse_options(const char* options, const char* decoder_id)
     return o;
 }
 
-Decoder::Decoder(int device_id, const Options& opt)
+Decoder::Decoder(int device_id, const Options& opt, const Services& sv, HostPool* pool)
     : device_(device_id)
     , opt_(opt)
+    , sv_(sv)
+    , pool_(pool)
 {
 }
 
 Decoder::~Decoder()
 {
     cudaSetDevice(device_);
+    cudaDeviceSynchronize(); // pixel kernels of the last batch may still be running on a stream we no longer know to be alive
     if (ev_valid_)
         for (auto& e : ev_)
             cudaEventDestroy(e);
-    upload_.release();
-    scratch_.release();
-    cmp_.release();
-    coef_.release();
-    planes_.release();
-    bounce_.release();
-    scan_scratch_.release();
-    scan_host_.release();
-    upload_host_.release();
-    state_host_.release();
+    if (entropy_event_)
+        cudaEventDestroy(entropy_event_);
+    if (done_event_)
+        cudaEventDestroy(done_event_);
+    if (side_stream_)
+        cudaStreamDestroy(side_stream_);
+    for (DeviceBuffer* b : {&upload_, &scratch_, &cmp_, &coef_, &planes_, &bounce_, &scan_scratch_})
+        b->release(sv_);
+    for (PinnedBuffer* b : {&scan_host_, &upload_host_, &state_host_})
+        b->release(sv_);
 }
 
 int Decoder::fail(int code, const std::string& msg)
@@ -162,12 +301,50 @@ void Decoder::mark(int stage, cudaStream_t s)
         cudaEventRecord(ev_[stage], s);
 }
 
-int Decoder::prepare(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, cudaStream_t stream)
+void Decoder::parallel_for(int n, void (*fn)(int, void*), void* arg)
+{
+    if (sv_.parallel_for)
+        sv_.parallel_for(sv_.par_ctx, n, fn, arg);
+    else if (pool_)
+        pool_->run(n, fn, arg);
+    else
+        for (int i = 0; i < n; ++i)
+            fn(i, arg);
+}
+
+// The marker walk of one input (both walks for a stream that comes in three scans).
+void parse_input(const void* data, size_t len, ParsedInput* out)
+{
+    out->scans.reset();
+    out->multi_status = kStreamOk;
+    out->status = data ? parse_stream(static_cast<const uint8_t*>(data), len, &out->frame) : kStreamNotJpeg;
+    if (out->status == kStreamMultiScan) {
+        out->scans.reset(new StreamHeader[3]);
+        out->multi_status = parse_multiscan(static_cast<const uint8_t*>(data), len, &out->frame, out->scans.get());
+    }
+}
+
+int Decoder::prepare(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, cudaStream_t stream,
+    const ParsedInput* const* parsed, int sources_pinned)
 {
     if (n < 0 || (n > 0 && (!data || !len || !outs)))
         return fail(B200JPEG_ERR_ARG, "null argument");
     if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
         return B200JPEG_ERR_CUDA;
+    // The arenas and the pinned staging block are reused.  A batch that was never waited for may still be uploading out
+    // of the staging block; pixel kernels of the last batch may still be running on another stream.
+    if (inflight_ && !cuda_ok(cudaStreamSynchronize(last_stream_), "synchronize"))
+        return B200JPEG_ERR_CUDA;
+    inflight_ = false;
+    if (have_done_ && last_stream_ != stream)
+        cudaStreamWaitEvent(stream, done_event_, 0);
+    if (!entropy_event_) {
+        if (!cuda_ok(cudaEventCreateWithFlags(&entropy_event_, cudaEventDisableTiming), "event") ||
+            !cuda_ok(cudaEventCreateWithFlags(&done_event_, cudaEventDisableTiming), "event") ||
+            !cuda_ok(cudaStreamCreateWithFlags(&side_stream_, cudaStreamNonBlocking), "stream"))
+            return B200JPEG_ERR_CUDA;
+    }
+    nvtx3::scoped_range nvtx_prepare{"b200jpeg prepare (marker walk, layout, staging, H2D)"};
     prepared_ = executed_ = false;
     n_in_ = n;
     host_status_.assign(n, B200JPEG_OK);
@@ -177,8 +354,11 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     imgs_.clear();
     host_outs_.clear();
     set_index_.clear();
+    any_host_out_ = false;
+    if (set_cache_.size() > kSetCacheMax) // never while a batch is being built: `sets` points into the cache
+        set_cache_.clear();
     std::vector<const HuffSetDev*> sets;
-    std::vector<StreamHeader> hdrs;
+    std::vector<const StreamHeader*> hdrs;
     hdrs.reserve(n);
     std::vector<size_t> item_of_dev; // device image -> its entry in hdrs
 
@@ -208,6 +388,28 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     uint32_t n_tiles = 0, n_sub = 0, n_seq = 0, n_wseq = 0, n_bnd = 0, n_dc = 0, n_idct = 0, n_color = 0;
     comp_bytes_ = n_coefs_ = out_bytes_ = 0;
 
+    // Marker walks: one per input the caller has not walked already, spread over the helper threads when there are many.
+    parsed_own_.resize(size_t(n));
+    {
+        nvtx3::scoped_range nvtx_walk{"b200jpeg marker walk"};
+        struct Ctx {
+            const void* const* data;
+            const size_t* len;
+            const ParsedInput* const* given;
+            ParsedInput* own;
+        } ctx{data, len, parsed, parsed_own_.data()};
+        auto walk = [](int i, void* a) {
+            Ctx& c = *static_cast<Ctx*>(a);
+            if (!(c.given && c.given[i]))
+                parse_input(c.data[i], c.len[i], &c.own[i]);
+        };
+        if (n >= 16)
+            parallel_for(n, walk, &ctx);
+        else
+            for (int i = 0; i < n; ++i)
+                walk(i, &ctx);
+    }
+
     // Work list: one entry per device image.  A stream whose three components come in three scans becomes up to three
     // one-component images (kChild; each decodes like a grayscale image of the component's size) plus the image itself
     // (kParent: no entropy data of its own, its colour stage reads the children's planes).
@@ -224,35 +426,35 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     std::memset(&child_out, 0, sizeof(child_out));
     child_out.buffer = &child_out; // never written: a child has no colour stage
     child_out.format = B200JPEG_FMT_Y;
+    std::vector<StreamHeader> parent_frames; // frames of multi-scan streams with restart_interval cleared (the parent has no scan)
+    parent_frames.reserve(n);
     for (int i = 0; i < n; ++i) {
-        StreamHeader hd;
-        const StreamStatus ss = data[i] ? parse_stream(static_cast<const uint8_t*>(data[i]), len[i], &hd) : kStreamNotJpeg;
-        if (ss == kStreamOk) {
-            hdrs.push_back(hd);
+        const ParsedInput& pi = (parsed && parsed[i]) ? *parsed[i] : parsed_own_[size_t(i)];
+        if (pi.status == kStreamOk) {
+            hdrs.push_back(&pi.frame);
             items.push_back({i, kNormal});
-        } else if (ss == kStreamMultiScan) {
-            StreamHeader frame, sc[3];
-            const StreamStatus ms = parse_multiscan(static_cast<const uint8_t*>(data[i]), len[i], &frame, sc);
-            if (ms != kStreamOk) {
-                host_status_[i] = status_of(ms);
+        } else if (pi.status == kStreamMultiScan) {
+            if (pi.multi_status != kStreamOk || !pi.scans) {
+                host_status_[i] = status_of(pi.multi_status);
                 continue;
             }
             const int n_child = outs[i].format == B200JPEG_FMT_Y ? 1 : 3; // Y output consumes luma only
             for (int c = 0; c < n_child; ++c) {
-                hdrs.push_back(sc[c]);
+                hdrs.push_back(&pi.scans[c]);
                 items.push_back({i, kChild});
             }
-            frame.restart_interval = 0; // the parent has no scan of its own
-            hdrs.push_back(frame);
+            parent_frames.push_back(pi.frame);
+            parent_frames.back().restart_interval = 0;
+            hdrs.push_back(&parent_frames.back());
             items.push_back({i, kParent});
         } else {
-            host_status_[i] = status_of(ss);
+            host_status_[i] = status_of(pi.status);
         }
     }
     int children_ok = 0; // children of the multi-scan stream under way that made it into the batch
     for (size_t item = 0; item < items.size(); ++item) {
         const int i = items[item].i, role = items[item].role;
-        const StreamHeader& hd = hdrs[item];
+        const StreamHeader& hd = *hdrs[item];
         if (role == kChild && (item == 0 || items[item - 1].role != kChild || items[item - 1].i != i))
             children_ok = 0;
         const b200jpegOutput_t& o = role == kChild ? child_out : outs[i];
@@ -291,6 +493,22 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         if (hd.scan_length >= (size_t(1) << 28)) { // bit positions (and the bit after the last subsequence) must fit 32 bits
             host_status_[i] = B200JPEG_ERR_TOO_LARGE;
             continue;
+        }
+        if (role != kParent) {
+            // The arenas are sized from the frame header, which costs an attacker nothing to inflate.  Every coded block
+            // takes at least two bits (a DC code and an end-of-block code), so a scan shorter than that cannot hold the
+            // blocks the header claims: corrupt, before anything is allocated.  What remains is bounded per image
+            // (max_arena_mb) and by the 32-bit block / group indices of the kernels.
+            const uint64_t blocks = uint64_t(hd.mcus_x) * uint64_t(hd.mcus_y) * uint64_t(hd.blocks_per_mcu);
+            if (uint64_t(hd.scan_length) * 8 < 2 * blocks) {
+                host_status_[i] = B200JPEG_ERR_CORRUPT;
+                continue;
+            }
+            const uint64_t arena = blocks * 128 + blocks * 64; // coefficients + planes, upper bound
+            if (arena > (uint64_t(opt_.max_arena_mb) << 20) || coef_elems / 64 + blocks >= (uint64_t(1) << 28)) {
+                host_status_[i] = B200JPEG_ERR_TOO_LARGE;
+                continue;
+            }
         }
         ImageDev im;
         std::memset(&im, 0, sizeof(im));
@@ -419,10 +637,11 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 im.n_color_cta_x = im.n_color_cta_y = 0; // planes only
         }
         n_color += im.n_color_cta_x * im.n_color_cta_y;
-        HostOut ho{nullptr, 0, obytes};
+        HostOut ho{nullptr, 0, obytes, stride, tight, (planar ? 3 : 1) * out_h};
         if (role == kChild) {
             im.out = nullptr;
         } else if (o.buffer_is_host) {
+            any_host_out_ = true;
             ho.host_ptr = o.buffer;
             ho.bounce_off = bounce_bytes;
             bounce_bytes += align_up(obytes, 256);
@@ -430,25 +649,27 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         } else {
             im.out = static_cast<uint8_t*>(o.buffer);
         }
-        // huffman set (deduplicated by content hash)
-        const uint64_t hsh = role == kParent ? 0 : hash_huff_set(hd);
-        auto it = set_index_.find(hsh);
+        // huffman set: deduplicated by content (the canonical bytes of the table specs are the key, so two streams share
+        // device tables only when their specs are equal).  Cache nodes stay where they are for the whole batch: eviction
+        // happens at the top of prepare() only.
         if (role == kParent) {
             im.huff_set = 0;
-        } else if (it == set_index_.end()) {
-            auto ci = set_cache_.find(hsh);
+        } else {
+            huff_set_key(hd, &set_key_);
+            auto ci = set_cache_.find(set_key_);
             if (ci == set_cache_.end()) {
-                if (set_cache_.size() > 4096)
-                    set_cache_.clear();
                 HuffSetDev hs;
                 build_huff_set(hd, &hs);
-                ci = set_cache_.emplace(hsh, hs).first;
+                ci = set_cache_.emplace(set_key_, hs).first;
             }
-            it = set_index_.emplace(hsh, int(sets.size())).first;
-            sets.push_back(&ci->second);
-        }
-        if (role != kParent)
+            const HuffSetDev* node = &ci->second;
+            auto it = set_index_.find(node);
+            if (it == set_index_.end()) {
+                it = set_index_.emplace(node, int(sets.size())).first;
+                sets.push_back(node);
+            }
             im.huff_set = uint32_t(it->second);
+        }
 
         if (role != kChild)
             comp_bytes_ += int64_t(len[i]);
@@ -530,11 +751,11 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     so = align_up(so + 4ull * (coef_elems / 64), 256);
 
     coef_bytes_ = coef_elems * sizeof(int16_t);
-    if (!upload_host_.ensure(upload_bytes) || !state_host_.ensure(sizeof(ImageState) * std::max(nd, 1)))
+    if (!upload_host_.ensure(upload_bytes, sv_, stream) || !state_host_.ensure(sizeof(ImageState) * std::max(nd, 1), sv_, stream))
         return fail(B200JPEG_ERR_CUDA, "pinned host allocation failed");
-    if (!upload_.ensure(upload_bytes, &device_bytes_) || !scratch_.ensure(so + 256, &device_bytes_) ||
-        !cmp_.ensure(cmp_bytes + 256, &device_bytes_) || !coef_.ensure(coef_bytes_ + 256, &device_bytes_) ||
-        !planes_.ensure(plane_bytes + 256, &device_bytes_) || !bounce_.ensure(bounce_bytes + 256, &device_bytes_))
+    if (!upload_.ensure(upload_bytes, &device_bytes_, sv_, stream) || !scratch_.ensure(so + 256, &device_bytes_, sv_, stream) ||
+        !cmp_.ensure(cmp_bytes + 256, &device_bytes_, sv_, stream) || !coef_.ensure(coef_bytes_ + 256, &device_bytes_, sv_, stream) ||
+        !planes_.ensure(plane_bytes + 256, &device_bytes_, sv_, stream) || !bounce_.ensure(bounce_bytes + 256, &device_bytes_, sv_, stream))
         return fail(B200JPEG_ERR_CUDA, "device allocation failed");
 
     uint8_t* up = upload_host_.as<uint8_t>();
@@ -544,7 +765,15 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     uint32_t* dc_img = reinterpret_cast<uint32_t*>(up + off_dc);
     uint32_t* idct_img = reinterpret_cast<uint32_t*>(up + off_idct);
     uint32_t* color_img = reinterpret_cast<uint32_t*>(up + off_color);
-    std::vector<uint8_t> direct(size_t(nd), 0); // source is pinned / registered host memory: copy without staging
+    // Bitstreams that already sit in pinned / registered host memory are copied from where they lie when they are big
+    // enough to be worth a copy of their own; everything else is gathered into the pinned staging block (one big copy).
+    // Whether the sources are pinned is asked once per batch (the pipeline asks once per call), not per image.
+    if (sources_pinned < 0) {
+        cudaPointerAttributes attr{};
+        sources_pinned = (nd && cudaPointerGetAttributes(&attr, data[in_index_[0]]) == cudaSuccess && attr.type == cudaMemoryTypeHost) ? 1 : 0;
+        cudaGetLastError();
+    }
+    std::vector<uint8_t> direct(size_t(nd), 0);
     size_t staged_bytes = 0;
     for (int d = 0; d < nd; ++d) {
         ImageDev& im = imgs_[d];
@@ -556,35 +785,54 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         std::fill(dc_img + im.dc_cta_off, dc_img + im.dc_cta_off + im.n_dc_cta, uint32_t(d));
         std::fill(idct_img + im.idct_cta_off, idct_img + im.idct_cta_off + im.n_idct_cta, uint32_t(d));
         std::fill(color_img + im.color_cta_off, color_img + im.color_cta_off + im.n_color_cta_x * im.n_color_cta_y, uint32_t(d));
-        cudaPointerAttributes attr{};
-        // small streams are cheaper to gather into the staging block (one big copy) than to copy one by one
-        if (im.raw_len >= (uint32_t(opt_.direct_kb) << 10) && cudaPointerGetAttributes(&attr, data[in_index_[d]]) == cudaSuccess && attr.type == cudaMemoryTypeHost)
+        if (sources_pinned && im.raw_len >= (uint32_t(opt_.direct_kb) << 10))
             direct[d] = 1;
-        else {
-            cudaGetLastError();
+        else
             staged_bytes += im.raw_len;
-        }
     }
     if (staged_bytes) {
-        // pageable sources: copy into the pinned staging block, a few threads when it is worth it
-        auto stage = [&](int d0, int d1) {
-            for (int d = d0; d < d1; ++d) {
-                if (direct[d])
+        nvtx3::scoped_range nvtx_stage{"b200jpeg stage bitstreams"};
+        // staging copies, cut into jobs of about 1 MB for the helper threads
+        struct Job {
+            int d0, d1;
+        };
+        std::vector<Job> jobs;
+        {
+            size_t acc = 0;
+            int d0 = 0;
+            for (int d = 0; d < nd; ++d) {
+                acc += direct[d] ? 0 : imgs_[d].raw_len;
+                if (acc >= (size_t(1) << 20) || d + 1 == nd) {
+                    jobs.push_back({d0, d + 1});
+                    d0 = d + 1;
+                    acc = 0;
+                }
+            }
+        }
+        struct Ctx {
+            const Job* jobs;
+            const uint8_t* direct;
+            const ImageDev* imgs;
+            const void* const* data;
+            const int* in_index;
+            const StreamHeader* const* hdrs;
+            const size_t* item_of_dev;
+            uint8_t* dst;
+        } ctx{jobs.data(), direct.data(), imgs_.data(), data, in_index_.data(), hdrs.data(), item_of_dev.data(), up + off_raw};
+        auto stage = [](int j, void* a) {
+            const Ctx& c = *static_cast<const Ctx*>(a);
+            for (int d = c.jobs[j].d0; d < c.jobs[j].d1; ++d) {
+                if (c.direct[d])
                     continue;
-                const ImageDev& im = imgs_[d];
-                std::memcpy(up + off_raw + im.raw_off, static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[item_of_dev[d]].scan_offset, im.raw_len);
+                const ImageDev& im = c.imgs[d];
+                std::memcpy(c.dst + im.raw_off, static_cast<const uint8_t*>(c.data[c.in_index[d]]) + c.hdrs[c.item_of_dev[d]]->scan_offset, im.raw_len);
             }
         };
-        const int nthreads = staged_bytes > (size_t(8) << 20) ? std::min(4, std::max(1, int(std::thread::hardware_concurrency()) / 2)) : 1;
-        if (nthreads <= 1) {
-            stage(0, nd);
-        } else {
-            std::vector<std::thread> pool;
-            for (int t = 0; t < nthreads; ++t)
-                pool.emplace_back(stage, nd * t / nthreads, nd * (t + 1) / nthreads);
-            for (auto& th : pool)
-                th.join();
-        }
+        if (staged_bytes >= (size_t(2) << 20))
+            parallel_for(int(jobs.size()), stage, &ctx);
+        else
+            for (int j = 0; j < int(jobs.size()); ++j)
+                stage(j, &ctx);
     }
     if (nd) {
         std::memcpy(up + off_img, imgs_.data(), sizeof(ImageDev) * nd);
@@ -595,6 +843,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
 
     // one H2D for descriptors + maps + tables (+ the staged raw bytes), then one per directly copied image
     const size_t first_copy = staged_bytes ? upload_bytes : off_raw;
+    last_stream_ = stream;
+    inflight_ = nd > 0;
     if (nd && !cuda_ok(cudaMemcpyAsync(upload_.ptr, up, first_copy, cudaMemcpyHostToDevice, stream), "upload"))
         return B200JPEG_ERR_CUDA;
     for (int d = 0; d < nd; ++d) {
@@ -602,7 +852,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             continue;
         const ImageDev& im = imgs_[d];
         if (!cuda_ok(cudaMemcpyAsync(upload_.as<uint8_t>() + off_raw + im.raw_off,
-                         static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[item_of_dev[d]].scan_offset, im.raw_len, cudaMemcpyHostToDevice, stream),
+                         static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[item_of_dev[d]]->scan_offset, im.raw_len, cudaMemcpyHostToDevice, stream),
                 "bitstream upload"))
             return B200JPEG_ERR_CUDA;
     }
@@ -660,6 +910,7 @@ int Decoder::execute(cudaStream_t stream)
         return fail(B200JPEG_ERR_STATE, "execute without a prepared batch");
     if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
         return B200JPEG_ERR_CUDA;
+    nvtx3::scoped_range nvtx_execute{"b200jpeg execute (K0-K4 launches)"};
     launches_ = 0;
     executed_ = true;
     ev_recorded_ = false;
@@ -676,18 +927,33 @@ int Decoder::execute(cudaStream_t stream)
     launches_ += launch_write(bd_, false, stream); // writes every coefficient exactly once: no clearing pass
     mark(4, stream);
     launches_ += launch_dc_scan(bd_, false, stream);
+    // Everything a status depends on is known once the entropy stage is through (the pixel kernels only read the
+    // flags).  The read-back goes over a side stream so that it neither waits for the pixel kernels nor holds them up;
+    // finish_wait() then only has to wait for it, and the caller gets its statuses while the pixels are still being made.
+    cudaEventRecord(entropy_event_, stream);
+    cudaStreamWaitEvent(side_stream_, entropy_event_, 0);
+    cudaMemcpyAsync(state_host_.ptr, bd_.state, sizeof(ImageState) * bd_.n_images, cudaMemcpyDeviceToHost, side_stream_);
+    cudaEventRecord(entropy_event_, side_stream_);
     mark(5, stream);
-    launches_ += launch_idct(bd_, false, stream);
-    mark(6, stream);
-    launches_ += launch_color(bd_, false, stream);
+    launches_ += launch_pixels(false, stream);
     mark(7, stream);
     ev_recorded_ = profiling_ && ev_valid_;
+    last_stream_ = stream;
     if (!cuda_ok(cudaGetLastError(), "kernel launch"))
         return B200JPEG_ERR_CUDA;
     return B200JPEG_OK;
 }
 
-// Finish, part 1 (asynchronous): queue the state read-back and the copies of host outputs.
+int Decoder::launch_pixels(bool redo_only, cudaStream_t stream)
+{
+    int n = launch_idct(bd_, redo_only, stream);
+    if (!redo_only)
+        mark(6, stream);
+    n += launch_color(bd_, redo_only, stream);
+    return n;
+}
+
+// Finish, part 1 (asynchronous): queue the copies of host outputs, mark the end of the batch.
 int Decoder::finish_async(cudaStream_t stream)
 {
     if (!executed_)
@@ -695,32 +961,50 @@ int Decoder::finish_async(cudaStream_t stream)
     if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
         return B200JPEG_ERR_CUDA;
     const int nd = bd_.n_images;
-    if (nd && !cuda_ok(cudaMemcpyAsync(state_host_.ptr, bd_.state, sizeof(ImageState) * nd, cudaMemcpyDeviceToHost, stream), "state read-back"))
-        return B200JPEG_ERR_CUDA;
-    for (int d = 0; d < nd; ++d) {
-        const HostOut& ho = host_outs_[d];
-        if (ho.host_ptr &&
-            !cuda_ok(cudaMemcpyAsync(ho.host_ptr, bounce_.as<uint8_t>() + ho.bounce_off, ho.bytes, cudaMemcpyDeviceToHost, stream), "output copy"))
+    for (int d = 0; d < nd; ++d)
+        if (!copy_host_output(d, stream))
             return B200JPEG_ERR_CUDA;
-    }
+    cudaEventRecord(done_event_, stream);
+    have_done_ = true;
+    last_stream_ = stream;
     finish_queued_ = true;
     return B200JPEG_OK;
 }
 
-// Finish, part 2: wait, run the rare re-synchronisation path, report statuses.
+// Pixels of a host output: only the pixel bytes of every row travel (a caller's row padding is left alone, and a
+// buffer that ends with the last pixel of the last row is not overrun).
+bool Decoder::copy_host_output(int d, cudaStream_t stream)
+{
+    const HostOut& ho = host_outs_[d];
+    if (!ho.host_ptr)
+        return true;
+    const uint8_t* src = bounce_.as<uint8_t>() + ho.bounce_off;
+    if (ho.stride == ho.tight)
+        return cuda_ok(cudaMemcpyAsync(ho.host_ptr, src, ho.tight * ho.rows, cudaMemcpyDeviceToHost, stream), "output copy");
+    return cuda_ok(cudaMemcpy2DAsync(ho.host_ptr, ho.stride, src, ho.stride, ho.tight, ho.rows, cudaMemcpyDeviceToHost, stream), "output copy");
+}
+
+// Finish, part 2: wait for the statuses (and for the pixels when some of them go to host memory), run the rare
+// re-synchronisation path, report.  With device outputs only, the pixel kernels may still be running on `stream` when
+// this returns: work queued on that stream afterwards sees the finished pixels, as with any stream-ordered CUDA call.
 int Decoder::finish_wait(int* status, cudaStream_t stream)
 {
     if (!finish_queued_)
         return fail(B200JPEG_ERR_STATE, "finish_wait without finish_async");
     finish_queued_ = false;
+    nvtx3::scoped_range nvtx_finish{"b200jpeg finish (wait for statuses)"};
     if (!cuda_ok(cudaSetDevice(device_), "cudaSetDevice"))
         return B200JPEG_ERR_CUDA;
     const int nd = bd_.n_images;
     resync_images_ = 0;
-    if (!cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
-        return B200JPEG_ERR_CUDA;
-    if (nd)
+    if (nd) {
+        if (!cuda_ok(cudaEventSynchronize(entropy_event_), "synchronize"))
+            return B200JPEG_ERR_CUDA;
         std::memcpy(states_.data(), state_host_.ptr, sizeof(ImageState) * nd);
+    }
+    inflight_ = false; // the uploads lie before the entropy stage
+    if ((any_host_out_ || opt_.sync_finish) && !cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
+        return B200JPEG_ERR_CUDA;
     auto read_states = [&]() -> bool {
         if (!cuda_ok(cudaMemcpyAsync(state_host_.ptr, bd_.state, sizeof(ImageState) * nd, cudaMemcpyDeviceToHost, stream), "state read-back"))
             return false;
@@ -742,6 +1026,7 @@ int Decoder::finish_wait(int* status, cudaStream_t stream)
         // Rare path: some sequence of some image did not enter with the state its predecessor left.
         // Propagate corrected entry states one sequence per round until K2 finds every image consistent,
         // then produce coefficients and pixels of those images again.
+        nvtx3::scoped_range nvtx_fix{"b200jpeg re-synchronisation path"};
         resync_images_ = dirty;
         int rounds = 0;
         while (dirty && rounds < opt_.max_fix_rounds) {
@@ -754,21 +1039,20 @@ int Decoder::finish_wait(int* status, cudaStream_t stream)
         }
         launches_ += launch_write(bd_, true, stream);
         launches_ += launch_dc_scan(bd_, true, stream);
-        launches_ += launch_idct(bd_, true, stream);
-        launches_ += launch_color(bd_, true, stream);
+        launches_ += launch_pixels(true, stream);
         if (!read_states())
             return B200JPEG_ERR_CUDA;
         bool any_host = false;
         for (int d = 0; d < nd; ++d) {
-            const HostOut& ho = host_outs_[d];
-            if (!ho.host_ptr || !(flags_of(d) & kFlagRedo))
+            if (!host_outs_[d].host_ptr || !(flags_of(d) & kFlagRedo))
                 continue;
             any_host = true;
-            if (!cuda_ok(cudaMemcpyAsync(ho.host_ptr, bounce_.as<uint8_t>() + ho.bounce_off, ho.bytes, cudaMemcpyDeviceToHost, stream), "output copy"))
+            if (!copy_host_output(d, stream))
                 return B200JPEG_ERR_CUDA;
         }
         if (any_host && !cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
             return B200JPEG_ERR_CUDA;
+        cudaEventRecord(done_event_, stream);
     }
     if (status) {
         for (int i = 0; i < n_in_; ++i) {
@@ -875,7 +1159,7 @@ int Decoder::scan_segment(const void* dev_raw, size_t length, uint32_t expected_
     const size_t off_info = align_up(off_tile + 4ull * n_tiles, 256);
     const size_t off_base = align_up(off_info + 8ull * n_tiles, 256);
     const size_t total = off_base + 8ull * n_tiles;
-    if (!scan_scratch_.ensure(total, &device_bytes_) || !scan_host_.ensure(off_info))
+    if (!scan_scratch_.ensure(total, &device_bytes_, sv_, stream) || !scan_host_.ensure(off_info, sv_, stream))
         return fail(B200JPEG_ERR_CUDA, "allocation failed");
     // the previous call's upload may still be in flight out of the pinned staging block
     if (!cuda_ok(cudaStreamSynchronize(stream), "synchronize"))
@@ -916,18 +1200,32 @@ int Decoder::scan_segment(const void* dev_raw, size_t length, uint32_t expected_
 // i and the D2H of chunk i-1 overlap.  Chunk results are identical to an unchunked decode: images
 // are independent.
 // ------------------------------------------------------------------------------------------------
-Pipeline::Pipeline(int device_id, const Options& opt, int n_lanes)
+Pipeline::Pipeline(int device_id, const Options& opt, int n_lanes, const Services& sv)
     : device_(device_id)
     , opt_(opt)
+    , sv_(sv)
 {
+    if (!sv_.parallel_for) {
+        int n = opt_.host_threads;
+        if (n <= 0) {
+            cpu_set_t set;
+            CPU_ZERO(&set);
+            const int cpus = sched_getaffinity(0, sizeof(set), &set) == 0 ? CPU_COUNT(&set) : int(std::thread::hardware_concurrency());
+            n = std::min(8, std::max(1, cpus / 2));
+        }
+        if (n > 1)
+            pool_ = std::make_unique<HostPool>(n - 1); // the calling thread takes part
+    }
     lanes_.resize(size_t(std::max(1, n_lanes)));
     for (auto& l : lanes_)
-        l.dec = std::make_unique<Decoder>(device_id, opt);
+        l.dec = std::make_unique<Decoder>(device_id, opt, sv_, pool_.get());
 }
 
 Pipeline::~Pipeline()
 {
     cudaSetDevice(device_);
+    for (auto& l : lanes_)
+        l.dec.reset(); // while the lane streams are still alive
     for (auto& l : lanes_) {
         if (l.stream)
             cudaStreamDestroy(l.stream);
@@ -936,7 +1234,8 @@ Pipeline::~Pipeline()
         cudaEventDestroy(user_event_);
 }
 
-int Pipeline::decode(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, int* status, cudaStream_t user_stream)
+int Pipeline::decode(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, int* status, cudaStream_t user_stream,
+    const ParsedInput* const* parsed)
 {
     if (n < 0 || (n > 0 && (!data || !len || !outs)))
         return B200JPEG_ERR_ARG;
@@ -944,6 +1243,16 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         return B200JPEG_ERR_CUDA;
     last_launches_ = 0;
     last_resync_ = 0;
+    // are the bitstreams in pinned memory?  asked once per call
+    int pinned = 0;
+    for (int i = 0; i < n && !pinned; ++i) {
+        if (!data[i])
+            continue;
+        cudaPointerAttributes attr{};
+        pinned = (cudaPointerGetAttributes(&attr, data[i]) == cudaSuccess && attr.type == cudaMemoryTypeHost) ? 1 : 0;
+        cudaGetLastError();
+        break;
+    }
     // chunk boundaries: chunk_mb of bitstream or chunk_images images, whichever comes first; small batches stay whole
     std::vector<int> cuts{0};
     {
@@ -955,10 +1264,7 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         size_t chunk_bytes = size_t(opt_.chunk_mb) << 20;
         if (!chunk_bytes) {
             // Pinned bitstreams are copied straight from the caller's buffers: small chunks start the GPU early.  Pageable ones
-            // are gathered into a pinned staging block first (a few threads per chunk): that wants bigger chunks.
-            cudaPointerAttributes attr{};
-            const bool pinned = n > 0 && data[0] && cudaPointerGetAttributes(&attr, data[0]) == cudaSuccess && attr.type == cudaMemoryTypeHost;
-            cudaGetLastError();
+            // are gathered into a pinned staging block first (helper threads): that wants bigger chunks.
             chunk_bytes = size_t(pinned ? 8 : 24) << 20;
         }
         const int chunk_images = opt_.chunk_images;
@@ -975,7 +1281,7 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         cuts.push_back(n);
     }
     const int n_chunks = int(cuts.size()) - 1;
-    if (n_chunks > 1 || lanes_[0].stream) {
+    if (n_chunks > 1) {
         // lanes run on their own streams, ordered after whatever the caller already queued
         if (!user_event_ && cudaEventCreateWithFlags(&user_event_, cudaEventDisableTiming) != cudaSuccess)
             return B200JPEG_ERR_CUDA;
@@ -994,6 +1300,8 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         last_resync_ += l.dec->stat(B200JPEG_STAT_RESYNC_IMAGES);
         l.busy = false;
     };
+    for (auto& l : lanes_)
+        l.used = false;
     for (int c = 0; c < n_chunks; ++c) {
         Lane& l = lanes_[size_t(c) % lanes_.size()];
         drain(l);
@@ -1005,7 +1313,7 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
             s = l.stream;
             cudaStreamWaitEvent(s, user_event_, 0);
         }
-        int rc = l.dec->prepare(cnt, data + first, len + first, outs + first, s);
+        int rc = l.dec->prepare(cnt, data + first, len + first, outs + first, s, parsed ? parsed + first : nullptr, pinned);
         if (rc == B200JPEG_OK)
             rc = l.dec->execute(s);
         if (rc == B200JPEG_OK)
@@ -1023,9 +1331,15 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         l.first = first;
         l.active_stream = s;
         l.busy = true;
+        l.used = true;
     }
     for (auto& l : lanes_)
         drain(l);
+    // The caller's stream sees the pixels: it waits (on the device, not on the host) for the last work of every lane.
+    if (n_chunks > 1)
+        for (auto& l : lanes_)
+            if (l.used)
+                cudaStreamWaitEvent(user_stream, l.dec->done_event(), 0);
     return rc_all;
 }
 

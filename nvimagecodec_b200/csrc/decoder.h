@@ -8,6 +8,7 @@
 #include <cstdint>
 #include <memory>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -17,11 +18,31 @@
 
 namespace b200jpeg {
 
+// Where a decoder gets its memory and its helper threads from.  An nvImageCodec host hands plugins its own
+// allocators (nvimgcodecExecutionParams_t::device_allocator / pinned_allocator, include/nvimgcodec.h:246-281:
+// stream-ordered, the size is passed back on free) and its executor; the extension adapter forwards them here.
+// Unset members fall back to what the reference's own buffers do (src/imgproc/device_buffer.cpp:42-69):
+// cudaMallocAsync / cudaFreeAsync on the batch's stream where the device has memory pools, else cudaMalloc;
+// cudaMallocHost for pinned memory; a small internal thread pool for host-side fan-out.
+struct Services {
+    void* device_ctx = nullptr;
+    int (*device_malloc)(void* ctx, void** ptr, size_t size, cudaStream_t stream) = nullptr;
+    int (*device_free)(void* ctx, void* ptr, size_t size, cudaStream_t stream) = nullptr;
+    void* pinned_ctx = nullptr;
+    int (*pinned_malloc)(void* ctx, void** ptr, size_t size, cudaStream_t stream) = nullptr;
+    int (*pinned_free)(void* ctx, void* ptr, size_t size, cudaStream_t stream) = nullptr;
+    // run fn(i, arg) for i in [0, n) on helper threads (the caller may take part); returns when all are done
+    void* par_ctx = nullptr;
+    void (*parallel_for)(void* ctx, int n, void (*fn)(int i, void* arg), void* arg) = nullptr;
+};
+
 struct DeviceBuffer {
     void* ptr = nullptr;
     size_t cap = 0;
-    bool ensure(size_t bytes, size_t* total); // grow-only
-    void release();
+    cudaStream_t stream = nullptr; // the stream the block was allocated on (frees are ordered on it)
+    int idle = 0;                  // consecutive batches that needed less than a quarter of the block
+    bool ensure(size_t bytes, size_t* total, const Services& sv, cudaStream_t s); // grows; shrinks after a run of small batches
+    void release(const Services& sv);
     template <typename T>
     T* as() const { return static_cast<T*>(ptr); }
 };
@@ -29,35 +50,65 @@ struct DeviceBuffer {
 struct PinnedBuffer {
     void* ptr = nullptr;
     size_t cap = 0;
-    bool ensure(size_t bytes);
-    void release();
+    bool ensure(size_t bytes, const Services& sv, cudaStream_t s);
+    void release(const Services& sv);
     template <typename T>
     T* as() const { return static_cast<T*>(ptr); }
+};
+
+// A few persistent helper threads for the host side of a batch (marker walks, staging copies).
+class HostPool {
+  public:
+    explicit HostPool(int n_threads);
+    ~HostPool();
+    void run(int n, void (*fn)(int, void*), void* arg); // caller takes part; returns when all n are done
+    int size() const { return int(threads_.size()); }
+
+  private:
+    struct Impl;
+    Impl* impl_;
+    std::vector<std::thread> threads_;
 };
 
 struct Options {
     bool fancy_upsampling = true; // libjpeg_turbo_ext default (libjpeg_turbo_decoder.cpp:223-249)
     bool debug_no_warm = false;   // test hook: forces the re-synchronisation path
     int max_fix_rounds = 1 << 20;
-    int subseq_bits = 0;          // 0 = choose per batch; else 1024 / 2048 / 4096
-    int chunk_mb = 0;             // pipeline chunk: this much bitstream (0 = 8 MB for pinned sources, 24 MB for pageable ones, which are staged by a few threads) ...
+    int subseq_bits = 0;          // 0 = choose per batch; else 512 / 1024 / 2048 / 4096
+    int chunk_mb = 0;             // pipeline chunk: this much bitstream (0 = 8 MB for pinned sources, 24 MB for pageable ones, which are staged by helper threads) ...
     int direct_kb = 128;          // pinned bitstreams of at least this many KiB are copied straight from the caller's buffer
     int lanes = 6;                // pipeline lanes (decoder + stream each) the chunks rotate over
     int chunk_images = 64;        // ... or this many images, whichever comes first
+    int host_threads = 0;         // helper threads for marker walks / staging (0 = by the CPUs this process may run on, at most 8)
+    bool sync_finish = false;     // Finish / DecodeBatch wait for the pixel kernels too, not only for the statuses
+    int max_arena_mb = 32768;     // refuse (ERR_TOO_LARGE) images whose coefficient + plane arenas would exceed this many MiB
 };
 
 Options parse_options(const char* options, const char* decoder_id);
+struct ParsedInput;
+void parse_input(const void* data, size_t len, ParsedInput* out);
+
+// What the marker walk found for one input of a batch; computed by Decoder::parse_inputs (in parallel when the
+// batch is large) or handed in by a caller that walked the stream already (the extension's canDecode).
+struct ParsedInput {
+    StreamStatus status = kStreamNotJpeg;
+    StreamHeader frame;          // kStreamOk: the stream; kStreamMultiScan: geometry of the whole image
+    std::unique_ptr<StreamHeader[]> scans; // kStreamMultiScan only: the three one-component scans
+    StreamStatus multi_status = kStreamOk;
+};
 
 class Decoder {
   public:
-    Decoder(int device_id, const Options& opt);
+    Decoder(int device_id, const Options& opt, const Services& sv, HostPool* pool);
     ~Decoder();
 
-    int prepare(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, cudaStream_t stream);
+    // parsed: nullptr, or n entries of which the non-null ones replace the marker walk of that input
+    int prepare(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, cudaStream_t stream,
+        const ParsedInput* const* parsed = nullptr, int sources_pinned = -1);
     int execute(cudaStream_t stream);
     int finish(int* status, cudaStream_t stream);
     int finish_async(cudaStream_t stream);          // queue read-backs / host-output copies
-    int finish_wait(int* status, cudaStream_t stream); // wait, fix-up path, statuses
+    int finish_wait(int* status, cudaStream_t stream); // wait (for the entropy stage only when no output is a host buffer), fix-up path, statuses
 
     int64_t stat(int which) const;
     void set_profiling(bool on) { profiling_ = on; }
@@ -67,14 +118,21 @@ class Decoder {
         void* dev_result, cudaStream_t stream);
     const char* last_error() const { return err_.c_str(); }
     int device() const { return device_; }
+    cudaEvent_t done_event() const { return done_event_; } // recorded behind the last kernel / copy of the last batch
+    bool has_host_outputs() const { return any_host_out_; }
 
   private:
     int fail(int code, const std::string& msg);
     bool cuda_ok(cudaError_t e, const char* what);
     void mark(int stage, cudaStream_t s);
+    void parallel_for(int n, void (*fn)(int, void*), void* arg);
+    int launch_pixels(bool redo_only, cudaStream_t stream);
+    bool copy_host_output(int d, cudaStream_t stream);
 
     int device_;
     Options opt_;
+    Services sv_;
+    HostPool* pool_;
     std::string err_;
 
     // batch bookkeeping (host)
@@ -88,9 +146,11 @@ class Decoder {
     struct HostOut {
         void* host_ptr;
         size_t bounce_off, bytes;
+        size_t stride, tight, rows; // rows of `tight` pixel bytes, `stride` apart (all planes of a planar image together)
     };
     std::vector<HostOut> host_outs_;    // per device image; host_ptr == nullptr if output is a device buffer
-    bool prepared_ = false, executed_ = false, finish_queued_ = false;
+    std::vector<ParsedInput> parsed_own_;
+    bool prepared_ = false, executed_ = false, finish_queued_ = false, any_host_out_ = false;
 
     // device memory
     DeviceBuffer upload_, scratch_, cmp_, coef_, planes_, bounce_, scan_scratch_;
@@ -98,10 +158,18 @@ class Decoder {
     size_t device_bytes_ = 0;
     size_t coef_bytes_ = 0;
     BatchDev bd_{};
+    cudaEvent_t entropy_event_ = nullptr; // behind the state read-back that follows the entropy stage
+    cudaEvent_t done_event_ = nullptr;
+    cudaStream_t side_stream_ = nullptr;  // carries the state read-back so that it does not sit between the kernels
+    cudaStream_t last_stream_ = nullptr;
+    bool have_done_ = false;  // done_event_ was recorded for the last batch
+    bool inflight_ = false;   // a prepared batch has not been waited for yet (its uploads may still read the pinned staging)
 
-    // huffman set cache (content keyed by hash)
-    std::unordered_map<uint64_t, int> set_index_; // per batch
-    std::unordered_map<uint64_t, HuffSetDev> set_cache_;
+    // huffman set cache, keyed by the canonical bytes of the table specs (huff_set_key)
+    static constexpr size_t kSetCacheMax = 4096;
+    std::unordered_map<const HuffSetDev*, int> set_index_; // per batch: cache node -> index in the upload
+    std::unordered_map<std::string, HuffSetDev> set_cache_;
+    std::string set_key_;
 
     // stats
     int64_t launches_ = 0, algo_bytes_ = 0, comp_bytes_ = 0, n_coefs_ = 0, out_bytes_ = 0, resync_images_ = 0;
@@ -117,9 +185,10 @@ class Decoder {
 // Chunked, overlapped decode of a whole batch (what b200jpegDecodeBatch and the extension's decodeBatch use).
 class Pipeline {
   public:
-    Pipeline(int device_id, const Options& opt, int n_lanes = 6);
+    Pipeline(int device_id, const Options& opt, int n_lanes = 6, const Services& sv = Services());
     ~Pipeline();
-    int decode(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, int* status, cudaStream_t user_stream);
+    int decode(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, int* status, cudaStream_t user_stream,
+        const ParsedInput* const* parsed = nullptr);
     Decoder& lane0() { return *lanes_[0].dec; } // Prepare / Execute / Finish and the kernel-level entry points use this one
     int64_t last_launches() const { return last_launches_; }
     int64_t last_resync() const { return last_resync_; }
@@ -133,9 +202,12 @@ class Pipeline {
         cudaStream_t active_stream = nullptr;
         int first = 0;
         bool busy = false;
+        bool used = false; // took part in the current call (its done event gates the caller's stream)
     };
     int device_;
     Options opt_;
+    Services sv_;
+    std::unique_ptr<HostPool> pool_;
     std::vector<Lane> lanes_;
     cudaEvent_t user_event_ = nullptr;
     int64_t last_launches_ = 0, last_resync_ = 0;

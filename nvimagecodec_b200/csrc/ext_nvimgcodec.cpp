@@ -13,11 +13,15 @@
 #include <nvimgcodec.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstring>
+#include <deque>
 #include <memory>
 #include <mutex>
 #include <sstream>
 #include <string>
+#include <thread>
+#include <unordered_map>
 #include <vector>
 
 #include "b200jpeg.h"
@@ -205,6 +209,64 @@ nvimgcodecProcessingStatus_t to_processing_status(int b200_status)
     }
 }
 
+// ---- what the host framework lends a plugin: its allocators and its executor (SURVEY.md 8b "Memory / ownership")
+// One job handed to the framework's executor.  The helpers pull indices from a shared counter; the caller takes part
+// and only waits until every index is done, so helpers that the executor starts late (its threads may be busy with
+// the framework's own per-sample work) find nothing to do and drop their reference.
+struct ParJob {
+    std::atomic<int> next{0}, done{0}, refs{1};
+    int n = 0;
+    void (*fn)(int, void*) = nullptr;
+    void* arg = nullptr;
+    static void drop(ParJob* j)
+    {
+        if (j->refs.fetch_sub(1) == 1)
+            delete j;
+    }
+    static void worker(int, int, void* ctx)
+    {
+        ParJob* j = static_cast<ParJob*>(ctx);
+        for (int i; (i = j->next.fetch_add(1)) < j->n;) {
+            j->fn(i, j->arg);
+            j->done.fetch_add(1, std::memory_order_release);
+        }
+        drop(j);
+    }
+};
+
+struct ExecutorCtx {
+    nvimgcodecExecutorDesc_t* executor = nullptr;
+    int device_id = 0;
+};
+
+void executor_parallel_for(void* ctx, int n, void (*fn)(int, void*), void* arg)
+{
+    auto* ec = static_cast<ExecutorCtx*>(ctx);
+    nvimgcodecExecutorDesc_t* ex = ec->executor;
+    const int helpers = std::min(n - 1, std::min(8, ex->getNumThreads(ex->instance)));
+    ParJob* job = new ParJob;
+    job->n = n;
+    job->fn = fn;
+    job->arg = arg;
+    int scheduled = 0;
+    for (int h = 0; h < helpers; ++h) {
+        job->refs.fetch_add(1);
+        if (ex->schedule(ex->instance, ec->device_id, h, job, &ParJob::worker) == NVIMGCODEC_STATUS_SUCCESS)
+            ++scheduled;
+        else
+            job->refs.fetch_sub(1);
+    }
+    if (scheduled)
+        ex->run(ex->instance, ec->device_id);
+    for (int i; (i = job->next.fetch_add(1)) < n;) {
+        fn(i, arg);
+        job->done.fetch_add(1, std::memory_order_release);
+    }
+    while (job->done.load(std::memory_order_acquire) < n)
+        std::this_thread::yield();
+    ParJob::drop(job);
+}
+
 class DecoderImpl {
   public:
     DecoderImpl(const nvimgcodecFrameworkDesc_t* fw, const nvimgcodecExecutionParams_t* ep, const char* options)
@@ -215,11 +277,30 @@ class DecoderImpl {
         int n = 1;
         if (ep_->executor && ep_->executor->getNumThreads)
             n = ep_->executor->getNumThreads(ep_->executor->instance) + 1;
-        cores_.resize(size_t(n) + 1);
+        walked_.resize(size_t(n) + 1);
+        // memory and helper threads come from the host when it offers them (include/nvimgcodec.h:246-281, 1045-1084),
+        // as src/imgproc/device_buffer.cpp:42-69 and the reference's plugins do
+        if (ep_->device_allocator && ep_->device_allocator->device_malloc && ep_->device_allocator->device_free) {
+            sv_.device_ctx = ep_->device_allocator->device_ctx;
+            sv_.device_malloc = ep_->device_allocator->device_malloc;
+            sv_.device_free = ep_->device_allocator->device_free;
+        }
+        if (ep_->pinned_allocator && ep_->pinned_allocator->pinned_malloc && ep_->pinned_allocator->pinned_free) {
+            sv_.pinned_ctx = ep_->pinned_allocator->pinned_ctx;
+            sv_.pinned_malloc = ep_->pinned_allocator->pinned_malloc;
+            sv_.pinned_free = ep_->pinned_allocator->pinned_free;
+        }
+        if (ep_->executor && ep_->executor->schedule && ep_->executor->run && ep_->executor->getNumThreads &&
+            ep_->executor->getNumThreads(ep_->executor->instance) > 0) {
+            exec_ctx_.executor = ep_->executor;
+            exec_ctx_.device_id = ep_->device_id;
+            sv_.par_ctx = &exec_ctx_;
+            sv_.parallel_for = &executor_parallel_for;
+        }
     }
 
     nvimgcodecProcessingStatus_t can_decode(const nvimgcodecImageDesc_t* image, const nvimgcodecCodeStreamDesc_t* cs,
-        const nvimgcodecDecodeParams_t* params)
+        const nvimgcodecDecodeParams_t* params, int thread_idx)
     {
         if (!image || !cs || !params)
             return NVIMGCODEC_PROCESSING_STATUS_FAIL;
@@ -254,27 +335,62 @@ class DecoderImpl {
             st |= NVIMGCODEC_PROCESSING_STATUS_SAMPLE_FORMAT_UNSUPPORTED;
         if (st != NVIMGCODEC_PROCESSING_STATUS_SUCCESS)
             return st;
-        // stream-level acceptance: our own marker walk (the built-in parser stops before DQT/DHT/DRI/SOS)
+        // stream-level acceptance: our own marker walk (the built-in parser stops before DQT/DHT/DRI/SOS).  Its result
+        // is kept for decodeBatch, which would otherwise walk the same bytes again.
         MappedStream ms;
         if (!map_stream(cs, &ms))
             return NVIMGCODEC_PROCESSING_STATUS_FAIL;
-        b200jpegStreamInfo_t si;
-        const int rc = b200jpegProbe(ms.data, ms.size, &si);
-        if (rc == B200JPEG_OK)
+        auto walked = std::make_unique<Walked>();
+        walked->data = ms.owned.empty() ? ms.data : nullptr; // an unmapped stream was read into a temporary: nothing to key on
+        walked->size = ms.size;
+        b200jpeg::parse_input(ms.data, ms.size, &walked->parsed);
+        const b200jpeg::ParsedInput& pi = walked->parsed;
+        b200jpeg::StreamStatus ss = pi.status;
+        size_t longest_scan = pi.frame.scan_length;
+        if (ss == b200jpeg::kStreamMultiScan) {
+            ss = pi.multi_status;
+            for (int c = 0; c < 3 && pi.scans; ++c)
+                longest_scan = std::max(longest_scan, pi.scans[c].scan_length);
+        }
+        if (ss == b200jpeg::kStreamOk && longest_scan >= (size_t(1) << 28))
+            return NVIMGCODEC_PROCESSING_STATUS_CODESTREAM_UNSUPPORTED;
+        if (ss == b200jpeg::kStreamOk) {
+            if (walked->data)
+                remember(thread_idx, cs, std::move(walked));
             return NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
-        if (rc == B200JPEG_ERR_CORRUPT || rc == B200JPEG_ERR_NOT_JPEG)
+        }
+        if (ss == b200jpeg::kStreamCorrupt || ss == b200jpeg::kStreamNotJpeg)
             return NVIMGCODEC_PROCESSING_STATUS_IMAGE_CORRUPTED;
         return NVIMGCODEC_PROCESSING_STATUS_CODESTREAM_UNSUPPORTED;
     }
 
-    // Shared by decodeBatch (thread_idx 0, whole batch on one framework stream) and the per-sample
-    // decode safety net (one core per executor thread).
-    nvimgcodecStatus_t decode_batch(const nvimgcodecImageDesc_t** images, const nvimgcodecCodeStreamDesc_t** css, int n, int thread_idx,
+    // Shared by decodeBatch (the whole batch on one framework stream, the chunked pipeline) and the per-sample
+    // decode safety net (one extra single-lane pipeline, serialised, released by the next batch).
+    nvimgcodecStatus_t decode_batch(const nvimgcodecImageDesc_t** images, const nvimgcodecCodeStreamDesc_t** css, int n, bool batched,
         bool apply_orientation)
     {
         if (n <= 0)
             return NVIMGCODEC_STATUS_SUCCESS;
-        b200jpeg::Pipeline* core = core_for(thread_idx);
+        std::unique_lock<std::mutex> fallback_lock(fallback_mu_, std::defer_lock);
+        b200jpeg::Pipeline* core = nullptr;
+        try {
+            if (batched) {
+                {
+                    std::lock_guard<std::mutex> lk(fallback_mu_);
+                    fallback_.reset(); // what a per-sample retry allocated is not kept across batches
+                }
+                if (!batch_)
+                    batch_ = std::make_unique<b200jpeg::Pipeline>(ep_->device_id, opt_, opt_.lanes, sv_);
+                core = batch_.get();
+            } else {
+                fallback_lock.lock();
+                if (!fallback_)
+                    fallback_ = std::make_unique<b200jpeg::Pipeline>(ep_->device_id, opt_, 1, sv_);
+                core = fallback_.get();
+            }
+        } catch (...) {
+            core = nullptr;
+        }
         if (!core) {
             for (int i = 0; i < n; ++i)
                 images[i]->imageReady(images[i]->instance, NVIMGCODEC_PROCESSING_STATUS_FAIL);
@@ -286,6 +402,8 @@ class DecoderImpl {
         std::vector<b200jpegOutput_t> outs(n);
         std::vector<nvimgcodecProcessingStatus_t> pre(n, NVIMGCODEC_PROCESSING_STATUS_SUCCESS);
         std::vector<int> status(n, B200JPEG_ERR_STATE);
+        std::vector<std::unique_ptr<Walked>> walked(n);
+        std::vector<const b200jpeg::ParsedInput*> parsed(n, nullptr);
         cudaStream_t stream = nullptr;
         bool have_stream = false;
         for (int i = 0; i < n; ++i) {
@@ -309,9 +427,12 @@ class DecoderImpl {
             if (pre[i] == NVIMGCODEC_PROCESSING_STATUS_SUCCESS) {
                 data[i] = streams[i].data;
                 len[i] = streams[i].size;
+                walked[i] = recall(css[i], streams[i].data, streams[i].size);
+                if (walked[i])
+                    parsed[i] = &walked[i]->parsed;
             }
         }
-        const int rc = core->decode(n, data.data(), len.data(), outs.data(), status.data(), stream);
+        const int rc = core->decode(n, data.data(), len.data(), outs.data(), status.data(), stream, parsed.data());
         if (rc != B200JPEG_OK)
             log_msg(fw_, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_ERROR, std::string("b200 jpeg batch decode failed: ") + core->last_error());
         for (int i = 0; i < n; ++i) {
@@ -324,22 +445,51 @@ class DecoderImpl {
     }
 
   private:
-    b200jpeg::Pipeline* core_for(int thread_idx)
+    // Marker walks done by canDecode, waiting for the decode call that follows it in the same nvimgcodecDecoderDecode.
+    // canDecode runs on executor threads (thread_idx in [0, N]): one table per thread, each with its own lock.
+    struct Walked {
+        const void* data = nullptr;
+        size_t size = 0;
+        b200jpeg::ParsedInput parsed;
+    };
+    struct WalkTable {
+        std::mutex mu;
+        std::unordered_map<const void*, std::unique_ptr<Walked>> map;
+    };
+    void remember(int thread_idx, const nvimgcodecCodeStreamDesc_t* cs, std::unique_ptr<Walked> w)
     {
-        std::lock_guard<std::mutex> lock(mu_);
-        size_t slot = thread_idx < 0 ? cores_.size() - 1 : size_t(thread_idx);
-        if (slot >= cores_.size())
-            cores_.resize(slot + 1);
-        if (!cores_[slot])
-            cores_[slot] = std::make_unique<b200jpeg::Pipeline>(ep_->device_id, opt_, slot == 0 ? 3 : 1);
-        return cores_[slot].get();
+        const size_t slot = (thread_idx < 0 || size_t(thread_idx) >= walked_.size()) ? walked_.size() - 1 : size_t(thread_idx);
+        WalkTable& t = walked_[slot];
+        std::lock_guard<std::mutex> lk(t.mu);
+        if (t.map.size() > 16384) // walked but never decoded by us (another decoder took them): do not let them pile up
+            t.map.clear();
+        t.map[cs->instance] = std::move(w);
+    }
+    std::unique_ptr<Walked> recall(const nvimgcodecCodeStreamDesc_t* cs, const void* data, size_t size)
+    {
+        for (WalkTable& t : walked_) {
+            std::lock_guard<std::mutex> lk(t.mu);
+            auto it = t.map.find(cs->instance);
+            if (it == t.map.end())
+                continue;
+            std::unique_ptr<Walked> w = std::move(it->second);
+            t.map.erase(it);
+            if (w && w->data == data && w->size == size) // the same mapped bytes canDecode looked at
+                return w;
+            return nullptr;
+        }
+        return nullptr;
     }
 
     const nvimgcodecFrameworkDesc_t* fw_;
     const nvimgcodecExecutionParams_t* ep_;
     b200jpeg::Options opt_;
-    std::mutex mu_;
-    std::vector<std::unique_ptr<b200jpeg::Pipeline>> cores_;
+    b200jpeg::Services sv_;
+    ExecutorCtx exec_ctx_;
+    std::deque<WalkTable> walked_;
+    std::unique_ptr<b200jpeg::Pipeline> batch_;
+    std::mutex fallback_mu_;
+    std::unique_ptr<b200jpeg::Pipeline> fallback_;
 };
 
 // ---- C trampolines of nvimgcodecDecoderDesc_t (never let an exception cross the ABI)
@@ -375,22 +525,20 @@ nvimgcodecStatus_t dec_get_metadata(nvimgcodecDecoder_t, const nvimgcodecCodeStr
 }
 
 nvimgcodecProcessingStatus_t dec_can_decode(nvimgcodecDecoder_t decoder, const nvimgcodecImageDesc_t* image,
-    const nvimgcodecCodeStreamDesc_t* cs, const nvimgcodecDecodeParams_t* params, int)
+    const nvimgcodecCodeStreamDesc_t* cs, const nvimgcodecDecodeParams_t* params, int thread_idx)
 {
     try {
-        return reinterpret_cast<DecoderImpl*>(decoder)->can_decode(image, cs, params);
+        return reinterpret_cast<DecoderImpl*>(decoder)->can_decode(image, cs, params, thread_idx);
     } catch (...) {
         return NVIMGCODEC_PROCESSING_STATUS_FAIL;
     }
 }
 
 nvimgcodecStatus_t dec_decode(nvimgcodecDecoder_t decoder, const nvimgcodecImageDesc_t* image, const nvimgcodecCodeStreamDesc_t* cs,
-    const nvimgcodecDecodeParams_t* params, int thread_idx)
+    const nvimgcodecDecodeParams_t* params, int)
 {
     try {
-        // +1: slot 0 belongs to decodeBatch, which the framework calls with thread_idx 0 on the caller thread
-        return reinterpret_cast<DecoderImpl*>(decoder)->decode_batch(&image, &cs, 1, thread_idx < 0 ? -1 : thread_idx + 1,
-            params && params->apply_exif_orientation);
+        return reinterpret_cast<DecoderImpl*>(decoder)->decode_batch(&image, &cs, 1, false, params && params->apply_exif_orientation);
     } catch (...) {
         if (image)
             image->imageReady(image->instance, NVIMGCODEC_PROCESSING_STATUS_FAIL);
@@ -402,7 +550,7 @@ nvimgcodecStatus_t dec_decode_batch(nvimgcodecDecoder_t decoder, const nvimgcode
     const nvimgcodecCodeStreamDesc_t** css, int batch_size, const nvimgcodecDecodeParams_t* params, int)
 {
     try {
-        return reinterpret_cast<DecoderImpl*>(decoder)->decode_batch(images, css, batch_size, 0, params && params->apply_exif_orientation);
+        return reinterpret_cast<DecoderImpl*>(decoder)->decode_batch(images, css, batch_size, true, params && params->apply_exif_orientation);
     } catch (...) {
         for (int i = 0; i < batch_size; ++i)
             images[i]->imageReady(images[i]->instance, NVIMGCODEC_PROCESSING_STATUS_FAIL);

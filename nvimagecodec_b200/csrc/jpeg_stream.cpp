@@ -1,6 +1,8 @@
 // Host marker walk + Huffman lookup-table construction (see jpeg_stream.h).
 #include "jpeg_stream.h"
 
+#include <string>
+
 #include <algorithm>
 #include <cstring>
 
@@ -430,26 +432,24 @@ void build_huff_table(const HuffSpec& spec, bool is_dc, HuffTableDev* out)
     }
 }
 
-uint64_t hash_huff_set(const StreamHeader& hdr)
+// Canonical byte string of the four table specs an image uses (presence, code-length counts, the symbols
+// those counts cover): equal strings <=> equal device tables, so it is the cache key itself -- a hash of it
+// alone could be made to collide by a crafted DHT and would decode a neighbour with the wrong tables.
+void huff_set_key(const StreamHeader& hdr, std::string* key)
 {
-    uint64_t hsh = 1469598103934665603ull;
-    auto mix = [&](const uint8_t* p, size_t n) {
-        for (size_t i = 0; i < n; ++i) {
-            hsh ^= p[i];
-            hsh *= 1099511628211ull;
-        }
-    };
+    key->clear();
     for (int cls = 0; cls < 2; ++cls)
         for (int id = 0; id < 2; ++id) {
             const HuffSpec& s = hdr.huff[cls][id];
-            const uint8_t tag = s.present ? 1 : 0;
-            mix(&tag, 1);
-            if (s.present) {
-                mix(s.bits, 17);
-                mix(s.vals, 256);
-            }
+            key->push_back(s.present ? char(1) : char(0));
+            if (!s.present)
+                continue;
+            int n = 0;
+            for (int l = 1; l <= 16; ++l)
+                n += s.bits[l];
+            key->append(reinterpret_cast<const char*>(s.bits + 1), 16);
+            key->append(reinterpret_cast<const char*>(s.vals), size_t(n > 256 ? 256 : n));
         }
-    return hsh;
 }
 
 void build_huff_set(const StreamHeader& hdr, HuffSetDev* out)

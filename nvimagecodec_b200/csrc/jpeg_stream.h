@@ -6,6 +6,7 @@
 #pragma once
 #include <cstddef>
 #include <cstdint>
+#include <string>
 
 namespace b200jpeg {
 
@@ -65,7 +66,7 @@ struct alignas(16) HuffSetDev {
 };
 
 void build_huff_table(const HuffSpec& spec, bool is_dc, HuffTableDev* out);
-uint64_t hash_huff_set(const StreamHeader& hdr);
+void huff_set_key(const StreamHeader& hdr, std::string* key); // canonical bytes of the table specs: the cache key
 void build_huff_set(const StreamHeader& hdr, HuffSetDev* out);
 
 } // namespace b200jpeg

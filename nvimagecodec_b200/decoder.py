@@ -41,14 +41,20 @@ class Batch:
 
 class Decoder:
     # Same default as the reference's Python binding (python/decoder.cpp:492).
-    def __init__(self, device_id=None, options=":fancy_upsampling=0"):
+    def __init__(self, device_id=None, options=":fancy_upsampling=0", allocators=None):
+        """allocators: an optional ``_lib.Allocators`` (the caller's device / pinned allocation callbacks, the C-ABI
+        form of nvimgcodecExecutionParams_t::device_allocator / pinned_allocator); kept alive with the decoder."""
         self._L = _lib.load()
         if not torch.cuda.is_available():
             raise DecodeError("nvimagecodec_b200 needs a CUDA device (there is no CPU fallback)")
         self.device_id = torch.cuda.current_device() if device_id is None else int(device_id)
         self.device = torch.device("cuda", self.device_id)
         h = ctypes.c_void_p()
-        rc = self._L.b200jpegCreate(ctypes.byref(h), self.device_id, (options or "").encode())
+        self._allocators = allocators
+        if allocators is None:
+            rc = self._L.b200jpegCreate(ctypes.byref(h), self.device_id, (options or "").encode())
+        else:
+            rc = self._L.b200jpegCreateEx(ctypes.byref(h), self.device_id, (options or "").encode(), ctypes.byref(allocators))
         if rc != _lib.OK:
             raise DecodeError(f"b200jpegCreate failed: {_lib.STATUS_NAMES[rc]}")
         self._h = h

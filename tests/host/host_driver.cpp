@@ -10,6 +10,12 @@
 //   decoders -- ours vs the reference's nvjpeg_ext -- through the very same framework path).
 //   manifest line: <jpeg path> <I_RGB|I_BGR|P_RGB|P_BGR|I_Y> <y0> <x0> <y1> <x1> <device|host>
 //                  (all-zero ROI = whole image)
+//   environment:
+//     HOST_DRIVER_CRC=<k>        write the CRC-32 (zlib polynomial) of every k-th output into status.txt (0 for the others)
+//                                instead of dumping the raw pixels (large batches)
+//     HOST_DRIVER_COUNT_ALLOC=1  hand the decoder counting device / pinned allocators through nvimgcodecExecutionParams_t
+//                                (include/nvimgcodec.h:1095-1096) and print how often each was called
+//     HOST_DRIVER_PINNED=1       host output buffers are pinned (cudaMallocHost) instead of malloc'ed
 #include <cuda_runtime_api.h>
 #include <nvimgcodec.h>
 
@@ -32,6 +38,51 @@
         }                                                                         \
     } while (0)
 
+static uint32_t crc32_of(const unsigned char* p, size_t n)
+{
+    static uint32_t table[256];
+    static bool init = false;
+    if (!init) {
+        for (uint32_t i = 0; i < 256; ++i) {
+            uint32_t c = i;
+            for (int k = 0; k < 8; ++k)
+                c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+            table[i] = c;
+        }
+        init = true;
+    }
+    uint32_t c = 0xFFFFFFFFu;
+    for (size_t i = 0; i < n; ++i)
+        c = table[(c ^ p[i]) & 0xFF] ^ (c >> 8);
+    return c ^ 0xFFFFFFFFu;
+}
+
+// counting allocators (signatures: include/nvimgcodec.h:246-281)
+static long g_dev_malloc = 0, g_dev_free = 0, g_pin_malloc = 0, g_pin_free = 0;
+static long long g_dev_bytes = 0, g_dev_freed = 0;
+static int count_dev_malloc(void*, void** ptr, size_t size, cudaStream_t)
+{
+    ++g_dev_malloc;
+    g_dev_bytes += (long long)size;
+    return cudaMalloc(ptr, size) == cudaSuccess ? 0 : 1;
+}
+static int count_dev_free(void*, void* ptr, size_t size, cudaStream_t)
+{
+    ++g_dev_free;
+    g_dev_freed += (long long)size;
+    return cudaFree(ptr) == cudaSuccess ? 0 : 1;
+}
+static int count_pin_malloc(void*, void** ptr, size_t size, cudaStream_t)
+{
+    ++g_pin_malloc;
+    return cudaMallocHost(ptr, size) == cudaSuccess ? 0 : 1;
+}
+static int count_pin_free(void*, void* ptr, size_t, cudaStream_t)
+{
+    ++g_pin_free;
+    return cudaFreeHost(ptr) == cudaSuccess ? 0 : 1;
+}
+
 struct Item {
     std::string path, fmt, where;
     int y0, x0, y1, x1;
@@ -52,6 +103,10 @@ int main(int argc, char** argv)
     const int repeat = argc > 5 ? std::atoi(argv[5]) : 0;
     const std::string backend = argc > 6 ? argv[6] : "any";
     const bool apply_exif = argc > 7 && std::string(argv[7]) == "exif";
+    const bool crc_mode = std::getenv("HOST_DRIVER_CRC") != nullptr;
+    const int crc_every = crc_mode ? std::max(1, std::atoi(std::getenv("HOST_DRIVER_CRC"))) : 1;
+    const bool count_alloc = std::getenv("HOST_DRIVER_COUNT_ALLOC") != nullptr;
+    const bool pinned_out = std::getenv("HOST_DRIVER_PINNED") != nullptr;
     std::vector<Item> items;
     {
         std::ifstream f(manifest);
@@ -92,6 +147,14 @@ int main(int argc, char** argv)
                                         : NVIMGCODEC_BACKEND_KIND_CPU_ONLY;
         ep.num_backends = 1;
         ep.backends = &be;
+    }
+    nvimgcodecDeviceAllocator_t dev_alloc{NVIMGCODEC_STRUCTURE_TYPE_DEVICE_ALLOCATOR, sizeof(nvimgcodecDeviceAllocator_t), nullptr,
+        count_dev_malloc, count_dev_free, nullptr, 0};
+    nvimgcodecPinnedAllocator_t pin_alloc{NVIMGCODEC_STRUCTURE_TYPE_PINNED_ALLOCATOR, sizeof(nvimgcodecPinnedAllocator_t), nullptr,
+        count_pin_malloc, count_pin_free, nullptr, 0};
+    if (count_alloc) {
+        ep.device_allocator = &dev_alloc;
+        ep.pinned_allocator = &pin_alloc;
     }
     nvimgcodecDecoder_t decoder = nullptr;
     CHECK(nvimgcodecDecoderCreate(instance, &decoder, &ep, options));
@@ -149,7 +212,10 @@ int main(int argc, char** argv)
             it.out_bytes += size_t(it.w) * channels * it.h;
         }
         if (it.where == "host") {
-            it.buffer = std::malloc(it.out_bytes);
+            if (pinned_out)
+                cudaMallocHost(&it.buffer, it.out_bytes);
+            else
+                it.buffer = std::malloc(it.out_bytes);
             info.buffer_kind = NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_HOST;
         } else {
             cudaMalloc(&it.buffer, it.out_bytes);
@@ -199,19 +265,28 @@ int main(int argc, char** argv)
         double mpix = 0;
         for (int i = 0; i < n; ++i)
             mpix += double(items[i].w) * items[i].h / 1e6;
-        std::printf("BENCH images=%d ok=%d repeat=%d seconds=%.6f images_per_s=%.1f mpix_per_s=%.1f\n", n, ok, repeat, dt, n * repeat / dt,
-            mpix * repeat / dt);
+        std::printf("BENCH images=%d ok=%d repeat=%d seconds=%.6f images_per_s=%.1f mpix_per_s=%.1f ms_per_batch=%.3f\n", n, ok, repeat, dt,
+            n * repeat / dt, mpix * repeat / dt, dt / repeat * 1e3);
     }
 
     std::ofstream sf(out_dir + "/status.txt");
     for (int i = 0; i < n; ++i) {
         Item& it = items[i];
-        sf << int(st[i]) << " " << it.w << " " << it.h << "\n";
+        sf << int(st[i]) << " " << it.w << " " << it.h;
+        if (crc_mode && i % crc_every != 0) {
+            sf << " 0\n";
+            continue;
+        }
         std::vector<unsigned char> host(it.out_bytes);
         if (it.where == "host")
             std::memcpy(host.data(), it.buffer, it.out_bytes);
         else
             cudaMemcpy(host.data(), it.buffer, it.out_bytes, cudaMemcpyDeviceToHost);
+        if (crc_mode) {
+            sf << " " << crc32_of(host.data(), host.size()) << "\n";
+            continue;
+        }
+        sf << "\n";
         std::ofstream o(out_dir + "/" + std::to_string(i) + ".raw", std::ios::binary);
         o.write(reinterpret_cast<const char*>(host.data()), std::streamsize(host.size()));
     }
@@ -221,13 +296,19 @@ int main(int argc, char** argv)
         if (streams[i] != parents[i])
             nvimgcodecCodeStreamDestroy(streams[i]);
         nvimgcodecCodeStreamDestroy(parents[i]);
-        if (items[i].where == "host")
-            std::free(items[i].buffer);
-        else
+        if (items[i].where == "host") {
+            if (pinned_out)
+                cudaFreeHost(items[i].buffer);
+            else
+                std::free(items[i].buffer);
+        } else
             cudaFree(items[i].buffer);
     }
     nvimgcodecDecoderDestroy(decoder);
     nvimgcodecInstanceDestroy(instance);
+    if (count_alloc)
+        std::printf("ALLOC device_malloc=%ld device_free=%ld device_bytes=%lld device_bytes_freed=%lld pinned_malloc=%ld pinned_free=%ld\n", g_dev_malloc,
+            g_dev_free, g_dev_bytes, g_dev_freed, g_pin_malloc, g_pin_free);
     std::printf("decoded %d images through nvimgcodecDecoderDecode\n", n);
     return 0;
 }

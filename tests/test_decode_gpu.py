@@ -492,3 +492,29 @@ def test_three_scans_of_one_component_each(decoder_cls, dec_fancy, dec_plain):
     outs = dec_fancy.decode([bytes(bad), srcs[1], origs[0]], "I_RGB")
     assert dec_fancy.last_status[1:] == [_lib.OK, _lib.OK]
     assert np.array_equal(outs[2].cpu().numpy(), oracle.decode(origs[0], oracle.FMT_I_RGB, True))
+
+
+def test_huffman_set_cache_crossing_its_limit(decoder_cls):
+    """Optimised-Huffman streams carry their own table sets.  More distinct sets than the decoder's cache holds (4096), in
+    batches that cross the limit: the sets of a batch stay valid while it is being built (eviction only between batches),
+    and equal-looking sets are told apart by content, not by a hash."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    rng = np.random.default_rng(77)
+    dec = decoder_cls(0, options=":fancy_upsampling=1")
+    seen = set()
+    for rnd in range(4):
+        srcs = []
+        for k in range(1300):
+            img = rng.integers(0, 256, size=(16, 24, 3), dtype=np.uint8)
+            img[:, : int(rng.integers(1, 24))] //= int(rng.integers(1, 9))
+            srcs.append(corpus.encode(img, int(rng.integers(40, 99)), ["420", "444", "422"][k % 3], optimize=True))
+        for d in srcs:
+            i = d.index(b"\xff\xc4")
+            seen.add(d[i:d.index(b"\xff\xda")])
+        outs = dec.decode(srcs, "I_RGB")
+        assert dec.last_status == [_lib.OK] * len(srcs)
+        for j in list(range(0, len(srcs), 53)) + [len(srcs) - 1]:
+            assert np.array_equal(outs[j].cpu().numpy(), oracle.decode(srcs[j], oracle.FMT_I_RGB, True)), (rnd, j)
+    assert len(seen) > 4096 + 600, len(seen)  # the cache limit was crossed inside a batch
+    dec.close()
