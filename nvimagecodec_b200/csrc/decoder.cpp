@@ -317,6 +317,7 @@ void parse_input(const void* data, size_t len, ParsedInput* out)
 {
     out->scans.reset();
     out->multi_status = kStreamOk;
+    out->frame = StreamHeader(); // entries are reused across batches: nothing of the previous stream (restart interval, tables) may survive
     out->status = data ? parse_stream(static_cast<const uint8_t*>(data), len, &out->frame) : kStreamNotJpeg;
     if (out->status == kStreamMultiScan) {
         out->scans.reset(new StreamHeader[3]);
