@@ -7,7 +7,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb200jpeg_ext.so")
+# B200JPEG_LIB: another build of the same library (kernel experiments: variants are compared in one GPU session)
+LIB_PATH = os.environ.get("B200JPEG_LIB") or os.path.join(_HERE, "lib", "libb200jpeg_ext.so")
 
 OK, ERR_ARG, ERR_NOT_JPEG, ERR_UNSUPPORTED, ERR_CORRUPT, ERR_CUDA, ERR_STATE, ERR_TOO_LARGE = range(8)
 STATUS_NAMES = ["OK", "ERR_ARG", "ERR_NOT_JPEG", "ERR_UNSUPPORTED", "ERR_CORRUPT", "ERR_CUDA", "ERR_STATE", "ERR_TOO_LARGE"]

@@ -17,7 +17,7 @@ namespace b200jpeg {
 
 namespace {
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-const char* kStageNames[] = {"scan(K0)", "huff_sync(K1)", "verify_scan(K2)", "huff_write(K3)", "dc_scan(K3b)", "idct(K4a)", "color(K4b)"};
+const char* kStageNames[] = {"scan(K0)", "huff_sync(K1)", "verify_scan(K2)", "huff_write(K3)", "dc_scan(K3b)", "idct(K4a)", "color(K4b)", "pixels(K4)"};
 } // namespace
 
 // ---- memory: the host's allocators when it supplied some, else stream-ordered allocation (cudaMallocAsync) where the
@@ -238,6 +238,8 @@ Options parse_options(const char* options, const char* decoder_id)
             o.lanes = std::min(8, std::max(1, std::atoi(value.c_str())));
         else if (name == "chunk_images")
             o.chunk_images = std::max(1, std::atoi(value.c_str()));
+        else if (name == "fused_pixels")
+            o.fused_pixels = std::atoi(value.c_str()) != 0;
         else if (name == "sync_finish")
             o.sync_finish = std::atoi(value.c_str()) != 0;
         else if (name == "host_threads")
@@ -514,6 +516,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         ImageDev im;
         std::memset(&im, 0, sizeof(im));
         uint32_t gate[3] = {0, 0, 0};
+        const size_t plane_bytes_before = plane_bytes;
         im.raw_off = raw_bytes;
         im.raw_len = uint32_t(hd.scan_length);
         raw_bytes += align_up(hd.scan_length, 16) + 16;
@@ -637,6 +640,26 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             if (role == kChild)
                 im.n_color_cta_x = im.n_color_cta_y = 0; // planes only
         }
+        // Fused pixel kernel (K4) for the specialised sampling modes: tiles over the MCUs the region touches.  Strip width and
+        // band height are set for the whole batch once every image is known (below); here only the MCU window.
+        {
+            bool fused = opt_.fused_pixels && role == kNormal && im.color_mode >= 1 && o.orientation <= 1;
+            for (int c = 0; c < hd.ncomp; ++c)
+                fused = fused && hd.h[c] <= 2 && hd.v[c] <= 2;
+            if (fused) {
+                const int mcu_w = 8 * hd.hmax;
+                im.px_mcu_col_lo = uint16_t(x0 / mcu_w);
+                im.px_mcu_col_hi = uint16_t((x1 + mcu_w - 1) / mcu_w);
+                im.px_mcu_row_lo = uint16_t(y0 / mcu_h);
+                im.px_mcu_row_hi = uint16_t((y1 + mcu_h - 1) / mcu_h);
+                im.px_n_cta = 1; // marks the image; the real count follows
+                // the idct / color kernels and the plane arena are not needed
+                plane_bytes = plane_bytes_before;
+                n_idct -= im.n_idct_cta;
+                im.n_idct_cta = 0;
+                im.n_color_cta_x = im.n_color_cta_y = 0;
+            }
+        }
         n_color += im.n_color_cta_x * im.n_color_cta_y;
         HostOut ho{nullptr, 0, obytes, stride, tight, (planar ? 3 : 1) * out_h};
         if (role == kChild) {
@@ -702,6 +725,58 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     algo_bytes_ = comp_bytes_ + 4 * n_coefs_ + out_bytes_;
     const int nd = int(imgs_.size());
 
+    // ---- tiles of the fused pixel kernel.  Strips are at most 2048 luma pixels wide (so that the component tiles of an MCU
+    // row fit in shared memory with two or three CTAs per SM), narrower when the batch is too small to fill the GPU
+    // otherwise; bands are as tall as still leaves every SM a few CTAs (tall bands amortise the extra chroma rows the
+    // vertical triangle filter needs at a band's top and bottom).
+    uint32_t n_px = 0;
+    size_t px_smem = 0;
+    {
+        auto tiles = [&](int strip_px_max, long* rows_total) {
+            *rows_total = 0;
+            for (ImageDev& im : imgs_) {
+                if (!im.px_n_cta)
+                    continue;
+                const int mcu_w = 8 * im.hmax;
+                const int cols = im.px_mcu_col_hi - im.px_mcu_col_lo;
+                int per_strip_max = std::max(1, strip_px_max / mcu_w);
+                const int mode = im.color_mode;
+                int hh[3] = {im.h[0], im.h[1], im.h[2]}, vv[3] = {im.v[0], im.v[1], im.v[2]};
+                // three CTAs per SM: at most 72 KB of tiles each
+                while (per_strip_max > 1 &&
+                       pixels_tile_smem(mode == 1 ? 1 : 3, hh, vv, im.vmax, std::min(per_strip_max, cols), mode == 6 || mode == 8, mode == 7 || mode == 8) > 72 * 1024)
+                    per_strip_max = (per_strip_max + 1) / 2;
+                const int n_strips = (cols + per_strip_max - 1) / per_strip_max;
+                im.px_n_strips = uint16_t(n_strips);
+                im.px_strip_mcus = uint16_t((cols + n_strips - 1) / n_strips);
+                *rows_total += long(n_strips) * (im.px_mcu_row_hi - im.px_mcu_row_lo);
+            }
+        };
+        long rows_total = 0;
+        tiles(2048, &rows_total);
+        const long fill = 148 * 4;
+        if (rows_total > 0 && rows_total < fill)
+            tiles(rows_total >= fill / 4 ? 1024 : 512, &rows_total);
+        const int band = int(std::max<long>(1, std::min<long>(64, rows_total / (fill * 3))));
+        for (ImageDev& im : imgs_) {
+            if (!im.px_n_cta)
+                continue;
+            const int rows = im.px_mcu_row_hi - im.px_mcu_row_lo;
+            const int n_bands = (rows + band - 1) / band;
+            im.px_band_rows = uint16_t((rows + n_bands - 1) / n_bands);
+            im.px_n_bands = uint16_t((rows + im.px_band_rows - 1) / im.px_band_rows);
+            im.px_cta_off = n_px;
+            im.px_n_cta = uint32_t(im.px_n_bands) * im.px_n_strips;
+            n_px += im.px_n_cta;
+            const int mode = im.color_mode;
+            const bool fancy_h = mode == 6 || mode == 8, fancy_v = mode == 7 || mode == 8;
+            int hh[3] = {im.h[0], im.h[1], im.h[2]}, vv[3] = {im.v[0], im.v[1], im.v[2]};
+            px_smem = std::max(px_smem, pixels_tile_smem(mode == 1 ? 1 : 3, hh, vv, im.vmax, im.px_strip_mcus, fancy_h, fancy_v));
+        }
+        if (px_smem > kPixelsMaxSmem)
+            return fail(B200JPEG_ERR_STATE, "pixel tile exceeds its shared-memory budget");
+    }
+
     // ---- upload arena: descriptors | cta->image maps | huffman sets | raw scan bytes
     size_t off = 0;
     const size_t off_img = off;
@@ -718,6 +793,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     off = align_up(off + 4ull * n_idct, 256);
     const size_t off_color = off;
     off = align_up(off + 4ull * n_color, 256);
+    const size_t off_px = off;
+    off = align_up(off + 4ull * n_px, 256);
     const size_t off_gate = off;
     off = align_up(off + 12ull * nd, 256);
     const size_t off_huff = off;
@@ -766,6 +843,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     uint32_t* dc_img = reinterpret_cast<uint32_t*>(up + off_dc);
     uint32_t* idct_img = reinterpret_cast<uint32_t*>(up + off_idct);
     uint32_t* color_img = reinterpret_cast<uint32_t*>(up + off_color);
+    uint32_t* px_img = reinterpret_cast<uint32_t*>(up + off_px);
     // Bitstreams that already sit in pinned / registered host memory are copied from where they lie when they are big
     // enough to be worth a copy of their own; everything else is gathered into the pinned staging block (one big copy).
     // Whether the sources are pinned is asked once per batch (the pipeline asks once per call), not per image.
@@ -786,6 +864,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         std::fill(dc_img + im.dc_cta_off, dc_img + im.dc_cta_off + im.n_dc_cta, uint32_t(d));
         std::fill(idct_img + im.idct_cta_off, idct_img + im.idct_cta_off + im.n_idct_cta, uint32_t(d));
         std::fill(color_img + im.color_cta_off, color_img + im.color_cta_off + im.n_color_cta_x * im.n_color_cta_y, uint32_t(d));
+        std::fill(px_img + im.px_cta_off, px_img + im.px_cta_off + im.px_n_cta, uint32_t(d));
         if (sources_pinned && im.raw_len >= (uint32_t(opt_.direct_kb) << 10))
             direct[d] = 1;
         else
@@ -868,6 +947,9 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.dc_cta_img = reinterpret_cast<const uint32_t*>(dv + off_dc);
     bd_.idct_cta_img = reinterpret_cast<const uint32_t*>(dv + off_idct);
     bd_.color_cta_img = reinterpret_cast<const uint32_t*>(dv + off_color);
+    bd_.px_cta_img = reinterpret_cast<const uint32_t*>(dv + off_px);
+    bd_.n_px_cta = int(n_px);
+    bd_.px_smem = uint32_t(px_smem);
     bd_.gate = reinterpret_cast<const uint32_t*>(dv + off_gate);
     bd_.n_multi = 0;
     for (const ImageDev& im : imgs_)
@@ -936,8 +1018,8 @@ int Decoder::execute(cudaStream_t stream)
     cudaMemcpyAsync(state_host_.ptr, bd_.state, sizeof(ImageState) * bd_.n_images, cudaMemcpyDeviceToHost, side_stream_);
     cudaEventRecord(entropy_event_, side_stream_);
     mark(5, stream);
-    launches_ += launch_pixels(false, stream);
-    mark(7, stream);
+    launches_ += run_pixel_stage(false, stream);
+    mark(8, stream);
     ev_recorded_ = profiling_ && ev_valid_;
     last_stream_ = stream;
     if (!cuda_ok(cudaGetLastError(), "kernel launch"))
@@ -945,12 +1027,15 @@ int Decoder::execute(cudaStream_t stream)
     return B200JPEG_OK;
 }
 
-int Decoder::launch_pixels(bool redo_only, cudaStream_t stream)
+int Decoder::run_pixel_stage(bool redo_only, cudaStream_t stream)
 {
     int n = launch_idct(bd_, redo_only, stream);
     if (!redo_only)
         mark(6, stream);
     n += launch_color(bd_, redo_only, stream);
+    if (!redo_only)
+        mark(7, stream);
+    n += launch_pixels(bd_, redo_only, stream);
     return n;
 }
 
@@ -1040,7 +1125,7 @@ int Decoder::finish_wait(int* status, cudaStream_t stream)
         }
         launches_ += launch_write(bd_, true, stream);
         launches_ += launch_dc_scan(bd_, true, stream);
-        launches_ += launch_pixels(true, stream);
+        launches_ += run_pixel_stage(true, stream);
         if (!read_states())
             return B200JPEG_ERR_CUDA;
         bool any_host = false;

@@ -80,6 +80,7 @@ struct Options {
     int lanes = 6;                // pipeline lanes (decoder + stream each) the chunks rotate over
     int chunk_images = 64;        // ... or this many images, whichever comes first
     int host_threads = 0;         // helper threads for marker walks / staging (0 = by the CPUs this process may run on, at most 8)
+    bool fused_pixels = true;     // IDCT + upsampling + colour in one kernel (0: the separate idct / color kernels for every image; experiments)
     bool sync_finish = false;     // Finish / DecodeBatch wait for the pixel kernels too, not only for the statuses
     int max_arena_mb = 32768;     // refuse (ERR_TOO_LARGE) images whose coefficient + plane arenas would exceed this many MiB
 };
@@ -126,7 +127,7 @@ class Decoder {
     bool cuda_ok(cudaError_t e, const char* what);
     void mark(int stage, cudaStream_t s);
     void parallel_for(int n, void (*fn)(int, void*), void* arg);
-    int launch_pixels(bool redo_only, cudaStream_t stream);
+    int run_pixel_stage(bool redo_only, cudaStream_t stream);
     bool copy_host_output(int d, cudaStream_t stream);
 
     int device_;
@@ -176,7 +177,7 @@ class Decoder {
 
     // profiling
     bool profiling_ = false;
-    static constexpr int kStages = 7;
+    static constexpr int kStages = 8;
     cudaEvent_t ev_[kStages + 1] = {};
     bool ev_valid_ = false;
     bool ev_recorded_ = false;

@@ -1803,6 +1803,8 @@ __global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev b
     }
 }
 
+#include "pixels.cuh"
+
 constexpr size_t kSyncSmem = kSyncPairOffset + 2 * sizeof(HuffTableDev);
 constexpr size_t kWriteSmem = sizeof(HuffSetDev) + sizeof(BlockTable);
 
@@ -1884,6 +1886,34 @@ int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s)
     }
     color_kernel<<<b.n_color_cta, kColorTx * kColorTy, 0, s>>>(b, redo_only ? 1 : 0);
     return launched;
+}
+
+// Shared memory of one tile of the fused pixel kernel (the same arithmetic as pixels_kernel's set-up).
+size_t pixels_tile_smem(int ncomp, const int* h, const int* v, int vmax, int strip_mcus, bool fancy_h, bool fancy_v)
+{
+    (void)vmax;
+    const int carry = fancy_v ? 2 : 0;
+    size_t total = 0;
+    for (int c = 0; c < ncomp; ++c) {
+        const int cols = (strip_mcus + ((c > 0 && fancy_h) ? 2 : 0)) * h[c];
+        total += size_t(carry + 8 * v[c]) * size_t(cols * 8 + 16);
+    }
+    return (total + 15) / 16 * 16;
+}
+
+int launch_pixels(const BatchDev& b, bool redo_only, cudaStream_t s)
+{
+    if (b.n_px_cta == 0)
+        return 0;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        cudaFuncSetAttribute(pixels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kPixelsMaxSmem));
+        attr_set[dev] = true;
+    }
+    pixels_kernel<<<b.n_px_cta, kPxThreads, b.px_smem, s>>>(b, redo_only ? 1 : 0);
+    return 1;
 }
 
 } // namespace b200jpeg

@@ -70,6 +70,11 @@ struct ImageDev {
     uint32_t idct_cta_off, n_idct_cta;
     uint32_t color_cta_off, n_color_cta_x, n_color_cta_y;
     uint32_t color_cta_x_rcp;       // ceil(2^32 / n_color_cta_x): cta -> (row, column) without a division
+    // fused pixel kernel (K4): tiles = strips of MCU columns x bands of MCU rows over the MCUs the region of interest touches;
+    // px_n_cta == 0: the image goes through the idct + color kernels instead (generic sampling, EXIF orientation, three-scan streams)
+    uint32_t px_cta_off, px_n_cta;
+    uint16_t px_strip_mcus, px_n_strips, px_band_rows, px_n_bands;
+    uint16_t px_mcu_col_lo, px_mcu_col_hi, px_mcu_row_lo, px_mcu_row_hi;
     uint32_t plane_stride_px[3];    // row pitch of each MCU-padded component plane
     uint16_t comp_w[3], comp_h[3];  // real component size ceil(W*h/hmax) x ceil(H*v/vmax): where edges replicate
     uint16_t width, height, mcus_x, mcus_y;
@@ -124,6 +129,9 @@ struct BatchDev {
     int4* dc_sum;                 // K3b: per chunk (reset seen, DC sums of the three components)
     const uint32_t* idct_cta_img;
     const uint32_t* color_cta_img;
+    const uint32_t* px_cta_img;   // fused pixel kernel CTA -> image
+    int n_px_cta;
+    uint32_t px_smem;             // dynamic shared memory of the fused pixel kernel: the largest tile of the batch
     const uint32_t* gate;         // three image indices per image, see ImageDev::multi
     int n_tiles, n_seq, n_wseq, n_sub, n_dc_cta, n_idct_cta, n_color_cta;
     int n_multi;            // images with ImageDev::multi set
@@ -140,5 +148,8 @@ int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s);  // K3
 int launch_dc_scan(const BatchDev& b, bool redo_only, cudaStream_t s); // K3b
 int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s);   // K4a
 int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s);  // K4b
+int launch_pixels(const BatchDev& b, bool redo_only, cudaStream_t s); // K4 fused (IDCT + upsampling + colour)
+size_t pixels_tile_smem(int ncomp, const int* h, const int* v, int vmax, int strip_mcus, bool fancy_h, bool fancy_v); // its shared memory for one tile shape
+constexpr size_t kPixelsMaxSmem = 96 * 1024; // tiles are cut so that two or three CTAs fit an SM
 
 } // namespace b200jpeg

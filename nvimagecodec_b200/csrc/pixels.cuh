@@ -1,0 +1,516 @@
+// K4 (fused): dequantise + ISLOW IDCT -> component tiles in shared memory -> chroma upsampling + YCbCr->RGB ->
+// 128-bit stores into the caller's buffer.  Included by kernels.cu (inside its anonymous namespace, after the
+// IDCT / colour helpers).
+//
+// Replaces the scanline loop of the reference's CPU path (extensions/libjpeg_turbo/jpeg_mem.cpp:311-379 driving
+// libjpeg-turbo's jidctint / jdsample / jdcolor); the component planes never leave the SM.
+//
+// One CTA owns a tile: a strip of MCU columns x a band of MCU rows of one image, and walks the band top to bottom, one
+// MCU row per step:
+//   phase A  every thread takes 8x8 blocks of that MCU row: coefficients -> registers -> IDCT -> 8-byte row stores
+//            into the component tiles in shared memory;
+//   phase B  every thread takes units of 16 pixels x (1 or 2) rows: luma and chroma from shared memory, triangle or box
+//            upsampling, colour transform, three 16-byte stores per row (interleaved RGB).
+// The vertical triangle filter of 4:2:0 / 4:4:0 looks one chroma row up and down, so with it the output trails the
+// IDCT by one chroma row (two luma rows): the last two rows of every tile are carried over to the next step, and a
+// band starts / ends with a step that only transforms the one chroma row its first / last output rows look at (a
+// one-row IDCT: the column pass computes one output per column).  The horizontal filter looks one chroma sample left
+// and right: a strip keeps the chroma of one more MCU column on each side.
+#pragma once
+
+constexpr int kPxThreads = 256;
+constexpr int kPxUnit = 16; // pixels per thread and row in phase B
+
+struct PxComp {
+    int bx0, nbx;     // block columns held: [bx0, bx0 + nbx)
+    int lh, lv;       // log2 of the sampling factors
+    int off, stride;  // plane in shared memory: byte offset, bytes per row
+    int first;        // block-in-MCU index of the component's first block
+};
+
+struct PxTile {
+    PxComp c[3];
+    int ncomp;        // components held (1: luma only)
+    int mx0, mx1;     // MCU columns of the strip
+    int r_lo, r_hi;   // MCU rows of the band
+    int lag;          // 1: the output trails the IDCT by one unit row (vertical triangle filter)
+    int carry;        // rows carried over from the previous MCU row at the top of every plane (2 * lag)
+    int urows;        // unit rows per MCU row (chroma rows per MCU row; luma rows when VX == 1)
+};
+
+// Coefficients of one block (dense layout: 16-byte groups in zig-zag order, a mask of the groups K3 wrote, DC in the record).
+__device__ __forceinline__ void px_fetch_block(const BatchDev& bd, const ImageDev& im, uint32_t blk_in_image, int32_t (&zz)[64])
+{
+    const size_t blk = im.coef_off / 64 + blk_in_image;
+    const uint4* s4 = reinterpret_cast<const uint4*>(bd.coef) + blk * 8;
+    const uint32_t rec = __ldg(bd.blkrec + blk);
+    const uint32_t mask = rec & 0xFFu;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if ((mask >> i) & 1u)
+            v = __ldg(s4 + i);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            zz[i * 8 + 2 * j] = int32_t(int16_t(w[j] & 0xFFFFu));
+            zz[i * 8 + 2 * j + 1] = int32_t(int16_t(w[j] >> 16));
+        }
+    }
+    zz[0] = int32_t(rec) >> 16;
+}
+
+// kRows: 0 = all eight rows, 1 = only row 7, 2 = only row 0 (the rows a band's first / last step needs); what is not
+// asked for is never computed (everything is unrolled, unused column outputs are dead code).
+template <int kRows>
+__device__ __forceinline__ void px_idct_block(const int32_t (&zz)[64], const uint16_t* __restrict__ q, uint8_t* __restrict__ dst, int stride)
+{
+    constexpr int kZzPos[64] = {0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43, 9, 11, 18, 24,
+        31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60, 21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48,
+        49, 57, 58, 62, 63};
+    int32_t ws[64];
+#pragma unroll
+    for (int x = 0; x < 8; ++x) {
+        int32_t col[8], o[8];
+#pragma unroll
+        for (int y = 0; y < 8; ++y)
+            col[y] = zz[kZzPos[y * 8 + x]] * int32_t(q[y * 8 + x]);
+        idct8<11, 0u>(col[0], col[1], col[2], col[3], col[4], col[5], col[6], col[7], o);
+#pragma unroll
+        for (int y = 0; y < 8; ++y)
+            ws[y * 8 + x] = o[y];
+    }
+#pragma unroll
+    for (int y = 0; y < 8; ++y) {
+        if ((kRows == 1 && y != 7) || (kRows == 2 && y != 0))
+            continue;
+        int32_t o[8];
+        idct8<18, (512u << 18)>(ws[y * 8 + 0], ws[y * 8 + 1], ws[y * 8 + 2], ws[y * 8 + 3], ws[y * 8 + 4], ws[y * 8 + 5], ws[y * 8 + 6], ws[y * 8 + 7], o);
+        uint2 pk;
+        pk.x = range_limit(o[0]) | (range_limit(o[1]) << 8) | (range_limit(o[2]) << 16) | (range_limit(o[3]) << 24);
+        pk.y = range_limit(o[4]) | (range_limit(o[5]) << 8) | (range_limit(o[6]) << 16) | (range_limit(o[7]) << 24);
+        *reinterpret_cast<uint2*>(dst + y * stride) = pk;
+    }
+}
+
+// Phase A of one step: the blocks of MCU row r.  kind 0: every component, all rows; 1: chroma only, last row of the
+// MCU row (the step above a band); 2: chroma only, first row (the step below a band).
+__device__ __noinline__ void px_idct_phase(const BatchDev& bd, const ImageDev& im, const PxTile& T, const uint16_t (*s_q)[64], uint8_t* smem, int r, int kind)
+{
+    int n[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const bool on = c < T.ncomp && (kind == 0 || c > 0);
+        n[c] = on ? (T.c[c].nbx << (kind == 0 ? T.c[c].lv : 0)) : 0;
+    }
+    const int total = n[0] + n[1] + n[2];
+#pragma unroll 1
+    for (int t = threadIdx.x; t < total; t += kPxThreads) {
+        int c = 0, local = t;
+        if (local >= n[0]) {
+            local -= n[0];
+            c = 1;
+            if (local >= n[1]) {
+                local -= n[1];
+                c = 2;
+            }
+        }
+        const PxComp pc = T.c[c];
+        int by = 0; // block row inside the MCU row
+        if (kind == 0) {
+            if (local >= pc.nbx) { // sampling factors are 1 or 2 on this path
+                local -= pc.nbx;
+                by = 1;
+            }
+        } else if (kind == 1) {
+            by = (1 << pc.lv) - 1;
+        }
+        const int bx = pc.bx0 + local;
+        const int mcu = bx >> pc.lh;
+        const uint32_t bim = uint32_t(pc.first + (by << pc.lh) + (bx - (mcu << pc.lh)));
+        const uint32_t blk = (uint32_t(r) * im.mcus_x + uint32_t(mcu)) * im.bpm + bim;
+        int32_t zz[64];
+        px_fetch_block(bd, im, blk, zz);
+        uint8_t* dst = smem + pc.off + (T.carry + by * 8) * pc.stride + local * 8;
+        if (kind == 0)
+            px_idct_block<0>(zz, s_q[c], dst, pc.stride);
+        else if (kind == 1)
+            px_idct_block<1>(zz, s_q[c], dst, pc.stride);
+        else
+            px_idct_block<2>(zz, s_q[c], dst, pc.stride);
+    }
+}
+
+// ---- phase B helpers
+// Output buffers are device memory: say so, the pointer comes out of a descriptor and would otherwise be stored through generically.
+__device__ __forceinline__ void px_stg128(uint8_t* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+{
+    asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(__cvta_generic_to_global(p)), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void px_stg64(uint8_t* p, uint32_t a, uint32_t b)
+{
+    asm volatile("st.global.v2.u32 [%0], {%1, %2};" ::"l"(__cvta_generic_to_global(p)), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ int px_byte(uint32_t w, int k) { return int(__byte_perm(w, 0u, 0x4440 + k)); } // byte k of w
+
+// Chroma samples of one row for eight pixels.  HX == 2: c[0] = left neighbour, c[1..4] = the four samples, c[5] = right
+// neighbour (neighbours clamped to the real component width, where libjpeg's edge formulas replicate); HX == 1: c[0..7].
+// row points at sample column `xorg` of the component; j0 is the first sample's column.
+template <int HX>
+__device__ __forceinline__ void px_load_chroma(const uint8_t* row, int xorg, int j0, int dw, int* c)
+{
+    if (HX == 2) {
+        const uint32_t v = *reinterpret_cast<const uint32_t*>(row + (j0 - xorg));
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            c[1 + k] = px_byte(v, k);
+        c[0] = row[(j0 > 0 ? j0 - 1 : 0) - xorg];
+        c[5] = row[(j0 + 4 < dw ? j0 + 4 : dw - 1) - xorg];
+        if (j0 + 3 > dw - 1) { // the right image edge lies inside these samples: replicate the last real one
+            const int last = row[dw - 1 - xorg];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (j0 + k > dw - 1)
+                    c[1 + k] = last;
+        }
+    } else {
+        const uint2 v = *reinterpret_cast<const uint2*>(row + (j0 - xorg));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            c[k] = px_byte(v.x, k);
+            c[4 + k] = px_byte(v.y, k);
+        }
+    }
+}
+
+// Vertical part of the upsampling for one output row: s[] = what the horizontal part works on.
+//   h2v2 triangle: 3 * cur + nbr (the horizontal part divides by 16); h1v2 triangle: the finished sample;
+//   everything else: the sample itself.
+template <int HX, int VX, bool kFancy>
+__device__ __forceinline__ void px_vertical(const int* cur, const int* nbr, int rr, int* s)
+{
+    constexpr int NC = (HX == 2) ? 6 : 8;
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+        if (VX == 2 && kFancy)
+            s[k] = (HX == 2) ? 3 * cur[k] + nbr[k] : (3 * cur[k] + nbr[k] + 1 + rr) >> 2;
+        else
+            s[k] = cur[k];
+    }
+}
+
+// Horizontal part for the four pixels 4g .. 4g+3 (g = 0, 1) of the eight (jdsample.c).
+template <int HX, int VX, bool kFancy>
+__device__ __forceinline__ void px_horizontal4(const int* s, int g, int* out)
+{
+    if (HX == 2) {
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+            const int k = 2 * g + m + 1; // centre sample
+            if (VX == 2 && kFancy) {
+                const int t = 3 * s[k] + 8;
+                out[2 * m] = (t + s[k - 1]) >> 4;
+                out[2 * m + 1] = (t + s[k + 1] - 1) >> 4;
+            } else if (kFancy) {
+                out[2 * m] = (3 * s[k] + s[k - 1] + 1) >> 2;
+                out[2 * m + 1] = (3 * s[k] + s[k + 1] + 2) >> 2;
+            } else {
+                out[2 * m] = out[2 * m + 1] = s[k];
+            }
+        }
+    } else {
+#pragma unroll
+        for (int m = 0; m < 4; ++m)
+            out[m] = s[4 * g + m];
+    }
+}
+
+// How the three output channels are made from (luma << 16, chroma A, chroma B): channel 0 = y + ka * a,
+// channel 2 = y + kb * b, channel 1 = y + ga * a + gb * b (constants 16 bits up, the -128 and the rounding folded in).
+// RGB order: a = Cr, b = Cb; BGR order: a = Cb, b = Cr -- swapping the planes instead of the results costs nothing per pixel.
+struct PxColor {
+    int ka, ca, kb, cb, ga, gb, cg;
+    int plane_a, plane_b; // component index of chroma A / B
+    int yuv;              // 1: no transform (Y, Cb, Cr as they are)
+    int planar;           // 1: one plane per channel (or the single plane of Y output)
+    int nch;              // planes to write
+};
+
+__device__ __forceinline__ PxColor px_color_setup(int fmt)
+{
+    PxColor k;
+    const bool bgr = (fmt == kFmtIBGR || fmt == kFmtPBGR);
+    constexpr int kRr = 91881, kBb = 116130, kGb = -22554, kGr = -46802;
+    k.ka = bgr ? kBb : kRr;
+    k.kb = bgr ? kRr : kBb;
+    k.ca = 32768 - 128 * k.ka;
+    k.cb = 32768 - 128 * k.kb;
+    k.ga = bgr ? kGb : kGr;
+    k.gb = bgr ? kGr : kGb;
+    k.cg = 32768 - 128 * (kGb + kGr);
+    k.plane_a = bgr ? 1 : 2;
+    k.plane_b = bgr ? 2 : 1;
+    k.yuv = (fmt == kFmtIYUV || fmt == kFmtPYUV) ? 1 : 0;
+    if (k.yuv) {
+        k.plane_a = 1;
+        k.plane_b = 2;
+    }
+    k.planar = (fmt == kFmtY || fmt == kFmtPRGB || fmt == kFmtPBGR || fmt == kFmtPYUV) ? 1 : 0;
+    k.nch = (fmt == kFmtY) ? 1 : 3;
+    return k;
+}
+
+// Stores eight pixels of one output row: half `hf` (0 / 1) of a 16-pixel unit whose first byte lies at `o`.
+// Interleaved: pk[0..5] = the 24 bytes; with `o` 16-byte aligned half 0 goes out as 16 + 8 bytes, half 1 (at o + 24) as
+// 8 + 16 bytes, so that a unit row is two 128-bit and two 64-bit stores.  Planar: pk[2 * ch + 0..1] = the 8 bytes of channel ch.
+// x_lo / x_hi: the part of the eight pixels inside the region of interest (0 / 8 when all of them are).
+__device__ __forceinline__ void px_store_half(const ImageDev& im, const PxColor& K, int ox, int oy, int hf, const uint32_t* pk, int x_lo, int x_hi)
+{
+    const bool full = x_lo == 0 && x_hi == 8;
+    if (K.planar) {
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            if (ch >= K.nch)
+                break;
+            uint8_t* o = im.out + size_t(ch) * im.plane_stride + size_t(oy) * im.row_stride + ox;
+            if (full) {
+                if ((reinterpret_cast<uintptr_t>(o) & 7u) == 0)
+                    px_stg64(o, pk[2 * ch], pk[2 * ch + 1]);
+                else
+                    store_words_any<2>(o, pk + 2 * ch);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    if (i >= x_lo && i < x_hi)
+                        o[i] = uint8_t(pk[2 * ch + (i >> 2)] >> (8 * (i & 3)));
+            }
+        }
+        return;
+    }
+    uint8_t* o = im.out + size_t(oy) * im.row_stride + ptrdiff_t(ox) * 3;
+    if (full) {
+        const uint32_t a = uint32_t(reinterpret_cast<uintptr_t>(o)) & 15u;
+        if (hf == 0 && a == 0) {
+            px_stg128(o, pk[0], pk[1], pk[2], pk[3]);
+            px_stg64(o + 16, pk[4], pk[5]);
+        } else if (hf == 1 && a == 8) {
+            px_stg64(o, pk[0], pk[1]);
+            px_stg128(o + 8, pk[2], pk[3], pk[4], pk[5]);
+        } else {
+            store_words_any<6>(o, pk);
+        }
+    } else {
+#pragma unroll
+        for (int b = 0; b < 24; ++b)
+            if (b >= 3 * x_lo && b < 3 * x_hi)
+                o[b] = uint8_t(pk[b >> 2] >> (8 * (b & 3)));
+    }
+}
+
+// Phase B of one step for one sampling mode.  Unit row m of MCU row r is chroma row (luma row when VX == 1)
+// i = urows * r - lag + m; its luma rows VX * i .. sit at plane rows VX * m .., its chroma rows i - 1, i, i + 1 (clamped
+// to the component's real height, where libjpeg replicates) at plane rows (row) - (urows * r - carry).
+// A thread takes 16 pixels of a row as two halves of eight.
+template <int HX, int VX, bool kFancy, bool kLumaOnly>
+__device__ __forceinline__ void px_color_phase(const ImageDev& im, const PxTile& T, const PxColor& K, const uint8_t* smem, int r, int y_lo, int y_hi)
+{
+    constexpr bool fancy_v = kFancy && VX == 2;
+    constexpr int NC = (HX == 2) ? 6 : 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int X_strip = T.mx0 * (8 << T.c[0].lh);
+    const int strip_px = T.c[0].nbx * 8;
+    const int ucols = (strip_px + kPxUnit - 1) / kPxUnit;
+    const int dw = kLumaOnly ? 0 : int(im.comp_w[1]), dh = kLumaOnly ? 0 : int(im.comp_h[1]);
+    const int crow0 = T.urows * r - T.carry; // chroma row held at plane row 0
+    const int ystride = T.c[0].stride;
+    const uint8_t* p0 = smem + T.c[0].off;
+    const uint8_t* pa = kLumaOnly ? p0 : smem + T.c[K.plane_a].off;
+    const uint8_t* pb = kLumaOnly ? p0 : smem + T.c[K.plane_b].off;
+    const int cstride = kLumaOnly ? 0 : T.c[1].stride;
+    const int cxorg = kLumaOnly ? 0 : T.c[1].bx0 * 8;
+    const int roi_x0 = im.roi_x0, roi_x1 = im.roi_x1, roi_y0 = im.roi_y0;
+#pragma unroll 1
+    for (int m = warp; m < T.urows; m += kPxThreads / 32) {
+        const int i = T.urows * r - T.lag + m;
+        const int y0 = VX * i;
+        if (y0 + VX <= y_lo || y0 >= y_hi)
+            continue;
+#pragma unroll 1
+        for (int ux = lane; ux < ucols; ux += 32) {
+            const int X0 = X_strip + ux * kPxUnit;
+            if (X0 >= roi_x1 || X0 + kPxUnit <= roi_x0)
+                continue;
+#pragma unroll 1
+            for (int rr = 0; rr < VX; ++rr) {
+                const int y = y0 + rr;
+                if (y < y_lo || y >= y_hi)
+                    continue;
+                int nb = i; // the vertical neighbour row (the row itself where no vertical filter applies)
+                if (fancy_v) {
+                    nb = rr == 0 ? i - 1 : i + 1;
+                    nb = nb < 0 ? 0 : (nb > dh - 1 ? dh - 1 : nb);
+                }
+                const uint8_t* yrow = p0 + (VX * m + rr) * ystride + (X0 - X_strip);
+#pragma unroll
+                for (int hf = 0; hf < 2; ++hf) {
+                    const int X = X0 + 8 * hf;
+                    if (X >= roi_x1 || X + 8 <= roi_x0 || X - X_strip >= strip_px)
+                        continue;
+                    const int x_lo = max(roi_x0 - X, 0), x_hi = min(roi_x1 - X, 8);
+                    int sa[NC], sb[NC];
+                    if (!kLumaOnly) {
+                        const int j0 = X / HX;
+                        int cur[NC], nbr[NC];
+                        px_load_chroma<HX>(pa + (i - crow0) * cstride, cxorg, j0, dw, cur);
+                        if (fancy_v)
+                            px_load_chroma<HX>(pa + (nb - crow0) * cstride, cxorg, j0, dw, nbr);
+                        px_vertical<HX, VX, kFancy>(cur, fancy_v ? nbr : cur, rr, sa);
+                        px_load_chroma<HX>(pb + (i - crow0) * cstride, cxorg, j0, dw, cur);
+                        if (fancy_v)
+                            px_load_chroma<HX>(pb + (nb - crow0) * cstride, cxorg, j0, dw, nbr);
+                        px_vertical<HX, VX, kFancy>(cur, fancy_v ? nbr : cur, rr, sb);
+                    }
+                    const uint2 yv = *reinterpret_cast<const uint2*>(yrow + 8 * hf);
+                    const uint32_t yw[2] = {yv.x, yv.y};
+                    uint32_t pk[6];
+#pragma unroll
+                    for (int g = 0; g < 2; ++g) {
+                        uint32_t c0[4], c1[4], c2[4];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            c0[k] = __byte_perm(yw[g], 0u, 0x4044 + 0x100 * k); // luma << 16
+                        if (kLumaOnly) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                c1[k] = c2[k] = c0[k];
+                        } else {
+                            int ua[4], ub[4];
+                            px_horizontal4<HX, VX, kFancy>(sa, g, ua);
+                            px_horizontal4<HX, VX, kFancy>(sb, g, ub);
+                            if (K.yuv) {
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) {
+                                    c1[k] = uint32_t(ua[k]) << 16;
+                                    c2[k] = uint32_t(ub[k]) << 16;
+                                }
+                            } else {
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) {
+                                    const int yk = int(c0[k]);
+                                    c0[k] = uint32_t(__viaddmin_s32_relu(yk, K.ka * ua[k] + K.ca, 0xFFFFFF));
+                                    c1[k] = uint32_t(__viaddmin_s32_relu(yk, K.ga * ua[k] + (K.gb * ub[k] + K.cg), 0xFFFFFF));
+                                    c2[k] = uint32_t(__viaddmin_s32_relu(yk, K.kb * ub[k] + K.cb, 0xFFFFFF));
+                                }
+                            }
+                        }
+                        if (K.planar) {
+                            pk[g] = pack_b2(c0[0], c0[1], c0[2], c0[3]);
+                            pk[2 + g] = pack_b2(c1[0], c1[1], c1[2], c1[3]);
+                            pk[4 + g] = pack_b2(c2[0], c2[1], c2[2], c2[3]);
+                        } else {
+                            pk[3 * g + 0] = pack_b2(c0[0], c1[0], c2[0], c0[1]);
+                            pk[3 * g + 1] = pack_b2(c1[1], c2[1], c0[2], c1[2]);
+                            pk[3 * g + 2] = pack_b2(c2[2], c0[3], c1[3], c2[3]);
+                        }
+                    }
+                    px_store_half(im, K, X - roi_x0, y - roi_y0, hf, pk, x_lo, x_hi);
+                }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kPxThreads, 3) pixels_kernel(BatchDev bd, int redo_only)
+{
+    extern __shared__ uint4 s_px_raw[];
+    __shared__ uint16_t s_q[3][64];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(s_px_raw);
+    const uint32_t cta = blockIdx.x;
+    const uint32_t img = bd.px_cta_img[cta];
+    const ImageDev& im = bd.img[img];
+    const uint32_t flags = bd.state[img].flags;
+    if ((flags & (kFlagDirty | kFlagBadMarker)) || (redo_only && !(flags & kFlagRedo)))
+        return;
+    for (int i = threadIdx.x; i < 3 * 64; i += kPxThreads)
+        s_q[i / 64][i % 64] = im.qt[i / 64][i % 64];
+    // ---- tile geometry (uniform over the CTA; lives in shared memory: the phases index it dynamically)
+    __shared__ PxTile s_tile;
+    if (threadIdx.x == 0) {
+        PxTile& T = s_tile;
+        const int local = int(cta - im.px_cta_off);
+        const int band = local / int(im.px_n_strips), strip = local - band * int(im.px_n_strips);
+        const int mode = im.color_mode; // 1: luma only, 2..5: (hx, vx) = (1,1), (2,1), (1,2), (2,2) replicated, 6..8: 3..5 with the triangle filter
+        const int hx = (mode == 3 || mode == 5 || mode == 6 || mode == 8) ? 2 : 1;
+        const int vx = (mode == 4 || mode == 5 || mode == 7 || mode == 8) ? 2 : 1;
+        const bool fancy_h = (mode == 6 || mode == 8), fancy_v = (mode == 7 || mode == 8);
+        T.ncomp = (mode == 1) ? 1 : 3;
+        T.mx0 = int(im.px_mcu_col_lo) + strip * int(im.px_strip_mcus);
+        T.mx1 = min(T.mx0 + int(im.px_strip_mcus), int(im.px_mcu_col_hi));
+        T.r_lo = int(im.px_mcu_row_lo) + band * int(im.px_band_rows);
+        T.r_hi = min(T.r_lo + int(im.px_band_rows), int(im.px_mcu_row_hi));
+        T.lag = fancy_v ? 1 : 0;
+        T.carry = 2 * T.lag;
+        T.urows = (8 * int(im.vmax)) / vx;
+        int off = 0;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            PxComp& pc = T.c[c];
+            const int cc = c < T.ncomp ? c : 0;
+            pc.lh = 31 - __clz(int(im.h[cc]));
+            pc.lv = 31 - __clz(int(im.v[cc]));
+            pc.first = im.blk_first[cc];
+            const int m0 = (c > 0 && fancy_h) ? max(T.mx0 - 1, 0) : T.mx0;
+            const int m1 = (c > 0 && fancy_h) ? min(T.mx1 + 1, int(im.mcus_x)) : T.mx1;
+            pc.bx0 = m0 << pc.lh;
+            pc.nbx = (m1 - m0) << pc.lh;
+            pc.stride = pc.nbx * 8 + 16; // the padding keeps 16-byte row alignment and staggers the rows over the banks
+            pc.off = off;
+            if (c < T.ncomp)
+                off += (T.carry + (8 << pc.lv)) * pc.stride;
+        }
+        (void)hx;
+    }
+    const PxColor K = px_color_setup(im.fmt);
+    __syncthreads();
+    const PxTile& T = s_tile;
+    const int mcu_h = 8 * int(im.vmax);
+    const int y_lo = max(T.r_lo * mcu_h, int(im.roi_y0)), y_hi = min(T.r_hi * mcu_h, int(im.roi_y1));
+    const int r_first = (T.lag && T.r_lo > 0) ? T.r_lo - 1 : T.r_lo;
+    // with the lag the last unit row of the band is still pending after its last MCU row: one more step, which
+    // transforms the chroma row below it (none at the bottom of the image: the filter replicates there)
+    const int r_last = T.lag ? T.r_hi : T.r_hi - 1;
+#pragma unroll 1
+    for (int r = r_first; r <= r_last; ++r) {
+        const int kind = r < T.r_lo ? 1 : (r >= T.r_hi ? 2 : 0);
+        if (r < int(im.mcus_y))
+            px_idct_phase(bd, im, T, s_q, smem, r, kind);
+        __syncthreads();
+        if (kind != 1) {
+            switch (im.color_mode) {
+            case 1: px_color_phase<1, 1, false, true>(im, T, K, smem, r, y_lo, y_hi); break;
+            case 2: px_color_phase<1, 1, false, false>(im, T, K, smem, r, y_lo, y_hi); break;
+            case 3: px_color_phase<2, 1, false, false>(im, T, K, smem, r, y_lo, y_hi); break;
+            case 4: px_color_phase<1, 2, false, false>(im, T, K, smem, r, y_lo, y_hi); break;
+            case 5: px_color_phase<2, 2, false, false>(im, T, K, smem, r, y_lo, y_hi); break;
+            case 6: px_color_phase<2, 1, true, false>(im, T, K, smem, r, y_lo, y_hi); break;
+            case 7: px_color_phase<1, 2, true, false>(im, T, K, smem, r, y_lo, y_hi); break;
+            default: px_color_phase<2, 2, true, false>(im, T, K, smem, r, y_lo, y_hi); break;
+            }
+        }
+        if (T.lag && r < r_last) {
+            // the last two rows of every plane become the first two of the next step
+            __syncthreads();
+            for (int c = 0; c < T.ncomp; ++c) {
+                const PxComp& pc = T.c[c];
+                const int rows = T.carry + (8 << pc.lv);
+                const int words = pc.stride / 4;
+                for (int k = threadIdx.x; k < 2 * words; k += kPxThreads) {
+                    const int row = k / words, w = k - row * words;
+                    reinterpret_cast<uint32_t*>(smem + pc.off + row * pc.stride)[w] =
+                        reinterpret_cast<const uint32_t*>(smem + pc.off + (rows - 2 + row) * pc.stride)[w];
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
