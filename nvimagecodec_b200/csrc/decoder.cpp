@@ -7,6 +7,8 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <cstdlib>
 #include <condition_variable>
 #include <cstdio>
 #include <cstring>
@@ -19,6 +21,16 @@ namespace {
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 const char* kStageNames[] = {"scan(K0)", "huff_sync(K1)", "verify_scan(K2)", "huff_write(K3)", "dc_scan(K3b)", "idct(K4a)", "color(K4b)", "pixels(K4)"};
 } // namespace
+
+bool trace_enabled()
+{
+    static const bool on = std::getenv("B200JPEG_TRACE") != nullptr;
+    return on;
+}
+double trace_now_us()
+{
+    return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 // ---- memory: the host's allocators when it supplied some, else stream-ordered allocation (cudaMallocAsync) where the
 // device has memory pools, else cudaMalloc -- the order src/imgproc/device_buffer.cpp:42-69 uses.
@@ -391,6 +403,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     uint32_t n_tiles = 0, n_sub = 0, n_seq = 0, n_wseq = 0, n_bnd = 0, n_dc = 0, n_idct = 0, n_color = 0;
     comp_bytes_ = n_coefs_ = out_bytes_ = 0;
 
+    const double t0 = trace_enabled() ? trace_now_us() : 0;
     // Marker walks: one per input the caller has not walked already, spread over the helper threads when there are many.
     parsed_own_.resize(size_t(n));
     {
@@ -413,6 +426,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 walk(i, &ctx);
     }
 
+    const double t1 = trace_enabled() ? trace_now_us() : 0;
     // Work list: one entry per device image.  A stream whose three components come in three scans becomes up to three
     // one-component images (kChild; each decodes like a grayscale image of the component's size) plus the image itself
     // (kParent: no entropy data of its own, its colour stage reads the children's planes).
@@ -644,8 +658,11 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         // band height are set for the whole batch once every image is known (below); here only the MCU window.
         {
             bool fused = opt_.fused_pixels && role == kNormal && im.color_mode >= 1 && o.orientation <= 1;
-            for (int c = 0; c < hd.ncomp; ++c)
+            for (int c = 0; c < hd.ncomp; ++c) {
                 fused = fused && hd.h[c] <= 2 && hd.v[c] <= 2;
+                for (int k = 0; k < 64; ++k) // the fused kernel dequantises with 8-bit quantisers (every baseline table is)
+                    fused = fused && hd.qt[hd.tq[c]][k] <= 255;
+            }
             if (fused) {
                 const int mcu_w = 8 * hd.hmax;
                 im.px_mcu_col_lo = uint16_t(x0 / mcu_w);
@@ -870,6 +887,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         else
             staged_bytes += im.raw_len;
     }
+    const double t2 = trace_enabled() ? trace_now_us() : 0;
     if (staged_bytes) {
         nvtx3::scoped_range nvtx_stage{"b200jpeg stage bitstreams"};
         // staging copies, cut into jobs of about 1 MB for the helper threads
@@ -921,6 +939,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     for (size_t si = 0; si < sets.size(); ++si)
         std::memcpy(up + off_huff + si * sizeof(HuffSetDev), sets[si], sizeof(HuffSetDev));
 
+    const double t3 = trace_enabled() ? trace_now_us() : 0;
     // one H2D for descriptors + maps + tables (+ the staged raw bytes), then one per directly copied image
     const size_t first_copy = staged_bytes ? upload_bytes : off_raw;
     last_stream_ = stream;
@@ -937,6 +956,13 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             return B200JPEG_ERR_CUDA;
     }
 
+    if (trace_enabled()) {
+        const double t4 = trace_now_us();
+        t_walk_ = t1 - t0;
+        t_layout_ = t2 - t1;
+        t_stage_ = t3 - t2;
+        t_h2d_ = t4 - t3;
+    }
     uint8_t* dv = upload_.as<uint8_t>();
     uint8_t* sc = scratch_.as<uint8_t>();
     bd_.n_images = nd;
@@ -1374,10 +1400,15 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         cudaEventRecord(user_event_, user_stream);
     }
     int rc_all = B200JPEG_OK;
+    const double tr0 = trace_enabled() ? trace_now_us() : 0;
+    double tr_walk = 0, tr_layout = 0, tr_stage = 0, tr_h2d = 0, tr_exec = 0, tr_wait = 0;
     auto drain = [&](Lane& l) {
         if (!l.busy)
             return;
+        const double w0 = trace_enabled() ? trace_now_us() : 0;
         const int rc = l.dec->finish_wait(status ? status + l.first : nullptr, l.active_stream);
+        if (trace_enabled())
+            tr_wait += trace_now_us() - w0;
         if (rc != B200JPEG_OK && rc_all == B200JPEG_OK) {
             rc_all = rc;
             err_ = l.dec->last_error();
@@ -1400,10 +1431,20 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
             cudaStreamWaitEvent(s, user_event_, 0);
         }
         int rc = l.dec->prepare(cnt, data + first, len + first, outs + first, s, parsed ? parsed + first : nullptr, pinned);
+        const double e0 = trace_enabled() ? trace_now_us() : 0;
         if (rc == B200JPEG_OK)
             rc = l.dec->execute(s);
         if (rc == B200JPEG_OK)
             rc = l.dec->finish_async(s);
+        if (trace_enabled()) {
+            double a, b, c2, d;
+            l.dec->trace_times(&a, &b, &c2, &d);
+            tr_walk += a;
+            tr_layout += b;
+            tr_stage += c2;
+            tr_h2d += d;
+            tr_exec += trace_now_us() - e0;
+        }
         if (rc != B200JPEG_OK) {
             if (rc_all == B200JPEG_OK) {
                 rc_all = rc;
@@ -1426,6 +1467,9 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         for (auto& l : lanes_)
             if (l.used)
                 cudaStreamWaitEvent(user_stream, l.dec->done_event(), 0);
+    if (trace_enabled())
+        std::fprintf(stderr, "[b200jpeg] decode n=%d chunks=%d pinned=%d total=%.0f us: walk %.0f layout %.0f stage %.0f h2d-issue %.0f launch %.0f wait %.0f\n", n,
+            n_chunks, pinned, trace_now_us() - tr0, tr_walk, tr_layout, tr_stage, tr_h2d, tr_exec, tr_wait);
     return rc_all;
 }
 

@@ -36,6 +36,10 @@ struct Services {
     void (*parallel_for)(void* ctx, int n, void (*fn)(int i, void* arg), void* arg) = nullptr;
 };
 
+// B200JPEG_TRACE=1 in the environment: one line per batch on stderr with the host-side phase times (microseconds).
+bool trace_enabled();
+double trace_now_us();
+
 struct DeviceBuffer {
     void* ptr = nullptr;
     size_t cap = 0;
@@ -173,6 +177,16 @@ class Decoder {
     std::string set_key_;
 
     // stats
+    double t_walk_ = 0, t_layout_ = 0, t_stage_ = 0, t_h2d_ = 0; // host phases of the last prepare (B200JPEG_TRACE)
+  public:
+    void trace_times(double* walk, double* layout, double* stage, double* h2d) const
+    {
+        *walk = t_walk_;
+        *layout = t_layout_;
+        *stage = t_stage_;
+        *h2d = t_h2d_;
+    }
+  private:
     int64_t launches_ = 0, algo_bytes_ = 0, comp_bytes_ = 0, n_coefs_ = 0, out_bytes_ = 0, resync_images_ = 0;
 
     // profiling

@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cstdio>
 #include <cstring>
 #include <deque>
 #include <memory>
@@ -304,6 +305,16 @@ class DecoderImpl {
     {
         if (!image || !cs || !params)
             return NVIMGCODEC_PROCESSING_STATUS_FAIL;
+        struct Timer {
+            std::atomic<long>& acc;
+            double t0;
+            explicit Timer(std::atomic<long>& a) : acc(a), t0(b200jpeg::trace_enabled() ? b200jpeg::trace_now_us() : 0) {}
+            ~Timer()
+            {
+                if (b200jpeg::trace_enabled())
+                    acc.fetch_add(long(b200jpeg::trace_now_us() - t0));
+            }
+        } timer(can_decode_us_);
         nvimgcodecJpegImageInfo_t jpeg_info{NVIMGCODEC_STRUCTURE_TYPE_JPEG_IMAGE_INFO, sizeof(nvimgcodecJpegImageInfo_t), nullptr};
         nvimgcodecImageInfo_t cs_info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), &jpeg_info};
         if (cs->getImageInfo(cs->instance, &cs_info) != NVIMGCODEC_STATUS_SUCCESS)
@@ -371,6 +382,7 @@ class DecoderImpl {
     {
         if (n <= 0)
             return NVIMGCODEC_STATUS_SUCCESS;
+        const double tr0 = b200jpeg::trace_enabled() ? b200jpeg::trace_now_us() : 0;
         std::unique_lock<std::mutex> fallback_lock(fallback_mu_, std::defer_lock);
         b200jpeg::Pipeline* core = nullptr;
         try {
@@ -432,7 +444,15 @@ class DecoderImpl {
                     parsed[i] = &walked[i]->parsed;
             }
         }
+        const double tr1 = b200jpeg::trace_enabled() ? b200jpeg::trace_now_us() : 0;
         const int rc = core->decode(n, data.data(), len.data(), outs.data(), status.data(), stream, parsed.data());
+        if (b200jpeg::trace_enabled()) {
+            int reused = 0;
+            for (int i = 0; i < n; ++i)
+                reused += parsed[i] != nullptr;
+            std::fprintf(stderr, "[b200jpeg] decodeBatch n=%d: descriptors %.0f us, decode %.0f us, canDecode since last batch %ld us (summed over threads), walks reused %d, since last decodeBatch return %.0f us\n",
+                n, tr1 - tr0, b200jpeg::trace_now_us() - tr1, can_decode_us_.exchange(0), reused, last_return_us_ ? tr0 - last_return_us_ : 0.0);
+        }
         if (rc != B200JPEG_OK)
             log_msg(fw_, NVIMGCODEC_DEBUG_MESSAGE_SEVERITY_ERROR, std::string("b200 jpeg batch decode failed: ") + core->last_error());
         for (int i = 0; i < n; ++i) {
@@ -441,6 +461,8 @@ class DecoderImpl {
                 ps = (rc == B200JPEG_OK) ? to_processing_status(status[i]) : NVIMGCODEC_PROCESSING_STATUS_FAIL;
             images[i]->imageReady(images[i]->instance, ps);
         }
+        if (b200jpeg::trace_enabled())
+            last_return_us_ = b200jpeg::trace_now_us();
         return rc == B200JPEG_OK ? NVIMGCODEC_STATUS_SUCCESS : NVIMGCODEC_STATUS_EXTENSION_EXECUTION_FAILED;
     }
 
@@ -490,6 +512,8 @@ class DecoderImpl {
     std::unique_ptr<b200jpeg::Pipeline> batch_;
     std::mutex fallback_mu_;
     std::unique_ptr<b200jpeg::Pipeline> fallback_;
+    std::atomic<long> can_decode_us_{0};
+    double last_return_us_ = 0;
 };
 
 // ---- C trampolines of nvimgcodecDecoderDesc_t (never let an exception cross the ABI)

@@ -1896,7 +1896,7 @@ size_t pixels_tile_smem(int ncomp, const int* h, const int* v, int vmax, int str
     size_t total = 0;
     for (int c = 0; c < ncomp; ++c) {
         const int cols = (strip_mcus + ((c > 0 && fancy_h) ? 2 : 0)) * h[c];
-        total += size_t(carry + 8 * v[c]) * size_t(cols * 8 + 16);
+        total += size_t(carry + 8 * v[c]) * size_t((cols * 8 + 15) / 16 * 16 + 32); // rows padded to 16 bytes + kPxApron on either side
     }
     return (total + 15) / 16 * 16;
 }

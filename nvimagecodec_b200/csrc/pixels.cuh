@@ -20,6 +20,7 @@
 
 constexpr int kPxThreads = 256;
 constexpr int kPxUnit = 16; // pixels per thread and row in phase B
+constexpr int kPxApron = 16; // bytes before and after the samples of every plane row
 
 struct PxComp {
     int bx0, nbx;     // block columns held: [bx0, bx0 + nbx)
@@ -38,32 +39,54 @@ struct PxTile {
     int urows;        // unit rows per MCU row (chroma rows per MCU row; luma rows when VX == 1)
 };
 
-// Coefficients of one block (dense layout: 16-byte groups in zig-zag order, a mask of the groups K3 wrote, DC in the record).
-__device__ __forceinline__ void px_fetch_block(const BatchDev& bd, const ImageDev& im, uint32_t blk_in_image, int32_t (&zz)[64])
+// Coefficients of one block (dense layout: 16-byte groups in zig-zag order, a mask of the groups K3 wrote, DC in the record),
+// as they lie in memory: w[j] = positions 2j (low half) and 2j + 1 (high half) of the zig-zag sequence; position 0 is not
+// stored there, the DC value comes back separately.
+__device__ __forceinline__ int32_t px_fetch_block(const int16_t* __restrict__ coef, const uint32_t* __restrict__ blkrec, size_t blk, uint32_t (&w)[32])
 {
-    const size_t blk = im.coef_off / 64 + blk_in_image;
-    const uint4* s4 = reinterpret_cast<const uint4*>(bd.coef) + blk * 8;
-    const uint32_t rec = __ldg(bd.blkrec + blk);
+    const uint4* s4 = reinterpret_cast<const uint4*>(coef) + blk * 8;
+    const uint32_t rec = __ldg(blkrec + blk);
     const uint32_t mask = rec & 0xFFu;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
         if ((mask >> i) & 1u)
             v = __ldg(s4 + i);
-        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            zz[i * 8 + 2 * j] = int32_t(int16_t(w[j] & 0xFFFFu));
-            zz[i * 8 + 2 * j + 1] = int32_t(int16_t(w[j] >> 16));
-        }
+        w[4 * i + 0] = v.x;
+        w[4 * i + 1] = v.y;
+        w[4 * i + 2] = v.z;
+        w[4 * i + 3] = v.w;
     }
-    zz[0] = int32_t(rec) >> 16;
+    return int32_t(rec) >> 16;
 }
 
+// signed 16-bit halves of a times unsigned bytes of b: lo = a.lo * b.b0 + a.hi * b.b1, hi = a.lo * b.b2 + a.hi * b.b3
+__device__ __forceinline__ int32_t px_dp2a_lo(uint32_t a, uint32_t b)
+{
+    int32_t d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(0));
+    return d;
+}
+__device__ __forceinline__ int32_t px_dp2a_hi(uint32_t a, uint32_t b)
+{
+    int32_t d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(0));
+    return d;
+}
+
+__device__ __forceinline__ void px_sts64(uint32_t addr, uint32_t a, uint32_t b)
+{
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
+}
+
+// Dequantisation straight from the packed pairs: one dot-product instruction per coefficient picks the 16-bit half, sign-extends
+// it and multiplies by the 8-bit quantiser (qz[j] = q(2j) | q(2j+1) << 24 in zig-zag order: the lo form sees q(2j) and a zero
+// byte, the hi form a zero byte and q(2j+1)).  Baseline tables are 8 bits wide; streams with 16-bit tables take the idct kernel.
+// dst: shared-window address of the block's first row.
 // kRows: 0 = all eight rows, 1 = only row 7, 2 = only row 0 (the rows a band's first / last step needs); what is not
 // asked for is never computed (everything is unrolled, unused column outputs are dead code).
 template <int kRows>
-__device__ __forceinline__ void px_idct_block(const int32_t (&zz)[64], const uint16_t* __restrict__ q, uint8_t* __restrict__ dst, int stride)
+__device__ __forceinline__ void px_idct_block(const uint32_t (&w)[32], int32_t dc, const uint32_t* __restrict__ qz, uint32_t dst, int stride)
 {
     constexpr int kZzPos[64] = {0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43, 9, 11, 18, 24,
         31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60, 21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48,
@@ -73,8 +96,15 @@ __device__ __forceinline__ void px_idct_block(const int32_t (&zz)[64], const uin
     for (int x = 0; x < 8; ++x) {
         int32_t col[8], o[8];
 #pragma unroll
-        for (int y = 0; y < 8; ++y)
-            col[y] = zz[kZzPos[y * 8 + x]] * int32_t(q[y * 8 + x]);
+        for (int y = 0; y < 8; ++y) {
+            const int z = kZzPos[y * 8 + x];
+            if (z == 0)
+                col[y] = dc * int32_t(qz[0] & 0xFFu);
+            else if (z & 1)
+                col[y] = px_dp2a_hi(w[z >> 1], qz[z >> 1]);
+            else
+                col[y] = px_dp2a_lo(w[z >> 1], qz[z >> 1]);
+        }
         idct8<11, 0u>(col[0], col[1], col[2], col[3], col[4], col[5], col[6], col[7], o);
 #pragma unroll
         for (int y = 0; y < 8; ++y)
@@ -89,13 +119,20 @@ __device__ __forceinline__ void px_idct_block(const int32_t (&zz)[64], const uin
         uint2 pk;
         pk.x = range_limit(o[0]) | (range_limit(o[1]) << 8) | (range_limit(o[2]) << 16) | (range_limit(o[3]) << 24);
         pk.y = range_limit(o[4]) | (range_limit(o[5]) << 8) | (range_limit(o[6]) << 16) | (range_limit(o[7]) << 24);
-        *reinterpret_cast<uint2*>(dst + y * stride) = pk;
+        px_sts64(dst + uint32_t(y * stride), pk.x, pk.y);
     }
 }
 
 // Phase A of one step: the blocks of MCU row r.  kind 0: every component, all rows; 1: chroma only, last row of the
 // MCU row (the step above a band); 2: chroma only, first row (the step below a band).
-__device__ __noinline__ void px_idct_phase(const BatchDev& bd, const ImageDev& im, const PxTile& T, const uint16_t (*s_q)[64], uint8_t* smem, int r, int kind)
+struct PxSource {          // what phase A needs of the batch and the image, read once per CTA
+    const int16_t* coef;
+    const uint32_t* blkrec;
+    size_t blk0;           // first block of the image in the batch arenas
+    uint32_t mcus_x, bpm;
+};
+
+__device__ __noinline__ void px_idct_phase(const PxSource src, const PxTile& T, const uint32_t (*s_qz)[32], uint32_t smem, int r, int kind)
 {
     int n[3];
 #pragma unroll
@@ -128,16 +165,16 @@ __device__ __noinline__ void px_idct_phase(const BatchDev& bd, const ImageDev& i
         const int bx = pc.bx0 + local;
         const int mcu = bx >> pc.lh;
         const uint32_t bim = uint32_t(pc.first + (by << pc.lh) + (bx - (mcu << pc.lh)));
-        const uint32_t blk = (uint32_t(r) * im.mcus_x + uint32_t(mcu)) * im.bpm + bim;
-        int32_t zz[64];
-        px_fetch_block(bd, im, blk, zz);
-        uint8_t* dst = smem + pc.off + (T.carry + by * 8) * pc.stride + local * 8;
+        const uint32_t blk = (uint32_t(r) * src.mcus_x + uint32_t(mcu)) * src.bpm + bim;
+        uint32_t w[32];
+        const int32_t dc = px_fetch_block(src.coef, src.blkrec, src.blk0 + blk, w);
+        const uint32_t dst = smem + uint32_t(pc.off + (T.carry + by * 8) * pc.stride + kPxApron + local * 8);
         if (kind == 0)
-            px_idct_block<0>(zz, s_q[c], dst, pc.stride);
+            px_idct_block<0>(w, dc, s_qz[c], dst, pc.stride);
         else if (kind == 1)
-            px_idct_block<1>(zz, s_q[c], dst, pc.stride);
+            px_idct_block<1>(w, dc, s_qz[c], dst, pc.stride);
         else
-            px_idct_block<2>(zz, s_q[c], dst, pc.stride);
+            px_idct_block<2>(w, dc, s_qz[c], dst, pc.stride);
     }
 }
 
@@ -153,75 +190,52 @@ __device__ __forceinline__ void px_stg64(uint8_t* p, uint32_t a, uint32_t b)
 }
 __device__ __forceinline__ int px_byte(uint32_t w, int k) { return int(__byte_perm(w, 0u, 0x4440 + k)); } // byte k of w
 
-// Chroma samples of one row for eight pixels.  HX == 2: c[0] = left neighbour, c[1..4] = the four samples, c[5] = right
-// neighbour (neighbours clamped to the real component width, where libjpeg's edge formulas replicate); HX == 1: c[0..7].
-// row points at sample column `xorg` of the component; j0 is the first sample's column.
-template <int HX>
-__device__ __forceinline__ void px_load_chroma(const uint8_t* row, int xorg, int j0, int dw, int* c)
+// Chroma for eight pixels (half hf of a unit) of one output row, HX == 2: the six samples the horizontal filter looks at
+// (left neighbour, four centres, right neighbour) of the current row and of its vertical neighbour row, taken from what
+// was loaded once per unit: w0 / w1 = samples 0..3 / 4..7, l / r = the samples before and after them.
+// s[] = the vertical part: 3 * cur + nbr for the h2v2 triangle, the sample itself otherwise.
+template <int VX, bool kFancy>
+__device__ __forceinline__ void px_vertical_h2(int hf, uint32_t cw0, uint32_t cw1, int cl, int cr, uint32_t nw0, uint32_t nw1, int nl, int nr, int* s)
 {
-    if (HX == 2) {
-        const uint32_t v = *reinterpret_cast<const uint32_t*>(row + (j0 - xorg));
+    int c[6], n[6];
+    const uint32_t cw = hf ? cw1 : cw0, nw = hf ? nw1 : nw0;
+    c[0] = hf ? px_byte(cw0, 3) : cl;
+    c[5] = hf ? cr : px_byte(cw1, 0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        c[1 + k] = px_byte(cw, k);
+    if (VX == 2 && kFancy) {
+        n[0] = hf ? px_byte(nw0, 3) : nl;
+        n[5] = hf ? nr : px_byte(nw1, 0);
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-            c[1 + k] = px_byte(v, k);
-        c[0] = row[(j0 > 0 ? j0 - 1 : 0) - xorg];
-        c[5] = row[(j0 + 4 < dw ? j0 + 4 : dw - 1) - xorg];
-        if (j0 + 3 > dw - 1) { // the right image edge lies inside these samples: replicate the last real one
-            const int last = row[dw - 1 - xorg];
+            n[1 + k] = px_byte(nw, k);
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (j0 + k > dw - 1)
-                    c[1 + k] = last;
-        }
+        for (int k = 0; k < 6; ++k)
+            s[k] = 3 * c[k] + n[k];
     } else {
-        const uint2 v = *reinterpret_cast<const uint2*>(row + (j0 - xorg));
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            c[k] = px_byte(v.x, k);
-            c[4 + k] = px_byte(v.y, k);
-        }
+        for (int k = 0; k < 6; ++k)
+            s[k] = c[k];
     }
 }
 
-// Vertical part of the upsampling for one output row: s[] = what the horizontal part works on.
-//   h2v2 triangle: 3 * cur + nbr (the horizontal part divides by 16); h1v2 triangle: the finished sample;
-//   everything else: the sample itself.
-template <int HX, int VX, bool kFancy>
-__device__ __forceinline__ void px_vertical(const int* cur, const int* nbr, int rr, int* s)
+// Horizontal part for the four pixels 4g .. 4g+3 (g = 0, 1) of the eight, HX == 2 (jdsample.c).
+template <int VX, bool kFancy>
+__device__ __forceinline__ void px_horizontal_h2(const int* s, int g, int* out)
 {
-    constexpr int NC = (HX == 2) ? 6 : 8;
 #pragma unroll
-    for (int k = 0; k < NC; ++k) {
-        if (VX == 2 && kFancy)
-            s[k] = (HX == 2) ? 3 * cur[k] + nbr[k] : (3 * cur[k] + nbr[k] + 1 + rr) >> 2;
-        else
-            s[k] = cur[k];
-    }
-}
-
-// Horizontal part for the four pixels 4g .. 4g+3 (g = 0, 1) of the eight (jdsample.c).
-template <int HX, int VX, bool kFancy>
-__device__ __forceinline__ void px_horizontal4(const int* s, int g, int* out)
-{
-    if (HX == 2) {
-#pragma unroll
-        for (int m = 0; m < 2; ++m) {
-            const int k = 2 * g + m + 1; // centre sample
-            if (VX == 2 && kFancy) {
-                const int t = 3 * s[k] + 8;
-                out[2 * m] = (t + s[k - 1]) >> 4;
-                out[2 * m + 1] = (t + s[k + 1] - 1) >> 4;
-            } else if (kFancy) {
-                out[2 * m] = (3 * s[k] + s[k - 1] + 1) >> 2;
-                out[2 * m + 1] = (3 * s[k] + s[k + 1] + 2) >> 2;
-            } else {
-                out[2 * m] = out[2 * m + 1] = s[k];
-            }
+    for (int m = 0; m < 2; ++m) {
+        const int k = 2 * g + m + 1; // centre sample
+        if (VX == 2 && kFancy) {
+            out[2 * m] = (3 * s[k] + 8 + s[k - 1]) >> 4;
+            out[2 * m + 1] = (3 * s[k] + 7 + s[k + 1]) >> 4;
+        } else if (kFancy) {
+            out[2 * m] = (3 * s[k] + 1 + s[k - 1]) >> 2;
+            out[2 * m + 1] = (3 * s[k] + 2 + s[k + 1]) >> 2;
+        } else {
+            out[2 * m] = out[2 * m + 1] = s[k];
         }
-    } else {
-#pragma unroll
-        for (int m = 0; m < 4; ++m)
-            out[m] = s[4 * g + m];
     }
 }
 
@@ -264,7 +278,15 @@ __device__ __forceinline__ PxColor px_color_setup(int fmt)
 // Interleaved: pk[0..5] = the 24 bytes; with `o` 16-byte aligned half 0 goes out as 16 + 8 bytes, half 1 (at o + 24) as
 // 8 + 16 bytes, so that a unit row is two 128-bit and two 64-bit stores.  Planar: pk[2 * ch + 0..1] = the 8 bytes of channel ch.
 // x_lo / x_hi: the part of the eight pixels inside the region of interest (0 / 8 when all of them are).
-__device__ __forceinline__ void px_store_half(const ImageDev& im, const PxColor& K, int ox, int oy, int hf, const uint32_t* pk, int x_lo, int x_hi)
+struct PxOut {             // where the pixels go, read once per CTA (stores through `out` would otherwise force re-reads of the descriptor)
+    uint8_t* out;
+    size_t plane_stride;
+    uint32_t row_stride;
+    int roi_x0, roi_x1, roi_y0;
+    int dw, dh;            // real size of the chroma components
+};
+
+__device__ __forceinline__ void px_store_half(const PxOut& im, const PxColor& K, int ox, int oy, int hf, const uint32_t* pk, int x_lo, int x_hi)
 {
     const bool full = x_lo == 0 && x_hi == 8;
     if (K.planar) {
@@ -310,24 +332,24 @@ __device__ __forceinline__ void px_store_half(const ImageDev& im, const PxColor&
 // Phase B of one step for one sampling mode.  Unit row m of MCU row r is chroma row (luma row when VX == 1)
 // i = urows * r - lag + m; its luma rows VX * i .. sit at plane rows VX * m .., its chroma rows i - 1, i, i + 1 (clamped
 // to the component's real height, where libjpeg replicates) at plane rows (row) - (urows * r - carry).
-// A thread takes 16 pixels of a row as two halves of eight.
+// A thread takes 16 pixels of VX rows: everything it needs is loaded once (packed), then worked through in halves of
+// eight pixels.  The aprons of the planes hold the replicated edge samples, so no address is clamped horizontally.
 template <int HX, int VX, bool kFancy, bool kLumaOnly>
-__device__ __forceinline__ void px_color_phase(const ImageDev& im, const PxTile& T, const PxColor& K, const uint8_t* smem, int r, int y_lo, int y_hi)
+__device__ __forceinline__ void px_color_phase(const PxOut& im, const PxTile& T, const PxColor& K, const uint8_t* smem, int r, int y_lo, int y_hi)
 {
     constexpr bool fancy_v = kFancy && VX == 2;
-    constexpr int NC = (HX == 2) ? 6 : 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int X_strip = T.mx0 * (8 << T.c[0].lh);
     const int strip_px = T.c[0].nbx * 8;
     const int ucols = (strip_px + kPxUnit - 1) / kPxUnit;
-    const int dw = kLumaOnly ? 0 : int(im.comp_w[1]), dh = kLumaOnly ? 0 : int(im.comp_h[1]);
+    const int dh = im.dh;
     const int crow0 = T.urows * r - T.carry; // chroma row held at plane row 0
     const int ystride = T.c[0].stride;
-    const uint8_t* p0 = smem + T.c[0].off;
-    const uint8_t* pa = kLumaOnly ? p0 : smem + T.c[K.plane_a].off;
-    const uint8_t* pb = kLumaOnly ? p0 : smem + T.c[K.plane_b].off;
+    const uint8_t* p0 = smem + T.c[0].off + kPxApron;
     const int cstride = kLumaOnly ? 0 : T.c[1].stride;
-    const int cxorg = kLumaOnly ? 0 : T.c[1].bx0 * 8;
+    // sample column of the strip's first pixel inside the chroma planes
+    const uint8_t* pa = kLumaOnly ? p0 : smem + T.c[K.plane_a].off + kPxApron + (X_strip / HX - T.c[1].bx0 * 8);
+    const ptrdiff_t a_to_b = kLumaOnly ? 0 : ptrdiff_t(T.c[K.plane_b].off) - ptrdiff_t(T.c[K.plane_a].off);
     const int roi_x0 = im.roi_x0, roi_x1 = im.roi_x1, roi_y0 = im.roi_y0;
 #pragma unroll 1
     for (int m = warp; m < T.urows; m += kPxThreads / 32) {
@@ -335,58 +357,105 @@ __device__ __forceinline__ void px_color_phase(const ImageDev& im, const PxTile&
         const int y0 = VX * i;
         if (y0 + VX <= y_lo || y0 >= y_hi)
             continue;
+        int up = i - 1, dn = i + 1; // vertical neighbour rows, replicated at the component's top and bottom
+        up = up < 0 ? 0 : up;
+        dn = dn > dh - 1 ? dh - 1 : dn;
 #pragma unroll 1
         for (int ux = lane; ux < ucols; ux += 32) {
             const int X0 = X_strip + ux * kPxUnit;
             if (X0 >= roi_x1 || X0 + kPxUnit <= roi_x0)
                 continue;
-#pragma unroll 1
+            // ---- loads: luma of VX rows, chroma of the row (and of its vertical neighbours)
+            const uint8_t* yp = p0 + (VX * m) * ystride + ux * kPxUnit;
+            uint4 yv[VX];
+#pragma unroll
+            for (int rr = 0; rr < VX; ++rr)
+                yv[rr] = *reinterpret_cast<const uint4*>(yp + rr * ystride);
+            // chroma, packed: [plane a / b][row: cur, up, dn][words]; HX == 2: 8 samples + the two around them, HX == 1: 16 samples
+            uint32_t cw[2][3][4];
+            int cl[2][3], cr[2][3];
+            if (!kLumaOnly) {
+                const uint8_t* ca = pa + (i - crow0) * cstride + ux * (kPxUnit / HX);
+#pragma unroll
+                for (int ab = 0; ab < 2; ++ab) {
+#pragma unroll
+                    for (int row = 0; row < 3; ++row) {
+                        if (row > 0 && !fancy_v)
+                            continue;
+                        const uint8_t* q = ca + (ab ? a_to_b : 0) + (row == 0 ? 0 : ((row == 1 ? up : dn) - i) * cstride);
+                        if (HX == 2) {
+                            const uint2 v = *reinterpret_cast<const uint2*>(q);
+                            cw[ab][row][0] = v.x;
+                            cw[ab][row][1] = v.y;
+                            if (kFancy) {
+                                cl[ab][row] = q[-1];
+                                cr[ab][row] = q[8];
+                            }
+                        } else {
+                            const uint4 v = *reinterpret_cast<const uint4*>(q);
+                            cw[ab][row][0] = v.x;
+                            cw[ab][row][1] = v.y;
+                            cw[ab][row][2] = v.z;
+                            cw[ab][row][3] = v.w;
+                        }
+                    }
+                }
+            }
+#pragma unroll
             for (int rr = 0; rr < VX; ++rr) {
                 const int y = y0 + rr;
                 if (y < y_lo || y >= y_hi)
                     continue;
-                int nb = i; // the vertical neighbour row (the row itself where no vertical filter applies)
-                if (fancy_v) {
-                    nb = rr == 0 ? i - 1 : i + 1;
-                    nb = nb < 0 ? 0 : (nb > dh - 1 ? dh - 1 : nb);
-                }
-                const uint8_t* yrow = p0 + (VX * m + rr) * ystride + (X0 - X_strip);
+                const int nrow = fancy_v ? 1 + rr : 0; // the vertical neighbour of this output row: up for the first, down for the second
+                const uint32_t yw[4] = {yv[rr].x, yv[rr].y, yv[rr].z, yv[rr].w};
 #pragma unroll
                 for (int hf = 0; hf < 2; ++hf) {
                     const int X = X0 + 8 * hf;
                     if (X >= roi_x1 || X + 8 <= roi_x0 || X - X_strip >= strip_px)
                         continue;
                     const int x_lo = max(roi_x0 - X, 0), x_hi = min(roi_x1 - X, 8);
-                    int sa[NC], sb[NC];
+                    int sa[8], sb[8]; // HX == 2: six vertically filtered samples; HX == 1: the eight finished samples
                     if (!kLumaOnly) {
-                        const int j0 = X / HX;
-                        int cur[NC], nbr[NC];
-                        px_load_chroma<HX>(pa + (i - crow0) * cstride, cxorg, j0, dw, cur);
-                        if (fancy_v)
-                            px_load_chroma<HX>(pa + (nb - crow0) * cstride, cxorg, j0, dw, nbr);
-                        px_vertical<HX, VX, kFancy>(cur, fancy_v ? nbr : cur, rr, sa);
-                        px_load_chroma<HX>(pb + (i - crow0) * cstride, cxorg, j0, dw, cur);
-                        if (fancy_v)
-                            px_load_chroma<HX>(pb + (nb - crow0) * cstride, cxorg, j0, dw, nbr);
-                        px_vertical<HX, VX, kFancy>(cur, fancy_v ? nbr : cur, rr, sb);
+                        if (HX == 2) {
+                            px_vertical_h2<VX, kFancy>(hf, cw[0][0][0], cw[0][0][1], cl[0][0], cr[0][0], cw[0][nrow][0], cw[0][nrow][1], cl[0][nrow], cr[0][nrow], sa);
+                            px_vertical_h2<VX, kFancy>(hf, cw[1][0][0], cw[1][0][1], cl[1][0], cr[1][0], cw[1][nrow][0], cw[1][nrow][1], cl[1][nrow], cr[1][nrow], sb);
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) {
+                                const int ca8 = px_byte(cw[0][0][2 * hf + (k >> 2)], k & 3), cb8 = px_byte(cw[1][0][2 * hf + (k >> 2)], k & 3);
+                                if (fancy_v) { // h1v2 triangle
+                                    sa[k] = (3 * ca8 + px_byte(cw[0][nrow][2 * hf + (k >> 2)], k & 3) + 1 + rr) >> 2;
+                                    sb[k] = (3 * cb8 + px_byte(cw[1][nrow][2 * hf + (k >> 2)], k & 3) + 1 + rr) >> 2;
+                                } else {
+                                    sa[k] = ca8;
+                                    sb[k] = cb8;
+                                }
+                            }
+                        }
                     }
-                    const uint2 yv = *reinterpret_cast<const uint2*>(yrow + 8 * hf);
-                    const uint32_t yw[2] = {yv.x, yv.y};
                     uint32_t pk[6];
 #pragma unroll
                     for (int g = 0; g < 2; ++g) {
                         uint32_t c0[4], c1[4], c2[4];
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            c0[k] = __byte_perm(yw[g], 0u, 0x4044 + 0x100 * k); // luma << 16
+                            c0[k] = __byte_perm(yw[2 * hf + g], 0u, 0x4044 + 0x100 * k); // luma << 16
                         if (kLumaOnly) {
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
                                 c1[k] = c2[k] = c0[k];
                         } else {
                             int ua[4], ub[4];
-                            px_horizontal4<HX, VX, kFancy>(sa, g, ua);
-                            px_horizontal4<HX, VX, kFancy>(sb, g, ub);
+                            if (HX == 2) {
+                                px_horizontal_h2<VX, kFancy>(sa, g, ua);
+                                px_horizontal_h2<VX, kFancy>(sb, g, ub);
+                            } else {
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) {
+                                    ua[k] = sa[4 * g + k];
+                                    ub[k] = sb[4 * g + k];
+                                }
+                            }
                             if (K.yuv) {
 #pragma unroll
                                 for (int k = 0; k < 4; ++k) {
@@ -394,12 +463,13 @@ __device__ __forceinline__ void px_color_phase(const ImageDev& im, const PxTile&
                                     c2[k] = uint32_t(ub[k]) << 16;
                                 }
                             } else {
+                                // one descriptor-dependent operand per instruction: the sums are the same in any order
 #pragma unroll
                                 for (int k = 0; k < 4; ++k) {
                                     const int yk = int(c0[k]);
-                                    c0[k] = uint32_t(__viaddmin_s32_relu(yk, K.ka * ua[k] + K.ca, 0xFFFFFF));
-                                    c1[k] = uint32_t(__viaddmin_s32_relu(yk, K.ga * ua[k] + (K.gb * ub[k] + K.cg), 0xFFFFFF));
-                                    c2[k] = uint32_t(__viaddmin_s32_relu(yk, K.kb * ub[k] + K.cb, 0xFFFFFF));
+                                    c0[k] = uint32_t(__viaddmin_s32_relu(K.ka * ua[k] + yk, K.ca, 0xFFFFFF));
+                                    c1[k] = uint32_t(__viaddmin_s32_relu(K.gb * ub[k] + (K.ga * ua[k] + yk), K.cg, 0xFFFFFF));
+                                    c2[k] = uint32_t(__viaddmin_s32_relu(K.kb * ub[k] + yk, K.cb, 0xFFFFFF));
                                 }
                             }
                         }
@@ -420,10 +490,28 @@ __device__ __forceinline__ void px_color_phase(const ImageDev& im, const PxTile&
     }
 }
 
+// After phase A, before phase B: the samples the horizontal triangle filter replicates at the left and right edge of the
+// image go into the aprons of the chroma rows written in this step (column -1 = column 0, column dw = column dw - 1).
+__device__ __forceinline__ void px_edge_phase(const PxTile& T, uint8_t* smem, int dw, int first_row, int n_rows)
+{
+    for (int t = threadIdx.x; t < 2 * n_rows * 2; t += kPxThreads) {
+        const int c = 1 + (t & 1), side = (t >> 1) & 1, row = first_row + (t >> 2);
+        const PxComp& pc = T.c[c];
+        uint8_t* q = smem + pc.off + row * pc.stride + kPxApron;
+        const int xorg = pc.bx0 * 8;
+        if (side == 0) {
+            if (xorg == 0)
+                q[-1] = q[0];
+        } else if (dw - xorg >= 1 && dw - xorg <= pc.nbx * 8) {
+            q[dw - xorg] = q[dw - 1 - xorg];
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kPxThreads, 3) pixels_kernel(BatchDev bd, int redo_only)
 {
     extern __shared__ uint4 s_px_raw[];
-    __shared__ uint16_t s_q[3][64];
+    __shared__ uint32_t s_qz[3][32];
     uint8_t* smem = reinterpret_cast<uint8_t*>(s_px_raw);
     const uint32_t cta = blockIdx.x;
     const uint32_t img = bd.px_cta_img[cta];
@@ -431,8 +519,13 @@ __global__ void __launch_bounds__(kPxThreads, 3) pixels_kernel(BatchDev bd, int 
     const uint32_t flags = bd.state[img].flags;
     if ((flags & (kFlagDirty | kFlagBadMarker)) || (redo_only && !(flags & kFlagRedo)))
         return;
-    for (int i = threadIdx.x; i < 3 * 64; i += kPxThreads)
-        s_q[i / 64][i % 64] = im.qt[i / 64][i % 64];
+    if (threadIdx.x < 96) { // quantisers paired in zig-zag order: q(2j) | q(2j+1) << 24
+        constexpr uint8_t kNatural[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7,
+            14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62,
+            63};
+        const int c = threadIdx.x >> 5, j = threadIdx.x & 31;
+        s_qz[c][j] = uint32_t(im.qt[c][kNatural[2 * j]]) | (uint32_t(im.qt[c][kNatural[2 * j + 1]]) << 24);
+    }
     // ---- tile geometry (uniform over the CTA; lives in shared memory: the phases index it dynamically)
     __shared__ PxTile s_tile;
     if (threadIdx.x == 0) {
@@ -463,7 +556,7 @@ __global__ void __launch_bounds__(kPxThreads, 3) pixels_kernel(BatchDev bd, int 
             const int m1 = (c > 0 && fancy_h) ? min(T.mx1 + 1, int(im.mcus_x)) : T.mx1;
             pc.bx0 = m0 << pc.lh;
             pc.nbx = (m1 - m0) << pc.lh;
-            pc.stride = pc.nbx * 8 + 16; // the padding keeps 16-byte row alignment and staggers the rows over the banks
+            pc.stride = ((pc.nbx * 8 + 15) & ~15) + 2 * kPxApron; // an apron on either side: the samples the horizontal filter replicates at the image edges
             pc.off = off;
             if (c < T.ncomp)
                 off += (T.carry + (8 << pc.lv)) * pc.stride;
@@ -471,6 +564,24 @@ __global__ void __launch_bounds__(kPxThreads, 3) pixels_kernel(BatchDev bd, int 
         (void)hx;
     }
     const PxColor K = px_color_setup(im.fmt);
+    PxOut po;
+    po.out = im.out;
+    po.plane_stride = im.plane_stride;
+    po.row_stride = im.row_stride;
+    po.roi_x0 = im.roi_x0;
+    po.roi_x1 = im.roi_x1;
+    po.roi_y0 = im.roi_y0;
+    po.dw = im.comp_w[1];
+    po.dh = im.comp_h[1];
+    PxSource src;
+    src.coef = bd.coef;
+    src.blkrec = bd.blkrec;
+    src.blk0 = size_t(im.coef_off / 64);
+    src.mcus_x = im.mcus_x;
+    src.bpm = im.bpm;
+    const int color_mode = im.color_mode, mcus_y = im.mcus_y;
+    const bool fancy_h_mode = color_mode == 6 || color_mode == 8;
+    const uint32_t smem_addr32 = smem_addr(smem);
     __syncthreads();
     const PxTile& T = s_tile;
     const int mcu_h = 8 * int(im.vmax);
@@ -482,19 +593,25 @@ __global__ void __launch_bounds__(kPxThreads, 3) pixels_kernel(BatchDev bd, int 
 #pragma unroll 1
     for (int r = r_first; r <= r_last; ++r) {
         const int kind = r < T.r_lo ? 1 : (r >= T.r_hi ? 2 : 0);
-        if (r < int(im.mcus_y))
-            px_idct_phase(bd, im, T, s_q, smem, r, kind);
+        if (r < mcus_y)
+            px_idct_phase(src, T, s_qz, smem_addr32, r, kind);
         __syncthreads();
+        if (fancy_h_mode && r < mcus_y) {
+            // rows written in this step: all of them, or only the last / the first chroma row (steps above / below the band)
+            const int rows_c = 8 << T.c[1].lv;
+            px_edge_phase(T, smem, po.dw, T.carry + (kind == 1 ? rows_c - 1 : 0), kind == 0 ? rows_c : 1);
+            __syncthreads();
+        }
         if (kind != 1) {
-            switch (im.color_mode) {
-            case 1: px_color_phase<1, 1, false, true>(im, T, K, smem, r, y_lo, y_hi); break;
-            case 2: px_color_phase<1, 1, false, false>(im, T, K, smem, r, y_lo, y_hi); break;
-            case 3: px_color_phase<2, 1, false, false>(im, T, K, smem, r, y_lo, y_hi); break;
-            case 4: px_color_phase<1, 2, false, false>(im, T, K, smem, r, y_lo, y_hi); break;
-            case 5: px_color_phase<2, 2, false, false>(im, T, K, smem, r, y_lo, y_hi); break;
-            case 6: px_color_phase<2, 1, true, false>(im, T, K, smem, r, y_lo, y_hi); break;
-            case 7: px_color_phase<1, 2, true, false>(im, T, K, smem, r, y_lo, y_hi); break;
-            default: px_color_phase<2, 2, true, false>(im, T, K, smem, r, y_lo, y_hi); break;
+            switch (color_mode) {
+            case 1: px_color_phase<1, 1, false, true>(po, T, K, smem, r, y_lo, y_hi); break;
+            case 2: px_color_phase<1, 1, false, false>(po, T, K, smem, r, y_lo, y_hi); break;
+            case 3: px_color_phase<2, 1, false, false>(po, T, K, smem, r, y_lo, y_hi); break;
+            case 4: px_color_phase<1, 2, false, false>(po, T, K, smem, r, y_lo, y_hi); break;
+            case 5: px_color_phase<2, 2, false, false>(po, T, K, smem, r, y_lo, y_hi); break;
+            case 6: px_color_phase<2, 1, true, false>(po, T, K, smem, r, y_lo, y_hi); break;
+            case 7: px_color_phase<1, 2, true, false>(po, T, K, smem, r, y_lo, y_hi); break;
+            default: px_color_phase<2, 2, true, false>(po, T, K, smem, r, y_lo, y_hi); break;
             }
         }
         if (T.lag && r < r_last) {

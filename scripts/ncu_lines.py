@@ -5,7 +5,7 @@ import collections, csv, io, os, re, subprocess, sys, tempfile
 rep, kern = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-so = os.path.join(root, "nvimagecodec_b200", "lib", "libb200jpeg_ext.so")
+so = os.environ.get("B200JPEG_LIB") or os.path.join(root, "nvimagecodec_b200", "lib", "libb200jpeg_ext.so")
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "kernels.sm_100a.cubin", so], cwd=tmp, capture_output=True)
 cub = [f for f in os.listdir(tmp) if f.endswith(".cubin")][0]
@@ -17,7 +17,7 @@ cur, seq = None, []
 for l in sass[start:end]:
     m = re.search(r'//## File "([^"]+)", line (\d+)', l)
     if m:
-        cur = int(m.group(2))
+        cur = (os.path.basename(m.group(1)), int(m.group(2)))
         continue
     m = re.match(r"\s+/\*([0-9a-f]{4,})\*/\s+(.*?);", l)
     if m:
@@ -46,7 +46,20 @@ for (addr, line, txt), r in zip(seq, data):
     by[line][1] += th
     by[line][2] += sm
     tot += ex
-src = open(os.path.join(root, "nvimagecodec_b200", "csrc", "kernels.cu")).read().split("\n")
+srcdir = os.environ.get("B200JPEG_SRC") or os.path.join(root, "nvimagecodec_b200", "csrc")
+files = {}
+
+
+def text(key):
+    if not key:
+        return ""
+    fn, ln = key
+    if fn not in files:
+        try:
+            files[fn] = open(os.path.join(srcdir, fn)).read().split("\n")
+        except Exception:
+            files[fn] = []
+    return "%s:%d %s" % (fn, ln, files[fn][ln - 1].strip()[:90] if ln - 1 < len(files[fn]) else "")
 print("sass instrs", len(seq), "ncu rows", len(data), "warp instrs", int(tot))
 for line, (ex, th, sm) in sorted(by.items(), key=lambda kv: -kv[1][0])[:top]:
-    print("%5s ex=%5.2f%% lanes=%4.1f samples=%6d | %s" % (line, 100 * ex / tot, th / ex if ex else 0, sm, src[line - 1].strip()[:100] if line else ""))
+    print("ex=%5.2f%% lanes=%4.1f samples=%6d | %s" % (100 * ex / tot, th / ex if ex else 0, sm, text(line)))
