@@ -759,9 +759,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 int per_strip_max = std::max(1, strip_px_max / mcu_w);
                 const int mode = im.color_mode;
                 int hh[3] = {im.h[0], im.h[1], im.h[2]}, vv[3] = {im.v[0], im.v[1], im.v[2]};
-                // three CTAs per SM: at most 72 KB of tiles each
                 while (per_strip_max > 1 &&
-                       pixels_tile_smem(mode == 1 ? 1 : 3, hh, vv, im.vmax, std::min(per_strip_max, cols), mode == 6 || mode == 8, mode == 7 || mode == 8) > 72 * 1024)
+                       pixels_tile_smem(mode == 1 ? 1 : 3, hh, vv, im.vmax, std::min(per_strip_max, cols), mode == 6 || mode == 8, mode == 7 || mode == 8) > pixels_smem_budget())
                     per_strip_max = (per_strip_max + 1) / 2;
                 const int n_strips = (cols + per_strip_max - 1) / per_strip_max;
                 im.px_n_strips = uint16_t(n_strips);
@@ -770,10 +769,10 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             }
         };
         long rows_total = 0;
-        tiles(2048, &rows_total);
+        tiles(pixels_strip_px(), &rows_total);
         const long fill = 148 * 4;
         if (rows_total > 0 && rows_total < fill)
-            tiles(rows_total >= fill / 4 ? 1024 : 512, &rows_total);
+            tiles(rows_total >= fill / 4 ? pixels_strip_px() / 2 : pixels_strip_px() / 4, &rows_total);
         const int band = int(std::max<long>(1, std::min<long>(64, rows_total / (fill * 3))));
         for (ImageDev& im : imgs_) {
             if (!im.px_n_cta)

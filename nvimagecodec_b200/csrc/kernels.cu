@@ -1901,6 +1901,9 @@ size_t pixels_tile_smem(int ncomp, const int* h, const int* v, int vmax, int str
     return (total + 15) / 16 * 16;
 }
 
+size_t pixels_smem_budget() { return size_t(216 * 1024) / kPxCtasPerSm; }
+int pixels_strip_px() { return kPxThreads >= 256 ? 2048 : 1024; }
+
 int launch_pixels(const BatchDev& b, bool redo_only, cudaStream_t s)
 {
     if (b.n_px_cta == 0)

@@ -150,6 +150,8 @@ int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s);   // K4a
 int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s);  // K4b
 int launch_pixels(const BatchDev& b, bool redo_only, cudaStream_t s); // K4 fused (IDCT + upsampling + colour)
 size_t pixels_tile_smem(int ncomp, const int* h, const int* v, int vmax, int strip_mcus, bool fancy_h, bool fancy_v); // its shared memory for one tile shape
-constexpr size_t kPixelsMaxSmem = 96 * 1024; // tiles are cut so that two or three CTAs fit an SM
+constexpr size_t kPixelsMaxSmem = 96 * 1024; // hard limit of a tile; strips are cut to pixels_smem_budget()
+size_t pixels_smem_budget(); // shared memory a tile may take so that the intended number of CTAs fits an SM
+int pixels_strip_px();       // widest strip in luma pixels
 
 } // namespace b200jpeg

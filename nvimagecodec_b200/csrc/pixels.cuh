@@ -18,7 +18,11 @@
 // and right: a strip keeps the chroma of one more MCU column on each side.
 #pragma once
 
-constexpr int kPxThreads = 256;
+#ifndef B200_PX_THREADS
+#define B200_PX_THREADS 256
+#endif
+constexpr int kPxThreads = B200_PX_THREADS;
+constexpr int kPxCtasPerSm = kPxThreads >= 256 ? 3 : 6;
 constexpr int kPxUnit = 16; // pixels per thread and row in phase B
 constexpr int kPxApron = 16; // bytes before and after the samples of every plane row
 
@@ -42,10 +46,9 @@ struct PxTile {
 // Coefficients of one block (dense layout: 16-byte groups in zig-zag order, a mask of the groups K3 wrote, DC in the record),
 // as they lie in memory: w[j] = positions 2j (low half) and 2j + 1 (high half) of the zig-zag sequence; position 0 is not
 // stored there, the DC value comes back separately.
-__device__ __forceinline__ int32_t px_fetch_block(const int16_t* __restrict__ coef, const uint32_t* __restrict__ blkrec, size_t blk, uint32_t (&w)[32])
+__device__ __forceinline__ int32_t px_fetch_block(const int16_t* __restrict__ coef, uint32_t rec, size_t blk, uint32_t (&w)[32])
 {
     const uint4* s4 = reinterpret_cast<const uint4*>(coef) + blk * 8;
-    const uint32_t rec = __ldg(blkrec + blk);
     const uint32_t mask = rec & 0xFFu;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -91,21 +94,23 @@ __device__ __forceinline__ void px_idct_block(const uint32_t (&w)[32], int32_t d
     constexpr int kZzPos[64] = {0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43, 9, 11, 18, 24,
         31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60, 21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48,
         49, 57, 58, 62, 63};
+    constexpr int kNat[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21,
+        28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+    (void)kZzPos;
+    // dequantised coefficients in natural order, produced word by word so that the packed words die as they are consumed
     int32_t ws[64];
+    ws[0] = dc * int32_t(qz[0] & 0xFFu);
+    ws[kNat[1]] = px_dp2a_hi(w[0], qz[0]);
+#pragma unroll
+    for (int j = 1; j < 32; ++j) {
+        ws[kNat[2 * j]] = px_dp2a_lo(w[j], qz[j]);
+        ws[kNat[2 * j + 1]] = px_dp2a_hi(w[j], qz[j]);
+    }
+    // pass 1: columns, in place
 #pragma unroll
     for (int x = 0; x < 8; ++x) {
-        int32_t col[8], o[8];
-#pragma unroll
-        for (int y = 0; y < 8; ++y) {
-            const int z = kZzPos[y * 8 + x];
-            if (z == 0)
-                col[y] = dc * int32_t(qz[0] & 0xFFu);
-            else if (z & 1)
-                col[y] = px_dp2a_hi(w[z >> 1], qz[z >> 1]);
-            else
-                col[y] = px_dp2a_lo(w[z >> 1], qz[z >> 1]);
-        }
-        idct8<11, 0u>(col[0], col[1], col[2], col[3], col[4], col[5], col[6], col[7], o);
+        int32_t o[8];
+        idct8<11, 0u>(ws[x], ws[8 + x], ws[16 + x], ws[24 + x], ws[32 + x], ws[40 + x], ws[48 + x], ws[56 + x], o);
 #pragma unroll
         for (int y = 0; y < 8; ++y)
             ws[y * 8 + x] = o[y];
@@ -141,9 +146,10 @@ __device__ __noinline__ void px_idct_phase(const PxSource src, const PxTile& T, 
         n[c] = on ? (T.c[c].nbx << (kind == 0 ? T.c[c].lv : 0)) : 0;
     }
     const int total = n[0] + n[1] + n[2];
-#pragma unroll 1
-    for (int t = threadIdx.x; t < total; t += kPxThreads) {
-        int c = 0, local = t;
+    // item -> (component, block row, block column, block index)
+    auto locate = [&](int t, int& c, int& by, int& local) -> uint32_t {
+        c = 0;
+        local = t;
         if (local >= n[0]) {
             local -= n[0];
             c = 1;
@@ -152,8 +158,8 @@ __device__ __noinline__ void px_idct_phase(const PxSource src, const PxTile& T, 
                 c = 2;
             }
         }
-        const PxComp pc = T.c[c];
-        int by = 0; // block row inside the MCU row
+        const PxComp& pc = T.c[c];
+        by = 0; // block row inside the MCU row
         if (kind == 0) {
             if (local >= pc.nbx) { // sampling factors are 1 or 2 on this path
                 local -= pc.nbx;
@@ -165,16 +171,31 @@ __device__ __noinline__ void px_idct_phase(const PxSource src, const PxTile& T, 
         const int bx = pc.bx0 + local;
         const int mcu = bx >> pc.lh;
         const uint32_t bim = uint32_t(pc.first + (by << pc.lh) + (bx - (mcu << pc.lh)));
-        const uint32_t blk = (uint32_t(r) * src.mcus_x + uint32_t(mcu)) * src.bpm + bim;
+        return (uint32_t(r) * src.mcus_x + uint32_t(mcu)) * src.bpm + bim;
+    };
+    int c, by, local;
+    uint32_t blk = 0, rec = 0;
+    if (int(threadIdx.x) < total) {
+        blk = locate(threadIdx.x, c, by, local);
+        rec = __ldg(src.blkrec + src.blk0 + blk);
+    }
+#pragma unroll 1
+    for (int t = threadIdx.x; t < total; t += kPxThreads) {
+        const PxComp pc = T.c[c];
         uint32_t w[32];
-        const int32_t dc = px_fetch_block(src.coef, src.blkrec, src.blk0 + blk, w);
+        const int32_t dc = px_fetch_block(src.coef, rec, src.blk0 + blk, w);
         const uint32_t dst = smem + uint32_t(pc.off + (T.carry + by * 8) * pc.stride + kPxApron + local * 8);
+        const int cq = c;
+        if (t + kPxThreads < total) { // the next item's record travels while this block is transformed
+            blk = locate(t + kPxThreads, c, by, local);
+            rec = __ldg(src.blkrec + src.blk0 + blk);
+        }
         if (kind == 0)
-            px_idct_block<0>(w, dc, s_qz[c], dst, pc.stride);
+            px_idct_block<0>(w, dc, s_qz[cq], dst, pc.stride);
         else if (kind == 1)
-            px_idct_block<1>(w, dc, s_qz[c], dst, pc.stride);
+            px_idct_block<1>(w, dc, s_qz[cq], dst, pc.stride);
         else
-            px_idct_block<2>(w, dc, s_qz[c], dst, pc.stride);
+            px_idct_block<2>(w, dc, s_qz[cq], dst, pc.stride);
     }
 }
 
@@ -239,12 +260,10 @@ __device__ __forceinline__ void px_horizontal_h2(const int* s, int g, int* out)
     }
 }
 
-// How the three output channels are made from (luma << 16, chroma A, chroma B): channel 0 = y + ka * a,
-// channel 2 = y + kb * b, channel 1 = y + ga * a + gb * b (constants 16 bits up, the -128 and the rounding folded in).
-// RGB order: a = Cr, b = Cb; BGR order: a = Cb, b = Cr -- swapping the planes instead of the results costs nothing per pixel.
+// Output layout of an image, uniform over the CTA.  The colour transform itself always runs in R, G, B terms with
+// immediate constants (16 bits up, the -128 and the rounding folded in); BGR only changes the order of packing.
 struct PxColor {
-    int ka, ca, kb, cb, ga, gb, cg;
-    int plane_a, plane_b; // component index of chroma A / B
+    int bgr;              // 1: channel 0 is blue
     int yuv;              // 1: no transform (Y, Cb, Cr as they are)
     int planar;           // 1: one plane per channel (or the single plane of Y output)
     int nch;              // planes to write
@@ -253,22 +272,8 @@ struct PxColor {
 __device__ __forceinline__ PxColor px_color_setup(int fmt)
 {
     PxColor k;
-    const bool bgr = (fmt == kFmtIBGR || fmt == kFmtPBGR);
-    constexpr int kRr = 91881, kBb = 116130, kGb = -22554, kGr = -46802;
-    k.ka = bgr ? kBb : kRr;
-    k.kb = bgr ? kRr : kBb;
-    k.ca = 32768 - 128 * k.ka;
-    k.cb = 32768 - 128 * k.kb;
-    k.ga = bgr ? kGb : kGr;
-    k.gb = bgr ? kGr : kGb;
-    k.cg = 32768 - 128 * (kGb + kGr);
-    k.plane_a = bgr ? 1 : 2;
-    k.plane_b = bgr ? 2 : 1;
+    k.bgr = (fmt == kFmtIBGR || fmt == kFmtPBGR) ? 1 : 0;
     k.yuv = (fmt == kFmtIYUV || fmt == kFmtPYUV) ? 1 : 0;
-    if (k.yuv) {
-        k.plane_a = 1;
-        k.plane_b = 2;
-    }
     k.planar = (fmt == kFmtY || fmt == kFmtPRGB || fmt == kFmtPBGR || fmt == kFmtPYUV) ? 1 : 0;
     k.nch = (fmt == kFmtY) ? 1 : 3;
     return k;
@@ -348,8 +353,9 @@ __device__ __forceinline__ void px_color_phase(const PxOut& im, const PxTile& T,
     const uint8_t* p0 = smem + T.c[0].off + kPxApron;
     const int cstride = kLumaOnly ? 0 : T.c[1].stride;
     // sample column of the strip's first pixel inside the chroma planes
-    const uint8_t* pa = kLumaOnly ? p0 : smem + T.c[K.plane_a].off + kPxApron + (X_strip / HX - T.c[1].bx0 * 8);
-    const ptrdiff_t a_to_b = kLumaOnly ? 0 : ptrdiff_t(T.c[K.plane_b].off) - ptrdiff_t(T.c[K.plane_a].off);
+    // plane a = Cb, plane b = Cr
+    const uint8_t* pa = kLumaOnly ? p0 : smem + T.c[1].off + kPxApron + (X_strip / HX - T.c[1].bx0 * 8);
+    const ptrdiff_t a_to_b = kLumaOnly ? 0 : ptrdiff_t(T.c[2].off) - ptrdiff_t(T.c[1].off);
     const int roi_x0 = im.roi_x0, roi_x1 = im.roi_x1, roi_y0 = im.roi_y0;
 #pragma unroll 1
     for (int m = warp; m < T.urows; m += kPxThreads / 32) {
@@ -463,20 +469,26 @@ __device__ __forceinline__ void px_color_phase(const PxOut& im, const PxTile& T,
                                     c2[k] = uint32_t(ub[k]) << 16;
                                 }
                             } else {
-                                // one descriptor-dependent operand per instruction: the sums are the same in any order
+                                // jdcolor.c 16 bits up: ua = Cb, ub = Cr
+                                constexpr int kR = 32768 - 128 * 91881, kG = 32768 + 128 * (22554 + 46802), kB = 32768 - 128 * 116130;
 #pragma unroll
                                 for (int k = 0; k < 4; ++k) {
                                     const int yk = int(c0[k]);
-                                    c0[k] = uint32_t(__viaddmin_s32_relu(K.ka * ua[k] + yk, K.ca, 0xFFFFFF));
-                                    c1[k] = uint32_t(__viaddmin_s32_relu(K.gb * ub[k] + (K.ga * ua[k] + yk), K.cg, 0xFFFFFF));
-                                    c2[k] = uint32_t(__viaddmin_s32_relu(K.kb * ub[k] + yk, K.cb, 0xFFFFFF));
+                                    c0[k] = uint32_t(__viaddmin_s32_relu(91881 * ub[k] + yk, kR, 0xFFFFFF));
+                                    c1[k] = uint32_t(__viaddmin_s32_relu(-46802 * ub[k] + (-22554 * ua[k] + yk), kG, 0xFFFFFF));
+                                    c2[k] = uint32_t(__viaddmin_s32_relu(116130 * ua[k] + yk, kB, 0xFFFFFF));
                                 }
                             }
                         }
                         if (K.planar) {
-                            pk[g] = pack_b2(c0[0], c0[1], c0[2], c0[3]);
+                            const uint32_t p0w = pack_b2(c0[0], c0[1], c0[2], c0[3]), p2w = pack_b2(c2[0], c2[1], c2[2], c2[3]);
+                            pk[g] = K.bgr ? p2w : p0w;
                             pk[2 + g] = pack_b2(c1[0], c1[1], c1[2], c1[3]);
-                            pk[4 + g] = pack_b2(c2[0], c2[1], c2[2], c2[3]);
+                            pk[4 + g] = K.bgr ? p0w : p2w;
+                        } else if (K.bgr) {
+                            pk[3 * g + 0] = pack_b2(c2[0], c1[0], c0[0], c2[1]);
+                            pk[3 * g + 1] = pack_b2(c1[1], c0[1], c2[2], c1[2]);
+                            pk[3 * g + 2] = pack_b2(c0[2], c2[3], c1[3], c0[3]);
                         } else {
                             pk[3 * g + 0] = pack_b2(c0[0], c1[0], c2[0], c0[1]);
                             pk[3 * g + 1] = pack_b2(c1[1], c2[1], c0[2], c1[2]);
@@ -508,7 +520,7 @@ __device__ __forceinline__ void px_edge_phase(const PxTile& T, uint8_t* smem, in
     }
 }
 
-__global__ void __launch_bounds__(kPxThreads, 3) pixels_kernel(BatchDev bd, int redo_only)
+__global__ void __launch_bounds__(kPxThreads, kPxCtasPerSm) pixels_kernel(BatchDev bd, int redo_only)
 {
     extern __shared__ uint4 s_px_raw[];
     __shared__ uint32_t s_qz[3][32];
