@@ -742,38 +742,40 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     algo_bytes_ = comp_bytes_ + 4 * n_coefs_ + out_bytes_;
     const int nd = int(imgs_.size());
 
-    // ---- tiles of the fused pixel kernel.  Strips are at most 2048 luma pixels wide (so that the component tiles of an MCU
-    // row fit in shared memory with two or three CTAs per SM), narrower when the batch is too small to fill the GPU
-    // otherwise; bands are as tall as still leaves every SM a few CTAs (tall bands amortise the extra chroma rows the
-    // vertical triangle filter needs at a band's top and bottom).
+    // ---- tiles of the fused pixel kernel: one per warp.  A strip is as wide as gives the warp three full passes of blocks per
+    // MCU row (96 blocks, the chroma of the two neighbouring MCU columns included where the horizontal triangle filter
+    // needs it), narrower if its component tiles would not fit the warp's share of shared memory; bands are as tall as
+    // still leaves every SM several waves of warps (tall bands amortise the extra chroma rows the vertical triangle
+    // filter needs at a band's top and bottom).
     uint32_t n_px = 0;
     size_t px_smem = 0;
     {
-        auto tiles = [&](int strip_px_max, long* rows_total) {
-            *rows_total = 0;
-            for (ImageDev& im : imgs_) {
-                if (!im.px_n_cta)
-                    continue;
-                const int mcu_w = 8 * im.hmax;
-                const int cols = im.px_mcu_col_hi - im.px_mcu_col_lo;
-                int per_strip_max = std::max(1, strip_px_max / mcu_w);
-                const int mode = im.color_mode;
-                int hh[3] = {im.h[0], im.h[1], im.h[2]}, vv[3] = {im.v[0], im.v[1], im.v[2]};
-                while (per_strip_max > 1 &&
-                       pixels_tile_smem(mode == 1 ? 1 : 3, hh, vv, im.vmax, std::min(per_strip_max, cols), mode == 6 || mode == 8, mode == 7 || mode == 8) > pixels_smem_budget())
-                    per_strip_max = (per_strip_max + 1) / 2;
-                const int n_strips = (cols + per_strip_max - 1) / per_strip_max;
-                im.px_n_strips = uint16_t(n_strips);
-                im.px_strip_mcus = uint16_t((cols + n_strips - 1) / n_strips);
-                *rows_total += long(n_strips) * (im.px_mcu_row_hi - im.px_mcu_row_lo);
-            }
-        };
         long rows_total = 0;
-        tiles(pixels_strip_px(), &rows_total);
-        const long fill = 148 * 4;
-        if (rows_total > 0 && rows_total < fill)
-            tiles(rows_total >= fill / 4 ? pixels_strip_px() / 2 : pixels_strip_px() / 4, &rows_total);
-        const int band = int(std::max<long>(1, std::min<long>(64, rows_total / (fill * 3))));
+        for (ImageDev& im : imgs_) {
+            if (!im.px_n_cta)
+                continue;
+            const int mode = im.color_mode;
+            const bool fancy_h = mode == 6 || mode == 8, fancy_v = mode == 7 || mode == 8;
+            const int ncomp = mode == 1 ? 1 : 3;
+            int hh[3] = {im.h[0], im.h[1], im.h[2]}, vv[3] = {im.v[0], im.v[1], im.v[2]};
+            int bpm_held = 0, halo = 0;
+            for (int c = 0; c < ncomp; ++c) {
+                bpm_held += hh[c] * vv[c];
+                if (c > 0 && fancy_h)
+                    halo += 2 * hh[c] * vv[c];
+            }
+            const int cols = im.px_mcu_col_hi - im.px_mcu_col_lo;
+            int per_strip = std::min(cols, pixels_strip_mcus(bpm_held, halo));
+            while (per_strip > 1 && pixels_tile_smem(ncomp, hh, vv, im.vmax, per_strip, fancy_h, fancy_v) > pixels_smem_budget())
+                --per_strip;
+            const int n_strips = (cols + per_strip - 1) / per_strip;
+            im.px_n_strips = uint16_t(n_strips);
+            im.px_strip_mcus = uint16_t(per_strip); // (not evened out: full strips keep the passes full, the last one takes the rest)
+            rows_total += long(n_strips) * (im.px_mcu_row_hi - im.px_mcu_row_lo);
+            px_smem = std::max(px_smem, pixels_tile_smem(ncomp, hh, vv, im.vmax, per_strip, fancy_h, fancy_v));
+        }
+        const long waves = 148L * 24 * 4; // warps an SM holds x a few rounds
+        const int band = int(std::max<long>(1, std::min<long>(64, rows_total / waves)));
         for (ImageDev& im : imgs_) {
             if (!im.px_n_cta)
                 continue;
@@ -784,12 +786,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             im.px_cta_off = n_px;
             im.px_n_cta = uint32_t(im.px_n_bands) * im.px_n_strips;
             n_px += im.px_n_cta;
-            const int mode = im.color_mode;
-            const bool fancy_h = mode == 6 || mode == 8, fancy_v = mode == 7 || mode == 8;
-            int hh[3] = {im.h[0], im.h[1], im.h[2]}, vv[3] = {im.v[0], im.v[1], im.v[2]};
-            px_smem = std::max(px_smem, pixels_tile_smem(mode == 1 ? 1 : 3, hh, vv, im.vmax, im.px_strip_mcus, fancy_h, fancy_v));
         }
-        if (px_smem > kPixelsMaxSmem)
+        if (px_smem > pixels_smem_budget())
             return fail(B200JPEG_ERR_STATE, "pixel tile exceeds its shared-memory budget");
     }
 
@@ -973,7 +971,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.idct_cta_img = reinterpret_cast<const uint32_t*>(dv + off_idct);
     bd_.color_cta_img = reinterpret_cast<const uint32_t*>(dv + off_color);
     bd_.px_cta_img = reinterpret_cast<const uint32_t*>(dv + off_px);
-    bd_.n_px_cta = int(n_px);
+    bd_.n_px_task = int(n_px);
     bd_.px_smem = uint32_t(px_smem);
     bd_.gate = reinterpret_cast<const uint32_t*>(dv + off_gate);
     bd_.n_multi = 0;

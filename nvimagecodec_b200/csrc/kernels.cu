@@ -13,6 +13,8 @@
 // No tensor cores: the work is bit-serial entropy decode and 8x8 integer butterflies.
 #include "kernels.cuh"
 
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -354,6 +356,7 @@ struct StreamView {
     uint32_t blk_base;
     uint32_t write_lo;           // AC coefficients are wanted from here (first MCU row a ROI touches) ...
     uint32_t dc_lo, dc_span;     // ... DC differences in [dc_lo, dc_lo + dc_span): the chain K3b integrates, up to the last wanted row
+    uint32_t bit_base;           // subtracted from bit positions stored in blkpos (0: positions are relative to the image's stream)
 };
 
 // Coefficient block assembly for K3: the 64 int16 of the block being decoded are emitted as
@@ -710,6 +713,7 @@ __device__ __forceinline__ StreamView make_view(const BatchDev& bd, const ImageD
     sv.write_lo = im.write_blk_lo;
     sv.dc_lo = im.dc_blk_lo;
     sv.dc_span = im.write_blk_hi - im.dc_blk_lo;
+    sv.bit_base = 0;
     return sv;
 }
 
@@ -1002,6 +1006,206 @@ __global__ void __launch_bounds__(kSeqThreads, 5) huff_write_kernel(BatchDev bd,
     } else {
         decode_subsequence<true>(sv, s_hs, s_bt, k * bd.sub_bits, (k + 1) * bd.sub_bits, in, int32_t(sv.blk_base + start), bd.coef, bd.blkrec, res);
         err |= res.err;
+    }
+    if (err)
+        atomicOr(&bd.state[img].flags, err);
+}
+
+// K3, entry-stream form.  Every thread decodes exactly the code words that start in its subsequence (as K1 does: no block
+// ownership, nothing is decoded twice) and writes one 16-bit entry per loop iteration, whatever the iteration met; the
+// eight entries of a chunk sit at fixed places of four registers (the chunk loop is unrolled), and the lanes of a warp
+// store their chunks side by side -- 512 contiguous bytes per warp and chunk row.  Nothing depends on the symbol but the
+// entry's value: no group stores, no per-block flush, the end of a block is a predicated table switch as in K1.  The one
+// scattered store left is the block record at a DC symbol (entry slot + DC difference, and the bit position in blkpos).
+constexpr uint32_t kEntEob = 0x0000u, kEntNop = 0x1000u, kEntEnd = 0x2000u, kEntZrl = 0xF000u;
+
+__device__ __forceinline__ uint32_t emit_subsequence(const StreamView& sv, const HuffSetDev* __restrict__ hs, const BlockTable* __restrict__ bt,
+    uint32_t base_bit, uint32_t end_bit, uint32_t in_state, int32_t blk, uint32_t* __restrict__ blkrec, uint32_t* __restrict__ blkpos,
+    uint4* __restrict__ out, uint32_t max_chunks)
+{
+    uint32_t err = 0;
+    if (in_state & kStateDone) { // past the end of the stream: an empty entry list
+        out[0] = make_uint4(kEntEnd | (kEntNop << 16), kEntNop * 0x10001u, kEntNop * 0x10001u, kEntNop * 0x10001u);
+        return 0;
+    }
+    uint32_t p = base_bit + (in_state & 63u);
+    uint32_t z = (in_state >> 6) & 63u;
+    uint32_t r = 0; // first boundary strictly after p
+    if (sv.nb > 1) {
+        uint32_t lo = 0, hi = sv.nb - 1;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(sv.bnd + mid) * 8u > p)
+                hi = mid;
+            else
+                lo = mid + 1;
+        }
+        r = lo;
+    }
+    uint32_t next_bnd = (r == sv.nb - 1) ? sv.total_bits : __ldg(sv.bnd + r) * 8u;
+    uint32_t limit = min(end_bit, max(next_bnd, 7u) - 7u);
+    const uint32_t s_hs = smem_addr(hs), s_bt = smem_addr(bt);
+    BitReader br;
+    br.seek(sv.words, p);
+    uint4 bi = lds_v4(s_bt + ((in_state >> 12) & 15u) * 16u);
+    uint32_t taddr = (z == 0u) ? bi.x : bi.y;
+    uint32_t win = br.window(p);
+    bool running = true;
+#pragma unroll 1
+    for (uint32_t c = 0;; ++c) {
+        uint32_t q[4] = {kEntNop * 0x10001u, kEntNop * 0x10001u, kEntNop * 0x10001u, kEntNop * 0x10001u};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (!running)
+                continue;
+            uint32_t ent = kEntNop;
+            bool symbol = true;
+            if (p >= limit) {
+                // End of a restart interval (or of the stream): the decoder ran across the boundary, or fewer than 8 bits
+                // remain and they are all 1-bits (the byte-alignment padding of T.81 F.1.2.3), see decode_subsequence.
+                bool at_boundary = false;
+                if (p + 7u >= next_bnd) {
+                    const uint32_t rem = next_bnd - p;
+                    at_boundary = p >= next_bnd || (win >> (32u - rem)) == ((1u << rem) - 1u);
+                }
+                if (at_boundary) {
+                    symbol = false;
+                    if (r == sv.nb - 1) { // end of the stream
+                        if (z != 0u || uint32_t(blk) != sv.blk_base + sv.total_blocks)
+                            err |= kFlagOverrun;
+                        ent = kEntEnd;
+                        running = false;
+                    } else {
+                        p = next_bnd;
+                        ++r;
+                        next_bnd = (r == sv.nb - 1) ? sv.total_bits : __ldg(sv.bnd + r) * 8u;
+                        limit = min(end_bit, max(next_bnd, 7u) - 7u);
+                        if (z != 0u || ((bi.w >> 8) & 15u) != 0u || uint32_t(blk) != sv.blk_base + r * sv.ri_blocks)
+                            err |= kFlagOverrun;
+                        blk = int32_t(sv.blk_base + r * sv.ri_blocks);
+                        z = 0;
+                        bi = lds_v4(s_bt);
+                        taddr = bi.x;
+                        br.seek(sv.words, p);
+                        win = br.window(p);
+                        if (p >= end_bit) { // the interval that starts here belongs to the next subsequence
+                            ent = kEntEnd;
+                            running = false;
+                        }
+                    }
+                } else if (p >= end_bit) {
+                    symbol = false;
+                    ent = kEntEnd;
+                    running = false;
+                }
+            }
+            if (symbol) {
+                const bool is_dc = (z == 0u);
+                uint32_t e = lds_u16(taddr + ((win >> (31 - kLutBits)) & ((2u << kLutBits) - 2u)));
+                if ((e & 31u) == 0u) {
+                    const HuffTableDev* tab = reinterpret_cast<const HuffTableDev*>(reinterpret_cast<const uint8_t*>(hs) + (taddr - s_hs));
+                    const uint32_t i2 = (win >> 16) - tab->first16;
+                    e = (i2 < tab->n2) ? tab->lut2[i2] : 0u;
+                    if (tab->n2 == 0u && (win >> 16) >= tab->first16) {
+#pragma unroll 1
+                        for (int l = kLutBits + 1; l <= 16; ++l) {
+                            const int32_t code = int32_t(win >> (32 - l));
+                            if (code <= tab->maxcode[l]) {
+                                e = tab->sym[(tab->valoff[l] + code) & 255];
+                                break;
+                            }
+                        }
+                    }
+                    if ((e & 31u) == 0u) {
+                        e = 16u | (1u << 9);
+                        err |= kFlagBadHuffman;
+                    }
+                }
+                const uint32_t tot = e & 31u, size = (e >> 5) & 15u, skip = e >> 9;
+                const uint32_t p_sym = p;
+                br.advance(p, p + tot);
+                p += tot;
+                const uint32_t rest = win << (tot - size);
+                const uint32_t mag = __funnelshift_l(rest, 0u, size);
+                const int32_t val = (rest >> 31) ? int32_t(mag) : int32_t(mag) - int32_t((1u << size) - 1u);
+                if (is_dc) {
+                    // block record: where the block's entries start (this slot, which itself stays a no-op) and its DC difference
+                    if (uint32_t(blk) - sv.dc_lo < sv.dc_span && (bi.w & (1u << 24))) {
+                        blkrec[blk] = (c * 8u + uint32_t(j)) | (uint32_t(val) << 16);
+                        blkpos[blk] = p_sym - sv.bit_base;
+                    }
+                } else if (size != 0u) {
+                    err |= (z + skip - 1u > 63u) ? uint32_t(kFlagBadHuffman) : 0u;
+                    ent = ((skip - 1u) << 12) | (uint32_t(val) & 0xFFFu);
+                } else {
+                    ent = (skip == 16u) ? kEntZrl : kEntEob;
+                }
+                z += skip;
+                asm("{\n\t.reg .pred q;\n\t"
+                    "setp.gt.u32 q, %4, 63;\n\t"
+                    "@q ld.shared.v4.u32 {%0,%1,%2,%3}, [%2];\n\t}"
+                    : "+r"(bi.x), "+r"(bi.y), "+r"(bi.z), "+r"(bi.w)
+                    : "r"(z));
+                blk += (z > 63u) ? 1 : 0;
+                z = (z > 63u) ? 0u : z;
+                taddr = (z == 0u) ? bi.x : bi.y;
+                win = br.window(p);
+            }
+            if (j & 1)
+                q[j >> 1] = (q[j >> 1] & 0xFFFFu) | (ent << 16);
+            else
+                q[j >> 1] = (q[j >> 1] & 0xFFFF0000u) | ent;
+        }
+        if (c < max_chunks) {
+            out[size_t(c) * 32] = make_uint4(q[0], q[1], q[2], q[3]);
+        } else { // more entries than a subsequence can legitimately have: damaged data
+            err |= kFlagOverrun;
+            break;
+        }
+        if (!running)
+            break;
+    }
+    return err;
+}
+
+__global__ void __launch_bounds__(kSeqThreads, 5) huff_emit_kernel(BatchDev bd, int redo_only)
+{
+    extern __shared__ uint4 s_raw[];
+    HuffSetDev* s_hs = reinterpret_cast<HuffSetDev*>(s_raw);
+    BlockTable* s_bt = reinterpret_cast<BlockTable*>(reinterpret_cast<uint8_t*>(s_raw) + sizeof(HuffSetDev));
+    const uint32_t cta = blockIdx.x;
+    const uint32_t img = bd.wseq_img[cta];
+    const ImageDev& im = bd.img[img];
+    const ImageState st = bd.state[img];
+    if (st.n_sub == 0u || (st.flags & kFlagDirty) || (redo_only && !(st.flags & kFlagRedo)))
+        return;
+    const uint32_t first_k = (cta - im.wseq_off) * kSeqThreads;
+    if (first_k >= st.n_sub)
+        return;
+    load_huff_set(s_hs, bd.huff + im.huff_set);
+    build_block_table(s_bt, s_hs, im);
+    __syncthreads();
+    const uint32_t k = first_k + threadIdx.x;
+    if (k >= st.n_sub)
+        return;
+    StreamView sv = make_view(bd, im, st);
+    sv.blk_base = uint32_t(im.coef_off / 64); // blocks are counted in the batch's arena from here on
+    sv.dc_lo += sv.blk_base;
+    const uint32_t g = im.sub_off + k;
+    const uint32_t in = bd.sub_in[g];
+    const uint32_t start = bd.sub_start[g];
+    // ROI: threads whose blocks all lie past the wanted MCU rows, or before the restart interval they start in, have nothing to
+    // contribute (no wanted block continues into them either: the block under way at their entry is `start`)
+    const uint32_t next_start = (k + 1 < st.n_sub) ? bd.sub_start[g + 1] : im.total_blocks;
+    if (start >= im.write_blk_hi || next_start < im.dc_blk_lo)
+        return;
+    uint32_t err = 0;
+    if (!(in & kStateDone) && (start % im.bpm) != ((in >> 12) & 15u)) {
+        err |= kFlagPhase;
+    } else {
+        uint4* out = bd.sym + im.sym_off + size_t(k >> 5) * bd.sym_chunks * 32 + (k & 31u);
+        err |= emit_subsequence(sv, s_hs, s_bt, k * bd.sub_bits, (k + 1) * bd.sub_bits, in, int32_t(sv.blk_base + start), bd.blkrec, bd.blkpos, out,
+            bd.sym_chunks);
     }
     if (err)
         atomicOr(&bd.state[img].flags, err);
@@ -1832,6 +2036,7 @@ int launch_sync(const BatchDev& b, bool fix_mode, bool no_warm, cudaStream_t s)
         cudaFuncSetAttribute(huff_sync_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSyncSmem));
         cudaFuncSetAttribute(huff_sync_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSyncSmem));
         cudaFuncSetAttribute(huff_write_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kWriteSmem));
+        cudaFuncSetAttribute(huff_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kWriteSmem));
         attr_set[dev] = true;
     }
     const int mode = (fix_mode ? 1 : 0) | (no_warm ? 2 : 0);
@@ -1854,7 +2059,10 @@ int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s)
 {
     if (b.n_wseq == 0)
         return 0;
-    huff_write_kernel<<<b.n_wseq, kSeqThreads, kWriteSmem, s>>>(b, redo_only ? 1 : 0);
+    if (b.sym_mode)
+        huff_emit_kernel<<<b.n_wseq, kSeqThreads, kWriteSmem, s>>>(b, redo_only ? 1 : 0);
+    else
+        huff_write_kernel<<<b.n_wseq, kSeqThreads, kWriteSmem, s>>>(b, redo_only ? 1 : 0);
     return 1;
 }
 
@@ -1901,21 +2109,26 @@ size_t pixels_tile_smem(int ncomp, const int* h, const int* v, int vmax, int str
     return (total + 15) / 16 * 16;
 }
 
-size_t pixels_smem_budget() { return size_t(216 * 1024) / kPxCtasPerSm; }
-int pixels_strip_px() { return kPxThreads >= 256 ? 2048 : 1024; }
+// A loop iteration of K3 consumes at least one bit (the shortest code) or hops over a restart boundary (at most one per byte);
+// one more entry ends the list.
+uint32_t sym_chunks_for(uint32_t sub_bits) { return (sub_bits + sub_bits / 8 + 16 + 7) / 8; }
+
+size_t pixels_smem_budget() { return (size_t(227 - 5 * kPxCtasPerSm) * 1024 / (kPxCtasPerSm * kPxWarps)) / 256 * 256; } // 8704 bytes per warp at 3 x 8 warps
+int pixels_strip_mcus(int bpm_held, int halo_blocks) { return std::max(1, (96 - halo_blocks) / std::max(1, bpm_held)); }
 
 int launch_pixels(const BatchDev& b, bool redo_only, cudaStream_t s)
 {
-    if (b.n_px_cta == 0)
+    if (b.n_px_task == 0)
         return 0;
     static bool attr_set[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        cudaFuncSetAttribute(pixels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kPixelsMaxSmem));
+        cudaFuncSetAttribute(pixels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pixels_smem_budget() * kPxWarps));
         attr_set[dev] = true;
     }
-    pixels_kernel<<<b.n_px_cta, kPxThreads, b.px_smem, s>>>(b, redo_only ? 1 : 0);
+    static const int debug = std::getenv("B200JPEG_PX_DEBUG") ? std::atoi(std::getenv("B200JPEG_PX_DEBUG")) : 0; // 2: no phase B, 4: no phase A (timing experiments)
+    pixels_kernel<<<(b.n_px_task + kPxWarps - 1) / kPxWarps, kPxThreads, size_t(b.px_smem) * kPxWarps, s>>>(b, (redo_only ? 1 : 0) | debug);
     return 1;
 }
 

@@ -49,7 +49,8 @@ struct ImageDev {
     // stream geometry
     uint64_t raw_off;   // bytes into the raw (byte-stuffed) arena, 16-aligned
     uint64_t cmp_off;   // bytes into the unstuffed arena, 16-aligned
-    uint64_t coef_off;  // int16 elements into the coefficient arena
+    uint64_t coef_off;  // int16 elements into the coefficient arena (block index * 64; also locates the block records)
+    uint64_t sym_off;   // 16-byte chunks into the entry-stream arena (entry-stream form of K3)
     uint64_t plane_off[3]; // bytes into the plane arena
     uint32_t raw_len;
     uint32_t tile_off, n_tiles;     // K0 tiles
@@ -70,8 +71,9 @@ struct ImageDev {
     uint32_t idct_cta_off, n_idct_cta;
     uint32_t color_cta_off, n_color_cta_x, n_color_cta_y;
     uint32_t color_cta_x_rcp;       // ceil(2^32 / n_color_cta_x): cta -> (row, column) without a division
-    // fused pixel kernel (K4): tiles = strips of MCU columns x bands of MCU rows over the MCUs the region of interest touches;
-    // px_n_cta == 0: the image goes through the idct + color kernels instead (generic sampling, EXIF orientation, three-scan streams)
+    // fused pixel kernel (K4): tiles (one per warp) = strips of MCU columns x bands of MCU rows over the MCUs the region of interest
+    // touches; px_n_cta tiles from px_cta_off on; 0: the image goes through the idct + color kernels instead (generic sampling,
+    // EXIF orientation, three-scan streams)
     uint32_t px_cta_off, px_n_cta;
     uint16_t px_strip_mcus, px_n_strips, px_band_rows, px_n_bands;
     uint16_t px_mcu_col_lo, px_mcu_col_hi, px_mcu_row_lo, px_mcu_row_hi;
@@ -122,6 +124,18 @@ struct BatchDev {
     uint32_t* sub_start;    // exclusive scan: absolute block index at entry
     const HuffSetDev* huff;
     int16_t* coef;
+    // Entry-stream form of the coefficients (K3 huff_emit / the walkers of K4): every subsequence thread of K3 writes one
+    // 16-bit entry per decoded symbol -- run << 12 | value (12 bits, signed) for a coefficient, 0x0000 end of block,
+    // 0xF000 sixteen zeros, 0x1000 nothing (DC symbols, restart hops), 0x2000 end of the subsequence's entries -- in chunks
+    // of eight (16 bytes).  The chunks of the 32 subsequences of a warp interleave, so that a warp's store of a chunk row
+    // is 512 contiguous bytes: chunk c of subsequence k of an image lies at sym[sym_off + ((k >> 5) * sym_chunks + c) * 32 + (k & 31)].
+    // blkpos[block] = bit position of the block's DC code word (-> the subsequence that holds it), the low half of
+    // blkrec[block] = the entry slot of that DC symbol inside the subsequence.
+    uint4* sym;
+    uint32_t* blkpos;
+    uint32_t sym_chunks;    // chunks reserved per subsequence
+    uint32_t sub_shift;     // log2(sub_bits)
+    int sym_mode;           // 1: entry-stream form, 0: dense 16-byte coefficient groups
     uint32_t* blkrec;       // per coefficient block: bits 0-7 which of its eight 16-byte groups K3 wrote (bit g = group g),
                             // bits 16-31 its DC: the coded difference out of K3, the value after K3b
     uint8_t* planes;
@@ -129,9 +143,9 @@ struct BatchDev {
     int4* dc_sum;                 // K3b: per chunk (reset seen, DC sums of the three components)
     const uint32_t* idct_cta_img;
     const uint32_t* color_cta_img;
-    const uint32_t* px_cta_img;   // fused pixel kernel CTA -> image
-    int n_px_cta;
-    uint32_t px_smem;             // dynamic shared memory of the fused pixel kernel: the largest tile of the batch
+    const uint32_t* px_cta_img;   // fused pixel kernel: tile (one per warp) -> image
+    int n_px_task;                // tiles
+    uint32_t px_smem;             // shared memory per warp of the fused pixel kernel: the largest tile of the batch
     const uint32_t* gate;         // three image indices per image, see ImageDev::multi
     int n_tiles, n_seq, n_wseq, n_sub, n_dc_cta, n_idct_cta, n_color_cta;
     int n_multi;            // images with ImageDev::multi set
@@ -144,14 +158,15 @@ struct BatchDev {
 int launch_scan(const BatchDev& b, cudaStream_t s);                 // K0a, K0b, K0c
 int launch_sync(const BatchDev& b, bool fix_mode, bool no_warm, cudaStream_t s); // K1 (first pass or fix-up pass)
 int launch_verify_scan(const BatchDev& b, bool fix_mode, cudaStream_t s); // K2
-int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s);  // K3
+int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s);  // K3 (dense groups or entry stream, by b.sym_mode)
+uint32_t sym_chunks_for(uint32_t sub_bits); // chunks of eight entries a subsequence of that many bits can need at most
 int launch_dc_scan(const BatchDev& b, bool redo_only, cudaStream_t s); // K3b
 int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s);   // K4a
 int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s);  // K4b
 int launch_pixels(const BatchDev& b, bool redo_only, cudaStream_t s); // K4 fused (IDCT + upsampling + colour)
 size_t pixels_tile_smem(int ncomp, const int* h, const int* v, int vmax, int strip_mcus, bool fancy_h, bool fancy_v); // its shared memory for one tile shape
 constexpr size_t kPixelsMaxSmem = 96 * 1024; // hard limit of a tile; strips are cut to pixels_smem_budget()
-size_t pixels_smem_budget(); // shared memory a tile may take so that the intended number of CTAs fits an SM
-int pixels_strip_px();       // widest strip in luma pixels
+size_t pixels_smem_budget(); // shared memory a warp's tile may take so that the intended number of warps fits an SM
+int pixels_strip_mcus(int bpm_held, int halo_blocks); // MCUs per strip: three full passes of blocks per warp and step
 
 } // namespace b200jpeg

@@ -5,12 +5,15 @@
 // Replaces the scanline loop of the reference's CPU path (extensions/libjpeg_turbo/jpeg_mem.cpp:311-379 driving
 // libjpeg-turbo's jidctint / jdsample / jdcolor); the component planes never leave the SM.
 //
-// One CTA owns a tile: a strip of MCU columns x a band of MCU rows of one image, and walks the band top to bottom, one
+// One WARP owns a tile: a strip of MCU columns x a band of MCU rows of one image, and walks the band top to bottom, one
 // MCU row per step:
-//   phase A  every thread takes 8x8 blocks of that MCU row: coefficients -> registers -> IDCT -> 8-byte row stores
-//            into the component tiles in shared memory;
-//   phase B  every thread takes units of 16 pixels x (1 or 2) rows: luma and chroma from shared memory, triangle or box
-//            upsampling, colour transform, three 16-byte stores per row (interleaved RGB).
+//   phase A  every lane takes 8x8 blocks of that MCU row: coefficients -> registers -> IDCT -> 8-byte row stores
+//            into the warp's component tiles in shared memory;
+//   phase B  every lane takes units of 16 pixels x (1 or 2) rows: luma and chroma from shared memory, triangle or box
+//            upsampling, colour transform, 16-byte + 8-byte stores (interleaved RGB: 48 bytes per row).
+// Warps never wait for each other (the phases are separated by __syncwarp only): the 24 warps of an SM drift apart, so
+// that at any time some transform, some colour-convert and some wait for their coefficients -- which is what keeps the
+// integer pipes issuing.  A strip is as wide as gives a warp three full passes of blocks per step (96 blocks).
 // The vertical triangle filter of 4:2:0 / 4:4:0 looks one chroma row up and down, so with it the output trails the
 // IDCT by one chroma row (two luma rows): the last two rows of every tile are carried over to the next step, and a
 // band starts / ends with a step that only transforms the one chroma row its first / last output rows look at (a
@@ -173,21 +176,22 @@ __device__ __noinline__ void px_idct_phase(const PxSource src, const PxTile& T, 
         const uint32_t bim = uint32_t(pc.first + (by << pc.lh) + (bx - (mcu << pc.lh)));
         return (uint32_t(r) * src.mcus_x + uint32_t(mcu)) * src.bpm + bim;
     };
+    const int lane = threadIdx.x & 31;
     int c, by, local;
     uint32_t blk = 0, rec = 0;
-    if (int(threadIdx.x) < total) {
-        blk = locate(threadIdx.x, c, by, local);
+    if (lane < total) {
+        blk = locate(lane, c, by, local);
         rec = __ldg(src.blkrec + src.blk0 + blk);
     }
 #pragma unroll 1
-    for (int t = threadIdx.x; t < total; t += kPxThreads) {
+    for (int t = lane; t < total; t += 32) {
         const PxComp pc = T.c[c];
         uint32_t w[32];
         const int32_t dc = px_fetch_block(src.coef, rec, src.blk0 + blk, w);
         const uint32_t dst = smem + uint32_t(pc.off + (T.carry + by * 8) * pc.stride + kPxApron + local * 8);
         const int cq = c;
-        if (t + kPxThreads < total) { // the next item's record travels while this block is transformed
-            blk = locate(t + kPxThreads, c, by, local);
+        if (t + 32 < total) { // the next item's record travels while this block is transformed
+            blk = locate(t + 32, c, by, local);
             rec = __ldg(src.blkrec + src.blk0 + blk);
         }
         if (kind == 0)
@@ -343,10 +347,11 @@ template <int HX, int VX, bool kFancy, bool kLumaOnly>
 __device__ __forceinline__ void px_color_phase(const PxOut& im, const PxTile& T, const PxColor& K, const uint8_t* smem, int r, int y_lo, int y_hi)
 {
     constexpr bool fancy_v = kFancy && VX == 2;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31;
     const int X_strip = T.mx0 * (8 << T.c[0].lh);
     const int strip_px = T.c[0].nbx * 8;
     const int ucols = (strip_px + kPxUnit - 1) / kPxUnit;
+    const uint32_t ucols_rcp = 65536u / uint32_t(ucols) + 1u; // u / ucols == (u * rcp) >> 16 for the few hundred units of a step
     const int dh = im.dh;
     const int crow0 = T.urows * r - T.carry; // chroma row held at plane row 0
     const int ystride = T.c[0].stride;
@@ -357,17 +362,22 @@ __device__ __forceinline__ void px_color_phase(const PxOut& im, const PxTile& T,
     const uint8_t* pa = kLumaOnly ? p0 : smem + T.c[1].off + kPxApron + (X_strip / HX - T.c[1].bx0 * 8);
     const ptrdiff_t a_to_b = kLumaOnly ? 0 : ptrdiff_t(T.c[2].off) - ptrdiff_t(T.c[1].off);
     const int roi_x0 = im.roi_x0, roi_x1 = im.roi_x1, roi_y0 = im.roi_y0;
+    // unit rows of this step that lie inside the band and the region: [m_lo, m_hi)
+    const int i0 = T.urows * r - T.lag;
+    const int m_lo = max(0, (y_lo - VX * i0) / VX), m_hi = min(T.urows, (y_hi - VX * i0 + VX - 1) / VX);
+    if (y_hi <= VX * i0 || m_lo >= m_hi)
+        return;
+    const int n_units = (m_hi - m_lo) * ucols;
 #pragma unroll 1
-    for (int m = warp; m < T.urows; m += kPxThreads / 32) {
-        const int i = T.urows * r - T.lag + m;
+    for (int u = lane; u < n_units; u += 32) {
+        const int mr = int((uint32_t(u) * ucols_rcp) >> 16);
+        const int m = m_lo + mr, ux = u - mr * ucols;
+        const int i = i0 + m;
         const int y0 = VX * i;
-        if (y0 + VX <= y_lo || y0 >= y_hi)
-            continue;
         int up = i - 1, dn = i + 1; // vertical neighbour rows, replicated at the component's top and bottom
         up = up < 0 ? 0 : up;
         dn = dn > dh - 1 ? dh - 1 : dn;
-#pragma unroll 1
-        for (int ux = lane; ux < ucols; ux += 32) {
+        {
             const int X0 = X_strip + ux * kPxUnit;
             if (X0 >= roi_x1 || X0 + kPxUnit <= roi_x0)
                 continue;
@@ -506,7 +516,7 @@ __device__ __forceinline__ void px_color_phase(const PxOut& im, const PxTile& T,
 // image go into the aprons of the chroma rows written in this step (column -1 = column 0, column dw = column dw - 1).
 __device__ __forceinline__ void px_edge_phase(const PxTile& T, uint8_t* smem, int dw, int first_row, int n_rows)
 {
-    for (int t = threadIdx.x; t < 2 * n_rows * 2; t += kPxThreads) {
+    for (int t = threadIdx.x & 31; t < 2 * n_rows * 2; t += 32) {
         const int c = 1 + (t & 1), side = (t >> 1) & 1, row = first_row + (t >> 2);
         const PxComp& pc = T.c[c];
         uint8_t* q = smem + pc.off + row * pc.stride + kPxApron;
@@ -520,32 +530,38 @@ __device__ __forceinline__ void px_edge_phase(const PxTile& T, uint8_t* smem, in
     }
 }
 
+constexpr int kPxWarps = kPxThreads / 32;
+
 __global__ void __launch_bounds__(kPxThreads, kPxCtasPerSm) pixels_kernel(BatchDev bd, int redo_only)
 {
     extern __shared__ uint4 s_px_raw[];
-    __shared__ uint32_t s_qz[3][32];
-    uint8_t* smem = reinterpret_cast<uint8_t*>(s_px_raw);
-    const uint32_t cta = blockIdx.x;
-    const uint32_t img = bd.px_cta_img[cta];
+    __shared__ uint32_t s_qz_all[kPxWarps][3][32];
+    __shared__ PxTile s_tile_all[kPxWarps];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t task = blockIdx.x * kPxWarps + warp; // one tile per warp
+    if (task >= uint32_t(bd.n_px_task))
+        return;
+    uint8_t* smem = reinterpret_cast<uint8_t*>(s_px_raw) + size_t(warp) * bd.px_smem;
+    uint32_t (*s_qz)[32] = s_qz_all[warp];
+    const uint32_t img = bd.px_cta_img[task];
     const ImageDev& im = bd.img[img];
     const uint32_t flags = bd.state[img].flags;
-    if ((flags & (kFlagDirty | kFlagBadMarker)) || (redo_only && !(flags & kFlagRedo)))
+    if ((flags & (kFlagDirty | kFlagBadMarker)) || ((redo_only & 1) && !(flags & kFlagRedo)))
         return;
-    if (threadIdx.x < 96) { // quantisers paired in zig-zag order: q(2j) | q(2j+1) << 24
+    { // quantisers paired in zig-zag order: q(2j) | q(2j+1) << 24
         constexpr uint8_t kNatural[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7,
             14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62,
             63};
-        const int c = threadIdx.x >> 5, j = threadIdx.x & 31;
-        s_qz[c][j] = uint32_t(im.qt[c][kNatural[2 * j]]) | (uint32_t(im.qt[c][kNatural[2 * j + 1]]) << 24);
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+            s_qz[c][lane] = uint32_t(im.qt[c][kNatural[2 * lane]]) | (uint32_t(im.qt[c][kNatural[2 * lane + 1]]) << 24);
     }
-    // ---- tile geometry (uniform over the CTA; lives in shared memory: the phases index it dynamically)
-    __shared__ PxTile s_tile;
-    if (threadIdx.x == 0) {
-        PxTile& T = s_tile;
-        const int local = int(cta - im.px_cta_off);
+    // ---- tile geometry (uniform over the warp; lives in shared memory: the phases index it dynamically)
+    if (lane == 0) {
+        PxTile& T = s_tile_all[warp];
+        const int local = int(task - im.px_cta_off);
         const int band = local / int(im.px_n_strips), strip = local - band * int(im.px_n_strips);
         const int mode = im.color_mode; // 1: luma only, 2..5: (hx, vx) = (1,1), (2,1), (1,2), (2,2) replicated, 6..8: 3..5 with the triangle filter
-        const int hx = (mode == 3 || mode == 5 || mode == 6 || mode == 8) ? 2 : 1;
         const int vx = (mode == 4 || mode == 5 || mode == 7 || mode == 8) ? 2 : 1;
         const bool fancy_h = (mode == 6 || mode == 8), fancy_v = (mode == 7 || mode == 8);
         T.ncomp = (mode == 1) ? 1 : 3;
@@ -573,7 +589,6 @@ __global__ void __launch_bounds__(kPxThreads, kPxCtasPerSm) pixels_kernel(BatchD
             if (c < T.ncomp)
                 off += (T.carry + (8 << pc.lv)) * pc.stride;
         }
-        (void)hx;
     }
     const PxColor K = px_color_setup(im.fmt);
     PxOut po;
@@ -594,8 +609,8 @@ __global__ void __launch_bounds__(kPxThreads, kPxCtasPerSm) pixels_kernel(BatchD
     const int color_mode = im.color_mode, mcus_y = im.mcus_y;
     const bool fancy_h_mode = color_mode == 6 || color_mode == 8;
     const uint32_t smem_addr32 = smem_addr(smem);
-    __syncthreads();
-    const PxTile& T = s_tile;
+    __syncwarp();
+    const PxTile& T = s_tile_all[warp];
     const int mcu_h = 8 * int(im.vmax);
     const int y_lo = max(T.r_lo * mcu_h, int(im.roi_y0)), y_hi = min(T.r_hi * mcu_h, int(im.roi_y1));
     const int r_first = (T.lag && T.r_lo > 0) ? T.r_lo - 1 : T.r_lo;
@@ -605,16 +620,16 @@ __global__ void __launch_bounds__(kPxThreads, kPxCtasPerSm) pixels_kernel(BatchD
 #pragma unroll 1
     for (int r = r_first; r <= r_last; ++r) {
         const int kind = r < T.r_lo ? 1 : (r >= T.r_hi ? 2 : 0);
-        if (r < mcus_y)
+        if (r < mcus_y && !(redo_only & 4))
             px_idct_phase(src, T, s_qz, smem_addr32, r, kind);
-        __syncthreads();
+        __syncwarp();
         if (fancy_h_mode && r < mcus_y) {
             // rows written in this step: all of them, or only the last / the first chroma row (steps above / below the band)
             const int rows_c = 8 << T.c[1].lv;
             px_edge_phase(T, smem, po.dw, T.carry + (kind == 1 ? rows_c - 1 : 0), kind == 0 ? rows_c : 1);
-            __syncthreads();
+            __syncwarp();
         }
-        if (kind != 1) {
+        if (kind != 1 && !(redo_only & 2)) {
             switch (color_mode) {
             case 1: px_color_phase<1, 1, false, true>(po, T, K, smem, r, y_lo, y_hi); break;
             case 2: px_color_phase<1, 1, false, false>(po, T, K, smem, r, y_lo, y_hi); break;
@@ -628,18 +643,18 @@ __global__ void __launch_bounds__(kPxThreads, kPxCtasPerSm) pixels_kernel(BatchD
         }
         if (T.lag && r < r_last) {
             // the last two rows of every plane become the first two of the next step
-            __syncthreads();
+            __syncwarp();
             for (int c = 0; c < T.ncomp; ++c) {
                 const PxComp& pc = T.c[c];
                 const int rows = T.carry + (8 << pc.lv);
                 const int words = pc.stride / 4;
-                for (int k = threadIdx.x; k < 2 * words; k += kPxThreads) {
-                    const int row = k / words, w = k - row * words;
+                for (int k = lane; k < 2 * words; k += 32) {
+                    const int row = k >= words ? 1 : 0, w = k - row * words;
                     reinterpret_cast<uint32_t*>(smem + pc.off + row * pc.stride)[w] =
                         reinterpret_cast<const uint32_t*>(smem + pc.off + (rows - 2 + row) * pc.stride)[w];
                 }
             }
         }
-        __syncthreads();
+        __syncwarp();
     }
 }
