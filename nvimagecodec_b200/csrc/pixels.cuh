@@ -49,21 +49,21 @@ struct PxTile {
 // Coefficients of one block (dense layout: 16-byte groups in zig-zag order, a mask of the groups K3 wrote, DC in the record),
 // as they lie in memory: w[j] = positions 2j (low half) and 2j + 1 (high half) of the zig-zag sequence; position 0 is not
 // stored there, the DC value comes back separately.
-__device__ __forceinline__ int32_t px_fetch_block(const int16_t* __restrict__ coef, uint32_t rec, size_t blk, uint32_t (&w)[32])
+// kHalf: 0 = groups 0..3, 1 = groups 4..7, 2 = all eight
+template <int kHalf>
+__device__ __forceinline__ void px_fetch_block(const int16_t* __restrict__ coef, uint32_t rec, size_t blk, uint32_t (&w)[32])
 {
     const uint4* s4 = reinterpret_cast<const uint4*>(coef) + blk * 8;
-    const uint32_t mask = rec & 0xFFu;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if ((mask >> i) & 1u)
-            v = __ldg(s4 + i);
-        w[4 * i + 0] = v.x;
-        w[4 * i + 1] = v.y;
-        w[4 * i + 2] = v.z;
-        w[4 * i + 3] = v.w;
+    for (int i = (kHalf == 1 ? 4 : 0); i < (kHalf == 0 ? 4 : 8); ++i) {
+        // (volatile: these loads are issued where the code says -- in the middle of the previous block's row pass)
+        asm volatile("{\n\t.reg .pred q;\n\t"
+                     "setp.ne.u32 q, %5, 0;\n\t"
+                     "mov.u32 %0, 0;\n\tmov.u32 %1, 0;\n\tmov.u32 %2, 0;\n\tmov.u32 %3, 0;\n\t"
+                     "@q ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
+                     : "=r"(w[4 * i]), "=r"(w[4 * i + 1]), "=r"(w[4 * i + 2]), "=r"(w[4 * i + 3])
+                     : "l"(s4 + i), "r"(rec & (1u << i)));
     }
-    return int32_t(rec) >> 16;
 }
 
 // signed 16-bit halves of a times unsigned bytes of b: lo = a.lo * b.b0 + a.hi * b.b1, hi = a.lo * b.b2 + a.hi * b.b3
@@ -91,8 +91,10 @@ __device__ __forceinline__ void px_sts64(uint32_t addr, uint32_t a, uint32_t b)
 // dst: shared-window address of the block's first row.
 // kRows: 0 = all eight rows, 1 = only row 7, 2 = only row 0 (the rows a band's first / last step needs); what is not
 // asked for is never computed (everything is unrolled, unused column outputs are dead code).
-template <int kRows>
-__device__ __forceinline__ void px_idct_block(const uint32_t (&w)[32], int32_t dc, const uint32_t* __restrict__ qz, uint32_t dst, int stride)
+// mid(0) / mid(1): called when four / six of the eight rows are out (the packed words are long dead by then) -- where the two
+// halves of the next block's loads are issued: by then enough registers of this block are free to receive them.
+template <int kRows, typename Mid>
+__device__ __forceinline__ void px_idct_block(const uint32_t (&w)[32], int32_t dc, const uint32_t* __restrict__ qz, uint32_t dst, int stride, Mid mid)
 {
     constexpr int kZzPos[64] = {0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43, 9, 11, 18, 24,
         31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60, 21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48,
@@ -120,6 +122,10 @@ __device__ __forceinline__ void px_idct_block(const uint32_t (&w)[32], int32_t d
     }
 #pragma unroll
     for (int y = 0; y < 8; ++y) {
+        if (y == 4)
+            mid(0);
+        if (y == 6)
+            mid(1);
         if ((kRows == 1 && y != 7) || (kRows == 2 && y != 0))
             continue;
         int32_t o[8];
@@ -140,7 +146,7 @@ struct PxSource {          // what phase A needs of the batch and the image, rea
     uint32_t mcus_x, bpm;
 };
 
-__device__ __noinline__ void px_idct_phase(const PxSource src, const PxTile& T, const uint32_t (*s_qz)[32], uint32_t smem, int r, int kind)
+__device__ __forceinline__ void px_idct_phase(const PxSource src, const PxTile& T, const uint32_t (*s_qz)[32], uint32_t smem, int r, int kind)
 {
     int n[3];
 #pragma unroll
@@ -177,29 +183,40 @@ __device__ __noinline__ void px_idct_phase(const PxSource src, const PxTile& T, 
         return (uint32_t(r) * src.mcus_x + uint32_t(mcu)) * src.bpm + bim;
     };
     const int lane = threadIdx.x & 31;
+    if (lane >= total)
+        return;
+    // Software pipeline over the lane's items: while a block is transformed, the record of the next one is already
+    // here and its coefficient words are requested as soon as the registers of the current block's words are free.
     int c, by, local;
-    uint32_t blk = 0, rec = 0;
-    if (lane < total) {
-        blk = locate(lane, c, by, local);
-        rec = __ldg(src.blkrec + src.blk0 + blk);
-    }
+    uint32_t blk = locate(lane, c, by, local);
+    uint32_t rec = __ldg(src.blkrec + src.blk0 + blk);
+    uint32_t w[32];
+    px_fetch_block<2>(src.coef, rec, src.blk0 + blk, w);
 #pragma unroll 1
     for (int t = lane; t < total; t += 32) {
-        const PxComp pc = T.c[c];
-        uint32_t w[32];
-        const int32_t dc = px_fetch_block(src.coef, rec, src.blk0 + blk, w);
-        const uint32_t dst = smem + uint32_t(pc.off + (T.carry + by * 8) * pc.stride + kPxApron + local * 8);
-        const int cq = c;
-        if (t + 32 < total) { // the next item's record travels while this block is transformed
+        const int stride = T.c[c].stride;
+        const uint32_t dst = smem + uint32_t(T.c[c].off + (T.carry + by * 8) * stride + kPxApron + local * 8);
+        const uint32_t* qz = s_qz[c];
+        const int32_t dc = int32_t(rec) >> 16;
+        const bool more = t + 32 < total;
+        if (more) {
             blk = locate(t + 32, c, by, local);
             rec = __ldg(src.blkrec + src.blk0 + blk);
         }
+        auto next = [&](int half) {
+            if (more) {
+                if (half == 0)
+                    px_fetch_block<0>(src.coef, rec, src.blk0 + blk, w);
+                else
+                    px_fetch_block<1>(src.coef, rec, src.blk0 + blk, w);
+            }
+        };
         if (kind == 0)
-            px_idct_block<0>(w, dc, s_qz[cq], dst, pc.stride);
+            px_idct_block<0>(w, dc, qz, dst, stride, next);
         else if (kind == 1)
-            px_idct_block<1>(w, dc, s_qz[cq], dst, pc.stride);
+            px_idct_block<1>(w, dc, qz, dst, stride, next);
         else
-            px_idct_block<2>(w, dc, s_qz[cq], dst, pc.stride);
+            px_idct_block<2>(w, dc, qz, dst, stride, next);
     }
 }
 
@@ -214,55 +231,6 @@ __device__ __forceinline__ void px_stg64(uint8_t* p, uint32_t a, uint32_t b)
     asm volatile("st.global.v2.u32 [%0], {%1, %2};" ::"l"(__cvta_generic_to_global(p)), "r"(a), "r"(b) : "memory");
 }
 __device__ __forceinline__ int px_byte(uint32_t w, int k) { return int(__byte_perm(w, 0u, 0x4440 + k)); } // byte k of w
-
-// Chroma for eight pixels (half hf of a unit) of one output row, HX == 2: the six samples the horizontal filter looks at
-// (left neighbour, four centres, right neighbour) of the current row and of its vertical neighbour row, taken from what
-// was loaded once per unit: w0 / w1 = samples 0..3 / 4..7, l / r = the samples before and after them.
-// s[] = the vertical part: 3 * cur + nbr for the h2v2 triangle, the sample itself otherwise.
-template <int VX, bool kFancy>
-__device__ __forceinline__ void px_vertical_h2(int hf, uint32_t cw0, uint32_t cw1, int cl, int cr, uint32_t nw0, uint32_t nw1, int nl, int nr, int* s)
-{
-    int c[6], n[6];
-    const uint32_t cw = hf ? cw1 : cw0, nw = hf ? nw1 : nw0;
-    c[0] = hf ? px_byte(cw0, 3) : cl;
-    c[5] = hf ? cr : px_byte(cw1, 0);
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-        c[1 + k] = px_byte(cw, k);
-    if (VX == 2 && kFancy) {
-        n[0] = hf ? px_byte(nw0, 3) : nl;
-        n[5] = hf ? nr : px_byte(nw1, 0);
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            n[1 + k] = px_byte(nw, k);
-#pragma unroll
-        for (int k = 0; k < 6; ++k)
-            s[k] = 3 * c[k] + n[k];
-    } else {
-#pragma unroll
-        for (int k = 0; k < 6; ++k)
-            s[k] = c[k];
-    }
-}
-
-// Horizontal part for the four pixels 4g .. 4g+3 (g = 0, 1) of the eight, HX == 2 (jdsample.c).
-template <int VX, bool kFancy>
-__device__ __forceinline__ void px_horizontal_h2(const int* s, int g, int* out)
-{
-#pragma unroll
-    for (int m = 0; m < 2; ++m) {
-        const int k = 2 * g + m + 1; // centre sample
-        if (VX == 2 && kFancy) {
-            out[2 * m] = (3 * s[k] + 8 + s[k - 1]) >> 4;
-            out[2 * m + 1] = (3 * s[k] + 7 + s[k + 1]) >> 4;
-        } else if (kFancy) {
-            out[2 * m] = (3 * s[k] + 1 + s[k - 1]) >> 2;
-            out[2 * m + 1] = (3 * s[k] + 2 + s[k + 1]) >> 2;
-        } else {
-            out[2 * m] = out[2 * m + 1] = s[k];
-        }
-    }
-}
 
 // Output layout of an image, uniform over the CTA.  The colour transform itself always runs in R, G, B terms with
 // immediate constants (16 bits up, the -128 and the rounding folded in); BGR only changes the order of packing.
@@ -295,7 +263,7 @@ struct PxOut {             // where the pixels go, read once per CTA (stores thr
     int dw, dh;            // real size of the chroma components
 };
 
-__device__ __forceinline__ void px_store_half(const PxOut& im, const PxColor& K, int ox, int oy, int hf, const uint32_t* pk, int x_lo, int x_hi)
+__device__ __forceinline__ void px_store_half(const PxOut& im, const PxColor& K, uint8_t* orow, int ox, int hf, const uint32_t* pk, int x_lo, int x_hi)
 {
     const bool full = x_lo == 0 && x_hi == 8;
     if (K.planar) {
@@ -303,7 +271,7 @@ __device__ __forceinline__ void px_store_half(const PxOut& im, const PxColor& K,
         for (int ch = 0; ch < 3; ++ch) {
             if (ch >= K.nch)
                 break;
-            uint8_t* o = im.out + size_t(ch) * im.plane_stride + size_t(oy) * im.row_stride + ox;
+            uint8_t* o = orow + size_t(ch) * im.plane_stride + ox;
             if (full) {
                 if ((reinterpret_cast<uintptr_t>(o) & 7u) == 0)
                     px_stg64(o, pk[2 * ch], pk[2 * ch + 1]);
@@ -318,7 +286,7 @@ __device__ __forceinline__ void px_store_half(const PxOut& im, const PxColor& K,
         }
         return;
     }
-    uint8_t* o = im.out + size_t(oy) * im.row_stride + ptrdiff_t(ox) * 3;
+    uint8_t* o = orow + ptrdiff_t(ox) * 3;
     if (full) {
         const uint32_t a = uint32_t(reinterpret_cast<uintptr_t>(o)) & 15u;
         if (hf == 0 && a == 0) {
@@ -338,11 +306,13 @@ __device__ __forceinline__ void px_store_half(const PxOut& im, const PxColor& K,
     }
 }
 
-// Phase B of one step for one sampling mode.  Unit row m of MCU row r is chroma row (luma row when VX == 1)
-// i = urows * r - lag + m; its luma rows VX * i .. sit at plane rows VX * m .., its chroma rows i - 1, i, i + 1 (clamped
-// to the component's real height, where libjpeg replicates) at plane rows (row) - (urows * r - carry).
-// A thread takes 16 pixels of VX rows: everything it needs is loaded once (packed), then worked through in halves of
-// eight pixels.  The aprons of the planes hold the replicated edge samples, so no address is clamped horizontally.
+// Phase B of one step for one sampling mode.  The step's output rows are Y0 = VX * (urows * r - lag) onwards; output row y
+// belongs to chroma row i = y / VX, which sits (with its vertical neighbours i - 1 / i + 1, clamped to the component's real
+// height, where libjpeg replicates) at plane row (chroma row) - (urows * r - carry); luma row y sits at plane row y - Y0.
+// A lane takes one item at a time: 16 pixels of one output row, consecutive lanes consecutive pixels of the row.  The loop
+// body is kept small on purpose (it shares the instruction cache with the IDCT): everything an item needs comes from
+// shared memory when it needs it, worked through in two halves of eight pixels.  The aprons of the planes hold the
+// replicated edge samples, so no address is clamped horizontally.
 template <int HX, int VX, bool kFancy, bool kLumaOnly>
 __device__ __forceinline__ void px_color_phase(const PxOut& im, const PxTile& T, const PxColor& K, const uint8_t* smem, int r, int y_lo, int y_hi)
 {
@@ -351,163 +321,136 @@ __device__ __forceinline__ void px_color_phase(const PxOut& im, const PxTile& T,
     const int X_strip = T.mx0 * (8 << T.c[0].lh);
     const int strip_px = T.c[0].nbx * 8;
     const int ucols = (strip_px + kPxUnit - 1) / kPxUnit;
-    const uint32_t ucols_rcp = 65536u / uint32_t(ucols) + 1u; // u / ucols == (u * rcp) >> 16 for the few hundred units of a step
+    const uint32_t ucols_rcp = 65536u / uint32_t(ucols) + 1u; // u / ucols == (u * rcp) >> 16 for the few hundred items of a step
     const int dh = im.dh;
+    const int i0 = T.urows * r - T.lag;
+    const int Y0 = VX * i0;
+    const int ya = max(y_lo, Y0), yb = min(y_hi, Y0 + VX * T.urows);
+    if (ya >= yb)
+        return;
     const int crow0 = T.urows * r - T.carry; // chroma row held at plane row 0
     const int ystride = T.c[0].stride;
     const uint8_t* p0 = smem + T.c[0].off + kPxApron;
     const int cstride = kLumaOnly ? 0 : T.c[1].stride;
-    // sample column of the strip's first pixel inside the chroma planes
-    // plane a = Cb, plane b = Cr
+    // plane a = Cb, plane b = Cr; pa points at the sample column of the strip's first pixel
     const uint8_t* pa = kLumaOnly ? p0 : smem + T.c[1].off + kPxApron + (X_strip / HX - T.c[1].bx0 * 8);
     const ptrdiff_t a_to_b = kLumaOnly ? 0 : ptrdiff_t(T.c[2].off) - ptrdiff_t(T.c[1].off);
     const int roi_x0 = im.roi_x0, roi_x1 = im.roi_x1, roi_y0 = im.roi_y0;
-    // unit rows of this step that lie inside the band and the region: [m_lo, m_hi)
-    const int i0 = T.urows * r - T.lag;
-    const int m_lo = max(0, (y_lo - VX * i0) / VX), m_hi = min(T.urows, (y_hi - VX * i0 + VX - 1) / VX);
-    if (y_hi <= VX * i0 || m_lo >= m_hi)
-        return;
-    const int n_units = (m_hi - m_lo) * ucols;
+    const int n_items = (yb - ya) * ucols;
 #pragma unroll 1
-    for (int u = lane; u < n_units; u += 32) {
-        const int mr = int((uint32_t(u) * ucols_rcp) >> 16);
-        const int m = m_lo + mr, ux = u - mr * ucols;
-        const int i = i0 + m;
-        const int y0 = VX * i;
-        int up = i - 1, dn = i + 1; // vertical neighbour rows, replicated at the component's top and bottom
-        up = up < 0 ? 0 : up;
-        dn = dn > dh - 1 ? dh - 1 : dn;
-        {
-            const int X0 = X_strip + ux * kPxUnit;
-            if (X0 >= roi_x1 || X0 + kPxUnit <= roi_x0)
-                continue;
-            // ---- loads: luma of VX rows, chroma of the row (and of its vertical neighbours)
-            const uint8_t* yp = p0 + (VX * m) * ystride + ux * kPxUnit;
-            uint4 yv[VX];
+    for (int u = lane; u < n_items; u += 32) {
+        const int row = int((uint32_t(u) * ucols_rcp) >> 16);
+        const int ux = u - row * ucols;
+        const int y = ya + row;
+        const int i = VX == 2 ? (y >> 1) : y, rr = VX == 2 ? (y & 1) : 0;
+        const int X0 = X_strip + ux * kPxUnit;
+        if (X0 >= roi_x1 || X0 + kPxUnit <= roi_x0)
+            continue;
+        const uint8_t* yp = p0 + (y - Y0) * ystride + ux * kPxUnit;
+        const uint8_t* ca = pa + (i - crow0) * cstride + ux * (kPxUnit / HX); // Cb, current row
+        int nb = rr == 0 ? i - 1 : i + 1; // vertical neighbour, replicated at the component's top and bottom
+        nb = nb < 0 ? 0 : (nb > dh - 1 ? dh - 1 : nb);
+        const ptrdiff_t to_nb = fancy_v ? ptrdiff_t(nb - i) * cstride : 0;
+        uint8_t* const orow = im.out + size_t(y - roi_y0) * im.row_stride;
 #pragma unroll
-            for (int rr = 0; rr < VX; ++rr)
-                yv[rr] = *reinterpret_cast<const uint4*>(yp + rr * ystride);
-            // chroma, packed: [plane a / b][row: cur, up, dn][words]; HX == 2: 8 samples + the two around them, HX == 1: 16 samples
-            uint32_t cw[2][3][4];
-            int cl[2][3], cr[2][3];
+        for (int hf = 0; hf < 2; ++hf) {
+            const int X = X0 + 8 * hf;
+            if (X >= roi_x1 || X + 8 <= roi_x0 || X - X_strip >= strip_px)
+                continue;
+            const int x_lo = max(roi_x0 - X, 0), x_hi = min(roi_x1 - X, 8);
+            int ua[8], ub[8]; // the eight upsampled Cb / Cr samples
             if (!kLumaOnly) {
-                const uint8_t* ca = pa + (i - crow0) * cstride + ux * (kPxUnit / HX);
 #pragma unroll
                 for (int ab = 0; ab < 2; ++ab) {
-#pragma unroll
-                    for (int row = 0; row < 3; ++row) {
-                        if (row > 0 && !fancy_v)
-                            continue;
-                        const uint8_t* q = ca + (ab ? a_to_b : 0) + (row == 0 ? 0 : ((row == 1 ? up : dn) - i) * cstride);
-                        if (HX == 2) {
-                            const uint2 v = *reinterpret_cast<const uint2*>(q);
-                            cw[ab][row][0] = v.x;
-                            cw[ab][row][1] = v.y;
-                            if (kFancy) {
-                                cl[ab][row] = q[-1];
-                                cr[ab][row] = q[8];
-                            }
-                        } else {
-                            const uint4 v = *reinterpret_cast<const uint4*>(q);
-                            cw[ab][row][0] = v.x;
-                            cw[ab][row][1] = v.y;
-                            cw[ab][row][2] = v.z;
-                            cw[ab][row][3] = v.w;
-                        }
-                    }
-                }
-            }
-#pragma unroll
-            for (int rr = 0; rr < VX; ++rr) {
-                const int y = y0 + rr;
-                if (y < y_lo || y >= y_hi)
-                    continue;
-                const int nrow = fancy_v ? 1 + rr : 0; // the vertical neighbour of this output row: up for the first, down for the second
-                const uint32_t yw[4] = {yv[rr].x, yv[rr].y, yv[rr].z, yv[rr].w};
-#pragma unroll
-                for (int hf = 0; hf < 2; ++hf) {
-                    const int X = X0 + 8 * hf;
-                    if (X >= roi_x1 || X + 8 <= roi_x0 || X - X_strip >= strip_px)
-                        continue;
-                    const int x_lo = max(roi_x0 - X, 0), x_hi = min(roi_x1 - X, 8);
-                    int sa[8], sb[8]; // HX == 2: six vertically filtered samples; HX == 1: the eight finished samples
-                    if (!kLumaOnly) {
-                        if (HX == 2) {
-                            px_vertical_h2<VX, kFancy>(hf, cw[0][0][0], cw[0][0][1], cl[0][0], cr[0][0], cw[0][nrow][0], cw[0][nrow][1], cl[0][nrow], cr[0][nrow], sa);
-                            px_vertical_h2<VX, kFancy>(hf, cw[1][0][0], cw[1][0][1], cl[1][0], cr[1][0], cw[1][nrow][0], cw[1][nrow][1], cl[1][nrow], cr[1][nrow], sb);
-                        } else {
-#pragma unroll
-                            for (int k = 0; k < 8; ++k) {
-                                const int ca8 = px_byte(cw[0][0][2 * hf + (k >> 2)], k & 3), cb8 = px_byte(cw[1][0][2 * hf + (k >> 2)], k & 3);
-                                if (fancy_v) { // h1v2 triangle
-                                    sa[k] = (3 * ca8 + px_byte(cw[0][nrow][2 * hf + (k >> 2)], k & 3) + 1 + rr) >> 2;
-                                    sb[k] = (3 * cb8 + px_byte(cw[1][nrow][2 * hf + (k >> 2)], k & 3) + 1 + rr) >> 2;
-                                } else {
-                                    sa[k] = ca8;
-                                    sb[k] = cb8;
-                                }
-                            }
-                        }
-                    }
-                    uint32_t pk[6];
-#pragma unroll
-                    for (int g = 0; g < 2; ++g) {
-                        uint32_t c0[4], c1[4], c2[4];
+                    const uint8_t* q = ca + (ab ? a_to_b : 0) + hf * (8 / HX);
+                    int* out = ab ? ub : ua;
+                    if (HX == 2) {
+                        int s[6]; // left neighbour, four samples, right neighbour, vertically filtered
+                        const uint32_t cw = *reinterpret_cast<const uint32_t*>(q);
+                        s[0] = q[-1];
+                        s[5] = q[4];
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            c0[k] = __byte_perm(yw[2 * hf + g], 0u, 0x4044 + 0x100 * k); // luma << 16
-                        if (kLumaOnly) {
+                            s[1 + k] = px_byte(cw, k);
+                        if (fancy_v) {
+                            const uint32_t nw = *reinterpret_cast<const uint32_t*>(q + to_nb);
+                            s[0] = 3 * s[0] + q[to_nb - 1];
+                            s[5] = 3 * s[5] + q[to_nb + 4];
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
-                                c1[k] = c2[k] = c0[k];
-                        } else {
-                            int ua[4], ub[4];
-                            if (HX == 2) {
-                                px_horizontal_h2<VX, kFancy>(sa, g, ua);
-                                px_horizontal_h2<VX, kFancy>(sb, g, ub);
+                                s[1 + k] = 3 * s[1 + k] + px_byte(nw, k);
+                        }
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            if (fancy_v) { // h2v2 triangle (jdsample.c)
+                                out[2 * k] = (3 * s[k + 1] + 8 + s[k]) >> 4;
+                                out[2 * k + 1] = (3 * s[k + 1] + 7 + s[k + 2]) >> 4;
+                            } else if (kFancy) { // h2v1 triangle
+                                out[2 * k] = (3 * s[k + 1] + 1 + s[k]) >> 2;
+                                out[2 * k + 1] = (3 * s[k + 1] + 2 + s[k + 2]) >> 2;
                             } else {
-#pragma unroll
-                                for (int k = 0; k < 4; ++k) {
-                                    ua[k] = sa[4 * g + k];
-                                    ub[k] = sb[4 * g + k];
-                                }
-                            }
-                            if (K.yuv) {
-#pragma unroll
-                                for (int k = 0; k < 4; ++k) {
-                                    c1[k] = uint32_t(ua[k]) << 16;
-                                    c2[k] = uint32_t(ub[k]) << 16;
-                                }
-                            } else {
-                                // jdcolor.c 16 bits up: ua = Cb, ub = Cr
-                                constexpr int kR = 32768 - 128 * 91881, kG = 32768 + 128 * (22554 + 46802), kB = 32768 - 128 * 116130;
-#pragma unroll
-                                for (int k = 0; k < 4; ++k) {
-                                    const int yk = int(c0[k]);
-                                    c0[k] = uint32_t(__viaddmin_s32_relu(91881 * ub[k] + yk, kR, 0xFFFFFF));
-                                    c1[k] = uint32_t(__viaddmin_s32_relu(-46802 * ub[k] + (-22554 * ua[k] + yk), kG, 0xFFFFFF));
-                                    c2[k] = uint32_t(__viaddmin_s32_relu(116130 * ua[k] + yk, kB, 0xFFFFFF));
-                                }
+                                out[2 * k] = out[2 * k + 1] = s[k + 1];
                             }
                         }
-                        if (K.planar) {
-                            const uint32_t p0w = pack_b2(c0[0], c0[1], c0[2], c0[3]), p2w = pack_b2(c2[0], c2[1], c2[2], c2[3]);
-                            pk[g] = K.bgr ? p2w : p0w;
-                            pk[2 + g] = pack_b2(c1[0], c1[1], c1[2], c1[3]);
-                            pk[4 + g] = K.bgr ? p0w : p2w;
-                        } else if (K.bgr) {
-                            pk[3 * g + 0] = pack_b2(c2[0], c1[0], c0[0], c2[1]);
-                            pk[3 * g + 1] = pack_b2(c1[1], c0[1], c2[2], c1[2]);
-                            pk[3 * g + 2] = pack_b2(c0[2], c2[3], c1[3], c0[3]);
-                        } else {
-                            pk[3 * g + 0] = pack_b2(c0[0], c1[0], c2[0], c0[1]);
-                            pk[3 * g + 1] = pack_b2(c1[1], c2[1], c0[2], c1[2]);
-                            pk[3 * g + 2] = pack_b2(c2[2], c0[3], c1[3], c2[3]);
+                    } else {
+                        const uint2 cw = *reinterpret_cast<const uint2*>(q);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k)
+                            out[k] = px_byte(k < 4 ? cw.x : cw.y, k & 3);
+                        if (fancy_v) { // h1v2 triangle
+                            const uint2 nw = *reinterpret_cast<const uint2*>(q + to_nb);
+#pragma unroll
+                            for (int k = 0; k < 8; ++k)
+                                out[k] = (3 * out[k] + px_byte(k < 4 ? nw.x : nw.y, k & 3) + 1 + rr) >> 2;
                         }
                     }
-                    px_store_half(im, K, X - roi_x0, y - roi_y0, hf, pk, x_lo, x_hi);
                 }
             }
+            const uint2 yv = *reinterpret_cast<const uint2*>(yp + 8 * hf);
+            uint32_t pk[6];
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+                uint32_t c0[4], c1[4], c2[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    c0[k] = __byte_perm(g ? yv.y : yv.x, 0u, 0x4044 + 0x100 * k); // luma << 16
+                if (kLumaOnly) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        c1[k] = c2[k] = c0[k];
+                } else if (K.yuv) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        c1[k] = uint32_t(ua[4 * g + k]) << 16;
+                        c2[k] = uint32_t(ub[4 * g + k]) << 16;
+                    }
+                } else {
+                    // jdcolor.c 16 bits up: ua = Cb, ub = Cr
+                    constexpr int kR = 32768 - 128 * 91881, kG = 32768 + 128 * (22554 + 46802), kB = 32768 - 128 * 116130;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int yk = int(c0[k]), cb = ua[4 * g + k], cr = ub[4 * g + k];
+                        c0[k] = uint32_t(__viaddmin_s32_relu(91881 * cr + yk, kR, 0xFFFFFF));
+                        c1[k] = uint32_t(__viaddmin_s32_relu(-46802 * cr + (-22554 * cb + yk), kG, 0xFFFFFF));
+                        c2[k] = uint32_t(__viaddmin_s32_relu(116130 * cb + yk, kB, 0xFFFFFF));
+                    }
+                }
+                if (K.planar) {
+                    const uint32_t p0w = pack_b2(c0[0], c0[1], c0[2], c0[3]), p2w = pack_b2(c2[0], c2[1], c2[2], c2[3]);
+                    pk[g] = K.bgr ? p2w : p0w;
+                    pk[2 + g] = pack_b2(c1[0], c1[1], c1[2], c1[3]);
+                    pk[4 + g] = K.bgr ? p0w : p2w;
+                } else if (K.bgr) {
+                    pk[3 * g + 0] = pack_b2(c2[0], c1[0], c0[0], c2[1]);
+                    pk[3 * g + 1] = pack_b2(c1[1], c0[1], c2[2], c1[2]);
+                    pk[3 * g + 2] = pack_b2(c0[2], c2[3], c1[3], c0[3]);
+                } else {
+                    pk[3 * g + 0] = pack_b2(c0[0], c1[0], c2[0], c0[1]);
+                    pk[3 * g + 1] = pack_b2(c1[1], c2[1], c0[2], c1[2]);
+                    pk[3 * g + 2] = pack_b2(c2[2], c0[3], c1[3], c2[3]);
+                }
+            }
+            px_store_half(im, K, orow, X - roi_x0, hf, pk, x_lo, x_hi);
         }
     }
 }
