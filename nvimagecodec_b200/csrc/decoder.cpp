@@ -646,9 +646,11 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         }
         {
             const int ur = im.color_unit_rows;
-            const size_t ax0 = size_t(x0) & ~size_t(7), ay0 = size_t(y0) / ur * ur; // units are aligned in image coordinates
+            // units are aligned in image coordinates: 16 pixels wide on the specialised paths, 8 on the generic one
+            const size_t uw = (im.color_mode >= 1 && o.orientation <= 1) ? 16 : 8;
+            const size_t ax0 = size_t(x0) & ~(uw - 1), ay0 = size_t(y0) / ur * ur;
             im.color_cta_off = n_color;
-            im.n_color_cta_x = uint32_t((size_t(x1) - ax0 + 255) / 256);
+            im.n_color_cta_x = uint32_t((size_t(x1) - ax0 + 32 * uw - 1) / (32 * uw));
             im.n_color_cta_y = uint32_t((size_t(y1) - ay0 + 8 * ur * kColorUnitsY - 1) / (8 * ur * kColorUnitsY));
             im.color_cta_x_rcp = im.n_color_cta_x > 1 ? uint32_t((uint64_t(1) << 32) / im.n_color_cta_x + 1) : 0u;
             if (role == kChild)
@@ -657,12 +659,14 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         // Fused pixel kernel (K4) for the specialised sampling modes: tiles over the MCUs the region touches.  Strip width and
         // band height are set for the whole batch once every image is known (below); here only the MCU window.
         {
-            bool fused = opt_.fused_pixels && role == kNormal && im.color_mode >= 1 && o.orientation <= 1;
-            for (int c = 0; c < hd.ncomp; ++c) {
+            im.q8 = 1;
+            for (int c = 0; c < hd.ncomp; ++c)
+                for (int k = 0; k < 64; ++k)
+                    im.q8 = (im.q8 && hd.qt[hd.tq[c]][k] <= 255) ? 1 : 0;
+            // (the fused kernel dequantises with 8-bit quantisers only; every baseline table is 8 bits wide)
+            bool fused = opt_.fused_pixels && role == kNormal && im.color_mode >= 1 && o.orientation <= 1 && im.q8;
+            for (int c = 0; c < hd.ncomp; ++c)
                 fused = fused && hd.h[c] <= 2 && hd.v[c] <= 2;
-                for (int k = 0; k < 64; ++k) // the fused kernel dequantises with 8-bit quantisers (every baseline table is)
-                    fused = fused && hd.qt[hd.tq[c]][k] <= 255;
-            }
             if (fused) {
                 const int mcu_w = 8 * hd.hmax;
                 im.px_mcu_col_lo = uint16_t(x0 / mcu_w);

@@ -84,7 +84,7 @@ struct Options {
     int lanes = 6;                // pipeline lanes (decoder + stream each) the chunks rotate over
     int chunk_images = 64;        // ... or this many images, whichever comes first
     int host_threads = 0;         // helper threads for marker walks / staging (0 = by the CPUs this process may run on, at most 8)
-    bool fused_pixels = true;     // IDCT + upsampling + colour in one kernel (0: the separate idct / color kernels for every image; experiments)
+    bool fused_pixels = false;    // IDCT + upsampling + colour in one kernel (pixels_kernel); off: the idct and color kernels, which are faster as measured (profiles/)
     bool sync_finish = false;     // Finish / DecodeBatch wait for the pixel kernels too, not only for the statuses
     int max_arena_mb = 32768;     // refuse (ERR_TOO_LARGE) images whose coefficient + plane arenas would exceed this many MiB
 };

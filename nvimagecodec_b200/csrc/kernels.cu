@@ -1426,9 +1426,12 @@ __device__ __forceinline__ uint32_t range_limit(int32_t x)
     return uint32_t(__vimin_s32_relu((x & 1023) - 384, 255)); // x already carries the + 512
 }
 
+#include "pixels.cuh"
+
 __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
 {
     __shared__ uint16_t s_q[3][64];
+    __shared__ uint32_t s_qz[3][32]; // 8-bit quantisers paired in zig-zag order (px_idct_rows)
     const uint32_t cta = blockIdx.x;
     const uint32_t img = bd.idct_cta_img[cta];
     const ImageDev& im = bd.img[img];
@@ -1437,6 +1440,14 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
         return;
     for (int i = threadIdx.x; i < 3 * 64; i += blockDim.x)
         s_q[i / 64][i % 64] = im.qt[i / 64][i % 64];
+    if (threadIdx.x < 96) {
+        constexpr uint8_t kNatural[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7,
+            14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62,
+            63};
+        const int c = threadIdx.x >> 5, j = threadIdx.x & 31;
+        s_qz[c][j] = uint32_t(im.qt[c][kNatural[2 * j]] & 0xFFu) | (uint32_t(im.qt[c][kNatural[2 * j + 1]] & 0xFFu) << 24);
+    }
+    const bool q8 = im.q8 != 0; // every quantiser fits 8 bits: dequantise with dot-product instructions straight from the packed pairs
     __syncthreads();
     // block index over the wanted rows of the planes of the needed components, row-major per plane; a thread takes
     // kIdctPer blocks, blockDim.x apart (neighbouring threads keep neighbouring blocks: the row stores coalesce)
@@ -1469,6 +1480,16 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
     const uint32_t mx = bx >> lh, my = by >> lv;
     const uint32_t bim = im.blk_first[c] + ((by - (my << lv)) << lh) + (bx - (mx << lh));
     const int16_t* src = bd.coef + im.coef_off + (size_t(my * im.mcus_x + mx) * im.bpm + bim) * 64;
+    if (q8) {
+        const uint32_t rec = __ldg(bd.blkrec + im.coef_off / 64 + (size_t(my * im.mcus_x + mx) * im.bpm + bim));
+        uint32_t w[32];
+        px_fetch_block<2>(bd.coef, rec, im.coef_off / 64 + (size_t(my * im.mcus_x + mx) * im.bpm + bim), w);
+        uint8_t* dst8 = bd.planes + im.plane_off[c] + size_t(by) * 8 * (bw * 8) + bx * 8;
+        const uint32_t pitch = bw * 8;
+        px_idct_rows<0>(w, int32_t(rec) >> 16, s_qz[c], [](int) {}, [&](int y, uint32_t lo, uint32_t hi) {
+            *reinterpret_cast<uint2*>(dst8 + size_t(y) * pitch) = make_uint2(lo, hi);
+        });
+    } else {
     // 64 coefficients, zig-zag order
     int32_t zz[64];
     {
@@ -1518,6 +1539,7 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
         pk.y = range_limit(o[4]) | (range_limit(o[5]) << 8) | (range_limit(o[6]) << 16) | (range_limit(o[7]) << 24);
         *reinterpret_cast<uint2*>(dst + size_t(y) * (bw * 8)) = pk;
     }
+    } // 16-bit quantisers
     // the next block of this thread lies blockDim.x further on
     bx += blockDim.x;
     while (bx >= bw) {
@@ -1957,7 +1979,9 @@ __global__ void gate_flags_kernel(BatchDev bd)
     bd.state[img].flags = bd.state[bd.gate[3 * img]].flags | bd.state[bd.gate[3 * img + 1]].flags | bd.state[bd.gate[3 * img + 2]].flags;
 }
 
-__global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev bd, int redo_only)
+// K4b.  Specialised sampling modes without EXIF orientation: a thread owns 16 pixels x (4 unit rows of 1 or 2 output rows),
+// a CTA 512 x (32 or 64) pixels (px_color_global).  Everything else (generic sampling, orientation): one pixel at a time.
+__global__ void __launch_bounds__(kColorTx* kColorTy, 3) color_kernel(BatchDev bd, int redo_only)
 {
     const uint32_t cta = blockIdx.x;
     const uint32_t img = bd.color_cta_img[cta];
@@ -1970,44 +1994,53 @@ __global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev b
     const uint32_t cx = local - cy * im.n_color_cta_x;
     const int tx = threadIdx.x % kColorTx, ty = threadIdx.x / kColorTx;
     const int urows = im.color_unit_rows;
+    if (im.color_mode >= 1 && im.orient <= 1) {
+        const int X0 = (int(im.roi_x0) & ~(kPxUnit - 1)) + (int(cx) * kColorTx + tx) * kPxUnit;
+        const int i_first = int(im.roi_y0) / urows + (int(cy) * kColorTy + ty) * kColorUnitsY;
+        if (X0 >= int(im.roi_x1) || i_first * urows >= int(im.roi_y1))
+            return;
+        const PxColor K = px_color_setup(im.fmt);
+        PxOut po;
+        po.out = im.out;
+        po.plane_stride = im.plane_stride;
+        po.row_stride = im.row_stride;
+        po.roi_x0 = im.roi_x0;
+        po.roi_x1 = im.roi_x1;
+        po.roi_y0 = im.roi_y0;
+        po.dw = im.comp_w[1];
+        po.dh = im.comp_h[1];
+        PxPlanes P;
+        P.y = bd.planes + im.plane_off[0];
+        P.cb = bd.planes + im.plane_off[1];
+        P.cr = bd.planes + im.plane_off[2];
+        P.ystride = int(im.plane_stride_px[0]);
+        P.cstride = int(im.plane_stride_px[1]);
+        P.dw = po.dw;
+        P.dh = po.dh;
+        const int y_hi = im.roi_y1;
+        switch (im.color_mode) {
+        case 1: px_color_global<1, 1, false, true>(po, P, K, X0, i_first, kColorUnitsY, y_hi); break;
+        case 2: px_color_global<1, 1, false, false>(po, P, K, X0, i_first, kColorUnitsY, y_hi); break;
+        case 3: px_color_global<2, 1, false, false>(po, P, K, X0, i_first, kColorUnitsY, y_hi); break;
+        case 4: px_color_global<1, 2, false, false>(po, P, K, X0, i_first, kColorUnitsY, y_hi); break;
+        case 5: px_color_global<2, 2, false, false>(po, P, K, X0, i_first, kColorUnitsY, y_hi); break;
+        case 6: px_color_global<2, 1, true, false>(po, P, K, X0, i_first, kColorUnitsY, y_hi); break;
+        case 7: px_color_global<1, 2, true, false>(po, P, K, X0, i_first, kColorUnitsY, y_hi); break;
+        default: px_color_global<2, 2, true, false>(po, P, K, X0, i_first, kColorUnitsY, y_hi); break;
+        }
+        return;
+    }
     const int X0 = (int(im.roi_x0) & ~7) + (int(cx) * kColorTx + tx) * 8;
     const int Y0 = (int(im.roi_y0) & ~(urows - 1)) + ((int(cy) * kColorTy + ty) * kColorUnitsY) * urows; // urows is 1 or 2; kColorUnitsY units per thread
     if (X0 >= int(im.roi_x1) || Y0 >= int(im.roi_y1))
         return;
-    const int order = (im.fmt == kFmtIBGR || im.fmt == kFmtPBGR) ? 1 : ((im.fmt == kFmtIYUV || im.fmt == kFmtPYUV) ? 2 : 0);
-#define B200_COLOR_CASE(mode, HX, VX, FANCY, LUMA)               \
-    case mode:                                                                 \
-        for (int u = 0; u < kColorUnitsY && Y0 + u * VX < int(im.roi_y1); ++u) {   \
-            if (order == 0)                                                        \
-                color_unit<HX, VX, FANCY, LUMA, 0>(bd, im, X0, Y0 + u * VX);       \
-            else if (order == 1)                                                   \
-                color_unit<HX, VX, FANCY, LUMA, 1>(bd, im, X0, Y0 + u * VX);       \
-            else                                                                   \
-                color_unit<HX, VX, FANCY, LUMA, 2>(bd, im, X0, Y0 + u * VX);       \
-        }                                                                          \
-        break;
-    switch (im.color_mode) {
-        B200_COLOR_CASE(1, 1, 1, false, true)
-        B200_COLOR_CASE(2, 1, 1, false, false)
-        B200_COLOR_CASE(3, 2, 1, false, false)
-        B200_COLOR_CASE(4, 1, 2, false, false)
-        B200_COLOR_CASE(5, 2, 2, false, false)
-        B200_COLOR_CASE(6, 2, 1, true, false)
-        B200_COLOR_CASE(7, 1, 2, true, false)
-        B200_COLOR_CASE(8, 2, 2, true, false)
-#undef B200_COLOR_CASE
-    default:
-        for (int r = 0; r < urows * kColorUnitsY; ++r)
-            for (int i = 0; i < 8; ++i) {
-                const int x = X0 + i, y = Y0 + r;
-                if (x >= int(im.roi_x0) && x < int(im.roi_x1) && y >= int(im.roi_y0) && y < int(im.roi_y1))
-                    color_pixel_generic(bd, im, x, y);
-            }
-        break;
-    }
+    for (int r = 0; r < urows * kColorUnitsY; ++r)
+        for (int i = 0; i < 8; ++i) {
+            const int x = X0 + i, y = Y0 + r;
+            if (x >= int(im.roi_x0) && x < int(im.roi_x1) && y >= int(im.roi_y0) && y < int(im.roi_y1))
+                color_pixel_generic(bd, im, x, y);
+        }
 }
-
-#include "pixels.cuh"
 
 constexpr size_t kSyncSmem = kSyncPairOffset + 2 * sizeof(HuffTableDev);
 constexpr size_t kWriteSmem = sizeof(HuffSetDev) + sizeof(BlockTable);

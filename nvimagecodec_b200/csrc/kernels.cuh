@@ -94,6 +94,7 @@ struct ImageDev {
     uint8_t color_mode;      // K4b specialisation: 0 generic, 1 luma only, 2..5 chroma (hx,vx) = (1,1),(2,1),(1,2),(2,2) replicated, 6..8 = 3..5 with the triangle filter
     uint8_t color_unit_rows; // output rows per K4b thread (the chroma vertical factor on the fast paths)
     uint8_t orient;          // EXIF orientation code applied when storing (0/1 = none; 5..8 transpose)
+    uint8_t q8;              // 1: every quantiser of the image fits 8 bits (all baseline tables do)
     uint8_t multi;           // 1: the components came in three scans and were decoded as one-component images of their own;
                              //    BatchDev::gate names them (their state flags become this image's before K4b)
 };

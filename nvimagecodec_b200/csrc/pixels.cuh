@@ -21,6 +21,11 @@
 // and right: a strip keeps the chroma of one more MCU column on each side.
 #pragma once
 
+// defined further down in kernels.cu, next to the colour helpers
+__device__ __forceinline__ uint32_t pack_b2(uint32_t a, uint32_t b, uint32_t c, uint32_t d);
+template <int NW>
+__device__ __forceinline__ void store_words_any(uint8_t* o, const uint32_t* w);
+
 #ifndef B200_PX_THREADS
 #define B200_PX_THREADS 256
 #endif
@@ -93,8 +98,9 @@ __device__ __forceinline__ void px_sts64(uint32_t addr, uint32_t a, uint32_t b)
 // asked for is never computed (everything is unrolled, unused column outputs are dead code).
 // mid(0) / mid(1): called when four / six of the eight rows are out (the packed words are long dead by then) -- where the two
 // halves of the next block's loads are issued: by then enough registers of this block are free to receive them.
-template <int kRows, typename Mid>
-__device__ __forceinline__ void px_idct_block(const uint32_t (&w)[32], int32_t dc, const uint32_t* __restrict__ qz, uint32_t dst, int stride, Mid mid)
+// store(y, lo, hi): row y of the block, eight pixels in two words.
+template <int kRows, typename Mid, typename Store>
+__device__ __forceinline__ void px_idct_rows(const uint32_t (&w)[32], int32_t dc, const uint32_t* __restrict__ qz, Mid mid, Store store)
 {
     constexpr int kZzPos[64] = {0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43, 9, 11, 18, 24,
         31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60, 21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48,
@@ -133,8 +139,14 @@ __device__ __forceinline__ void px_idct_block(const uint32_t (&w)[32], int32_t d
         uint2 pk;
         pk.x = range_limit(o[0]) | (range_limit(o[1]) << 8) | (range_limit(o[2]) << 16) | (range_limit(o[3]) << 24);
         pk.y = range_limit(o[4]) | (range_limit(o[5]) << 8) | (range_limit(o[6]) << 16) | (range_limit(o[7]) << 24);
-        px_sts64(dst + uint32_t(y * stride), pk.x, pk.y);
+        store(y, pk.x, pk.y);
     }
+}
+
+template <int kRows, typename Mid>
+__device__ __forceinline__ void px_idct_block(const uint32_t (&w)[32], int32_t dc, const uint32_t* __restrict__ qz, uint32_t dst, int stride, Mid mid)
+{
+    px_idct_rows<kRows>(w, dc, qz, mid, [&](int y, uint32_t lo, uint32_t hi) { px_sts64(dst + uint32_t(y * stride), lo, hi); });
 }
 
 // Phase A of one step: the blocks of MCU row r.  kind 0: every component, all rows; 1: chroma only, last row of the
@@ -426,6 +438,154 @@ __device__ __forceinline__ void px_color_phase(const PxOut& im, const PxTile& T,
                     }
                 } else {
                     // jdcolor.c 16 bits up: ua = Cb, ub = Cr
+                    constexpr int kR = 32768 - 128 * 91881, kG = 32768 + 128 * (22554 + 46802), kB = 32768 - 128 * 116130;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int yk = int(c0[k]), cb = ua[4 * g + k], cr = ub[4 * g + k];
+                        c0[k] = uint32_t(__viaddmin_s32_relu(91881 * cr + yk, kR, 0xFFFFFF));
+                        c1[k] = uint32_t(__viaddmin_s32_relu(-46802 * cr + (-22554 * cb + yk), kG, 0xFFFFFF));
+                        c2[k] = uint32_t(__viaddmin_s32_relu(116130 * cb + yk, kB, 0xFFFFFF));
+                    }
+                }
+                if (K.planar) {
+                    const uint32_t p0w = pack_b2(c0[0], c0[1], c0[2], c0[3]), p2w = pack_b2(c2[0], c2[1], c2[2], c2[3]);
+                    pk[g] = K.bgr ? p2w : p0w;
+                    pk[2 + g] = pack_b2(c1[0], c1[1], c1[2], c1[3]);
+                    pk[4 + g] = K.bgr ? p0w : p2w;
+                } else if (K.bgr) {
+                    pk[3 * g + 0] = pack_b2(c2[0], c1[0], c0[0], c2[1]);
+                    pk[3 * g + 1] = pack_b2(c1[1], c0[1], c2[2], c1[2]);
+                    pk[3 * g + 2] = pack_b2(c0[2], c2[3], c1[3], c0[3]);
+                } else {
+                    pk[3 * g + 0] = pack_b2(c0[0], c1[0], c2[0], c0[1]);
+                    pk[3 * g + 1] = pack_b2(c1[1], c2[1], c0[2], c1[2]);
+                    pk[3 * g + 2] = pack_b2(c2[2], c0[3], c1[3], c2[3]);
+                }
+            }
+            px_store_half(im, K, orow, X - roi_x0, hf, pk, x_lo, x_hi);
+        }
+    }
+}
+
+// The same colour stage over component planes in global memory (the color kernel: images that do not take the fused
+// kernel, and the pixel stage when fused_pixels is off).  A thread takes 16 pixels of `n_rows` consecutive unit rows
+// starting at unit row i_first; neighbours are clamped to the component's real size here (the planes have no aprons).
+struct PxPlanes {
+    const uint8_t* y;
+    const uint8_t* cb;
+    const uint8_t* cr;
+    int ystride, cstride;
+    int dw, dh; // real chroma size
+};
+
+template <int HX, int VX, bool kFancy, bool kLumaOnly>
+__device__ __forceinline__ void px_color_global(const PxOut& im, const PxPlanes& P, const PxColor& K, int X0, int i_first, int n_rows, int y_hi)
+{
+    constexpr bool fancy_v = kFancy && VX == 2;
+    const int roi_x0 = im.roi_x0, roi_x1 = im.roi_x1, roi_y0 = im.roi_y0;
+    if (X0 >= roi_x1 || X0 + kPxUnit <= roi_x0)
+        return;
+#pragma unroll 1
+    for (int row = 0; row < n_rows * VX; ++row) {
+        const int y = VX * i_first + row;
+        if (y < roi_y0 || y >= y_hi)
+            continue;
+        const int i = VX == 2 ? (y >> 1) : y, rr = VX == 2 ? (y & 1) : 0;
+        int nb = rr == 0 ? i - 1 : i + 1; // vertical neighbour, replicated at the component's top and bottom
+        nb = nb < 0 ? 0 : (nb > P.dh - 1 ? P.dh - 1 : nb);
+        const uint8_t* yp = P.y + size_t(y) * P.ystride + X0;
+        const uint8_t* ca = kLumaOnly ? P.y : P.cb + size_t(i) * P.cstride + X0 / HX;
+        const ptrdiff_t a_to_b = kLumaOnly ? 0 : P.cr - P.cb;
+        const ptrdiff_t to_nb = fancy_v ? ptrdiff_t(nb - i) * P.cstride : 0;
+        uint8_t* const orow = im.out + size_t(y - roi_y0) * im.row_stride;
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+            const int X = X0 + 8 * hf;
+            if (X >= roi_x1 || X + 8 <= roi_x0)
+                continue;
+            const int x_lo = max(roi_x0 - X, 0), x_hi = min(roi_x1 - X, 8);
+            int ua[8], ub[8];
+            if (!kLumaOnly) {
+                const int j = X / HX; // first chroma sample of this half
+#pragma unroll
+                for (int ab = 0; ab < 2; ++ab) {
+                    const uint8_t* q = ca + (ab ? a_to_b : 0) + hf * (8 / HX);
+                    int* out = ab ? ub : ua;
+                    if (HX == 2) {
+                        int s[6];
+                        const int lo = j > 0 ? -1 : 0, hi = j + 4 < P.dw ? 4 : P.dw - 1 - j; // where the filter replicates
+                        const uint32_t cw = __ldg(reinterpret_cast<const uint32_t*>(q));
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            s[1 + k] = px_byte(cw, k);
+                        if (kFancy) {
+                            s[0] = __ldg(q + lo);
+                            s[5] = __ldg(q + hi);
+                        }
+                        if (fancy_v) {
+                            const uint32_t nw = __ldg(reinterpret_cast<const uint32_t*>(q + to_nb));
+                            s[0] = 3 * s[0] + __ldg(q + to_nb + lo);
+                            s[5] = 3 * s[5] + __ldg(q + to_nb + hi);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                s[1 + k] = 3 * s[1 + k] + px_byte(nw, k);
+                        }
+                        if (kFancy && j + 3 > P.dw - 1) { // the right image edge lies inside these samples: the last real one repeats
+                            int last = s[1];
+#pragma unroll
+                            for (int k = 1; k < 4; ++k)
+                                if (j + k <= P.dw - 1)
+                                    last = s[1 + k];
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                if (j + k > P.dw - 1)
+                                    s[1 + k] = last;
+                        }
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            if (fancy_v) {
+                                out[2 * k] = (3 * s[k + 1] + 8 + s[k]) >> 4;
+                                out[2 * k + 1] = (3 * s[k + 1] + 7 + s[k + 2]) >> 4;
+                            } else if (kFancy) {
+                                out[2 * k] = (3 * s[k + 1] + 1 + s[k]) >> 2;
+                                out[2 * k + 1] = (3 * s[k + 1] + 2 + s[k + 2]) >> 2;
+                            } else {
+                                out[2 * k] = out[2 * k + 1] = s[k + 1];
+                            }
+                        }
+                    } else {
+                        const uint2 cw = __ldg(reinterpret_cast<const uint2*>(q));
+#pragma unroll
+                        for (int k = 0; k < 8; ++k)
+                            out[k] = px_byte(k < 4 ? cw.x : cw.y, k & 3);
+                        if (fancy_v) {
+                            const uint2 nw = __ldg(reinterpret_cast<const uint2*>(q + to_nb));
+#pragma unroll
+                            for (int k = 0; k < 8; ++k)
+                                out[k] = (3 * out[k] + px_byte(k < 4 ? nw.x : nw.y, k & 3) + 1 + rr) >> 2;
+                        }
+                    }
+                }
+            }
+            const uint2 yv = __ldg(reinterpret_cast<const uint2*>(yp + 8 * hf));
+            uint32_t pk[6];
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+                uint32_t c0[4], c1[4], c2[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    c0[k] = __byte_perm(g ? yv.y : yv.x, 0u, 0x4044 + 0x100 * k);
+                if (kLumaOnly) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        c1[k] = c2[k] = c0[k];
+                } else if (K.yuv) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        c1[k] = uint32_t(ua[4 * g + k]) << 16;
+                        c2[k] = uint32_t(ub[4 * g + k]) << 16;
+                    }
+                } else {
                     constexpr int kR = 32768 - 128 * 91881, kG = 32768 + 128 * (22554 + 46802), kB = 32768 - 128 * 116130;
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {

@@ -518,3 +518,42 @@ def test_huffman_set_cache_crossing_its_limit(decoder_cls):
             assert np.array_equal(outs[j].cpu().numpy(), oracle.decode(srcs[j], oracle.FMT_I_RGB, True)), (rnd, j)
     assert len(seen) > 4096 + 600, len(seen)  # the cache limit was crossed inside a batch
     dec.close()
+
+
+@pytest.mark.parametrize("fancy", [1, 0])
+def test_fused_pixel_kernel_bit_exact(decoder_cls, fancy):
+    """Option fused_pixels=1: IDCT, upsampling and colour in one kernel (component tiles in shared memory, one tile per warp,
+    sliding window for the vertical triangle filter).  Every golden vector, cropped and planar / BGR / Y requests, and a
+    full-size image, against the same references as the default pixel kernels."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    entries, datas = _gold()
+    dec = decoder_cls(0, options=f":fancy_upsampling={fancy} b200_jpeg_decoder:fused_pixels=1")
+    outs = dec.decode(datas, "I_RGB")
+    assert dec.last_status == [_lib.OK] * len(datas)
+    for e, o in zip(entries, outs):
+        assert _sha(o.cpu().numpy()) == e["sha256_rgb_fancy" if fancy else "sha256_rgb_box"], e["name"]
+    if not fancy:
+        outs = dec.decode(datas, "I_RGB", [tuple(e["roi"]) for e in entries])
+        for e, o in zip(entries, outs):
+            assert _sha(o.cpu().numpy()) == e["sha256_roi_box"], e["name"]
+    rng = np.random.default_rng(11)
+    srcs, fmts, rois = [], [], []
+    for i in range(30):
+        h, w = int(rng.integers(17, 700)), int(rng.integers(17, 900))
+        samp = ["444", "422", "420", "440"][i % 4]
+        srcs.append(corpus.encode(corpus.synth(h, w, 7000 + i), 88, samp, rst_interval=int(rng.integers(0, 9))))
+        y0, x0 = int(rng.integers(0, h)), int(rng.integers(0, w))
+        rois.append((y0, x0, int(rng.integers(y0 + 1, h + 1)), int(rng.integers(x0 + 1, w + 1))) if i % 3 else None)
+        fmts.append(["I_RGB", "I_Y", "P_RGB", "I_BGR", "P_BGR"][i % 5])
+    srcs.append(corpus.encode(corpus.synth(1080, 1920, 7100), 90, "420"))
+    fmts.append("I_RGB")
+    rois.append(None)
+    srcs.append(corpus.encode(corpus.synth(90, 70, 7101), 90, gray=True))
+    fmts.append("I_RGB")
+    rois.append(None)
+    outs = dec.decode(srcs, fmts, rois)
+    assert dec.last_status == [_lib.OK] * len(srcs)
+    for d, f, r, o in zip(srcs, fmts, rois, outs):
+        assert np.array_equal(o.cpu().numpy(), oracle.decode(d, OFMT[f], fancy=bool(fancy), roi=r)), (f, r)
+    dec.close()
