@@ -250,6 +250,8 @@ Options parse_options(const char* options, const char* decoder_id)
             o.lanes = std::min(8, std::max(1, std::atoi(value.c_str())));
         else if (name == "chunk_images")
             o.chunk_images = std::max(1, std::atoi(value.c_str()));
+        else if (name == "entry_stream")
+            o.entry_stream = std::atoi(value.c_str()) != 0;
         else if (name == "fused_pixels")
             o.fused_pixels = std::atoi(value.c_str()) != 0;
         else if (name == "sync_finish")
@@ -289,7 +291,7 @@ Decoder::~Decoder()
         cudaEventDestroy(done_event_);
     if (side_stream_)
         cudaStreamDestroy(side_stream_);
-    for (DeviceBuffer* b : {&upload_, &scratch_, &cmp_, &coef_, &planes_, &bounce_, &scan_scratch_})
+    for (DeviceBuffer* b : {&upload_, &scratch_, &cmp_, &coef_, &sym_, &planes_, &bounce_, &scan_scratch_})
         b->release(sv_);
     for (PinnedBuffer* b : {&scan_host_, &upload_host_, &state_host_})
         b->release(sv_);
@@ -397,9 +399,14 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             sb = 1024;
         bd_.sub_bits = sb;
         bd_.seq_warm = std::max<uint32_t>(kSeqWarmMin, kSeqWarmBits / sb);
+        bd_.sym_mode = opt_.entry_stream ? 1 : 0;
+        bd_.sym_chunks = sym_chunks_for(sb);
+        bd_.sub_shift = 0;
+        while ((1u << bd_.sub_shift) < sb)
+            ++bd_.sub_shift;
     }
     const size_t sub_bytes = bd_.sub_bits / 8;
-    size_t raw_bytes = 0, cmp_bytes = 0, coef_elems = 0, plane_bytes = 0, bounce_bytes = 0;
+    size_t raw_bytes = 0, cmp_bytes = 0, coef_elems = 0, plane_bytes = 0, bounce_bytes = 0, sym_chunks_total = 0;
     uint32_t n_tiles = 0, n_sub = 0, n_seq = 0, n_wseq = 0, n_bnd = 0, n_dc = 0, n_idct = 0, n_color = 0;
     comp_bytes_ = n_coefs_ = out_bytes_ = 0;
 
@@ -521,7 +528,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 host_status_[i] = B200JPEG_ERR_CORRUPT;
                 continue;
             }
-            const uint64_t arena = blocks * 128 + blocks * 64; // coefficients + planes, upper bound
+            // coefficients (dense groups, or the entry stream: 18 bytes reserved per byte of scan) + planes, upper bound
+            const uint64_t arena = (bd_.sym_mode ? uint64_t(hd.scan_length) * 20 : blocks * 128) + blocks * 64;
             if (arena > (uint64_t(opt_.max_arena_mb) << 20) || coef_elems / 64 + blocks >= (uint64_t(1) << 28)) {
                 host_status_[i] = B200JPEG_ERR_TOO_LARGE;
                 continue;
@@ -557,6 +565,9 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.total_blocks = role == kParent ? 0u : n_mcu * uint32_t(hd.blocks_per_mcu);
         im.coef_off = coef_elems;
         coef_elems += size_t(im.total_blocks) * 64;
+        im.sym_off = sym_chunks_total; // entry stream: the chunks of 32 subsequences interleave
+        if (role != kParent)
+            sym_chunks_total += size_t((im.n_sub_max + 31) / 32) * bd_.sym_chunks * 32;
         im.width = uint16_t(hd.width);
         im.height = uint16_t(hd.height);
         im.mcus_x = uint16_t(hd.mcus_x);
@@ -664,7 +675,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 for (int k = 0; k < 64; ++k)
                     im.q8 = (im.q8 && hd.qt[hd.tq[c]][k] <= 255) ? 1 : 0;
             // (the fused kernel dequantises with 8-bit quantisers only; every baseline table is 8 bits wide)
-            bool fused = opt_.fused_pixels && role == kNormal && im.color_mode >= 1 && o.orientation <= 1 && im.q8;
+            bool fused = opt_.fused_pixels && !bd_.sym_mode && role == kNormal && im.color_mode >= 1 && o.orientation <= 1 && im.q8;
             for (int c = 0; c < hd.ncomp; ++c)
                 fused = fused && hd.h[c] <= 2 && hd.v[c] <= 2;
             if (fused) {
@@ -845,12 +856,17 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     so += 256;
     const size_t so_mask = so;
     so = align_up(so + 4ull * (coef_elems / 64), 256);
+    const size_t so_pos = so;
+    so = align_up(so + (bd_.sym_mode ? 4ull * (coef_elems / 64) : 0ull), 256);
 
-    coef_bytes_ = coef_elems * sizeof(int16_t);
+    // the coefficients live either as dense 16-byte groups (coef_) or as the entry stream (sym_), never both
+    coef_bytes_ = bd_.sym_mode ? 0 : coef_elems * sizeof(int16_t);
+    const size_t sym_bytes = bd_.sym_mode ? sym_chunks_total * 16 : 0;
     if (!upload_host_.ensure(upload_bytes, sv_, stream) || !state_host_.ensure(sizeof(ImageState) * std::max(nd, 1), sv_, stream))
         return fail(B200JPEG_ERR_CUDA, "pinned host allocation failed");
     if (!upload_.ensure(upload_bytes, &device_bytes_, sv_, stream) || !scratch_.ensure(so + 256, &device_bytes_, sv_, stream) ||
         !cmp_.ensure(cmp_bytes + 256, &device_bytes_, sv_, stream) || !coef_.ensure(coef_bytes_ + 256, &device_bytes_, sv_, stream) ||
+        !sym_.ensure(sym_bytes + 256, &device_bytes_, sv_, stream) ||
         !planes_.ensure(plane_bytes + 256, &device_bytes_, sv_, stream) || !bounce_.ensure(bounce_bytes + 256, &device_bytes_, sv_, stream))
         return fail(B200JPEG_ERR_CUDA, "device allocation failed");
 
@@ -995,6 +1011,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.blkrec = reinterpret_cast<uint32_t*>(sc + so_mask);
     bd_.cmp = cmp_.as<uint32_t>();
     bd_.coef = coef_.as<int16_t>();
+    bd_.sym = sym_.as<uint4>();
+    bd_.blkpos = reinterpret_cast<uint32_t*>(sc + so_pos);
     bd_.planes = planes_.as<uint8_t>();
     bd_.n_tiles = int(n_tiles);
     bd_.n_seq = int(n_seq);
@@ -1239,6 +1257,53 @@ int Decoder::copy_coefficients(int index, int16_t* host_out, size_t cap_elems)
     if (cap_elems < elems)
         return fail(B200JPEG_ERR_ARG, "buffer too small");
     cudaSetDevice(device_);
+    if (bd_.sym_mode) {
+        // entry-stream form: the same walk the IDCT stage does (sym_fetch_block in pixels.cuh), on the host
+        const int d = dev_index_[index];
+        cudaDeviceSynchronize();
+        const size_t chunks = size_t((im.n_sub_max + 31) / 32) * bd_.sym_chunks * 32;
+        std::vector<uint16_t> sym(chunks * 8);
+        std::vector<uint32_t> recs(im.total_blocks), pos(im.total_blocks);
+        ImageState st{};
+        if (!cuda_ok(cudaMemcpy(sym.data(), bd_.sym + im.sym_off, chunks * 16, cudaMemcpyDeviceToHost), "entry copy") ||
+            !cuda_ok(cudaMemcpy(recs.data(), bd_.blkrec + im.coef_off / 64, recs.size() * 4, cudaMemcpyDeviceToHost), "record copy") ||
+            !cuda_ok(cudaMemcpy(pos.data(), bd_.blkpos + im.coef_off / 64, pos.size() * 4, cudaMemcpyDeviceToHost), "record copy") ||
+            !cuda_ok(cudaMemcpy(&st, bd_.state + d, sizeof(st), cudaMemcpyDeviceToHost), "state copy"))
+            return B200JPEG_ERR_CUDA;
+        std::memset(host_out, 0, elems * sizeof(int16_t));
+        for (size_t b = 0; b < recs.size(); ++b) {
+            int16_t* blk = host_out + b * 64;
+            blk[0] = int16_t(recs[b] >> 16);
+            uint32_t k = pos[b] >> bd_.sub_shift, slot = (recs[b] & 0xFFFFu) + 1u, z = 1;
+            bool done = k >= st.n_sub;
+            for (int guard = 0; !done && guard < 4096; ++guard) {
+                if (slot >= bd_.sym_chunks * 8)
+                    break;
+                const size_t chunk = (size_t(k >> 5) * bd_.sym_chunks + (slot >> 3)) * 32 + (k & 31u);
+                const uint32_t e = sym[chunk * 8 + (slot & 7u)];
+                const int32_t val = int32_t(e << 20) >> 20;
+                const uint32_t run = e >> 12;
+                ++slot;
+                if (val != 0) {
+                    z += run;
+                    if (z > 63)
+                        break;
+                    blk[z++] = int16_t(val);
+                    done = z > 63;
+                } else if (run == 0) {
+                    done = true;
+                } else if (run == 15) {
+                    z += 16;
+                    done = z > 63;
+                } else if (run == 2) {
+                    ++k;
+                    slot = 0;
+                    done = k >= st.n_sub;
+                }
+            }
+        }
+        return B200JPEG_OK;
+    }
     if (!cuda_ok(cudaMemcpy(host_out, bd_.coef + im.coef_off, elems * sizeof(int16_t), cudaMemcpyDeviceToHost), "coefficient copy"))
         return B200JPEG_ERR_CUDA;
     // groups K3 skipped (all zero) hold stale bytes on the device: blank them using the per-block records,

@@ -84,6 +84,7 @@ struct Options {
     int lanes = 6;                // pipeline lanes (decoder + stream each) the chunks rotate over
     int chunk_images = 64;        // ... or this many images, whichever comes first
     int host_threads = 0;         // helper threads for marker walks / staging (0 = by the CPUs this process may run on, at most 8)
+    bool entry_stream = true;     // K3 writes the coefficients as a stream of 16-bit entries (huff_emit) instead of dense 16-byte groups (huff_write)
     bool fused_pixels = false;    // IDCT + upsampling + colour in one kernel (pixels_kernel); off: the idct and color kernels, which are faster as measured (profiles/)
     bool sync_finish = false;     // Finish / DecodeBatch wait for the pixel kernels too, not only for the statuses
     int max_arena_mb = 32768;     // refuse (ERR_TOO_LARGE) images whose coefficient + plane arenas would exceed this many MiB
@@ -158,7 +159,7 @@ class Decoder {
     bool prepared_ = false, executed_ = false, finish_queued_ = false, any_host_out_ = false;
 
     // device memory
-    DeviceBuffer upload_, scratch_, cmp_, coef_, planes_, bounce_, scan_scratch_;
+    DeviceBuffer upload_, scratch_, cmp_, coef_, sym_, planes_, bounce_, scan_scratch_;
     PinnedBuffer upload_host_, state_host_, scan_host_;
     size_t device_bytes_ = 0;
     size_t coef_bytes_ = 0;

@@ -1428,10 +1428,11 @@ __device__ __forceinline__ uint32_t range_limit(int32_t x)
 
 #include "pixels.cuh"
 
-__global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
+__global__ void __launch_bounds__(128, 6) idct_kernel(BatchDev bd, int redo_only)
 {
     __shared__ uint16_t s_q[3][64];
     __shared__ uint32_t s_qz[3][32]; // 8-bit quantisers paired in zig-zag order (px_idct_rows)
+    __shared__ uint32_t s_scatter[32 * 128]; // entry-stream form: one column of 32 words per thread (sym_fetch_block)
     const uint32_t cta = blockIdx.x;
     const uint32_t img = bd.idct_cta_img[cta];
     const ImageDev& im = bd.img[img];
@@ -1481,9 +1482,19 @@ __global__ void __launch_bounds__(128) idct_kernel(BatchDev bd, int redo_only)
     const uint32_t bim = im.blk_first[c] + ((by - (my << lv)) << lh) + (bx - (mx << lh));
     const int16_t* src = bd.coef + im.coef_off + (size_t(my * im.mcus_x + mx) * im.bpm + bim) * 64;
     if (q8) {
-        const uint32_t rec = __ldg(bd.blkrec + im.coef_off / 64 + (size_t(my * im.mcus_x + mx) * im.bpm + bim));
+        const size_t blk = im.coef_off / 64 + (size_t(my * im.mcus_x + mx) * im.bpm + bim);
+        const uint32_t rec = __ldg(bd.blkrec + blk);
         uint32_t w[32];
-        px_fetch_block<2>(bd.coef, rec, im.coef_off / 64 + (size_t(my * im.mcus_x + mx) * im.bpm + bim), w);
+        if (bd.sym_mode) {
+            SymSource S;
+            S.sym = bd.sym + im.sym_off;
+            S.chunks = bd.sym_chunks;
+            S.shift = bd.sub_shift;
+            S.n_sub = bd.state[img].n_sub;
+            sym_fetch_block(S, rec, __ldg(bd.blkpos + blk), smem_addr(s_scatter) + threadIdx.x * 4u, 128u * 4u, w);
+        } else {
+            px_fetch_block<2>(bd.coef, rec, blk, w);
+        }
         uint8_t* dst8 = bd.planes + im.plane_off[c] + size_t(by) * 8 * (bw * 8) + bx * 8;
         const uint32_t pitch = bw * 8;
         px_idct_rows<0>(w, int32_t(rec) >> 16, s_qz[c], [](int) {}, [&](int y, uint32_t lo, uint32_t hi) {
@@ -1981,7 +1992,7 @@ __global__ void gate_flags_kernel(BatchDev bd)
 
 // K4b.  Specialised sampling modes without EXIF orientation: a thread owns 16 pixels x (4 unit rows of 1 or 2 output rows),
 // a CTA 512 x (32 or 64) pixels (px_color_global).  Everything else (generic sampling, orientation): one pixel at a time.
-__global__ void __launch_bounds__(kColorTx* kColorTy, 3) color_kernel(BatchDev bd, int redo_only)
+__global__ void __launch_bounds__(kColorTx* kColorTy, 4) color_kernel(BatchDev bd, int redo_only)
 {
     const uint32_t cta = blockIdx.x;
     const uint32_t img = bd.color_cta_img[cta];

@@ -71,6 +71,73 @@ __device__ __forceinline__ void px_fetch_block(const int16_t* __restrict__ coef,
     }
 }
 
+// Coefficients of one block from the entry stream K3 wrote (huff_emit_kernel; format in kernels.cuh): the block's entries
+// start behind the slot its record names, in the subsequence its DC code word lies in, and may continue in the next
+// subsequence.  They are scattered into a per-thread column of shared memory (word j of thread t at scat + j * stride:
+// consecutive threads hit consecutive banks) in the packed zig-zag pair layout the dense form has in memory, and read back.
+// Every address is bounded by what the host reserved, whatever the entries say (damaged streams are reported, never
+// followed out of bounds).
+struct SymSource {
+    const uint4* sym;      // entry stream of the image
+    uint32_t chunks;       // chunks reserved per subsequence
+    uint32_t shift;        // log2 of the subsequence length in bits
+    uint32_t n_sub;        // subsequences of the image
+};
+
+__device__ __forceinline__ void sym_fetch_block(const SymSource& S, uint32_t rec, uint32_t pos, uint32_t scat, uint32_t stride, uint32_t (&w)[32])
+{
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(scat + uint32_t(j) * stride), "r"(0u) : "memory");
+    uint32_t k = pos >> S.shift, slot = (rec & 0xFFFFu) + 1u; // the entry behind the DC symbol's
+    uint32_t z = 1;
+    bool done = k >= S.n_sub;
+#pragma unroll 1
+    for (int guard = 0; !done && guard < 160; ++guard) {
+        const uint32_t c = slot >> 3;
+        if (c >= S.chunks)
+            break;
+        const uint4 ch = __ldg(S.sym + (size_t(k >> 5) * S.chunks + c) * 32 + (k & 31u));
+        const uint32_t cw[4] = {ch.x, ch.y, ch.z, ch.w};
+        bool hop = false;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (done || hop || uint32_t(j) < (slot & 7u))
+                continue;
+            const uint32_t e = (j & 1) ? (cw[j >> 1] >> 16) : (cw[j >> 1] & 0xFFFFu);
+            const int32_t val = int32_t(e << 20) >> 20;
+            const uint32_t run = e >> 12;
+            if (val != 0) {
+                z += run;
+                if (z > 63u) {
+                    done = true;
+                } else {
+                    asm volatile("st.shared.u16 [%0], %1;" ::"r"(scat + (z >> 1) * stride + (z & 1u) * 2u), "h"(uint16_t(val)) : "memory");
+                    ++z;
+                    done = z > 63u;
+                }
+            } else if (run == 0u) { // end of block
+                done = true;
+            } else if (run == 15u) { // sixteen zeros
+                z += 16u;
+                done = z > 63u;
+            } else if (run == 2u) { // the subsequence's entries end here: the block continues in the next one
+                hop = true;
+            }
+        }
+        if (hop) {
+            ++k;
+            slot = 0;
+            done = k >= S.n_sub;
+        } else {
+            slot = (c + 1u) * 8u;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[j]) : "r"(scat + uint32_t(j) * stride) : "memory");
+}
+
 // signed 16-bit halves of a times unsigned bytes of b: lo = a.lo * b.b0 + a.hi * b.b1, hi = a.lo * b.b2 + a.hi * b.b3
 __device__ __forceinline__ int32_t px_dp2a_lo(uint32_t a, uint32_t b)
 {
@@ -478,9 +545,16 @@ struct PxPlanes {
     int dw, dh; // real chroma size
 };
 
-template <int HX, int VX, bool kFancy, bool kLumaOnly>
-__device__ __forceinline__ void px_color_global(const PxOut& im, const PxPlanes& P, const PxColor& K, int X0, int i_first, int n_rows, int y_hi)
+template <int HX, int VX, bool kFancy, bool kLumaOnly, bool kPlainRgb>
+__device__ __forceinline__ void px_color_global_impl(const PxOut& im, const PxPlanes& P, const PxColor& Kin, int X0, int i_first, int n_rows, int y_hi)
 {
+    PxColor K = Kin;
+    if (kPlainRgb) { // interleaved R, G, B: the layout branches fold away
+        K.bgr = 0;
+        K.yuv = 0;
+        K.planar = 0;
+        K.nch = 3;
+    }
     constexpr bool fancy_v = kFancy && VX == 2;
     const int roi_x0 = im.roi_x0, roi_x1 = im.roi_x1, roi_y0 = im.roi_y0;
     if (X0 >= roi_x1 || X0 + kPxUnit <= roi_x0)
@@ -613,6 +687,15 @@ __device__ __forceinline__ void px_color_global(const PxOut& im, const PxPlanes&
             px_store_half(im, K, orow, X - roi_x0, hf, pk, x_lo, x_hi);
         }
     }
+}
+
+template <int HX, int VX, bool kFancy, bool kLumaOnly>
+__device__ __forceinline__ void px_color_global(const PxOut& im, const PxPlanes& P, const PxColor& K, int X0, int i_first, int n_rows, int y_hi)
+{
+    if (!K.bgr && !K.yuv && !K.planar)
+        px_color_global_impl<HX, VX, kFancy, kLumaOnly, true>(im, P, K, X0, i_first, n_rows, y_hi);
+    else
+        px_color_global_impl<HX, VX, kFancy, kLumaOnly, false>(im, P, K, X0, i_first, n_rows, y_hi);
 }
 
 // After phase A, before phase B: the samples the horizontal triangle filter replicates at the left and right edge of the
