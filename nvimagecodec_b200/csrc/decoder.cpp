@@ -244,8 +244,6 @@ Options parse_options(const char* options, const char* decoder_id)
             o.debug_no_warm = std::atoi(value.c_str()) != 0;
         else if (name == "chunk_mb")
             o.chunk_mb = std::max(0, std::atoi(value.c_str()));
-        else if (name == "first_chunk_mb")
-            o.first_chunk_mb = std::max(1, std::atoi(value.c_str()));
         else if (name == "direct_kb")
             o.direct_kb = std::max(1, std::atoi(value.c_str()));
         else if (name == "lanes")
@@ -1441,21 +1439,21 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
         size_t total = 0;
         for (int i = 0; i < n; ++i)
             total += len[i];
-        // Chunks grow geometrically (2, 4, 8 ... MB of bitstream, at most chunk_mb): a small first chunk gets the GPU going while
-        // the host is still walking / staging the rest, the later ones are large enough for the kernels to run at their
-        // full-batch efficiency.  chunk_mb = 0: 64 MB.
-        const size_t chunk_cap = size_t(opt_.chunk_mb ? opt_.chunk_mb : 64) << 20;
-        size_t chunk_bytes = std::min(chunk_cap, size_t(opt_.first_chunk_mb) << 20);
+        size_t chunk_bytes = size_t(opt_.chunk_mb) << 20;
+        if (!chunk_bytes) {
+            // Pinned bitstreams are copied straight from the caller's buffers: small chunks start the GPU early.  Pageable ones
+            // are gathered into a pinned staging block first (helper threads): that wants bigger chunks.
+            chunk_bytes = size_t(pinned ? 8 : 24) << 20;
+        }
         const int chunk_images = opt_.chunk_images;
-        const bool split = lanes_.size() > 1 && (total > (size_t(12) << 20) || n > 2 * chunk_images); // small batches stay whole
+        const bool split = lanes_.size() > 1 && (total > chunk_bytes + chunk_bytes / 3 || n > 2 * chunk_images);
         for (int i = 0; i < n; ++i) {
             acc += len[i];
             ++cnt;
-            if (split && (acc >= chunk_bytes || cnt >= chunk_images * int(std::max<size_t>(1, chunk_bytes >> 21))) && i + 1 < n) {
+            if (split && (acc >= chunk_bytes || cnt >= chunk_images) && i + 1 < n) {
                 cuts.push_back(i + 1);
                 acc = 0;
                 cnt = 0;
-                chunk_bytes = std::min(chunk_cap, chunk_bytes * 2);
             }
         }
         cuts.push_back(n);

@@ -79,11 +79,10 @@ struct Options {
     bool debug_no_warm = false;   // test hook: forces the re-synchronisation path
     int max_fix_rounds = 1 << 20;
     int subseq_bits = 0;          // 0 = choose per batch; else 512 / 1024 / 2048 / 4096
-    int chunk_mb = 0;             // largest pipeline chunk in MB of bitstream (0 = 64); chunks grow geometrically from first_chunk_mb ...
-    int first_chunk_mb = 2;       // ... so that the GPU starts early and the later chunks are large enough for full kernel efficiency
+    int chunk_mb = 0;             // pipeline chunk: this much bitstream (0 = 8 MB for pinned sources, 24 MB for pageable ones, which are staged by helper threads) ...
     int direct_kb = 128;          // pinned bitstreams of at least this many KiB are copied straight from the caller's buffer
     int lanes = 6;                // pipeline lanes (decoder + stream each) the chunks rotate over
-    int chunk_images = 64;        // ... or this many images per 2 MB of chunk budget, whichever comes first
+    int chunk_images = 64;        // ... or this many images, whichever comes first
     int host_threads = 0;         // helper threads for marker walks / staging (0 = by the CPUs this process may run on, at most 8)
     bool entry_stream = true;     // K3 writes the coefficients as a stream of 16-bit entries (huff_emit) instead of dense 16-byte groups (huff_write)
     bool fused_pixels = false;    // IDCT + upsampling + colour in one kernel (pixels_kernel); off: the idct and color kernels, which are faster as measured (profiles/)
