@@ -93,7 +93,7 @@ B200JPEG_API int b200jpegProbe(const void* data, size_t length, b200jpegStreamIn
  * understood: fancy_upsampling=<0|1> (default 1, as libjpeg_turbo_decoder.cpp:223-249).
  * Tuning knobs (defaults are measured choices, results do not depend on them): subseq_bits=<512|1024|2048|4096>
  * (bits of entropy-coded data per GPU thread; default by batch size), lanes=<1..8> (pipeline lanes, default 6),
- * chunk_mb / chunk_images (pipeline chunk, default 8 MB for pinned bitstreams, 24 MB for pageable ones, 64 images),
+ * chunk_mb / chunk_images (pipeline chunk, default 8 MB of bitstream or 64 images),
  * direct_kb (pinned bitstreams of at least this size are copied without staging, default 128), host_threads (helper
  * threads for marker walks and staging copies, default by the CPUs the process may use, at most 8), max_arena_mb (images whose
  * coefficient + plane arenas would exceed it are refused with B200JPEG_ERR_TOO_LARGE, default 32768), max_fix_rounds;

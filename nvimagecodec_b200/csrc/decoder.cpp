@@ -135,6 +135,7 @@ void PinnedBuffer::release(const Services& sv)
 
 // ---- helper threads
 struct HostPool::Impl {
+    std::mutex run_mu; // one job at a time (callers on different threads take turns)
     std::mutex mu;
     std::condition_variable cv_work, cv_done;
     void (*fn)(int, void*) = nullptr;
@@ -192,6 +193,7 @@ void HostPool::run(int n, void (*fn)(int, void*), void* arg)
             fn(i, arg);
         return;
     }
+    std::lock_guard<std::mutex> turn(m.run_mu);
     {
         std::lock_guard<std::mutex> lk(m.mu);
         m.fn = fn;
@@ -254,6 +256,8 @@ Options parse_options(const char* options, const char* decoder_id)
             o.entry_stream = std::atoi(value.c_str()) != 0;
         else if (name == "fused_pixels")
             o.fused_pixels = std::atoi(value.c_str()) != 0;
+        else if (name == "use_executor")
+            o.use_executor = std::atoi(value.c_str()) != 0;
         else if (name == "sync_finish")
             o.sync_finish = std::atoi(value.c_str()) != 0;
         else if (name == "host_threads")
@@ -342,7 +346,7 @@ void parse_input(const void* data, size_t len, ParsedInput* out)
 }
 
 int Decoder::prepare(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, cudaStream_t stream,
-    const ParsedInput* const* parsed, int sources_pinned)
+    const ParsedInput* const* parsed, int sources_pinned, bool defer_upload)
 {
     if (n < 0 || (n > 0 && (!data || !len || !outs)))
         return fail(B200JPEG_ERR_ARG, "null argument");
@@ -426,9 +430,12 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             if (!(c.given && c.given[i]))
                 parse_input(c.data[i], c.len[i], &c.own[i]);
         };
-        if (n >= 16)
+        int to_walk = 0;
+        for (int i = 0; i < n; ++i)
+            to_walk += (parsed && parsed[i]) ? 0 : 1;
+        if (to_walk >= 16)
             parallel_for(n, walk, &ctx);
-        else
+        else if (to_walk)
             for (int i = 0; i < n; ++i)
                 walk(i, &ctx);
     }
@@ -886,8 +893,9 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         sources_pinned = (nd && cudaPointerGetAttributes(&attr, data[in_index_[0]]) == cudaSuccess && attr.type == cudaMemoryTypeHost) ? 1 : 0;
         cudaGetLastError();
     }
-    std::vector<uint8_t> direct(size_t(nd), 0);
-    size_t staged_bytes = 0;
+    direct_.assign(size_t(nd), 0);
+    src_scan_.assign(size_t(nd), nullptr);
+    staged_bytes_ = 0;
     for (int d = 0; d < nd; ++d) {
         ImageDev& im = imgs_[d];
         if (host_outs_[d].host_ptr)
@@ -899,55 +907,11 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         std::fill(idct_img + im.idct_cta_off, idct_img + im.idct_cta_off + im.n_idct_cta, uint32_t(d));
         std::fill(color_img + im.color_cta_off, color_img + im.color_cta_off + im.n_color_cta_x * im.n_color_cta_y, uint32_t(d));
         std::fill(px_img + im.px_cta_off, px_img + im.px_cta_off + im.px_n_cta, uint32_t(d));
+        src_scan_[d] = static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[item_of_dev[d]]->scan_offset;
         if (sources_pinned && im.raw_len >= (uint32_t(opt_.direct_kb) << 10))
-            direct[d] = 1;
+            direct_[d] = 1;
         else
-            staged_bytes += im.raw_len;
-    }
-    const double t2 = trace_enabled() ? trace_now_us() : 0;
-    if (staged_bytes) {
-        nvtx3::scoped_range nvtx_stage{"b200jpeg stage bitstreams"};
-        // staging copies, cut into jobs of about 1 MB for the helper threads
-        struct Job {
-            int d0, d1;
-        };
-        std::vector<Job> jobs;
-        {
-            size_t acc = 0;
-            int d0 = 0;
-            for (int d = 0; d < nd; ++d) {
-                acc += direct[d] ? 0 : imgs_[d].raw_len;
-                if (acc >= (size_t(1) << 20) || d + 1 == nd) {
-                    jobs.push_back({d0, d + 1});
-                    d0 = d + 1;
-                    acc = 0;
-                }
-            }
-        }
-        struct Ctx {
-            const Job* jobs;
-            const uint8_t* direct;
-            const ImageDev* imgs;
-            const void* const* data;
-            const int* in_index;
-            const StreamHeader* const* hdrs;
-            const size_t* item_of_dev;
-            uint8_t* dst;
-        } ctx{jobs.data(), direct.data(), imgs_.data(), data, in_index_.data(), hdrs.data(), item_of_dev.data(), up + off_raw};
-        auto stage = [](int j, void* a) {
-            const Ctx& c = *static_cast<const Ctx*>(a);
-            for (int d = c.jobs[j].d0; d < c.jobs[j].d1; ++d) {
-                if (c.direct[d])
-                    continue;
-                const ImageDev& im = c.imgs[d];
-                std::memcpy(c.dst + im.raw_off, static_cast<const uint8_t*>(c.data[c.in_index[d]]) + c.hdrs[c.item_of_dev[d]]->scan_offset, im.raw_len);
-            }
-        };
-        if (staged_bytes >= (size_t(2) << 20))
-            parallel_for(int(jobs.size()), stage, &ctx);
-        else
-            for (int j = 0; j < int(jobs.size()); ++j)
-                stage(j, &ctx);
+            staged_bytes_ += im.raw_len;
     }
     if (nd) {
         std::memcpy(up + off_img, imgs_.data(), sizeof(ImageDev) * nd);
@@ -955,31 +919,15 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     }
     for (size_t si = 0; si < sets.size(); ++si)
         std::memcpy(up + off_huff + si * sizeof(HuffSetDev), sets[si], sizeof(HuffSetDev));
-
-    const double t3 = trace_enabled() ? trace_now_us() : 0;
-    // one H2D for descriptors + maps + tables (+ the staged raw bytes), then one per directly copied image
-    const size_t first_copy = staged_bytes ? upload_bytes : off_raw;
-    last_stream_ = stream;
-    inflight_ = nd > 0;
-    if (nd && !cuda_ok(cudaMemcpyAsync(upload_.ptr, up, first_copy, cudaMemcpyHostToDevice, stream), "upload"))
-        return B200JPEG_ERR_CUDA;
-    for (int d = 0; d < nd; ++d) {
-        if (!direct[d])
-            continue;
-        const ImageDev& im = imgs_[d];
-        if (!cuda_ok(cudaMemcpyAsync(upload_.as<uint8_t>() + off_raw + im.raw_off,
-                         static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[item_of_dev[d]]->scan_offset, im.raw_len, cudaMemcpyHostToDevice, stream),
-                "bitstream upload"))
-            return B200JPEG_ERR_CUDA;
-    }
-
+    off_raw_ = off_raw;
+    upload_bytes_ = upload_bytes;
+    const double t2 = trace_enabled() ? trace_now_us() : 0;
     if (trace_enabled()) {
-        const double t4 = trace_now_us();
         t_walk_ = t1 - t0;
         t_layout_ = t2 - t1;
-        t_stage_ = t3 - t2;
-        t_h2d_ = t4 - t3;
+        t_stage_ = t_h2d_ = 0;
     }
+
     uint8_t* dv = upload_.as<uint8_t>();
     uint8_t* sc = scratch_.as<uint8_t>();
     bd_.n_images = nd;
@@ -1029,6 +977,85 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         ev_valid_ = true;
     }
     prepared_ = true;
+    staged_ = false;
+    if (defer_upload)
+        return B200JPEG_OK;
+    stage_run();
+    return upload(stream);
+}
+
+// The staging copies of a prepared batch (bitstreams that are not copied straight from the caller's buffers) into the pinned
+// block, cut into jobs of about 1 MB for the helper threads.  May run on any host thread.
+void Decoder::stage_run()
+{
+    const double t0 = trace_enabled() ? trace_now_us() : 0;
+    const int nd = int(imgs_.size());
+    if (staged_bytes_) {
+        nvtx3::scoped_range nvtx_stage{"b200jpeg stage bitstreams"};
+        struct Job {
+            int d0, d1;
+        };
+        std::vector<Job> jobs;
+        {
+            size_t acc = 0;
+            int d0 = 0;
+            for (int d = 0; d < nd; ++d) {
+                acc += direct_[d] ? 0 : imgs_[d].raw_len;
+                if (acc >= (size_t(1) << 20) || d + 1 == nd) {
+                    jobs.push_back({d0, d + 1});
+                    d0 = d + 1;
+                    acc = 0;
+                }
+            }
+        }
+        struct Ctx {
+            const Job* jobs;
+            const uint8_t* direct;
+            const ImageDev* imgs;
+            const uint8_t* const* src;
+            uint8_t* dst;
+        } ctx{jobs.data(), direct_.data(), imgs_.data(), src_scan_.data(), upload_host_.as<uint8_t>() + off_raw_};
+        auto stage = [](int j, void* a) {
+            const Ctx& c = *static_cast<const Ctx*>(a);
+            for (int d = c.jobs[j].d0; d < c.jobs[j].d1; ++d)
+                if (!c.direct[d])
+                    std::memcpy(c.dst + c.imgs[d].raw_off, c.src[d], c.imgs[d].raw_len);
+        };
+        if (staged_bytes_ >= (size_t(2) << 20))
+            parallel_for(int(jobs.size()), stage, &ctx);
+        else
+            for (int j = 0; j < int(jobs.size()); ++j)
+                stage(j, &ctx);
+    }
+    staged_ = true;
+    if (trace_enabled())
+        t_stage_ = trace_now_us() - t0;
+}
+
+// Host-to-device copies of a prepared and staged batch: one for descriptors + maps + tables (+ the staged bitstreams), then
+// one per bitstream that is copied straight from the caller's pinned buffer.
+int Decoder::upload(cudaStream_t stream)
+{
+    if (!prepared_ || !staged_)
+        return fail(B200JPEG_ERR_STATE, "upload without a prepared and staged batch");
+    const double t0 = trace_enabled() ? trace_now_us() : 0;
+    const int nd = int(imgs_.size());
+    const uint8_t* up = upload_host_.as<uint8_t>();
+    const size_t first_copy = staged_bytes_ ? upload_bytes_ : off_raw_;
+    last_stream_ = stream;
+    inflight_ = nd > 0;
+    if (nd && !cuda_ok(cudaMemcpyAsync(upload_.ptr, up, first_copy, cudaMemcpyHostToDevice, stream), "upload"))
+        return B200JPEG_ERR_CUDA;
+    for (int d = 0; d < nd; ++d) {
+        if (!direct_[d])
+            continue;
+        const ImageDev& im = imgs_[d];
+        if (!cuda_ok(cudaMemcpyAsync(upload_.as<uint8_t>() + off_raw_ + im.raw_off, src_scan_[d], im.raw_len, cudaMemcpyHostToDevice, stream),
+                "bitstream upload"))
+            return B200JPEG_ERR_CUDA;
+    }
+    if (trace_enabled())
+        t_h2d_ = trace_now_us() - t0;
     return B200JPEG_OK;
 }
 
@@ -1399,8 +1426,55 @@ Pipeline::Pipeline(int device_id, const Options& opt, int n_lanes, const Service
         l.dec = std::make_unique<Decoder>(device_id, opt, sv_, pool_.get());
 }
 
+void Pipeline::stager_main()
+{
+    for (;;) {
+        Lane* l;
+        {
+            std::unique_lock<std::mutex> lk(st_mu_);
+            st_cv_.wait(lk, [&] { return st_stop_ || !st_queue_.empty(); });
+            if (st_queue_.empty())
+                return;
+            l = st_queue_.front();
+            st_queue_.pop_front();
+        }
+        l->dec->stage_run();
+        {
+            std::lock_guard<std::mutex> lk(st_mu_);
+            l->staged = true;
+        }
+        st_done_cv_.notify_all();
+    }
+}
+
+void Pipeline::submit_stage(Lane& l)
+{
+    if (!stager_.joinable())
+        stager_ = std::thread([this] { stager_main(); });
+    {
+        std::lock_guard<std::mutex> lk(st_mu_);
+        l.staged = false;
+        st_queue_.push_back(&l);
+    }
+    st_cv_.notify_one();
+}
+
+void Pipeline::wait_staged(Lane& l)
+{
+    std::unique_lock<std::mutex> lk(st_mu_);
+    st_done_cv_.wait(lk, [&] { return l.staged; });
+}
+
 Pipeline::~Pipeline()
 {
+    if (stager_.joinable()) {
+        {
+            std::lock_guard<std::mutex> lk(st_mu_);
+            st_stop_ = true;
+        }
+        st_cv_.notify_all();
+        stager_.join();
+    }
     cudaSetDevice(device_);
     for (auto& l : lanes_)
         l.dec.reset(); // while the lane streams are still alive
@@ -1441,9 +1515,9 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
             total += len[i];
         size_t chunk_bytes = size_t(opt_.chunk_mb) << 20;
         if (!chunk_bytes) {
-            // Pinned bitstreams are copied straight from the caller's buffers: small chunks start the GPU early.  Pageable ones
-            // are gathered into a pinned staging block first (helper threads): that wants bigger chunks.
-            chunk_bytes = size_t(pinned ? 8 : 24) << 20;
+            // Small chunks start the GPU early.  Pinned bitstreams are copied straight from the caller's buffers; pageable ones
+            // are gathered into a pinned staging block by the background stager while the previous chunk is launched.
+            chunk_bytes = size_t(8) << 20;
         }
         const int chunk_images = opt_.chunk_images;
         const bool split = lanes_.size() > 1 && (total > chunk_bytes + chunk_bytes / 3 || n > 2 * chunk_images);
@@ -1485,19 +1559,16 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
     };
     for (auto& l : lanes_)
         l.used = false;
-    for (int c = 0; c < n_chunks; ++c) {
-        Lane& l = lanes_[size_t(c) % lanes_.size()];
-        drain(l);
-        const int first = cuts[c], cnt = cuts[c + 1] - cuts[c];
-        cudaStream_t s = user_stream;
-        if (n_chunks > 1) {
-            if (!l.stream && cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking) != cudaSuccess)
-                return B200JPEG_ERR_CUDA;
-            s = l.stream;
-            cudaStreamWaitEvent(s, user_event_, 0);
-        }
-        int rc = l.dec->prepare(cnt, data + first, len + first, outs + first, s, parsed ? parsed + first : nullptr, pinned);
+    // Pageable bitstreams of a split batch are staged in the background: chunk c is being gathered into pinned memory while
+    // this thread lays out chunk c + 1 and uploads / launches chunk c - 1.
+    const bool background = n_chunks > 1 && !pinned;
+    auto launch = [&](Lane& l, int first, int cnt, int rc) {
+        cudaStream_t s = l.active_stream;
         const double e0 = trace_enabled() ? trace_now_us() : 0;
+        if (rc == B200JPEG_OK && background) {
+            wait_staged(l);
+            rc = l.dec->upload(s);
+        }
         if (rc == B200JPEG_OK)
             rc = l.dec->execute(s);
         if (rc == B200JPEG_OK)
@@ -1519,13 +1590,46 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
             if (status)
                 for (int i = 0; i < cnt; ++i)
                     status[first + i] = rc;
-            continue;
+            return;
         }
         l.first = first;
-        l.active_stream = s;
         l.busy = true;
         l.used = true;
+    };
+    Lane* pending = nullptr; // laid out and handed to the stager, not launched yet
+    int pending_first = 0, pending_cnt = 0, pending_rc = B200JPEG_OK;
+    for (int c = 0; c < n_chunks; ++c) {
+        Lane& l = lanes_[size_t(c) % lanes_.size()];
+        if (pending == &l) { // (a single lane: nothing to overlap with)
+            launch(*pending, pending_first, pending_cnt, pending_rc);
+            pending = nullptr;
+        }
+        drain(l);
+        const int first = cuts[c], cnt = cuts[c + 1] - cuts[c];
+        cudaStream_t s = user_stream;
+        if (n_chunks > 1) {
+            if (!l.stream && cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking) != cudaSuccess)
+                return B200JPEG_ERR_CUDA;
+            s = l.stream;
+            cudaStreamWaitEvent(s, user_event_, 0);
+        }
+        l.active_stream = s;
+        const int rc = l.dec->prepare(cnt, data + first, len + first, outs + first, s, parsed ? parsed + first : nullptr, pinned, background);
+        if (background) {
+            if (rc == B200JPEG_OK)
+                submit_stage(l);
+            if (pending)
+                launch(*pending, pending_first, pending_cnt, pending_rc);
+            pending = &l;
+            pending_first = first;
+            pending_cnt = cnt;
+            pending_rc = rc;
+        } else {
+            launch(l, first, cnt, rc);
+        }
     }
+    if (pending)
+        launch(*pending, pending_first, pending_cnt, pending_rc);
     for (auto& l : lanes_)
         drain(l);
     // The caller's stream sees the pixels: it waits (on the device, not on the host) for the last work of every lane.

@@ -5,8 +5,11 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <condition_variable>
 #include <cstdint>
+#include <deque>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <unordered_map>
@@ -79,13 +82,14 @@ struct Options {
     bool debug_no_warm = false;   // test hook: forces the re-synchronisation path
     int max_fix_rounds = 1 << 20;
     int subseq_bits = 0;          // 0 = choose per batch; else 512 / 1024 / 2048 / 4096
-    int chunk_mb = 0;             // pipeline chunk: this much bitstream (0 = 8 MB for pinned sources, 24 MB for pageable ones, which are staged by helper threads) ...
+    int chunk_mb = 0;             // pipeline chunk: this much bitstream (0 = 8 MB) ...
     int direct_kb = 128;          // pinned bitstreams of at least this many KiB are copied straight from the caller's buffer
     int lanes = 6;                // pipeline lanes (decoder + stream each) the chunks rotate over
     int chunk_images = 64;        // ... or this many images, whichever comes first
     int host_threads = 0;         // helper threads for marker walks / staging (0 = by the CPUs this process may run on, at most 8)
     bool entry_stream = true;     // K3 writes the coefficients as a stream of 16-bit entries (huff_emit) instead of dense 16-byte groups (huff_write)
     bool fused_pixels = false;    // IDCT + upsampling + colour in one kernel (pixels_kernel); off: the idct and color kernels, which are faster as measured (profiles/)
+    bool use_executor = false;    // (extension) fan host work out over the framework's executor instead of the decoder's own helper threads (measured: ~0.1 ms of dispatch latency per fan-out)
     bool sync_finish = false;     // Finish / DecodeBatch wait for the pixel kernels too, not only for the statuses
     int max_arena_mb = 32768;     // refuse (ERR_TOO_LARGE) images whose coefficient + plane arenas would exceed this many MiB
 };
@@ -110,7 +114,10 @@ class Decoder {
 
     // parsed: nullptr, or n entries of which the non-null ones replace the marker walk of that input
     int prepare(int n, const void* const* data, const size_t* len, const b200jpegOutput_t* outs, cudaStream_t stream,
-        const ParsedInput* const* parsed = nullptr, int sources_pinned = -1);
+        const ParsedInput* const* parsed = nullptr, int sources_pinned = -1, bool defer_upload = false);
+    // defer_upload: prepare() stops after the layout; the caller then runs stage_run() (on any host thread) and upload()
+    void stage_run();
+    int upload(cudaStream_t stream);
     int execute(cudaStream_t stream);
     int finish(int* status, cudaStream_t stream);
     int finish_async(cudaStream_t stream);          // queue read-backs / host-output copies
@@ -156,6 +163,10 @@ class Decoder {
     };
     std::vector<HostOut> host_outs_;    // per device image; host_ptr == nullptr if output is a device buffer
     std::vector<ParsedInput> parsed_own_;
+    std::vector<uint8_t> direct_;            // per device image: copied straight from the caller's (pinned) buffer
+    std::vector<const uint8_t*> src_scan_;   // per device image: first byte of its entropy-coded segment in the caller's buffer
+    size_t staged_bytes_ = 0, off_raw_ = 0, upload_bytes_ = 0;
+    bool staged_ = false;
     bool prepared_ = false, executed_ = false, finish_queued_ = false, any_host_out_ = false;
 
     // device memory
@@ -219,7 +230,19 @@ class Pipeline {
         int first = 0;
         bool busy = false;
         bool used = false; // took part in the current call (its done event gates the caller's stream)
+        bool staged = true; // (under st_mu_) the background staging of its current chunk has finished
     };
+    // Staging of pageable bitstreams runs on a background thread (which fans the copies out over the helper threads): the
+    // calling thread meanwhile lays out the next chunk and uploads / launches the previous one.
+    void stager_main();
+    void submit_stage(Lane& l);
+    void wait_staged(Lane& l);
+    std::thread stager_;
+    std::mutex st_mu_;
+    std::condition_variable st_cv_, st_done_cv_;
+    std::deque<Lane*> st_queue_;
+    bool st_stop_ = false;
+
     int device_;
     Options opt_;
     Services sv_;

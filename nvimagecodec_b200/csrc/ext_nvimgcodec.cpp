@@ -291,7 +291,7 @@ class DecoderImpl {
             sv_.pinned_malloc = ep_->pinned_allocator->pinned_malloc;
             sv_.pinned_free = ep_->pinned_allocator->pinned_free;
         }
-        if (ep_->executor && ep_->executor->schedule && ep_->executor->run && ep_->executor->getNumThreads &&
+        if (opt_.use_executor && ep_->executor && ep_->executor->schedule && ep_->executor->run && ep_->executor->getNumThreads &&
             ep_->executor->getNumThreads(ep_->executor->instance) > 0) {
             exec_ctx_.executor = ep_->executor;
             exec_ctx_.device_id = ep_->device_id;
