@@ -3,6 +3,9 @@
 #include "decoder.h"
 
 #include <nvtx3/nvtx3.hpp>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 #include <sched.h>
 
 #include <algorithm>
@@ -984,6 +987,29 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     return upload(stream);
 }
 
+// Copy into the pinned staging block with non-temporal stores: the block is only ever read by the copy engine, so pulling its
+// lines into the caches first (what a plain store does) is wasted memory traffic.  dst is 16-byte aligned.
+static void stream_copy(uint8_t* dst, const uint8_t* src, size_t n)
+{
+#if defined(__SSE2__)
+    size_t i = 0;
+    for (; i + 64 <= n; i += 64) {
+        const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i));
+        const __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i + 16));
+        const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i + 32));
+        const __m128i d = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i + 48));
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i), a);
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i + 16), b);
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i + 32), c);
+        _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i + 48), d);
+    }
+    if (i < n)
+        std::memcpy(dst + i, src + i, n - i);
+#else
+    std::memcpy(dst, src, n);
+#endif
+}
+
 // The staging copies of a prepared batch (bitstreams that are not copied straight from the caller's buffers) into the pinned
 // block, cut into jobs of about 1 MB for the helper threads.  May run on any host thread.
 void Decoder::stage_run()
@@ -1019,7 +1045,10 @@ void Decoder::stage_run()
             const Ctx& c = *static_cast<const Ctx*>(a);
             for (int d = c.jobs[j].d0; d < c.jobs[j].d1; ++d)
                 if (!c.direct[d])
-                    std::memcpy(c.dst + c.imgs[d].raw_off, c.src[d], c.imgs[d].raw_len);
+                    stream_copy(c.dst + c.imgs[d].raw_off, c.src[d], c.imgs[d].raw_len);
+#if defined(__SSE2__)
+            _mm_sfence();
+#endif
         };
         if (staged_bytes_ >= (size_t(2) << 20))
             parallel_for(int(jobs.size()), stage, &ctx);
@@ -1416,7 +1445,7 @@ Pipeline::Pipeline(int device_id, const Options& opt, int n_lanes, const Service
             cpu_set_t set;
             CPU_ZERO(&set);
             const int cpus = sched_getaffinity(0, sizeof(set), &set) == 0 ? CPU_COUNT(&set) : int(std::thread::hardware_concurrency());
-            n = std::min(8, std::max(1, cpus / 2));
+            n = std::min(12, std::max(1, cpus - 4));
         }
         if (n > 1)
             pool_ = std::make_unique<HostPool>(n - 1); // the calling thread takes part
