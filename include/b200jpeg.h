@@ -80,6 +80,9 @@ typedef struct {
                            swap width and height: the buffer then holds roi_width rows of roi_height pixels.  What
                            nvimgcodecDecodeParams_t::apply_exif_orientation asks of a decoder (include/nvimgcodec.h:784);
                            the reference's CPU plugin declines it (libjpeg_turbo_decoder.cpp:206-209), nvjpeg_ext applies it. */
+    size_t plane_stride; /* bytes between the planes of a planar output; 0 = row_stride * rows of the decoded region (planes back
+                           to back).  Set when the region is embedded in a taller image, e.g. an out-of-bounds region whose
+                           border the caller fills (src/imgproc/out_of_bound_roi_fill.cpp:90-171). */
 } b200jpegOutput_t;
 
 /* Host-only marker walk (SOI .. SOS): tables present, sampling, restart interval,

@@ -45,7 +45,7 @@ class Allocators(ctypes.Structure):
 class Output(ctypes.Structure):
     _fields_ = [("buffer", ctypes.c_void_p), ("format", ctypes.c_int), ("buffer_is_host", ctypes.c_int),
                 ("row_stride", ctypes.c_size_t), ("roi_x0", ctypes.c_int), ("roi_y0", ctypes.c_int),
-                ("roi_x1", ctypes.c_int), ("roi_y1", ctypes.c_int), ("orientation", ctypes.c_int)]
+                ("roi_x1", ctypes.c_int), ("roi_y1", ctypes.c_int), ("orientation", ctypes.c_int), ("plane_stride", ctypes.c_size_t)]
 
 
 EXPORTS = ["b200jpegProbe", "b200jpegCreate", "b200jpegCreateEx", "b200jpegDestroy", "b200jpegDecodeBatch", "b200jpegPrepareBatch",

@@ -40,6 +40,9 @@ double trace_now_us()
 namespace {
 bool device_has_pools()
 {
+    static const bool off = std::getenv("B200JPEG_NO_POOL") != nullptr; // experiments: plain cudaMalloc instead of stream-ordered allocation
+    if (off)
+        return false;
     static int cached[64];
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
@@ -641,7 +644,11 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         im.roi_x1 = uint16_t(x1);
         im.roi_y1 = uint16_t(y1);
         im.row_stride = uint32_t(stride);
-        im.plane_stride = stride * out_h;
+        im.plane_stride = o.plane_stride ? o.plane_stride : stride * out_h;
+        if (planar && o.plane_stride && (o.plane_stride < stride * out_h || o.buffer_is_host)) {
+            host_status_[i] = B200JPEG_ERR_ARG; // (host outputs are bounced tightly: no embedding there)
+            continue;
+        }
         im.orient = uint8_t(o.orientation);
         const size_t obytes = planar ? 3 * stride * out_h : stride * out_h;
         // K4b specialisation (kernels.cu color_kernel): fast paths need full-resolution luma and

@@ -81,10 +81,37 @@ bool map_stream(const nvimgcodecCodeStreamDesc_t* cs, MappedStream* out)
 
 int to_exif_code(const nvimgcodecOrientation_t& o);
 
+// A region that reaches outside the image (what nvjpeg_ext accepts and fills, extensions/nvjpeg/cuda_decoder.cpp:763-766 with
+// src/imgproc/out_of_bound_roi_fill.cpp:90-199): the decoder writes the part inside the image at its place in the caller's
+// buffer, the border is set to the region's constant samples -- one value per plane -- with 2-D memsets on the batch's stream.
+struct BorderFill {
+    bool needed = false;
+    uint8_t* base = nullptr;   // the caller's buffer
+    size_t row_stride = 0, plane_bytes = 0;
+    int planes = 1, bytes_per_px = 1;
+    int width = 0, height = 0; // the whole region, in pixels
+    int in_x0 = 0, in_y0 = 0, in_x1 = 0, in_y1 = 0; // the part inside the image, in region coordinates
+    int value[3] = {0, 0, 0};
+};
+
+uint32_t fill_bits(const nvimgcodecRegion_t& region, uint32_t comp) // get_fill_bits, out_of_bound_roi_fill.cpp:48-88, for 8-bit samples
+{
+    const auto& sm = region.out_of_bounds_samples[std::min<uint32_t>(comp, NVIMGCODEC_MAX_ROI_FILL_CHANNELS - 1)];
+    switch (sm.type) {
+    case NVIMGCODEC_SAMPLE_DATA_TYPE_UINT8:
+    case NVIMGCODEC_SAMPLE_DATA_TYPE_UINT16:
+    case NVIMGCODEC_SAMPLE_DATA_TYPE_UINT32: return sm.value.as_uint;
+    case NVIMGCODEC_SAMPLE_DATA_TYPE_INT8:
+    case NVIMGCODEC_SAMPLE_DATA_TYPE_INT16:
+    case NVIMGCODEC_SAMPLE_DATA_TYPE_INT32: return uint32_t(sm.value.as_int);
+    default: return 0;
+    }
+}
+
 // Translate the requested nvimgcodecImageInfo_t into a b200jpegOutput_t.  Returns a processing
 // status: SUCCESS or an OR of the *_UNSUPPORTED bits (include/nvimgcodec.h:735-768).
 nvimgcodecProcessingStatus_t translate_output(const nvimgcodecImageInfo_t& info, const nvimgcodecRegion_t* region, int img_w, int img_h,
-    bool apply_orientation, b200jpegOutput_t* out)
+    bool apply_orientation, b200jpegOutput_t* out, BorderFill* border = nullptr)
 {
     nvimgcodecProcessingStatus_t st = NVIMGCODEC_PROCESSING_STATUS_SUCCESS;
     std::memset(out, 0, sizeof(*out));
@@ -137,8 +164,38 @@ nvimgcodecProcessingStatus_t translate_output(const nvimgcodecImageInfo_t& info,
         } else {
             // start/end are [y, x] (extensions/libjpeg_turbo/libjpeg_turbo_decoder.cpp:359-362)
             const int y0 = region->start[0], x0 = region->start[1], y1 = region->end[0], x1 = region->end[1];
-            if (y0 < 0 || x0 < 0 || y1 > img_h || x1 > img_w || y0 >= y1 || x0 >= x1) {
-                st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED; // out-of-bounds ROI: declined like libjpeg_turbo_ext (:154-157)
+            const bool oob = y0 < 0 || x0 < 0 || y1 > img_h || x1 > img_w;
+            const int cy0 = std::max(y0, 0), cx0 = std::max(x0, 0), cy1 = std::min(y1, img_h), cx1 = std::min(x1, img_w);
+            if (y0 >= y1 || x0 >= x1) {
+                st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED;
+            } else if (oob) {
+                // Out of bounds: filled like nvjpeg_ext does where that is well defined -- constant policy, device buffer, some of
+                // the region inside the image, one fill value per plane (out_of_bound_roi_fill.cpp:104-107, 190-192)
+                bool ok = cy0 < cy1 && cx0 < cx1 && region->out_of_bounds_policy == NVIMGCODEC_OUT_OF_BOUNDS_POLICY_CONSTANT &&
+                          info.buffer_kind == NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_DEVICE;
+                if (want_planes == 1 && want_channels == 3)
+                    ok = ok && (fill_bits(*region, 0) & 0xFFu) == (fill_bits(*region, 1) & 0xFFu) && (fill_bits(*region, 0) & 0xFFu) == (fill_bits(*region, 2) & 0xFFu);
+                if (!ok) {
+                    st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED;
+                } else {
+                    out->roi_x0 = cx0;
+                    out->roi_y0 = cy0;
+                    out->roi_x1 = cx1;
+                    out->roi_y1 = cy1;
+                    rw = x1 - x0; // the image the caller holds has the size of the whole region
+                    rh = y1 - y0;
+                    if (border) {
+                        border->needed = true;
+                        border->width = rw;
+                        border->height = rh;
+                        border->in_x0 = cx0 - x0;
+                        border->in_y0 = cy0 - y0;
+                        border->in_x1 = cx1 - x0;
+                        border->in_y1 = cy1 - y0;
+                        for (int p = 0; p < 3; ++p)
+                            border->value[p] = int(fill_bits(*region, want_planes == 3 ? uint32_t(p) : 0u) & 0xFFu);
+                    }
+                }
             } else {
                 out->roi_x0 = x0;
                 out->roi_y0 = y0;
@@ -167,6 +224,18 @@ nvimgcodecProcessingStatus_t translate_output(const nvimgcodecImageInfo_t& info,
     out->buffer = info.buffer;
     out->buffer_is_host = (info.buffer_kind == NVIMGCODEC_IMAGE_BUFFER_KIND_STRIDED_HOST) ? 1 : 0;
     out->row_stride = info.plane_info[0].row_stride;
+    if (border && border->needed) {
+        if (exif > 1)
+            st |= NVIMGCODEC_PROCESSING_STATUS_ROI_UNSUPPORTED;
+        border->base = static_cast<uint8_t*>(info.buffer);
+        border->row_stride = info.plane_info[0].row_stride;
+        border->planes = want_planes;
+        border->bytes_per_px = want_planes == 1 ? want_channels : 1;
+        border->plane_bytes = border->row_stride * size_t(info.plane_info[0].height);
+        // the decoder writes the inside part where it belongs in the caller's image
+        out->buffer = border->base + size_t(border->in_y0) * border->row_stride + size_t(border->in_x0) * border->bytes_per_px;
+        out->plane_stride = border->plane_bytes;
+    }
     // planes of a planar image lie back to back at row_stride*height (extensions/nvjpeg/cuda_decoder.cpp:716-722);
     // the kernels assume exactly that with height == ROI height
     if (want_planes == 3 && int(info.plane_info[0].height) != rh)
@@ -338,8 +407,9 @@ class DecoderImpl {
             region = &csi.code_stream_view->region;
         }
         b200jpegOutput_t out;
+        BorderFill border;
         st |= translate_output(info, region, int(cs_info.plane_info[0].width), int(cs_info.plane_info[0].height),
-            params->apply_exif_orientation != 0, &out);
+            params->apply_exif_orientation != 0, &out, &border);
         // YCbCr output only for YCbCr streams without subsampling, as libjpeg_turbo_decoder.cpp:180-189
         if ((info.sample_format == NVIMGCODEC_SAMPLEFORMAT_I_YUV || info.sample_format == NVIMGCODEC_SAMPLEFORMAT_P_YUV) &&
             (cs_info.color_spec != NVIMGCODEC_COLORSPEC_SYCC || cs_info.chroma_subsampling != NVIMGCODEC_SAMPLING_444))
@@ -415,6 +485,7 @@ class DecoderImpl {
         std::vector<nvimgcodecProcessingStatus_t> pre(n, NVIMGCODEC_PROCESSING_STATUS_SUCCESS);
         std::vector<int> status(n, B200JPEG_ERR_STATE);
         std::vector<std::unique_ptr<Walked>> walked(n);
+        std::vector<BorderFill> borders; // samples whose region reaches outside the image
         std::vector<const b200jpeg::ParsedInput*> parsed(n, nullptr);
         cudaStream_t stream = nullptr;
         bool have_stream = false;
@@ -434,14 +505,31 @@ class DecoderImpl {
                 have_stream = true;
             }
             const nvimgcodecRegion_t* region = csi.code_stream_view ? &csi.code_stream_view->region : nullptr;
+            BorderFill border;
             pre[i] = translate_output(info, region, int(cs_info.plane_info[0].width), int(cs_info.plane_info[0].height), apply_orientation,
-                &outs[i]);
+                &outs[i], &border);
+            if (pre[i] == NVIMGCODEC_PROCESSING_STATUS_SUCCESS && border.needed)
+                borders.push_back(border);
             if (pre[i] == NVIMGCODEC_PROCESSING_STATUS_SUCCESS) {
                 data[i] = streams[i].data;
                 len[i] = streams[i].size;
                 walked[i] = recall(css[i], streams[i].data, streams[i].size);
                 if (walked[i])
                     parsed[i] = &walked[i]->parsed;
+            }
+        }
+        for (const BorderFill& b : borders) { // four strips around the part inside the image, per plane
+            for (int p = 0; p < b.planes; ++p) {
+                uint8_t* plane = b.base + size_t(p) * b.plane_bytes;
+                const size_t bpp = size_t(b.bytes_per_px);
+                auto fill = [&](int x, int y, int w, int h) {
+                    if (w > 0 && h > 0)
+                        cudaMemset2DAsync(plane + size_t(y) * b.row_stride + size_t(x) * bpp, b.row_stride, b.value[p], size_t(w) * bpp, size_t(h), stream);
+                };
+                fill(0, 0, b.width, b.in_y0);
+                fill(0, b.in_y1, b.width, b.height - b.in_y1);
+                fill(0, b.in_y0, b.in_x0, b.in_y1 - b.in_y0);
+                fill(b.in_x1, b.in_y0, b.width - b.in_x1, b.in_y1 - b.in_y0);
             }
         }
         const double tr1 = b200jpeg::trace_enabled() ? b200jpeg::trace_now_us() : 0;

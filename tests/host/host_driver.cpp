@@ -16,6 +16,7 @@
 //     HOST_DRIVER_COUNT_ALLOC=1  hand the decoder counting device / pinned allocators through nvimgcodecExecutionParams_t
 //                                (include/nvimgcodec.h:1095-1096) and print how often each was called
 //     HOST_DRIVER_PINNED=1       host output buffers are pinned (cudaMallocHost) instead of malloc'ed
+//     HOST_DRIVER_FILL=<0..255>  constant sample for the parts of a region that lie outside the image (include/nvimgcodec.h:495-519)
 #include <cuda_runtime_api.h>
 #include <nvimgcodec.h>
 
@@ -184,6 +185,13 @@ int main(int argc, char** argv)
             view.region.start[1] = it.x0;
             view.region.end[0] = it.y1;
             view.region.end[1] = it.x1;
+            if (const char* fv = std::getenv("HOST_DRIVER_FILL")) {
+                view.region.out_of_bounds_policy = NVIMGCODEC_OUT_OF_BOUNDS_POLICY_CONSTANT;
+                for (int k = 0; k < NVIMGCODEC_MAX_ROI_FILL_CHANNELS; ++k) {
+                    view.region.out_of_bounds_samples[k].type = NVIMGCODEC_SAMPLE_DATA_TYPE_UINT8;
+                    view.region.out_of_bounds_samples[k].value.as_uint = unsigned(std::atoi(fv));
+                }
+            }
             CHECK(nvimgcodecCodeStreamGetSubCodeStream(parents[i], &streams[i], &view));
             it.w = it.x1 - it.x0;
             it.h = it.y1 - it.y0;

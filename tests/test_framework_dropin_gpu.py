@@ -221,3 +221,40 @@ def test_reference_python_binding_picks_the_extension(tmp_path):
         assert np.array_equal(rgb, oracle.decode(data, oracle.FMT_I_RGB, fancy=False)), name
         gray = np.load(tmp_path / (name + "_gray.npy"))
         assert np.array_equal(gray.reshape(gray.shape[0], gray.shape[1]), oracle.decode(data, oracle.FMT_Y, fancy=False)), name
+
+
+@pytest.mark.skipif(not os.path.exists(DRIVER), reason="reference core not built (oracle/build_ref.sh)")
+def test_out_of_bounds_region_is_filled(tmp_path):
+    """Regions that reach outside the image (nvimgcodecRegion_t with the constant out-of-bounds policy): what nvjpeg_ext accepts
+    and fills (extensions/nvjpeg/cuda_decoder.cpp:763-766, src/imgproc/out_of_bound_roi_fill.cpp) and libjpeg_turbo_ext declines.
+    The part inside the image must equal the crop of the full decode, everything else the fill sample."""
+    from nvimagecodec_b200 import corpus
+
+    cases = [(120, 160, "420", "I_RGB", (-7, -11, 100, 130)), (97, 131, "444", "P_RGB", (10, 20, 140, 150)),
+             (64, 200, "422", "I_Y", (-5, 30, 70, 260)), (80, 80, "420", "I_BGR", (-16, -16, 96, 96)),
+             (75, 61, "444", "P_BGR", (5, -9, 60, 40))]
+    entries = []
+    for k, (h, w, samp, fmt, roi) in enumerate(cases):
+        entries.append((corpus.encode(corpus.synth(h, w, 880 + k), 88, samp, rst_interval=k), fmt, roi, "device"))
+    old = os.environ.get("HOST_DRIVER_FILL")
+    os.environ["HOST_DRIVER_FILL"] = "77"
+    try:
+        status, raws, log = _run(tmp_path, entries, ":fancy_upsampling=1")
+    finally:
+        if old is None:
+            os.environ.pop("HOST_DRIVER_FILL")
+        else:
+            os.environ["HOST_DRIVER_FILL"] = old
+    for (data, fmt, roi, _), (h, w, _, _, _), st, raw in zip(entries, cases, status, raws):
+        assert st[0] == 1, (st, log[-1500:])
+        full = oracle.decode(data, OFMT[fmt], fancy=True)
+        y0, x0, y1, x1 = roi
+        planar = fmt.startswith("P_")
+        shape = (3, y1 - y0, x1 - x0) if planar else ((y1 - y0, x1 - x0) if fmt == "I_Y" else (y1 - y0, x1 - x0, 3))
+        want = np.full(shape, 77, np.uint8)
+        cy0, cx0, cy1, cx1 = max(y0, 0), max(x0, 0), min(y1, h), min(x1, w)
+        if planar:
+            want[:, cy0 - y0:cy1 - y0, cx0 - x0:cx1 - x0] = full[:, cy0:cy1, cx0:cx1]
+        else:
+            want[cy0 - y0:cy1 - y0, cx0 - x0:cx1 - x0] = full[cy0:cy1, cx0:cx1]
+        assert raw.size == want.size and np.array_equal(raw, want.reshape(-1)), (fmt, roi)
