@@ -1621,8 +1621,6 @@ __device__ __forceinline__ int sample_plane(const PlaneView& pv, int x, int y)
     return (3 * cur + 3 * s0[j - 1] + s1[j - 1] + 8) >> 4;
 }
 
-__device__ __forceinline__ uint32_t clamp255(int v) { return uint32_t(__vimin_s32_relu(v, 255)); }
-
 // jdcolor.c fixed-point YCbCr -> RGB (SURVEY.md 8c "Colour"); __viaddmin_s32_relu(a, b, c) is
 // max(min(a + b, c), 0) in one instruction, i.e. the add and the [0,255] clamp together.
 __device__ __forceinline__ void ycc_to_rgb(int y, int cb, int cr, uint32_t& r, uint32_t& g, uint32_t& b)
@@ -1634,35 +1632,11 @@ __device__ __forceinline__ void ycc_to_rgb(int y, int cb, int cr, uint32_t& r, u
     b = uint32_t(__viaddmin_s32_relu(y, (116130 * cb + 32768) >> 16, 255));
 }
 
-// The same transform 16 bits up, for the 8-pixel units: with y16 = y << 16 the sample is byte 2 of
-//   clamp(y16 + C * (c - 128) + 32768, 0, 0xFFFFFF)      (floor((y16 + t) / 65536) == y + floor(t / 65536)),
-// the -128 folded into the constant, so a channel costs one multiply-add and one add-clamp, no shift; the
-// byte permutes that pack the output words pick byte 2 instead of byte 0.
-__device__ __forceinline__ void ycc_to_rgb16(int y16, int cb, int cr, uint32_t& r, uint32_t& g, uint32_t& b)
-{
-    constexpr int kR = 32768 - 128 * 91881, kG = 32768 + 128 * (22554 + 46802), kB = 32768 - 128 * 116130;
-    r = uint32_t(__viaddmin_s32_relu(y16, 91881 * cr + kR, 0xFFFFFF));
-    g = uint32_t(__viaddmin_s32_relu(y16, -22554 * cb + (-46802 * cr + kG), 0xFFFFFF));
-    b = uint32_t(__viaddmin_s32_relu(y16, 116130 * cb + kB, 0xFFFFFF));
-}
 // byte 2 of a, b, c, d -> one little-endian word
 __device__ __forceinline__ uint32_t pack_b2(uint32_t a, uint32_t b, uint32_t c, uint32_t d)
 {
     return __byte_perm(__byte_perm(a, b, 0x0062), __byte_perm(c, d, 0x0062), 0x5410);
 }
-// the eight bytes of v, each moved to byte 2 of its own word
-__device__ __forceinline__ void unpack8_b2(uint2 v, uint32_t* o)
-{
-    o[0] = __byte_perm(v.x, 0u, 0x4044);
-    o[1] = __byte_perm(v.x, 0u, 0x4144);
-    o[2] = __byte_perm(v.x, 0u, 0x4244);
-    o[3] = __byte_perm(v.x, 0u, 0x4344);
-    o[4] = __byte_perm(v.y, 0u, 0x4044);
-    o[5] = __byte_perm(v.y, 0u, 0x4144);
-    o[6] = __byte_perm(v.y, 0u, 0x4244);
-    o[7] = __byte_perm(v.y, 0u, 0x4344);
-}
-
 constexpr int kColorTx = 32; // threads in x, 8 pixels each
 constexpr int kColorTy = 8;  // thread rows, color_unit_rows output rows each
 
@@ -1746,86 +1720,6 @@ __device__ __forceinline__ void color_pixel_generic(const BatchDev& bd, const Im
     }
 }
 
-__device__ __forceinline__ void unpack8(uint2 v, int* o)
-{
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        o[i] = int((v.x >> (8 * i)) & 0xFFu);
-        o[4 + i] = int((v.y >> (8 * i)) & 0xFFu);
-    }
-}
-
-// Chroma samples for 8 output pixels of one chroma row: HX == 2 -> 6 values (left neighbour, 4
-// centres, right neighbour, all clamped to [0, dw-1] which reproduces libjpeg's edge formulas);
-// HX == 1 -> 8 values.
-template <int HX>
-__device__ __forceinline__ void load_chroma_row(const uint8_t* row, int j0, int dw, int* c)
-{
-    if (HX == 2) {
-        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(row + j0));
-        c[0] = __ldg(row + (j0 > 0 ? j0 - 1 : 0));
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            c[1 + k] = int((w >> (8 * k)) & 0xFFu);
-        c[5] = __ldg(row + (j0 + 4 < dw ? j0 + 4 : dw - 1));
-        if (j0 + 3 > dw - 1) { // right image edge inside this unit: replicate the last real sample
-            int last = c[1];
-#pragma unroll
-            for (int k = 1; k < 4; ++k)
-                if (j0 + k <= dw - 1)
-                    last = c[1 + k];
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (j0 + k > dw - 1)
-                    c[1 + k] = last;
-        }
-    } else {
-        unpack8(__ldg(reinterpret_cast<const uint2*>(row + j0)), c);
-    }
-}
-
-// Upsampled chroma for the 8 output pixels of output row `r` (0 or 1 inside the unit).
-//   cur / nbr: chroma row samples as loaded by load_chroma_row (nbr = vertical neighbour, or == cur)
-template <int HX, int VX, bool kFancy>
-__device__ __forceinline__ void upsample8(const int* cur, const int* nbr, int r, int* out)
-{
-    constexpr bool fancy_h = kFancy, fancy_v = kFancy;
-    if (HX == 2) {
-        if (VX == 2 && fancy_v) { // h2v2 triangle (jdsample.c h2v2_fancy_upsample)
-            int s[6];
-#pragma unroll
-            for (int k = 0; k < 6; ++k)
-                s[k] = 3 * cur[k] + nbr[k];
-#pragma unroll
-            for (int m = 0; m < 4; ++m) {
-                const int t = 3 * s[m + 1] + 8;
-                out[2 * m] = (t + s[m]) >> 4;
-                out[2 * m + 1] = (t + s[m + 2] - 1) >> 4;
-            }
-        } else if (VX == 1 && fancy_h) { // h2v1 triangle
-#pragma unroll
-            for (int m = 0; m < 4; ++m) {
-                out[2 * m] = (3 * cur[m + 1] + cur[m] + 1) >> 2;
-                out[2 * m + 1] = (3 * cur[m + 1] + cur[m + 2] + 2) >> 2;
-            }
-        } else { // box
-#pragma unroll
-            for (int m = 0; m < 4; ++m)
-                out[2 * m] = out[2 * m + 1] = cur[m + 1];
-        }
-    } else {
-        if (VX == 2 && fancy_v) { // h1v2 triangle
-#pragma unroll
-            for (int m = 0; m < 8; ++m)
-                out[m] = (3 * cur[m] + nbr[m] + (r ? 2 : 1)) >> 2;
-        } else {
-#pragma unroll
-            for (int m = 0; m < 8; ++m)
-                out[m] = cur[m];
-        }
-    }
-}
-
 // Stores 4 * NW contiguous bytes (little-endian words w[0..NW)) at ANY byte address.  Tightly pitched rows of
 // odd widths put most rows of an image off the 8-byte grid: aligned words go out as words (funnel-shifted by
 // the misalignment, which is the same for every lane of the warp), only the 4 bytes of head and tail singly.
@@ -1861,125 +1755,6 @@ __device__ __forceinline__ void store_words_any(uint8_t* o, const uint32_t* w)
             tail[j] = uint8_t(w[NW - 1] >> (sh + 8 * j));
 }
 
-// One unit = 8 pixels x VX rows at image position (X0, Y0), X0 % 8 == 0, Y0 % VX == 0.
-// kLumaOnly: grayscale stream or Y output.
-// kFancy: the triangle filter applies (decided on the host: fancy_upsampling option, the expansion
-// factors and libjpeg's downsampled_width > 2 condition).
-template <int HX, int VX, bool kFancy, bool kLumaOnly, int kOrder>
-__device__ __forceinline__ void color_unit(const BatchDev& bd, const ImageDev& im, int X0, int Y0)
-{
-    const uint8_t* p0 = bd.planes + im.plane_off[0];
-    const int stride0 = int(im.plane_stride_px[0]);
-    int cb[VX][8], cr[VX][8];
-    if (!kLumaOnly) {
-        const int stride_c = int(im.plane_stride_px[1]);
-        const int dw = int(im.comp_w[1]), dh = int(im.comp_h[1]); // real (not MCU-padded) chroma size: edges replicate there
-        constexpr bool fancy_v = kFancy && VX == 2;
-        const int j0 = X0 / HX;
-        const int ci = Y0 / VX;
-        constexpr int NC = (HX == 2) ? 6 : 8;
-#pragma unroll
-        for (int comp = 1; comp <= 2; ++comp) {
-            const uint8_t* pc = bd.planes + im.plane_off[comp];
-            int cur[NC], up[NC] = {}, dn[NC] = {};
-            load_chroma_row<HX>(pc + size_t(ci) * stride_c, j0, dw, cur);
-            if (VX == 2 && fancy_v) {
-                load_chroma_row<HX>(pc + size_t(ci > 0 ? ci - 1 : 0) * stride_c, j0, dw, up);
-                load_chroma_row<HX>(pc + size_t(ci + 1 < dh ? ci + 1 : dh - 1) * stride_c, j0, dw, dn);
-            }
-#pragma unroll
-            for (int r = 0; r < VX; ++r) {
-                int nb[NC], res[8];
-#pragma unroll
-                for (int k = 0; k < NC; ++k)
-                    nb[k] = (VX == 2 && fancy_v) ? (r == 0 ? up[k] : dn[k]) : cur[k];
-                upsample8<HX, VX, kFancy>(cur, nb, r, res);
-#pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    if (comp == 1)
-                        cb[r][k] = res[k];
-                    else
-                        cr[r][k] = res[k];
-                }
-            }
-        }
-    }
-    constexpr bool swap = (kOrder == 1); // BGR orders; kOrder == 2: Y, Cb, Cr written as they are
-    const bool full_x = X0 >= int(im.roi_x0) && X0 + 8 <= int(im.roi_x1);
-#pragma unroll
-    for (int r = 0; r < VX; ++r) {
-        const int y = Y0 + r;
-        if (y < int(im.roi_y0) || y >= int(im.roi_y1))
-            continue;
-        uint32_t yy[8]; // luma << 16; every channel value below sits in byte 2 of its word
-        unpack8_b2(__ldg(reinterpret_cast<const uint2*>(p0 + size_t(y) * stride0 + X0)), yy);
-        uint32_t c0[8], c1[8], c2[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            if (kLumaOnly) {
-                c0[i] = c1[i] = c2[i] = yy[i];
-            } else {
-                uint32_t rr, gg, bb;
-                if (kOrder == 2) {
-                    rr = yy[i];
-                    gg = uint32_t(cb[r][i]) << 16;
-                    bb = uint32_t(cr[r][i]) << 16;
-                } else {
-                    ycc_to_rgb16(int(yy[i]), cb[r][i], cr[r][i], rr, gg, bb);
-                }
-                c0[i] = swap ? bb : rr;
-                c1[i] = gg;
-                c2[i] = swap ? rr : bb;
-            }
-        }
-        const int oy = y - im.roi_y0, ox = X0 - int(im.roi_x0);
-        if (im.orient > 1) { // flipped / rotated output: the values are the same, only the addresses differ
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-                if (X0 + i >= int(im.roi_x0) && X0 + i < int(im.roi_x1))
-                    store_pixel_oriented(im, ox + i, oy, c0[i] >> 16, c1[i] >> 16, c2[i] >> 16);
-            continue;
-        }
-        if (im.fmt == kFmtY || im.fmt == kFmtPRGB || im.fmt == kFmtPBGR || im.fmt == kFmtPYUV) {
-            const int nch = (im.fmt == kFmtY) ? 1 : 3;
-#pragma unroll
-            for (int ch = 0; ch < 3; ++ch) {
-                if (ch >= nch)
-                    break;
-                const uint32_t* v = ch == 0 ? c0 : (ch == 1 ? c1 : c2);
-                uint8_t* o = im.out + size_t(ch) * im.plane_stride + size_t(oy) * im.row_stride + ox;
-                if (full_x) {
-                    const uint32_t pk[2] = {pack_b2(v[0], v[1], v[2], v[3]), pack_b2(v[4], v[5], v[6], v[7])};
-                    store_words_any<2>(o, pk);
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        if (X0 + i >= int(im.roi_x0) && X0 + i < int(im.roi_x1))
-                            o[i] = uint8_t(v[i] >> 16);
-                }
-            }
-        } else {
-            uint8_t* o = im.out + size_t(oy) * im.row_stride + ptrdiff_t(ox) * 3;
-            if (full_x) {
-                const uint32_t pk[6] = {pack_b2(c0[0], c1[0], c2[0], c0[1]), pack_b2(c1[1], c2[1], c0[2], c1[2]),
-                    pack_b2(c2[2], c0[3], c1[3], c2[3]), pack_b2(c0[4], c1[4], c2[4], c0[5]), pack_b2(c1[5], c2[5], c0[6], c1[6]),
-                    pack_b2(c2[6], c0[7], c1[7], c2[7])};
-                store_words_any<6>(o, pk);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    if (X0 + i >= int(im.roi_x0) && X0 + i < int(im.roi_x1)) {
-                        o[3 * i + 0] = uint8_t(c0[i] >> 16);
-                        o[3 * i + 1] = uint8_t(c1[i] >> 16);
-                        o[3 * i + 2] = uint8_t(c2[i] >> 16);
-                    }
-            }
-        }
-    }
-}
-
-// K4b.  CTA = 32 x 8 threads; a thread owns one unit of 8 pixels x unit_rows rows, aligned in image
-// coordinates so that every plane load is a naturally aligned 4- or 8-byte word.
 // Streams whose components came in three scans: the image proper has no entropy data, its planes were decoded as
 // one-component images of their own (BatchDev::gate).  Their state flags become the image's before K4b looks at them.
 __global__ void gate_flags_kernel(BatchDev bd)
