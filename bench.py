@@ -215,6 +215,39 @@ def nvjpeg_hw_backend_status():
 
 
 
+def pinned_near_gpu(nbytes, device):
+    """A pinned host buffer for the decoded pixels on the memory node the GPU reads and writes fastest.  On these (virtualised,
+    two-node) boxes the node a pinned allocation lands on is a matter of which CPU the allocating thread happens to run on, and
+    the far node halves the D2H rate (measured: 48-70 ms instead of 33 ms per 1.59 GB step).  So: allocate under each candidate
+    CPU set, time a D2H copy, keep the fastest.  Returns (tensor, {"gbs": [...], "chosen": i})."""
+    import torch
+
+    cpus = sorted(os.sched_getaffinity(0))
+    half = len(cpus) // 2
+    candidates = [set(cpus)] if half < 2 else [set(cpus[:half]), set(cpus[half:])]
+    probe_bytes = min(nbytes, 256 << 20)
+    src = torch.empty(probe_bytes, dtype=torch.uint8, device=device)
+    best, rates = None, []
+    try:
+        for cs in candidates:
+            os.sched_setaffinity(0, cs)
+            t = torch.empty(max(nbytes, 1), dtype=torch.uint8, pin_memory=True)
+            t[:probe_bytes].copy_(src, non_blocking=True)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(3):
+                t[:probe_bytes].copy_(src, non_blocking=True)
+            torch.cuda.synchronize()
+            gbs = 3 * probe_bytes / (time.perf_counter() - t0) / 1e9
+            rates.append(round(gbs, 1))
+            if best is None or gbs > best[0]:
+                best = (gbs, t)
+            del t
+    finally:
+        os.sched_setaffinity(0, set(cpus))
+    return best[1], {"d2h_gbs_per_candidate_node": rates, "chosen": rates.index(max(rates))}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
 
@@ -439,7 +472,9 @@ def main():
             n_ok += 1
         return n_ok
 
-    host_batch = dec.make_batch(srcs, fmts, rois, to_host=True)
+    probe_batch = dec.make_batch(srcs, fmts, rois, to_host=True, out_storage=torch.empty(0, dtype=torch.uint8), size_only=True)
+    host_storage, host_placement = pinned_near_gpu(probe_batch, torch.device("cuda", local))
+    host_batch = dec.make_batch(srcs, fmts, rois, to_host=True, out_storage=host_storage)
     for _ in range(args.warmup):
         dec.run(host_batch)
     barrier()
@@ -575,7 +610,8 @@ def main():
                    "sample": f"{len(sample)} of the batch's images x 2 passes on {cores} threads; {how}"}
         e2e_capi = {"value": job_mpix * args.steps / (ms_e2e * 1e-3), "unit": "MPix/s", "images_per_s": job_imgs * args.steps / (ms_e2e * 1e-3),
                     "h2d_bytes_per_step": host_batch.h2d_bytes, "d2h_bytes_per_step": host_batch.d2h_bytes,
-                    "call": "Decoder.run(batch) == b200jpegDecodeBatch, pinned host bitstreams in, pinned host pixels out"}
+                    "call": "Decoder.run(batch) == b200jpegDecodeBatch, pinned host bitstreams in, pinned host pixels out",
+                    "pinned_buffer_placement": host_placement}
         e2e_capi_dev = {"value": job_mpix * args.steps / (ms_e2e_dev * 1e-3), "unit": "MPix/s",
                         "h2d_bytes_per_step": dev_batch.h2d_bytes, "d2h_bytes_per_step": 16 * n_img,
                         "note": "same call, pixels left in HBM (what a GPU consumer of nvImageCodec sees); statuses read back"}

@@ -91,13 +91,19 @@ __device__ __forceinline__ void sym_fetch_block(const SymSource& S, uint32_t rec
         asm volatile("st.shared.u32 [%0], %1;" ::"r"(scat + uint32_t(j) * stride), "r"(0u) : "memory");
     uint32_t k = pos >> S.shift, slot = (rec & 0xFFFFu) + 1u; // the entry behind the DC symbol's
     uint32_t z = 1;
-    bool done = k >= S.n_sub;
+    bool done = k >= S.n_sub || (slot >> 3) >= S.chunks;
+    auto chunk_at = [&](uint32_t kk, uint32_t c) { return __ldg(S.sym + (size_t(kk >> 5) * S.chunks + c) * 32 + (kk & 31u)); };
+    uint4 ch = make_uint4(0u, 0u, 0u, 0u);
+    if (!done)
+        ch = chunk_at(k, slot >> 3);
 #pragma unroll 1
     for (int guard = 0; !done && guard < 160; ++guard) {
         const uint32_t c = slot >> 3;
-        if (c >= S.chunks)
-            break;
-        const uint4 ch = __ldg(S.sym + (size_t(k >> 5) * S.chunks + c) * 32 + (k & 31u));
+        // the next chunk of the column is requested before this one is worked through (most blocks span two or three)
+        uint4 nx = make_uint4(0u, 0u, 0u, 0u);
+        const bool have_next = c + 1u < S.chunks;
+        if (have_next)
+            nx = chunk_at(k, c + 1u);
         const uint32_t cw[4] = {ch.x, ch.y, ch.z, ch.w};
         bool hop = false;
 #pragma unroll
@@ -129,8 +135,12 @@ __device__ __forceinline__ void sym_fetch_block(const SymSource& S, uint32_t rec
             ++k;
             slot = 0;
             done = k >= S.n_sub;
+            if (!done)
+                ch = chunk_at(k, 0u);
         } else {
             slot = (c + 1u) * 8u;
+            ch = nx;
+            done = done || !have_next;
         }
     }
 #pragma unroll

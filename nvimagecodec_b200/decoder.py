@@ -71,7 +71,7 @@ class Decoder:
             pass
 
     # ------------------------------------------------------------------ batch construction
-    def make_batch(self, srcs, fmt="I_RGB", rois=None, to_host=False, out_storage=None, row_align=1, orientations=None):
+    def make_batch(self, srcs, fmt="I_RGB", rois=None, to_host=False, out_storage=None, row_align=1, orientations=None, size_only=False):
         """srcs: list of bytes / uint8 arrays.  fmt: one name or a list of names per image.
         rois: None or list of None | (y0, x0, y1, x1) (nvimgcodecRegion_t order).
         to_host: write into pinned host tensors (decoder bounces through HBM + D2H)."""
@@ -111,6 +111,8 @@ class Decoder:
             nbytes = stride * hgt * (3 if f.startswith("P_") and f != "P_Y" else 1)
             shapes.append((shape, stride, total, nbytes, f))
             total += (max(nbytes, 1) + 255) // 256 * 256
+        if size_only:  # how many bytes of output storage the batch needs
+            return total
         if out_storage is None:
             if to_host:
                 out_storage = torch.empty(max(total, 1), dtype=torch.uint8, pin_memory=True)

@@ -15,8 +15,11 @@
 //                                instead of dumping the raw pixels (large batches)
 //     HOST_DRIVER_COUNT_ALLOC=1  hand the decoder counting device / pinned allocators through nvimgcodecExecutionParams_t
 //                                (include/nvimgcodec.h:1095-1096) and print how often each was called
-//     HOST_DRIVER_PINNED=1       host output buffers are pinned (cudaMallocHost) instead of malloc'ed
+//     HOST_DRIVER_PINNED=1       host output buffers are pinned (cudaMallocHost) instead of malloc'ed, allocated on the memory node
+//                                with the faster device-to-host copies (probed: on a two-node box the far node halves the rate)
 //     HOST_DRIVER_FILL=<0..255>  constant sample for the parts of a region that lie outside the image (include/nvimgcodec.h:495-519)
+#include <sched.h>
+
 #include <cuda_runtime_api.h>
 #include <nvimgcodec.h>
 
@@ -162,6 +165,45 @@ int main(int argc, char** argv)
 
     cudaStream_t stream;
     cudaStreamCreate(&stream);
+    // pinned outputs: choose the CPU set (memory node) under which a pinned buffer copies fastest from the device
+    cpu_set_t all_cpus, best_cpus;
+    CPU_ZERO(&all_cpus);
+    sched_getaffinity(0, sizeof(all_cpus), &all_cpus);
+    best_cpus = all_cpus;
+    if (pinned_out) {
+        std::vector<int> cpus;
+        for (int c = 0; c < CPU_SETSIZE; ++c)
+            if (CPU_ISSET(c, &all_cpus))
+                cpus.push_back(c);
+        if (cpus.size() >= 4) {
+            const size_t probe = size_t(256) << 20;
+            void* dsrc = nullptr;
+            cudaMalloc(&dsrc, probe);
+            double best = 0;
+            for (int half = 0; half < 2; ++half) {
+                cpu_set_t cs;
+                CPU_ZERO(&cs);
+                for (size_t i = half ? cpus.size() / 2 : 0; i < (half ? cpus.size() : cpus.size() / 2); ++i)
+                    CPU_SET(cpus[i], &cs);
+                sched_setaffinity(0, sizeof(cs), &cs);
+                void* h = nullptr;
+                cudaMallocHost(&h, probe);
+                cudaMemcpy(h, dsrc, probe, cudaMemcpyDeviceToHost);
+                const auto t0 = std::chrono::steady_clock::now();
+                for (int r = 0; r < 3; ++r)
+                    cudaMemcpy(h, dsrc, probe, cudaMemcpyDeviceToHost);
+                const double gbs = 3.0 * probe / std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() / 1e9;
+                std::printf("PLACEMENT cpu half %d: D2H %.1f GB/s\n", half, gbs);
+                if (gbs > best) {
+                    best = gbs;
+                    best_cpus = cs;
+                }
+                cudaFreeHost(h);
+            }
+            cudaFree(dsrc);
+        }
+        sched_setaffinity(0, sizeof(best_cpus), &best_cpus); // ... for the allocations below; the full set comes back after them
+    }
     std::vector<nvimgcodecCodeStream_t> parents(n, nullptr), streams(n, nullptr);
     std::vector<nvimgcodecImage_t> images(n, nullptr);
     for (int i = 0; i < n; ++i) {
@@ -234,6 +276,7 @@ int main(int argc, char** argv)
         CHECK(nvimgcodecImageCreate(instance, &images[i], &info));
     }
 
+    sched_setaffinity(0, sizeof(all_cpus), &all_cpus);
     nvimgcodecDecodeParams_t dp{NVIMGCODEC_STRUCTURE_TYPE_DECODE_PARAMS, sizeof(nvimgcodecDecodeParams_t), nullptr};
     dp.apply_exif_orientation = apply_exif ? 1 : 0;
     nvimgcodecFuture_t future = nullptr;
