@@ -541,8 +541,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 host_status_[i] = B200JPEG_ERR_CORRUPT;
                 continue;
             }
-            // coefficients (dense groups, or the entry stream: 18 bytes reserved per byte of scan) + planes, upper bound
-            const uint64_t arena = (bd_.sym_mode ? uint64_t(hd.scan_length) * 20 : blocks * 128) + blocks * 64;
+            // coefficients (dense groups, or the entry stream: 36 bytes reserved per byte of scan) + planes, upper bound
+            const uint64_t arena = (bd_.sym_mode ? uint64_t(hd.scan_length) * 40 : blocks * 128) + blocks * 64;
             if (arena > (uint64_t(opt_.max_arena_mb) << 20) || coef_elems / 64 + blocks >= (uint64_t(1) << 28)) {
                 host_status_[i] = B200JPEG_ERR_TOO_LARGE;
                 continue;
@@ -1325,7 +1325,7 @@ int Decoder::copy_coefficients(int index, int16_t* host_out, size_t cap_elems)
         const int d = dev_index_[index];
         cudaDeviceSynchronize();
         const size_t chunks = size_t((im.n_sub_max + 31) / 32) * bd_.sym_chunks * 32;
-        std::vector<uint16_t> sym(chunks * 8);
+        std::vector<uint32_t> sym(chunks * 4);
         std::vector<uint32_t> recs(im.total_blocks), pos(im.total_blocks);
         ImageState st{};
         if (!cuda_ok(cudaMemcpy(sym.data(), bd_.sym + im.sym_off, chunks * 16, cudaMemcpyDeviceToHost), "entry copy") ||
@@ -1336,34 +1336,25 @@ int Decoder::copy_coefficients(int index, int16_t* host_out, size_t cap_elems)
         std::memset(host_out, 0, elems * sizeof(int16_t));
         for (size_t b = 0; b < recs.size(); ++b) {
             int16_t* blk = host_out + b * 64;
-            blk[0] = int16_t(recs[b] >> 16);
-            uint32_t k = pos[b] >> bd_.sub_shift, slot = (recs[b] & 0xFFFFu) + 1u, z = 1;
+            uint32_t k = pos[b] >> bd_.sub_shift, slot = (recs[b] & 0xFFFFu) + 1u;
             bool done = k >= st.n_sub;
-            for (int guard = 0; !done && guard < 4096; ++guard) {
-                if (slot >= bd_.sym_chunks * 8)
+            for (int guard = 0; !done && guard < 8192; ++guard) {
+                if (slot >= bd_.sym_chunks * 4)
                     break;
-                const size_t chunk = (size_t(k >> 5) * bd_.sym_chunks + (slot >> 3)) * 32 + (k & 31u);
-                const uint32_t e = sym[chunk * 8 + (slot & 7u)];
-                const int32_t val = int32_t(e << 20) >> 20;
-                const uint32_t run = e >> 12;
+                const size_t chunk = (size_t(k >> 5) * bd_.sym_chunks + (slot >> 2)) * 32 + (k & 31u);
+                const uint32_t e = sym[chunk * 4 + (slot & 3u)];
                 ++slot;
-                if (val != 0) {
-                    z += run;
-                    if (z > 63)
-                        break;
-                    blk[z++] = int16_t(val);
-                    done = z > 63;
-                } else if (run == 0) {
+                const uint32_t off = (e >> 16) & 0x3FFFu; // byte offset in the scatter column -> zig-zag position
+                blk[((off / kScatterStride) << 1) | ((off >> 1) & 1u)] = int16_t(e & 0xFFFFu);
+                if (e & 0x40000000u) {
                     done = true;
-                } else if (run == 15) {
-                    z += 16;
-                    done = z > 63;
-                } else if (run == 2) {
+                } else if (e & 0x80000000u) {
                     ++k;
                     slot = 0;
                     done = k >= st.n_sub;
                 }
             }
+            blk[0] = int16_t(recs[b] >> 16);
         }
         return B200JPEG_OK;
     }

@@ -1012,12 +1012,17 @@ __global__ void __launch_bounds__(kSeqThreads, 5) huff_write_kernel(BatchDev bd,
 }
 
 // K3, entry-stream form.  Every thread decodes exactly the code words that start in its subsequence (as K1 does: no block
-// ownership, nothing is decoded twice) and writes one 16-bit entry per loop iteration, whatever the iteration met; the
-// eight entries of a chunk sit at fixed places of four registers (the chunk loop is unrolled), and the lanes of a warp
-// store their chunks side by side -- 512 contiguous bytes per warp and chunk row.  Nothing depends on the symbol but the
-// entry's value: no group stores, no per-block flush, the end of a block is a predicated table switch as in K1.  The one
-// scattered store left is the block record at a DC symbol (entry slot + DC difference, and the bit position in blkpos).
-constexpr uint32_t kEntEob = 0x0000u, kEntNop = 0x1000u, kEntEnd = 0x2000u, kEntZrl = 0xF000u;
+// ownership, nothing is decoded twice) and writes one 32-bit entry per loop iteration, whatever the iteration met; the
+// four entries of a chunk are four registers (the chunk loop is unrolled), and the lanes of a warp store their chunks side
+// by side -- 512 contiguous bytes per warp and chunk row.  Nothing depends on the symbol but the entry's value: no group
+// stores, no per-block flush, the end of a block is a predicated table switch as in K1.  The one scattered store left is
+// the block record at a DC symbol (entry slot + DC difference, and the bit position in blkpos).
+// An entry is made for its consumer (sym_fetch_block): value in the low half; in the high half the byte offset at which
+// the IDCT kernel's scatter column holds that zig-zag position, plus two flags.  An iteration that carries no coefficient
+// (DC symbol, sixteen zeros, restart hop) leaves 0, which the consumer may store like any other entry: offset 0 is the
+// unused DC position.
+constexpr uint32_t kEntNop = 0u, kEntLast = 0x40000000u /* the block ends with this entry */, kEntEnd = 0x80000000u /* the subsequence's entries end */;
+__device__ __forceinline__ uint32_t ent_offset(uint32_t pos) { return ((pos >> 1) * kScatterStride) | ((pos & 1u) << 1); }
 
 __device__ __forceinline__ uint32_t emit_subsequence(const StreamView& sv, const HuffSetDev* __restrict__ hs, const BlockTable* __restrict__ bt,
     uint32_t base_bit, uint32_t end_bit, uint32_t in_state, int32_t blk, uint32_t* __restrict__ blkrec, uint32_t* __restrict__ blkpos,
@@ -1025,7 +1030,7 @@ __device__ __forceinline__ uint32_t emit_subsequence(const StreamView& sv, const
 {
     uint32_t err = 0;
     if (in_state & kStateDone) { // past the end of the stream: an empty entry list
-        out[0] = make_uint4(kEntEnd | (kEntNop << 16), kEntNop * 0x10001u, kEntNop * 0x10001u, kEntNop * 0x10001u);
+        out[0] = make_uint4(kEntEnd, kEntNop, kEntNop, kEntNop);
         return 0;
     }
     uint32_t p = base_bit + (in_state & 63u);
@@ -1053,9 +1058,9 @@ __device__ __forceinline__ uint32_t emit_subsequence(const StreamView& sv, const
     bool running = true;
 #pragma unroll 1
     for (uint32_t c = 0;; ++c) {
-        uint32_t q[4] = {kEntNop * 0x10001u, kEntNop * 0x10001u, kEntNop * 0x10001u, kEntNop * 0x10001u};
+        uint32_t q[4] = {kEntNop, kEntNop, kEntNop, kEntNop};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < 4; ++j) {
             if (!running)
                 continue;
             uint32_t ent = kEntNop;
@@ -1128,19 +1133,19 @@ __device__ __forceinline__ uint32_t emit_subsequence(const StreamView& sv, const
                 const uint32_t rest = win << (tot - size);
                 const uint32_t mag = __funnelshift_l(rest, 0u, size);
                 const int32_t val = (rest >> 31) ? int32_t(mag) : int32_t(mag) - int32_t((1u << size) - 1u);
+                z += skip;
                 if (is_dc) {
-                    // block record: where the block's entries start (this slot, which itself stays a no-op) and its DC difference
+                    // block record: where the block's entries start (this slot, which itself carries nothing) and its DC difference
                     if (uint32_t(blk) - sv.dc_lo < sv.dc_span && (bi.w & (1u << 24))) {
-                        blkrec[blk] = (c * 8u + uint32_t(j)) | (uint32_t(val) << 16);
+                        blkrec[blk] = (c * 4u + uint32_t(j)) | (uint32_t(val) << 16);
                         blkpos[blk] = p_sym - sv.bit_base;
                     }
-                } else if (size != 0u) {
-                    err |= (z + skip - 1u > 63u) ? uint32_t(kFlagBadHuffman) : 0u;
-                    ent = ((skip - 1u) << 12) | (uint32_t(val) & 0xFFFu);
                 } else {
-                    ent = (skip == 16u) ? kEntZrl : kEntEob;
+                    const uint32_t pos = z - 1u; // zig-zag position of the coefficient a run/size symbol carries
+                    err |= (size != 0u && pos > 63u) ? uint32_t(kFlagBadHuffman) : 0u;
+                    ent = (size != 0u) ? ((ent_offset(pos & 63u) << 16) | (uint32_t(val) & 0xFFFFu)) : kEntNop;
+                    ent |= (z > 63u) ? kEntLast : 0u; // an end-of-block symbol, or the coefficient at position 63
                 }
-                z += skip;
                 asm("{\n\t.reg .pred q;\n\t"
                     "setp.gt.u32 q, %4, 63;\n\t"
                     "@q ld.shared.v4.u32 {%0,%1,%2,%3}, [%2];\n\t}"
@@ -1151,10 +1156,7 @@ __device__ __forceinline__ uint32_t emit_subsequence(const StreamView& sv, const
                 taddr = (z == 0u) ? bi.x : bi.y;
                 win = br.window(p);
             }
-            if (j & 1)
-                q[j >> 1] = (q[j >> 1] & 0xFFFFu) | (ent << 16);
-            else
-                q[j >> 1] = (q[j >> 1] & 0xFFFF0000u) | ent;
+            q[j] = ent;
         }
         if (c < max_chunks) {
             out[size_t(c) * 32] = make_uint4(q[0], q[1], q[2], q[3]);
@@ -1491,7 +1493,8 @@ __global__ void __launch_bounds__(128, 6) idct_kernel(BatchDev bd, int redo_only
             S.chunks = bd.sym_chunks;
             S.shift = bd.sub_shift;
             S.n_sub = bd.state[img].n_sub;
-            sym_fetch_block(S, rec, __ldg(bd.blkpos + blk), smem_addr(s_scatter) + threadIdx.x * 4u, 128u * 4u, w);
+            static_assert(kScatterStride == 128u * 4u, "the entries carry offsets into this column layout");
+            sym_fetch_block(S, rec, __ldg(bd.blkpos + blk), smem_addr(s_scatter) + threadIdx.x * 4u, w);
         } else {
             px_fetch_block<2>(bd.coef, rec, blk, w);
         }
@@ -1930,7 +1933,7 @@ size_t pixels_tile_smem(int ncomp, const int* h, const int* v, int vmax, int str
 
 // A loop iteration of K3 consumes at least one bit (the shortest code) or hops over a restart boundary (at most one per byte);
 // one more entry ends the list.
-uint32_t sym_chunks_for(uint32_t sub_bits) { return (sub_bits + sub_bits / 8 + 16 + 7) / 8; }
+uint32_t sym_chunks_for(uint32_t sub_bits) { return (sub_bits + sub_bits / 8 + 16 + 3) / 4; } // four entries to a chunk
 
 size_t pixels_smem_budget() { return (size_t(227 - 5 * kPxCtasPerSm) * 1024 / (kPxCtasPerSm * kPxWarps)) / 256 * 256; } // 8704 bytes per warp at 3 x 8 warps
 int pixels_strip_mcus(int bpm_held, int halo_blocks) { return std::max(1, (96 - halo_blocks) / std::max(1, bpm_held)); }

@@ -28,6 +28,7 @@ constexpr int kIdctPer = B200_IDCT_PER;        // K4a: blocks per thread (table 
 #define B200_COLOR_UNITS_Y 4
 #endif
 constexpr int kColorUnitsY = B200_COLOR_UNITS_Y;       // K4b: vertically adjacent units per thread (descriptor reads, index arithmetic and the mode switch amortised)
+constexpr uint32_t kScatterStride = 512; // bytes between consecutive words of a thread's scatter column in the IDCT kernel (128 threads x 4)
 constexpr int kDcThreads = 512;       // K3b: threads per CTA, ...
 constexpr int kDcPer = 8;             //      blocks per thread,
 constexpr int kDcChunk = kDcThreads * kDcPer; // blocks per CTA
@@ -125,11 +126,12 @@ struct BatchDev {
     uint32_t* sub_start;    // exclusive scan: absolute block index at entry
     const HuffSetDev* huff;
     int16_t* coef;
-    // Entry-stream form of the coefficients (K3 huff_emit / the walkers of K4): every subsequence thread of K3 writes one
-    // 16-bit entry per decoded symbol -- run << 12 | value (12 bits, signed) for a coefficient, 0x0000 end of block,
-    // 0xF000 sixteen zeros, 0x1000 nothing (DC symbols, restart hops), 0x2000 end of the subsequence's entries -- in chunks
-    // of eight (16 bytes).  The chunks of the 32 subsequences of a warp interleave, so that a warp's store of a chunk row
-    // is 512 contiguous bytes: chunk c of subsequence k of an image lies at sym[sym_off + ((k >> 5) * sym_chunks + c) * 32 + (k & 31)].
+    // Entry-stream form of the coefficients (K3 huff_emit / the walker of the IDCT kernel): every subsequence thread of K3 writes
+    // one 32-bit entry per decoded symbol -- low half: the coefficient; high half: the byte offset of its zig-zag position in
+    // the IDCT kernel's scatter column (kScatterStride), bit 14: the block ends with this entry, bit 15: the subsequence's
+    // entries end here; 0 for symbols that carry no coefficient -- in chunks of four (16 bytes).  The chunks of the 32
+    // subsequences of a warp interleave, so that a warp's store of a chunk row is 512 contiguous bytes: chunk c of
+    // subsequence k of an image lies at sym[sym_off + ((k >> 5) * sym_chunks + c) * 32 + (k & 31)].
     // blkpos[block] = bit position of the block's DC code word (-> the subsequence that holds it), the low half of
     // blkrec[block] = the entry slot of that DC symbol inside the subsequence.
     uint4* sym;

@@ -84,22 +84,21 @@ struct SymSource {
     uint32_t n_sub;        // subsequences of the image
 };
 
-__device__ __forceinline__ void sym_fetch_block(const SymSource& S, uint32_t rec, uint32_t pos, uint32_t scat, uint32_t stride, uint32_t (&w)[32])
+__device__ __forceinline__ void sym_fetch_block(const SymSource& S, uint32_t rec, uint32_t pos, uint32_t scat, uint32_t (&w)[32])
 {
 #pragma unroll
     for (int j = 0; j < 32; ++j)
-        asm volatile("st.shared.u32 [%0], %1;" ::"r"(scat + uint32_t(j) * stride), "r"(0u) : "memory");
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(scat + uint32_t(j) * kScatterStride), "r"(0u) : "memory");
     uint32_t k = pos >> S.shift, slot = (rec & 0xFFFFu) + 1u; // the entry behind the DC symbol's
-    uint32_t z = 1;
-    bool done = k >= S.n_sub || (slot >> 3) >= S.chunks;
+    bool done = k >= S.n_sub || (slot >> 2) >= S.chunks;
     auto chunk_at = [&](uint32_t kk, uint32_t c) { return __ldg(S.sym + (size_t(kk >> 5) * S.chunks + c) * 32 + (kk & 31u)); };
     uint4 ch = make_uint4(0u, 0u, 0u, 0u);
     if (!done)
-        ch = chunk_at(k, slot >> 3);
+        ch = chunk_at(k, slot >> 2);
 #pragma unroll 1
-    for (int guard = 0; !done && guard < 160; ++guard) {
-        const uint32_t c = slot >> 3;
-        // the next chunk of the column is requested before this one is worked through (most blocks span two or three)
+    for (int guard = 0; !done && guard < 320; ++guard) {
+        const uint32_t c = slot >> 2;
+        // the next chunk of the column is requested before this one is worked through (most blocks span several)
         uint4 nx = make_uint4(0u, 0u, 0u, 0u);
         const bool have_next = c + 1u < S.chunks;
         if (have_next)
@@ -107,29 +106,14 @@ __device__ __forceinline__ void sym_fetch_block(const SymSource& S, uint32_t rec
         const uint32_t cw[4] = {ch.x, ch.y, ch.z, ch.w};
         bool hop = false;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            if (done || hop || uint32_t(j) < (slot & 7u))
+        for (int j = 0; j < 4; ++j) {
+            if (done || hop || uint32_t(j) < (slot & 3u))
                 continue;
-            const uint32_t e = (j & 1) ? (cw[j >> 1] >> 16) : (cw[j >> 1] & 0xFFFFu);
-            const int32_t val = int32_t(e << 20) >> 20;
-            const uint32_t run = e >> 12;
-            if (val != 0) {
-                z += run;
-                if (z > 63u) {
-                    done = true;
-                } else {
-                    asm volatile("st.shared.u16 [%0], %1;" ::"r"(scat + (z >> 1) * stride + (z & 1u) * 2u), "h"(uint16_t(val)) : "memory");
-                    ++z;
-                    done = z > 63u;
-                }
-            } else if (run == 0u) { // end of block
-                done = true;
-            } else if (run == 15u) { // sixteen zeros
-                z += 16u;
-                done = z > 63u;
-            } else if (run == 2u) { // the subsequence's entries end here: the block continues in the next one
-                hop = true;
-            }
+            // every entry may be stored as it is: those without a coefficient put a zero at the unused DC position
+            const uint32_t e = cw[j];
+            asm volatile("st.shared.u16 [%0], %1;" ::"r"(scat + ((e >> 16) & 0x3FFFu)), "h"(uint16_t(e)) : "memory");
+            done = (e & 0x40000000u) != 0u; // the block ends with this entry
+            hop = (e & 0x80000000u) != 0u;  // the subsequence's entries end: the block continues in the next one
         }
         if (hop) {
             ++k;
@@ -138,14 +122,14 @@ __device__ __forceinline__ void sym_fetch_block(const SymSource& S, uint32_t rec
             if (!done)
                 ch = chunk_at(k, 0u);
         } else {
-            slot = (c + 1u) * 8u;
+            slot = (c + 1u) * 4u;
             ch = nx;
             done = done || !have_next;
         }
     }
 #pragma unroll
     for (int j = 0; j < 32; ++j)
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[j]) : "r"(scat + uint32_t(j) * stride) : "memory");
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[j]) : "r"(scat + uint32_t(j) * kScatterStride) : "memory");
 }
 
 // signed 16-bit halves of a times unsigned bytes of b: lo = a.lo * b.b0 + a.hi * b.b1, hi = a.lo * b.b2 + a.hi * b.b3
