@@ -1344,7 +1344,7 @@ int Decoder::copy_coefficients(int index, int16_t* host_out, size_t cap_elems)
                 const size_t chunk = (size_t(k >> 5) * bd_.sym_chunks + (slot >> 2)) * 32 + (k & 31u);
                 const uint32_t e = sym[chunk * 4 + (slot & 3u)];
                 ++slot;
-                const uint32_t off = (e >> 16) & 0x3FFFu; // byte offset in the scatter column -> zig-zag position
+                const uint32_t off = (e >> 16) & 0x3E02u; // byte offset in the scatter column -> zig-zag position
                 blk[((off / kScatterStride) << 1) | ((off >> 1) & 1u)] = int16_t(e & 0xFFFFu);
                 if (e & 0x40000000u) {
                     done = true;

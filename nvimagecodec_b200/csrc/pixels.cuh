@@ -111,7 +111,9 @@ __device__ __forceinline__ void sym_fetch_block(const SymSource& S, uint32_t rec
                 continue;
             // every entry may be stored as it is: those without a coefficient put a zero at the unused DC position
             const uint32_t e = cw[j];
-            asm volatile("st.shared.u16 [%0], %1;" ::"r"(scat + ((e >> 16) & 0x3FFFu)), "h"(uint16_t(e)) : "memory");
+            // (the mask keeps the word row and the half bit only: whatever a damaged stream left in an entry, the store stays
+            // aligned and inside this thread's column)
+            asm volatile("st.shared.u16 [%0], %1;" ::"r"(scat + ((e >> 16) & 0x3E02u)), "h"(uint16_t(e)) : "memory");
             done = (e & 0x40000000u) != 0u; // the block ends with this entry
             hop = (e & 0x80000000u) != 0u;  // the subsequence's entries end: the block continues in the next one
         }
