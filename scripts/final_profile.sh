@@ -10,10 +10,7 @@ for w in c3 c4 c5; do
 done
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${TAG}_bench_reference.json 2>/dev/null
 python tests/tools/latency.py > gpurun_out/${TAG}_latency.txt 2>&1
-# compute-sanitizer: every kernel on a small mixed batch (memcheck, then racecheck)
-compute-sanitizer --tool memcheck --error-exitcode 9 python tests/tools/sanitize_case.py > gpurun_out/${TAG}_sanitizer_memcheck.log 2>&1; echo "memcheck rc=$?" >> gpurun_out/${TAG}_sanitizer_memcheck.log
-compute-sanitizer --tool racecheck --error-exitcode 9 python tests/tools/sanitize_case.py > gpurun_out/${TAG}_sanitizer_racecheck.log 2>&1; echo "racecheck rc=$?" >> gpurun_out/${TAG}_sanitizer_racecheck.log
-tail -3 gpurun_out/${TAG}_sanitizer_memcheck.log gpurun_out/${TAG}_sanitizer_racecheck.log
+# (compute-sanitizer is closed on this GPU pool: no memcheck / racecheck log can be produced here; see profiles/README.md)
 # launch list (cold-cache, serialised: shares only) and one full-set capture of every kernel -- after the same command exited 0 above
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 --no-extras > gpurun_out/${TAG}_ncu_launches.log 2>&1
 TAG=${TAG}_prof COUNT=10 scripts/ncu_k.sh "."
