@@ -9,7 +9,7 @@ A "step" is one pass of the hot path over one batch.  `value` times the kernels 
 (bitstreams already resident in HBM, outputs left in HBM).  `e2e` is the same metric through the
 reference-facing plugin call -- nvimgcodecDecoderDecode of the UNMODIFIED nvImageCodec core
 (oracle/_ref/libnvimgcodec.so, built from the reference sources) with this repo's extension picked
-up by priority -- with HOST buffers: pageable bitstreams in, pinned host pixels out, H2D and D2H
+up by priority -- with HOST buffers: pinned bitstreams in, pinned host pixels out, H2D and D2H
 inside the timed region (tests/host/host_driver.cpp drives it; one driver process per rank).
 `e2e_capi` is the same through the plain C ABI (b200jpegDecodeBatch, pinned bitstreams in, pinned
 pixels out); the *_device_out variants leave the pixels in HBM (what a GPU consumer sees).
@@ -159,7 +159,7 @@ class PluginDriver:
     def available():
         return os.path.exists(DRIVER) and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libnvimgcodec.so"))
 
-    def run(self, where, options, repeat, ext_dir=EXT_DIR, backend="any", fmts=None, rois=None, crc_every=0, timeout=600):
+    def run(self, where, options, repeat, ext_dir=EXT_DIR, backend="any", fmts=None, rois=None, crc_every=0, timeout=600, pinned_in=True, threads=0):
         man = os.path.join(self.dir, f"manifest_{where}.txt")
         with open(man, "w") as f:
             for i, p in enumerate(self.paths):
@@ -171,6 +171,11 @@ class PluginDriver:
         env["LD_LIBRARY_PATH"] = os.path.dirname(DRIVER) + ":/usr/local/cuda/lib64:" + env.get("LD_LIBRARY_PATH", "")
         env["CUDA_VISIBLE_DEVICES"] = str(self.device_index)
         env["HOST_DRIVER_PINNED"] = "1"
+        env.pop("HOST_DRIVER_PINNED_INPUT", None)
+        if pinned_in:
+            env["HOST_DRIVER_PINNED_INPUT"] = "1"
+        if threads:
+            env["HOST_DRIVER_THREADS"] = str(threads)
         env["HOST_DRIVER_CRC"] = str(crc_every if crc_every else 1 << 30)
         for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
             env.pop(k, None)
@@ -508,10 +513,14 @@ def main():
         rep_host = max(3, min(args.steps, int(1.0 / max(t_e2e / args.steps, 1e-3)) + 1))
         rep_dev = max(5, min(10 * args.steps, int(1.0 / max(t_e2e_dev / args.steps, 1e-4)) + 1))
         barrier()
-        plugin["host"] = drv.run("host", opts, rep_host, fmts=fmts, rois=rois, crc_every=max(1, n_img // 8))
+        drv_threads = max(2, cores // world) if world > 1 else 0  # the ranks share the host cores
+        plugin["host"] = drv.run("host", opts, rep_host, fmts=fmts, rois=rois, crc_every=max(1, n_img // 8), threads=drv_threads)
         barrier()
-        plugin["device"] = drv.run("device", opts, rep_dev, fmts=fmts, rois=rois, crc_every=max(1, n_img // 8))
+        plugin["device"] = drv.run("device", opts, rep_dev, fmts=fmts, rois=rois, crc_every=max(1, n_img // 8), threads=drv_threads)
         barrier()
+        if world == 1 and not args.no_extras:  # the same two calls with the bitstreams in pageable memory (staged by the extension)
+            plugin["host_pageable"] = drv.run("host", opts, rep_host, fmts=fmts, rois=rois, pinned_in=False)
+            plugin["device_pageable"] = drv.run("device", opts, rep_dev, fmts=fmts, rois=rois, pinned_in=False)
         import zlib
 
         import numpy as np
@@ -590,7 +599,7 @@ def main():
                 traffic = {k.replace("_kernel", ""): v["dram_bytes"] for k, v in json.load(f)["kernels"].items()}
         except Exception:
             pass
-        ncu_name = {"scan(K0)": "scan_scatter", "huff_sync(K1)": "huff_sync", "verify_scan(K2)": "verify_scan", "huff_write(K3)": "huff_write", "dc_scan(K3b)": "dc_apply",
+        ncu_name = {"scan(K0)": "scan_scatter", "huff_sync(K1)": "huff_sync", "verify_scan(K2)": "verify_scan", "huff_write(K3)": "huff_emit" if "huff_emit" in traffic else "huff_write", "dc_scan(K3b)": "dc_apply",
                     "idct(K4a)": "idct", "color(K4b)": "color", "pixels(K4)": "pixels"}
         if top:
             ach = kbytes[top] / (stages[top] * 1e-3) / 1e9
@@ -619,12 +628,17 @@ def main():
             e2e = {"value": job_mpix / (ms_plug_host * 1e-3), "unit": "MPix/s", "images_per_s": job_imgs / (ms_plug_host * 1e-3),
                    "h2d_bytes_per_step": host_batch.h2d_bytes, "d2h_bytes_per_step": host_batch.d2h_bytes,
                    "call": "nvimgcodecDecoderDecode + future wait + stream sync on the unmodified reference core (oracle/_ref/libnvimgcodec.so) "
-                           "with this extension picked by priority; pageable host bitstreams in, pinned host pixels out; one driver "
+                           "with this extension picked by priority; pinned host bitstreams in, pinned host pixels out; one driver "
                            "process (tests/host/host_driver.cpp) per rank, wall clock inside the driver, max over ranks",
                    "steps_timed": plugin["host"]["repeat"]}
             e2e_dev = {"value": job_mpix / (ms_plug_dev * 1e-3), "unit": "MPix/s", "images_per_s": job_imgs / (ms_plug_dev * 1e-3),
                        "h2d_bytes_per_step": dev_batch.h2d_bytes, "d2h_bytes_per_step": 0,
                        "note": "same plugin call, device output buffers", "steps_timed": plugin["device"]["repeat"]}
+            for key, leg, tgt in (("pageable_in", "host_pageable", e2e), ("pageable_in", "device_pageable", e2e_dev)):
+                r = plugin.get(leg)
+                if r and "error" not in r:
+                    tgt[key] = {"value": r["mpix_per_s"], "unit": "MPix/s",
+                                "note": "same call with the bitstreams in pageable memory: the extension stages them into pinned memory on host threads"}
         else:
             e2e = dict(e2e_capi, note="oracle/_ref/host_driver is not built here: the plugin leg falls back to the C ABI")
             e2e_dev = e2e_capi_dev

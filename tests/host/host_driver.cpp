@@ -17,6 +17,9 @@
 //                                (include/nvimgcodec.h:1095-1096) and print how often each was called
 //     HOST_DRIVER_PINNED=1       host output buffers are pinned (cudaMallocHost) instead of malloc'ed, allocated on the memory node
 //                                with the faster device-to-host copies (probed: on a two-node box the far node halves the rate)
+//     HOST_DRIVER_PINNED_INPUT=1 the bitstreams are handed to the framework in pinned host memory (what a loader that feeds a GPU decoder
+//                                reads files into) instead of pageable std::vector storage
+//     HOST_DRIVER_THREADS=<n>    nvimgcodecExecutionParams_t::max_num_cpu_threads for timing runs (default 0 = all cores)
 //     HOST_DRIVER_FILL=<0..255>  constant sample for the parts of a region that lie outside the image (include/nvimgcodec.h:495-519)
 #include <sched.h>
 
@@ -141,7 +144,7 @@ int main(int argc, char** argv)
 
     nvimgcodecExecutionParams_t ep{NVIMGCODEC_STRUCTURE_TYPE_EXECUTION_PARAMS, sizeof(nvimgcodecExecutionParams_t), nullptr};
     ep.device_id = 0;
-    ep.max_num_cpu_threads = repeat > 0 ? 0 : 4; // timing runs: all host cores, like the default executor
+    ep.max_num_cpu_threads = repeat > 0 ? (std::getenv("HOST_DRIVER_THREADS") ? std::atoi(std::getenv("HOST_DRIVER_THREADS")) : 0) : 4; // timing runs: all host cores by default, like the default executor
     nvimgcodecBackend_t be{NVIMGCODEC_STRUCTURE_TYPE_BACKEND, sizeof(nvimgcodecBackend_t), nullptr};
     be.params = {NVIMGCODEC_STRUCTURE_TYPE_BACKEND_PARAMS, sizeof(nvimgcodecBackendParams_t), nullptr, 1.0f, NVIMGCODEC_LOAD_HINT_POLICY_FIXED};
     if (backend != "any") {
@@ -208,7 +211,15 @@ int main(int argc, char** argv)
     std::vector<nvimgcodecImage_t> images(n, nullptr);
     for (int i = 0; i < n; ++i) {
         Item& it = items[i];
-        CHECK(nvimgcodecCodeStreamCreateFromHostMem(instance, &parents[i], it.bytes.data(), it.bytes.size(), nullptr));
+        const unsigned char* src_bytes = it.bytes.data();
+        if (std::getenv("HOST_DRIVER_PINNED_INPUT")) {
+            void* pin = nullptr;
+            if (cudaMallocHost(&pin, it.bytes.size()) == cudaSuccess) { // (lives until the process ends)
+                std::memcpy(pin, it.bytes.data(), it.bytes.size());
+                src_bytes = static_cast<const unsigned char*>(pin);
+            }
+        }
+        CHECK(nvimgcodecCodeStreamCreateFromHostMem(instance, &parents[i], src_bytes, it.bytes.size(), nullptr));
         nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
         CHECK(nvimgcodecCodeStreamGetImageInfo(parents[i], &info));
         it.w = int(info.plane_info[0].width);
