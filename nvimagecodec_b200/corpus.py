@@ -33,7 +33,7 @@ def synth(height, width, seed):
     return np.clip(img, 0, 255).astype(np.uint8)
 
 
-def encode(rgb, quality=90, sampling="420", rst_interval=0, optimize=False, gray=False):
+def encode(rgb, quality=90, sampling="420", rst_interval=0, optimize=False, gray=False, progressive=False):
     import cv2
 
     params = [cv2.IMWRITE_JPEG_QUALITY, int(quality)]
@@ -43,6 +43,8 @@ def encode(rgb, quality=90, sampling="420", rst_interval=0, optimize=False, gray
         params += [cv2.IMWRITE_JPEG_RST_INTERVAL, int(rst_interval)]
     if optimize:
         params += [cv2.IMWRITE_JPEG_OPTIMIZE, 1]
+    if progressive:  # libjpeg's jpeg_simple_progression script (ten scans for a colour image), optimised tables per scan
+        params += [cv2.IMWRITE_JPEG_PROGRESSIVE, 1]
     src = cv2.cvtColor(rgb, cv2.COLOR_RGB2GRAY) if gray else rgb[..., ::-1]
     ok, buf = cv2.imencode(".jpg", np.ascontiguousarray(src), params)
     if not ok:

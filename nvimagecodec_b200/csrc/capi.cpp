@@ -43,6 +43,15 @@ int b200jpegProbe(const void* data, size_t length, b200jpegStreamInfo_t* info)
                     hd.scan_length = sc[c].scan_length;
         }
     }
+    if (st == b200jpeg::kStreamProgressive) { // SOF2: the scans are decoded one after the other into dense coefficient blocks
+        b200jpeg::ProgStream pg;
+        st = b200jpeg::parse_progressive(static_cast<const uint8_t*>(data), length, &hd, &pg);
+        if (st == b200jpeg::kStreamOk) {
+            hd.scan_offset = pg.scans[0].offset;
+            for (const b200jpeg::ProgScan& ps : pg.scans)
+                hd.scan_length = std::max(hd.scan_length, ps.length);
+        }
+    }
     info->width = hd.width;
     info->height = hd.height;
     info->num_components = hd.ncomp;

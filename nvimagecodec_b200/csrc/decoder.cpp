@@ -260,6 +260,8 @@ Options parse_options(const char* options, const char* decoder_id)
             o.chunk_images = std::max(1, std::atoi(value.c_str()));
         else if (name == "entry_stream")
             o.entry_stream = std::atoi(value.c_str()) != 0;
+        else if (name == "progressive")
+            o.progressive = std::atoi(value.c_str()) != 0;
         else if (name == "fused_pixels")
             o.fused_pixels = std::atoi(value.c_str()) != 0;
         else if (name == "use_executor")
@@ -301,7 +303,7 @@ Decoder::~Decoder()
         cudaEventDestroy(done_event_);
     if (side_stream_)
         cudaStreamDestroy(side_stream_);
-    for (DeviceBuffer* b : {&upload_, &scratch_, &cmp_, &coef_, &sym_, &planes_, &bounce_, &scan_scratch_})
+    for (DeviceBuffer* b : {&upload_, &scratch_, &cmp_, &coef_, &sym_, &pcoef_, &planes_, &bounce_, &scan_scratch_})
         b->release(sv_);
     for (PinnedBuffer* b : {&scan_host_, &upload_host_, &state_host_})
         b->release(sv_);
@@ -345,9 +347,13 @@ void parse_input(const void* data, size_t len, ParsedInput* out)
     out->multi_status = kStreamOk;
     out->frame = StreamHeader(); // entries are reused across batches: nothing of the previous stream (restart interval, tables) may survive
     out->status = data ? parse_stream(static_cast<const uint8_t*>(data), len, &out->frame) : kStreamNotJpeg;
+    out->prog.reset();
     if (out->status == kStreamMultiScan) {
         out->scans.reset(new StreamHeader[3]);
         out->multi_status = parse_multiscan(static_cast<const uint8_t*>(data), len, &out->frame, out->scans.get());
+    } else if (out->status == kStreamProgressive) {
+        out->prog.reset(new ProgStream);
+        out->multi_status = parse_progressive(static_cast<const uint8_t*>(data), len, &out->frame, out->prog.get());
     }
 }
 
@@ -450,9 +456,11 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     // Work list: one entry per device image.  A stream whose three components come in three scans becomes up to three
     // one-component images (kChild; each decodes like a grayscale image of the component's size) plus the image itself
     // (kParent: no entropy data of its own, its colour stage reads the children's planes).
-    enum { kNormal = 0, kChild = 1, kParent = 2 };
+    // A progressive stream becomes one image per scan (kScan: K0 only -- unstuffed words and restart boundaries for the
+    // progressive kernels) plus the image itself (kProg: coefficient blocks, planes, pixel stage).
+    enum { kNormal = 0, kChild = 1, kParent = 2, kScan = 3, kProg = 4 };
     struct Item {
-        int i, role;
+        int i, role, scan;
     };
     std::vector<Item> items;
     items.reserve(n);
@@ -469,7 +477,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         const ParsedInput& pi = (parsed && parsed[i]) ? *parsed[i] : parsed_own_[size_t(i)];
         if (pi.status == kStreamOk) {
             hdrs.push_back(&pi.frame);
-            items.push_back({i, kNormal});
+            items.push_back({i, kNormal, 0});
         } else if (pi.status == kStreamMultiScan) {
             if (pi.multi_status != kStreamOk || !pi.scans) {
                 host_status_[i] = status_of(pi.multi_status);
@@ -478,23 +486,98 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             const int n_child = outs[i].format == B200JPEG_FMT_Y ? 1 : 3; // Y output consumes luma only
             for (int c = 0; c < n_child; ++c) {
                 hdrs.push_back(&pi.scans[c]);
-                items.push_back({i, kChild});
+                items.push_back({i, kChild, 0});
             }
             parent_frames.push_back(pi.frame);
             parent_frames.back().restart_interval = 0;
             hdrs.push_back(&parent_frames.back());
-            items.push_back({i, kParent});
+            items.push_back({i, kParent, 0});
+        } else if (pi.status == kStreamProgressive) {
+            if (!opt_.progressive) {
+                host_status_[i] = B200JPEG_ERR_UNSUPPORTED;
+                continue;
+            }
+            if (pi.multi_status != kStreamOk || !pi.prog) {
+                host_status_[i] = status_of(pi.multi_status);
+                continue;
+            }
+            for (size_t sidx = 0; sidx < pi.prog->scans.size(); ++sidx) {
+                hdrs.push_back(&pi.frame);
+                items.push_back({i, kScan, int(sidx)});
+            }
+            hdrs.push_back(&pi.frame);
+            items.push_back({i, kProg, 0});
         } else {
             host_status_[i] = status_of(pi.status);
         }
     }
     int children_ok = 0; // children of the multi-scan stream under way that made it into the batch
+    std::vector<ProgScanDev> prog_scans;
+    std::vector<int> prog_scan_wave;
+    std::vector<ProgHuffDev> prog_tables;
+    std::vector<uint32_t> prog_imgs;
+    int prog_waves = 0;
+    uint32_t prog_max_blocks = 0;
+    size_t pcoef_elems = 0;
+    std::vector<size_t> scan_offs; // per device image: where its entropy-coded bytes start in the input
+    scan_offs.reserve(items.size());
     for (size_t item = 0; item < items.size(); ++item) {
         const int i = items[item].i, role = items[item].role;
         const StreamHeader& hd = *hdrs[item];
-        if (role == kChild && (item == 0 || items[item - 1].role != kChild || items[item - 1].i != i))
+        if ((role == kChild || role == kScan) && (item == 0 || items[item - 1].role != role || items[item - 1].i != i))
             children_ok = 0;
+        if (role == kScan) {
+            // one scan of a progressive stream: what K0 needs, nothing else
+            const ParsedInput& pi = (parsed && parsed[i]) ? *parsed[i] : parsed_own_[size_t(i)];
+            const ProgScan& ps = pi.prog->scans[size_t(items[item].scan)];
+            if (ps.length >= (size_t(1) << 28)) {
+                host_status_[i] = B200JPEG_ERR_TOO_LARGE;
+                continue;
+            }
+            ImageDev im;
+            std::memset(&im, 0, sizeof(im));
+            im.raw_off = raw_bytes;
+            im.raw_len = uint32_t(ps.length);
+            raw_bytes += align_up(ps.length, 16) + 16;
+            im.cmp_off = cmp_bytes;
+            cmp_bytes += align_up(ps.length, 16) + 32;
+            im.tile_off = n_tiles;
+            im.n_tiles = uint32_t((ps.length + kScanTileBytes - 1) / kScanTileBytes);
+            n_tiles += im.n_tiles;
+            im.sub_off = n_sub;
+            im.seq_off = n_seq;
+            im.wseq_off = n_wseq;
+            im.restart_interval = uint32_t(ps.restart_interval);
+            im.n_rst_expected = ps.restart_interval ? uint32_t((ps.mcus + ps.restart_interval - 1) / ps.restart_interval - 1) : 0u;
+            im.bnd_off = n_bnd;
+            im.n_bnd_cap = im.n_rst_expected + 1;
+            n_bnd += im.n_bnd_cap;
+            im.coef_off = coef_elems;
+            im.sym_off = sym_chunks_total;
+            im.dc_cta_off = n_dc;
+            im.idct_cta_off = n_idct;
+            im.color_cta_off = n_color;
+            im.ncomp = im.ncomp_needed = 1;
+            const uint32_t self = uint32_t(imgs_.size());
+            const uint32_t gate_self[3] = {self, self, self};
+            gates_.insert(gates_.end(), gate_self, gate_self + 3);
+            in_index_.push_back(i);
+            item_of_dev.push_back(item);
+            scan_offs.push_back(ps.offset);
+            imgs_.push_back(im);
+            host_outs_.push_back(HostOut{nullptr, 0, 0, 0, 0, 0});
+            ++children_ok;
+            continue;
+        }
         const b200jpegOutput_t& o = role == kChild ? child_out : outs[i];
+        if (role == kProg) {
+            const ParsedInput& pi = (parsed && parsed[i]) ? *parsed[i] : parsed_own_[size_t(i)];
+            if (host_status_[i] != B200JPEG_OK || children_ok != int(pi.prog->scans.size())) {
+                if (host_status_[i] == B200JPEG_OK)
+                    host_status_[i] = B200JPEG_ERR_UNSUPPORTED;
+                continue;
+            }
+        }
         if (role == kParent) {
             const int want = o.format == B200JPEG_FMT_Y ? 1 : 3;
             if (host_status_[i] != B200JPEG_OK || children_ok != want) {
@@ -531,7 +614,22 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             host_status_[i] = B200JPEG_ERR_TOO_LARGE;
             continue;
         }
-        if (role != kParent) {
+        if (role == kProg) {
+            // Same reasoning as below: a first DC scan spends at least one bit per block.
+            const ParsedInput& pi = (parsed && parsed[i]) ? *parsed[i] : parsed_own_[size_t(i)];
+            const uint64_t blocks = uint64_t(hd.mcus_x) * uint64_t(hd.mcus_y) * uint64_t(hd.blocks_per_mcu);
+            uint64_t scan_bytes = 0;
+            for (const ProgScan& ps : pi.prog->scans)
+                scan_bytes += ps.length;
+            if (scan_bytes * 8 < blocks) {
+                host_status_[i] = B200JPEG_ERR_CORRUPT;
+                continue;
+            }
+            if (blocks * 192 > (uint64_t(opt_.max_arena_mb) << 20) || coef_elems / 64 + blocks >= (uint64_t(1) << 28)) {
+                host_status_[i] = B200JPEG_ERR_TOO_LARGE;
+                continue;
+            }
+        } else if (role != kParent) {
             // The arenas are sized from the frame header, which costs an attacker nothing to inflate.  Every coded block
             // takes at least two bits (a DC code and an end-of-block code), so a scan shorter than that cannot hold the
             // blocks the header claims: corrupt, before anything is allocated.  What remains is bounded per image
@@ -604,7 +702,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             const uint32_t ri_blocks = uint32_t(hd.restart_interval) * uint32_t(hd.blocks_per_mcu);
             im.dc_blk_lo = ri_blocks ? im.write_blk_lo / ri_blocks * ri_blocks : 0u;
             im.dc_cta_off = n_dc;
-            im.n_dc_cta = (im.write_blk_hi - im.dc_blk_lo + kDcChunk - 1) / kDcChunk;
+            im.n_dc_cta = role == kProg ? 0u : (im.write_blk_hi - im.dc_blk_lo + kDcChunk - 1) / kDcChunk; // (progressive DC values are final)
             n_dc += im.n_dc_cta;
         }
         int b = 0;
@@ -725,7 +823,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         // huffman set: deduplicated by content (the canonical bytes of the table specs are the key, so two streams share
         // device tables only when their specs are equal).  Cache nodes stay where they are for the whole batch: eviction
         // happens at the top of prepare() only.
-        if (role == kParent) {
+        if (role == kParent || role == kProg) {
             im.huff_set = 0;
         } else {
             huff_set_key(hd, &set_key_);
@@ -765,12 +863,65 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         else if (im.ncomp_needed == 1)
             gate[1] = gate[2] = gate[0];
         im.multi = role == kParent ? 1 : 0;
+        if (role == kProg) {
+            // the scans just pushed are this image's; their chains are laid out by wave once every image is known
+            const ParsedInput& pi = (parsed && parsed[i]) ? *parsed[i] : parsed_own_[size_t(i)];
+            const ProgStream& pg = *pi.prog;
+            im.prog = 1;
+            im.pcoef_off = pcoef_elems;
+            pcoef_elems += size_t(im.total_blocks) * 64;
+            const uint32_t self = uint32_t(imgs_.size()), table0 = uint32_t(prog_tables.size());
+            for (const HuffSpec& hs : pg.tables) {
+                prog_tables.emplace_back();
+                build_prog_table(hs, &prog_tables.back());
+            }
+            for (size_t sidx = 0; sidx < pg.scans.size(); ++sidx) {
+                const ProgScan& ps = pg.scans[sidx];
+                ProgScanDev sd;
+                std::memset(&sd, 0, sizeof(sd));
+                sd.parent = self;
+                sd.child = self - uint32_t(pg.scans.size()) + uint32_t(sidx);
+                sd.ri = uint32_t(ps.restart_interval);
+                sd.n_mcu = uint32_t(ps.mcus);
+                sd.n_chain = ps.restart_interval ? uint32_t((ps.mcus + ps.restart_interval - 1) / ps.restart_interval) : 1u;
+                sd.wb = uint16_t(ps.wb);
+                sd.hb = uint16_t(ps.hb);
+                sd.ncomp = uint8_t(ps.ncomp);
+                for (int k = 0; k < ps.ncomp; ++k) {
+                    sd.comp[k] = uint8_t(ps.comp[k]);
+                    sd.table[k] = ps.table[k] >= 0 ? table0 + uint32_t(ps.table[k]) : 0u;
+                }
+                sd.ss = uint8_t(ps.ss);
+                sd.se = uint8_t(ps.se);
+                sd.ah = uint8_t(ps.ah);
+                sd.al = uint8_t(ps.al);
+                prog_scans.push_back(sd);
+                prog_scan_wave.push_back(ps.wave);
+                prog_waves = std::max(prog_waves, ps.wave + 1);
+            }
+            prog_imgs.push_back(self);
+            prog_max_blocks = std::max(prog_max_blocks, im.total_blocks);
+        }
         gates_.insert(gates_.end(), gate, gate + 3);
         in_index_.push_back(i);
         item_of_dev.push_back(item);
+        scan_offs.push_back(hd.scan_offset);
         imgs_.push_back(im);
         host_outs_.push_back(ho);
     }
+    // chains of the progressive scans, wave by wave (a scan's chains are contiguous: chain - chain_off = restart interval)
+    std::vector<uint32_t> prog_chain_scan;
+    prog_wave_off_.assign(size_t(prog_waves) + 1, 0u);
+    for (int w = 0; w < prog_waves; ++w) {
+        prog_wave_off_[size_t(w)] = uint32_t(prog_chain_scan.size());
+        for (size_t k = 0; k < prog_scans.size(); ++k) {
+            if (prog_scan_wave[k] != w)
+                continue;
+            prog_scans[k].chain_off = uint32_t(prog_chain_scan.size());
+            prog_chain_scan.insert(prog_chain_scan.end(), prog_scans[k].n_chain, uint32_t(k));
+        }
+    }
+    prog_wave_off_[size_t(prog_waves)] = uint32_t(prog_chain_scan.size());
     algo_bytes_ = comp_bytes_ + 4 * n_coefs_ + out_bytes_;
     const int nd = int(imgs_.size());
 
@@ -845,6 +996,14 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     off = align_up(off + 12ull * nd, 256);
     const size_t off_huff = off;
     off = align_up(off + sizeof(HuffSetDev) * sets.size(), 256);
+    const size_t off_pscan = off;
+    off = align_up(off + sizeof(ProgScanDev) * prog_scans.size(), 256);
+    const size_t off_pchain = off;
+    off = align_up(off + 4ull * prog_chain_scan.size(), 256);
+    const size_t off_phuff = off;
+    off = align_up(off + sizeof(ProgHuffDev) * prog_tables.size(), 256);
+    const size_t off_pimg = off;
+    off = align_up(off + 4ull * prog_imgs.size(), 256);
     const size_t off_raw = off;
     off += raw_bytes + 256;
     const size_t upload_bytes = off;
@@ -883,7 +1042,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         return fail(B200JPEG_ERR_CUDA, "pinned host allocation failed");
     if (!upload_.ensure(upload_bytes, &device_bytes_, sv_, stream) || !scratch_.ensure(so + 256, &device_bytes_, sv_, stream) ||
         !cmp_.ensure(cmp_bytes + 256, &device_bytes_, sv_, stream) || !coef_.ensure(coef_bytes_ + 256, &device_bytes_, sv_, stream) ||
-        !sym_.ensure(sym_bytes + 256, &device_bytes_, sv_, stream) ||
+        !sym_.ensure(sym_bytes + 256, &device_bytes_, sv_, stream) || !pcoef_.ensure(pcoef_elems * sizeof(int16_t) + 256, &device_bytes_, sv_, stream) ||
         !planes_.ensure(plane_bytes + 256, &device_bytes_, sv_, stream) || !bounce_.ensure(bounce_bytes + 256, &device_bytes_, sv_, stream))
         return fail(B200JPEG_ERR_CUDA, "device allocation failed");
 
@@ -917,7 +1076,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         std::fill(idct_img + im.idct_cta_off, idct_img + im.idct_cta_off + im.n_idct_cta, uint32_t(d));
         std::fill(color_img + im.color_cta_off, color_img + im.color_cta_off + im.n_color_cta_x * im.n_color_cta_y, uint32_t(d));
         std::fill(px_img + im.px_cta_off, px_img + im.px_cta_off + im.px_n_cta, uint32_t(d));
-        src_scan_[d] = static_cast<const uint8_t*>(data[in_index_[d]]) + hdrs[item_of_dev[d]]->scan_offset;
+        src_scan_[d] = static_cast<const uint8_t*>(data[in_index_[d]]) + scan_offs[size_t(d)];
         if (sources_pinned && im.raw_len >= (uint32_t(opt_.direct_kb) << 10))
             direct_[d] = 1;
         else
@@ -929,6 +1088,13 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     }
     for (size_t si = 0; si < sets.size(); ++si)
         std::memcpy(up + off_huff + si * sizeof(HuffSetDev), sets[si], sizeof(HuffSetDev));
+    if (!prog_scans.empty()) {
+        std::memcpy(up + off_pscan, prog_scans.data(), sizeof(ProgScanDev) * prog_scans.size());
+        std::memcpy(up + off_pchain, prog_chain_scan.data(), 4ull * prog_chain_scan.size());
+        std::memcpy(up + off_phuff, prog_tables.data(), sizeof(ProgHuffDev) * prog_tables.size());
+        std::memcpy(up + off_pimg, prog_imgs.data(), 4ull * prog_imgs.size());
+    }
+    pcoef_bytes_ = pcoef_elems * sizeof(int16_t);
     off_raw_ = off_raw;
     upload_bytes_ = upload_bytes;
     const double t2 = trace_enabled() ? trace_now_us() : 0;
@@ -956,6 +1122,13 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     for (const ImageDev& im : imgs_)
         bd_.n_multi += im.multi;
     bd_.huff = reinterpret_cast<const HuffSetDev*>(dv + off_huff);
+    bd_.prog_scan = reinterpret_cast<const ProgScanDev*>(dv + off_pscan);
+    bd_.prog_chain = reinterpret_cast<const uint32_t*>(dv + off_pchain);
+    bd_.prog_huff = reinterpret_cast<const ProgHuffDev*>(dv + off_phuff);
+    bd_.prog_img = reinterpret_cast<const uint32_t*>(dv + off_pimg);
+    bd_.pcoef = pcoef_.as<int16_t>();
+    bd_.n_prog_img = int(prog_imgs.size());
+    bd_.prog_max_blocks = prog_max_blocks;
     bd_.raw = dv + off_raw;
     bd_.state = reinterpret_cast<ImageState*>(sc + so_state);
     bd_.tile_info = reinterpret_cast<uint2*>(sc + so_tinfo);
@@ -1118,6 +1291,10 @@ int Decoder::execute(cudaStream_t stream)
     launches_ += launch_write(bd_, false, stream); // writes every coefficient exactly once: no clearing pass
     mark(4, stream);
     launches_ += launch_dc_scan(bd_, false, stream);
+    if (bd_.n_prog_img) { // progressive images: their scans accumulate into zeroed blocks, wave by wave
+        cudaMemsetAsync(bd_.pcoef, 0, pcoef_bytes_, stream);
+        launches_ += launch_progressive(bd_, prog_wave_off_.data(), int(prog_wave_off_.size()) - 1, stream);
+    }
     // Everything a status depends on is known once the entropy stage is through (the pixel kernels only read the
     // flags).  The read-back goes over a side stream so that it neither waits for the pixel kernels nor holds them up;
     // finish_wait() then only has to wait for it, and the caller gets its statuses while the pixels are still being made.
@@ -1320,6 +1497,15 @@ int Decoder::copy_coefficients(int index, int16_t* host_out, size_t cap_elems)
     if (cap_elems < elems)
         return fail(B200JPEG_ERR_ARG, "buffer too small");
     cudaSetDevice(device_);
+    if (im.prog) { // dense blocks of their own; the record pass moved the DC value into the block record
+        std::vector<uint32_t> recs(im.total_blocks);
+        if (!cuda_ok(cudaMemcpy(host_out, bd_.pcoef + im.pcoef_off, elems * sizeof(int16_t), cudaMemcpyDeviceToHost), "coefficient copy") ||
+            !cuda_ok(cudaMemcpy(recs.data(), bd_.blkrec + im.coef_off / 64, recs.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost), "record copy"))
+            return B200JPEG_ERR_CUDA;
+        for (size_t b = 0; b < recs.size(); ++b)
+            host_out[b * 64] = int16_t(recs[b] >> 16);
+        return B200JPEG_OK;
+    }
     if (bd_.sym_mode) {
         // entry-stream form: the same walk the IDCT stage does (sym_fetch_block in pixels.cuh), on the host
         const int d = dev_index_[index];

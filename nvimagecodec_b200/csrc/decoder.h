@@ -88,6 +88,7 @@ struct Options {
     int chunk_images = 64;        // ... or this many images, whichever comes first
     int host_threads = 0;         // helper threads for marker walks / staging (0 = by the CPUs this process may run on, at most 8)
     bool entry_stream = true;     // K3 writes the coefficients as a stream of 16-bit entries (huff_emit) instead of dense 16-byte groups (huff_write)
+    bool progressive = true;      // take progressive (SOF2) streams (progressive.cuh); off: they are declined and fall to the next decoder
     bool fused_pixels = false;    // IDCT + upsampling + colour in one kernel (pixels_kernel); off: the idct and color kernels, which are faster as measured (profiles/)
     bool use_executor = false;    // (extension) fan host work out over the framework's executor instead of the decoder's own helper threads (measured: ~0.1 ms of dispatch latency per fan-out)
     bool sync_finish = false;     // Finish / DecodeBatch wait for the pixel kernels too, not only for the statuses
@@ -105,6 +106,7 @@ struct ParsedInput {
     StreamHeader frame;          // kStreamOk: the stream; kStreamMultiScan: geometry of the whole image
     std::unique_ptr<StreamHeader[]> scans; // kStreamMultiScan only: the three one-component scans
     StreamStatus multi_status = kStreamOk;
+    std::unique_ptr<ProgStream> prog;      // kStreamProgressive only: the scans (frame = geometry of the image)
 };
 
 class Decoder {
@@ -170,7 +172,9 @@ class Decoder {
     bool prepared_ = false, executed_ = false, finish_queued_ = false, any_host_out_ = false;
 
     // device memory
-    DeviceBuffer upload_, scratch_, cmp_, coef_, sym_, planes_, bounce_, scan_scratch_;
+    DeviceBuffer upload_, scratch_, cmp_, coef_, sym_, pcoef_, planes_, bounce_, scan_scratch_;
+    std::vector<uint32_t> prog_wave_off_; // progressive chains of the batch, by wave: [w] .. [w + 1)
+    size_t pcoef_bytes_ = 0;
     PinnedBuffer upload_host_, state_host_, scan_host_;
     size_t device_bytes_ = 0;
     size_t coef_bytes_ = 0;

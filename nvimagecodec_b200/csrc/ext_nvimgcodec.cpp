@@ -391,7 +391,8 @@ class DecoderImpl {
         if (std::strcmp(cs_info.codec_name, "jpeg") != 0)
             return NVIMGCODEC_PROCESSING_STATUS_CODEC_UNSUPPORTED;
         if (jpeg_info.encoding != NVIMGCODEC_JPEG_ENCODING_BASELINE_DCT &&
-            jpeg_info.encoding != NVIMGCODEC_JPEG_ENCODING_EXTENDED_SEQUENTIAL_DCT_HUFFMAN)
+            jpeg_info.encoding != NVIMGCODEC_JPEG_ENCODING_EXTENDED_SEQUENTIAL_DCT_HUFFMAN &&
+            !(jpeg_info.encoding == NVIMGCODEC_JPEG_ENCODING_PROGRESSIVE_DCT_HUFFMAN && opt_.progressive))
             return NVIMGCODEC_PROCESSING_STATUS_ENCODING_UNSUPPORTED;
         nvimgcodecImageInfo_t info{NVIMGCODEC_STRUCTURE_TYPE_IMAGE_INFO, sizeof(nvimgcodecImageInfo_t), nullptr};
         if (image->getImageInfo(image->instance, &info) != NVIMGCODEC_STATUS_SUCCESS)
@@ -432,6 +433,10 @@ class DecoderImpl {
             ss = pi.multi_status;
             for (int c = 0; c < 3 && pi.scans; ++c)
                 longest_scan = std::max(longest_scan, pi.scans[c].scan_length);
+        } else if (ss == b200jpeg::kStreamProgressive) {
+            ss = pi.multi_status;
+            for (size_t k = 0; pi.prog && k < pi.prog->scans.size(); ++k)
+                longest_scan = std::max(longest_scan, pi.prog->scans[k].length);
         }
         if (ss == b200jpeg::kStreamOk && longest_scan >= (size_t(1) << 28))
             return NVIMGCODEC_PROCESSING_STATUS_CODESTREAM_UNSUPPORTED;

@@ -4,6 +4,7 @@
 #include <string>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace b200jpeg {
@@ -139,10 +140,14 @@ StreamStatus parse_stream(const uint8_t* d, size_t n, StreamHeader* hdr)
             }
             // SOF0 baseline and SOF1 extended-sequential Huffman decode identically at 8 bits (SOF1 merely
             // allows 4 tables per class and 12-bit samples; those are declined below / here)
-            if ((m != 0xC0 && m != 0xC1) || hdr->precision != 8)
-                verdict = kStreamUnsupported; // progressive / lossless / arithmetic / 12-bit
+            if (m == 0xC2 && hdr->precision == 8)
+                verdict = kStreamProgressive; // parse_progressive lists its scans
+            else if ((m != 0xC0 && m != 0xC1) || hdr->precision != 8)
+                verdict = kStreamUnsupported; // lossless / arithmetic / 12-bit
             if (hdr->width == 0 || hdr->height == 0)
                 verdict = kStreamUnsupported; // DNL-defined height
+            if (verdict == kStreamProgressive && hdr->ncomp != 1 && hdr->ncomp != 3)
+                verdict = kStreamUnsupported;
         } else if (m == 0xDA) {
             if (!have_sof || sl < 1)
                 return kStreamCorrupt;
@@ -363,6 +368,271 @@ StreamStatus parse_multiscan(const uint8_t* d, size_t n, StreamHeader* frame, St
     frame->mcus_x = (frame->width + 8 * frame->hmax - 1) / (8 * frame->hmax);
     frame->mcus_y = (frame->height + 8 * frame->vmax - 1) / (8 * frame->vmax);
     return kStreamOk;
+}
+
+namespace {
+
+// End of an entropy-coded segment that starts at `from`: the first marker that is neither a stuffed FF00, a fill FF nor
+// RSTn (or the end of the data).
+size_t segment_end(const uint8_t* d, size_t n, size_t from)
+{
+    size_t q = from;
+    for (;;) {
+        const void* f = q < n ? std::memchr(d + q, 0xFF, n - q) : nullptr;
+        if (!f)
+            return n;
+        q = size_t(static_cast<const uint8_t*>(f) - d);
+        if (q + 1 >= n)
+            return n;
+        const int x = d[q + 1];
+        if (x == 0x00 || (x >= 0xD0 && x <= 0xD7))
+            q += 2;
+        else if (x == 0xFF)
+            q += 1;
+        else
+            return q;
+    }
+}
+
+int max_jpeg_scans()
+{
+    static const int v = [] {
+        const char* e = std::getenv("NVIMGCODEC_MAX_JPEG_SCANS");
+        const int x = e ? std::atoi(e) : 0;
+        return x > 0 ? x : 256;
+    }();
+    return v;
+}
+
+} // namespace
+
+StreamStatus parse_progressive(const uint8_t* d, size_t n, StreamHeader* frame, ProgStream* out)
+{
+    out->scans.clear();
+    out->tables.clear();
+    out->n_waves = 0;
+    StreamHeader cur;
+    for (int c = 0; c < 2; ++c)
+        for (int t = 0; t < 4; ++t)
+            cur.huff[c][t].present = false;
+    if (n < 4 || d[0] != 0xFF || d[1] != 0xD8)
+        return kStreamNotJpeg;
+    size_t p = 2;
+    bool have_sof = false;
+    int coef_bits[kMaxComp][64]; // bits still missing per coefficient, -1 = never sent (jdphuff.c coef_bits)
+    int last_wave[kMaxComp][64];
+    int table_of[2][4] = {{-1, -1, -1, -1}, {-1, -1, -1, -1}}; // tables already copied for the specs in force
+    for (int c = 0; c < kMaxComp; ++c)
+        for (int k = 0; k < 64; ++k) {
+            coef_bits[c][k] = -1;
+            last_wave[c][k] = -1;
+        }
+    for (;;) {
+        if (p + 2 > n)
+            break; // no EOI: what was listed stands if the progression is complete
+        if (d[p] != 0xFF)
+            return kStreamCorrupt;
+        while (p < n && d[p] == 0xFF)
+            ++p;
+        if (p >= n)
+            break;
+        const int m = d[p++];
+        if (m == 0xD9)
+            break;
+        if (m == 0xD8 || m == 0x01 || (m >= 0xD0 && m <= 0xD7))
+            continue;
+        if (p + 2 > n)
+            return kStreamCorrupt;
+        const size_t len = be16(d + p);
+        if (len < 2 || p + len > n)
+            return kStreamCorrupt;
+        const uint8_t* s = d + p + 2;
+        const size_t sl = len - 2;
+        if (m == 0xDB) {
+            if (!out->scans.empty())
+                return kStreamUnsupported; // quantisation tables redefined between scans
+            if (!read_dqt(s, sl, &cur))
+                return kStreamCorrupt;
+        } else if (m == 0xC4) {
+            if (!read_dht(s, sl, &cur))
+                return kStreamCorrupt;
+            for (size_t q = 0; q < sl;) { // the tables this segment (re)defined need a fresh copy
+                const int tc = s[q] >> 4, th = s[q] & 15;
+                int total = 0;
+                for (int l = 1; l <= 16; ++l)
+                    total += s[q + l];
+                table_of[tc][th] = -1;
+                q += 17 + size_t(total);
+            }
+        } else if (m == 0xDD) {
+            if (sl < 2)
+                return kStreamCorrupt;
+            cur.restart_interval = int(be16(s));
+        } else if (m == 0xE0) {
+            if (sl >= 5 && std::memcmp(s, "JFIF", 5) == 0)
+                cur.has_jfif = true;
+        } else if (m == 0xEE) {
+            if (sl >= 12 && std::memcmp(s, "Adobe", 5) == 0)
+                cur.adobe_transform = s[11];
+        } else if (m == 0xC2) {
+            if (have_sof || sl < 6)
+                return kStreamCorrupt;
+            have_sof = true;
+            cur.sof = m;
+            cur.precision = s[0];
+            cur.height = int(be16(s + 1));
+            cur.width = int(be16(s + 3));
+            cur.ncomp = s[5];
+            if (cur.precision != 8 || cur.width == 0 || cur.height == 0 || (cur.ncomp != 1 && cur.ncomp != 3))
+                return kStreamUnsupported;
+            if (sl < 6 + 3 * size_t(cur.ncomp))
+                return kStreamCorrupt;
+            for (int c = 0; c < cur.ncomp; ++c) {
+                cur.comp_id[c] = s[6 + 3 * c];
+                cur.h[c] = s[7 + 3 * c] >> 4;
+                cur.v[c] = s[7 + 3 * c] & 15;
+                cur.tq[c] = s[8 + 3 * c];
+                if (cur.h[c] < 1 || cur.h[c] > 4 || cur.v[c] < 1 || cur.v[c] > 4 || cur.tq[c] > 3)
+                    return kStreamCorrupt;
+            }
+            if (cur.ncomp == 1)
+                cur.h[0] = cur.v[0] = 1;
+            cur.hmax = cur.vmax = 1;
+            cur.blocks_per_mcu = 0;
+            for (int c = 0; c < cur.ncomp; ++c) {
+                cur.hmax = std::max(cur.hmax, cur.h[c]);
+                cur.vmax = std::max(cur.vmax, cur.v[c]);
+                cur.blocks_per_mcu += cur.h[c] * cur.v[c];
+            }
+            if (cur.blocks_per_mcu > kMaxBlocksPerMcu)
+                return kStreamCorrupt;
+            for (int c = 0; c < cur.ncomp; ++c)
+                if (cur.h[c] == 3 || cur.v[c] == 3 || cur.hmax % cur.h[c] || cur.vmax % cur.v[c])
+                    return kStreamUnsupported;
+            cur.mcus_x = (cur.width + 8 * cur.hmax - 1) / (8 * cur.hmax);
+            cur.mcus_y = (cur.height + 8 * cur.vmax - 1) / (8 * cur.vmax);
+        } else if (m >= 0xC0 && m <= 0xCF && m != 0xC8 && m != 0xCC) {
+            return have_sof ? kStreamCorrupt : kStreamUnsupported;
+        } else if (m == 0xDA) {
+            if (!have_sof || sl < 1)
+                return kStreamCorrupt;
+            if (int(out->scans.size()) >= max_jpeg_scans())
+                return kStreamUnsupported;
+            const int ns = s[0];
+            if (ns < 1 || ns > 4 || sl < 1 + 2 * size_t(ns) + 3)
+                return kStreamCorrupt;
+            ProgScan sc;
+            sc.ncomp = ns;
+            int td[kMaxComp] = {0, 0, 0, 0}, ta[kMaxComp] = {0, 0, 0, 0};
+            for (int i = 0; i < ns; ++i) {
+                int c = -1;
+                for (int k = 0; k < cur.ncomp; ++k)
+                    if (s[1 + 2 * i] == cur.comp_id[k])
+                        c = k;
+                td[i] = s[2 + 2 * i] >> 4;
+                ta[i] = s[2 + 2 * i] & 15;
+                if (c < 0 || td[i] > 3 || ta[i] > 3 || (i > 0 && c <= sc.comp[i - 1]))
+                    return kStreamCorrupt;
+                sc.comp[i] = c;
+            }
+            sc.ss = s[1 + 2 * ns];
+            sc.se = s[2 + 2 * ns];
+            sc.ah = s[3 + 2 * ns] >> 4;
+            sc.al = s[3 + 2 * ns] & 15;
+            // jdphuff.c start_pass_phuff_decoder
+            bool bad = sc.ss == 0 ? sc.se != 0 : (sc.se < sc.ss || sc.se > 63 || ns != 1);
+            bad = bad || (sc.ah != 0 && sc.ah - 1 != sc.al) || sc.al > 13;
+            if (bad)
+                return kStreamCorrupt;
+            if (ns != 1 && ns != cur.ncomp)
+                return kStreamUnsupported; // a scan that interleaves only some of the components
+            for (int i = 0; i < ns; ++i) {
+                const int c = sc.comp[i];
+                if (!cur.qt_present[cur.tq[c]])
+                    return kStreamCorrupt;
+                if (sc.ss && coef_bits[c][0] < 0)
+                    return kStreamUnsupported; // AC before DC (libjpeg warns and goes on)
+                for (int k = sc.ss; k <= sc.se; ++k) {
+                    if (sc.ah != (coef_bits[c][k] < 0 ? 0 : coef_bits[c][k]))
+                        return kStreamUnsupported; // out-of-order refinement (libjpeg warns and goes on)
+                    coef_bits[c][k] = sc.al;
+                    sc.wave = std::max(sc.wave, last_wave[c][k] + 1);
+                }
+            }
+            for (int i = 0; i < ns; ++i)
+                for (int k = sc.ss; k <= sc.se; ++k)
+                    last_wave[sc.comp[i]][k] = sc.wave;
+            out->n_waves = std::max(out->n_waves, sc.wave + 1);
+            if (!(sc.ss == 0 && sc.ah != 0)) { // every scan type but DC refinement decodes Huffman symbols
+                for (int i = 0; i < ns; ++i) {
+                    const int cls = sc.ss ? 1 : 0, id = sc.ss ? ta[i] : td[i];
+                    if (!cur.huff[cls][id].present)
+                        return kStreamCorrupt;
+                    if (table_of[cls][id] < 0) {
+                        table_of[cls][id] = int(out->tables.size());
+                        out->tables.push_back(cur.huff[cls][id]);
+                    }
+                    sc.table[i] = table_of[cls][id];
+                }
+            }
+            sc.restart_interval = cur.restart_interval;
+            if (ns == 1) {
+                const int c = sc.comp[0];
+                const int cw = (cur.width * cur.h[c] + cur.hmax - 1) / cur.hmax, ch = (cur.height * cur.v[c] + cur.vmax - 1) / cur.vmax;
+                sc.wb = (cw + 7) / 8;
+                sc.hb = (ch + 7) / 8;
+                sc.mcus = sc.wb * sc.hb;
+            } else {
+                sc.mcus = cur.mcus_x * cur.mcus_y;
+            }
+            sc.offset = p + len;
+            const size_t q = segment_end(d, n, sc.offset);
+            sc.length = std::min(n, q + 2) - sc.offset;
+            out->scans.push_back(sc);
+            p = q;
+            continue;
+        }
+        p += len;
+    }
+    if (!have_sof || out->scans.empty())
+        return kStreamCorrupt;
+    for (int c = 0; c < cur.ncomp; ++c)
+        for (int k = 0; k < 64; ++k)
+            if (coef_bits[c][k] != 0)
+                return kStreamUnsupported; // incomplete progression
+    if (cur.ncomp == 3) {
+        if (cur.adobe_transform == 0)
+            return kStreamUnsupported;
+        if (!cur.has_jfif && cur.adobe_transform < 0 && cur.comp_id[0] == 'R' && cur.comp_id[1] == 'G' && cur.comp_id[2] == 'B')
+            return kStreamUnsupported;
+    }
+    *frame = cur;
+    frame->nscans = int(out->scans.size());
+    frame->restart_interval = 0;
+    frame->scan_offset = frame->scan_length = 0;
+    return kStreamOk;
+}
+
+void build_prog_table(const HuffSpec& spec, ProgHuffDev* out)
+{
+    std::memset(out, 0, sizeof(*out));
+    int code = 0, k = 0;
+    for (int l = 1; l <= 16; ++l) {
+        out->valoff[l] = k - code;
+        const int cnt = spec.bits[l];
+        for (int i = 0; i < cnt; ++i, ++code, ++k) {
+            if (l <= 9) {
+                const int first = code << (9 - l), span = 1 << (9 - l);
+                for (int j = 0; j < span; ++j)
+                    out->lut[first + j] = uint16_t((l << 8) | spec.vals[k]);
+            }
+        }
+        out->maxcode[l] = cnt ? code - 1 : -1;
+        code <<= 1;
+    }
+    out->maxcode[0] = -1;
+    out->maxcode[17] = 0x7fffffff;
+    std::memcpy(out->vals, spec.vals, 256);
 }
 
 // What a decoded symbol does, packed for the device (kernels.cu decode_subsequence):

@@ -7,6 +7,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <string>
+#include <vector>
 
 namespace b200jpeg {
 
@@ -15,7 +16,7 @@ constexpr int kMaxBlocksPerMcu = 10;
 constexpr int kLutBits = 11;    // first-level Huffman lookup width
 constexpr int kLut2Size = 256;  // second-level entries (16-bit windows of the codes longer than kLutBits)
 
-enum StreamStatus { kStreamOk = 0, kStreamNotJpeg, kStreamUnsupported, kStreamCorrupt, kStreamMultiScan };
+enum StreamStatus { kStreamOk = 0, kStreamNotJpeg, kStreamUnsupported, kStreamCorrupt, kStreamMultiScan, kStreamProgressive };
 
 struct HuffSpec {
     uint8_t bits[17]; // bits[l] = number of codes of length l (1..16)
@@ -48,6 +49,43 @@ StreamStatus parse_stream(const uint8_t* data, size_t len, StreamHeader* hdr);
 // quantisation / Huffman tables and the restart interval in force when its scan starts, where its entropy-coded data lies.
 // Each scan then decodes like a grayscale image of the component's size; the colour stage reads the three planes.
 StreamStatus parse_multiscan(const uint8_t* data, size_t len, StreamHeader* frame, StreamHeader* scans /* [3] */);
+
+// Progressive streams (SOF2, Huffman, 8 bits): parse_stream answers kStreamProgressive for them and this walk lists the
+// scans (T.81 G.1: spectral selection Ss..Se, successive approximation Ah/Al; jdphuff.c start_pass_phuff_decoder checks).
+// Every scan keeps a copy of the Huffman tables in force at its SOS (they are usually redefined before every scan).
+// `wave` orders the scans of one image for the device: scans of the same wave touch disjoint coefficients (other
+// components or other bands) and may decode concurrently; a scan's wave is one more than the latest wave that wrote
+// any coefficient of its band.  Only complete progressions are taken (every coefficient of every component refined
+// down to its last bit): libjpeg smooths blocks of incomplete ones (jdcoefct.c smoothing_ok), so those stay with
+// the CPU decoders.  The scan-count limit is NVIMGCODEC_MAX_JPEG_SCANS (default 256), as in
+// extensions/libjpeg_turbo/jpeg_handle.cpp:38-75.
+struct ProgScan {
+    int ncomp = 0;               // components in the scan: 1, or all of the frame's (interleaved; DC scans only)
+    int comp[kMaxComp] = {0, 0, 0, 0};   // frame component index of each
+    int table[kMaxComp] = {-1, -1, -1, -1}; // index into ProgStream::tables (-1: none -- DC refinement reads raw bits)
+    int ss = 0, se = 0, ah = 0, al = 0;
+    int restart_interval = 0;    // in MCUs of THIS scan (one block each for a one-component scan)
+    int mcus = 0;                // MCUs of this scan
+    int wb = 0, hb = 0;          // one-component scan: block columns / rows of the component, ceil(size / 8)
+    size_t offset = 0, length = 0; // entropy-coded segment, up to and including the marker that ends it
+    int wave = 0;
+};
+struct ProgStream {
+    std::vector<ProgScan> scans;
+    std::vector<HuffSpec> tables;
+    int n_waves = 0;
+};
+StreamStatus parse_progressive(const uint8_t* data, size_t len, StreamHeader* frame, ProgStream* out);
+
+// Device image of one Huffman table for the progressive scan kernel (progressive.cuh): plain symbols, not the packed
+// actions of the sequential kernels -- a progressive symbol's meaning depends on the scan type.
+struct alignas(16) ProgHuffDev {
+    uint16_t lut[512];   // 9-bit window -> (code length << 8) | symbol; 0 = longer than 9 bits or unassigned
+    int32_t maxcode[18]; // largest code of length l (1..16), -1 if none; [17] = sentinel
+    int32_t valoff[18];  // symbol index = valoff[l] + code
+    uint8_t vals[256];
+};
+void build_prog_table(const HuffSpec& spec, ProgHuffDev* out);
 
 // Device-side Huffman table image (one per table; a "set" is DC0, DC1, AC0, AC1).
 struct alignas(16) HuffTableDev {

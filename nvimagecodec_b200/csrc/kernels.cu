@@ -1429,6 +1429,7 @@ __device__ __forceinline__ uint32_t range_limit(int32_t x)
 }
 
 #include "pixels.cuh"
+#include "progressive.cuh"
 
 __global__ void __launch_bounds__(128, 6) idct_kernel(BatchDev bd, int redo_only)
 {
@@ -1482,45 +1483,39 @@ __global__ void __launch_bounds__(128, 6) idct_kernel(BatchDev bd, int redo_only
     }
     const uint32_t mx = bx >> lh, my = by >> lv;
     const uint32_t bim = im.blk_first[c] + ((by - (my << lv)) << lh) + (bx - (mx << lh));
-    const int16_t* src = bd.coef + im.coef_off + (size_t(my * im.mcus_x + mx) * im.bpm + bim) * 64;
+    const size_t blk_in_img = size_t(my * im.mcus_x + mx) * im.bpm + bim;
+    // dense blocks: the sequential path's arena, or the progressive one (whose images never have an entry stream)
+    const int16_t* dense = im.prog ? bd.pcoef + im.pcoef_off : bd.coef + im.coef_off;
+    const size_t blk = im.coef_off / 64 + blk_in_img;
+    const uint32_t rec = __ldg(bd.blkrec + blk);
+    uint32_t w[32]; // the block as packed zig-zag pairs (DC slot unused: the DC value is in the record)
+    if (im.prog) {
+        px_fetch_block<2>(dense, rec, blk_in_img, w);
+    } else if (bd.sym_mode) {
+        SymSource S;
+        S.sym = bd.sym + im.sym_off;
+        S.chunks = bd.sym_chunks;
+        S.shift = bd.sub_shift;
+        S.n_sub = bd.state[img].n_sub;
+        static_assert(kScatterStride == 128u * 4u, "the entries carry offsets into this column layout");
+        sym_fetch_block(S, rec, __ldg(bd.blkpos + blk), smem_addr(s_scatter) + threadIdx.x * 4u, w);
+    } else {
+        px_fetch_block<2>(bd.coef, rec, blk, w);
+    }
     if (q8) {
-        const size_t blk = im.coef_off / 64 + (size_t(my * im.mcus_x + mx) * im.bpm + bim);
-        const uint32_t rec = __ldg(bd.blkrec + blk);
-        uint32_t w[32];
-        if (bd.sym_mode) {
-            SymSource S;
-            S.sym = bd.sym + im.sym_off;
-            S.chunks = bd.sym_chunks;
-            S.shift = bd.sub_shift;
-            S.n_sub = bd.state[img].n_sub;
-            static_assert(kScatterStride == 128u * 4u, "the entries carry offsets into this column layout");
-            sym_fetch_block(S, rec, __ldg(bd.blkpos + blk), smem_addr(s_scatter) + threadIdx.x * 4u, w);
-        } else {
-            px_fetch_block<2>(bd.coef, rec, blk, w);
-        }
         uint8_t* dst8 = bd.planes + im.plane_off[c] + size_t(by) * 8 * (bw * 8) + bx * 8;
         const uint32_t pitch = bw * 8;
         px_idct_rows<0>(w, int32_t(rec) >> 16, s_qz[c], [](int) {}, [&](int y, uint32_t lo, uint32_t hi) {
             *reinterpret_cast<uint2*>(dst8 + size_t(y) * pitch) = make_uint2(lo, hi);
         });
     } else {
-    // 64 coefficients, zig-zag order
+    // 16-bit quantisers (extended-sequential / progressive streams only): 64 coefficients, zig-zag order
     int32_t zz[64];
     {
-        const uint4* s4 = reinterpret_cast<const uint4*>(src);
-        const uint32_t rec = __ldg(bd.blkrec + im.coef_off / 64 + (size_t(my * im.mcus_x + mx) * im.bpm + bim));
-        const uint32_t mask = rec & 0xFFu; // which groups K3 wrote; the DC value (K3b) sits in the upper half
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-            if ((mask >> i) & 1u) // groups K3 did not write are all zero
-                v = __ldg(s4 + i);
-            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                zz[i * 8 + 2 * j] = int32_t(int16_t(w[j] & 0xFFFFu));
-                zz[i * 8 + 2 * j + 1] = int32_t(int16_t(w[j] >> 16));
-            }
+        for (int j = 0; j < 32; ++j) {
+            zz[2 * j] = int32_t(int16_t(w[j] & 0xFFFFu));
+            zz[2 * j + 1] = int32_t(int16_t(w[j] >> 16));
         }
         zz[0] = int32_t(rec) >> 16;
     }
@@ -1903,6 +1898,22 @@ int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s)
         return 0;
     idct_kernel<<<b.n_idct_cta, 128, 0, s>>>(b, redo_only ? 1 : 0);
     return 1;
+}
+
+int launch_progressive(const BatchDev& b, const uint32_t* wave_off, int n_waves, cudaStream_t s)
+{
+    if (b.n_prog_img == 0)
+        return 0;
+    int n = 0;
+    for (int w = 0; w < n_waves; ++w) {
+        const uint32_t c0 = wave_off[w], c1 = wave_off[w + 1];
+        if (c1 > c0) {
+            prog_scan_kernel<<<c1 - c0, 32, 0, s>>>(b, c0);
+            ++n;
+        }
+    }
+    prog_record_kernel<<<dim3((b.prog_max_blocks * 8u + 255u) / 256u, unsigned(b.n_prog_img)), 256, 0, s>>>(b);
+    return n + 1;
 }
 
 int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s)

@@ -52,6 +52,7 @@ struct ImageDev {
     uint64_t cmp_off;   // bytes into the unstuffed arena, 16-aligned
     uint64_t coef_off;  // int16 elements into the coefficient arena (block index * 64; also locates the block records)
     uint64_t sym_off;   // 16-byte chunks into the entry-stream arena (entry-stream form of K3)
+    uint64_t pcoef_off; // progressive images: int16 elements into BatchDev::pcoef (dense zig-zag blocks, MCU order)
     uint64_t plane_off[3]; // bytes into the plane arena
     uint32_t raw_len;
     uint32_t tile_off, n_tiles;     // K0 tiles
@@ -96,6 +97,8 @@ struct ImageDev {
     uint8_t color_unit_rows; // output rows per K4b thread (the chroma vertical factor on the fast paths)
     uint8_t orient;          // EXIF orientation code applied when storing (0/1 = none; 5..8 transpose)
     uint8_t q8;              // 1: every quantiser of the image fits 8 bits (all baseline tables do)
+    uint8_t prog;            // 1: progressive stream -- its scans (device images of their own, K0 only) were decoded into
+                             //    BatchDev::pcoef by the progressive kernels; the IDCT stage reads the dense blocks from there
     uint8_t multi;           // 1: the components came in three scans and were decoded as one-component images of their own;
                              //    BatchDev::gate names them (their state flags become this image's before K4b)
 };
@@ -105,6 +108,18 @@ struct ImageState {
     uint32_t n_rst;    // RST markers found
     uint32_t n_sub;    // ceil(cmp_len*8 / sub_bits)
     uint32_t flags;
+};
+
+// One scan of a progressive image (progressive.cuh).  Its entropy-coded segment went through K0 as a device image of its
+// own (`child`: unstuffed words, restart boundaries); `parent` holds the geometry and the coefficient blocks.  A chain is
+// one restart interval of the scan (the whole scan without restarts): one warp decodes it serially.
+struct ProgScanDev {
+    uint32_t parent, child;
+    uint32_t chain_off, n_chain;
+    uint32_t table[4];      // BatchDev::prog_huff index per scan component
+    uint32_t ri, n_mcu;     // restart interval and size of the scan in ITS MCUs
+    uint16_t wb, hb;        // one-component scan: the component's block columns / rows
+    uint8_t ncomp, comp[4], ss, se, ah, al;
 };
 
 // All device pointers of one prepared batch.
@@ -149,6 +164,14 @@ struct BatchDev {
     const uint32_t* px_cta_img;   // fused pixel kernel: tile (one per warp) -> image
     int n_px_task;                // tiles
     uint32_t px_smem;             // shared memory per warp of the fused pixel kernel: the largest tile of the batch
+    // progressive images
+    const ProgScanDev* prog_scan;
+    const uint32_t* prog_chain;   // chain -> scan
+    const ProgHuffDev* prog_huff;
+    const uint32_t* prog_img;     // the progressive images of the batch (for the record pass)
+    int16_t* pcoef;               // their coefficient blocks: 64 int16 in zig-zag order per block, MCU order, DC included
+    int n_prog_img;
+    uint32_t prog_max_blocks;     // largest total_blocks among them
     const uint32_t* gate;         // three image indices per image, see ImageDev::multi
     int n_tiles, n_seq, n_wseq, n_sub, n_dc_cta, n_idct_cta, n_color_cta;
     int n_multi;            // images with ImageDev::multi set
@@ -164,6 +187,8 @@ int launch_verify_scan(const BatchDev& b, bool fix_mode, cudaStream_t s); // K2
 int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s);  // K3 (dense groups or entry stream, by b.sym_mode)
 uint32_t sym_chunks_for(uint32_t sub_bits); // chunks of eight entries a subsequence of that many bits can need at most
 int launch_dc_scan(const BatchDev& b, bool redo_only, cudaStream_t s); // K3b
+// Progressive scans: one launch per wave (chains [wave_off[w], wave_off[w + 1])), then the per-block records for the IDCT stage
+int launch_progressive(const BatchDev& b, const uint32_t* wave_off, int n_waves, cudaStream_t s);
 int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s);   // K4a
 int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s);  // K4b
 int launch_pixels(const BatchDev& b, bool redo_only, cudaStream_t s); // K4 fused (IDCT + upsampling + colour)

@@ -83,6 +83,20 @@ def main():
     add("c1_padlock_420_opt", corpus.encode(rgb, 75, "420", optimize=True), "padlock re-encoded 4:2:0 q75, optimised Huffman tables")
     add("c1_padlock_gray", corpus.encode(rgb, 90, gray=True), "padlock re-encoded as grayscale q90")
 
+    # ---- set P: progressive (SOF2) streams.  The reference pins progressive decode with
+    # test/extensions/libjpeg_turbo_ext_decoder_test.cpp:115-130 on progressive-subsampled-imagenet-n02089973_1957.jpg (a git-LFS
+    # stub here); its decoded golden is re-encoded as a progressive stream, like set A.
+    prog = np.asarray(Image.open(os.path.join(REF, "progressive-subsampled-imagenet-n02089973_1957.ppm")).convert("RGB"))
+    add("p_imagenet_1957_420", corpus.encode(prog, 90, "420", progressive=True), "resources/ref/jpeg/progressive-...1957.ppm re-encoded progressive 4:2:0 q90")
+    add("p_imagenet_1957_444_rst", corpus.encode(prog, 80, "444", rst_interval=5, progressive=True), "the same, progressive 4:4:4 q80, RST every 5 MCUs")
+    add("p_padlock_422", corpus.encode(rgb, 85, "422", progressive=True), "padlock re-encoded progressive 4:2:2 q85")
+    add("p_padlock_gray", corpus.encode(rgb, 90, gray=True, progressive=True), "padlock re-encoded progressive grayscale q90")
+    for (h, w) in [(8, 8), (17, 9), (37, 53)]:
+        img = corpus.synth(h, w, 31 * h + w)
+        for samp in ["444", "420", "440"]:
+            add("p_syn_%dx%d_%s" % (h, w, samp), corpus.encode(img, 75, samp, rst_interval=(2 if samp == "440" else 0), progressive=True),
+                "synthetic progressive")
+
     # ---- set B: synthetic edge cases
     for (h, w) in [(1, 1), (8, 8), (17, 9), (37, 53), (48, 64), (2, 300), (300, 3)]:
         img = corpus.synth(h, w, 31 * h + w)

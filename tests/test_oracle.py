@@ -108,6 +108,27 @@ def test_live_against_pillow_when_available():
         assert np.array_equal(oracle.decode(data, oracle.FMT_I_RGB, fancy=True), ref)
 
 
+def test_progressive_live_against_pillow_when_available():
+    """SOF2 streams (spectral selection + successive approximation, ten scans from libjpeg's simple progression; jdphuff.c)
+    against Pillow's libjpeg-turbo, and the incomplete progression that is left to libjpeg."""
+    PIL = pytest.importorskip("PIL.Image")
+    pytest.importorskip("cv2")
+    from nvimagecodec_b200 import corpus
+
+    rng = np.random.default_rng(7)
+    for i in range(16):
+        h, w = int(rng.integers(1, 260)), int(rng.integers(1, 260))
+        samp = ["444", "422", "420", "440"][i % 4]
+        data = corpus.encode(corpus.synth(h, w, 700 + i), int(rng.integers(25, 100)), samp, int(rng.integers(0, 5)) if i & 1 else 0,
+                             gray=(i % 7 == 6), progressive=True)
+        ref = np.asarray(PIL.open(io.BytesIO(data)).convert("RGB"))
+        assert np.array_equal(oracle.decode(data, oracle.FMT_I_RGB, fancy=True), ref), i
+    cut = data[:data.rfind(b"\xff\xda")] + b"\xff\xd9"
+    with pytest.raises(oracle.OracleError) as ei:
+        oracle.decode(cut)
+    assert ei.value.code == 2
+
+
 def test_live_against_reference_glue_when_built():
     """oracle/_ref/libref_turbo.so = the reference's libjpeg_turbo::Uncompress compiled from its own
     sources (oracle/build_ref.sh); it can switch fancy upsampling off and crop, which Pillow cannot."""

@@ -1,0 +1,108 @@
+"""Progressive (SOF2) streams through the CUDA path (reference: libjpeg-turbo's jdphuff.c behind
+extensions/libjpeg_turbo/jpeg_mem.cpp:154-219, pinned by test/extensions/libjpeg_turbo_ext_decoder_test.cpp:115-130).
+Bar: bit-exact against the oracle (itself pinned against Pillow's libjpeg-turbo in tests/test_oracle.py)."""
+import numpy as np
+import pytest
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dec(decoder_cls):
+    d = decoder_cls(0, options=":fancy_upsampling=1")
+    yield d
+    d.close()
+
+
+def _cases():
+    from nvimagecodec_b200 import corpus
+
+    out = []
+    seed = 100
+    for (h, w) in [(213, 200), (64, 64), (375, 500), (17, 9), (8, 8), (600, 801)]:
+        for sampling in ("420", "444", "422", "440"):
+            for rst in (0, 3):
+                seed += 1
+                out.append(corpus.encode(corpus.synth(h, w, seed), 60 + (seed * 7) % 38, sampling, rst_interval=rst, progressive=True))
+        out.append(corpus.encode(corpus.synth(h, w, seed), 85, gray=True, progressive=True))
+    return out
+
+
+def test_progressive_bit_exact(dec):
+    from nvimagecodec_b200 import _lib
+
+    srcs = _cases()
+    outs = dec.decode(srcs, "I_RGB")
+    assert dec.last_status == [_lib.OK] * len(srcs)
+    for i, (s, o) in enumerate(zip(srcs, outs)):
+        assert np.array_equal(o.cpu().numpy(), oracle.decode(s, oracle.FMT_I_RGB, fancy=True)), i
+    outs = dec.decode(srcs, "I_Y")
+    for i, (s, o) in enumerate(zip(srcs, outs)):
+        assert np.array_equal(o.cpu().numpy(), oracle.decode(s, oracle.FMT_Y, fancy=True)), i
+
+
+def test_progressive_coefficients_match_oracle(dec):
+    from nvimagecodec_b200 import corpus
+
+    srcs = [corpus.encode(corpus.synth(120, 200, 11), 92, "420", rst_interval=5, progressive=True),
+            corpus.encode(corpus.synth(96, 80, 12), 60, "444", progressive=True),
+            corpus.encode(corpus.synth(70, 70, 13), 85, gray=True, progressive=True),
+            corpus.encode(corpus.synth(1080, 1920, 14), 90, "420", progressive=True)]
+    dec.decode(srcs, "I_RGB")
+    for i, d in enumerate(srcs):
+        ref = oracle.coefficients(d)
+        got = dec.coefficients(i, ref.size).reshape(ref.shape)
+        assert np.array_equal(got, ref), i
+
+
+def test_progressive_mixed_with_sequential_roi_and_formats(dec):
+    """Progressive and baseline streams in one batch, regions of interest, BGR / planar output."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    srcs, rois = [], []
+    for k in range(24):
+        h, w = 90 + 37 * k, 120 + 53 * k
+        srcs.append(corpus.encode(corpus.synth(h, w, 300 + k), 70 + k, ("420", "444", "422")[k % 3], rst_interval=(0, 7)[k % 2],
+                                  progressive=(k % 2 == 0)))
+        rois.append((h // 5, w // 7, h - h // 6, w - w // 9) if k % 3 else None)
+    for fmt, ofmt in (("I_BGR", oracle.FMT_I_BGR), ("P_RGB", oracle.FMT_P_RGB)):
+        outs = dec.decode(srcs, fmt, rois)
+        assert dec.last_status == [_lib.OK] * len(srcs)
+        for i, (s, o) in enumerate(zip(srcs, outs)):
+            assert np.array_equal(o.cpu().numpy(), oracle.decode(s, ofmt, fancy=True, roi=rois[i])), (fmt, i)
+
+
+def test_progressive_damaged_scans_are_reported_and_neighbours_stay_exact(dec):
+    from nvimagecodec_b200 import _lib, corpus
+
+    good = corpus.encode(corpus.synth(200, 300, 501), 88, "420", progressive=True)
+    base = corpus.encode(corpus.synth(160, 240, 502), 88, "420")
+    rng = np.random.default_rng(5)
+    srcs = [good, base]
+    for k in range(40):
+        b = bytearray(good)
+        for _ in range(1 + k % 4):
+            pos = int(rng.integers(len(b) // 3, len(b) - 2))
+            b[pos] = int(rng.integers(0, 255))
+        srcs.append(bytes(b[:len(b) - (k % 5) * 37]) if k % 5 else bytes(b))
+    outs = dec.decode(srcs, "I_RGB")
+    assert dec.last_status[0] == _lib.OK and dec.last_status[1] == _lib.OK
+    assert np.array_equal(outs[0].cpu().numpy(), oracle.decode(good))
+    assert np.array_equal(outs[1].cpu().numpy(), oracle.decode(base))
+    # and the decoder is usable afterwards
+    again = dec.decode([good], "I_RGB")
+    assert np.array_equal(again[0].cpu().numpy(), oracle.decode(good))
+
+
+def test_progressive_can_be_switched_off(decoder_cls):
+    from nvimagecodec_b200 import _lib, corpus
+
+    d = decoder_cls(0, options=":progressive=0")
+    try:
+        s = corpus.encode(corpus.synth(64, 64, 9), 80, "420", progressive=True)
+        d.decode([s], "I_RGB")
+        assert d.last_status == [_lib.ERR_UNSUPPORTED]
+    finally:
+        d.close()
