@@ -1589,6 +1589,7 @@ int Decoder::scan_segment(const void* dev_raw, size_t length, uint32_t expected_
     im.n_tiles = n_tiles;
     im.n_rst_expected = expected_rst;
     im.n_bnd_cap = bnd_cap;
+    im.n_sub_max = 0xFFFFFFFFu; // (no subsequence arrays here: the count is only reported)
     std::memcpy(hp, &im, sizeof(im));
     std::memset(hp + off_tile, 0, 4ull * n_tiles);
     uint8_t* dp = scan_scratch_.as<uint8_t>();

@@ -223,7 +223,8 @@ __global__ void __launch_bounds__(128) scan_prefix_kernel(BatchDev bd)
         st.cmp_len = carry_k;
         st.n_rst = carry_r;
         st.flags = (carry_r != im.n_rst_expected) ? kFlagBadMarker : 0u;
-        st.n_sub = st.flags ? 0u : (carry_k * 8u + bd.sub_bits - 1u) / bd.sub_bits;
+        // (images without subsequences of their own -- the scans of a progressive stream -- stay out of K1-K3)
+        st.n_sub = (st.flags || im.n_sub_max == 0u) ? 0u : min(im.n_sub_max, (carry_k * 8u + bd.sub_bits - 1u) / bd.sub_bits);
         bd.state[img] = st;
         const uint32_t slot = carry_r < im.n_bnd_cap ? carry_r : im.n_bnd_cap - 1;
         bd.bnd[im.bnd_off + slot] = carry_k; // end of stream closes the last restart interval
@@ -2007,6 +2008,7 @@ __global__ void noalloc_scan_setup_kernel(unsigned char* scratch, NoAllocParams 
         im->n_tiles = p.n_tiles;
         im->n_rst_expected = p.n_rst_expected;
         im->n_bnd_cap = p.n_bnd_cap;
+        im->n_sub_max = 0xFFFFFFFFu; // (no subsequence arrays here: the count is only reported)
     }
 }
 

@@ -39,10 +39,10 @@ __device__ __forceinline__ void pb_seek(PBits& b, uint32_t p)
     b.w2 = pb_word(b, b.base + 2u);
 }
 
-// the 32 bits at the current position
+// the 32 bits at the current position (callers consume at most 32 bits between two peeks: one refill step at most)
 __device__ __forceinline__ uint32_t pb_peek(PBits& b)
 {
-    while ((b.p >> 5) != b.base) { // at most two steps: never more than 32 bits are consumed between two peeks
+    if ((b.p >> 5) != b.base) {
         ++b.base;
         b.w0 = b.w1;
         b.w1 = b.w2;
@@ -87,33 +87,71 @@ __device__ __forceinline__ int32_t pb_extend(uint32_t r, uint32_t s) // T.81 F.2
     return s == 0u ? 0 : (r >= (1u << (s - 1u)) ? int32_t(r) : int32_t(r) - int32_t((1u << s) - 1u));
 }
 
-// Block m of a one-component scan (raster order over the component's own wb x hb blocks) -> its place in the image's
-// MCU-order block array.
+// Blocks of a one-component scan run in raster order over the component's own wb x hb blocks; PMap turns (bx, by) into
+// the block's place in the image's MCU-order array.  Sampling factors are 1, 2 or 4: shifts, no divisions in the loops.
 struct PMap {
-    uint32_t wb, h, v, mcus_x, bpm, first;
+    uint32_t wb, lh, lv, mcus_x, bpm, first;
+    uint32_t bx, by;
 };
-__device__ __forceinline__ uint32_t pmap_block(const PMap& g, uint32_t m)
+__device__ __forceinline__ void pmap_seek(PMap& g, uint32_t m)
 {
-    const uint32_t by = m / g.wb, bx = m - by * g.wb;
-    const uint32_t my = by / g.v, mx = bx / g.h;
-    return (my * g.mcus_x + mx) * g.bpm + g.first + (by - my * g.v) * g.h + (bx - mx * g.h);
+    g.by = m / g.wb;
+    g.bx = m - g.by * g.wb;
+}
+__device__ __forceinline__ void pmap_advance(PMap& g, uint32_t n)
+{
+    g.bx += n;
+    if (g.bx >= g.wb) {
+        if (g.bx < 2u * g.wb) {
+            g.bx -= g.wb;
+            ++g.by;
+        } else {
+            const uint32_t rows = g.bx / g.wb;
+            g.by += rows;
+            g.bx -= rows * g.wb;
+        }
+    }
+}
+__device__ __forceinline__ uint32_t pmap_index(const PMap& g, uint32_t bx, uint32_t by)
+{
+    const uint32_t mx = bx >> g.lh, my = by >> g.lv;
+    return (my * g.mcus_x + mx) * g.bpm + g.first + ((by - (my << g.lv)) << g.lh) + (bx - (mx << g.lh));
+}
+__device__ __forceinline__ uint32_t pmap_block(const PMap& g) { return pmap_index(g, g.bx, g.by); }
+__device__ __forceinline__ uint32_t pmap_block_at(const PMap& g, uint32_t m) // any block (one division: not for inner loops)
+{
+    const uint32_t by = m / g.wb;
+    return pmap_index(g, m - by * g.wb, by);
 }
 
 // ---- the four scan types.  Each decodes MCUs [m0, m1) of its scan; everything is warp-uniform except the stores.
 
+// Everything the scan loops read is held in registers (PScan, PMap): the descriptors live in global memory, and a loop that
+// stores coefficients would otherwise re-read them after every store.
+struct PScan {
+    int ncomp, ss, se, al;
+    int nb[4];   // interleaved scan: blocks per MCU of each scan component
+    uint32_t bpm;
+};
+
 // DC, first pass (decode_mcu_DC_first): one Huffman symbol + magnitude bits per block, DPCM per component, value << Al.
-__device__ __forceinline__ void prog_dc_first(PBits& b, const ProgHuffDev* tab, const ProgScanDev& sc, const ImageDev& im, const PMap& g,
-    int16_t* coef, uint32_t m0, uint32_t m1, int lane, uint32_t& err)
+__device__ __forceinline__ void prog_dc_first(PBits& b, const ProgHuffDev* tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
+    int lane, uint32_t& err)
 {
     int32_t pred[4] = {0, 0, 0, 0};
+    pmap_seek(g, m0);
 #pragma unroll 1
     for (uint32_t m = m0; m < m1; ++m) {
-        uint32_t blk = sc.ncomp == 1 ? pmap_block(g, m) : m * im.bpm;
+        uint32_t blk = m * sc.bpm;
+        if (sc.ncomp == 1) {
+            blk = pmap_block(g);
+            pmap_advance(g, 1u);
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             if (i >= sc.ncomp)
                 break;
-            const int nb = sc.ncomp == 1 ? 1 : im.h[sc.comp[i]] * im.v[sc.comp[i]];
+            const int nb = sc.ncomp == 1 ? 1 : sc.nb[i];
 #pragma unroll 1
             for (int j = 0; j < nb; ++j, ++blk) {
                 const uint32_t s = pb_symbol(b, tab[i], err);
@@ -128,10 +166,9 @@ __device__ __forceinline__ void prog_dc_first(PBits& b, const ProgHuffDev* tab, 
 }
 
 // DC, refinement (decode_mcu_DC_refine): one raw bit per block; 32 blocks per step, one per lane.
-__device__ __forceinline__ void prog_dc_refine(PBits& b, const ProgScanDev& sc, const ImageDev& im, const PMap& g, int16_t* coef, uint32_t m0,
-    uint32_t m1, int lane)
+__device__ __forceinline__ void prog_dc_refine(PBits& b, const PScan& sc, const PMap& g, int16_t* coef, uint32_t m0, uint32_t m1, int lane)
 {
-    const uint32_t per = sc.ncomp == 1 ? 1u : im.bpm;
+    const uint32_t per = sc.ncomp == 1 ? 1u : sc.bpm;
     const uint32_t nb = (m1 - m0) * per;
     const int16_t p1 = int16_t(1 << sc.al);
 #pragma unroll 1
@@ -139,7 +176,7 @@ __device__ __forceinline__ void prog_dc_refine(PBits& b, const ProgScanDev& sc, 
         const uint32_t win = pb_peek(b);
         const uint32_t j = j0 + uint32_t(lane);
         if (j < nb && ((win >> (31 - lane)) & 1u)) {
-            const uint32_t blk = sc.ncomp == 1 ? pmap_block(g, m0 + j) : m0 * per + j;
+            const uint32_t blk = sc.ncomp == 1 ? pmap_block_at(g, m0 + j) : m0 * per + j;
             coef[size_t(blk) * 64] |= p1;
         }
         b.p += min(32u, nb - j0);
@@ -147,20 +184,23 @@ __device__ __forceinline__ void prog_dc_refine(PBits& b, const ProgScanDev& sc, 
 }
 
 // AC, first pass (decode_mcu_AC_first): run/size symbols inside the band, end-of-band runs over whole blocks.
-__device__ __forceinline__ void prog_ac_first(PBits& b, const ProgHuffDev& tab, const ProgScanDev& sc, const PMap& g, int16_t* coef, uint32_t m0,
-    uint32_t m1, int lane, uint32_t& err)
+__device__ __forceinline__ void prog_ac_first(PBits& b, const ProgHuffDev& tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
+    int lane, uint32_t& err)
 {
     uint32_t eobrun = 0;
     const uint32_t ss = sc.ss, se = sc.se;
+    pmap_seek(g, m0);
 #pragma unroll 1
     for (uint32_t m = m0; m < m1; ++m) {
         if (eobrun) { // the band of these blocks stays zero
             const uint32_t skip = min(eobrun, m1 - m);
             eobrun -= skip;
             m += skip - 1u;
+            pmap_advance(g, skip);
             continue;
         }
-        int16_t* cb = coef + size_t(pmap_block(g, m)) * 64;
+        int16_t* cb = coef + size_t(pmap_block(g)) * 64;
+        pmap_advance(g, 1u);
         uint32_t k = ss;
 #pragma unroll 1
         while (k <= se) {
@@ -186,64 +226,80 @@ __device__ __forceinline__ void prog_ac_first(PBits& b, const ProgHuffDev& tab, 
     }
 }
 
-// Correction bits (decode_mcu_AC_refine, the `if (*thiscoef != 0)` arm) for the positions of set C, lowest position first:
-// a set bit moves the coefficient one step (1 << Al) away from zero unless its bit Al is already set.  lo / hi: this
-// lane's coefficients at positions lane and lane + 32.
-__device__ __forceinline__ void prog_correct(PBits& b, uint64_t C, int32_t& lo, int32_t& hi, bool& dlo, bool& dhi, int lane, int32_t p1)
+// Correction bits (decode_mcu_AC_refine, the `if (*thiscoef != 0)` arm) of the n non-zero-history coefficients at positions
+// [k, t), lowest position first: a set bit moves the coefficient one step (1 << Al) away from zero unless its bit Al is
+// already set.  lo / hi: this lane's coefficients at positions lane and lane + 32; rlo / rhi: how many non-zero-history
+// coefficients of the band lie before them; before_k: how many lie before k.
+__device__ __forceinline__ void prog_correct(PBits& b, uint32_t n, uint32_t k, uint32_t t, uint32_t before_k, bool mine_lo, bool mine_hi,
+    uint32_t rlo, uint32_t rhi, int32_t& lo, int32_t& hi, bool& dlo, bool& dhi, uint32_t lane, int32_t p1)
 {
-    const uint32_t clo = uint32_t(C), chi = uint32_t(C >> 32);
-    const uint32_t n = uint32_t(__popc(clo) + __popc(chi));
     if (n == 0u)
         return;
     const uint32_t n1 = min(n, 32u);
     const uint32_t v1 = pb_get(b, n1) << (32u - n1); // first bit read = bit 31
     const uint32_t v2 = n > 32u ? pb_get(b, n - 32u) << (64u - n) : 0u;
-    const uint32_t below = (1u << lane) - 1u;
     auto bit_of = [&](uint32_t idx) { return idx < 32u ? (v1 >> (31u - idx)) & 1u : (v2 >> (63u - idx)) & 1u; };
-    if ((clo >> lane) & 1u) {
-        if (bit_of(uint32_t(__popc(clo & below))) && (lo & p1) == 0) {
+    if (mine_lo && lane >= k && lane < t) {
+        if (bit_of(rlo - before_k) && (lo & p1) == 0) {
             lo += lo >= 0 ? p1 : -p1;
             dlo = true;
         }
     }
-    if ((chi >> lane) & 1u) {
-        if (bit_of(uint32_t(__popc(clo) + __popc(chi & below))) && (hi & p1) == 0) {
+    if (mine_hi && lane + 32u >= k && lane + 32u < t) {
+        if (bit_of(rhi - before_k) && (hi & p1) == 0) {
             hi += hi >= 0 ? p1 : -p1;
             dhi = true;
         }
     }
 }
 
-// AC, refinement (decode_mcu_AC_refine).
-__device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab, const ProgScanDev& sc, const PMap& g, int16_t* coef, uint32_t m0,
-    uint32_t m1, int lane, uint32_t& err)
+// AC, refinement (decode_mcu_AC_refine).  A symbol passes r zero-history positions and stops at the next one; the non-zero
+// ones passed on the way take a correction bit each.  The positions of a block's zero-history coefficients are listed
+// once per block (s_q, by the lanes that own them), so "the (j + r)-th zero from the start of the band" is one
+// shared-memory read and the number of correction bits follows from positions and counts alone: the parse never loops
+// over coefficients.
+__device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
+    uint32_t lane, uint32_t& err, uint8_t* s_q)
 {
     uint32_t eobrun = 0;
     const uint32_t ss = sc.ss, se = sc.se;
     const int32_t p1 = 1 << sc.al;
     const uint64_t band = (se == 63u ? ~uint64_t(0) : ((uint64_t(1) << (se + 1u)) - 1u)) & ~((uint64_t(1) << ss) - 1u);
+    const uint32_t bandlo = uint32_t(band), bandhi = uint32_t(band >> 32);
+    const uint32_t below = (1u << lane) - 1u;
     // the block after this one is requested while this one is worked on
-    int16_t* cb = coef + size_t(pmap_block(g, m0)) * 64;
+    pmap_seek(g, m0);
+    int16_t* cb = coef + size_t(pmap_block(g)) * 64;
     int32_t nlo = cb[lane], nhi = cb[lane + 32];
 #pragma unroll 1
     for (uint32_t m = m0; m < m1; ++m) {
         int32_t lo = nlo, hi = nhi;
         int16_t* cur = cb;
         if (m + 1u < m1) {
-            cb = coef + size_t(pmap_block(g, m + 1u)) * 64;
+            pmap_advance(g, 1u);
+            cb = coef + size_t(pmap_block(g)) * 64;
             nlo = cb[lane];
             nhi = cb[lane + 32];
         }
         // history: which coefficients of the band the earlier scans left non-zero
-        const uint64_t nz = (uint64_t(__ballot_sync(0xffffffffu, lo != 0)) | (uint64_t(__ballot_sync(0xffffffffu, hi != 0)) << 32)) & band;
+        const uint32_t nzlo = __ballot_sync(0xffffffffu, lo != 0) & bandlo, nzhi = __ballot_sync(0xffffffffu, hi != 0) & bandhi;
+        const uint32_t zlo = ~nzlo & bandlo, zhi = ~nzhi & bandhi;
+        const uint32_t n_zlo = uint32_t(__popc(zlo)), n_z = n_zlo + uint32_t(__popc(zhi));
+        __syncwarp();
+        if ((zlo >> lane) & 1u)
+            s_q[__popc(zlo & below)] = uint8_t(lane);
+        if ((zhi >> lane) & 1u)
+            s_q[n_zlo + uint32_t(__popc(zhi & below))] = uint8_t(lane + 32u);
+        __syncwarp();
+        const bool mine_lo = (nzlo >> lane) & 1u, mine_hi = (nzhi >> lane) & 1u;
+        const uint32_t rlo = uint32_t(__popc(nzlo & below)), rhi = uint32_t(__popc(nzlo)) + uint32_t(__popc(nzhi & below));
         bool dlo = false, dhi = false; // only what this scan changed is stored: other bands may be in other scans' hands
-        uint32_t k = ss;
+        uint32_t k = ss, j = 0; // j: how many zero-history positions of the band lie before k
         if (eobrun == 0u) {
 #pragma unroll 1
             while (k <= se) {
                 const uint32_t sym = pb_symbol(b, tab, err);
-                uint32_t r = sym >> 4;
-                const uint32_t s = sym & 15u;
+                const uint32_t r = sym >> 4, s = sym & 15u;
                 int32_t newv = 0;
                 if (s) {
                     if (s != 1u)
@@ -253,22 +309,17 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab,
                     eobrun = (1u << r) + pb_get(b, r);
                     break; // the rest of the band: correction bits only, below
                 }
-                // pass r zero-history positions from k on and stop at the next one (position t, se + 1 when the band ends
-                // first); the non-zero ones passed on the way take a correction bit each
-                const uint64_t from_k = band & ~((uint64_t(1) << k) - 1u);
-                uint64_t z = ~nz & from_k;
-#pragma unroll 1
-                for (; r && z; --r)
-                    z &= z - 1u;
-                const uint32_t t = z ? uint32_t(__ffsll((long long)z)) - 1u : se + 1u;
-                const uint64_t upto_t = t >= 64u ? ~uint64_t(0) : (uint64_t(1) << t) - 1u;
-                prog_correct(b, nz & from_k & upto_t, lo, hi, dlo, dhi, lane, p1);
+                const uint32_t idx = j + r;
+                const bool found = idx < n_z;
+                const uint32_t t = found ? uint32_t(s_q[idx]) : se + 1u; // where the symbol stops
+                const uint32_t n = (t - k) - (found ? r : n_z - j);     // positions passed that are not zero-history ones
+                prog_correct(b, n, k, t, (k - ss) - j, mine_lo, mine_hi, rlo, rhi, lo, hi, dlo, dhi, lane, p1);
                 if (newv) {
-                    if (t > se) {
+                    if (!found) {
                         err |= kFlagOverrun;
                         break;
                     }
-                    if (uint32_t(lane) == (t & 31u)) {
+                    if (lane == (t & 31u)) {
                         if (t < 32u) {
                             lo = newv;
                             dlo = true;
@@ -279,11 +330,12 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab,
                     }
                 }
                 k = t + 1u;
+                j = idx + 1u;
             }
         }
         if (eobrun > 0u) {
             if (k <= se)
-                prog_correct(b, nz & ~((uint64_t(1) << k) - 1u), lo, hi, dlo, dhi, lane, p1);
+                prog_correct(b, (se + 1u - k) - (n_z - min(j, n_z)), k, se + 1u, (k - ss) - j, mine_lo, mine_hi, rlo, rhi, lo, hi, dlo, dhi, lane, p1);
             --eobrun;
         }
         if (dlo)
@@ -297,21 +349,25 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab,
 __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd, uint32_t chain0)
 {
     __shared__ ProgHuffDev s_tab[4];
+    __shared__ uint8_t s_q[64];
     const int lane = threadIdx.x;
     const uint32_t chain = chain0 + blockIdx.x;
-    const ProgScanDev& sc = bd.prog_scan[bd.prog_chain[chain]];
-    const ImageDev& im = bd.img[sc.parent];
-    const ImageDev& ch = bd.img[sc.child];
-    const ImageState cst = bd.state[sc.child];
+    const ProgScanDev sd = bd.prog_scan[bd.prog_chain[chain]];
+    const ImageDev& im = bd.img[sd.parent];
+    const ImageDev& ch = bd.img[sd.child];
+    const ImageState cst = bd.state[sd.child];
     if (cst.flags) { // K0 found the restart markers of this scan out of order / miscounted
         if (lane == 0)
-            atomicOr(&bd.state[sc.parent].flags, cst.flags);
+            atomicOr(&bd.state[sd.parent].flags, cst.flags);
         return;
     }
-    const bool huffman = !(sc.ss == 0 && sc.ah != 0);
+    const bool huffman = !(sd.ss == 0 && sd.ah != 0);
     if (huffman) {
-        for (int i = 0; i < sc.ncomp; ++i) {
-            const uint4* src = reinterpret_cast<const uint4*>(bd.prog_huff + sc.table[i]);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (i >= sd.ncomp)
+                break;
+            const uint4* src = reinterpret_cast<const uint4*>(bd.prog_huff + sd.table[i]);
             uint4* dst = reinterpret_cast<uint4*>(&s_tab[i]);
             for (int j = lane; j < int(sizeof(ProgHuffDev) / 16); j += 32)
                 dst[j] = __ldg(src + j);
@@ -319,36 +375,46 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd, uint32_t cha
     }
     __syncwarp();
     // the chain's MCUs and bytes
-    const uint32_t j = chain - sc.chain_off;
-    const uint32_t m0 = sc.ri ? j * sc.ri : 0u, m1 = sc.ri ? min(sc.n_mcu, m0 + sc.ri) : sc.n_mcu;
+    const uint32_t j = chain - sd.chain_off;
+    const uint32_t m0 = sd.ri ? j * sd.ri : 0u, m1 = sd.ri ? min(sd.n_mcu, m0 + sd.ri) : sd.n_mcu;
     const uint32_t byte0 = j ? bd.bnd[ch.bnd_off + j - 1u] : 0u;
-    const uint32_t byte1 = j + 1u < sc.n_chain ? bd.bnd[ch.bnd_off + j] : cst.cmp_len;
+    const uint32_t byte1 = j + 1u < sd.n_chain ? bd.bnd[ch.bnd_off + j] : cst.cmp_len;
     PBits b;
     b.w = bd.cmp + ch.cmp_off / 4;
     b.wmax = (ch.raw_len + 15u) / 4u; // inside what the host reserved for this scan (the words past cmp_len are never trusted)
     pb_seek(b, byte0 * 8u);
     PMap g;
-    const int c0 = sc.comp[0];
-    g.wb = max(1u, uint32_t(sc.wb));
-    g.h = im.h[c0];
-    g.v = im.v[c0];
+    const int c0 = sd.comp[0];
+    g.wb = max(1u, uint32_t(sd.wb));
+    g.lh = 31u - uint32_t(__clz(int(im.h[c0])));
+    g.lv = 31u - uint32_t(__clz(int(im.v[c0])));
+    g.bx = g.by = 0u;
     g.mcus_x = im.mcus_x;
     g.bpm = im.bpm;
     g.first = im.blk_first[c0];
     int16_t* coef = bd.pcoef + im.pcoef_off;
+    PScan sc;
+    sc.ncomp = sd.ncomp;
+    sc.ss = sd.ss;
+    sc.se = sd.se;
+    sc.al = sd.al;
+    sc.bpm = im.bpm;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        sc.nb[i] = i < sd.ncomp ? int(im.h[sd.comp[i] & 3]) * int(im.v[sd.comp[i] & 3]) : 0;
     uint32_t err = 0;
-    if (sc.ss == 0 && sc.ah == 0)
-        prog_dc_first(b, s_tab, sc, im, g, coef, m0, m1, lane, err);
-    else if (sc.ss == 0)
-        prog_dc_refine(b, sc, im, g, coef, m0, m1, lane);
-    else if (sc.ah == 0)
+    if (sd.ss == 0 && sd.ah == 0)
+        prog_dc_first(b, s_tab, sc, g, coef, m0, m1, lane, err);
+    else if (sd.ss == 0)
+        prog_dc_refine(b, sc, g, coef, m0, m1, lane);
+    else if (sd.ah == 0)
         prog_ac_first(b, s_tab[0], sc, g, coef, m0, m1, lane, err);
     else
-        prog_ac_refine(b, s_tab[0], sc, g, coef, m0, m1, lane, err);
+        prog_ac_refine(b, s_tab[0], sc, g, coef, m0, m1, uint32_t(lane), err, s_q);
     if (b.p > byte1 * 8u)
         err |= kFlagOverrun; // the chain read past its restart interval / the end of the scan
     if (err && lane == 0)
-        atomicOr(&bd.state[sc.parent].flags, err);
+        atomicOr(&bd.state[sd.parent].flags, err);
 }
 
 // After the last wave: the per-block records the IDCT stage reads (bits 0-7: which 16-byte groups hold a non-zero AC

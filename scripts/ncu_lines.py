@@ -22,7 +22,7 @@ for l in sass[start:end]:
     m = re.match(r"\s+/\*([0-9a-f]{4,})\*/\s+(.*?);", l)
     if m:
         seq.append((int(m.group(1), 16), cur, m.group(2)))
-raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kern], capture_output=True, text=True).stdout
+raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kern] + os.environ.get("NCU_ARGS", "").split(), capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hi = [i for i, r in enumerate(rows) if "Instructions Executed" in r][0]
 hdr = rows[hi]

@@ -153,6 +153,8 @@ def test_bad_and_unsupported_streams_report_per_image_status(dec_fancy):
     img = corpus.synth(90, 120, 9)
     good = corpus.encode(img, 90, "420", rst_interval=3)
     ok, prog = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_PROGRESSIVE, 1])
+    prog = prog.tobytes()
+    prog = prog[:prog.rfind(b"\xff\xda")] + b"\xff\xd9"  # a progression that stops early: left to libjpeg (it smooths such blocks)
     info = oracle.info(good)
     cut = bytearray(good)
     mid = info["scan_offset"] + (len(good) - info["scan_offset"]) // 2
@@ -164,7 +166,7 @@ def test_bad_and_unsupported_streams_report_per_image_status(dec_fancy):
         if noisy[p] != 0xFF and noisy[p - 1] != 0xFF:
             noisy[p] = (noisy[p] ^ 0x5A) if (noisy[p] ^ 0x5A) != 0xFF else 0x11
     badrst = good.replace(b"\xff\xd1", b"\xff\xd5", 1)
-    srcs = [good, prog.tobytes(), b"garbage", trunc, bytes(noisy), badrst, good]
+    srcs = [good, prog, b"garbage", trunc, bytes(noisy), badrst, good]
     outs = dec_fancy.decode(srcs, "I_RGB")
     st = dec_fancy.last_status
     assert st[0] == _lib.OK and st[6] == _lib.OK

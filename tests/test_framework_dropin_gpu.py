@@ -76,20 +76,45 @@ def test_extension_is_picked_up_and_bit_exact(tmp_path, fancy):
 
 @pytest.mark.skipif(not os.path.exists(DRIVER), reason="reference core not built (oracle/build_ref.sh)")
 def test_unsupported_streams_are_declined_not_crashed(tmp_path):
-    """A progressive stream must be refused in canDecode (there is no fallback decoder loaded here,
-    so the framework reports a non-success status) while the rest of the batch decodes."""
+    """A stream the kernels do not take (here: progressive decoding switched off, and a 4-component stream) must be refused in
+    canDecode (there is no fallback decoder loaded here, so the framework reports a non-success status) while the rest of
+    the batch decodes."""
     cv2 = pytest.importorskip("cv2")
+    import io
+    from PIL import Image
     from nvimagecodec_b200 import corpus
 
     img = corpus.synth(64, 96, 4)
     ok, prog = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_PROGRESSIVE, 1])
+    buf = io.BytesIO()
+    Image.fromarray(np.dstack([img, img[..., 0]])).convert("CMYK").save(buf, format="JPEG")
     good = corpus.encode(img, 90, "420")
     status, raws, log = _run(tmp_path, [(good, "I_RGB", None, "device"), (prog.tobytes(), "I_RGB", None, "device"),
-                                        (good, "I_RGB", None, "device")], "")
+                                        (good, "I_RGB", None, "device"), (buf.getvalue(), "I_RGB", None, "device")], ":progressive=0")
     assert status[0][0] == 1 and status[2][0] == 1
-    assert status[1][0] != 1
+    assert status[1][0] != 1 and status[3][0] != 1
     ref = oracle.decode(good, oracle.FMT_I_RGB, fancy=True)
     assert np.array_equal(raws[0], ref.reshape(-1)) and np.array_equal(raws[2], ref.reshape(-1))
+
+
+@pytest.mark.skipif(not os.path.exists(DRIVER), reason="reference core not built (oracle/build_ref.sh)")
+def test_progressive_streams_through_the_framework(tmp_path):
+    """SOF2 streams are taken by the extension (the reference's parser reports NVIMGCODEC_JPEG_ENCODING_PROGRESSIVE_DCT_HUFFMAN)
+    and decode bit-exactly next to baseline ones; test/extensions/libjpeg_turbo_ext_decoder_test.cpp:115-130 is the
+    reference's own progressive case."""
+    from nvimagecodec_b200 import corpus
+
+    entries = []
+    for k, (h, w, samp, rst) in enumerate([(213, 200, "420", 0), (96, 128, "444", 3), (301, 77, "422", 0)]):
+        entries.append((corpus.encode(corpus.synth(h, w, 880 + k), 88, samp, rst_interval=rst, progressive=True),
+                        ["I_RGB", "I_BGR", "I_Y"][k], (11, 9, h - 20, w - 13) if k == 0 else None, ["device", "host", "device"][k]))
+    entries.append((corpus.encode(corpus.synth(90, 60, 78), 90, gray=True, progressive=True), "I_RGB", None, "device"))
+    entries.append((corpus.encode(corpus.synth(120, 160, 79), 90, "420"), "I_RGB", None, "device"))
+    status, raws, log = _run(tmp_path, entries, ":fancy_upsampling=1")
+    for (data, fmt, roi, where), st, raw in zip(entries, status, raws):
+        assert st[0] == 1, (st, log[-2000:])
+        ref = oracle.decode(data, OFMT[fmt], fancy=True, roi=roi)
+        assert np.array_equal(raw, ref.reshape(-1))
 
 
 @pytest.mark.skipif(not os.path.exists(DRIVER), reason="reference core not built (oracle/build_ref.sh)")
