@@ -513,10 +513,9 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     }
     int children_ok = 0; // children of the multi-scan stream under way that made it into the batch
     std::vector<ProgScanDev> prog_scans;
-    std::vector<int> prog_scan_wave;
     std::vector<ProgHuffDev> prog_tables;
     std::vector<uint32_t> prog_imgs;
-    int prog_waves = 0;
+    std::vector<uint32_t> prog_chain_scan; // chain -> scan, image by image, scans in file order (predecessors first)
     uint32_t prog_max_blocks = 0;
     size_t pcoef_elems = 0;
     std::vector<size_t> scan_offs; // per device image: where its entropy-coded bytes start in the input
@@ -875,10 +874,31 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 prog_tables.emplace_back();
                 build_prog_table(hs, &prog_tables.back());
             }
+            int last_scan[2][kMaxComp]; // per class (DC / AC) and component: the scan that wrote it last
+            for (int cls = 0; cls < 2; ++cls)
+                for (int c = 0; c < kMaxComp; ++c)
+                    last_scan[cls][c] = -1;
             for (size_t sidx = 0; sidx < pg.scans.size(); ++sidx) {
                 const ProgScan& ps = pg.scans[sidx];
                 ProgScanDev sd;
                 std::memset(&sd, 0, sizeof(sd));
+                const int cls = ps.ss ? 1 : 0;
+                for (int k = 0; k < ps.ncomp; ++k) {
+                    const int before = last_scan[cls][ps.comp[k]];
+                    bool known = before < 0;
+                    for (int q = 0; q < sd.n_pred; ++q)
+                        known = known || sd.pred[q] == uint32_t(before);
+                    if (!known)
+                        sd.pred[sd.n_pred++] = uint32_t(before);
+                    last_scan[cls][ps.comp[k]] = int(prog_scans.size());
+                }
+                if (sd.n_pred == 1) {
+                    const ProgScanDev& pd = prog_scans[sd.pred[0]];
+                    bool same = pd.ncomp == ps.ncomp && pd.ri == uint32_t(ps.restart_interval) && pd.n_mcu == uint32_t(ps.mcus);
+                    for (int k = 0; same && k < ps.ncomp; ++k)
+                        same = pd.comp[k] == ps.comp[k];
+                    sd.pred_fine = same ? 1 : 0;
+                }
                 sd.parent = self;
                 sd.child = self - uint32_t(pg.scans.size()) + uint32_t(sidx);
                 sd.ri = uint32_t(ps.restart_interval);
@@ -895,9 +915,9 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 sd.se = uint8_t(ps.se);
                 sd.ah = uint8_t(ps.ah);
                 sd.al = uint8_t(ps.al);
+                sd.chain_off = uint32_t(prog_chain_scan.size());
+                prog_chain_scan.insert(prog_chain_scan.end(), sd.n_chain, uint32_t(prog_scans.size()));
                 prog_scans.push_back(sd);
-                prog_scan_wave.push_back(ps.wave);
-                prog_waves = std::max(prog_waves, ps.wave + 1);
             }
             prog_imgs.push_back(self);
             prog_max_blocks = std::max(prog_max_blocks, im.total_blocks);
@@ -909,19 +929,6 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
         imgs_.push_back(im);
         host_outs_.push_back(ho);
     }
-    // chains of the progressive scans, wave by wave (a scan's chains are contiguous: chain - chain_off = restart interval)
-    std::vector<uint32_t> prog_chain_scan;
-    prog_wave_off_.assign(size_t(prog_waves) + 1, 0u);
-    for (int w = 0; w < prog_waves; ++w) {
-        prog_wave_off_[size_t(w)] = uint32_t(prog_chain_scan.size());
-        for (size_t k = 0; k < prog_scans.size(); ++k) {
-            if (prog_scan_wave[k] != w)
-                continue;
-            prog_scans[k].chain_off = uint32_t(prog_chain_scan.size());
-            prog_chain_scan.insert(prog_chain_scan.end(), prog_scans[k].n_chain, uint32_t(k));
-        }
-    }
-    prog_wave_off_[size_t(prog_waves)] = uint32_t(prog_chain_scan.size());
     algo_bytes_ = comp_bytes_ + 4 * n_coefs_ + out_bytes_;
     const int nd = int(imgs_.size());
 
@@ -1034,6 +1041,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     so = align_up(so + 4ull * (coef_elems / 64), 256);
     const size_t so_pos = so;
     so = align_up(so + (bd_.sym_mode ? 4ull * (coef_elems / 64) : 0ull), 256);
+    const size_t so_prog = so;
+    so = align_up(so + 4ull * prog_chain_scan.size(), 256);
 
     // the coefficients live either as dense 16-byte groups (coef_) or as the entry stream (sym_), never both
     coef_bytes_ = bd_.sym_mode ? 0 : coef_elems * sizeof(int16_t);
@@ -1128,6 +1137,8 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     bd_.prog_img = reinterpret_cast<const uint32_t*>(dv + off_pimg);
     bd_.pcoef = pcoef_.as<int16_t>();
     bd_.n_prog_img = int(prog_imgs.size());
+    bd_.n_prog_chain = int(prog_chain_scan.size());
+    bd_.prog_progress = reinterpret_cast<uint32_t*>(scratch_.as<uint8_t>() + so_prog);
     bd_.prog_max_blocks = prog_max_blocks;
     bd_.raw = dv + off_raw;
     bd_.state = reinterpret_cast<ImageState*>(sc + so_state);
@@ -1293,7 +1304,7 @@ int Decoder::execute(cudaStream_t stream)
     launches_ += launch_dc_scan(bd_, false, stream);
     if (bd_.n_prog_img) { // progressive images: their scans accumulate into zeroed blocks, wave by wave
         cudaMemsetAsync(bd_.pcoef, 0, pcoef_bytes_, stream);
-        launches_ += launch_progressive(bd_, prog_wave_off_.data(), int(prog_wave_off_.size()) - 1, stream);
+        launches_ += launch_progressive(bd_, stream);
     }
     // Everything a status depends on is known once the entropy stage is through (the pixel kernels only read the
     // flags).  The read-back goes over a side stream so that it neither waits for the pixel kernels nor holds them up;

@@ -173,7 +173,6 @@ class Decoder {
 
     // device memory
     DeviceBuffer upload_, scratch_, cmp_, coef_, sym_, pcoef_, planes_, bounce_, scan_scratch_;
-    std::vector<uint32_t> prog_wave_off_; // progressive chains of the batch, by wave: [w] .. [w + 1)
     size_t pcoef_bytes_ = 0;
     PinnedBuffer upload_host_, state_host_, scan_host_;
     size_t device_bytes_ = 0;

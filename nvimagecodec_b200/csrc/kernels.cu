@@ -1901,20 +1901,14 @@ int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s)
     return 1;
 }
 
-int launch_progressive(const BatchDev& b, const uint32_t* wave_off, int n_waves, cudaStream_t s)
+int launch_progressive(const BatchDev& b, cudaStream_t s)
 {
-    if (b.n_prog_img == 0)
+    if (b.n_prog_img == 0 || b.n_prog_chain == 0)
         return 0;
-    int n = 0;
-    for (int w = 0; w < n_waves; ++w) {
-        const uint32_t c0 = wave_off[w], c1 = wave_off[w + 1];
-        if (c1 > c0) {
-            prog_scan_kernel<<<c1 - c0, 32, 0, s>>>(b, c0);
-            ++n;
-        }
-    }
+    cudaMemsetAsync(b.prog_progress, 0, 4ull * size_t(b.n_prog_chain), s);
+    prog_scan_kernel<<<b.n_prog_chain, 32, 0, s>>>(b);
     prog_record_kernel<<<dim3((b.prog_max_blocks * 8u + 255u) / 256u, unsigned(b.n_prog_img)), 256, 0, s>>>(b);
-    return n + 1;
+    return 2;
 }
 
 int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s)

@@ -117,6 +117,9 @@ struct ProgScanDev {
     uint32_t parent, child;
     uint32_t chain_off, n_chain;
     uint32_t table[4];      // BatchDev::prog_huff index per scan component
+    uint32_t pred[4];       // scans (BatchDev::prog_scan indices, all lower than this one's) that last wrote coefficients of the
+    uint8_t n_pred;         //   same components and class (DC / AC) -- this scan follows them block by block when the MCU order
+    uint8_t pred_fine;      //   and restart interval agree (pred_fine: exactly one predecessor), else waits for their end
     uint32_t ri, n_mcu;     // restart interval and size of the scan in ITS MCUs
     uint16_t wb, hb;        // one-component scan: the component's block columns / rows
     uint8_t ncomp, comp[4], ss, se, ah, al;
@@ -167,6 +170,8 @@ struct BatchDev {
     // progressive images
     const ProgScanDev* prog_scan;
     const uint32_t* prog_chain;   // chain -> scan
+    uint32_t* prog_progress;      // per chain: MCUs of its scan finished so far (zeroed before the launch)
+    int n_prog_chain;
     const ProgHuffDev* prog_huff;
     const uint32_t* prog_img;     // the progressive images of the batch (for the record pass)
     int16_t* pcoef;               // their coefficient blocks: 64 int16 in zig-zag order per block, MCU order, DC included
@@ -187,8 +192,8 @@ int launch_verify_scan(const BatchDev& b, bool fix_mode, cudaStream_t s); // K2
 int launch_write(const BatchDev& b, bool redo_only, cudaStream_t s);  // K3 (dense groups or entry stream, by b.sym_mode)
 uint32_t sym_chunks_for(uint32_t sub_bits); // chunks of eight entries a subsequence of that many bits can need at most
 int launch_dc_scan(const BatchDev& b, bool redo_only, cudaStream_t s); // K3b
-// Progressive scans: one launch per wave (chains [wave_off[w], wave_off[w + 1])), then the per-block records for the IDCT stage
-int launch_progressive(const BatchDev& b, const uint32_t* wave_off, int n_waves, cudaStream_t s);
+// Progressive scans: every chain of the batch in one launch, then the per-block records for the IDCT stage
+int launch_progressive(const BatchDev& b, cudaStream_t s);
 int launch_idct(const BatchDev& b, bool redo_only, cudaStream_t s);   // K4a
 int launch_color(const BatchDev& b, bool redo_only, cudaStream_t s);  // K4b
 int launch_pixels(const BatchDev& b, bool redo_only, cudaStream_t s); // K4 fused (IDCT + upsampling + colour)

@@ -12,9 +12,15 @@
 // same parse (same bit window, same state: no divergence, table lookups broadcast from shared memory) and share the
 // per-block work: lane l owns the coefficients at zig-zag positions l and l + 32, so the history mask of a block is two
 // ballots, a run of r zero-history positions is found with bit operations on that mask, and all correction bits of a
-// symbol (or of a whole block inside an end-of-band run) are applied in one step.  Chains of different images, of
-// different scans of one image that touch disjoint coefficients (host: ProgScan::wave), and of different restart
-// intervals run side by side; waves are separate launches on the batch's stream.
+// symbol (or of a whole block inside an end-of-band run) are applied in one step.
+//
+// All chains of a batch run in ONE launch.  A scan that refines what an earlier scan of the same image wrote does not wait
+// for that scan to end: block m of a scan depends on block m of its predecessor only, so every chain publishes how far it
+// has come (BatchDev::prog_progress, release store every few blocks) and a successor chain follows it a few blocks behind
+// (acquire loads; coefficient reads go to L2, `ld.global.cg`, since another SM wrote them in the same launch).  The ten
+// scans of a typical stream thus decode side by side, and an image takes about as long as its longest scan instead of the
+// sum.  Chains are numbered so that a predecessor always has the lower index (image by image, scans in file order): with
+// CTAs dispatched in index order a waiting chain's predecessor is resident or finished, whatever the grid size.
 //
 // The scans' bytes went through K0 like any scan (unstuffed big-endian words, restart boundaries in BatchDev::bnd).
 #pragma once
@@ -124,6 +130,39 @@ __device__ __forceinline__ uint32_t pmap_block_at(const PMap& g, uint32_t m) // 
     return pmap_index(g, m - by * g.wb, by);
 }
 
+// ---- progress of a chain / following a predecessor chain (warp-uniform)
+struct PSync {
+    const uint32_t* pred;  // progress word of the predecessor chain (nullptr: none)
+    uint32_t avail;        // blocks [.., avail) of the predecessor are known to be finished
+    uint32_t* mine;        // progress word of this chain
+    uint32_t published;
+};
+__device__ __forceinline__ void ps_need(PSync& y, uint32_t m_excl) // the predecessor must have finished its MCUs below m_excl
+{
+    if (y.pred == nullptr || y.avail >= m_excl)
+        return;
+    for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(y.pred) : "memory");
+        if (v >= m_excl) {
+            y.avail = v;
+            return;
+        }
+        __nanosleep(200);
+    }
+}
+__device__ __forceinline__ void ps_publish(PSync& y, uint32_t m_done, bool force, uint32_t lane)
+{
+    if (!force && m_done < y.published + 16u)
+        return;
+    y.published = m_done;
+    __syncwarp();
+    __threadfence();
+    if (lane == 0u)
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(y.mine), "r"(m_done) : "memory");
+}
+__device__ __forceinline__ int32_t pc_load(const int16_t* p) { return int32_t(__ldcg(p)); } // coefficients: L2, never this SM's L1
+
 // ---- the four scan types.  Each decodes MCUs [m0, m1) of its scan; everything is warp-uniform except the stores.
 
 // Everything the scan loops read is held in registers (PScan, PMap): the descriptors live in global memory, and a loop that
@@ -136,12 +175,14 @@ struct PScan {
 
 // DC, first pass (decode_mcu_DC_first): one Huffman symbol + magnitude bits per block, DPCM per component, value << Al.
 __device__ __forceinline__ void prog_dc_first(PBits& b, const ProgHuffDev* tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
-    int lane, uint32_t& err)
+    int lane, uint32_t& err, PSync& y)
 {
     int32_t pred[4] = {0, 0, 0, 0};
     pmap_seek(g, m0);
 #pragma unroll 1
     for (uint32_t m = m0; m < m1; ++m) {
+        ps_need(y, m + 1u);
+        ps_publish(y, m, false, uint32_t(lane));
         uint32_t blk = m * sc.bpm;
         if (sc.ncomp == 1) {
             blk = pmap_block(g);
@@ -166,18 +207,21 @@ __device__ __forceinline__ void prog_dc_first(PBits& b, const ProgHuffDev* tab, 
 }
 
 // DC, refinement (decode_mcu_DC_refine): one raw bit per block; 32 blocks per step, one per lane.
-__device__ __forceinline__ void prog_dc_refine(PBits& b, const PScan& sc, const PMap& g, int16_t* coef, uint32_t m0, uint32_t m1, int lane)
+__device__ __forceinline__ void prog_dc_refine(PBits& b, const PScan& sc, const PMap& g, int16_t* coef, uint32_t m0, uint32_t m1, int lane, PSync& y)
 {
     const uint32_t per = sc.ncomp == 1 ? 1u : sc.bpm;
     const uint32_t nb = (m1 - m0) * per;
     const int16_t p1 = int16_t(1 << sc.al);
 #pragma unroll 1
     for (uint32_t j0 = 0; j0 < nb; j0 += 32u) {
+        ps_need(y, min(m1, m0 + (j0 + 32u + per - 1u) / per));
+        ps_publish(y, m0 + j0 / per, false, uint32_t(lane));
         const uint32_t win = pb_peek(b);
         const uint32_t j = j0 + uint32_t(lane);
         if (j < nb && ((win >> (31 - lane)) & 1u)) {
             const uint32_t blk = sc.ncomp == 1 ? pmap_block_at(g, m0 + j) : m0 * per + j;
-            coef[size_t(blk) * 64] |= p1;
+            int16_t* dc = coef + size_t(blk) * 64;
+            *dc = int16_t(pc_load(dc) | p1);
         }
         b.p += min(32u, nb - j0);
     }
@@ -185,20 +229,23 @@ __device__ __forceinline__ void prog_dc_refine(PBits& b, const PScan& sc, const 
 
 // AC, first pass (decode_mcu_AC_first): run/size symbols inside the band, end-of-band runs over whole blocks.
 __device__ __forceinline__ void prog_ac_first(PBits& b, const ProgHuffDev& tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
-    int lane, uint32_t& err)
+    int lane, uint32_t& err, PSync& y)
 {
     uint32_t eobrun = 0;
     const uint32_t ss = sc.ss, se = sc.se;
     pmap_seek(g, m0);
 #pragma unroll 1
     for (uint32_t m = m0; m < m1; ++m) {
+        ps_publish(y, m, false, uint32_t(lane));
         if (eobrun) { // the band of these blocks stays zero
             const uint32_t skip = min(eobrun, m1 - m);
+            ps_need(y, m + skip); // (nothing of them is read, but successors of this scan rely on the order)
             eobrun -= skip;
             m += skip - 1u;
             pmap_advance(g, skip);
             continue;
         }
+        ps_need(y, m + 1u);
         int16_t* cb = coef + size_t(pmap_block(g)) * 64;
         pmap_advance(g, 1u);
         uint32_t k = ss;
@@ -259,7 +306,7 @@ __device__ __forceinline__ void prog_correct(PBits& b, uint32_t n, uint32_t k, u
 // shared-memory read and the number of correction bits follows from positions and counts alone: the parse never loops
 // over coefficients.
 __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
-    uint32_t lane, uint32_t& err, uint8_t* s_q)
+    uint32_t lane, uint32_t& err, uint8_t* s_q, PSync& y)
 {
     uint32_t eobrun = 0;
     const uint32_t ss = sc.ss, se = sc.se;
@@ -269,17 +316,20 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab,
     const uint32_t below = (1u << lane) - 1u;
     // the block after this one is requested while this one is worked on
     pmap_seek(g, m0);
+    ps_need(y, min(m1, m0 + 1u));
     int16_t* cb = coef + size_t(pmap_block(g)) * 64;
-    int32_t nlo = cb[lane], nhi = cb[lane + 32];
+    int32_t nlo = pc_load(cb + lane), nhi = pc_load(cb + lane + 32);
 #pragma unroll 1
     for (uint32_t m = m0; m < m1; ++m) {
         int32_t lo = nlo, hi = nhi;
         int16_t* cur = cb;
+        ps_publish(y, m, false, lane);
         if (m + 1u < m1) {
+            ps_need(y, m + 2u);
             pmap_advance(g, 1u);
             cb = coef + size_t(pmap_block(g)) * 64;
-            nlo = cb[lane];
-            nhi = cb[lane + 32];
+            nlo = pc_load(cb + lane);
+            nhi = pc_load(cb + lane + 32);
         }
         // history: which coefficients of the band the earlier scans left non-zero
         const uint32_t nzlo = __ballot_sync(0xffffffffu, lo != 0) & bandlo, nzhi = __ballot_sync(0xffffffffu, hi != 0) & bandhi;
@@ -346,78 +396,99 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab,
 }
 
 // One warp per chain.
-__global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd, uint32_t chain0)
+__global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
 {
     __shared__ ProgHuffDev s_tab[4];
     __shared__ uint8_t s_q[64];
     const int lane = threadIdx.x;
-    const uint32_t chain = chain0 + blockIdx.x;
+    const uint32_t chain = blockIdx.x;
     const ProgScanDev sd = bd.prog_scan[bd.prog_chain[chain]];
     const ImageDev& im = bd.img[sd.parent];
     const ImageDev& ch = bd.img[sd.child];
     const ImageState cst = bd.state[sd.child];
-    if (cst.flags) { // K0 found the restart markers of this scan out of order / miscounted
-        if (lane == 0)
-            atomicOr(&bd.state[sd.parent].flags, cst.flags);
-        return;
-    }
-    const bool huffman = !(sd.ss == 0 && sd.ah != 0);
-    if (huffman) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            if (i >= sd.ncomp)
-                break;
-            const uint4* src = reinterpret_cast<const uint4*>(bd.prog_huff + sd.table[i]);
-            uint4* dst = reinterpret_cast<uint4*>(&s_tab[i]);
-            for (int j = lane; j < int(sizeof(ProgHuffDev) / 16); j += 32)
-                dst[j] = __ldg(src + j);
-        }
-    }
-    __syncwarp();
-    // the chain's MCUs and bytes
+    // the chain's MCUs
     const uint32_t j = chain - sd.chain_off;
     const uint32_t m0 = sd.ri ? j * sd.ri : 0u, m1 = sd.ri ? min(sd.n_mcu, m0 + sd.ri) : sd.n_mcu;
-    const uint32_t byte0 = j ? bd.bnd[ch.bnd_off + j - 1u] : 0u;
-    const uint32_t byte1 = j + 1u < sd.n_chain ? bd.bnd[ch.bnd_off + j] : cst.cmp_len;
-    PBits b;
-    b.w = bd.cmp + ch.cmp_off / 4;
-    b.wmax = (ch.raw_len + 15u) / 4u; // inside what the host reserved for this scan (the words past cmp_len are never trusted)
-    pb_seek(b, byte0 * 8u);
-    PMap g;
-    const int c0 = sd.comp[0];
-    g.wb = max(1u, uint32_t(sd.wb));
-    g.lh = 31u - uint32_t(__clz(int(im.h[c0])));
-    g.lv = 31u - uint32_t(__clz(int(im.v[c0])));
-    g.bx = g.by = 0u;
-    g.mcus_x = im.mcus_x;
-    g.bpm = im.bpm;
-    g.first = im.blk_first[c0];
-    int16_t* coef = bd.pcoef + im.pcoef_off;
-    PScan sc;
-    sc.ncomp = sd.ncomp;
-    sc.ss = sd.ss;
-    sc.se = sd.se;
-    sc.al = sd.al;
-    sc.bpm = im.bpm;
+    PSync y;
+    y.mine = bd.prog_progress + chain;
+    y.published = m0;
+    y.pred = nullptr;
+    y.avail = 0u;
+    if (sd.n_pred) {
+        if (sd.pred_fine) { // same MCU order and restart interval: chain j follows chain j of the predecessor scan
+            y.pred = bd.prog_progress + bd.prog_scan[sd.pred[0]].chain_off + j;
+        } else {            // otherwise every predecessor scan has to be through
+            for (uint32_t q = 0; q < sd.n_pred; ++q) {
+                const ProgScanDev& ps = bd.prog_scan[sd.pred[q]];
+                for (uint32_t c = 0; c < ps.n_chain; ++c) {
+                    PSync w;
+                    w.pred = bd.prog_progress + ps.chain_off + c;
+                    w.avail = 0u;
+                    ps_need(w, ps.ri ? min(ps.n_mcu, (c + 1u) * ps.ri) : ps.n_mcu);
+                }
+            }
+        }
+    }
+    uint32_t err = cst.flags; // K0 found the restart markers of this scan out of order / miscounted: nothing is decoded
+    if (!err) {
+        const bool huffman = !(sd.ss == 0 && sd.ah != 0);
+        if (huffman) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-        sc.nb[i] = i < sd.ncomp ? int(im.h[sd.comp[i] & 3]) * int(im.v[sd.comp[i] & 3]) : 0;
-    uint32_t err = 0;
-    if (sd.ss == 0 && sd.ah == 0)
-        prog_dc_first(b, s_tab, sc, g, coef, m0, m1, lane, err);
-    else if (sd.ss == 0)
-        prog_dc_refine(b, sc, g, coef, m0, m1, lane);
-    else if (sd.ah == 0)
-        prog_ac_first(b, s_tab[0], sc, g, coef, m0, m1, lane, err);
-    else
-        prog_ac_refine(b, s_tab[0], sc, g, coef, m0, m1, uint32_t(lane), err, s_q);
-    if (b.p > byte1 * 8u)
-        err |= kFlagOverrun; // the chain read past its restart interval / the end of the scan
+            for (int i = 0; i < 4; ++i) {
+                if (i >= sd.ncomp)
+                    break;
+                const uint4* src = reinterpret_cast<const uint4*>(bd.prog_huff + sd.table[i]);
+                uint4* dst = reinterpret_cast<uint4*>(&s_tab[i]);
+                for (int q = lane; q < int(sizeof(ProgHuffDev) / 16); q += 32)
+                    dst[q] = __ldg(src + q);
+            }
+        }
+        __syncwarp();
+        const uint32_t byte0 = j ? bd.bnd[ch.bnd_off + j - 1u] : 0u;
+        const uint32_t byte1 = j + 1u < sd.n_chain ? bd.bnd[ch.bnd_off + j] : cst.cmp_len;
+        PBits b;
+        b.w = bd.cmp + ch.cmp_off / 4;
+        b.wmax = (ch.raw_len + 15u) / 4u; // inside what the host reserved for this scan (the words past cmp_len are never trusted)
+        pb_seek(b, byte0 * 8u);
+        PMap g;
+        const int c0 = sd.comp[0];
+        g.wb = max(1u, uint32_t(sd.wb));
+        g.lh = 31u - uint32_t(__clz(int(im.h[c0])));
+        g.lv = 31u - uint32_t(__clz(int(im.v[c0])));
+        g.bx = g.by = 0u;
+        g.mcus_x = im.mcus_x;
+        g.bpm = im.bpm;
+        g.first = im.blk_first[c0];
+        int16_t* coef = bd.pcoef + im.pcoef_off;
+        PScan sc;
+        sc.ncomp = sd.ncomp;
+        sc.ss = sd.ss;
+        sc.se = sd.se;
+        sc.al = sd.al;
+        sc.bpm = im.bpm;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            sc.nb[i] = i < sd.ncomp ? int(im.h[sd.comp[i] & 3]) * int(im.v[sd.comp[i] & 3]) : 0;
+        if (sd.ss == 0 && sd.ah == 0)
+            prog_dc_first(b, s_tab, sc, g, coef, m0, m1, lane, err, y);
+        else if (sd.ss == 0)
+            prog_dc_refine(b, sc, g, coef, m0, m1, lane, y);
+        else if (sd.ah == 0)
+            prog_ac_first(b, s_tab[0], sc, g, coef, m0, m1, lane, err, y);
+        else
+            prog_ac_refine(b, s_tab[0], sc, g, coef, m0, m1, uint32_t(lane), err, s_q, y);
+        if (b.p > byte1 * 8u)
+            err |= kFlagOverrun; // the chain read past its restart interval / the end of the scan
+    }
     if (err && lane == 0)
         atomicOr(&bd.state[sd.parent].flags, err);
+    // whatever happened, the successors of this chain must not wait for ever; a fine-grained successor relies on this
+    // chain having followed ITS predecessor to the end (the order is transitive)
+    ps_need(y, m1);
+    ps_publish(y, m1, true, uint32_t(lane));
 }
 
-// After the last wave: the per-block records the IDCT stage reads (bits 0-7: which 16-byte groups hold a non-zero AC
+// After the scans: the per-block records the IDCT stage reads (bits 0-7: which 16-byte groups hold a non-zero AC
 // coefficient, bits 16-31: the DC value), and the DC slot of the block cleared, as in the dense form of the sequential
 // path.  Eight threads per block, one per group.
 __global__ void __launch_bounds__(256) prog_record_kernel(BatchDev bd)
