@@ -45,14 +45,19 @@ __device__ __forceinline__ void pb_seek(PBits& b, uint32_t p)
     b.w2 = pb_word(b, b.base + 2u);
 }
 
-// the 32 bits at the current position (callers consume at most 32 bits between two peeks: one refill step at most)
+// the 32 bits at the current position
 __device__ __forceinline__ uint32_t pb_peek(PBits& b)
 {
-    if ((b.p >> 5) != b.base) {
-        ++b.base;
-        b.w0 = b.w1;
-        b.w1 = b.w2;
-        b.w2 = pb_word(b, b.base + 2u);
+    const uint32_t d = (b.p >> 5) - b.base;
+    if (d) {
+        if (d == 1u) { // the usual step
+            ++b.base;
+            b.w0 = b.w1;
+            b.w1 = b.w2;
+            b.w2 = pb_word(b, b.base + 2u);
+        } else {       // a run of correction bits was skipped
+            pb_seek(b, b.p);
+        }
     }
     return __funnelshift_l(b.w1, b.w0, b.p & 31u);
 }
@@ -273,40 +278,31 @@ __device__ __forceinline__ void prog_ac_first(PBits& b, const ProgHuffDev& tab, 
     }
 }
 
-// Correction bits (decode_mcu_AC_refine, the `if (*thiscoef != 0)` arm) of the n non-zero-history coefficients at positions
-// [k, t), lowest position first: a set bit moves the coefficient one step (1 << Al) away from zero unless its bit Al is
-// already set.  lo / hi: this lane's coefficients at positions lane and lane + 32; rlo / rhi: how many non-zero-history
-// coefficients of the band lie before them; before_k: how many lie before k.
-__device__ __forceinline__ void prog_correct(PBits& b, uint32_t n, uint32_t k, uint32_t t, uint32_t before_k, bool mine_lo, bool mine_hi,
-    uint32_t rlo, uint32_t rhi, int32_t& lo, int32_t& hi, bool& dlo, bool& dhi, uint32_t lane, int32_t p1)
+// ---- AC, refinement (decode_mcu_AC_refine)
+// A symbol passes r zero-history positions and stops at the next one; the non-zero-history ones passed on the way take a
+// correction bit each (a set bit moves the coefficient one step (1 << Al) away from zero unless its bit Al is already set).
+//
+// The parse is one dependent chain per symbol (window -> table -> which zero -> how many correction bits -> next
+// window), so everything else is kept off it:
+// * the table is pre-decoded for this scan type (refine_entry): bits consumed including the sign bit, run, kind;
+// * the positions of a block's zero-history coefficients are listed once per block (s_q, written by the lanes that own
+//   them): "the (j + r)-th zero of the band" is one shared-memory read, and the number of correction bits follows from
+//   positions and counts alone -- the parse never loops over coefficients;
+// * correction bits are not extracted while parsing.  Every non-zero-history coefficient of the band takes exactly one,
+//   in position order, so the bit of the coefficient at position q sits at
+//       (block start) + (code, sign and run-length bits of the symbols that started at or before q) + (rank of q among them)
+//   and each lane only notes the middle term for its two positions (one compare-and-select per symbol); the bits are
+//   fetched and applied once per block.
+constexpr uint32_t kRefCoef = 1u << 9, kRefEob = 1u << 10, kRefBad = 1u << 11;
+// bits 0-4: code length + sign bit; bits 5-8: run
+__device__ __forceinline__ uint32_t refine_entry(uint32_t len, uint32_t sym)
 {
-    if (n == 0u)
-        return;
-    const uint32_t n1 = min(n, 32u);
-    const uint32_t v1 = pb_get(b, n1) << (32u - n1); // first bit read = bit 31
-    const uint32_t v2 = n > 32u ? pb_get(b, n - 32u) << (64u - n) : 0u;
-    auto bit_of = [&](uint32_t idx) { return idx < 32u ? (v1 >> (31u - idx)) & 1u : (v2 >> (63u - idx)) & 1u; };
-    if (mine_lo && lane >= k && lane < t) {
-        if (bit_of(rlo - before_k) && (lo & p1) == 0) {
-            lo += lo >= 0 ? p1 : -p1;
-            dlo = true;
-        }
-    }
-    if (mine_hi && lane + 32u >= k && lane + 32u < t) {
-        if (bit_of(rhi - before_k) && (hi & p1) == 0) {
-            hi += hi >= 0 ? p1 : -p1;
-            dhi = true;
-        }
-    }
+    const uint32_t r = sym >> 4, s = sym & 15u;
+    return (len + (s ? 1u : 0u)) | (r << 5) | (s ? kRefCoef : 0u) | ((s == 0u && r != 15u) ? kRefEob : 0u) | (s > 1u ? kRefBad : 0u);
 }
 
-// AC, refinement (decode_mcu_AC_refine).  A symbol passes r zero-history positions and stops at the next one; the non-zero
-// ones passed on the way take a correction bit each.  The positions of a block's zero-history coefficients are listed
-// once per block (s_q, by the lanes that own them), so "the (j + r)-th zero from the start of the band" is one
-// shared-memory read and the number of correction bits follows from positions and counts alone: the parse never loops
-// over coefficients.
-__device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
-    uint32_t lane, uint32_t& err, uint8_t* s_q, PSync& y)
+__device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab, const uint16_t* s_rl, const PScan& sc, PMap& g, int16_t* coef,
+    uint32_t m0, uint32_t m1, uint32_t lane, uint32_t& err, uint8_t* s_q, PSync& y)
 {
     uint32_t eobrun = 0;
     const uint32_t ss = sc.ss, se = sc.se;
@@ -335,62 +331,85 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab,
         const uint32_t nzlo = __ballot_sync(0xffffffffu, lo != 0) & bandlo, nzhi = __ballot_sync(0xffffffffu, hi != 0) & bandhi;
         const uint32_t zlo = ~nzlo & bandlo, zhi = ~nzhi & bandhi;
         const uint32_t n_zlo = uint32_t(__popc(zlo)), n_z = n_zlo + uint32_t(__popc(zhi));
-        __syncwarp();
-        if ((zlo >> lane) & 1u)
-            s_q[__popc(zlo & below)] = uint8_t(lane);
-        if ((zhi >> lane) & 1u)
-            s_q[n_zlo + uint32_t(__popc(zhi & below))] = uint8_t(lane + 32u);
-        __syncwarp();
-        const bool mine_lo = (nzlo >> lane) & 1u, mine_hi = (nzhi >> lane) & 1u;
-        const uint32_t rlo = uint32_t(__popc(nzlo & below)), rhi = uint32_t(__popc(nzlo)) + uint32_t(__popc(nzhi & below));
-        bool dlo = false, dhi = false; // only what this scan changed is stored: other bands may be in other scans' hands
-        uint32_t k = ss, j = 0; // j: how many zero-history positions of the band lie before k
+        const uint32_t n_nz = uint32_t(__popc(nzlo) + __popc(nzhi));
+        const int32_t lo0 = lo, hi0 = hi;
+        const uint32_t pstart = b.p;
+        uint32_t clo = 0, chi = 0; // symbol bits read up to (and including) the symbol that passes this lane's positions
+        uint32_t k = ss, j = 0;    // j: how many zero-history positions of the band lie before k
         if (eobrun == 0u) {
+            __syncwarp();
+            if ((zlo >> lane) & 1u)
+                s_q[__popc(zlo & below)] = uint8_t(lane);
+            if ((zhi >> lane) & 1u)
+                s_q[n_zlo + uint32_t(__popc(zhi & below))] = uint8_t(lane + 32u);
+            __syncwarp();
+            uint32_t c = 0; // symbol bits of this block so far
 #pragma unroll 1
             while (k <= se) {
-                const uint32_t sym = pb_symbol(b, tab, err);
-                const uint32_t r = sym >> 4, s = sym & 15u;
-                int32_t newv = 0;
-                if (s) {
-                    if (s != 1u)
-                        err |= kFlagBadHuffman; // (libjpeg warns and goes on)
-                    newv = pb_get(b, 1u) ? p1 : -p1;
-                } else if (r != 15u) {
-                    eobrun = (1u << r) + pb_get(b, r);
-                    break; // the rest of the band: correction bits only, below
+                const uint32_t win = pb_peek(b);
+                uint32_t e = s_rl[win >> 23];
+                if (e == 0u) { // a code longer than nine bits
+                    const uint32_t p0 = b.p;
+                    const uint32_t sym = pb_symbol(b, tab, err);
+                    e = refine_entry(b.p - p0, sym);
+                    b.p = p0;
                 }
+                const uint32_t total = e & 31u, r = (e >> 5) & 15u;
+                if (e & kRefEob) {
+                    b.p += total;
+                    c += total + r;
+                    eobrun = (1u << r) + pb_get(b, r);
+                    break; // the rest of the band: correction bits only
+                }
+                if (e & kRefBad)
+                    err |= kFlagBadHuffman; // (libjpeg warns and goes on)
+                const int32_t newv = (e & kRefCoef) ? (((win >> (32u - total)) & 1u) ? p1 : -p1) : 0;
                 const uint32_t idx = j + r;
                 const bool found = idx < n_z;
                 const uint32_t t = found ? uint32_t(s_q[idx]) : se + 1u; // where the symbol stops
                 const uint32_t n = (t - k) - (found ? r : n_z - j);     // positions passed that are not zero-history ones
-                prog_correct(b, n, k, t, (k - ss) - j, mine_lo, mine_hi, rlo, rhi, lo, hi, dlo, dhi, lane, p1);
+                c += total;
+                b.p += total + n;
+                clo = lane >= k ? c : clo;
+                chi = lane + 32u >= k ? c : chi;
                 if (newv) {
                     if (!found) {
                         err |= kFlagOverrun;
                         break;
                     }
-                    if (lane == (t & 31u)) {
-                        if (t < 32u) {
-                            lo = newv;
-                            dlo = true;
-                        } else {
-                            hi = newv;
-                            dhi = true;
-                        }
-                    }
+                    lo = lane == t ? newv : lo;
+                    hi = lane + 32u == t ? newv : hi;
                 }
                 k = t + 1u;
                 j = idx + 1u;
             }
+            if (eobrun > 0u && k <= se) { // the band's tail behind an end-of-band symbol
+                clo = lane >= k ? c : clo;
+                chi = lane + 32u >= k ? c : chi;
+                b.p += (se + 1u - k) - (n_z - min(j, n_z));
+            }
+        } else {
+            b.p += n_nz; // a block inside an end-of-band run: correction bits only
         }
-        if (eobrun > 0u) {
-            if (k <= se)
-                prog_correct(b, (se + 1u - k) - (n_z - min(j, n_z)), k, se + 1u, (k - ss) - j, mine_lo, mine_hi, rlo, rhi, lo, hi, dlo, dhi, lane, p1);
+        if (eobrun > 0u)
             --eobrun;
+        // correction bits, fetched where they lie
+        if (n_nz) {
+            if ((nzlo >> lane) & 1u) {
+                const uint32_t at = pstart + clo + uint32_t(__popc(nzlo & below));
+                if (((pb_word(b, at >> 5) >> (31u - (at & 31u))) & 1u) && (lo & p1) == 0)
+                    lo += lo >= 0 ? p1 : -p1;
+            }
+            if ((nzhi >> lane) & 1u) {
+                const uint32_t at = pstart + chi + uint32_t(__popc(nzlo)) + uint32_t(__popc(nzhi & below));
+                if (((pb_word(b, at >> 5) >> (31u - (at & 31u))) & 1u) && (hi & p1) == 0)
+                    hi += hi >= 0 ? p1 : -p1;
+            }
         }
-        if (dlo)
+        // only what this scan changed is stored: other bands may be in other scans' hands
+        if (lo != lo0)
             cur[lane] = int16_t(lo);
-        if (dhi)
+        if (hi != hi0)
             cur[lane + 32] = int16_t(hi);
     }
 }
@@ -400,6 +419,7 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
 {
     __shared__ ProgHuffDev s_tab[4];
     __shared__ uint8_t s_q[64];
+    __shared__ uint16_t s_rl[512]; // refinement scans: the first-level table pre-decoded (refine_entry)
     const int lane = threadIdx.x;
     const uint32_t chain = blockIdx.x;
     const ProgScanDev sd = bd.prog_scan[bd.prog_chain[chain]];
@@ -444,6 +464,13 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
             }
         }
         __syncwarp();
+        if (sd.ss != 0 && sd.ah != 0) {
+            for (int q = lane; q < 512; q += 32) {
+                const uint32_t e = s_tab[0].lut[q];
+                s_rl[q] = e ? uint16_t(refine_entry(e >> 8, e & 0xFFu)) : uint16_t(0);
+            }
+            __syncwarp();
+        }
         const uint32_t byte0 = j ? bd.bnd[ch.bnd_off + j - 1u] : 0u;
         const uint32_t byte1 = j + 1u < sd.n_chain ? bd.bnd[ch.bnd_off + j] : cst.cmp_len;
         PBits b;
@@ -476,7 +503,7 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
         else if (sd.ah == 0)
             prog_ac_first(b, s_tab[0], sc, g, coef, m0, m1, lane, err, y);
         else
-            prog_ac_refine(b, s_tab[0], sc, g, coef, m0, m1, uint32_t(lane), err, s_q, y);
+            prog_ac_refine(b, s_tab[0], s_rl, sc, g, coef, m0, m1, uint32_t(lane), err, s_q, y);
         if (b.p > byte1 * 8u)
             err |= kFlagOverrun; // the chain read past its restart interval / the end of the scan
     }
