@@ -262,6 +262,8 @@ Options parse_options(const char* options, const char* decoder_id)
             o.entry_stream = std::atoi(value.c_str()) != 0;
         else if (name == "progressive")
             o.progressive = std::atoi(value.c_str()) != 0;
+        else if (name == "progressive_min_batch")
+            o.progressive_min_batch = std::max(1, std::atoi(value.c_str()));
         else if (name == "fused_pixels")
             o.fused_pixels = std::atoi(value.c_str()) != 0;
         else if (name == "use_executor")
@@ -473,6 +475,9 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     child_out.format = B200JPEG_FMT_Y;
     std::vector<StreamHeader> parent_frames; // frames of multi-scan streams with restart_interval cleared (the parent has no scan)
     parent_frames.reserve(n);
+    int n_progressive = 0;
+    for (int i = 0; i < n; ++i)
+        n_progressive += ((parsed && parsed[i]) ? *parsed[i] : parsed_own_[size_t(i)]).status == kStreamProgressive ? 1 : 0;
     for (int i = 0; i < n; ++i) {
         const ParsedInput& pi = (parsed && parsed[i]) ? *parsed[i] : parsed_own_[size_t(i)];
         if (pi.status == kStreamOk) {
@@ -493,7 +498,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             hdrs.push_back(&parent_frames.back());
             items.push_back({i, kParent, 0});
         } else if (pi.status == kStreamProgressive) {
-            if (!opt_.progressive) {
+            if (!opt_.progressive || n_progressive < opt_.progressive_min_batch) {
                 host_status_[i] = B200JPEG_ERR_UNSUPPORTED;
                 continue;
             }

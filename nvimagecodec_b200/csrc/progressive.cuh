@@ -72,10 +72,24 @@ __device__ __forceinline__ uint32_t pb_get(PBits& b, uint32_t n) // n <= 32
 }
 
 // One Huffman symbol.  Codes of up to 9 bits come out of the first-level table, longer ones out of the canonical search.
-__device__ __forceinline__ uint32_t pb_symbol(PBits& b, const ProgHuffDev& t, uint32_t& err)
+// A table as the loops see it: the shared-space address of its first-level entries, pinned in a register (a generic pointer,
+// or an address the compiler may recompute, costs a special-register read per symbol), and the table itself for long codes.
+struct PTab {
+    uint32_t lut;
+    const ProgHuffDev* t;
+};
+__device__ __forceinline__ uint32_t pinned_smem_addr(const void* p)
 {
+    uint32_t a;
+    asm volatile("mov.u32 %0, %1;" : "=r"(a) : "r"(smem_addr(p)));
+    return a;
+}
+__device__ __forceinline__ uint32_t pb_symbol(PBits& b, const PTab& pt, uint32_t& err)
+{
+    const ProgHuffDev& t = *pt.t;
     const uint32_t win = pb_peek(b);
-    const uint32_t e = t.lut[win >> 23];
+    uint32_t e;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(e) : "r"(pt.lut + ((win >> 22) & 0x3FEu)));
     if (e) {
         b.p += e >> 8;
         return e & 0xFFu;
@@ -146,10 +160,11 @@ __device__ __forceinline__ void ps_need(PSync& y, uint32_t m_excl) // the predec
 {
     if (y.pred == nullptr || y.avail >= m_excl)
         return;
-    for (;;) {
+    for (;;) { // relaxed polls (an acquire load empties this SM's L1 every time), one fence once the predecessor is far enough
         uint32_t v;
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(y.pred) : "memory");
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(y.pred) : "memory");
         if (v >= m_excl) {
+            asm volatile("fence.acq_rel.gpu;" ::: "memory");
             y.avail = v;
             return;
         }
@@ -179,7 +194,7 @@ struct PScan {
 };
 
 // DC, first pass (decode_mcu_DC_first): one Huffman symbol + magnitude bits per block, DPCM per component, value << Al.
-__device__ __forceinline__ void prog_dc_first(PBits& b, const ProgHuffDev* tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
+__device__ __forceinline__ void prog_dc_first(PBits& b, const PTab* tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
     int lane, uint32_t& err, PSync& y)
 {
     int32_t pred[4] = {0, 0, 0, 0};
@@ -233,7 +248,7 @@ __device__ __forceinline__ void prog_dc_refine(PBits& b, const PScan& sc, const 
 }
 
 // AC, first pass (decode_mcu_AC_first): run/size symbols inside the band, end-of-band runs over whole blocks.
-__device__ __forceinline__ void prog_ac_first(PBits& b, const ProgHuffDev& tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
+__device__ __forceinline__ void prog_ac_first(PBits& b, const PTab& tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
     int lane, uint32_t& err, PSync& y)
 {
     uint32_t eobrun = 0;
@@ -301,7 +316,7 @@ __device__ __forceinline__ uint32_t refine_entry(uint32_t len, uint32_t sym)
     return (len + (s ? 1u : 0u)) | (r << 5) | (s ? kRefCoef : 0u) | ((s == 0u && r != 15u) ? kRefEob : 0u) | (s > 1u ? kRefBad : 0u);
 }
 
-__device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab, const uint16_t* s_rl, const PScan& sc, PMap& g, int16_t* coef,
+__device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const uint16_t* s_rl, const PScan& sc, PMap& g, int16_t* coef,
     uint32_t m0, uint32_t m1, uint32_t lane, uint32_t& err, uint8_t* s_q, PSync& y)
 {
     uint32_t eobrun = 0;
@@ -310,6 +325,8 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab,
     const uint64_t band = (se == 63u ? ~uint64_t(0) : ((uint64_t(1) << (se + 1u)) - 1u)) & ~((uint64_t(1) << ss) - 1u);
     const uint32_t bandlo = uint32_t(band), bandhi = uint32_t(band >> 32);
     const uint32_t below = (1u << lane) - 1u;
+    const uint32_t rl_addr = pinned_smem_addr(s_rl), q_addr = pinned_smem_addr(s_q);
+    uint32_t seen = 0; // every table entry used, or-ed: the "bad" flag is looked at once, after the scan
     // the block after this one is requested while this one is worked on
     pmap_seek(g, m0);
     ps_need(y, min(m1, m0 + 1u));
@@ -339,15 +356,16 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab,
         if (eobrun == 0u) {
             __syncwarp();
             if ((zlo >> lane) & 1u)
-                s_q[__popc(zlo & below)] = uint8_t(lane);
+                asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + uint32_t(__popc(zlo & below))), "r"(lane) : "memory");
             if ((zhi >> lane) & 1u)
-                s_q[n_zlo + uint32_t(__popc(zhi & below))] = uint8_t(lane + 32u);
+                asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + n_zlo + uint32_t(__popc(zhi & below))), "r"(lane + 32u) : "memory");
             __syncwarp();
             uint32_t c = 0; // symbol bits of this block so far
 #pragma unroll 1
             while (k <= se) {
                 const uint32_t win = pb_peek(b);
-                uint32_t e = s_rl[win >> 23];
+                uint32_t e;
+                asm volatile("ld.shared.u16 %0, [%1];" : "=r"(e) : "r"(rl_addr + ((win >> 22) & 0x3FEu)));
                 if (e == 0u) { // a code longer than nine bits
                     const uint32_t p0 = b.p;
                     const uint32_t sym = pb_symbol(b, tab, err);
@@ -361,12 +379,13 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab,
                     eobrun = (1u << r) + pb_get(b, r);
                     break; // the rest of the band: correction bits only
                 }
-                if (e & kRefBad)
-                    err |= kFlagBadHuffman; // (libjpeg warns and goes on)
+                seen |= e;
                 const int32_t newv = (e & kRefCoef) ? (((win >> (32u - total)) & 1u) ? p1 : -p1) : 0;
                 const uint32_t idx = j + r;
                 const bool found = idx < n_z;
-                const uint32_t t = found ? uint32_t(s_q[idx]) : se + 1u; // where the symbol stops
+                uint32_t t; // where the symbol stops
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t) : "r"(q_addr + min(idx, 63u)));
+                t = found ? t : se + 1u;
                 const uint32_t n = (t - k) - (found ? r : n_z - j);     // positions passed that are not zero-history ones
                 c += total;
                 b.p += total + n;
@@ -412,6 +431,8 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const ProgHuffDev& tab,
         if (hi != hi0)
             cur[lane + 32] = int16_t(hi);
     }
+    if (seen & kRefBad)
+        err |= kFlagBadHuffman; // a new coefficient of more than one bit (libjpeg warns and goes on)
 }
 
 // One warp per chain.
@@ -496,14 +517,20 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
 #pragma unroll
         for (int i = 0; i < 4; ++i)
             sc.nb[i] = i < sd.ncomp ? int(im.h[sd.comp[i] & 3]) * int(im.v[sd.comp[i] & 3]) : 0;
+        PTab tab[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            tab[i].lut = pinned_smem_addr(s_tab[i].lut);
+            tab[i].t = &s_tab[i];
+        }
         if (sd.ss == 0 && sd.ah == 0)
-            prog_dc_first(b, s_tab, sc, g, coef, m0, m1, lane, err, y);
+            prog_dc_first(b, tab, sc, g, coef, m0, m1, lane, err, y);
         else if (sd.ss == 0)
             prog_dc_refine(b, sc, g, coef, m0, m1, lane, y);
         else if (sd.ah == 0)
-            prog_ac_first(b, s_tab[0], sc, g, coef, m0, m1, lane, err, y);
+            prog_ac_first(b, tab[0], sc, g, coef, m0, m1, lane, err, y);
         else
-            prog_ac_refine(b, s_tab[0], s_rl, sc, g, coef, m0, m1, uint32_t(lane), err, s_q, y);
+            prog_ac_refine(b, tab[0], s_rl, sc, g, coef, m0, m1, uint32_t(lane), err, s_q, y);
         if (b.p > byte1 * 8u)
             err |= kFlagOverrun; // the chain read past its restart interval / the end of the scan
     }
