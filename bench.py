@@ -46,6 +46,12 @@ def _gen_spec(spec):
     return corpus.encode(corpus.synth(h, w, seed), q, samp, rst_interval=rst)
 
 
+def _gen_progressive(seed):
+    from nvimagecodec_b200 import corpus
+
+    return corpus.encode(corpus.synth(HEIGHT, WIDTH, seed), 90, "420", progressive=True)
+
+
 def _gen_one(seed):
     return _gen_spec((HEIGHT, WIDTH, seed, 90, "420", 0))
 
@@ -388,6 +394,8 @@ def main():
         if world == 1:
             extra_corpora["c3"] = make_workload("c3", 256, cores)
             extra_corpora["c4"] = make_workload("c4", 32, cores)
+            pj = _pmap(_gen_progressive, list(range(64)), cores)  # 64 distinct progressive 1080p streams, cycled to 256
+            extra_corpora["progressive"] = ([pj[i % 64] for i in range(256)], ["I_RGB"] * 256, [None] * 256)
     assert torch.cuda.is_available(), "bench.py needs a GPU (the decoder has no CPU path)"
     torch.cuda.set_device(local)
     # No CPU pinning per rank: measured on the 2-GPU box, the NVML CPU set of a GPU put the rank's pinned pixel buffer on the far
@@ -684,7 +692,8 @@ def main():
         # ---- the other BASELINE configs, bounded (N=1 only): kernels-only and C-ABI pixels-in-HBM numbers, statuses checked
         if world == 1 and args.workload == "c2" and not args.no_extras:
             others = []
-            for name, nb in (("c3", 256), ("c4", 32), ("c5", 2048)):
+            wl_names = dict(WORKLOADS, progressive="n3: 256 x 1920x1080 PROGRESSIVE (SOF2, libjpeg's ten-scan script) 4:2:0 q90 -> I_RGB")
+            for name, nb in (("c3", 256), ("c4", 32), ("c5", 2048), ("progressive", 256)):
                 try:
                     oj, of, orr = extra_corpora[name]
                     assert len(oj) == nb
@@ -710,12 +719,16 @@ def main():
                         dec.run(ob)
                     torch.cuda.synchronize()
                     pms = (time.perf_counter() - t0) / 5 * 1e3
-                    others.append({"workload": WORKLOADS[name], "images": nb, "all_ok": all(x == _lib.OK for x in ost),
+                    others.append({"workload": wl_names[name], "images": nb, "all_ok": all(x == _lib.OK for x in ost),
                                    "kernels_only_mpix_per_s": ompix / (kms * 1e-3), "ms_per_step": kms,
                                    "e2e_capi_device_out_mpix_per_s": ompix / (pms * 1e-3)})
+                    if name == "progressive":  # the reference's CPU path on the same streams: 32 of them, all host threads
+                        dt, how = cpu_reference_decode(oj[:32], cores, 1)
+                        others[-1]["cpu_reference_mpix_per_s"] = 32 * HEIGHT * WIDTH / 1e6 / dt
+                        others[-1]["cpu_reference"] = f"32 of the streams x 1 pass on {cores} threads; {how}"
                     del ob
                 except Exception as e:  # an extra must not take the headline down
-                    others.append({"workload": WORKLOADS[name], "error": repr(e)[:200]})
+                    others.append({"workload": wl_names[name], "error": repr(e)[:200]})
             line["other_configs"] = others
         sys.stdout.flush()
         os.dup2(stdout_fd, 1)

@@ -1047,7 +1047,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
     const size_t so_pos = so;
     so = align_up(so + (bd_.sym_mode ? 4ull * (coef_elems / 64) : 0ull), 256);
     const size_t so_prog = so;
-    so = align_up(so + 4ull * prog_chain_scan.size(), 256);
+    so = align_up(so + 8ull * prog_chain_scan.size(), 256); // progress words, then elapsed clocks (B200JPEG_TRACE)
 
     // the coefficients live either as dense 16-byte groups (coef_) or as the entry stream (sym_), never both
     coef_bytes_ = bd_.sym_mode ? 0 : coef_elems * sizeof(int16_t);
@@ -1310,6 +1310,19 @@ int Decoder::execute(cudaStream_t stream)
     if (bd_.n_prog_img) { // progressive images: their scans accumulate into zeroed blocks, wave by wave
         cudaMemsetAsync(bd_.pcoef, 0, pcoef_bytes_, stream);
         launches_ += launch_progressive(bd_, stream);
+        if (trace_enabled()) { // how long every chain took (thousands of SM clocks), with its scan's parameters
+            std::vector<uint32_t> clk(size_t(bd_.n_prog_chain)), chain_scan(size_t(bd_.n_prog_chain));
+            std::vector<ProgScanDev> scans(chain_scan.size());
+            cudaStreamSynchronize(stream);
+            cudaMemcpy(clk.data(), bd_.prog_progress + bd_.n_prog_chain, 4 * clk.size(), cudaMemcpyDeviceToHost);
+            cudaMemcpy(chain_scan.data(), bd_.prog_chain, 4 * clk.size(), cudaMemcpyDeviceToHost);
+            for (size_t c = 0; c < clk.size() && c < 24; ++c) {
+                ProgScanDev sd;
+                cudaMemcpy(&sd, bd_.prog_scan + chain_scan[c], sizeof(sd), cudaMemcpyDeviceToHost);
+                std::fprintf(stderr, "[b200jpeg] chain %zu: scan %u ncomp %u Ss %u Se %u Ah %u Al %u: %u kclk\n", c, chain_scan[c], sd.ncomp, sd.ss,
+                    sd.se, sd.ah, sd.al, clk[c]);
+            }
+        }
     }
     // Everything a status depends on is known once the entropy stage is through (the pixel kernels only read the
     // flags).  The read-back goes over a side stream so that it neither waits for the pixel kernels nor holds them up;

@@ -309,14 +309,18 @@ __device__ __forceinline__ void prog_ac_first(PBits& b, const PTab& tab, const P
 //   and each lane only notes the middle term for its two positions (one compare-and-select per symbol); the bits are
 //   fetched and applied once per block.
 constexpr uint32_t kRefCoef = 1u << 9, kRefEob = 1u << 10, kRefBad = 1u << 11;
-// bits 0-4: code length + sign bit; bits 5-8: run
+// the same for the common-symbol loop, one 32-bit word per nine-bit window: byte 0 = code length + sign bit, byte 1 = run,
+// kFastCoef / kFastBad, kFastEob = end of band for this block only (EOB0: the rest of the band takes correction bits, nothing
+// carries over), kRefSlow = not for that loop (a longer code, or an end-of-band run over several blocks)
+constexpr uint32_t kFastCoef = 1u << 16, kFastEob = 1u << 17, kFastBad = 1u << 18, kRefSlow = 1u << 20;
+// refine_entry: bits 0-4: code length + sign bit; bits 5-8: run
 __device__ __forceinline__ uint32_t refine_entry(uint32_t len, uint32_t sym)
 {
     const uint32_t r = sym >> 4, s = sym & 15u;
     return (len + (s ? 1u : 0u)) | (r << 5) | (s ? kRefCoef : 0u) | ((s == 0u && r != 15u) ? kRefEob : 0u) | (s > 1u ? kRefBad : 0u);
 }
 
-__device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const uint16_t* s_rl, const PScan& sc, PMap& g, int16_t* coef,
+__device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const uint32_t* s_rl, const PScan& sc, PMap& g, int16_t* coef,
     uint32_t m0, uint32_t m1, uint32_t lane, uint32_t& err, uint8_t* s_q, PSync& y)
 {
     uint32_t eobrun = 0;
@@ -326,7 +330,7 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
     const uint32_t bandlo = uint32_t(band), bandhi = uint32_t(band >> 32);
     const uint32_t below = (1u << lane) - 1u;
     const uint32_t rl_addr = pinned_smem_addr(s_rl), q_addr = pinned_smem_addr(s_q);
-    uint32_t seen = 0; // every table entry used, or-ed: the "bad" flag is looked at once, after the scan
+    uint32_t seen = 0, seen_fast = 0; // every table entry used, or-ed: the "bad" flag is looked at once, after the scan
     // the block after this one is requested while this one is worked on
     pmap_seek(g, m0);
     ps_need(y, min(m1, m0 + 1u));
@@ -359,49 +363,102 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + uint32_t(__popc(zlo & below))), "r"(lane) : "memory");
             if ((zhi >> lane) & 1u)
                 asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + n_zlo + uint32_t(__popc(zhi & below))), "r"(lane + 32u) : "memory");
+            if (lane < 16u) // "no such zero": a run that reaches past the last one stops behind the band
+                asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + n_z + lane), "r"(se + 1u) : "memory");
             __syncwarp();
             uint32_t c = 0; // symbol bits of this block so far
+            bool overrun = false;
 #pragma unroll 1
-            while (k <= se) {
-                const uint32_t win = pb_peek(b);
-                uint32_t e;
-                asm volatile("ld.shared.u16 %0, [%1];" : "=r"(e) : "r"(rl_addr + ((win >> 22) & 0x3FEu)));
-                if (e == 0u) { // a code longer than nine bits
-                    const uint32_t p0 = b.p;
-                    const uint32_t sym = pb_symbol(b, tab, err);
-                    e = refine_entry(b.p - p0, sym);
-                    b.p = p0;
-                }
+            for (;;) {
+                // ---- the common symbols: one pass of this loop each, nothing but the parse recurrence on its critical path
+                // (window -> table entry -> position of the zero the run stops at -> next window).  Rare things -- codes longer
+                // than nine bits, end-of-band symbols, a skip of more than a word of correction bits -- leave the loop with
+                // the symbol not yet consumed and are dealt with below.
+                if (k > se)
+                    break;
+                (void)pb_peek(b); // window registers brought to b.p
+                uint32_t o = b.p & 31u, base = b.base, w0 = b.w0, w1 = b.w1, w2 = b.w2;
+                bool slow = false;
+                // (no branch but the loop's own inside: a lone warp pays every one of them in full)
+                do {
+                    const bool upper = o >= 32u;
+                    const uint32_t win = upper ? __funnelshift_l(w2, w1, o) : __funnelshift_l(w1, w0, o);
+                    uint32_t e;
+                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(rl_addr + ((win >> 21) & 0x7FCu)));
+                    { // the window registers move on by a word when the upper half was used (off the critical path)
+                        const uint32_t* nw = b.w + min(base + 3u, b.wmax);
+                        uint32_t w3 = w2;
+                        asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q ld.global.nc.u32 %0, [%1];\n\t}"
+                                     : "+r"(w3)
+                                     : "l"(nw), "r"(uint32_t(upper)));
+                        w0 = upper ? w1 : w0;
+                        w1 = upper ? w2 : w1;
+                        w2 = w3;
+                        base += upper ? 1u : 0u;
+                        o -= upper ? 32u : 0u;
+                    }
+                    const uint32_t r = (e >> 8) & 0xFFu, total = e & 0xFFu;
+                    uint32_t t; // where the symbol stops: the (j + r)-th zero-history position, or behind the band
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t) : "r"(q_addr + j + r));
+                    slow = (e & kRefSlow) != 0u;
+                    const bool take = !slow;
+                    seen_fast |= e;
+                    const bool eob = (e & kFastEob) != 0u;                 // the band ends here: the rest takes correction bits only
+                    t = eob ? se + 1u : t;
+                    const uint32_t zp = eob ? n_z - j : min(r, n_z - j);   // zero-history positions passed
+                    const uint32_t cn = c + total;
+                    clo = (take && lane >= k) ? cn : clo;
+                    chi = (take && lane + 32u >= k) ? cn : chi;
+                    c = take ? cn : c;
+                    const bool place = take && (e & kFastCoef) != 0u;
+                    const int32_t newv = ((win >> ((32u - total) & 31u)) & 1u) ? p1 : -p1;
+                    overrun = overrun || (place && t > se);
+                    lo = (place && lane == t && t <= se) ? newv : lo;
+                    hi = (place && lane + 32u == t && t <= se) ? newv : hi;
+                    o = take ? (o + total - (k + zp)) + t : o; // += total + (positions passed that are not zero-history ones)
+                    k = take ? t + 1u : k;
+                    j = take ? j + r + 1u : j;
+                } while (!slow && k <= se && o < 64u);
+                b.base = base;
+                b.w0 = w0;
+                b.w1 = w1;
+                b.w2 = w2;
+                b.p = base * 32u + o;
+                j = min(j, n_z);
+                if (!slow)
+                    continue; // the band is through, or only the window had to be moved
+                // ---- a rare symbol, the plain way
+                const uint32_t p0 = b.p;
+                const uint32_t sym = pb_symbol(b, tab, err);
+                const uint32_t e = refine_entry(b.p - p0, sym);
                 const uint32_t total = e & 31u, r = (e >> 5) & 15u;
+                b.p = p0 + total;
+                c += total;
                 if (e & kRefEob) {
-                    b.p += total;
-                    c += total + r;
+                    c += r;
                     eobrun = (1u << r) + pb_get(b, r);
                     break; // the rest of the band: correction bits only
                 }
                 seen |= e;
-                const int32_t newv = (e & kRefCoef) ? (((win >> (32u - total)) & 1u) ? p1 : -p1) : 0;
+                const int32_t newv = (e & kRefCoef) ? ((pb_word(b, (b.p - 1u) >> 5) >> (31u - ((b.p - 1u) & 31u))) & 1u ? p1 : -p1) : 0;
                 const uint32_t idx = j + r;
                 const bool found = idx < n_z;
-                uint32_t t; // where the symbol stops
-                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t) : "r"(q_addr + min(idx, 63u)));
+                uint32_t t;
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t) : "r"(q_addr + min(idx, 79u)));
                 t = found ? t : se + 1u;
-                const uint32_t n = (t - k) - (found ? r : n_z - j);     // positions passed that are not zero-history ones
-                c += total;
-                b.p += total + n;
+                b.p += (t - k) - (found ? r : n_z - j);
                 clo = lane >= k ? c : clo;
                 chi = lane + 32u >= k ? c : chi;
                 if (newv) {
-                    if (!found) {
-                        err |= kFlagOverrun;
-                        break;
-                    }
-                    lo = lane == t ? newv : lo;
-                    hi = lane + 32u == t ? newv : hi;
+                    overrun = overrun || !found;
+                    lo = (lane == t && found) ? newv : lo;
+                    hi = (lane + 32u == t && found) ? newv : hi;
                 }
                 k = t + 1u;
-                j = idx + 1u;
+                j = min(idx + 1u, n_z);
             }
+            if (overrun)
+                err |= kFlagOverrun;
             if (eobrun > 0u && k <= se) { // the band's tail behind an end-of-band symbol
                 clo = lane >= k ? c : clo;
                 chi = lane + 32u >= k ? c : chi;
@@ -431,7 +488,7 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
         if (hi != hi0)
             cur[lane + 32] = int16_t(hi);
     }
-    if (seen & kRefBad)
+    if ((seen & kRefBad) || (seen_fast & kFastBad))
         err |= kFlagBadHuffman; // a new coefficient of more than one bit (libjpeg warns and goes on)
 }
 
@@ -439,8 +496,8 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
 __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
 {
     __shared__ ProgHuffDev s_tab[4];
-    __shared__ uint8_t s_q[64];
-    __shared__ uint16_t s_rl[512]; // refinement scans: the first-level table pre-decoded (refine_entry)
+    __shared__ uint8_t s_q[80]; // zero-history positions of the block under way + 16 "behind the band" entries
+    __shared__ uint32_t s_rl[512]; // refinement scans: the first-level table pre-decoded for the common-symbol loop
     const int lane = threadIdx.x;
     const uint32_t chain = blockIdx.x;
     const ProgScanDev sd = bd.prog_scan[bd.prog_chain[chain]];
@@ -450,6 +507,7 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
     // the chain's MCUs
     const uint32_t j = chain - sd.chain_off;
     const uint32_t m0 = sd.ri ? j * sd.ri : 0u, m1 = sd.ri ? min(sd.n_mcu, m0 + sd.ri) : sd.n_mcu;
+    const long long clk0 = clock64();
     PSync y;
     y.mine = bd.prog_progress + chain;
     y.published = m0;
@@ -488,7 +546,12 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
         if (sd.ss != 0 && sd.ah != 0) {
             for (int q = lane; q < 512; q += 32) {
                 const uint32_t e = s_tab[0].lut[q];
-                s_rl[q] = e ? uint16_t(refine_entry(e >> 8, e & 0xFFu)) : uint16_t(0);
+                const uint32_t f = e ? refine_entry(e >> 8, e & 0xFFu) : 0u;
+                const uint32_t run = (f >> 5) & 15u;
+                uint32_t v = (f & 31u) | (run << 8) | ((f & kRefCoef) ? kFastCoef : 0u) | ((f & kRefBad) ? kFastBad : 0u);
+                if (f & kRefEob)
+                    v = run ? kRefSlow : ((f & 31u) | kFastEob);
+                s_rl[q] = e ? v : kRefSlow;
             }
             __syncwarp();
         }
@@ -540,6 +603,8 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
     // chain having followed ITS predecessor to the end (the order is transitive)
     ps_need(y, m1);
     ps_publish(y, m1, true, uint32_t(lane));
+    if (lane == 0)
+        bd.prog_progress[bd.n_prog_chain + chain] = uint32_t((clock64() - clk0) >> 10); // (read back under B200JPEG_TRACE)
 }
 
 // After the scans: the per-block records the IDCT stage reads (bits 0-7: which 16-byte groups hold a non-zero AC
