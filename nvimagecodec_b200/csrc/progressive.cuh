@@ -26,23 +26,60 @@
 #pragma once
 
 // ---- bit reader over the unstuffed words of a scan: warp-uniform
+// The words pass through a ring of four 32-word chunks in shared memory that the warp fills a chunk at a time (one coalesced
+// load, requested a whole chunk before it is needed), so that a window after a jump -- a run of correction bits was skipped --
+// costs shared-memory reads, not three exposed global loads.  The ring always holds the words from (at least) 45 before to
+// 51 behind the current one: enough for one block's symbols ahead and for the correction bits of the block under way behind.
 struct PBits {
     const uint32_t* w;   // words of the scan
     uint32_t wmax;       // last word index that may be read
     uint32_t p;          // bit position
     uint32_t base;       // word index of w0
     uint32_t w0, w1, w2;
+    uint32_t ring;       // shared-memory address of the ring
+    uint32_t n_chunk;    // chunks [n_chunk - 4, n_chunk) are in the ring
+    uint32_t ahead;      // this lane's word of chunk n_chunk, already requested
+    uint32_t lane;
 };
+constexpr uint32_t kRingAhead = 51u;
 
-__device__ __forceinline__ uint32_t pb_word(const PBits& b, uint32_t i) { return __ldg(b.w + min(i, b.wmax)); }
+__device__ __forceinline__ void pb_fill(PBits& b, uint32_t word) // the ring must hold the words up to `word`
+{
+    if (b.n_chunk * 32u > word)
+        return;
+    __syncwarp();
+    do {
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(b.ring + (((b.n_chunk & 3u) * 32u + b.lane) << 2)), "r"(b.ahead) : "memory");
+        ++b.n_chunk;
+        b.ahead = __ldg(b.w + min(b.n_chunk * 32u + b.lane, b.wmax));
+    } while (b.n_chunk * 32u <= word);
+    __syncwarp();
+}
+__device__ __forceinline__ uint32_t pb_word(const PBits& b, uint32_t i)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(b.ring + ((i & 127u) << 2)));
+    return v;
+}
 
 __device__ __forceinline__ void pb_seek(PBits& b, uint32_t p)
 {
     b.p = p;
     b.base = p >> 5;
+    pb_fill(b, b.base + kRingAhead);
     b.w0 = pb_word(b, b.base);
     b.w1 = pb_word(b, b.base + 1u);
     b.w2 = pb_word(b, b.base + 2u);
+}
+__device__ __forceinline__ void pb_open(PBits& b, const uint32_t* words, uint32_t wmax, uint32_t ring, uint32_t lane, uint32_t p)
+{
+    b.w = words;
+    b.wmax = wmax;
+    b.ring = ring;
+    b.lane = lane;
+    b.n_chunk = p >> 10; // the chunk the first word lies in
+    b.ahead = __ldg(b.w + min(b.n_chunk * 32u + lane, wmax));
+    pb_seek(b, p);
 }
 
 // the 32 bits at the current position
@@ -52,6 +89,7 @@ __device__ __forceinline__ uint32_t pb_peek(PBits& b)
     if (d) {
         if (d == 1u) { // the usual step
             ++b.base;
+            pb_fill(b, b.base + kRingAhead);
             b.w0 = b.w1;
             b.w1 = b.w2;
             b.w2 = pb_word(b, b.base + 2u);
@@ -377,6 +415,7 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 if (k > se)
                     break;
                 (void)pb_peek(b); // window registers brought to b.p
+                pb_fill(b, b.base + kRingAhead);
                 uint32_t o = b.p & 31u, base = b.base, w0 = b.w0, w1 = b.w1, w2 = b.w2;
                 bool slow = false;
                 // (no branch but the loop's own inside: a lone warp pays every one of them in full)
@@ -386,11 +425,10 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                     uint32_t e;
                     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(rl_addr + ((win >> 21) & 0x7FCu)));
                     { // the window registers move on by a word when the upper half was used (off the critical path)
-                        const uint32_t* nw = b.w + min(base + 3u, b.wmax);
                         uint32_t w3 = w2;
-                        asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q ld.global.nc.u32 %0, [%1];\n\t}"
+                        asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q ld.shared.u32 %0, [%1];\n\t}"
                                      : "+r"(w3)
-                                     : "l"(nw), "r"(uint32_t(upper)));
+                                     : "r"(b.ring + (((base + 3u) & 127u) << 2)), "r"(uint32_t(upper)));
                         w0 = upper ? w1 : w0;
                         w1 = upper ? w2 : w1;
                         w2 = w3;
@@ -497,6 +535,7 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
 {
     __shared__ ProgHuffDev s_tab[4];
     __shared__ uint8_t s_q[80]; // zero-history positions of the block under way + 16 "behind the band" entries
+    __shared__ uint32_t s_ring[128]; // the scan's words around the current position (PBits)
     __shared__ uint32_t s_rl[512]; // refinement scans: the first-level table pre-decoded for the common-symbol loop
     const int lane = threadIdx.x;
     const uint32_t chain = blockIdx.x;
@@ -557,10 +596,8 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
         }
         const uint32_t byte0 = j ? bd.bnd[ch.bnd_off + j - 1u] : 0u;
         const uint32_t byte1 = j + 1u < sd.n_chain ? bd.bnd[ch.bnd_off + j] : cst.cmp_len;
-        PBits b;
-        b.w = bd.cmp + ch.cmp_off / 4;
-        b.wmax = (ch.raw_len + 15u) / 4u; // inside what the host reserved for this scan (the words past cmp_len are never trusted)
-        pb_seek(b, byte0 * 8u);
+        PBits b; // (wmax: inside what the host reserved for this scan; the words past cmp_len are never trusted)
+        pb_open(b, bd.cmp + ch.cmp_off / 4, (ch.raw_len + 15u) / 4u, pinned_smem_addr(s_ring), uint32_t(lane), byte0 * 8u);
         PMap g;
         const int c0 = sd.comp[0];
         g.wb = max(1u, uint32_t(sd.wb));
