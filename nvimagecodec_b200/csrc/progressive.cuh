@@ -347,10 +347,11 @@ __device__ __forceinline__ void prog_ac_first(PBits& b, const PTab& tab, const P
 //   and each lane only notes the middle term for its two positions (one compare-and-select per symbol); the bits are
 //   fetched and applied once per block.
 constexpr uint32_t kRefCoef = 1u << 9, kRefEob = 1u << 10, kRefBad = 1u << 11;
-// the same for the common-symbol loop, one 32-bit word per nine-bit window: byte 0 = code length + sign bit, byte 1 = run,
-// kFastCoef / kFastBad, kFastEob = end of band for this block only (EOB0: the rest of the band takes correction bits, nothing
-// carries over), kRefSlow = not for that loop (a longer code, or an end-of-band run over several blocks)
-constexpr uint32_t kFastCoef = 1u << 16, kFastEob = 1u << 17, kFastBad = 1u << 18, kRefSlow = 1u << 20;
+// the same for the common-symbol loop, two 32-bit words per nine-bit window.  x: byte 0 = code length + sign bit, byte 1 = run
+// (64 for an end of band that covers this block only, EOB0: the run then stops behind the band, the rest of the band takes
+// correction bits and nothing carries over), kFastBad, kRefSlow = not for that loop (a longer code, or an end-of-band run over
+// several blocks).  y: the sign bit's place in the 32-bit window when the symbol brings a new coefficient, else 0.
+constexpr uint32_t kFastBad = 1u << 18, kRefSlow = 1u << 20;
 // refine_entry: bits 0-4: code length + sign bit; bits 5-8: run
 __device__ __forceinline__ uint32_t refine_entry(uint32_t len, uint32_t sym)
 {
@@ -358,7 +359,7 @@ __device__ __forceinline__ uint32_t refine_entry(uint32_t len, uint32_t sym)
     return (len + (s ? 1u : 0u)) | (r << 5) | (s ? kRefCoef : 0u) | ((s == 0u && r != 15u) ? kRefEob : 0u) | (s > 1u ? kRefBad : 0u);
 }
 
-__device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const uint32_t* s_rl, const PScan& sc, PMap& g, int16_t* coef,
+__device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const uint2* s_rl, const PScan& sc, PMap& g, int16_t* coef,
     uint32_t m0, uint32_t m1, uint32_t lane, uint32_t& err, uint8_t* s_q, PSync& y)
 {
     uint32_t eobrun = 0;
@@ -368,6 +369,8 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
     const uint32_t bandlo = uint32_t(band), bandhi = uint32_t(band >> 32);
     const uint32_t below = (1u << lane) - 1u;
     const uint32_t rl_addr = pinned_smem_addr(s_rl), q_addr = pinned_smem_addr(s_q);
+    for (uint32_t q = 64u + lane; q < 144u; q += 32u) // (the entries behind any list: what an EOB0's run of 64 reads)
+        asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + q), "r"(se + 1u) : "memory");
     uint32_t seen = 0, seen_fast = 0; // every table entry used, or-ed: the "bad" flag is looked at once, after the scan
     // the block after this one is requested while this one is worked on
     pmap_seek(g, m0);
@@ -406,65 +409,70 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
             __syncwarp();
             uint32_t c = 0; // symbol bits of this block so far
             bool overrun = false;
+            (void)pb_peek(b);                // window registers brought to b.p,
+            pb_fill(b, b.base + kRingAhead); // and the ring far enough ahead for the whole block
+            uint32_t w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
 #pragma unroll 1
             for (;;) {
-                // ---- the common symbols: one pass of this loop each, nothing but the parse recurrence on its critical path
-                // (window -> table entry -> position of the zero the run stops at -> next window).  Rare things -- codes longer
-                // than nine bits, end-of-band symbols, a skip of more than a word of correction bits -- leave the loop with
-                // the symbol not yet consumed and are dealt with below.
-                if (k > se)
-                    break;
-                (void)pb_peek(b); // window registers brought to b.p
-                pb_fill(b, b.base + kRingAhead);
-                uint32_t o = b.p & 31u, base = b.base, w0 = b.w0, w1 = b.w1, w2 = b.w2;
+                // ---- the common symbols: one pass of the inner loop each.  A lone warp issues an instruction every other
+                // clock at best, so the loop is kept to the parse recurrence (window -> table entry -> position of the zero
+                // the run stops at -> next window) and a handful of selects; whatever is rare -- a code longer than nine
+                // bits, an end-of-band run over several blocks, the window moving on by a word (every eight symbols or so) --
+                // leaves it with the symbol not yet consumed.
                 bool slow = false;
-                // (no branch but the loop's own inside: a lone warp pays every one of them in full)
                 do {
-                    const bool upper = o >= 32u;
-                    const uint32_t win = upper ? __funnelshift_l(w2, w1, o) : __funnelshift_l(w1, w0, o);
-                    uint32_t e;
-                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(rl_addr + ((win >> 21) & 0x7FCu)));
-                    { // the window registers move on by a word when the upper half was used (off the critical path)
-                        uint32_t w3 = w2;
-                        asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q ld.shared.u32 %0, [%1];\n\t}"
-                                     : "+r"(w3)
-                                     : "r"(b.ring + (((base + 3u) & 127u) << 2)), "r"(uint32_t(upper)));
-                        w0 = upper ? w1 : w0;
-                        w1 = upper ? w2 : w1;
-                        w2 = w3;
-                        base += upper ? 1u : 0u;
-                        o -= upper ? 32u : 0u;
+                    const uint32_t win = __funnelshift_l(w1, w0, o);
+                    uint32_t ex, ey; // table entry: bits consumed / run / flags, and the sign bit's place in the window
+                    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ex), "=r"(ey) : "r"(rl_addr + ((win >> 20) & 0xFF8u)));
+                    if (ex & kRefSlow) {
+                        slow = true;
+                        break;
                     }
-                    const uint32_t r = (e >> 8) & 0xFFu, total = e & 0xFFu;
+                    const uint32_t r = (ex >> 8) & 0xFFu, total = ex & 0xFFu;
                     uint32_t t; // where the symbol stops: the (j + r)-th zero-history position, or behind the band
                     asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t) : "r"(q_addr + j + r));
-                    slow = (e & kRefSlow) != 0u;
-                    const bool take = !slow;
-                    seen_fast |= e;
-                    const bool eob = (e & kFastEob) != 0u;                 // the band ends here: the rest takes correction bits only
-                    t = eob ? se + 1u : t;
-                    const uint32_t zp = eob ? n_z - j : min(r, n_z - j);   // zero-history positions passed
-                    const uint32_t cn = c + total;
-                    clo = (take && lane >= k) ? cn : clo;
-                    chi = (take && lane + 32u >= k) ? cn : chi;
-                    c = take ? cn : c;
-                    const bool place = take && (e & kFastCoef) != 0u;
-                    const int32_t newv = ((win >> ((32u - total) & 31u)) & 1u) ? p1 : -p1;
-                    overrun = overrun || (place && t > se);
-                    lo = (place && lane == t && t <= se) ? newv : lo;
-                    hi = (place && lane + 32u == t && t <= se) ? newv : hi;
-                    o = take ? (o + total - (k + zp)) + t : o; // += total + (positions passed that are not zero-history ones)
-                    k = take ? t + 1u : k;
-                    j = take ? j + r + 1u : j;
-                } while (!slow && k <= se && o < 64u);
+                    seen_fast |= ex;
+                    const uint32_t zp = min(r, n_z - j); // zero-history positions passed
+                    c += total;
+                    clo = lane >= k ? c : clo;
+                    chi = lane + 32u >= k ? c : chi;
+                    const int32_t newv = (win & ey) ? p1 : -p1;
+                    const bool behind = t > se;
+                    const uint32_t tp = (ey != 0u && !behind) ? t : 255u; // where a new coefficient goes, if there is one
+                    overrun = overrun || (ey != 0u && behind);
+                    lo = lane == tp ? newv : lo;
+                    hi = lane + 32u == tp ? newv : hi;
+                    o = (o + total - (k + zp)) + t; // += total + (positions passed that are not zero-history ones)
+                    k = t + 1u;
+                    j += r + 1u;
+                } while (k <= se && o < 32u);
+                j = min(j, n_z);
+                if (!slow) {
+                    if (k > se) {
+                        b.p = base * 32u + o;
+                        b.base = base;
+                        b.w0 = w0;
+                        b.w1 = w1;
+                        b.w2 = w2;
+                        break;
+                    }
+                    if (o < 64u) { // the window moves on by a word
+                        ++base;
+                        w0 = w1;
+                        w1 = w2;
+                        w2 = pb_word(b, base + 2u);
+                        o -= 32u;
+                    } else {       // a longer run of correction bits was skipped
+                        pb_seek(b, base * 32u + o);
+                        w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
+                    }
+                    continue;
+                }
+                b.p = base * 32u + o; // (the plain path works on the reader itself)
                 b.base = base;
                 b.w0 = w0;
                 b.w1 = w1;
                 b.w2 = w2;
-                b.p = base * 32u + o;
-                j = min(j, n_z);
-                if (!slow)
-                    continue; // the band is through, or only the window had to be moved
                 // ---- a rare symbol, the plain way
                 const uint32_t p0 = b.p;
                 const uint32_t sym = pb_symbol(b, tab, err);
@@ -494,6 +502,10 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 }
                 k = t + 1u;
                 j = min(idx + 1u, n_z);
+                if (k > se)
+                    break;
+                (void)pb_peek(b);
+                w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
             }
             if (overrun)
                 err |= kFlagOverrun;
@@ -534,9 +546,9 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
 __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
 {
     __shared__ ProgHuffDev s_tab[4];
-    __shared__ uint8_t s_q[80]; // zero-history positions of the block under way + 16 "behind the band" entries
+    __shared__ uint8_t s_q[144]; // zero-history positions of the block under way; "behind the band" from there on
     __shared__ uint32_t s_ring[128]; // the scan's words around the current position (PBits)
-    __shared__ uint32_t s_rl[512]; // refinement scans: the first-level table pre-decoded for the common-symbol loop
+    __shared__ uint2 s_rl[512]; // refinement scans: the first-level table pre-decoded for the common-symbol loop
     const int lane = threadIdx.x;
     const uint32_t chain = blockIdx.x;
     const ProgScanDev sd = bd.prog_scan[bd.prog_chain[chain]];
@@ -587,10 +599,10 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
                 const uint32_t e = s_tab[0].lut[q];
                 const uint32_t f = e ? refine_entry(e >> 8, e & 0xFFu) : 0u;
                 const uint32_t run = (f >> 5) & 15u;
-                uint32_t v = (f & 31u) | (run << 8) | ((f & kRefCoef) ? kFastCoef : 0u) | ((f & kRefBad) ? kFastBad : 0u);
-                if (f & kRefEob)
-                    v = run ? kRefSlow : ((f & 31u) | kFastEob);
-                s_rl[q] = e ? v : kRefSlow;
+                uint32_t v = (f & 31u) | (run << 8) | ((f & kRefBad) ? kFastBad : 0u);
+                if (f & kRefEob) // an end of band for this block only runs "64 zeros" far, i.e. behind the band
+                    v = run ? kRefSlow : ((f & 31u) | (64u << 8));
+                s_rl[q] = e ? make_uint2(v, (f & kRefCoef) ? 1u << (32u - (f & 31u)) : 0u) : make_uint2(kRefSlow, 0u);
             }
             __syncwarp();
         }

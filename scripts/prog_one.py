@@ -7,6 +7,8 @@ os.environ["B200JPEG_TRACE"] = "1"
 from nvimagecodec_b200 import Decoder, corpus  # noqa: E402
 
 d = Decoder(0, options=":fancy_upsampling=1")
-s = corpus.encode(corpus.synth(1080, 1920, 0), 90, "420", progressive=True)
+q = int(sys.argv[1]) if len(sys.argv) > 1 else 90
+s = corpus.encode(corpus.synth(1080, 1920, 0), q, "420", progressive=True)
+print("quality", q, "bytes", len(s), file=sys.stderr)
 d.decode([s], "I_RGB")
 d.decode([s], "I_RGB")
