@@ -347,7 +347,7 @@ __device__ __forceinline__ void prog_ac_first(PBits& b, const PTab& tab, const P
 //   and each lane only notes the middle term for its two positions (one compare-and-select per symbol); the bits are
 //   fetched and applied once per block.
 constexpr uint32_t kRefCoef = 1u << 9, kRefEob = 1u << 10, kRefBad = 1u << 11;
-// the same for the common-symbol loop, two 32-bit words per nine-bit window.  x: byte 0 = code length + sign bit, byte 1 = run
+// the same for the common-symbol loop, two 32-bit words per nine-bit window.  x: byte 0 = code length + sign bit, byte 3 = run
 // (64 for an end of band that covers this block only, EOB0: the run then stops behind the band, the rest of the band takes
 // correction bits and nothing carries over), kFastBad, kRefSlow = not for that loop (a longer code, or an end-of-band run over
 // several blocks).  y: the sign bit's place in the 32-bit window when the symbol brings a new coefficient, else 0.
@@ -424,13 +424,13 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                     const uint32_t win = __funnelshift_l(w1, w0, o);
                     uint32_t ex, ey; // table entry: bits consumed / run / flags, and the sign bit's place in the window
                     asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ex), "=r"(ey) : "r"(rl_addr + ((win >> 20) & 0xFF8u)));
-                    if (ex & kRefSlow) {
+                    const uint32_t r = ex >> 24, total = ex & 0xFFu;
+                    uint32_t t; // where the symbol stops: the (j + r)-th zero-history position, or behind the band
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t) : "r"(q_addr + j + r));
+                    if (ex & kRefSlow) { // (looked at while the read above is under way)
                         slow = true;
                         break;
                     }
-                    const uint32_t r = (ex >> 8) & 0xFFu, total = ex & 0xFFu;
-                    uint32_t t; // where the symbol stops: the (j + r)-th zero-history position, or behind the band
-                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t) : "r"(q_addr + j + r));
                     seen_fast |= ex;
                     const uint32_t zp = min(r, n_z - j); // zero-history positions passed
                     c += total;
@@ -599,9 +599,9 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
                 const uint32_t e = s_tab[0].lut[q];
                 const uint32_t f = e ? refine_entry(e >> 8, e & 0xFFu) : 0u;
                 const uint32_t run = (f >> 5) & 15u;
-                uint32_t v = (f & 31u) | (run << 8) | ((f & kRefBad) ? kFastBad : 0u);
+                uint32_t v = (f & 31u) | (run << 24) | ((f & kRefBad) ? kFastBad : 0u);
                 if (f & kRefEob) // an end of band for this block only runs "64 zeros" far, i.e. behind the band
-                    v = run ? kRefSlow : ((f & 31u) | (64u << 8));
+                    v = run ? kRefSlow : ((f & 31u) | (64u << 24));
                 s_rl[q] = e ? make_uint2(v, (f & kRefCoef) ? 1u << (32u - (f & 31u)) : 0u) : make_uint2(kRefSlow, 0u);
             }
             __syncwarp();
