@@ -56,7 +56,7 @@ enum {
 typedef struct {
     int width, height, num_components;
     int h[4], v[4];          /* sampling factors per component */
-    int sof_marker;          /* 0xC0 baseline, 0xC2 progressive ... */
+    int sof_marker;          /* 0xC0 baseline, 0xC1 extended sequential, 0xC2 progressive ... */
     int precision;
     int restart_interval;    /* in MCUs, 0 = none */
     int num_scans_seen;      /* 1 for single interleaved scan */
@@ -93,7 +93,10 @@ B200JPEG_API int b200jpegProbe(const void* data, size_t length, b200jpegStreamIn
 
 /* Create / destroy a decoder bound to one GPU.  options is the nvImageCodec
  * option string ("<id>:<name>=<value>" tokens, include/nvimgcodec.h:1967-1971);
- * understood: fancy_upsampling=<0|1> (default 1, as libjpeg_turbo_decoder.cpp:223-249).
+ * understood: fancy_upsampling=<0|1> (default 1, as libjpeg_turbo_decoder.cpp:223-249); progressive=<0|1> (default 1: complete
+ * progressive SOF2 streams are decoded -- a throughput path, one warp per scan; 0: declined with
+ * B200JPEG_ERR_UNSUPPORTED), progressive_min_batch=<n> (default 1: progressive streams are taken only in batches that hold
+ * at least n of them, fewer are declined).
  * Tuning knobs (defaults are measured choices, results do not depend on them): subseq_bits=<512|1024|2048|4096>
  * (bits of entropy-coded data per GPU thread; default by batch size), lanes=<1..8> (pipeline lanes, default 6),
  * chunk_mb / chunk_images (pipeline chunk, default 8 MB of bitstream or 64 images),
