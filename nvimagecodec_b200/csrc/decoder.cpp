@@ -1763,7 +1763,18 @@ int Pipeline::decode(int n, const void* const* data, const size_t* len, const b2
             chunk_bytes = size_t(8) << 20;
         }
         const int chunk_images = opt_.chunk_images;
-        const bool split = lanes_.size() > 1 && (total > chunk_bytes + chunk_bytes / 3 || n > 2 * chunk_images);
+        // Progressive streams decode one warp per scan, each scan a serial chain: such a batch takes about as long as its
+        // longest scan however many images it holds, so cutting it up would only queue those latencies one behind the other.
+        bool any_progressive = false;
+        if (opt_.progressive)
+            for (int i = 0; i < n && !any_progressive; ++i) {
+                if (parsed && parsed[i]) {
+                    any_progressive = parsed[i]->status == kStreamProgressive;
+                } else if (data[i]) {
+                    any_progressive = sof_marker_of(static_cast<const uint8_t*>(data[i]), len[i]) == 0xC2;
+                }
+            }
+        const bool split = !any_progressive && lanes_.size() > 1 && (total > chunk_bytes + chunk_bytes / 3 || n > 2 * chunk_images);
         for (int i = 0; i < n; ++i) {
             acc += len[i];
             ++cnt;

@@ -406,6 +406,31 @@ int max_jpeg_scans()
 
 } // namespace
 
+int sof_marker_of(const uint8_t* d, size_t n)
+{
+    if (n < 4 || d[0] != 0xFF || d[1] != 0xD8)
+        return 0;
+    size_t p = 2;
+    while (p + 4 <= n && d[p] == 0xFF) {
+        while (p < n && d[p] == 0xFF)
+            ++p;
+        if (p >= n)
+            return 0;
+        const int m = d[p++];
+        if (m == 0xD8 || m == 0x01 || (m >= 0xD0 && m <= 0xD7))
+            continue;
+        if (m == 0xDA || m == 0xD9 || p + 2 > n)
+            return 0;
+        if (m >= 0xC0 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC)
+            return m;
+        const size_t len = be16(d + p);
+        if (len < 2)
+            return 0;
+        p += len;
+    }
+    return 0;
+}
+
 StreamStatus parse_progressive(const uint8_t* d, size_t n, StreamHeader* frame, ProgStream* out)
 {
     out->scans.clear();

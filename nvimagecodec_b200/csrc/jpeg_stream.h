@@ -76,6 +76,8 @@ struct ProgStream {
     int n_waves = 0;
 };
 StreamStatus parse_progressive(const uint8_t* data, size_t len, StreamHeader* frame, ProgStream* out);
+// The SOFn marker byte of a stream (0xC0 .. 0xCF), 0 if none is found before the first scan: segment headers only, no tables read.
+int sof_marker_of(const uint8_t* data, size_t len);
 
 // Device image of one Huffman table for the progressive scan kernel (progressive.cuh): plain symbols, not the packed
 // actions of the sequential kernels -- a progressive symbol's meaning depends on the scan type.
