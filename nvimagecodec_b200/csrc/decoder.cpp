@@ -629,7 +629,10 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                 host_status_[i] = B200JPEG_ERR_CORRUPT;
                 continue;
             }
-            if (blocks * 192 > (uint64_t(opt_.max_arena_mb) << 20) || coef_elems / 64 + blocks >= (uint64_t(1) << 28)) {
+            uint64_t chains = 0; // one warp (and a few words of bookkeeping) per restart interval of every scan
+            for (const ProgScan& ps : pi.prog->scans)
+                chains += ps.restart_interval ? uint64_t((ps.mcus + ps.restart_interval - 1) / ps.restart_interval) : 1u;
+            if (blocks * 192 > (uint64_t(opt_.max_arena_mb) << 20) || coef_elems / 64 + blocks >= (uint64_t(1) << 28) || chains > (uint64_t(1) << 20)) {
                 host_status_[i] = B200JPEG_ERR_TOO_LARGE;
                 continue;
             }
