@@ -106,3 +106,33 @@ def test_progressive_can_be_switched_off(decoder_cls):
         assert d.last_status == [_lib.ERR_UNSUPPORTED]
     finally:
         d.close()
+
+
+def test_sixteen_bit_quantisation_tables(decoder_cls):
+    """Quantisers above 255 (DQT with Pq = 1: extended-sequential and progressive streams only) take the IDCT stage's plain
+    dequantisation path instead of the packed dot products -- from the entry stream, from dense groups and from progressive
+    blocks."""
+    import io
+
+    PIL = pytest.importorskip("PIL.Image")
+    from nvimagecodec_b200 import _lib, corpus
+
+    srcs = []
+    for k, (h, w) in enumerate([(120, 168), (64, 64), (250, 333)]):
+        img = corpus.synth(h, w, 40 + k)
+        qt = [min(1000, 16 + (12 + 3 * k) * i) for i in range(64)]
+        for prog in (False, True):
+            for sub in (0, 2):
+                buf = io.BytesIO()
+                PIL.fromarray(img).save(buf, format="JPEG", qtables=[qt, qt], subsampling=sub, progressive=prog)
+                srcs.append(buf.getvalue())
+    assert any(s[s.find(b"\xff\xdb") + 4] >> 4 == 1 for s in srcs)  # 16-bit tables are really in there
+    for opts in (":fancy_upsampling=1", ":fancy_upsampling=1 :entry_stream=0"):
+        d = decoder_cls(0, options=opts)
+        try:
+            outs = d.decode(srcs, "I_RGB")
+            assert d.last_status == [_lib.OK] * len(srcs)
+            for i, (s, o) in enumerate(zip(srcs, outs)):
+                assert np.array_equal(o.cpu().numpy(), oracle.decode(s, oracle.FMT_I_RGB, fancy=True)), (opts, i)
+        finally:
+            d.close()
