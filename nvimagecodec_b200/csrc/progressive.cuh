@@ -420,12 +420,10 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 // bits, an end-of-band run over several blocks, the window moving on by a word (every eight symbols or so) --
                 // leaves it with the symbol not yet consumed.
                 bool slow = false;
-                // (the table entry of the next symbol is requested as soon as its window is known, ahead of the loop's
-                // own test; the window registers move on inside the loop with predicated instructions, off the recurrence)
-                uint32_t win = __funnelshift_l(w1, w0, o);
-                uint32_t ex, ey; // table entry: bits consumed / run / flags, and the sign bit's place in the window
-                asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ex), "=r"(ey) : "r"(rl_addr + ((win >> 20) & 0xFF8u)));
                 do {
+                    const uint32_t win = __funnelshift_l(w1, w0, o);
+                    uint32_t ex, ey; // table entry: bits consumed / run / flags, and the sign bit's place in the window
+                    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ex), "=r"(ey) : "r"(rl_addr + ((win >> 20) & 0xFF8u)));
                     const uint32_t r = ex >> 24, total = ex & 0xFFu;
                     uint32_t t; // where the symbol stops: the (j + r)-th zero-history position, or behind the band
                     asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t) : "r"(q_addr + j + r));
@@ -439,29 +437,12 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                     clo = lane >= k ? c : clo;
                     chi = lane + 32u >= k ? c : chi;
                     const int32_t newv = (win & ey) ? p1 : -p1;
-                    const uint32_t had = ey;
-                    o = (o + total - (k + zp)) + t; // += total + (positions passed that are not zero-history ones)
-                    // the next symbol's window and table entry (meaningless, and harmless, when the loop ends here)
-                    const bool upper = o >= 32u;
-                    win = upper ? __funnelshift_l(w2, w1, o) : __funnelshift_l(w1, w0, o);
-                    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ex), "=r"(ey) : "r"(rl_addr + ((win >> 20) & 0xFF8u)));
-                    { // the window registers move on by a word when the upper half was used
-                        uint32_t w3 = w2;
-                        asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q ld.shared.u32 %0, [%1];\n\t}"
-                                     : "+r"(w3)
-                                     : "r"(b.ring + (((base + 3u) & 127u) << 2)), "r"(uint32_t(upper && o < 64u)));
-                        const bool step = upper && o < 64u;
-                        w0 = step ? w1 : w0;
-                        w1 = step ? w2 : w1;
-                        w2 = w3;
-                        base += step ? 1u : 0u;
-                        o -= step ? 32u : 0u;
-                    }
                     const bool behind = t > se;
-                    const uint32_t tp = (had != 0u && !behind) ? t : 255u; // where a new coefficient goes, if there is one
-                    overrun = overrun || (had != 0u && behind);
+                    const uint32_t tp = (ey != 0u && !behind) ? t : 255u; // where a new coefficient goes, if there is one
+                    overrun = overrun || (ey != 0u && behind);
                     lo = lane == tp ? newv : lo;
                     hi = lane + 32u == tp ? newv : hi;
+                    o = (o + total - (k + zp)) + t; // += total + (positions passed that are not zero-history ones)
                     k = t + 1u;
                     j += r + 1u;
                 } while (k <= se && o < 32u);
@@ -475,9 +456,16 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                         b.w2 = w2;
                         break;
                     }
-                    // a run of correction bits longer than the window registers reach was skipped
-                    pb_seek(b, base * 32u + o);
-                    w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
+                    if (o < 64u) { // the window moves on by a word
+                        ++base;
+                        w0 = w1;
+                        w1 = w2;
+                        w2 = pb_word(b, base + 2u);
+                        o -= 32u;
+                    } else {       // a longer run of correction bits was skipped
+                        pb_seek(b, base * 32u + o);
+                        w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
+                    }
                     continue;
                 }
                 b.p = base * 32u + o; // (the plain path works on the reader itself)
