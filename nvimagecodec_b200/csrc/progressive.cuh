@@ -349,9 +349,10 @@ __device__ __forceinline__ void prog_ac_first(PBits& b, const PTab& tab, const P
 constexpr uint32_t kRefCoef = 1u << 9, kRefEob = 1u << 10, kRefBad = 1u << 11;
 // the same for the common-symbol loop, two 32-bit words per nine-bit window.  x: byte 0 = code length + sign bit, byte 3 = run
 // (64 for an end of band that covers this block only, EOB0: the run then stops behind the band, the rest of the band takes
-// correction bits and nothing carries over), kFastBad, kRefSlow = not for that loop (a longer code, or an end-of-band run over
-// several blocks).  y: the sign bit's place in the 32-bit window when the symbol brings a new coefficient, else 0.
-constexpr uint32_t kFastBad = 1u << 18, kRefSlow = 1u << 20;
+// correction bits and nothing carries over), kRefSlow = not for that loop (a longer code, an end-of-band run over several
+// blocks, a new coefficient of more than one bit).  y: the sign bit's place in the 32-bit window when the symbol brings a new coefficient, else 0.
+constexpr uint32_t kRefSlow = 1u << 20;
+constexpr uint32_t kBehind = 128u; // mark on the zero-list entries that stand for "behind the band" (positions are < 64)
 // refine_entry: bits 0-4: code length + sign bit; bits 5-8: run
 __device__ __forceinline__ uint32_t refine_entry(uint32_t len, uint32_t sym)
 {
@@ -370,8 +371,8 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
     const uint32_t below = (1u << lane) - 1u;
     const uint32_t rl_addr = pinned_smem_addr(s_rl), q_addr = pinned_smem_addr(s_q);
     for (uint32_t q = 64u + lane; q < 144u; q += 32u) // (the entries behind any list: what an EOB0's run of 64 reads)
-        asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + q), "r"(se + 1u) : "memory");
-    uint32_t seen = 0, seen_fast = 0; // every table entry used, or-ed: the "bad" flag is looked at once, after the scan
+        asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + q), "r"(se + 1u + kBehind) : "memory");
+    uint32_t seen = 0; // every entry of the plain path, or-ed: the "bad" flag is looked at once, after the scan
     // the block after this one is requested while this one is worked on
     pmap_seek(g, m0);
     ps_need(y, min(m1, m0 + 1u));
@@ -405,7 +406,7 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
             if ((zhi >> lane) & 1u)
                 asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + n_zlo + uint32_t(__popc(zhi & below))), "r"(lane + 32u) : "memory");
             if (lane < 16u) // "no such zero": a run that reaches past the last one stops behind the band
-                asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + n_z + lane), "r"(se + 1u) : "memory");
+                asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + n_z + lane), "r"(se + 1u + kBehind) : "memory");
             __syncwarp();
             uint32_t c = 0; // symbol bits of this block so far
             bool overrun = false;
@@ -420,32 +421,34 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 // bits, an end-of-band run over several blocks, the window moving on by a word (every eight symbols or so) --
                 // leaves it with the symbol not yet consumed.
                 bool slow = false;
+                uint32_t t, ey; // (looked at once more behind the loop)
                 do {
                     const uint32_t win = __funnelshift_l(w1, w0, o);
-                    uint32_t ex, ey; // table entry: bits consumed / run / flags, and the sign bit's place in the window
+                    uint32_t ex; // table entry: ex = bits consumed / run / flags, ey = the sign bit's place in the window
                     asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ex), "=r"(ey) : "r"(rl_addr + ((win >> 20) & 0xFF8u)));
                     const uint32_t r = ex >> 24, total = ex & 0xFFu;
-                    uint32_t t; // where the symbol stops: the (j + r)-th zero-history position, or behind the band
+                    // where the symbol stops: the (j + r)-th zero-history position, or kBehind + the position behind the band
                     asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t) : "r"(q_addr + j + r));
                     if (ex & kRefSlow) { // (looked at while the read above is under way)
                         slow = true;
                         break;
                     }
-                    seen_fast |= ex;
                     const uint32_t zp = min(r, n_z - j); // zero-history positions passed
                     c += total;
                     clo = lane >= k ? c : clo;
                     chi = lane + 32u >= k ? c : chi;
                     const int32_t newv = (win & ey) ? p1 : -p1;
-                    const bool behind = t > se;
-                    const uint32_t tp = (ey != 0u && !behind) ? t : 255u; // where a new coefficient goes, if there is one
-                    overrun = overrun || (ey != 0u && behind);
-                    lo = lane == tp ? newv : lo;
-                    hi = lane + 32u == tp ? newv : hi;
+                    lo = (ey != 0u && lane == t) ? newv : lo; // (no lane owns a position behind the band)
+                    hi = (ey != 0u && lane + 32u == t) ? newv : hi;
                     o = (o + total - (k + zp)) + t; // += total + (positions passed that are not zero-history ones)
                     k = t + 1u;
                     j += r + 1u;
                 } while (k <= se && o < 32u);
+                if (!slow && (t & kBehind)) { // the band ended: take the mark out of the position again
+                    o -= kBehind;
+                    k -= kBehind;
+                    overrun = overrun || ey != 0u; // a new coefficient with no place left for it
+                }
                 j = min(j, n_z);
                 if (!slow) {
                     if (k > se) {
@@ -489,7 +492,6 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 const int32_t newv = (e & kRefCoef) ? ((pb_word(b, (b.p - 1u) >> 5) >> (31u - ((b.p - 1u) & 31u))) & 1u ? p1 : -p1) : 0;
                 const uint32_t idx = j + r;
                 const bool found = idx < n_z;
-                uint32_t t;
                 asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t) : "r"(q_addr + min(idx, 79u)));
                 t = found ? t : se + 1u;
                 b.p += (t - k) - (found ? r : n_z - j);
@@ -538,7 +540,7 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
         if (hi != hi0)
             cur[lane + 32] = int16_t(hi);
     }
-    if ((seen & kRefBad) || (seen_fast & kFastBad))
+    if (seen & kRefBad)
         err |= kFlagBadHuffman; // a new coefficient of more than one bit (libjpeg warns and goes on)
 }
 
@@ -599,7 +601,7 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
                 const uint32_t e = s_tab[0].lut[q];
                 const uint32_t f = e ? refine_entry(e >> 8, e & 0xFFu) : 0u;
                 const uint32_t run = (f >> 5) & 15u;
-                uint32_t v = (f & 31u) | (run << 24) | ((f & kRefBad) ? kFastBad : 0u);
+                uint32_t v = (f & kRefBad) ? kRefSlow : ((f & 31u) | (run << 24));
                 if (f & kRefEob) // an end of band for this block only runs "64 zeros" far, i.e. behind the band
                     v = run ? kRefSlow : ((f & 31u) | (64u << 24));
                 s_rl[q] = e ? make_uint2(v, (f & kRefCoef) ? 1u << (32u - (f & 31u)) : 0u) : make_uint2(kRefSlow, 0u);
