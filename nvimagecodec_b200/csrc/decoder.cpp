@@ -896,8 +896,10 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
                     bool known = before < 0;
                     for (int q = 0; q < sd.n_pred; ++q)
                         known = known || sd.pred[q] == uint32_t(before);
-                    if (!known)
+                    if (!known) {
                         sd.pred[sd.n_pred++] = uint32_t(before);
+                        prog_scans[size_t(before)].followed = 1;
+                    }
                     last_scan[cls][ps.comp[k]] = int(prog_scans.size());
                 }
                 if (sd.n_pred == 1) {

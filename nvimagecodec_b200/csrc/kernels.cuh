@@ -120,6 +120,7 @@ struct ProgScanDev {
     uint32_t pred[4];       // scans (BatchDev::prog_scan indices, all lower than this one's) that last wrote coefficients of the
     uint8_t n_pred;         //   same components and class (DC / AC) -- this scan follows them block by block when the MCU order
     uint8_t pred_fine;      //   and restart interval agree (pred_fine: exactly one predecessor), else waits for their end
+    uint8_t followed;       // some later scan names this one as a predecessor: its chains publish their progress
     uint32_t ri, n_mcu;     // restart interval and size of the scan in ITS MCUs
     uint16_t wb, hb;        // one-component scan: the component's block columns / rows
     uint8_t ncomp, comp[4], ss, se, ah, al;

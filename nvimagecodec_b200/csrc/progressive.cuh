@@ -211,7 +211,7 @@ __device__ __forceinline__ void ps_need(PSync& y, uint32_t m_excl) // the predec
 }
 __device__ __forceinline__ void ps_publish(PSync& y, uint32_t m_done, bool force, uint32_t lane)
 {
-    if (!force && m_done < y.published + 16u)
+    if (y.mine == nullptr || (!force && m_done < y.published + 16u)) // (nobody follows the last scan of a component)
         return;
     y.published = m_done;
     __syncwarp();
@@ -562,7 +562,7 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
     const uint32_t m0 = sd.ri ? j * sd.ri : 0u, m1 = sd.ri ? min(sd.n_mcu, m0 + sd.ri) : sd.n_mcu;
     const long long clk0 = clock64();
     PSync y;
-    y.mine = bd.prog_progress + chain;
+    y.mine = sd.followed ? bd.prog_progress + chain : nullptr;
     y.published = m0;
     y.pred = nullptr;
     y.avail = 0u;
