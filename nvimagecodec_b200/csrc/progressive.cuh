@@ -11,13 +11,14 @@
 // of one scan (the whole scan when there are no restarts) -- decoded front to back by ONE WARP whose lanes all run the
 // same parse (same bit window, same state: no divergence, table lookups broadcast from shared memory) and share the
 // per-block work: lane l owns the coefficients at zig-zag positions l and l + 32, so the history mask of a block is two
-// ballots, a run of r zero-history positions is found with bit operations on that mask, and all correction bits of a
-// symbol (or of a whole block inside an end-of-band run) are applied in one step.
+// ballots, the positions of its zero-history coefficients are listed once per block in shared memory (a run of r of them
+// is one read of that list), and the correction bits of a block are fetched and applied by all lanes at once.
 //
 // All chains of a batch run in ONE launch.  A scan that refines what an earlier scan of the same image wrote does not wait
 // for that scan to end: block m of a scan depends on block m of its predecessor only, so every chain publishes how far it
 // has come (BatchDev::prog_progress, release store every few blocks) and a successor chain follows it a few blocks behind
-// (acquire loads; coefficient reads go to L2, `ld.global.cg`, since another SM wrote them in the same launch).  The ten
+// (relaxed polls and one fence per successful wait; coefficient reads go to L2, `ld.global.cg`, since another SM wrote
+// them in the same launch; the last scan of a component, which nobody follows, publishes nothing).  The ten
 // scans of a typical stream thus decode side by side, and an image takes about as long as its longest scan instead of the
 // sum.  Chains are numbered so that a predecessor always has the lower index (image by image, scans in file order): with
 // CTAs dispatched in index order a waiting chain's predecessor is resident or finished, whatever the grid size.
