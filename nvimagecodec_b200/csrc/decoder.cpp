@@ -871,7 +871,7 @@ int Decoder::prepare(int n, const void* const* data, const size_t* len, const b2
             gate[1] = gate[2] = gate[0];
         im.multi = role == kParent ? 1 : 0;
         if (role == kProg) {
-            // the scans just pushed are this image's; their chains are laid out by wave once every image is known
+            // the scans just pushed are this image's: their chains follow, in file order (a predecessor has the lower index)
             const ParsedInput& pi = (parsed && parsed[i]) ? *parsed[i] : parsed_own_[size_t(i)];
             const ProgStream& pg = *pi.prog;
             im.prog = 1;
@@ -1312,7 +1312,7 @@ int Decoder::execute(cudaStream_t stream)
     launches_ += launch_write(bd_, false, stream); // writes every coefficient exactly once: no clearing pass
     mark(4, stream);
     launches_ += launch_dc_scan(bd_, false, stream);
-    if (bd_.n_prog_img) { // progressive images: their scans accumulate into zeroed blocks, wave by wave
+    if (bd_.n_prog_img) { // progressive images: their scans accumulate into zeroed blocks
         cudaMemsetAsync(bd_.pcoef, 0, pcoef_bytes_, stream);
         launches_ += launch_progressive(bd_, stream);
         if (trace_enabled()) { // how long every chain took (thousands of SM clocks), with its scan's parameters

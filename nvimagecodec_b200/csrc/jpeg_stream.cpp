@@ -435,7 +435,6 @@ StreamStatus parse_progressive(const uint8_t* d, size_t n, StreamHeader* frame, 
 {
     out->scans.clear();
     out->tables.clear();
-    out->n_waves = 0;
     StreamHeader cur;
     for (int c = 0; c < 2; ++c)
         for (int t = 0; t < 4; ++t)
@@ -445,12 +444,10 @@ StreamStatus parse_progressive(const uint8_t* d, size_t n, StreamHeader* frame, 
     size_t p = 2;
     bool have_sof = false;
     int coef_bits[kMaxComp][64]; // bits still missing per coefficient, -1 = never sent (jdphuff.c coef_bits)
-    int last_wave[kMaxComp][64];
     int table_of[2][4] = {{-1, -1, -1, -1}, {-1, -1, -1, -1}}; // tables already copied for the specs in force
     for (int c = 0; c < kMaxComp; ++c)
         for (int k = 0; k < 64; ++k) {
             coef_bits[c][k] = -1;
-            last_wave[c][k] = -1;
         }
     for (;;) {
         if (p + 2 > n)
@@ -581,13 +578,8 @@ StreamStatus parse_progressive(const uint8_t* d, size_t n, StreamHeader* frame, 
                     if (sc.ah != (coef_bits[c][k] < 0 ? 0 : coef_bits[c][k]))
                         return kStreamUnsupported; // out-of-order refinement (libjpeg warns and goes on)
                     coef_bits[c][k] = sc.al;
-                    sc.wave = std::max(sc.wave, last_wave[c][k] + 1);
                 }
             }
-            for (int i = 0; i < ns; ++i)
-                for (int k = sc.ss; k <= sc.se; ++k)
-                    last_wave[sc.comp[i]][k] = sc.wave;
-            out->n_waves = std::max(out->n_waves, sc.wave + 1);
             if (!(sc.ss == 0 && sc.ah != 0)) { // every scan type but DC refinement decodes Huffman symbols
                 for (int i = 0; i < ns; ++i) {
                     const int cls = sc.ss ? 1 : 0, id = sc.ss ? ta[i] : td[i];

@@ -53,9 +53,7 @@ StreamStatus parse_multiscan(const uint8_t* data, size_t len, StreamHeader* fram
 // Progressive streams (SOF2, Huffman, 8 bits): parse_stream answers kStreamProgressive for them and this walk lists the
 // scans (T.81 G.1: spectral selection Ss..Se, successive approximation Ah/Al; jdphuff.c start_pass_phuff_decoder checks).
 // Every scan keeps a copy of the Huffman tables in force at its SOS (they are usually redefined before every scan).
-// `wave` orders the scans of one image for the device: scans of the same wave touch disjoint coefficients (other
-// components or other bands) and may decode concurrently; a scan's wave is one more than the latest wave that wrote
-// any coefficient of its band.  Only complete progressions are taken (every coefficient of every component refined
+// Only complete progressions are taken (every coefficient of every component refined
 // down to its last bit): libjpeg smooths blocks of incomplete ones (jdcoefct.c smoothing_ok), so those stay with
 // the CPU decoders.  The scan-count limit is NVIMGCODEC_MAX_JPEG_SCANS (default 256), as in
 // extensions/libjpeg_turbo/jpeg_handle.cpp:38-75.
@@ -68,12 +66,10 @@ struct ProgScan {
     int mcus = 0;                // MCUs of this scan
     int wb = 0, hb = 0;          // one-component scan: block columns / rows of the component, ceil(size / 8)
     size_t offset = 0, length = 0; // entropy-coded segment, up to and including the marker that ends it
-    int wave = 0;
 };
 struct ProgStream {
     std::vector<ProgScan> scans;
     std::vector<HuffSpec> tables;
-    int n_waves = 0;
 };
 StreamStatus parse_progressive(const uint8_t* data, size_t len, StreamHeader* frame, ProgStream* out);
 // The SOFn marker byte of a stream (0xC0 .. 0xCF), 0 if none is found before the first scan: segment headers only, no tables read.
