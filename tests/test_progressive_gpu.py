@@ -136,3 +136,20 @@ def test_sixteen_bit_quantisation_tables(decoder_cls):
                 assert np.array_equal(o.cpu().numpy(), oracle.decode(s, oracle.FMT_I_RGB, fancy=True)), (opts, i)
         finally:
             d.close()
+
+
+def test_progressive_random_shapes_and_qualities(dec):
+    """Forty random progressive streams (sizes 1..700, quality 15..98, every sampling, restart intervals, gray) in one batch,
+    box and triangle upsampling."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    rng = np.random.default_rng(2024)
+    srcs = []
+    for k in range(40):
+        h, w = int(rng.integers(1, 700)), int(rng.integers(1, 700))
+        srcs.append(corpus.encode(corpus.synth(h, w, 4000 + k), int(rng.integers(15, 99)), ("420", "444", "422", "440", "411")[k % 5],
+                                  rst_interval=int(rng.integers(0, 6)) if k % 3 == 0 else 0, gray=(k % 11 == 10), progressive=True))
+    outs = dec.decode(srcs, "I_RGB")
+    assert dec.last_status == [_lib.OK] * len(srcs)
+    for i, (s, o) in enumerate(zip(srcs, outs)):
+        assert np.array_equal(o.cpu().numpy(), oracle.decode(s, oracle.FMT_I_RGB, fancy=True)), i
