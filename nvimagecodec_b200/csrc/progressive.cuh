@@ -192,8 +192,9 @@ __device__ __forceinline__ uint32_t pmap_block_at(const PMap& g, uint32_t m) // 
 struct PSync {
     const uint32_t* pred;  // progress word of the predecessor chain (nullptr: none)
     uint32_t avail;        // blocks [.., avail) of the predecessor are known to be finished
-    uint32_t* mine;        // progress word of this chain
+    uint32_t* mine;        // progress word of this chain (nullptr: nobody follows it)
     uint32_t published;
+    bool one_writer;       // only lane 0 stores coefficients in this scan type: its release store alone orders them
 };
 __device__ __forceinline__ void ps_need(PSync& y, uint32_t m_excl) // the predecessor must have finished its MCUs below m_excl
 {
@@ -215,8 +216,10 @@ __device__ __forceinline__ void ps_publish(PSync& y, uint32_t m_done, bool force
     if (y.mine == nullptr || (!force && m_done < y.published + 16u)) // (nobody follows the last scan of a component)
         return;
     y.published = m_done;
-    __syncwarp();
-    __threadfence();
+    if (!y.one_writer) { // every lane stored: all of it has to be visible before the progress word says so
+        __syncwarp();
+        __threadfence();
+    }
     if (lane == 0u)
         asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(y.mine), "r"(m_done) : "memory");
 }
@@ -287,11 +290,26 @@ __device__ __forceinline__ void prog_dc_refine(PBits& b, const PScan& sc, const 
 }
 
 // AC, first pass (decode_mcu_AC_first): run/size symbols inside the band, end-of-band runs over whole blocks.
-__device__ __forceinline__ void prog_ac_first(PBits& b, const PTab& tab, const PScan& sc, PMap& g, int16_t* coef, uint32_t m0, uint32_t m1,
-    int lane, uint32_t& err, PSync& y)
+// The common symbols go through a pre-decoded table like those of the refinement scans (s_fl: one word per nine-bit window --
+// byte 0 = code length + magnitude bits, bits 8-11 = magnitude bits, byte 3 = run; an end of band for this block only is a run
+// of 64, i.e. past the band) in a loop whose recurrence is window -> table entry -> next window; codes longer than nine bits
+// and end-of-band runs over several blocks (kRefSlow) take the plain path.
+constexpr uint32_t kRefSlow = 1u << 20;
+__device__ __forceinline__ uint32_t first_entry(uint32_t len, uint32_t sym)
+{
+    const uint32_t r = sym >> 4, s = sym & 15u;
+    if (s == 0u && r != 15u)
+        return r ? kRefSlow : (len | (64u << 24));
+    return (len + s) | (s << 8) | (r << 24);
+}
+
+__device__ __forceinline__ void prog_ac_first(PBits& b, const PTab& tab, const uint32_t* s_fl, const PScan& sc, PMap& g, int16_t* coef,
+    uint32_t m0, uint32_t m1, int lane, uint32_t& err, PSync& y)
 {
     uint32_t eobrun = 0;
     const uint32_t ss = sc.ss, se = sc.se;
+    const uint32_t fl_addr = pinned_smem_addr(s_fl);
+    bool overrun = false;
     pmap_seek(g, m0);
 #pragma unroll 1
     for (uint32_t m = m0; m < m1; ++m) {
@@ -308,28 +326,76 @@ __device__ __forceinline__ void prog_ac_first(PBits& b, const PTab& tab, const P
         int16_t* cb = coef + size_t(pmap_block(g)) * 64;
         pmap_advance(g, 1u);
         uint32_t k = ss;
+        (void)pb_peek(b);                // window registers brought to b.p,
+        pb_fill(b, b.base + kRingAhead); // and the ring far enough ahead for the whole block
+        uint32_t w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
 #pragma unroll 1
-        while (k <= se) {
+        for (;;) {
+            bool slow = false;
+            do {
+                const uint32_t win = __funnelshift_l(w1, w0, o);
+                uint32_t e;
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(fl_addr + ((win >> 21) & 0x7FCu)));
+                if (e & kRefSlow) {
+                    slow = true;
+                    break;
+                }
+                const uint32_t total = e & 0xFFu, s = (e >> 8) & 15u;
+                k += e >> 24;
+                const uint32_t raw = (win >> ((32u - total) & 31u)) & ((1u << s) - 1u);
+                const int32_t v = pb_extend(raw, s);
+                overrun = overrun || (s != 0u && k > se);
+                if (s != 0u && k <= se && lane == 0)
+                    cb[k] = int16_t(v << sc.al);
+                ++k;
+                o += total;
+            } while (k <= se && o < 32u);
+            if (!slow) {
+                if (k > se)
+                    break;
+                ++base; // the window moves on by a word (a symbol takes 24 bits at most)
+                w0 = w1;
+                w1 = w2;
+                w2 = pb_word(b, base + 2u);
+                o -= 32u;
+                continue;
+            }
+            // ---- a rare symbol, the plain way
+            b.p = base * 32u + o;
+            b.base = base;
+            b.w0 = w0;
+            b.w1 = w1;
+            b.w2 = w2;
             const uint32_t sym = pb_symbol(b, tab, err);
             const uint32_t r = sym >> 4, s = sym & 15u;
             if (s) {
                 k += r;
                 const int32_t v = pb_extend(pb_get(b, s), s);
                 if (k > se) {
-                    err |= kFlagOverrun;
-                    break;
-                }
-                if (lane == 0)
+                    overrun = true;
+                } else if (lane == 0) {
                     cb[k] = int16_t(v << sc.al);
+                }
                 ++k;
             } else if (r == 15u) {
                 k += 16u;
             } else {
                 eobrun = (1u << r) + pb_get(b, r) - 1u; // this block is the first of the run
-                break;
+                k = se + 1u;
             }
+            (void)pb_peek(b);
+            w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
+            if (k > se)
+                break;
         }
+        b.p = base * 32u + o;
+        b.base = base;
+        b.w0 = w0;
+        b.w1 = w1;
+        b.w2 = w2;
     }
+    if (overrun)
+        err |= kFlagOverrun;
 }
 
 // ---- AC, refinement (decode_mcu_AC_refine)
@@ -352,7 +418,6 @@ constexpr uint32_t kRefCoef = 1u << 9, kRefEob = 1u << 10, kRefBad = 1u << 11;
 // (64 for an end of band that covers this block only, EOB0: the run then stops behind the band, the rest of the band takes
 // correction bits and nothing carries over), kRefSlow = not for that loop (a longer code, an end-of-band run over several
 // blocks, a new coefficient of more than one bit).  y: the sign bit's place in the 32-bit window when the symbol brings a new coefficient, else 0.
-constexpr uint32_t kRefSlow = 1u << 20;
 constexpr uint32_t kBehind = 128u; // mark on the zero-list entries that stand for "behind the band" (positions are < 64)
 // refine_entry: bits 0-4: code length + sign bit; bits 5-8: run
 __device__ __forceinline__ uint32_t refine_entry(uint32_t len, uint32_t sym)
@@ -565,6 +630,7 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
     PSync y;
     y.mine = sd.followed ? bd.prog_progress + chain : nullptr;
     y.published = m0;
+    y.one_writer = sd.ah == 0; // first scans (DC and AC) store through lane 0 only
     y.pred = nullptr;
     y.avail = 0u;
     if (sd.n_pred) {
@@ -597,6 +663,14 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
             }
         }
         __syncwarp();
+        if (sd.ss != 0 && sd.ah == 0) {
+            uint32_t* fl = reinterpret_cast<uint32_t*>(s_rl); // (the refinement table's storage: a chain is one or the other)
+            for (int q = lane; q < 512; q += 32) {
+                const uint32_t e = s_tab[0].lut[q];
+                fl[q] = e ? first_entry(e >> 8, e & 0xFFu) : kRefSlow;
+            }
+            __syncwarp();
+        }
         if (sd.ss != 0 && sd.ah != 0) {
             for (int q = lane; q < 512; q += 32) {
                 const uint32_t e = s_tab[0].lut[q];
@@ -643,7 +717,7 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
         else if (sd.ss == 0)
             prog_dc_refine(b, sc, g, coef, m0, m1, lane, y);
         else if (sd.ah == 0)
-            prog_ac_first(b, tab[0], sc, g, coef, m0, m1, lane, err, y);
+            prog_ac_first(b, tab[0], reinterpret_cast<const uint32_t*>(s_rl), sc, g, coef, m0, m1, lane, err, y);
         else
             prog_ac_refine(b, tab[0], s_rl, sc, g, coef, m0, m1, uint32_t(lane), err, s_q, y);
         if (b.p > byte1 * 8u)
