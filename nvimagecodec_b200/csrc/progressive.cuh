@@ -467,12 +467,16 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
         uint32_t k = ss, j = 0;    // j: how many zero-history positions of the band lie before k
         if (eobrun == 0u) {
             __syncwarp();
-            if ((zlo >> lane) & 1u)
-                asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + uint32_t(__popc(zlo & below))), "r"(lane) : "memory");
-            if ((zhi >> lane) & 1u)
-                asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + n_zlo + uint32_t(__popc(zhi & below))), "r"(lane + 32u) : "memory");
-            if (lane < 16u) // "no such zero": a run that reaches past the last one stops behind the band
-                asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + n_z + lane), "r"(se + 1u + kBehind) : "memory");
+            // (predicated stores, no divergent branches)
+            asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q st.shared.u8 [%0], %1;\n\t}" ::"r"(q_addr + uint32_t(__popc(zlo & below))), "r"(lane),
+                         "r"((zlo >> lane) & 1u)
+                         : "memory");
+            asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q st.shared.u8 [%0], %1;\n\t}" ::"r"(q_addr + n_zlo + uint32_t(__popc(zhi & below))),
+                         "r"(lane + 32u), "r"((zhi >> lane) & 1u)
+                         : "memory");
+            // "no such zero": a run that reaches past the last one stops behind the band
+            asm volatile("{\n\t.reg .pred q;\n\tsetp.lt.u32 q, %2, 16;\n\t@q st.shared.u8 [%0], %1;\n\t}" ::"r"(q_addr + n_z + lane), "r"(se + 1u + kBehind), "r"(lane)
+                         : "memory");
             __syncwarp();
             uint32_t c = 0; // symbol bits of this block so far
             bool overrun = false;
@@ -587,24 +591,21 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
         }
         if (eobrun > 0u)
             --eobrun;
-        // correction bits, fetched where they lie
-        if (n_nz) {
-            if ((nzlo >> lane) & 1u) {
-                const uint32_t at = pstart + clo + uint32_t(__popc(nzlo & below));
-                if (((pb_word(b, at >> 5) >> (31u - (at & 31u))) & 1u) && (lo & p1) == 0)
-                    lo += lo >= 0 ? p1 : -p1;
-            }
-            if ((nzhi >> lane) & 1u) {
-                const uint32_t at = pstart + chi + uint32_t(__popc(nzlo)) + uint32_t(__popc(nzhi & below));
-                if (((pb_word(b, at >> 5) >> (31u - (at & 31u))) & 1u) && (hi & p1) == 0)
-                    hi += hi >= 0 ? p1 : -p1;
-            }
+        // correction bits, fetched where they lie -- straight-line code for every lane (a lone warp pays a divergent branch
+        // dearly): lanes without a non-zero-history coefficient read some word of the ring and select nothing
+        {
+            const uint32_t at_lo = pstart + clo + uint32_t(__popc(nzlo & below));
+            const uint32_t at_hi = pstart + chi + uint32_t(__popc(nzlo)) + uint32_t(__popc(nzhi & below));
+            const uint32_t bit_lo = (pb_word(b, at_lo >> 5) >> (31u - (at_lo & 31u))) & 1u;
+            const uint32_t bit_hi = (pb_word(b, at_hi >> 5) >> (31u - (at_hi & 31u))) & 1u;
+            const bool up_lo = ((nzlo >> lane) & bit_lo) != 0u && (lo & p1) == 0;
+            const bool up_hi = ((nzhi >> lane) & bit_hi) != 0u && (hi & p1) == 0;
+            lo = up_lo ? lo + (lo >= 0 ? p1 : -p1) : lo;
+            hi = up_hi ? hi + (hi >= 0 ? p1 : -p1) : hi;
         }
         // only what this scan changed is stored: other bands may be in other scans' hands
-        if (lo != lo0)
-            cur[lane] = int16_t(lo);
-        if (hi != hi0)
-            cur[lane + 32] = int16_t(hi);
+        asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %1, %2;\n\t@q st.global.u16 [%0], %1;\n\t}" ::"l"(cur + lane), "r"(lo), "r"(lo0) : "memory");
+        asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %1, %2;\n\t@q st.global.u16 [%0], %1;\n\t}" ::"l"(cur + lane + 32), "r"(hi), "r"(hi0) : "memory");
     }
     if (seen & kRefBad)
         err |= kFlagBadHuffman; // a new coefficient of more than one bit (libjpeg warns and goes on)
