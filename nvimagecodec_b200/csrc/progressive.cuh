@@ -439,6 +439,10 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
     for (uint32_t q = 64u + lane; q < 144u; q += 32u) // (the entries behind any list: what an EOB0's run of 64 reads)
         asm volatile("st.shared.u8 [%0], %1;" ::"r"(q_addr + q), "r"(se + 1u + kBehind) : "memory");
     uint32_t seen = 0; // every entry of the plain path, or-ed: the "bad" flag is looked at once, after the scan
+    // the window lives in registers for the whole scan: three words from word `base` on, the position o bits into them
+    // (o may run past them while correction bits are skipped; it is brought back at the top of every block)
+    (void)pb_peek(b);
+    uint32_t w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
     // the block after this one is requested while this one is worked on
     pmap_seek(g, m0);
     ps_need(y, min(m1, m0 + 1u));
@@ -462,7 +466,17 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
         const uint32_t n_zlo = uint32_t(__popc(zlo)), n_z = n_zlo + uint32_t(__popc(zhi));
         const uint32_t n_nz = uint32_t(__popc(nzlo) + __popc(nzhi));
         const int32_t lo0 = lo, hi0 = hi;
-        const uint32_t pstart = b.p;
+        if (o >= 32u) {
+            base += o >> 5;
+            o &= 31u;
+            pb_fill(b, base + kRingAhead); // the ring far enough ahead for the whole block
+            w0 = pb_word(b, base);
+            w1 = pb_word(b, base + 1u);
+            w2 = pb_word(b, base + 2u);
+        } else {
+            pb_fill(b, base + kRingAhead);
+        }
+        const uint32_t pstart = base * 32u + o;
         uint32_t clo = 0, chi = 0; // symbol bits read up to (and including) the symbol that passes this lane's positions
         uint32_t k = ss, j = 0;    // j: how many zero-history positions of the band lie before k
         if (eobrun == 0u) {
@@ -480,9 +494,6 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
             __syncwarp();
             uint32_t c = 0; // symbol bits of this block so far
             bool overrun = false;
-            (void)pb_peek(b);                // window registers brought to b.p,
-            pb_fill(b, b.base + kRingAhead); // and the ring far enough ahead for the whole block
-            uint32_t w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
 #pragma unroll 1
             for (;;) {
                 // ---- the common symbols: one pass of the inner loop each.  A lone warp issues an instruction every other
@@ -521,23 +532,20 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 }
                 j = min(j, n_z);
                 if (!slow) {
-                    if (k > se) {
-                        b.p = base * 32u + o;
-                        b.base = base;
-                        b.w0 = w0;
-                        b.w1 = w1;
-                        b.w2 = w2;
+                    if (k > se)
                         break;
-                    }
                     if (o < 64u) { // the window moves on by a word
                         ++base;
                         w0 = w1;
                         w1 = w2;
                         w2 = pb_word(b, base + 2u);
                         o -= 32u;
-                    } else {       // a longer run of correction bits was skipped
-                        pb_seek(b, base * 32u + o);
-                        w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
+                    } else {       // a longer run of correction bits was skipped (the ring reaches far enough)
+                        base += o >> 5;
+                        o &= 31u;
+                        w0 = pb_word(b, base);
+                        w1 = pb_word(b, base + 1u);
+                        w2 = pb_word(b, base + 2u);
                     }
                     continue;
                 }
@@ -556,6 +564,8 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 if (e & kRefEob) {
                     c += r;
                     eobrun = (1u << r) + pb_get(b, r);
+                    (void)pb_peek(b);
+                    w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
                     break; // the rest of the band: correction bits only
                 }
                 seen |= e;
@@ -574,20 +584,20 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 }
                 k = t + 1u;
                 j = min(idx + 1u, n_z);
-                if (k > se)
-                    break;
                 (void)pb_peek(b);
                 w0 = b.w0, w1 = b.w1, w2 = b.w2, base = b.base, o = b.p & 31u;
+                if (k > se)
+                    break;
             }
             if (overrun)
                 err |= kFlagOverrun;
             if (eobrun > 0u && k <= se) { // the band's tail behind an end-of-band symbol
                 clo = lane >= k ? c : clo;
                 chi = lane + 32u >= k ? c : chi;
-                b.p += (se + 1u - k) - (n_z - min(j, n_z));
+                o += (se + 1u - k) - (n_z - min(j, n_z));
             }
         } else {
-            b.p += n_nz; // a block inside an end-of-band run: correction bits only
+            o += n_nz; // a block inside an end-of-band run: correction bits only
         }
         if (eobrun > 0u)
             --eobrun;
@@ -607,6 +617,7 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
         asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %1, %2;\n\t@q st.global.u16 [%0], %1;\n\t}" ::"l"(cur + lane), "r"(lo), "r"(lo0) : "memory");
         asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %1, %2;\n\t@q st.global.u16 [%0], %1;\n\t}" ::"l"(cur + lane + 32), "r"(hi), "r"(hi0) : "memory");
     }
+    b.p = base * 32u + o;
     if (seen & kRefBad)
         err |= kFlagBadHuffman; // a new coefficient of more than one bit (libjpeg warns and goes on)
 }
