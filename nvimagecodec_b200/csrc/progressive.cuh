@@ -224,6 +224,10 @@ __device__ __forceinline__ void ps_publish(PSync& y, uint32_t m_done, bool force
         asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(y.mine), "r"(m_done) : "memory");
 }
 __device__ __forceinline__ int32_t pc_load(const int16_t* p) { return int32_t(__ldcg(p)); } // coefficients: L2, never this SM's L1
+__device__ __forceinline__ void pc_store_if(bool on, int16_t* p, int32_t v) // a predicated store: no divergent branch for one lane's sake
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\t@q st.global.u16 [%0], %1;\n\t}" ::"l"(p), "r"(v), "r"(uint32_t(on)) : "memory");
+}
 
 // ---- the four scan types.  Each decodes MCUs [m0, m1) of its scan; everything is warp-uniform except the stores.
 
@@ -261,8 +265,7 @@ __device__ __forceinline__ void prog_dc_first(PBits& b, const PTab* tab, const P
                 if (s > 15u)
                     err |= kFlagBadHuffman;
                 pred[i] += pb_extend(pb_get(b, s & 15u), s & 15u);
-                if (lane == 0)
-                    coef[size_t(blk) * 64] = int16_t(pred[i] << sc.al);
+                pc_store_if(lane == 0, coef + size_t(blk) * 64, pred[i] << sc.al);
             }
         }
     }
@@ -345,8 +348,7 @@ __device__ __forceinline__ void prog_ac_first(PBits& b, const PTab& tab, const u
                 const uint32_t raw = (win >> ((32u - total) & 31u)) & ((1u << s) - 1u);
                 const int32_t v = pb_extend(raw, s);
                 overrun = overrun || (s != 0u && k > se);
-                if (s != 0u && k <= se && lane == 0)
-                    cb[k] = int16_t(v << sc.al);
+                pc_store_if(s != 0u && k <= se && lane == 0, cb + min(k, 63u), v << sc.al);
                 ++k;
                 o += total;
             } while (k <= se && o < 32u);
@@ -371,11 +373,8 @@ __device__ __forceinline__ void prog_ac_first(PBits& b, const PTab& tab, const u
             if (s) {
                 k += r;
                 const int32_t v = pb_extend(pb_get(b, s), s);
-                if (k > se) {
-                    overrun = true;
-                } else if (lane == 0) {
-                    cb[k] = int16_t(v << sc.al);
-                }
+                overrun = overrun || k > se;
+                pc_store_if(k <= se && lane == 0, cb + min(k, 63u), v << sc.al);
                 ++k;
             } else if (r == 15u) {
                 k += 16u;
