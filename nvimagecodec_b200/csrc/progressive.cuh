@@ -520,10 +520,20 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                     const int32_t newv = (win & ey) ? p1 : -p1;
                     lo = (ey != 0u && lane == t) ? newv : lo; // (no lane owns a position behind the band)
                     hi = (ey != 0u && lane + 32u == t) ? newv : hi;
-                    o = (o + total - (k + zp)) + t; // += total + (positions passed that are not zero-history ones)
+                    uint32_t pre = o + total - (k + zp); // (known before t arrives: one addition is left behind the read)
+                    asm volatile("" : "+r"(pre));
+                    o = pre + t; // += total + (positions passed that are not zero-history ones)
                     k = t + 1u;
                     j += r + 1u;
                 } while (k <= se && o < 32u);
+                if (!slow && k <= se && o < 64u) { // the usual way out: the window moves on by a word
+                    ++base;
+                    w0 = w1;
+                    w1 = w2;
+                    w2 = pb_word(b, base + 2u);
+                    o -= 32u;
+                    continue;
+                }
                 if (!slow && (t & kBehind)) { // the band ended: take the mark out of the position again
                     o -= kBehind;
                     k -= kBehind;
@@ -533,19 +543,12 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 if (!slow) {
                     if (k > se)
                         break;
-                    if (o < 64u) { // the window moves on by a word
-                        ++base;
-                        w0 = w1;
-                        w1 = w2;
-                        w2 = pb_word(b, base + 2u);
-                        o -= 32u;
-                    } else {       // a longer run of correction bits was skipped (the ring reaches far enough)
-                        base += o >> 5;
-                        o &= 31u;
-                        w0 = pb_word(b, base);
-                        w1 = pb_word(b, base + 1u);
-                        w2 = pb_word(b, base + 2u);
-                    }
+                    // a run of correction bits longer than the window registers reach was skipped (the ring reaches far enough)
+                    base += o >> 5;
+                    o &= 31u;
+                    w0 = pb_word(b, base);
+                    w1 = pb_word(b, base + 1u);
+                    w2 = pb_word(b, base + 2u);
                     continue;
                 }
                 b.p = base * 32u + o; // (the plain path works on the reader itself)
