@@ -198,7 +198,7 @@ struct PSync {
 };
 __device__ __forceinline__ void ps_need(PSync& y, uint32_t m_excl) // the predecessor must have finished its MCUs below m_excl
 {
-    if (y.pred == nullptr || y.avail >= m_excl)
+    if (y.avail >= m_excl) // (no predecessor: avail is all ones)
         return;
     for (;;) { // relaxed polls (an acquire load empties this SM's L1 every time), one fence once the predecessor is far enough
         uint32_t v;
@@ -534,13 +534,11 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                     o -= 32u;
                     continue;
                 }
-                if (!slow && (t & kBehind)) { // the band ended: take the mark out of the position again
-                    o -= kBehind;
-                    k -= kBehind;
-                    overrun = overrun || ey != 0u; // a new coefficient with no place left for it
-                }
-                j = min(j, n_z);
                 if (!slow) {
+                    const uint32_t mark = t & kBehind; // the band ended behind its last position: take the mark out again
+                    o -= mark;
+                    k -= mark;
+                    overrun = overrun || (mark != 0u && ey != 0u); // a new coefficient with no place left for it
                     if (k > se)
                         break;
                     // a run of correction bits longer than the window registers reach was skipped (the ring reaches far enough)
@@ -551,6 +549,7 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                     w2 = pb_word(b, base + 2u);
                     continue;
                 }
+                j = min(j, n_z);
                 b.p = base * 32u + o; // (the plain path works on the reader itself)
                 b.base = base;
                 b.w0 = w0;
@@ -646,10 +645,11 @@ __global__ void __launch_bounds__(32) prog_scan_kernel(BatchDev bd)
     y.published = m0;
     y.one_writer = sd.ah == 0; // first scans (DC and AC) store through lane 0 only
     y.pred = nullptr;
-    y.avail = 0u;
+    y.avail = 0xFFFFFFFFu;
     if (sd.n_pred) {
         if (sd.pred_fine) { // same MCU order and restart interval: chain j follows chain j of the predecessor scan
             y.pred = bd.prog_progress + bd.prog_scan[sd.pred[0]].chain_off + j;
+            y.avail = 0u;
         } else {            // otherwise every predecessor scan has to be through
             for (uint32_t q = 0; q < sd.n_pred; ++q) {
                 const ProgScanDev& ps = bd.prog_scan[sd.pred[q]];
