@@ -502,6 +502,7 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                 // leaves it with the symbol not yet consumed.
                 bool slow = false;
                 uint32_t t, ey; // (looked at once more behind the loop)
+                int32_t lim = 0;
                 do {
                     const uint32_t win = __funnelshift_l(w1, w0, o);
                     uint32_t ex; // table entry: ex = bits consumed / run / flags, ey = the sign bit's place in the window
@@ -520,12 +521,13 @@ __device__ __forceinline__ void prog_ac_refine(PBits& b, const PTab& tab, const 
                     const int32_t newv = (win & ey) ? p1 : -p1;
                     lo = (ey != 0u && lane == t) ? newv : lo; // (no lane owns a position behind the band)
                     hi = (ey != 0u && lane + 32u == t) ? newv : hi;
-                    uint32_t pre = o + total - (k + zp); // (known before t arrives: one addition is left behind the read)
-                    asm volatile("" : "+r"(pre));
+                    uint32_t pre = o + total - (k + zp); // (known before t arrives: one addition is left behind the read,
+                    asm volatile("" : "+r"(pre));        //  and the loop test compares t itself)
+                    lim = 32 - int32_t(pre);
                     o = pre + t; // += total + (positions passed that are not zero-history ones)
                     k = t + 1u;
                     j += r + 1u;
-                } while (k <= se && o < 32u);
+                } while (int32_t(t) < lim && t < se); // i.e. o < 32 and k <= se
                 if (!slow && k <= se && o < 64u) { // the usual way out: the window moves on by a word
                     ++base;
                     w0 = w1;
