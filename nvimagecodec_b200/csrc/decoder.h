@@ -90,7 +90,7 @@ struct Options {
     bool entry_stream = true;     // K3 writes the coefficients as a stream of 16-bit entries (huff_emit) instead of dense 16-byte groups (huff_write)
     bool progressive = true;      // take progressive (SOF2) streams (progressive.cuh); off: they are declined and fall to the next decoder
     int progressive_min_batch = 1; // progressive streams are taken only in batches that hold at least this many of them (a lone
-                                   // progressive image decodes slower here than on a CPU core): fewer -> declined
+                                   // progressive image gains nothing here over a CPU core, and it holds back the batch it travels in): fewer -> declined
     bool fused_pixels = false;    // IDCT + upsampling + colour in one kernel (pixels_kernel); off: the idct and color kernels, which are faster as measured (profiles/)
     bool use_executor = false;    // (extension) fan host work out over the framework's executor instead of the decoder's own helper threads (measured: ~0.1 ms of dispatch latency per fan-out)
     bool sync_finish = false;     // Finish / DecodeBatch wait for the pixel kernels too, not only for the statuses
