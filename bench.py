@@ -726,6 +726,17 @@ def main():
                         dt, how = cpu_reference_decode(oj[:32], cores, 1)
                         others[-1]["cpu_reference_mpix_per_s"] = 32 * HEIGHT * WIDTH / 1e6 / dt
                         others[-1]["cpu_reference"] = f"32 of the streams x 1 pass on {cores} threads; {how}"
+                        if drv:  # the same streams through the framework call, and the reference's own CUDA decoder beside it
+                            pdrv = PluginDriver(oj, local)
+                            try:
+                                r = pdrv.run("device", opts, 3)
+                                others[-1]["plugin_device_out_mpix_per_s"] = r.get("mpix_per_s", r.get("error"))
+                                others[-1]["plugin_ok"] = r.get("ok")
+                                if os.path.exists(os.path.join(NVJPEG_EXT_DIR, "libnvjpeg_ext.so")):
+                                    r = pdrv.run("device", opts, 2, ext_dir=NVJPEG_EXT_DIR, backend="hybrid")
+                                    others[-1]["nvjpeg_cuda_decoder_mpix_per_s"] = r.get("mpix_per_s", r.get("error"))
+                            finally:
+                                pdrv.close()
                     del ob
                 except Exception as e:  # an extra must not take the headline down
                     others.append({"workload": wl_names[name], "error": repr(e)[:200]})
