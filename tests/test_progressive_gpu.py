@@ -153,3 +153,18 @@ def test_progressive_random_shapes_and_qualities(dec):
     assert dec.last_status == [_lib.OK] * len(srcs)
     for i, (s, o) in enumerate(zip(srcs, outs)):
         assert np.array_equal(o.cpu().numpy(), oracle.decode(s, oracle.FMT_I_RGB, fancy=True)), i
+
+
+def test_more_chains_than_the_gpu_holds(dec):
+    """Restart intervals cut every scan into chains; 400 small images make far more one-warp CTAs than are resident at once.
+    The launch must finish -- a chain's predecessor always has the lower CTA index -- and the pixels must match."""
+    from nvimagecodec_b200 import _lib, corpus
+
+    base = [corpus.encode(corpus.synth(96 + 8 * (k % 5), 128 + 16 * (k % 3), 7000 + k), 85, ("420", "444")[k % 2], rst_interval=1 + k % 3,
+                          progressive=True) for k in range(16)]
+    srcs = [base[i % len(base)] for i in range(400)]
+    outs = dec.decode(srcs, "I_RGB")
+    assert dec.last_status == [_lib.OK] * len(srcs)
+    refs = [oracle.decode(b) for b in base]
+    for i in range(0, len(srcs), 5):
+        assert np.array_equal(outs[i].cpu().numpy(), refs[i % len(base)]), i
