@@ -168,3 +168,37 @@ def test_more_chains_than_the_gpu_holds(dec):
     refs = [oracle.decode(b) for b in base]
     for i in range(0, len(srcs), 5):
         assert np.array_equal(outs[i].cpu().numpy(), refs[i % len(base)]), i
+
+
+def test_progressive_damaged_headers_tables_and_scans(dec):
+    """400 damaged progressive streams (bytes flipped anywhere incl. SOS parameters and Huffman tables, truncation, dropped
+    slices) in batches between pristine ones: whatever the verdicts, nothing crashes or hangs and the neighbours stay exact."""
+    from nvimagecodec_b200 import corpus
+
+    rng = np.random.default_rng(99)
+    seeds = [corpus.encode(corpus.synth(72 + 16 * k, 88 + 24 * k, 60 + k), 82, ("420", "444", "422")[k % 3], rst_interval=(0, 2, 5)[k % 3],
+                           progressive=True) for k in range(6)]
+    good = seeds[0]
+    ref = oracle.decode(good)
+    for b0 in range(0, 400, 100):
+        srcs = [good]
+        for it in range(b0, b0 + 100):
+            b = bytearray(seeds[it % len(seeds)])
+            kind = it % 4
+            if kind == 0:
+                for _ in range(1 + it % 5):
+                    b[int(rng.integers(2, len(b)))] = int(rng.integers(0, 256))
+            elif kind == 1:
+                marks = [i for i in range(len(b) - 1) if b[i] == 0xFF and b[i + 1] in (0xC2, 0xC4, 0xDA, 0xDB, 0xDD)]
+                m = marks[int(rng.integers(0, len(marks)))]
+                b[min(len(b) - 1, m + int(rng.integers(2, 24)))] = int(rng.integers(0, 256))
+            elif kind == 2:
+                b = b[:int(rng.integers(4, len(b)))]
+            else:
+                a = int(rng.integers(2, len(b) - 2))
+                del b[a:a + int(rng.integers(1, 64))]
+            srcs.append(bytes(b))
+        srcs.append(good)
+        outs = dec.decode(srcs, "I_RGB")
+        assert dec.last_status[0] == 0 and dec.last_status[-1] == 0
+        assert np.array_equal(outs[0].cpu().numpy(), ref) and np.array_equal(outs[-1].cpu().numpy(), ref)
